@@ -1,0 +1,258 @@
+// C entry points over the UNMODIFIED reference objects compiled by oracle/Makefile from
+// /root/reference (CachedInterpolation.cc, CachedForwardInterpolation.cc, interpolation.c, ...).
+// TEST INFRASTRUCTURE: used to pin oracle/fimex_oracle.c and as the "reference" CPU baseline.
+// The mifi_* C functions of src/interpolation.c are exported by the same library as they are.
+#include "CachedForwardInterpolation.h"
+#include "fimex/CachedInterpolation.h"
+#include "fimex/FindNeighborElements.h"
+#include "fimex/MathUtils.h"
+#include "fimex/SharedArray.h"
+#include "fimex/interpolation.h"
+#include "fimex/reproject.h"
+#include "leap_iterator.h"
+#include "nanoflann/nanoflann.hpp"
+
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+using namespace MetNoFimex;
+
+namespace {
+struct RefCache {
+    CachedInterpolationInterface_p ci;
+};
+
+shared_array<double> clone_table(const double* p, size_t n)
+{
+    auto a = make_shared_array<double>(n ? n : 1);
+    std::memcpy(a.get(), p, n * sizeof(double));
+    return a;
+}
+
+shared_array<float> borrow(const float* p)
+{
+    // interpolateValues() only reads its input; a non-owning handle avoids timing a copy
+    return shared_array<float>(const_cast<float*>(p), [](float*) {});
+}
+} // namespace
+
+// The call sequence of flannTranslatePointsToClosestInputCell (CDMInterpolator.cc:953-1028) on the
+// reference's vendored nanoflann (that function sits in an anonymous namespace of a translation unit
+// that cannot be linked here, so the few lines that drive nanoflann are re-stated; the kd-tree, its
+// traversal order and the result sort are the reference's own code).
+namespace {
+struct Cloud {
+    struct P { double x, y, z; };
+    std::vector<P> pts;
+    size_t kdtree_get_point_count() const { return pts.size(); }
+    double kdtree_distance(const double* p1, const size_t idx, size_t) const
+    {
+        const double d0 = p1[0] - pts[idx].x, d1 = p1[1] - pts[idx].y, d2 = p1[2] - pts[idx].z;
+        return d0 * d0 + d1 * d1 + d2 * d2;
+    }
+    double kdtree_get_pt(const size_t idx, int dim) const { return dim == 0 ? pts[idx].x : (dim == 1 ? pts[idx].y : pts[idx].z); }
+    template <class BBOX> bool kdtree_get_bbox(BBOX&) const { return false; }
+};
+} // namespace
+
+extern "C" {
+
+int ref_num_threads(void)
+{
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+void ref_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
+// createCachedInterpolation (CachedInterpolation.cc:132-147) or the forward cache ctor for method >= FORWARD_SUM
+void* ref_cache_create(int method, const double* px, const double* py, size_t inX, size_t inY, size_t outX, size_t outY)
+{
+    try {
+        auto c = std::make_unique<RefCache>();
+        if (method >= MIFI_INTERPOL_FORWARD_SUM) {
+            c->ci = std::make_shared<CachedForwardInterpolation>("x", "y", method, clone_table(px, inX * inY), clone_table(py, inX * inY), inX, inY, outX, outY);
+        } else {
+            c->ci = createCachedInterpolation("x", "y", method, clone_table(px, outX * outY), clone_table(py, outX * outY), inX, inY, outX, outY);
+        }
+        return c.release();
+    } catch (...) {
+        return nullptr;
+    }
+}
+
+void ref_cache_info(void* h, size_t* inX, size_t* inY, size_t* outX, size_t* outY, int* reduced, size_t* xMin, size_t* yMin)
+{
+    auto* c = static_cast<RefCache*>(h);
+    *inX = c->ci->getInX();
+    *inY = c->ci->getInY();
+    *outX = c->ci->getOutX();
+    *outY = c->ci->getOutY();
+    auto rd = c->ci->reducedDomain();
+    *reduced = rd ? 1 : 0;
+    *xMin = rd ? rd->xMin : 0;
+    *yMin = rd ? rd->yMin : 0;
+}
+
+int ref_cache_apply(void* h, const float* in, size_t size, float* out)
+{
+    auto* c = static_cast<RefCache*>(h);
+    try {
+        size_t newSize = 0;
+        auto r = c->ci->interpolateValues(borrow(in), size, newSize);
+        std::memcpy(out, r.get(), newSize * sizeof(float));
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
+// time `reps` calls of interpolateValues (allocation of the result included, as in the reference; no copy-out)
+double ref_cache_apply_seconds(void* h, const float* in, size_t size, int reps)
+{
+    auto* c = static_cast<RefCache*>(h);
+    auto input = borrow(in);
+    size_t newSize = 0;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int r = 0; r < reps; ++r) {
+        auto res = c->ci->interpolateValues(input, size, newSize);
+        if (!res)
+            return -1;
+    }
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+void ref_cache_destroy(void* h) { delete static_cast<RefCache*>(h); }
+
+size_t ref_round_and_clamp(double d, size_t mini, size_t maxi, size_t invalid) { return RoundAndClamp(mini, maxi, invalid)(d); }
+
+// FindNeighborElements.h instantiated exactly as CDMVerticalInterpolator.cc:529-533 does
+void ref_find_closest_neighbor_distinct_elements(const float* col, size_t n, long stride, double x, long* first, long* second)
+{
+    const leap_iterator<const float*> b(col, stride);
+    const leap_iterator<const float*> e = b + n;
+    const auto pos = find_closest_neighbor_distinct_elements(b, e, x);
+    *first = pos.first;
+    *second = pos.second;
+}
+
+void ref_find_closest_distinct_elements(const float* col, size_t n, long stride, double x, long* first, long* second)
+{
+    const leap_iterator<const float*> b(col, stride);
+    const leap_iterator<const float*> e = b + n;
+    const auto pos = find_closest_distinct_elements(b, e, x);
+    *first = pos.first;
+    *second = pos.second;
+}
+
+int ref_kdtree_translate(double maxDist_m, double* pointsOnX_deg, double* pointsOnY_deg, size_t nPoints, const double* lon_deg, const double* lat_deg,
+                         size_t nx, size_t ny)
+{
+    using namespace nanoflann;
+    double maxDist = maxDist_m / 6371000.;
+    Cloud cloud;
+    cloud.pts.resize(nx * ny);
+    for (size_t pos = 0; pos < nx * ny; ++pos) {
+        if (!(std::isnan(lat_deg[pos]) || std::isnan(lon_deg[pos]))) {
+            const double la = deg_to_rad(lat_deg[pos]), lo = deg_to_rad(lon_deg[pos]);
+            cloud.pts[pos] = {std::cos(la) * std::cos(lo), std::cos(la) * std::sin(lo), std::sin(la)};
+        } else {
+            const double nan = std::numeric_limits<double>::quiet_NaN();
+            cloud.pts[pos] = {nan, nan, nan};
+        }
+    }
+    typedef KDTreeSingleIndexAdaptor<L2_Simple_Adaptor<double, Cloud>, Cloud, 3> tree_t;
+    tree_t index(3, cloud, KDTreeSingleIndexAdaptorParams(12));
+    index.buildIndex();
+    const double r2 = maxDist * maxDist;
+    SearchParams params;
+    params.sorted = true;
+    for (size_t i = 0; i < nPoints; ++i) {
+        const double la = deg_to_rad(pointsOnY_deg[i]), lo = deg_to_rad(pointsOnX_deg[i]);
+        const double q[3] = {std::cos(la) * std::cos(lo), std::cos(la) * std::sin(lo), std::sin(la)};
+        std::vector<std::pair<size_t, double>> matches;
+        const size_t n = index.radiusSearch(q, r2, matches, params);
+        if (n > 0) {
+            const size_t pos = matches.at(0).first;
+            pointsOnX_deg[i] = pos % nx;
+            pointsOnY_deg[i] = pos / nx;
+        } else {
+            pointsOnX_deg[i] = -1000;
+            pointsOnY_deg[i] = -1000;
+        }
+    }
+    return 0;
+}
+
+// ---- src/reproject.cc driven through its public functions (PROJ replaced by ref_shim/proj.h) ----
+int ref_reproject_axes(const char* proj_in, const char* proj_out, const double* in_x, const double* in_y, int ix, int iy, double* out_x, double* out_y)
+{
+    try {
+        reproject::reproject_axes(proj_in, proj_out, in_x, in_y, ix, iy, out_x, out_y);
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
+int ref_get_vector_reproject_matrix(const char* proj_in, const char* proj_out, const double* out_x_axis, const double* out_y_axis, int ox, int oy,
+                                    double* matrix3)
+{
+    try {
+        auto m = reproject::get_vector_reproject_matrix(proj_in, proj_out, out_x_axis, out_y_axis, MIFI_PROJ_AXIS, MIFI_PROJ_AXIS, ox, oy);
+        std::memcpy(matrix3, m->mtx(), sizeof(double) * 3 * ox * oy);
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
+namespace {
+reproject::Matrix_cp borrow_matrix(const double* matrix3, int ox, int oy)
+{
+    auto m = std::make_shared<reproject::Matrix>(ox, oy);
+    std::memcpy(m->mtx(), matrix3, sizeof(double) * 3 * ox * oy);
+    return m;
+}
+} // namespace
+
+void ref_vector_reproject_values_by_matrix_f(const double* matrix3, int ox, int oy, float* u, float* v, int oz)
+{
+    reproject::vector_reproject_values_by_matrix_f(borrow_matrix(matrix3, ox, oy), u, v, oz);
+}
+
+void ref_vector_reproject_direction_by_matrix_f(const double* matrix3, int ox, int oy, float* angle, int oz)
+{
+    reproject::vector_reproject_direction_by_matrix_f(borrow_matrix(matrix3, ox, oy), angle, oz);
+}
+
+int ref_reproject_f(int method, const char* proj_in, const float* infield, const double* in_x_axis, const double* in_y_axis, int in_x_type, int in_y_type,
+                    int ix, int iy, int iz, const char* proj_out, float* outfield, const double* out_x_axis, const double* out_y_axis, int out_x_type,
+                    int out_y_type, int ox, int oy)
+{
+    try {
+        reproject::reproject_f(method, proj_in, infield, in_x_axis, in_y_axis, in_x_type, in_y_type, ix, iy, iz, proj_out, outfield, out_x_axis,
+                               out_y_axis, out_x_type, out_y_type, ox, oy);
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
+} // extern "C"
