@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""bench.py -- cached bilinear regridding of the synthetic MEPS field (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--target T1|T2]
+
+One step = one pass of the hot path over one time-step slab: source [65][1069][949] f32 (Lambert, 2.5 km)
+-> target T1 [65][1021][2891] f32 (0.025 degree lat/lon), i.e. 191.9 M regridded points, through
+fimexcu_cache_apply_dev_f (one kernel launch) with the slab resident in HBM.  With N GPUs (torchrun, one
+process per GPU) every rank regrids its own slabs: the time/level/ensemble slabs are independent, so the
+path shards without any collective and the scaling is "weak".  Timed with CUDA events on the launching
+stream, barrier + synchronize on both sides, max over ranks.
+
+Prints ONE JSON line (rank 0).  Extra objects:
+  roofline      algorithmic bytes per launch (4 + 4*N_in'/N_out + 16/nz bytes per point) over the
+                mean launch duration, against the measured HBM copy bandwidth of MEASURED_PEAKS.json
+  cpu_baseline  the reference's own CPU code (oracle/_ref, OpenMP, all host cores) on a bounded sample
+  e2e           same metric through the host-pointer C ABI call (pinned host buffers; H2D and D2H inside)
+`--impl reference` times only the reference CPU implementation (oracle/_ref, else the oracle port).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "regridded Gpoints/s (cached bilinear, whole job)"
+UNIT = "Gpoints/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--target", default="T1", choices=["T1", "T2"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def workload(target):
+    from fimex_b200 import synthetic as S
+    px, py, ox, oy = S.meps_index_tables(target)
+    return S, px, py, ox, oy
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def cpu_reference(px, py, S, ox, oy, budget_s=12.0, max_levels=None):
+    """Times CachedInterpolation::interpolateValues of the reference (oracle/_ref, built with OpenMP = the reference's
+    ENABLE_FIMEX_OMP) on a bounded number of levels of the same slab.  Falls back to the scalar oracle port."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    lib = ol.ref(omp=True) or ol.ref(omp=False)
+    cores = os.cpu_count() or 1
+    if lib is not None:
+        kind = "reference"
+        lib.ref_set_num_threads(cores)
+        threads = lib.ref_num_threads()
+        h = lib.ref_cache_create(ol.BILINEAR, ol.dp(px.ravel()), ol.dp(py.ravel()), S.MEPS_NX, S.MEPS_NY, ox, oy)
+        import ctypes as C
+        v = [C.c_size_t() for _ in range(4)]
+        red, xm, ym = C.c_int(), C.c_size_t(), C.c_size_t()
+        lib.ref_cache_info(h, *[C.byref(t) for t in v], C.byref(red), C.byref(xm), C.byref(ym))
+        inx, iny = v[0].value, v[1].value
+
+        fields = {}
+
+        def run(levels, reps):
+            if levels not in fields:
+                fields.clear()
+                fields[levels] = S.meps_slab_numpy(t=0, nz=levels)[:, ym.value:ym.value + iny, xm.value:xm.value + inx].copy()
+            fld = fields[levels]
+            return lib.ref_cache_apply_seconds(h, ol.fp(fld), fld.size, reps) / reps
+    else:
+        kind, threads = "port", 1
+        o = ol.oracle()
+        h = o.orc_cached_interp_create(ol.BILINEAR, ol.dp(px.ravel()), ol.dp(py.ravel()), S.MEPS_NX, S.MEPS_NY, ox, oy)
+        c = h.contents
+
+        fields = {}
+
+        def run(levels, reps):
+            if levels not in fields:
+                fields.clear()
+                fields[levels] = S.meps_slab_numpy(t=0, nz=levels)[:, c.yMin:c.yMin + c.inY, c.xMin:c.xMin + c.inX].copy()
+            fld = fields[levels]
+            out = np.empty((levels, oy, ox), np.float32)
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                o.orc_cached_interp_apply(h, ol.fp(fld), fld.size, ol.fp(out))
+            return (time.perf_counter() - t0) / reps
+    t1 = run(1, 1)  # calibration: one level
+    levels = int(max(1, min(S.MEPS_NZ if max_levels is None else max_levels, budget_s / 2 / max(t1, 1e-4))))
+    return dict(run=run, levels=levels, kind=kind, threads=threads, t_level=t1)
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    S, px, py, ox, oy = workload(args.target)
+    ref = cpu_reference(px, py, S, ox, oy, budget_s=2.0)
+    levels = ref["levels"]
+    pts = levels * ox * oy
+    for _ in range(args.warmup):
+        ref["run"](levels, 1)
+    dt = sum(ref["run"](levels, 1) for _ in range(args.steps)) / args.steps  # seconds inside interpolateValues
+    value = pts / dt / 1e9
+    sample = f"{levels} of {S.MEPS_NZ} levels of one S->{args.target} slab per step ({pts / 1e6:.1f} Mpoints), {ref['threads']} OpenMP threads"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"MEPS S(949x1069x65) -> {args.target} ({ox}x{oy}) cached bilinear, reference CPU path on host cores",
+                   "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": ref["threads"], "kind": ref["kind"], "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def main_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import fimex_b200
+    from fimex_b200 import _lib
+    lib = fimex_b200.lib
+
+    S, px, py, ox, oy = workload(args.target)
+    nz = S.MEPS_NZ
+    ci = fimex_b200.CachedInterpolation("x", "y", 1, px, py, S.MEPS_NX, S.MEPS_NY, ox, oy)
+    inx, iny = ci.getInX(), ci.getInY()
+    rd = ci.reducedDomain()
+    n_slabs = 3  # distinct resident inputs, rotated: every step reads 264 MB and writes 767 MB, both far beyond the 126 MB L2
+    slabs = []
+    for k in range(n_slabs):
+        full = S.meps_slab_torch(t=rank * 1000 + k, device="cuda")
+        slabs.append(ci.reduceInput(full, S.MEPS_NX, S.MEPS_NY) if rd else full)
+        del full
+    outs = [torch.empty((nz, oy, ox), dtype=torch.float32, device="cuda") for _ in range(2)]
+    stream = _lib.current_stream_ptr()
+    points_per_step = nz * ox * oy
+    launches = 0
+
+    def step(i):
+        _lib.check(lib.fimexcu_cache_apply_dev_f(ci._h, slabs[i % n_slabs].data_ptr(), nz, outs[i % 2].data_ptr(), float("nan"), float("nan"),
+                                                 stream), "apply")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for i in range(args.steps):
+        step(i)
+    ev1.record()
+    barrier()
+    launches += args.steps
+    ms_total = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = world * points_per_step / (ms_step * 1e-3) / 1e9
+
+    # roofline of the dominant (only) kernel of the step
+    alg_bytes = S.bilinear_algorithmic_bytes(inx * iny, ox * oy, nz)
+    peak, peak_src = peaks()
+    my_ms = ms_total / args.steps  # this rank's mean launch duration (one launch per step)
+    achieved = alg_bytes / (my_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "kernel": "fxcu::bilinear_apply_kernel", "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
+                "bytes_per_point": alg_bytes / points_per_step}
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get("bilinear_apply_kernel_dram_bytes_per_launch")
+        except Exception:
+            pass
+
+    # end to end through the host-pointer entry point: pinned host slab in, pinned host result out
+    e2e = None
+    if not args.no_e2e:
+        in_bytes, out_bytes = slabs[0].numel() * 4, points_per_step * 4
+        h_in = lib.fimexcu_host_alloc(in_bytes)
+        h_out = lib.fimexcu_host_alloc(out_bytes)
+        if not h_in or not h_out:
+            raise RuntimeError("pinned allocation failed: " + _lib.last_error())
+        _lib.check(lib.fimexcu_memcpy_d2h(h_in, slabs[0].data_ptr(), in_bytes), "d2h")
+        import ctypes as C
+        new_size = C.c_size_t()
+        e2e_steps = max(2, min(args.steps, 6))
+
+        def e2e_step():
+            _lib.check(lib.fimexcu_cache_apply_f(ci._h, h_in, slabs[0].numel(), h_out, C.byref(new_size), float("nan"), float("nan")), "apply_f")
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        dt = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        chunks = 8
+        launches += (e2e_steps + 1) * chunks
+        e2e = {"value": world * points_per_step / float(dt.item()) / 1e9, "unit": UNIT, "h2d_bytes_per_step": in_bytes,
+               "d2h_bytes_per_step": out_bytes, "ms_per_step": float(dt.item()) * 1e3,
+               "call": "fimexcu_cache_apply_f (host pointers, pinned; H2D + kernel + D2H pipelined over level chunks)"}
+        lib.fimexcu_host_free(h_in)
+        lib.fimexcu_host_free(h_out)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            ref = cpu_reference(px, py, S, ox, oy, budget_s=12.0)
+            levels = ref["levels"]
+            reps = 2 if ref["t_level"] * levels < 6 else 1
+            dt = ref["run"](levels, reps)
+            cpu = {"value": levels * ox * oy / dt / 1e9, "unit": UNIT, "cores": ref["threads"], "kind": ref["kind"],
+                   "sample": f"{levels} of {nz} levels of one S->{args.target} slab x{reps} "
+                             f"(CachedInterpolation::interpolateValues, {ref['threads']} OpenMP threads)"}
+        except Exception as exc:  # the checker is optional on the GPU box; the GPU numbers stand on their own
+            cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": str(exc)[:200]}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "per_gpu": value / world,
+            "config": {"workload": f"BASELINE configs[1]: synthetic MEPS Lambert 949x1069 x 65 levels f32 -> {args.target} 0.025deg lat/lon "
+                                   f"({ox}x{oy}), cached bilinear, one time-step slab ({points_per_step / 1e6:.1f} Mpoints) per step per GPU",
+                       "reduced_source_window": [inx, iny], "sharding": f"independent time-step slabs, {world} rank(s), no collective",
+                       "l2": "inputs larger than L2: 3 rotating 264 MB source slabs, 767 MB written per step (L2 126 MB)"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    sys.exit(main_reference(a) if a.impl == "reference" else main_b200(a))

@@ -1,0 +1,23 @@
+// fxcu_handles.h -- the opaque handle types of include/fimexcu.h.
+#pragma once
+#include "fxcu_common.h"
+
+namespace fxcu {
+enum CacheKind { KIND_BILINEAR = 0, KIND_BICUBIC = 1, KIND_NN = 2 };
+}
+
+struct fimexcu_cache {
+    int method = 0;
+    int kind = 0;
+    int device = 0;
+    size_t inX = 0, inY = 0, outX = 0, outY = 0; // inX/inY: the (possibly reduced) source window
+    bool reduced = false;
+    size_t xMin = 0, yMin = 0;
+    fxcu::DevBuf off;    // int32 [outX*outY]
+    fxcu::DevBuf wx, wy; // f32 (bilinear) or f64 (bicubic) [outX*outY]
+};
+
+struct fimexcu_vecrot {
+    size_t ox = 0, oy = 0;
+    fxcu::DevBuf c, s, deg; // f64 [ox*oy] each: cos, sin, angle in degree
+};

@@ -1,0 +1,213 @@
+// fxcu_vecrot.cu -- wind-vector rotation by a cached per-cell matrix (K7) and the fused
+// "interpolate u and v, then rotate" pass that replaces the vector branch of CDMInterpolator::getDataSlice.
+//
+// Reference behaviour restated here (fimex 2.4.1):
+//   CachedVectorReprojection                 src/CachedVectorReprojection.cc:37-54
+//   vector_reproject_values_by_matrix_f      src/reproject.cc:488-507   (f64 products and sums, rounded one by one)
+//   vector_reproject_direction_by_matrix_f   src/reproject.cc:509-530
+//   reproject::Matrix (stride 3: cos, sin, angle in degree)   include/fimex/reproject.h:34-46
+//
+// HBM layout: the matrix is split into three f64 planes (cos, sin, degree) of ox*oy entries so that a warp reads
+// 256 contiguous bytes per plane; u, v are [nz][oy][ox] f32 rotated in place.
+#include "fxcu_handles.h"
+
+#include <memory>
+
+namespace fxcu {
+
+__global__ void __launch_bounds__(256) split_matrix_kernel(const double* __restrict__ m3, size_t n, double* __restrict__ c, double* __restrict__ s,
+                                                           double* __restrict__ deg)
+{
+    const size_t i = blockIdx.x * 256ull + threadIdx.x;
+    if (i >= n)
+        return;
+    c[i] = m3[3 * i];
+    s[i] = m3[3 * i + 1];
+    deg[i] = m3[3 * i + 2];
+}
+
+__device__ __forceinline__ void rotate_uv(float u, float v, double c, double s, float& ur, float& vr)
+{
+    const double du = static_cast<double>(u), dv = static_cast<double>(v);
+    ur = __double2float_rn(__dsub_rn(__dmul_rn(du, c), __dmul_rn(dv, s)));
+    vr = __double2float_rn(__dadd_rn(__dmul_rn(du, s), __dmul_rn(dv, c)));
+}
+
+__global__ void __launch_bounds__(256) rotate_kernel(const double* __restrict__ cs, const double* __restrict__ sn, float* __restrict__ u,
+                                                     float* __restrict__ v, size_t layer, int nz, int zchunk)
+{
+    const size_t i = blockIdx.x * 256ull + threadIdx.x;
+    if (i >= layer)
+        return;
+    const int z0 = blockIdx.y * zchunk, z1 = min(nz, z0 + zchunk);
+    const double c = cs[i], s = sn[i];
+    float* pu = u + static_cast<size_t>(z0) * layer + i;
+    float* pv = v + static_cast<size_t>(z0) * layer + i;
+#pragma unroll 4
+    for (int z = z0; z < z1; ++z, pu += layer, pv += layer) {
+        float ur, vr;
+        rotate_uv(*pu, *pv, c, s, ur, vr);
+        __stcs(pu, ur);
+        __stcs(pv, vr);
+    }
+}
+
+__global__ void __launch_bounds__(256) direction_kernel(const double* __restrict__ deg, float* __restrict__ ang, size_t layer, int nz, int zchunk)
+{
+    const size_t i = blockIdx.x * 256ull + threadIdx.x;
+    if (i >= layer)
+        return;
+    const int z0 = blockIdx.y * zchunk, z1 = min(nz, z0 + zchunk);
+    const double rot = deg[i];
+    float* p = ang + static_cast<size_t>(z0) * layer + i;
+#pragma unroll 4
+    for (int z = z0; z < z1; ++z, p += layer) {
+        double a = __dsub_rn(static_cast<double>(*p), rot);
+        if (a < 0)
+            a = __dadd_rn(a, 360.);
+        if (a > 360)
+            a = __dsub_rn(a, 360.);
+        __stcs(p, __double2float_rn(a));
+    }
+}
+
+static int zchunk_for(size_t layer, int nz)
+{
+    const size_t blocks_xy = (layer + 255) / 256;
+    const size_t want = static_cast<size_t>(sm_count()) * 16;
+    if (blocks_xy >= want || nz <= 1)
+        return nz;
+    size_t chunks = std::min<size_t>((want + blocks_xy - 1) / blocks_xy, static_cast<size_t>(nz));
+    return static_cast<int>((nz + chunks - 1) / chunks);
+}
+
+static fimexcu_vecrot* vecrot_build(const double* d_m3, size_t ox, size_t oy, cudaStream_t st)
+{
+    std::unique_ptr<fimexcu_vecrot> r(new fimexcu_vecrot());
+    r->ox = ox;
+    r->oy = oy;
+    const size_t n = ox * oy;
+    if (!r->c.alloc_sync(n * sizeof(double)) || !r->s.alloc_sync(n * sizeof(double)) || !r->deg.alloc_sync(n * sizeof(double)))
+        return nullptr;
+    if (n) {
+        split_matrix_kernel<<<blocks_for(n, 256), 256, 0, st>>>(d_m3, n, r->c.as<double>(), r->s.as<double>(), r->deg.as<double>());
+        FXCU_CUDA_NULL(cudaGetLastError());
+        FXCU_CUDA_NULL(cudaStreamSynchronize(st));
+    }
+    return r.release();
+}
+
+} // namespace fxcu
+
+using namespace fxcu;
+
+extern "C" {
+
+fimexcu_vecrot* fimexcu_vecrot_create_dev(const double* d_matrix3, size_t ox, size_t oy, void* stream)
+{
+    clear_error();
+    if (!require_device())
+        return nullptr;
+    return vecrot_build(d_matrix3, ox, oy, as_stream(stream));
+}
+
+fimexcu_vecrot* fimexcu_vecrot_create(const double* matrix3, size_t ox, size_t oy)
+{
+    clear_error();
+    if (!require_device())
+        return nullptr;
+    DevBuf m;
+    const size_t bytes = ox * oy * 3 * sizeof(double);
+    if (!m.alloc_sync(bytes))
+        return nullptr;
+    FXCU_CUDA_NULL(cudaMemcpy(m.p, matrix3, bytes, cudaMemcpyHostToDevice));
+    return vecrot_build(m.as<double>(), ox, oy, nullptr);
+}
+
+int fimexcu_vecrot_apply_dev_f(const fimexcu_vecrot* r, float* d_u, float* d_v, size_t nz, void* stream)
+{
+    clear_error();
+    if (!r)
+        FXCU_FAIL("fimexcu_vecrot_apply: null handle");
+    const size_t layer = r->ox * r->oy;
+    if (layer == 0 || nz == 0)
+        return FIMEXCU_OK;
+    const int inz = static_cast<int>(nz);
+    const int zc = zchunk_for(layer, inz);
+    const dim3 grid(blocks_for(layer, 256), (inz + zc - 1) / zc);
+    rotate_kernel<<<grid, 256, 0, as_stream(stream)>>>(r->c.as<double>(), r->s.as<double>(), d_u, d_v, layer, inz, zc);
+    FXCU_CUDA(cudaGetLastError());
+    return FIMEXCU_OK;
+}
+
+int fimexcu_vecrot_apply_f(const fimexcu_vecrot* r, float* u, float* v, size_t size)
+{
+    clear_error();
+    if (!r)
+        FXCU_FAIL("fimexcu_vecrot_apply: null handle");
+    if (!require_device())
+        return FIMEXCU_ERROR;
+    const size_t layer = r->ox * r->oy;
+    if (layer == 0)
+        return FIMEXCU_OK;
+    const size_t nz = size / layer; // CachedVectorReprojection.cc:46
+    if (nz == 0)
+        return FIMEXCU_OK;
+    const size_t bytes = nz * layer * sizeof(float);
+    DevBuf du, dv;
+    if (!du.alloc(bytes, nullptr) || !dv.alloc(bytes, nullptr))
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(du.p, u, bytes, cudaMemcpyHostToDevice, nullptr));
+    FXCU_CUDA(cudaMemcpyAsync(dv.p, v, bytes, cudaMemcpyHostToDevice, nullptr));
+    if (fimexcu_vecrot_apply_dev_f(r, du.as<float>(), dv.as<float>(), nz, nullptr) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(u, du.p, bytes, cudaMemcpyDeviceToHost, nullptr));
+    FXCU_CUDA(cudaMemcpyAsync(v, dv.p, bytes, cudaMemcpyDeviceToHost, nullptr));
+    FXCU_CUDA(cudaStreamSynchronize(nullptr));
+    return FIMEXCU_OK;
+}
+
+int fimexcu_vecrot_direction_dev_f(const fimexcu_vecrot* r, float* d_angles, size_t nz, void* stream)
+{
+    clear_error();
+    if (!r)
+        FXCU_FAIL("fimexcu_vecrot_direction: null handle");
+    const size_t layer = r->ox * r->oy;
+    if (layer == 0 || nz == 0)
+        return FIMEXCU_OK;
+    const int inz = static_cast<int>(nz);
+    const int zc = zchunk_for(layer, inz);
+    const dim3 grid(blocks_for(layer, 256), (inz + zc - 1) / zc);
+    direction_kernel<<<grid, 256, 0, as_stream(stream)>>>(r->deg.as<double>(), d_angles, layer, inz, zc);
+    FXCU_CUDA(cudaGetLastError());
+    return FIMEXCU_OK;
+}
+
+int fimexcu_vecrot_direction_f(const fimexcu_vecrot* r, float* angles, size_t size)
+{
+    clear_error();
+    if (!r)
+        FXCU_FAIL("fimexcu_vecrot_direction: null handle");
+    if (!require_device())
+        return FIMEXCU_ERROR;
+    const size_t layer = r->ox * r->oy;
+    if (layer == 0)
+        return FIMEXCU_OK;
+    const size_t nz = size / layer;
+    if (nz == 0)
+        return FIMEXCU_OK;
+    const size_t bytes = nz * layer * sizeof(float);
+    DevBuf d;
+    if (!d.alloc(bytes, nullptr))
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(d.p, angles, bytes, cudaMemcpyHostToDevice, nullptr));
+    if (fimexcu_vecrot_direction_dev_f(r, d.as<float>(), nz, nullptr) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(angles, d.p, bytes, cudaMemcpyDeviceToHost, nullptr));
+    FXCU_CUDA(cudaStreamSynchronize(nullptr));
+    return FIMEXCU_OK;
+}
+
+void fimexcu_vecrot_destroy(fimexcu_vecrot* r) { delete r; }
+
+} // extern "C"

@@ -1,0 +1,255 @@
+/*
+ * fimexcu.h -- C ABI of libfimexcu.so: the fimex regridding hot path on B200 (sm_100a).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, opaque handles, int status codes; no C++,
+ * torch or CUDA types.  Every entry point names the reference interface it replaces
+ * (fimex 2.4.1, paths relative to the reference tree).  INTEGRATION.md shows the few lines a fimex
+ * maintainer adds on the reference side to bind them.
+ *
+ * Conventions
+ *   - status: FIMEXCU_OK (1, == MIFI_OK) or FIMEXCU_ERROR (-1, == MIFI_ERROR, mifi_constants.h:259-261);
+ *     creators return NULL on error.  fimexcu_last_error() gives the message for the calling thread.
+ *   - fields are C-order [z][y][x], x fastest (mifi_3d_array_pos, interpolation.c:229-233), raw f32
+ *     values with NaN = undefined; z = product of all non-horizontal dimensions of the slab.
+ *   - "_dev" entry points take DEVICE pointers of the current CUDA device and an optional stream
+ *     (a cudaStream_t passed as void*, NULL = default stream); they enqueue and return.
+ *     The others take HOST pointers, copy in and out, and return when the result is in the output.
+ *   - handles are immutable after creation and may be used from several host threads at once.
+ *   - there is NO CPU fallback: every call fails with FIMEXCU_ERROR when no sm_100 device is usable.
+ */
+#ifndef FIMEXCU_H
+#define FIMEXCU_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FIMEXCU_OK 1
+#define FIMEXCU_ERROR (-1)
+
+/* interpolation methods: enum mifi_interpol_method, include/fimex/mifi_constants.h:52-138 */
+enum fimexcu_interpol_method {
+    FIMEXCU_INTERPOL_NEAREST_NEIGHBOR = 0,
+    FIMEXCU_INTERPOL_BILINEAR = 1,
+    FIMEXCU_INTERPOL_BICUBIC = 2,
+    FIMEXCU_INTERPOL_COORD_NN = 3,
+    FIMEXCU_INTERPOL_COORD_NN_KD = 4,
+    FIMEXCU_INTERPOL_FORWARD_SUM = 5,
+    FIMEXCU_INTERPOL_FORWARD_MEAN = 6,
+    FIMEXCU_INTERPOL_FORWARD_MEDIAN = 7,
+    FIMEXCU_INTERPOL_FORWARD_MAX = 8,
+    FIMEXCU_INTERPOL_FORWARD_MIN = 9,
+    FIMEXCU_INTERPOL_FORWARD_UNDEF_SUM = 10,
+    FIMEXCU_INTERPOL_FORWARD_UNDEF_MEAN = 11,
+    FIMEXCU_INTERPOL_FORWARD_UNDEF_MEDIAN = 12,
+    FIMEXCU_INTERPOL_FORWARD_UNDEF_MAX = 13,
+    FIMEXCU_INTERPOL_FORWARD_UNDEF_MIN = 14
+};
+/* vertical methods: enum mifi_vertical_interpol_method, mifi_constants.h:206-231 */
+enum fimexcu_vint_method {
+    FIMEXCU_VINT_METHOD_LIN = 0,
+    FIMEXCU_VINT_METHOD_LOG = 1,
+    FIMEXCU_VINT_METHOD_LOGLOG = 2,
+    FIMEXCU_VINT_METHOD_NN = 3,
+    FIMEXCU_VINT_METHOD_LIN_WEAK_EXTRA = 4,
+    FIMEXCU_VINT_METHOD_LIN_NO_EXTRA = 5,
+    FIMEXCU_VINT_METHOD_LIN_CONST_EXTRA = 6
+};
+/* axis types: mifi_constants.h:264-268 */
+enum fimexcu_axis_type { FIMEXCU_PROJ_AXIS = 0, FIMEXCU_LONGITUDE = 1, FIMEXCU_LATITUDE = 2 };
+
+/* ------------------------------------------------------------------------------------------------
+ * runtime
+ * ---------------------------------------------------------------------------------------------- */
+/* message of the last failed call on this thread ("" if none).  Replaces the CDMException text thrown at
+ * src/CachedInterpolation.cc:197-203 / src/reproject.cc:65-70. */
+const char* fimexcu_last_error(void);
+/* number of usable sm_100 devices; replaces mifi_setNumThreads()'s role of sizing the worker pool
+ * (src/ThreadPool.c:33-47): slabs are dealt to devices instead of OpenMP threads. */
+int fimexcu_device_count(void);
+/* make device `ordinal` current for the calling thread (one process or thread per GPU). */
+int fimexcu_set_device(int ordinal);
+/* pinned host memory for slabs (so the host<->device copies of the *_f entry points run at full PCIe
+ * speed); plays the part of make_shared_array<float>() in include/fimex/SharedArray.h:42-48. */
+void* fimexcu_host_alloc(size_t bytes);
+void fimexcu_host_free(void* p);
+/* plain device memory for callers that keep slabs resident between chained operators */
+void* fimexcu_dev_alloc(size_t bytes);
+void fimexcu_dev_free(void* p);
+int fimexcu_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes);
+int fimexcu_memcpy_d2h(void* dst_host, const void* src_dev, size_t bytes);
+int fimexcu_synchronize(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * horizontal interpolation cache (bilinear / bicubic / nearest / coord_nn / coord_kdtree)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct fimexcu_cache fimexcu_cache;
+
+/* Replaces createCachedInterpolation() (src/CachedInterpolation.cc:132-147) with the constructors of
+ * CachedInterpolation (:149-171, reduced domain :222-253) and CachedNNInterpolation (:262-315).
+ * pointsOnXAxis/pointsOnYAxis: outX*outY fractional source indices (HOST, not modified; the reference
+ * rebases its arrays in place -- read the offsets with fimexcu_cache_info()). */
+fimexcu_cache* fimexcu_cache_create(int method, const double* pointsOnXAxis, const double* pointsOnYAxis, size_t inX, size_t inY,
+                                    size_t outX, size_t outY);
+/* same with DEVICE tables (e.g. straight from fimexcu_project_axes_dev + fimexcu_points2position_dev) */
+fimexcu_cache* fimexcu_cache_create_dev(int method, const double* d_pointsOnXAxis, const double* d_pointsOnYAxis, size_t inX, size_t inY,
+                                        size_t outX, size_t outY, void* stream);
+/* getInX/getInY/getOutX/getOutY and reducedDomain() of CachedInterpolationInterface
+ * (include/fimex/CachedInterpolation.h:63-103): inX/inY are the sizes of the (possibly reduced) input
+ * window the apply calls expect, xMin/yMin its offset in the full source grid. */
+int fimexcu_cache_info(const fimexcu_cache* c, size_t* inX, size_t* inY, size_t* outX, size_t* outY, int* reduced, size_t* xMin, size_t* yMin);
+/* Replaces CachedInterpolationInterface::interpolateValues(inData, size, newSize)
+ * (CachedInterpolation.cc:173-209 bilinear/bicubic via interpolation.c:267-414; :317-337 nearest) with
+ * mifi_bad2nanf (interpolation.c:1064-1072, caller: CDMInterpolator.cc:140-145) fused on load and
+ * mifi_nanf2bad (:1074-1082; caller interpolationArray2Data, CDMInterpolator.cc:147-151) fused on store.
+ *   in   HOST [nz][inY][inX] f32, size = nz*inX*inY;  out HOST [nz][outY][outX] f32;  *newSize = nz*outX*outY
+ *   badIn   values equal to it are read as NaN (pass NaN for "none")
+ *   fillOut NaN results are written as this value (pass NaN to keep NaN) */
+int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, float* out, size_t* newSize, float badIn, float fillOut);
+/* same on DEVICE-resident slabs; enqueues on `stream` */
+int fimexcu_cache_apply_dev_f(const fimexcu_cache* c, const float* d_in, size_t nz, float* d_out, float badIn, float fillOut, void* stream);
+void fimexcu_cache_destroy(fimexcu_cache* c);
+
+/* Drop-in for the per-point C kernels with the reference signatures (include/fimex/interpolation.h:95-137,
+ * src/interpolation.c:251-414): one (x, y) position over iz levels.  infield/outvalues are HOST pointers.
+ * Provided for callers of the uncached path (reproject::reproject_f, src/reproject.cc:266-295); one launch
+ * per call -- use the cache for anything but single points. */
+int fimexcu_get_values_f(const float* infield, float* outvalues, double x, double y, int ix, int iy, int iz);
+int fimexcu_get_values_bilinear_f(const float* infield, float* outvalues, double x, double y, int ix, int iy, int iz);
+int fimexcu_get_values_bicubic_f(const float* infield, float* outvalues, double x, double y, int ix, int iy, int iz);
+
+/* ------------------------------------------------------------------------------------------------
+ * vector (wind) rotation
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct fimexcu_vecrot fimexcu_vecrot;
+
+/* Replaces CachedVectorReprojection(reproject::Matrix_cp) (src/CachedVectorReprojection.cc:37-42).
+ * matrix3: HOST ox*oy*3 doubles (cos, sin, angle in degree), the layout of reproject::Matrix
+ * (include/fimex/reproject.h:34-46). */
+fimexcu_vecrot* fimexcu_vecrot_create(const double* matrix3, size_t ox, size_t oy);
+fimexcu_vecrot* fimexcu_vecrot_create_dev(const double* d_matrix3, size_t ox, size_t oy, void* stream);
+/* Replaces CachedVectorReprojection::reprojectValues(u, v, size) -> reproject::vector_reproject_values_by_matrix_f
+ * (CachedVectorReprojection.cc:44-48, reproject.cc:488-507): in place, size = nz*ox*oy. */
+int fimexcu_vecrot_apply_f(const fimexcu_vecrot* r, float* u, float* v, size_t size);
+int fimexcu_vecrot_apply_dev_f(const fimexcu_vecrot* r, float* d_u, float* d_v, size_t nz, void* stream);
+/* Replaces CachedVectorReprojection::reprojectDirectionValues -> vector_reproject_direction_by_matrix_f
+ * (CachedVectorReprojection.cc:50-54, reproject.cc:509-530). */
+int fimexcu_vecrot_direction_f(const fimexcu_vecrot* r, float* angles, size_t size);
+int fimexcu_vecrot_direction_dev_f(const fimexcu_vecrot* r, float* d_angles, size_t nz, void* stream);
+void fimexcu_vecrot_destroy(fimexcu_vecrot* r);
+/* The vector branch of CDMInterpolator::getDataSlice (src/CDMInterpolator.cc:232-259) as ONE pass:
+ * interpolate u and v with the same cache and rotate them, instead of the reference's two
+ * interpolateValues() calls per component plus reprojectValues().  r may be NULL (no rotation). */
+int fimexcu_cache_apply_uv_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* u_in, const float* v_in, size_t size, float* u_out,
+                             float* v_out, size_t* newSize, float badU, float badV, float fillU, float fillV);
+int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* d_u_in, const float* d_v_in, size_t nz,
+                                 float* d_u_out, float* d_v_out, float badU, float badV, float fillU, float fillV, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * cache build: axes, projections, rotation matrix
+ * ---------------------------------------------------------------------------------------------- */
+/* Replaces mifi_points2position (include/fimex/interpolation.h:76-93, src/interpolation.c:154-227):
+ * coordinates -> fractional axis indices, in place.  HOST pointers. */
+int fimexcu_points2position(double* points, size_t n, const double* axis, int num, int axis_type);
+int fimexcu_points2position_dev(double* d_points, size_t n, const double* axis_host, int num, int axis_type, void* stream);
+/* Replaces reproject::reproject_axes (include/fimex/reproject.h:211-227, src/reproject.cc:573-587): broadcast the
+ * 1-D axes to an ix*iy lattice and transform proj_input -> proj_output (proj4 strings; degrees for geographic
+ * CRS as with PROJ >= 6).  Points that cannot be projected become +inf. */
+int fimexcu_reproject_axes(const char* proj_input, const char* proj_output, const double* in_x_axis, const double* in_y_axis, int ix, int iy,
+                           double* out_xproj_axis, double* out_yproj_axis);
+int fimexcu_reproject_axes_dev(const char* proj_input, const char* proj_output, const double* in_x_axis_host, const double* in_y_axis_host, int ix,
+                               int iy, double* d_out_xproj_axis, double* d_out_yproj_axis, void* stream);
+/* Replaces reproject::reproject_values (reproject.h:195-209, reproject.cc:567-571): n points in place. */
+int fimexcu_reproject_values(const char* proj_input, const char* proj_output, double* in_out_x_vals, double* in_out_y_vals, int num);
+int fimexcu_reproject_values_dev(const char* proj_input, const char* proj_output, double* d_x, double* d_y, size_t num, void* stream);
+/* Replaces reproject::get_vector_reproject_matrix (reproject.h:146-160, reproject.cc:463-486 with :363-397 and
+ * :310-357).  matrix3: ox*oy*3 doubles out. */
+int fimexcu_get_vector_reproject_matrix(const char* proj_input, const char* proj_output, const double* out_x_axis, const double* out_y_axis, int ox,
+                                        int oy, double* matrix3);
+/* Replaces reproject::get_vector_reproject_matrix_points (reproject.h:177-193, reproject.cc:432-447). */
+int fimexcu_get_vector_reproject_matrix_points(const char* proj_input, const char* proj_output, int inputIsMetric, const double* out_x_points,
+                                               const double* out_y_points, int ox, int oy, double* matrix3);
+/* One call for the whole of CDMInterpolator::changeProjectionByProjectionParameters' numeric part
+ * (src/CDMInterpolator.cc:1389-1404): reproject_axes(out -> in) + 2 x points2position + cache construction,
+ * all on the device; the index tables never visit the host. */
+fimexcu_cache* fimexcu_cache_create_from_projection(int method, const char* proj_input /* target CRS */, const char* proj_org /* source CRS */,
+                                                    const double* out_x_axis, const double* out_y_axis, size_t outX, size_t outY,
+                                                    const double* org_x_axis, const double* org_y_axis, size_t inX, size_t inY,
+                                                    int org_x_axis_type, int org_y_axis_type);
+
+/* ------------------------------------------------------------------------------------------------
+ * coordinate-based nearest neighbour (curvilinear sources)
+ * ---------------------------------------------------------------------------------------------- */
+/* Replaces flannTranslatePointsToClosestInputCell (src/CDMInterpolator.cc:953-1028; nanoflann radiusSearch, first
+ * sorted match).  pointsOnXAxis/pointsOnYAxis: in = target lon/lat in degrees, out = source (ix, iy) as doubles,
+ * or -1000 when nothing lies within maxDist (metres on the R=6371000 sphere).  HOST pointers. */
+int fimexcu_kdtree_translate(double maxDist, double* pointsOnXAxis, double* pointsOnYAxis, size_t pointsSize, const double* lonVals,
+                             const double* latVals, size_t orgXDimSize, size_t orgYDimSize);
+/* Replaces fastTranslatePointsToClosestInputCell + getGridDistance (CDMInterpolator.cc:1030-1190): misses give -1. */
+int fimexcu_coordnn_translate(double* pointsOnXAxis, double* pointsOnYAxis, size_t pointsSize, const double* lonVals, const double* latVals,
+                              size_t orgXDimSize, size_t orgYDimSize);
+
+/* ------------------------------------------------------------------------------------------------
+ * forward (scatter / aggregate) interpolation
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct fimexcu_forward fimexcu_forward;
+/* Replaces CachedForwardInterpolation's constructor (src/CachedForwardInterpolation.cc:133-201).  pOnX/pOnY:
+ * inX*inY target positions of every SOURCE cell (HOST). */
+fimexcu_forward* fimexcu_forward_create(int method, const double* pOnX, const double* pOnY, size_t inX, size_t inY, size_t outX, size_t outY);
+int fimexcu_forward_info(const fimexcu_forward* f, size_t* inX, size_t* inY, size_t* outX, size_t* outY, int* reduced, size_t* xMin,
+                         size_t* yMin, size_t* maxPointsInIn);
+/* Replaces CachedForwardInterpolation::interpolateValues (:205-224).  level_compat != 0 reproduces the reference
+ * literally (it reads inData[ii] without the level offset, so every output level aggregates input level 0);
+ * 0 aggregates each level from its own input level. */
+int fimexcu_forward_apply_f(const fimexcu_forward* f, const float* in, size_t size, float* out, size_t* newSize, float badIn, float fillOut,
+                            int level_compat);
+int fimexcu_forward_apply_dev_f(const fimexcu_forward* f, const float* d_in, size_t nz, float* d_out, float badIn, float fillOut,
+                                int level_compat, void* stream);
+void fimexcu_forward_destroy(fimexcu_forward* f);
+
+/* ------------------------------------------------------------------------------------------------
+ * vertical interpolation
+ * ---------------------------------------------------------------------------------------------- */
+/* Replaces the hot loop of CDMVerticalInterpolator::getLevelDataSlice (src/CDMVerticalInterpolator.cc:488-561):
+ * neighbour search (include/fimex/FindNeighborElements.h:46-125), the two-level kernel selected at :379-388
+ * (src/interpolation.c:416-546), the validity range test (:505-528) and the valid_min/valid_max clamp (:551-561).
+ * Layout: in [nOuter][nzi][nInner], vcoord_in the same shape (f32, as :483-486), out [nOuter][nzo][nInner];
+ * a column is (outer, inner).  Target: levels[nzo] (f64, `level1`) or, when levels == NULL, vcoord_out
+ * [nOuter][nzo][nInner] f32 (template / to-axis).  vmin/vmax: f64 per column (NULL = none).  valid_min /
+ * valid_max: NaN = none.  HOST pointers. */
+int fimexcu_vertical_interpolate_f(int method, const float* in, const float* vcoord_in, size_t nOuter, size_t nzi, size_t nInner,
+                                   const double* levels, const float* vcoord_out, size_t nzo, const double* vmin, const double* vmax,
+                                   double valid_min, double valid_max, float badIn, float fillOut, float* out);
+int fimexcu_vertical_interpolate_dev_f(int method, const float* d_in, const float* d_vcoord_in, size_t nOuter, size_t nzi, size_t nInner,
+                                       const double* levels_host, const float* d_vcoord_out, size_t nzo, const double* d_vmin,
+                                       const double* d_vmax, double valid_min, double valid_max, float badIn, float fillOut, float* d_out,
+                                       void* stream);
+/* Same with the hybrid-sigma pressure formed on the fly (never materialised): replaces
+ * HybridSigmaApToPressureConverter::getDataSlice (src/coordSys/verticalTransform/HybridSigmaApToPressureConverter.cc:71-100)
+ * -> mifi_atmosphere_hybrid_sigma_ap_pressure (src/vertical_coordinate_transformations.c:62-68) feeding the loop above.
+ * p[k] = ap[k] + b[k] * (ps * ps_scale) in f64, narrowed to f32 as at CDMVerticalInterpolator.cc:483.
+ * ps: f32 [nOuterPs][nInner] with nOuterPs == nOuter or 1 (broadcast over the outer dimension).
+ * For hybrid_sigma (a, p0) pass ap[k] = a[k]*p0. */
+int fimexcu_vertical_hybrid_pressure_f(int method, const float* in, size_t nOuter, size_t nzi, size_t nInner, const double* ap, const double* b,
+                                       const float* ps, size_t nOuterPs, double ps_scale, const double* levels, size_t nzo, double valid_min,
+                                       double valid_max, float badIn, float fillOut, float* out);
+int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t nOuter, size_t nzi, size_t nInner, const double* ap_host,
+                                           const double* b_host, const float* d_ps, size_t nOuterPs, double ps_scale, const double* levels_host,
+                                           size_t nzo, double valid_min, double valid_max, float badIn, float fillOut, float* d_out,
+                                           void* stream);
+/* Drop-ins with the reference signatures for the two-level kernels (include/fimex/interpolation.h:153-232,
+ * src/interpolation.c:416-546); HOST pointers, n values per level. */
+int fimexcu_get_values_nearest_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
+int fimexcu_get_values_linear_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
+int fimexcu_get_values_linear_weak_extrapol_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
+int fimexcu_get_values_linear_no_extrapol_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
+int fimexcu_get_values_linear_const_extrapol_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
+int fimexcu_get_values_log_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
+int fimexcu_get_values_log_log_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FIMEXCU_H */

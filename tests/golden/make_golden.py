@@ -1,0 +1,89 @@
+"""Generates tests/golden/*.npz from the reference's OWN code (oracle/_ref, compiled from /root/reference by
+oracle/Makefile).  Run in the build container:  python tests/golden/make_golden.py
+The GPU box has no /root/reference; the committed fixtures carry the reference's answers there."""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+import oracle_lib as ol  # noqa: E402
+from oracle_lib import dp, fp  # noqa: E402
+
+
+def tables(rng, in_x, in_y, n, margin=3.0):
+    px = rng.uniform(-margin, in_x - 1 + margin, n)
+    py = rng.uniform(-margin, in_y - 1 + margin, n)
+    k = n // 8
+    px[:k] = np.round(px[:k] * 2) / 2
+    py[:k] = np.round(py[:k] * 2) / 2
+    px[k:k + 4] = -999.
+    py[k + 2:k + 6] = -1000.
+    strip = (py >= in_y - 0.5) & (py < in_y + 0.5) & ~((np.floor(px) >= 0) & (np.floor(px) + 1 < in_x))
+    py[strip] += 1.0  # the reference's out-of-bounds corner strip (interpolation.c:322)
+    return px, py
+
+
+def main():
+    ref = ol.ref()
+    assert ref is not None, "build oracle/_ref first (make -C oracle)"
+    rng = np.random.default_rng(20261106)
+    out = {}
+    in_x, in_y, out_x, out_y, nz = 41, 33, 37, 29, 3
+    fld = rng.normal(280, 10, size=(nz, in_y, in_x)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.04] = np.nan
+    out["h_field"] = fld
+    out["h_dims"] = np.array([in_x, in_y, out_x, out_y, nz])
+    for tag, scale in (("full", 1.0), ("sub", 0.45)):
+        px, py = tables(rng, in_x, in_y, out_x * out_y)
+        if scale != 1.0:
+            px, py = 9 + px * scale, 7 + py * scale
+        out[f"h_{tag}_px"], out[f"h_{tag}_py"] = px, py
+        for name, m in (("bilinear", ol.BILINEAR), ("bicubic", ol.BICUBIC), ("nearest", ol.NEAREST)):
+            r, info = ol.r_cached_apply(m, px, py, in_x, in_y, out_x, out_y, fld)
+            out[f"h_{tag}_{name}_out"] = r
+            out[f"h_{tag}_{name}_info"] = np.array([info["inX"], info["inY"], int(info["reduced"]), info["xMin"], info["yMin"]])
+    # forward aggregation
+    fin_x, fin_y, fout_x, fout_y, fnz = 57, 43, 13, 11, 2
+    pox = rng.uniform(-2, fout_x + 1, fin_x * fin_y)
+    poy = rng.uniform(-2, fout_y + 1, fin_x * fin_y)
+    ffld = rng.normal(size=(fnz, fin_y, fin_x)).astype(np.float32)
+    ffld[rng.random(ffld.shape) < 0.1] = np.nan
+    out["f_field"], out["f_px"], out["f_py"] = ffld, pox, poy
+    out["f_dims"] = np.array([fin_x, fin_y, fout_x, fout_y, fnz])
+    for name, m in (("sum", ol.FWD_SUM), ("mean", ol.FWD_MEAN), ("median", ol.FWD_MEDIAN), ("max", ol.FWD_MAX), ("min", ol.FWD_MIN),
+                    ("undef_sum", ol.FWD_UNDEF_SUM), ("undef_mean", ol.FWD_UNDEF_MEAN), ("undef_max", ol.FWD_UNDEF_MAX),
+                    ("undef_min", ol.FWD_UNDEF_MIN)):
+        r, info = ol.r_cached_apply(m, pox, poy, fin_x, fin_y, fout_x, fout_y, ffld)
+        out[f"f_{name}_out"] = r
+    # vector rotation
+    ox, oy, vz = 23, 19, 2
+    ang = rng.uniform(-np.pi, np.pi, ox * oy)
+    m3 = np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy()
+    u = rng.normal(size=(vz, oy, ox)).astype(np.float32)
+    v = rng.normal(size=(vz, oy, ox)).astype(np.float32)
+    u[0, 0, :2] = np.nan
+    d = rng.uniform(0, 360, size=(vz, oy, ox)).astype(np.float32)
+    out["v_matrix"], out["v_u"], out["v_v"], out["v_dir"] = m3, u.copy(), v.copy(), d.copy()
+    ref.ref_vector_reproject_values_by_matrix_f(dp(m3), ox, oy, fp(u), fp(v), vz)
+    ref.ref_vector_reproject_direction_by_matrix_f(dp(m3), ox, oy, fp(d), vz)
+    out["v_u_out"], out["v_v_out"], out["v_dir_out"] = u, v, d
+    # points2position
+    axes = {"lcc_x": np.linspace(-1060084., 1309916., 949), "lat_desc": np.linspace(75.25, 49.75, 1021), "lon360": np.arange(0., 360., 0.5),
+            "lon180": np.arange(-180., 180., 0.25), "irregular": np.cumsum(rng.uniform(0.5, 2.0, 200))}
+    for k, ax in axes.items():
+        for t in (0, 1, 2):
+            lo, hi = ax.min(), ax.max()
+            pts = rng.uniform(lo - 0.3 * (hi - lo), hi + 0.3 * (hi - lo), 600)
+            pts[:60] = rng.choice(ax, 60)
+            pts[60:70] = [np.nan, np.inf, -np.inf, 360., -360., 180., -180., 0., 720., -0.0]
+            res = pts.copy()
+            ref.mifi_points2position(dp(res), res.size, dp(ax), ax.size, t)
+            out[f"p_{k}_{t}_axis"], out[f"p_{k}_{t}_in"], out[f"p_{k}_{t}_out"] = ax, pts, res
+    np.savez_compressed(os.path.join(HERE, "reference_small.npz"), **out)
+    print("wrote reference_small.npz with", len(out), "arrays")
+
+
+if __name__ == "__main__":
+    main()

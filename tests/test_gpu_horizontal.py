@@ -1,0 +1,241 @@
+"""GPU parity tests of the horizontal path, through the C ABI (ctypes -> libfimexcu.so).
+
+Checker: oracle/liboracle.so (pinned against the reference in test_oracle_*.py) and the committed golden
+fixtures produced by the reference's own code (tests/golden/reference_small.npz).
+Bar: BIT-EXACT for every value, index and undefined mask (the CUDA kernels reproduce the reference's
+rounding order; the 1e-5 relative tolerance of BASELINE.json is not needed and not used)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from oracle_lib import dp, fp
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_small.npz")
+
+
+def _eq(a, b):
+    a, b = np.asarray(a), np.asarray(b)
+    na, nb = np.isnan(a), np.isnan(b)
+    return a.shape == b.shape and np.array_equal(na, nb) and np.array_equal(a[~na], b[~nb])
+
+
+@pytest.fixture(scope="module")
+def fx():
+    import fimex_b200
+    assert fimex_b200.lib.fimexcu_device_count() >= 1, "no sm_100 device: the CUDA path must run, there is no fallback"
+    return fimex_b200
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(GOLDEN)
+
+
+def _tables(rng, in_x, in_y, n, margin=3.0):
+    px = rng.uniform(-margin, in_x - 1 + margin, n)
+    py = rng.uniform(-margin, in_y - 1 + margin, n)
+    k = n // 8
+    px[:k] = np.round(px[:k] * 2) / 2
+    py[:k] = np.round(py[:k] * 2) / 2
+    px[k:k + 4] = -999.
+    py[k + 2:k + 6] = -1000.
+    return px, py
+
+
+# ---------------------------------------------------------------------------------- points2position
+def test_points2position_golden(fx, gold):
+    names = sorted({k[:-5] for k in gold.files if k.startswith("p_") and k.endswith("_axis")})
+    assert len(names) == 15
+    for n in names:
+        t = int(n.rsplit("_", 1)[1])
+        got = fx.mifi_points2position(gold[n + "_in"], gold[n + "_axis"], t)
+        assert _eq(got, gold[n + "_out"]), n
+
+
+def test_points2position_vs_oracle_large(fx, oracle):
+    rng = np.random.default_rng(42)
+    ax = np.linspace(-1060084., 1309916., 949)
+    pts = rng.uniform(-2e6, 2e6, 300000)
+    pts[:1000] = rng.choice(ax, 1000)
+    want = pts.copy()
+    oracle.orc_points2position(dp(want), want.size, dp(ax), ax.size, ol.PROJ_AXIS)
+    assert _eq(fx.mifi_points2position(pts, ax, ol.PROJ_AXIS), want)
+
+
+# ---------------------------------------------------------------------------------- cached apply
+@pytest.mark.parametrize("tag", ["full", "sub"])
+@pytest.mark.parametrize("name,method", [("bilinear", ol.BILINEAR), ("bicubic", ol.BICUBIC), ("nearest", ol.NEAREST)])
+def test_cached_apply_golden(fx, gold, tag, name, method):
+    in_x, in_y, out_x, out_y, nz = (int(v) for v in gold["h_dims"])
+    ci = fx.createCachedInterpolation("x", "y", method, gold[f"h_{tag}_px"], gold[f"h_{tag}_py"], in_x, in_y, out_x, out_y)
+    info = gold[f"h_{tag}_{name}_info"]
+    assert (ci.getInX(), ci.getInY()) == (info[0], info[1])
+    assert (ci.reducedDomain() is not None) == bool(info[2])
+    if ci.reducedDomain() is not None:
+        assert (ci.reducedDomain().xMin, ci.reducedDomain().yMin) == (info[3], info[4])
+    sub = ci.reduceInput(gold["h_field"], in_x, in_y)
+    out, new_size = ci.interpolateValues(sub)
+    assert new_size == nz * out_x * out_y
+    assert _eq(out, gold[f"h_{tag}_{name}_out"])
+
+
+@pytest.mark.parametrize("method", [ol.BILINEAR, ol.BICUBIC, ol.NEAREST, ol.COORD_NN_KD])
+@pytest.mark.parametrize("shape", [(61, 47, 53, 39, 5), (300, 200, 517, 333, 7), (5, 4, 1, 1, 1), (2, 2, 40, 30, 2), (64, 64, 1000, 3, 65)])
+def test_cached_apply_vs_oracle(fx, method, shape):
+    in_x, in_y, out_x, out_y, nz = shape
+    rng = np.random.default_rng(sum(shape) + method)
+    px, py = _tables(rng, in_x, in_y, out_x * out_y)
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.03] = np.nan
+    want, info = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, fld)
+    ci = fx.createCachedInterpolation("x", "y", method, px, py, in_x, in_y, out_x, out_y)
+    assert (ci.getInX(), ci.getInY(), ci.reducedDomain() is not None) == (info["inX"], info["inY"], info["reduced"])
+    got, _ = ci.interpolateValues(ci.reduceInput(fld, in_x, in_y))
+    assert _eq(got, want)
+
+
+def test_cached_apply_device_resident_and_fused_bad_fill(fx, oracle):
+    """device pointers (torch only allocates) + bad->NaN on load and NaN->fill on store fused into the kernel
+    (data2InterpolationArray / interpolationArray2Data of CDMInterpolator.cc:140-151)."""
+    import torch
+    rng = np.random.default_rng(77)
+    in_x, in_y, out_x, out_y, nz = 120, 90, 233, 177, 9
+    bad, fill = np.float32(9.96921e36), np.float32(-32767.0)
+    for method in (ol.BILINEAR, ol.BICUBIC, ol.NEAREST):
+        px, py = _tables(rng, in_x, in_y, out_x * out_y)
+        fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+        fld[rng.random(fld.shape) < 0.05] = bad
+        clean = fld.copy()
+        oracle.orc_bad2nanf(fp(clean), clean.size, bad)
+        want, _ = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, clean)
+        oracle.orc_nanf2bad(fp(want), want.size, fill)
+        ci = fx.createCachedInterpolation("x", "y", method, px, py, in_x, in_y, out_x, out_y)
+        d_in = torch.from_numpy(ci.reduceInput(fld, in_x, in_y)).cuda()
+        d_out, _ = ci.interpolateValues(d_in, badValue=float(bad), fillValue=float(fill))
+        torch.cuda.synchronize()
+        assert _eq(d_out.cpu().numpy(), want)
+        # host path with the same fused conversions
+        h_out, _ = ci.interpolateValues(ci.reduceInput(fld, in_x, in_y), badValue=float(bad), fillValue=float(fill))
+        assert _eq(h_out, want)
+
+
+def test_cache_from_device_tables(fx):
+    import torch
+    rng = np.random.default_rng(5)
+    in_x, in_y, out_x, out_y, nz = 80, 60, 90, 70, 3
+    px, py = _tables(rng, in_x, in_y, out_x * out_y)
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    want, _ = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, fld)
+    ci = fx.CachedInterpolation("x", "y", ol.BILINEAR, torch.from_numpy(px).cuda(), torch.from_numpy(py).cuda(), in_x, in_y, out_x, out_y)
+    got, _ = ci.interpolateValues(ci.reduceInput(fld, in_x, in_y))
+    assert _eq(got, want)
+
+
+def test_unknown_method_is_an_error(fx):
+    with pytest.raises(fx.FimexCudaError, match="unknown interpolation function"):
+        fx.createCachedInterpolation("x", "y", 99, np.zeros(4), np.zeros(4), 2, 2, 2, 2)
+    assert fx.lib.fimexcu_cache_create(ol.FWD_SUM, None, None, 2, 2, 0, 0) is None  # forward goes through fimexcu_forward_create
+
+
+@pytest.mark.parametrize("method", [ol.NEAREST, ol.BILINEAR, ol.BICUBIC])
+def test_single_position_kernels(fx, oracle, method):
+    from fimex_b200.interpolation import mifi_get_values
+    rng = np.random.default_rng(8)
+    ix, iy, iz = 9, 7, 5
+    fld = rng.normal(size=(iz, iy, ix)).astype(np.float32)
+    fo = {ol.NEAREST: oracle.orc_get_values_f, ol.BILINEAR: oracle.orc_get_values_bilinear_f, ol.BICUBIC: oracle.orc_get_values_bicubic_f}[method]
+    want = np.zeros(iz, np.float32)
+    for x, y in [(0.3, 0.), (0., 0.3), (4.5, 3.5), (7.99, 5.99), (-0.4, 1), (-0.6, 1), (8.4, 6.4), (2.5, 2.5), (8, 6), (1.25, 1.75)]:
+        fo(fp(fld), fp(want), x, y, ix, iy, iz)
+        assert _eq(mifi_get_values(method, fld, x, y), want), (x, y)
+
+
+# ---------------------------------------------------------------------------------- vector rotation
+def test_vector_rotation_golden(fx, gold):
+    cvr = fx.CachedVectorReprojection(gold["v_matrix"].reshape(19, 23, 3))
+    u, v = gold["v_u"].copy(), gold["v_v"].copy()
+    cvr.reprojectValues(u, v)
+    assert _eq(u, gold["v_u_out"]) and _eq(v, gold["v_v_out"])
+    d = gold["v_dir"].copy()
+    cvr.reprojectDirectionValues(d)
+    assert _eq(d, gold["v_dir_out"])
+
+
+def test_fused_uv_matches_separate_reference_steps(fx, oracle):
+    """one fused pass == interpolate u, interpolate v, rotate (CDMInterpolator.cc:232-259)"""
+    from fimex_b200.interpolation import interpolateVectorValues
+    rng = np.random.default_rng(21)
+    in_x, in_y, out_x, out_y, nz = 70, 50, 131, 97, 6
+    ang = rng.uniform(-np.pi, np.pi, out_x * out_y)
+    m3 = np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy()
+    for method in (ol.BILINEAR, ol.BICUBIC, ol.NEAREST):
+        px, py = _tables(rng, in_x, in_y, out_x * out_y)
+        u = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+        v = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+        u[rng.random(u.shape) < 0.02] = np.nan
+        wu, _ = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, u)
+        wv, _ = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, v)
+        oracle.orc_vector_reproject_values_by_matrix_f(dp(m3), out_x * out_y, fp(wu), fp(wv), nz)
+        ci = fx.createCachedInterpolation("x", "y", method, px, py, in_x, in_y, out_x, out_y)
+        cvr = fx.CachedVectorReprojection(m3, out_x, out_y)
+        gu, gv = interpolateVectorValues(ci, cvr, ci.reduceInput(u, in_x, in_y), ci.reduceInput(v, in_x, in_y))
+        assert _eq(gu, wu) and _eq(gv, wv)
+
+
+# ---------------------------------------------------------------------------------- full-size properties (BASELINE configs[1])
+@pytest.fixture(scope="module")
+def meps_t1(fx):
+    from fimex_b200 import synthetic as S
+    px, py, ox, oy = S.meps_index_tables("T1")
+    ci = fx.CachedInterpolation("x", "y", ol.BILINEAR, px, py, S.MEPS_NX, S.MEPS_NY, ox, oy)
+    return S, px, py, ox, oy, ci
+
+
+def test_meps_t1_full_size_against_oracle_levels(fx, oracle, meps_t1):
+    """949x1069 -> 2891x1021 at full horizontal size; 2 of the 65 levels so the scalar oracle finishes in seconds"""
+    S, px, py, ox, oy, ci = meps_t1
+    fld = S.meps_slab_numpy(t=3, nz=2, nan_fraction=0.001)
+    want, info = ol.o_cached_apply(ol.BILINEAR, px, py, S.MEPS_NX, S.MEPS_NY, ox, oy, fld)
+    assert (ci.getInX(), ci.getInY()) == (info["inX"], info["inY"])
+    got, _ = ci.interpolateValues(ci.reduceInput(fld, S.MEPS_NX, S.MEPS_NY))
+    assert _eq(got, want)
+    frac_defined = 1.0 - np.isnan(want[0]).mean()
+    assert 0.60 < frac_defined < 0.66  # 63.4 % of T1 lies inside the MEPS domain
+
+
+def test_meps_t1_full_slab_properties(fx, meps_t1):
+    """all 65 levels, device resident: size-independent properties instead of the scalar oracle."""
+    import torch
+    S, px, py, ox, oy, ci = meps_t1
+    nz = S.MEPS_NZ
+    gx = torch.arange(S.MEPS_NX, device="cuda", dtype=torch.float32)[None, None, :]
+    gy = torch.arange(S.MEPS_NY, device="cuda", dtype=torch.float32)[None, :, None]
+    k = torch.arange(nz, device="cuda", dtype=torch.float32)[:, None, None]
+    # (1) a field that is affine in the grid indices is reproduced by bilinear interpolation: f = 2x + 3y + 10k
+    fld = (2 * gx + 3 * gy + 10 * k).contiguous()
+    sub = ci.reduceInput(fld, S.MEPS_NX, S.MEPS_NY)
+    out, n = ci.interpolateValues(sub)
+    torch.cuda.synchronize()
+    assert n == nz * ox * oy
+    out = out.cpu().numpy()
+    inside = (px >= 0) & (px <= S.MEPS_NX - 1) & (py >= 0) & (py <= S.MEPS_NY - 1)
+    expect = (2 * px + 3 * py)[None] + 10 * np.arange(nz)[:, None, None]
+    err = np.abs(out[:, inside] - expect[:, inside]) / np.abs(expect[:, inside]).clip(1)
+    assert err.max() < 1e-5  # BASELINE.json tolerance (float32 rounding of the weights)
+    # (2) undefined mask: identical on every level, NaN exactly where the position is >= 0.5 cell outside
+    mask0 = np.isnan(out[0])
+    assert all(np.array_equal(mask0, np.isnan(out[z])) for z in range(nz))
+    far_out = (px < -0.5) | (px > S.MEPS_NX - 0.5) | (py < -0.5) | (py > S.MEPS_NY - 0.5)
+    assert mask0[far_out].all() and not mask0[inside].any()
+    # (3) a constant field stays constant wherever defined (weights sum to one), and levels do not mix
+    const = (k + 1.0).expand(nz, S.MEPS_NY, S.MEPS_NX).contiguous()
+    outc, _ = ci.interpolateValues(ci.reduceInput(const, S.MEPS_NX, S.MEPS_NY))
+    outc = outc.cpu().numpy()
+    for z in (0, 31, 64):
+        vals = outc[z][~mask0]
+        assert np.abs(vals - (z + 1.0)).max() <= 1e-5 * (z + 1.0)

@@ -1,0 +1,206 @@
+"""Pins the C restatement (oracle/liboracle.so) against the reference's OWN code compiled from
+/root/reference into oracle/_ref (seeded random inputs, bit-exact).  Skipped when oracle/_ref is absent."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from oracle_lib import dp, fp
+
+
+def _eq(a, b):
+    """bit-level equality that treats any NaN as equal to any NaN"""
+    a, b = np.asarray(a), np.asarray(b)
+    na, nb = np.isnan(a), np.isnan(b)
+    return np.array_equal(na, nb) and np.array_equal(a[~na], b[~nb])
+
+
+def test_points2position_matches_reference(oracle, ref):
+    rng = np.random.default_rng(11)
+    axes = [np.linspace(-1060084., 1309916., 949), np.linspace(75.25, 49.75, 1021), np.arange(0., 360., 0.5), np.arange(-180., 180., 0.25),
+            np.cumsum(rng.uniform(0.5, 2.0, 200)), np.arange(-10., 31., 1.)]
+    for k, ax in enumerate(axes):
+        for t in (ol.PROJ_AXIS, ol.LONGITUDE, ol.LATITUDE):
+            lo, hi = ax.min(), ax.max()
+            pts = rng.uniform(lo - 0.3 * (hi - lo), hi + 0.3 * (hi - lo), 5000)
+            pts[:200] = rng.choice(ax, 200)  # exact hits
+            pts[200:210] = [np.nan, np.inf, -np.inf, 360., -360., 180., -180., 0., 720., -0.0]
+            a, b = pts.copy(), pts.copy()
+            oracle.orc_points2position(dp(a), a.size, dp(ax), ax.size, t)
+            ref.mifi_points2position(dp(b), b.size, dp(ax), ax.size, t)
+            assert _eq(a, b), (k, t)
+
+
+@pytest.mark.parametrize("name", ["f", "bilinear_f", "bicubic_f"])
+def test_point_kernels_match_reference(oracle, ref, name):
+    rng = np.random.default_rng(5)
+    ix, iy, iz = 23, 17, 4
+    fld = rng.normal(size=(iz, iy, ix)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.05] = np.nan
+    fo, fr = getattr(oracle, "orc_get_values_" + name), getattr(ref, "mifi_get_values_" + name)
+    xs = rng.uniform(-2, ix + 1, 20000)
+    ys = rng.uniform(-2, iy + 1, 20000)
+    xs[:4000] = np.round(xs[:4000] * 2) / 2  # half-integers and integers: the rounding edge cases
+    ys[:4000] = np.round(ys[:4000] * 2) / 2
+    a, b = np.zeros(iz, np.float32), np.zeros(iz, np.float32)
+    for x, y in zip(xs, ys):
+        if name == "bilinear_f" and (iy - 0.5 <= y < iy + 0.5) and not (0 <= np.floor(x) and np.floor(x) + 1 < ix):
+            continue  # the reference reads out of bounds there (interpolation.c:322); defined as NaN in oracle and CUDA
+        fo(fp(fld), fp(a), x, y, ix, iy, iz)
+        fr(fp(fld), fp(b), x, y, ix, iy, iz)
+        assert _eq(a, b), (x, y)
+
+
+@pytest.mark.parametrize("name", ["nearest", "linear", "linear_weak_extrapol", "linear_no_extrapol", "linear_const_extrapol", "log", "log_log"])
+def test_two_level_kernels_match_reference(oracle, ref, name):
+    rng = np.random.default_rng(7)
+    fo, fr = getattr(oracle, f"orc_get_values_{name}_f"), getattr(ref, f"mifi_get_values_{name}_f")
+    n = 64
+    for _ in range(300):
+        A = rng.normal(size=n).astype(np.float32)
+        B = rng.normal(size=n).astype(np.float32)
+        A[rng.random(n) < 0.1] = np.nan
+        xa, xb = rng.uniform(1, 1000, 2)
+        x = rng.choice([xa, xb, rng.uniform(-100, 1500), (xa + xb) / 2])
+        if rng.random() < 0.05:
+            xb = xa
+        o1 = np.full(n, 777, np.float32)
+        o2 = np.full(n, 777, np.float32)
+        r1 = fo(fp(A), fp(B), fp(o1), n, xa, xb, x)
+        r2 = fr(fp(A), fp(B), fp(o2), n, xa, xb, x)
+        assert r1 == r2 and _eq(o1, o2)
+
+
+def _tables(rng, in_x, in_y, out_x, out_y, margin=3.0):
+    """index tables with points inside, on the borders and outside"""
+    px = rng.uniform(-margin, in_x - 1 + margin, out_x * out_y)
+    py = rng.uniform(-margin, in_y - 1 + margin, out_x * out_y)
+    k = out_x * out_y // 10
+    px[:k] = np.round(px[:k] * 2) / 2
+    py[:k] = np.round(py[:k] * 2) / 2
+    px[k:k + 5] = -999.
+    py[k:k + 5] = -999.
+    # keep clear of the reference's out-of-bounds corner strip (interpolation.c:322)
+    strip = (py >= in_y - 0.5) & (py < in_y + 0.5) & ~((np.floor(px) >= 0) & (np.floor(px) + 1 < in_x))
+    py[strip] += 1.0
+    return px, py
+
+
+@pytest.mark.parametrize("method", [ol.BILINEAR, ol.BICUBIC, ol.NEAREST])
+@pytest.mark.parametrize("window", ["full", "reduced"])
+def test_cached_apply_matches_reference(oracle, ref, method, window):
+    rng = np.random.default_rng(100 + method)
+    in_x, in_y, out_x, out_y, nz = 61, 47, 53, 39, 3
+    px, py = _tables(rng, in_x, in_y, out_x, out_y)
+    if window == "reduced":  # targets cover only part of the source -> reduced domain kicks in
+        px = 10 + px * 0.4
+        py = 8 + py * 0.5
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.03] = np.nan
+    o, oi = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, fld)
+    r, ri = ol.r_cached_apply(method, px, py, in_x, in_y, out_x, out_y, fld)
+    assert oi == ri
+    if window == "reduced":
+        assert oi["reduced"] and (oi["inX"] < in_x and oi["inY"] < in_y)
+    # (the bilinear/bicubic cache always records a "reduced" domain, even one that spans the whole grid,
+    #  CachedInterpolation.cc:236-252)
+    assert _eq(o, r)
+
+
+@pytest.mark.parametrize("method", [ol.FWD_SUM, ol.FWD_MEAN, ol.FWD_MEDIAN, ol.FWD_MAX, ol.FWD_MIN, ol.FWD_UNDEF_SUM, ol.FWD_UNDEF_MEAN,
+                                    ol.FWD_UNDEF_MAX, ol.FWD_UNDEF_MIN])
+def test_forward_matches_reference(oracle, ref, method):
+    rng = np.random.default_rng(200 + method)
+    in_x, in_y, out_x, out_y, nz = 83, 59, 21, 17, 2
+    # every source cell gets a target position; several sources per target cell, some outside
+    pox = rng.uniform(-2, out_x + 1, in_x * in_y)
+    poy = rng.uniform(-2, out_y + 1, in_x * in_y)
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.1] = np.nan
+    o, oi = ol.o_cached_apply(method, pox, poy, in_x, in_y, out_x, out_y, fld, level_bug=1)
+    r, ri = ol.r_cached_apply(method, pox, poy, in_x, in_y, out_x, out_y, fld)
+    assert oi == ri
+    assert _eq(o, r)
+    # the reference aggregates input level 0 into every output level
+    assert _eq(r[0], r[1])
+
+
+def test_forward_reduced_window_matches_reference(oracle, ref):
+    rng = np.random.default_rng(31)
+    in_x, in_y, out_x, out_y = 90, 70, 12, 10
+    pox = rng.uniform(-40, out_x + 40, in_x * in_y)  # most sources fall outside the target
+    poy = rng.uniform(-40, out_y + 40, in_x * in_y)
+    gx, gy = np.meshgrid(np.arange(in_x), np.arange(in_y))
+    keep = ((gx > 20) & (gx < 60) & (gy > 15) & (gy < 50)).ravel()
+    pox[~keep] = -500.
+    fld = rng.normal(size=(1, in_y, in_x)).astype(np.float32)
+    o, oi = ol.o_cached_apply(ol.FWD_MEAN, pox, poy, in_x, in_y, out_x, out_y, fld)
+    r, ri = ol.r_cached_apply(ol.FWD_MEAN, pox, poy, in_x, in_y, out_x, out_y, fld)
+    assert oi == ri and oi["reduced"]
+    assert _eq(o, r)
+
+
+def test_round_and_clamp_matches_reference(oracle, ref):
+    vals = [-1.0, -0.5, -0.49999, -0.0, 0.0, 0.49999, 0.5, 1.5, 2.5, 9.4999, 9.5, 10.0, 1e12, -1e12]  # NaN: undefined behaviour in the reference (double -> size_t)
+    for v in vals:
+        assert oracle.orc_round_and_clamp(v, 0, 9, ol.INVALID_IDX) == ref.ref_round_and_clamp(v, 0, 9, ol.INVALID_IDX), v
+
+
+def test_neighbor_search_matches_reference(oracle, ref):
+    rng = np.random.default_rng(3)
+    for _ in range(2000):
+        n = int(rng.integers(1, 12))
+        col = rng.choice([1., 2., 3., 5., 8., 13., -4., 0.5], n).astype(np.float32) if rng.random() < 0.5 else np.sort(
+            rng.uniform(0, 1000, n)).astype(np.float32)
+        if rng.random() < 0.5:
+            col = col[::-1].copy()
+        x = float(rng.choice(np.concatenate([col, rng.uniform(-10, 1100, 3).astype(np.float32)])))
+        for fo, fr in ((oracle.orc_find_closest_neighbor_distinct_elements, ref.ref_find_closest_neighbor_distinct_elements),
+                       (oracle.orc_find_closest_distinct_elements, ref.ref_find_closest_distinct_elements)):
+            a0, a1 = C.c_size_t(), C.c_size_t()
+            b0, b1 = C.c_long(), C.c_long()
+            fo(fp(col), n, 1, x, C.byref(a0), C.byref(a1))
+            fr(fp(col), n, 1, x, C.byref(b0), C.byref(b1))
+            assert (a0.value, a1.value) == (b0.value, b1.value), (col, x)
+
+
+def test_vector_rotation_matches_reference(oracle, ref):
+    rng = np.random.default_rng(9)
+    ox, oy, nz = 31, 17, 3
+    ang = rng.uniform(-np.pi, np.pi, ox * oy)
+    m = np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy()
+    u = rng.normal(size=(nz, oy, ox)).astype(np.float32)
+    v = rng.normal(size=(nz, oy, ox)).astype(np.float32)
+    u[0, 0, :3] = np.nan
+    u1, v1, u2, v2 = u.copy(), v.copy(), u.copy(), v.copy()
+    oracle.orc_vector_reproject_values_by_matrix_f(dp(m), ox * oy, fp(u1), fp(v1), nz)
+    ref.ref_vector_reproject_values_by_matrix_f(dp(m), ox, oy, fp(u2), fp(v2), nz)
+    assert _eq(u1, u2) and _eq(v1, v2)
+    d = rng.uniform(0, 360, size=(nz, oy, ox)).astype(np.float32)
+    d1, d2 = d.copy(), d.copy()
+    oracle.orc_vector_reproject_direction_by_matrix_f(dp(m), ox * oy, fp(d1), nz)
+    ref.ref_vector_reproject_direction_by_matrix_f(dp(m), ox, oy, fp(d2), nz)
+    assert _eq(d1, d2)
+
+
+def test_reproject_matrix_restatement_matches_reference_logic(oracle, ref):
+    """reproject.cc's matrix logic (compiled unmodified over the proj.h shim) against its restatement."""
+    lcc = b"+proj=lcc +lat_0=63.3 +lon_0=15 +lat_1=63.3 +lat_2=63.3 +no_defs +R=6.371e+06"
+    stere = b"+proj=stere +lat_0=90 +lon_0=0 +lat_ts=60 +R=6.371e+06 +no_defs"
+    ll = b"+proj=latlong +R=6.371e+06 +no_defs"
+    lon = np.arange(-10., 40., 2.5)
+    lat = np.arange(52., 74., 2.)
+    xs = np.arange(-8e5, 8e5, 1e5)
+    ys = np.arange(-3.2e6, -1.6e6, 1e5)
+    for src, dst, ax, ay in ((lcc, ll, lon, lat), (lcc, stere, xs, ys), (ll, stere, xs, ys)):
+        a = np.zeros(ax.size * ay.size * 3)
+        b = np.zeros_like(a)
+        assert oracle.orc_get_vector_reproject_matrix(src, dst, dp(ax), dp(ay), ax.size, ay.size, dp(a)) == 0
+        assert ref.ref_get_vector_reproject_matrix(src, dst, dp(ax), dp(ay), ax.size, ay.size, dp(b)) == 0
+        assert _eq(a, b)
+    ox_, oy_ = np.zeros(lon.size * lat.size), np.zeros(lon.size * lat.size)
+    rx_, ry_ = np.zeros_like(ox_), np.zeros_like(oy_)
+    oracle.orc_reproject_axes(ll, lcc, dp(lon), dp(lat), lon.size, lat.size, dp(ox_), dp(oy_))
+    ref.ref_reproject_axes(ll, lcc, dp(lon), dp(lat), lon.size, lat.size, dp(rx_), dp(ry_))
+    assert _eq(ox_, rx_) and _eq(oy_, ry_)
