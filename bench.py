@@ -206,19 +206,26 @@ def main_b200(args):
     inx, iny = ci.getInX(), ci.getInY()
     rd = ci.reducedDomain()
     n_slabs = 3  # distinct resident inputs, rotated: every step reads 264 MB and writes 767 MB, both far beyond the 126 MB L2
+    # HBM layout of resident slabs: rows padded to 32 B (source) / 128 B (target), see DESIGN.md "data layout";
+    # FIMEXCU_BENCH_DENSE=1 times the reference's dense [z][y][x] layout instead.
+    dense = os.environ.get("FIMEXCU_BENCH_DENSE") == "1"
     slabs = []
     for k in range(n_slabs):
         full = S.meps_slab_torch(t=rank * 1000 + k, device="cuda")
-        slabs.append(ci.reduceInput(full, S.MEPS_NX, S.MEPS_NY) if rd else full)
-        del full
-    outs = [torch.empty((nz, oy, ox), dtype=torch.float32, device="cuda") for _ in range(2)]
+        sub = ci.reduceInput(full, S.MEPS_NX, S.MEPS_NY) if rd else full
+        slabs.append(sub if dense else ci.toPadded(sub))
+        del full, sub
+    ip, il, op, ol = ci.paddedLayout()
+    if dense:
+        ip, il, op, ol = inx, inx * iny, ox, ox * oy
+    outs = [torch.empty((nz, oy, op), dtype=torch.float32, device="cuda") for _ in range(2)]
     stream = _lib.current_stream_ptr()
     points_per_step = nz * ox * oy
     launches = 0
 
     def step(i):
-        _lib.check(lib.fimexcu_cache_apply_dev_f(ci._h, slabs[i % n_slabs].data_ptr(), nz, outs[i % 2].data_ptr(), float("nan"), float("nan"),
-                                                 stream), "apply")
+        _lib.check(lib.fimexcu_cache_apply_dev_strided_f(ci._h, slabs[i % n_slabs].data_ptr(), ip, il, nz, outs[i % 2].data_ptr(), op, ol,
+                                                         float("nan"), float("nan"), stream), "apply")
 
     def barrier():
         if world > 1:
@@ -253,30 +260,33 @@ def main_b200(args):
     my_ms = ms_total / args.steps  # this rank's mean launch duration (one launch per step)
     achieved = alg_bytes / (my_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "kernel": "fxcu::bilinear_apply_kernel", "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
+                "kernel": "fxcu::bilinear_apply_tma_kernel" if not os.environ.get("FIMEXCU_NO_TMA") else "fxcu::bilinear_apply_kernel", "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                 "bytes_per_point": alg_bytes / points_per_step}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
         try:
-            roofline["traffic"] = json.load(open(prof)).get("bilinear_apply_kernel_dram_bytes_per_launch")
+            roofline["traffic"] = json.load(open(prof)).get("bilinear_apply_tma_kernel_dram_bytes_per_launch")
         except Exception:
             pass
 
     # end to end through the host-pointer entry point: pinned host slab in, pinned host result out
     e2e = None
     if not args.no_e2e:
-        in_bytes, out_bytes = slabs[0].numel() * 4, points_per_step * 4
+        n_in = nz * iny * inx
+        in_bytes, out_bytes = n_in * 4, points_per_step * 4
         h_in = lib.fimexcu_host_alloc(in_bytes)
         h_out = lib.fimexcu_host_alloc(out_bytes)
         if not h_in or not h_out:
             raise RuntimeError("pinned allocation failed: " + _lib.last_error())
-        _lib.check(lib.fimexcu_memcpy_d2h(h_in, slabs[0].data_ptr(), in_bytes), "d2h")
+        dense_in = slabs[0] if dense else slabs[0][:, :, :inx].contiguous()
+        _lib.check(lib.fimexcu_memcpy_d2h(h_in, dense_in.data_ptr(), in_bytes), "d2h")
+        del dense_in
         import ctypes as C
         new_size = C.c_size_t()
         e2e_steps = max(2, min(args.steps, 6))
 
         def e2e_step():
-            _lib.check(lib.fimexcu_cache_apply_f(ci._h, h_in, slabs[0].numel(), h_out, C.byref(new_size), float("nan"), float("nan")), "apply_f")
+            _lib.check(lib.fimexcu_cache_apply_f(ci._h, h_in, n_in, h_out, C.byref(new_size), float("nan"), float("nan")), "apply_f")
 
         e2e_step()
         barrier()
@@ -316,7 +326,8 @@ def main_b200(args):
             "config": {"workload": f"BASELINE configs[1]: synthetic MEPS Lambert 949x1069 x 65 levels f32 -> {args.target} 0.025deg lat/lon "
                                    f"({ox}x{oy}), cached bilinear, one time-step slab ({points_per_step / 1e6:.1f} Mpoints) per step per GPU",
                        "reduced_source_window": [inx, iny], "sharding": f"independent time-step slabs, {world} rank(s), no collective",
-                       "l2": "inputs larger than L2: 3 rotating 264 MB source slabs, 767 MB written per step (L2 126 MB)"},
+                       "l2": "inputs larger than L2: 3 rotating 264 MB source slabs, 767 MB written per step (L2 126 MB)",
+                       "hbm_layout": "dense [z][y][x]" if dense else f"rows padded: source pitch {ip} (32 B), target pitch {op} (128 B)"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)

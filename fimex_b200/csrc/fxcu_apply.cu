@@ -250,6 +250,24 @@ __global__ void __launch_bounds__(256) rebase_nn_kernel(int* __restrict__ idx, s
 // ------------------------------------------------------------------------------------------------
 // apply kernels
 // ------------------------------------------------------------------------------------------------
+// All apply kernels share one parameter block.  Layouts are given by element strides so that the same kernels
+// serve the dense layout of the reference ([z][y][x], pitch == width) and the padded device-resident layout
+// (rows on 128 B boundaries) that lets every warp store be one aligned line and lets TMA describe the source.
+struct ApplyParams {
+    const int* off;
+    const void* wx;
+    const void* wy;
+    const float* in;
+    float* out;
+    int outX, outY, nz, zchunk;
+    int inX;       // row length the table offsets refer to (the cache's reduced window)
+    int inPitch;   // elements between source rows
+    size_t inLevel;  // elements between source levels
+    int outPitch;  // elements between target rows
+    size_t outLevel; // elements between target levels
+    float bad, fill;
+};
+
 template <bool BAD>
 __device__ __forceinline__ float load_in(const float* __restrict__ p, float bad)
 {
@@ -267,88 +285,123 @@ __device__ __forceinline__ void store_out(float* __restrict__ p, float v, float 
     __stcs(p, v); // written once, never re-read by this kernel: keep L2 for the source planes
 }
 
-// K4.  One thread per target xy, blockIdx.y selects a chunk of levels; table entry in registers for all
-// its levels.  Consecutive threads -> consecutive targets -> coalesced 128 B stores per warp and level.
-template <bool BAD, bool FILL>
-__global__ void __launch_bounds__(256) bilinear_apply_kernel(const int* __restrict__ off, const float* __restrict__ wx, const float* __restrict__ wy,
-                                                             const float* __restrict__ in, float* __restrict__ out, size_t nxy, int nz, int zchunk,
-                                                             size_t inLayer, int inX, float bad, float fill)
+// thread -> target cell of a 32 x 8 tile; returns false outside the grid
+__device__ __forceinline__ bool tile_cell(const ApplyParams& P, int& ox, int& oy)
 {
-    const size_t o = blockIdx.x * 256ull + threadIdx.x;
-    if (o >= nxy)
+    ox = blockIdx.x * 32 + (threadIdx.x & 31);
+    oy = blockIdx.y * 8 + (threadIdx.x >> 5);
+    return ox < P.outX && oy < P.outY;
+}
+
+// table offset (relative to a dense inX-wide level) -> offset in the pitched source level
+__device__ __forceinline__ int source_offset(const ApplyParams& P, int f)
+{
+    if (P.inPitch == P.inX)
+        return f;
+    const int y = f / P.inX;
+    return y * P.inPitch + (f - y * P.inX);
+}
+
+__device__ __forceinline__ float blend4(float s00, float s01, float s10, float s11, float fx, float fy, float omx, float omy)
+{
+    const float top = __fadd_rn(__fmul_rn(omx, s00), __fmul_rn(fx, s01));
+    const float bot = __fadd_rn(__fmul_rn(omx, s10), __fmul_rn(fx, s11));
+    return __fadd_rn(__fmul_rn(omy, top), __fmul_rn(fy, bot));
+}
+
+// value from 4 taps where a switched-off direction aliases the first tap (edge rules of interpolation.c:289-328)
+__device__ __forceinline__ float bilinear_value(float s00, float s01, float s10, float s11, float fx, float fy)
+{
+    if (fx >= 0.f && fy >= 0.f)
+        return blend4(s00, s01, s10, s11, fx, fy, __fsub_rn(1.f, fx), __fsub_rn(1.f, fy));
+    if (fx >= 0.f)
+        return __fadd_rn(__fmul_rn(__fsub_rn(1.f, fx), s00), __fmul_rn(fx, s01));
+    if (fy >= 0.f)
+        return __fadd_rn(__fmul_rn(__fsub_rn(1.f, fy), s00), __fmul_rn(fy, s10));
+    return s00;
+}
+
+// K4, direct-gather form.  One thread per target cell of a 32 x 8 tile, blockIdx.z selects a chunk of levels; the
+// table entry stays in registers for all its levels.  Used for small grids, for sources TMA cannot describe
+// (unaligned base or pitch) and for tiles whose source footprint does not fit the staged kernel's box.
+template <bool BAD, bool FILL>
+__global__ void __launch_bounds__(256) bilinear_apply_kernel(const ApplyParams P)
+{
+    int ox, oy;
+    if (!tile_cell(P, ox, oy))
         return;
-    const int z0 = blockIdx.y * zchunk;
-    const int z1 = min(nz, z0 + zchunk);
-    const int f = off[o];
-    const float fx = wx[o], fy = wy[o];
-    float* po = out + static_cast<size_t>(z0) * nxy + o;
+    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const int z0 = blockIdx.z * P.zchunk;
+    const int z1 = min(P.nz, z0 + P.zchunk);
+    const int f = P.off[o];
+    const float fx = static_cast<const float*>(P.wx)[o], fy = static_cast<const float*>(P.wy)[o];
+    float* po = P.out + static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
     if (f < 0) {
-        for (int z = z0; z < z1; ++z, po += nxy)
-            store_out<FILL>(po, nan_f(), fill);
+        for (int z = z0; z < z1; ++z, po += P.outLevel)
+            store_out<FILL>(po, nan_f(), P.fill);
         return;
     }
-    const float* p = in + static_cast<size_t>(z0) * inLayer + f;
+    const float* p = P.in + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
+    const int inX = P.inPitch;
     if (fx >= 0.f && fy >= 0.f) {
         const float omx = __fsub_rn(1.f, fx), omy = __fsub_rn(1.f, fy);
 #pragma unroll 4
-        for (int z = z0; z < z1; ++z, p += inLayer, po += nxy) {
-            const float s00 = load_in<BAD>(p, bad), s01 = load_in<BAD>(p + 1, bad);
-            const float s10 = load_in<BAD>(p + inX, bad), s11 = load_in<BAD>(p + inX + 1, bad);
-            const float top = __fadd_rn(__fmul_rn(omx, s00), __fmul_rn(fx, s01));
-            const float bot = __fadd_rn(__fmul_rn(omx, s10), __fmul_rn(fx, s11));
-            store_out<FILL>(po, __fadd_rn(__fmul_rn(omy, top), __fmul_rn(fy, bot)), fill);
+        for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel) {
+            const float s00 = load_in<BAD>(p, P.bad), s01 = load_in<BAD>(p + 1, P.bad);
+            const float s10 = load_in<BAD>(p + inX, P.bad), s11 = load_in<BAD>(p + inX + 1, P.bad);
+            store_out<FILL>(po, blend4(s00, s01, s10, s11, fx, fy, omx, omy), P.fill);
         }
     } else if (fx >= 0.f) { // linear in x on the nearest row (interpolation.c:289-299)
         const float omx = __fsub_rn(1.f, fx);
 #pragma unroll 4
-        for (int z = z0; z < z1; ++z, p += inLayer, po += nxy) {
-            const float s00 = load_in<BAD>(p, bad), s01 = load_in<BAD>(p + 1, bad);
-            store_out<FILL>(po, __fadd_rn(__fmul_rn(omx, s00), __fmul_rn(fx, s01)), fill);
+        for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel) {
+            const float s00 = load_in<BAD>(p, P.bad), s01 = load_in<BAD>(p + 1, P.bad);
+            store_out<FILL>(po, __fadd_rn(__fmul_rn(omx, s00), __fmul_rn(fx, s01)), P.fill);
         }
     } else if (fy >= 0.f) { // linear in y on the nearest column (:311-319)
         const float omy = __fsub_rn(1.f, fy);
 #pragma unroll 4
-        for (int z = z0; z < z1; ++z, p += inLayer, po += nxy) {
-            const float s00 = load_in<BAD>(p, bad), s10 = load_in<BAD>(p + inX, bad);
-            store_out<FILL>(po, __fadd_rn(__fmul_rn(omy, s00), __fmul_rn(fy, s10)), fill);
+        for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel) {
+            const float s00 = load_in<BAD>(p, P.bad), s10 = load_in<BAD>(p + inX, P.bad);
+            store_out<FILL>(po, __fadd_rn(__fmul_rn(omy, s00), __fmul_rn(fy, s10)), P.fill);
         }
     } else { // nearest cell (:321-328)
 #pragma unroll 4
-        for (int z = z0; z < z1; ++z, p += inLayer, po += nxy)
-            store_out<FILL>(po, load_in<BAD>(p, bad), fill);
+        for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel)
+            store_out<FILL>(po, load_in<BAD>(p, P.bad), P.fill);
     }
 }
 
 // K5.  Same mapping; 16 taps, weights in f64, the four column sums added into the f32 result one at a
 // time (interpolation.c:388-406).
 template <bool BAD, bool FILL>
-__global__ void __launch_bounds__(256) bicubic_apply_kernel(const int* __restrict__ off, const double* __restrict__ fxs, const double* __restrict__ fys,
-                                                            const float* __restrict__ in, float* __restrict__ out, size_t nxy, int nz, int zchunk,
-                                                            size_t inLayer, int inX, float bad, float fill)
+__global__ void __launch_bounds__(256) bicubic_apply_kernel(const ApplyParams P)
 {
-    const size_t o = blockIdx.x * 256ull + threadIdx.x;
-    if (o >= nxy)
+    int ox, oy;
+    if (!tile_cell(P, ox, oy))
         return;
-    const int z0 = blockIdx.y * zchunk;
-    const int z1 = min(nz, z0 + zchunk);
-    const int f = off[o];
-    float* po = out + static_cast<size_t>(z0) * nxy + o;
+    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const int z0 = blockIdx.z * P.zchunk;
+    const int z1 = min(P.nz, z0 + P.zchunk);
+    const int f = P.off[o];
+    float* po = P.out + static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
     if (f < 0) {
-        for (int z = z0; z < z1; ++z, po += nxy)
-            store_out<FILL>(po, nan_f(), fill);
+        for (int z = z0; z < z1; ++z, po += P.outLevel)
+            store_out<FILL>(po, nan_f(), P.fill);
         return;
     }
     double wxv[4], wyv[4];
-    cubic_weights(fxs[o], wxv);
-    cubic_weights(fys[o], wyv);
-    const float* p = in + static_cast<size_t>(z0) * inLayer + f;
-    for (int z = z0; z < z1; ++z, p += inLayer, po += nxy) {
+    cubic_weights(static_cast<const double*>(P.wx)[o], wxv);
+    cubic_weights(static_cast<const double*>(P.wy)[o], wyv);
+    const float* p = P.in + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
+    const int inX = P.inPitch;
+    for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel) {
         float v[4][4];
 #pragma unroll
         for (int j = 0; j < 4; ++j)
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-                v[j][i] = load_in<BAD>(p + j * inX + i, bad);
+                v[j][i] = load_in<BAD>(p + j * inX + i, P.bad);
         float acc = 0.f;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -358,89 +411,343 @@ __global__ void __launch_bounds__(256) bicubic_apply_kernel(const int* __restric
                 col = __dadd_rn(col, __dmul_rn(wxv[i], static_cast<double>(v[j][i])));
             acc = __double2float_rn(__dadd_rn(static_cast<double>(acc), __dmul_rn(col, wyv[j])));
         }
-        store_out<FILL>(po, acc, fill);
+        store_out<FILL>(po, acc, P.fill);
     }
 }
 
 // K6.  Pure gather.
 template <bool BAD, bool FILL>
-__global__ void __launch_bounds__(256) nearest_apply_kernel(const int* __restrict__ idx, const float* __restrict__ in, float* __restrict__ out,
-                                                            size_t nxy, int nz, int zchunk, size_t inLayer, float bad, float fill)
+__global__ void __launch_bounds__(256) nearest_apply_kernel(const ApplyParams P)
 {
-    const size_t o = blockIdx.x * 256ull + threadIdx.x;
-    if (o >= nxy)
+    int ox, oy;
+    if (!tile_cell(P, ox, oy))
         return;
-    const int z0 = blockIdx.y * zchunk;
-    const int z1 = min(nz, z0 + zchunk);
-    const int f = idx[o];
-    float* po = out + static_cast<size_t>(z0) * nxy + o;
+    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const int z0 = blockIdx.z * P.zchunk;
+    const int z1 = min(P.nz, z0 + P.zchunk);
+    const int f = P.off[o];
+    float* po = P.out + static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
     if (f < 0) {
-        for (int z = z0; z < z1; ++z, po += nxy)
-            store_out<FILL>(po, nan_f(), fill);
+        for (int z = z0; z < z1; ++z, po += P.outLevel)
+            store_out<FILL>(po, nan_f(), P.fill);
         return;
     }
-    const float* p = in + static_cast<size_t>(z0) * inLayer + f;
+    const float* p = P.in + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
 #pragma unroll 4
-    for (int z = z0; z < z1; ++z, p += inLayer, po += nxy)
-        store_out<FILL>(po, load_in<BAD>(p, bad), fill);
+    for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel)
+        store_out<FILL>(po, load_in<BAD>(p, P.bad), P.fill);
 }
 
-// Fused vector pass: bilinear u and v with one table read, then the rotation of reproject.cc:488-507, then the
-// stores.  Replaces four interpolateValues() calls and two reprojectValues() calls of the reference
-// (CDMInterpolator.cc:232-259 runs once for x_wind and once for y_wind).
-__device__ __forceinline__ float bilinear_value(const float s00, const float s01, const float s10, const float s11, float fx, float fy)
+// ------------------------------------------------------------------------------------------------
+// K4, staged form (the headline kernel): warp-specialised TMA pipeline.
+//   CTA = 8 consumer warps + 1 producer warp, target tile 32 x 8 (one row segment per consumer warp, so a warp
+//   store is one 128 B line when the target rows sit on 128 B boundaries).  The CTA finds the bounding box of
+//   the source cells its tile needs; the producer warp streams that box, TMA_ZB levels per stage, into a ring of
+//   shared-memory stages with cp.async.bulk.tensor (3-D tensor map over [level][row][col]) and full/empty
+//   mbarriers; consumers gather their four taps with LDS and never touch the global-load path.
+//   Tiles whose footprint exceeds the box (strong shear / coarsening) use direct gathers instead.
+// ------------------------------------------------------------------------------------------------
+constexpr int TMA_BW = 32;    // box width  (source columns): one shared-memory row == 32 banks
+constexpr int TMA_BH = 16;    // box height (source rows)
+constexpr int TMA_ZB = 4;     // levels per stage
+constexpr int TMA_STAGES = 3; // ring depth
+constexpr int TMA_TH = 8;     // consumer warps == tile rows
+constexpr int TMA_THREADS = 32 * TMA_TH + 32;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count)
 {
-    if (fx >= 0.f && fy >= 0.f) {
-        const float omx = __fsub_rn(1.f, fx), omy = __fsub_rn(1.f, fy);
-        const float top = __fadd_rn(__fmul_rn(omx, s00), __fmul_rn(fx, s01));
-        const float bot = __fadd_rn(__fmul_rn(omx, s10), __fmul_rn(fx, s11));
-        return __fadd_rn(__fmul_rn(omy, top), __fmul_rn(fy, bot));
-    }
-    if (fx >= 0.f)
-        return __fadd_rn(__fmul_rn(__fsub_rn(1.f, fx), s00), __fmul_rn(fx, s01));
-    if (fy >= 0.f)
-        return __fadd_rn(__fmul_rn(__fsub_rn(1.f, fy), s00), __fmul_rn(fy, s10));
-    return s00;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity)
+{
+    uint32_t ok = 0;
+    const uint32_t addr = smem_u32(bar);
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(addr), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int x, int y, int z)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(smem_u32(dst)),
+                 "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y), "r"(z)
+                 : "memory");
+}
+
+template <bool BAD>
+__device__ __forceinline__ float tap(const float* t, int i, float bad)
+{
+    float v = t[i];
+    if (BAD && v == bad)
+        v = nan_f();
+    return v;
+}
+
+template <bool BAD, bool FILL>
+__global__ void __launch_bounds__(TMA_THREADS, 6) bilinear_apply_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ApplyParams P)
+{
+    constexpr int STAGE_FLOATS = TMA_BW * TMA_BH * TMA_ZB;
+    constexpr int LVL = TMA_BW * TMA_BH;
+    __shared__ __align__(128) float tile[TMA_STAGES][STAGE_FLOATS];
+    __shared__ __align__(8) uint64_t full[TMA_STAGES];
+    __shared__ __align__(8) uint64_t empty[TMA_STAGES];
+    __shared__ int red[4][TMA_TH];
+    __shared__ int bbox[4];
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const bool consumer = warp < TMA_TH;
+    const int ox = blockIdx.x * 32 + lane, oy = blockIdx.y * TMA_TH + warp;
+    const bool in_grid = consumer && ox < P.outX && oy < P.outY;
+    int f = -1;
+    float fx = -1.f, fy = -1.f;
+    if (in_grid) {
+        const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+        f = P.off[o];
+        fx = static_cast<const float*>(P.wx)[o];
+        fy = static_cast<const float*>(P.wy)[o];
+    }
+    int x0 = 0x3fffffff, y0 = 0x3fffffff, x1 = -1, y1 = -1;
+    if (f >= 0) {
+        y0 = f / P.inX;
+        x0 = f - y0 * P.inX;
+        x1 = x0 + (fx >= 0.f ? 1 : 0);
+        y1 = y0 + (fy >= 0.f ? 1 : 0);
+    }
+    const bool interior = (f < 0) || (fx >= 0.f && fy >= 0.f);
+    int lox = x0, loy = y0, hix = x1, hiy = y1;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        lox = min(lox, __shfl_xor_sync(0xffffffffu, lox, s));
+        loy = min(loy, __shfl_xor_sync(0xffffffffu, loy, s));
+        hix = max(hix, __shfl_xor_sync(0xffffffffu, hix, s));
+        hiy = max(hiy, __shfl_xor_sync(0xffffffffu, hiy, s));
+    }
+    if (consumer && lane == 0) {
+        red[0][warp] = lox;
+        red[1][warp] = loy;
+        red[2][warp] = hix;
+        red[3][warp] = hiy;
+    }
+    if (tid == 0) {
+        for (int s = 0; s < TMA_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], TMA_TH);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    const int all_interior = __syncthreads_and(interior ? 1 : 0);
+    if (tid == 0) {
+        int a = red[0][0], b = red[1][0], c = red[2][0], d = red[3][0];
+        for (int w = 1; w < TMA_TH; ++w) {
+            a = min(a, red[0][w]);
+            b = min(b, red[1][w]);
+            c = max(c, red[2][w]);
+            d = max(d, red[3][w]);
+        }
+        bbox[0] = a & ~7; // box starts on a 32 B sector
+        bbox[1] = b;
+        bbox[2] = c;
+        bbox[3] = d;
+    }
+    __syncthreads();
+    const int bx0 = bbox[0], by0 = bbox[1], bx1 = bbox[2], by1 = bbox[3];
+    float* po = P.out + static_cast<size_t>(oy) * P.outPitch + ox;
+    if (bx1 < 0) { // nothing defined in this tile
+        if (in_grid)
+            for (int z = 0; z < P.nz; ++z, po += P.outLevel)
+                store_out<FILL>(po, nan_f(), P.fill);
+        return;
+    }
+    if (!((bx1 - bx0 + 1 <= TMA_BW) && (by1 - by0 + 1 <= TMA_BH))) { // footprint too large: direct gathers
+        if (!in_grid)
+            return;
+        if (f < 0) {
+            for (int z = 0; z < P.nz; ++z, po += P.outLevel)
+                store_out<FILL>(po, nan_f(), P.fill);
+            return;
+        }
+        const int dxg = fx >= 0.f ? 1 : 0, dyg = fy >= 0.f ? P.inPitch : 0;
+        const float* p = P.in + static_cast<size_t>(y0) * P.inPitch + x0;
+#pragma unroll 4
+        for (int z = 0; z < P.nz; ++z, p += P.inLevel, po += P.outLevel)
+            store_out<FILL>(po, bilinear_value(load_in<BAD>(p, P.bad), load_in<BAD>(p + dxg, P.bad), load_in<BAD>(p + dyg, P.bad),
+                                               load_in<BAD>(p + dyg + dxg, P.bad), fx, fy),
+                            P.fill);
+        return;
+    }
+    constexpr unsigned BYTES = STAGE_FLOATS * sizeof(float);
+    const int niter = (P.nz + TMA_ZB - 1) / TMA_ZB;
+    if (!consumer) { // producer warp: one lane keeps the ring full
+        if (lane == 0) {
+            for (int it = 0; it < niter; ++it) {
+                const int s = it % TMA_STAGES;
+                mbar_wait(&empty[s], ((it / TMA_STAGES) & 1) ^ 1); // passes at once the first time round
+                mbar_expect_tx(&full[s], BYTES);
+                tma_load_3d(&tile[s][0], &tmap, &full[s], bx0, by0, it * TMA_ZB);
+            }
+        }
+        return;
+    }
+    const int r = (f >= 0) ? (y0 - by0) * TMA_BW + (x0 - bx0) : 0;
+    if (all_interior) {
+        // undefined targets carry NaN weights: every product is NaN, no select in the loop
+        const float wfx = (f >= 0) ? fx : nan_f(), wfy = (f >= 0) ? fy : nan_f();
+        const float omx = __fsub_rn(1.f, wfx), omy = __fsub_rn(1.f, wfy);
+        for (int it = 0; it < niter; ++it) {
+            const int s = it % TMA_STAGES;
+            mbar_wait(&full[s], (it / TMA_STAGES) & 1);
+            const float* t = &tile[s][r];
+#pragma unroll
+            for (int k = 0; k < TMA_ZB; ++k) {
+                const float v = blend4(tap<BAD>(t, k * LVL, P.bad), tap<BAD>(t, k * LVL + 1, P.bad), tap<BAD>(t, k * LVL + TMA_BW, P.bad),
+                                       tap<BAD>(t, k * LVL + TMA_BW + 1, P.bad), wfx, wfy, omx, omy);
+                if (in_grid && it * TMA_ZB + k < P.nz)
+                    store_out<FILL>(po + k * P.outLevel, v, P.fill);
+            }
+            po += TMA_ZB * P.outLevel;
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&empty[s]);
+        }
+    } else { // tiles on the rim of the source grid: per-thread edge rules
+        const int dxs = fx >= 0.f ? 1 : 0, dys = fy >= 0.f ? TMA_BW : 0;
+        for (int it = 0; it < niter; ++it) {
+            const int s = it % TMA_STAGES;
+            mbar_wait(&full[s], (it / TMA_STAGES) & 1);
+            const float* t = &tile[s][r];
+#pragma unroll
+            for (int k = 0; k < TMA_ZB; ++k) {
+                float v = nan_f();
+                if (f >= 0)
+                    v = bilinear_value(tap<BAD>(t, k * LVL, P.bad), tap<BAD>(t, k * LVL + dxs, P.bad), tap<BAD>(t, k * LVL + dys, P.bad),
+                                       tap<BAD>(t, k * LVL + dys + dxs, P.bad), fx, fy);
+                if (in_grid && it * TMA_ZB + k < P.nz)
+                    store_out<FILL>(po + k * P.outLevel, v, P.fill);
+            }
+            po += TMA_ZB * P.outLevel;
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&empty[s]);
+        }
+    }
+}
+
+// fraction of 32 x 8 target tiles whose source footprint fits the staged kernel's box (decides, once per cache,
+// whether the staged kernel is worth launching).  counts[0] = tiles with data, counts[1] = of those, tiles that fit
+__global__ void __launch_bounds__(256) tile_fit_kernel(const int* __restrict__ off, const float* __restrict__ wx, const float* __restrict__ wy, int outX,
+                                                       int outY, int inX, unsigned* __restrict__ counts)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ox = blockIdx.x * 32 + lane, oy = blockIdx.y * 8 + warp;
+    int x0 = 0x3fffffff, y0 = 0x3fffffff, x1 = -1, y1 = -1;
+    if (ox < outX && oy < outY) {
+        const size_t o = static_cast<size_t>(oy) * outX + ox;
+        const int f = off[o];
+        if (f >= 0) {
+            y0 = f / inX;
+            x0 = f - y0 * inX;
+            x1 = x0 + (wx[o] >= 0.f ? 1 : 0);
+            y1 = y0 + (wy[o] >= 0.f ? 1 : 0);
+        }
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        x0 = min(x0, __shfl_xor_sync(0xffffffffu, x0, s));
+        y0 = min(y0, __shfl_xor_sync(0xffffffffu, y0, s));
+        x1 = max(x1, __shfl_xor_sync(0xffffffffu, x1, s));
+        y1 = max(y1, __shfl_xor_sync(0xffffffffu, y1, s));
+    }
+    __shared__ int red[4][8];
+    if (lane == 0) {
+        red[0][warp] = x0;
+        red[1][warp] = y0;
+        red[2][warp] = x1;
+        red[3][warp] = y1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) {
+            x0 = min(x0, red[0][w]);
+            y0 = min(y0, red[1][w]);
+            x1 = max(x1, red[2][w]);
+            y1 = max(y1, red[3][w]);
+        }
+        if (x1 >= 0) {
+            atomicAdd(&counts[0], 1u);
+            if ((x1 - (x0 & ~7) + 1 <= TMA_BW) && (y1 - y0 + 1 <= TMA_BH))
+                atomicAdd(&counts[1], 1u);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused vector pass (direct-gather form): bilinear u and v with one table read, the rotation of
+// reproject.cc:488-507, then the stores.  Replaces four interpolateValues() calls and two reprojectValues()
+// calls of the reference (CDMInterpolator.cc:232-259 runs once for x_wind and once for y_wind).
+// ------------------------------------------------------------------------------------------------
+struct UvParams {
+    const double* cs;
+    const double* sn;
+    const float* vin;
+    float* vout;
+    float badV, fillV;
+};
 
 template <bool BAD, bool FILL, bool ROT>
-__global__ void __launch_bounds__(256) bilinear_uv_kernel(const int* __restrict__ off, const float* __restrict__ wx, const float* __restrict__ wy,
-                                                          const double* __restrict__ cs, const double* __restrict__ sn, const float* __restrict__ uin,
-                                                          const float* __restrict__ vin, float* __restrict__ uout, float* __restrict__ vout, size_t nxy,
-                                                          int nz, int zchunk, size_t inLayer, int inX, float badU, float badV, float fillU, float fillV)
+__global__ void __launch_bounds__(256) bilinear_uv_kernel(const ApplyParams P, const UvParams Q)
 {
-    const size_t o = blockIdx.x * 256ull + threadIdx.x;
-    if (o >= nxy)
+    int ox, oy;
+    if (!tile_cell(P, ox, oy))
         return;
-    const int z0 = blockIdx.y * zchunk;
-    const int z1 = min(nz, z0 + zchunk);
-    const int f = off[o];
-    const float fx = wx[o], fy = wy[o];
-    float* pu = uout + static_cast<size_t>(z0) * nxy + o;
-    float* pv = vout + static_cast<size_t>(z0) * nxy + o;
+    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const int z0 = blockIdx.z * P.zchunk;
+    const int z1 = min(P.nz, z0 + P.zchunk);
+    const int f = P.off[o];
+    const float fx = static_cast<const float*>(P.wx)[o], fy = static_cast<const float*>(P.wy)[o];
+    const size_t obase = static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
+    float* pu = P.out + obase;
+    float* pv = Q.vout + obase;
     if (f < 0) {
-        for (int z = z0; z < z1; ++z, pu += nxy, pv += nxy) {
-            store_out<FILL>(pu, nan_f(), fillU);
-            store_out<FILL>(pv, nan_f(), fillV);
+        for (int z = z0; z < z1; ++z, pu += P.outLevel, pv += P.outLevel) {
+            store_out<FILL>(pu, nan_f(), P.fill);
+            store_out<FILL>(pv, nan_f(), Q.fillV);
         }
         return;
     }
     double c = 1., s = 0.;
     if (ROT) {
-        c = cs[o];
-        s = sn[o];
+        c = Q.cs[o];
+        s = Q.sn[o];
     }
     // taps that a switched-off direction does not use alias the first tap (never read out of range)
     const int dx = fx >= 0.f ? 1 : 0;
-    const int dy = fy >= 0.f ? inX : 0;
-    const float* qu = uin + static_cast<size_t>(z0) * inLayer + f;
-    const float* qv = vin + static_cast<size_t>(z0) * inLayer + f;
+    const int dy = fy >= 0.f ? P.inPitch : 0;
+    const size_t ibase = static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
+    const float* qu = P.in + ibase;
+    const float* qv = Q.vin + ibase;
 #pragma unroll 2
-    for (int z = z0; z < z1; ++z, qu += inLayer, qv += inLayer, pu += nxy, pv += nxy) {
-        const float u00 = load_in<BAD>(qu, badU), u01 = load_in<BAD>(qu + dx, badU);
-        const float u10 = load_in<BAD>(qu + dy, badU), u11 = load_in<BAD>(qu + dy + dx, badU);
-        const float v00 = load_in<BAD>(qv, badV), v01 = load_in<BAD>(qv + dx, badV);
-        const float v10 = load_in<BAD>(qv + dy, badV), v11 = load_in<BAD>(qv + dy + dx, badV);
+    for (int z = z0; z < z1; ++z, qu += P.inLevel, qv += P.inLevel, pu += P.outLevel, pv += P.outLevel) {
+        const float u00 = load_in<BAD>(qu, P.bad), u01 = load_in<BAD>(qu + dx, P.bad);
+        const float u10 = load_in<BAD>(qu + dy, P.bad), u11 = load_in<BAD>(qu + dy + dx, P.bad);
+        const float v00 = load_in<BAD>(qv, Q.badV), v01 = load_in<BAD>(qv + dx, Q.badV);
+        const float v10 = load_in<BAD>(qv + dy, Q.badV), v11 = load_in<BAD>(qv + dy + dx, Q.badV);
         float u = bilinear_value(u00, u01, u10, u11, fx, fy);
         float v = bilinear_value(v00, v01, v10, v11, fx, fy);
         if (ROT) {
@@ -448,9 +755,17 @@ __global__ void __launch_bounds__(256) bilinear_uv_kernel(const int* __restrict_
             u = __double2float_rn(__dsub_rn(__dmul_rn(du, c), __dmul_rn(dv, s)));
             v = __double2float_rn(__dadd_rn(__dmul_rn(du, s), __dmul_rn(dv, c)));
         }
-        store_out<FILL>(pu, u, fillU);
-        store_out<FILL>(pv, v, fillV);
+        store_out<FILL>(pu, u, P.fill);
+        store_out<FILL>(pv, v, Q.fillV);
     }
+}
+
+// NaN -> fill over a dense array (used where the fill cannot be fused: bicubic/nearest u,v with rotation)
+__global__ void __launch_bounds__(256) fill_kernel(float* __restrict__ a, size_t n, float fill)
+{
+    for (size_t i = blockIdx.x * 256ull + threadIdx.x; i < n; i += 256ull * gridDim.x)
+        if (isnan(a[i]))
+            a[i] = fill;
 }
 
 // single-position variants with the reference signatures (one launch; levels across threads)
@@ -461,22 +776,12 @@ __global__ void point_kernel(int method, const float* __restrict__ in, float* __
         int off;
         float fx, fy;
         bilinear_entry(x, y, ix, iy, off, fx, fy);
+        const int dx = fx >= 0.f ? 1 : 0, dy = fy >= 0.f ? ix : 0;
         for (int z = threadIdx.x; z < iz; z += blockDim.x) {
             float r = nan_f();
             if (off >= 0) {
                 const float* p = in + z * layer + off;
-                if (fx >= 0.f && fy >= 0.f) {
-                    const float omx = __fsub_rn(1.f, fx), omy = __fsub_rn(1.f, fy);
-                    const float top = __fadd_rn(__fmul_rn(omx, p[0]), __fmul_rn(fx, p[1]));
-                    const float bot = __fadd_rn(__fmul_rn(omx, p[ix]), __fmul_rn(fx, p[ix + 1]));
-                    r = __fadd_rn(__fmul_rn(omy, top), __fmul_rn(fy, bot));
-                } else if (fx >= 0.f) {
-                    r = __fadd_rn(__fmul_rn(__fsub_rn(1.f, fx), p[0]), __fmul_rn(fx, p[1]));
-                } else if (fy >= 0.f) {
-                    r = __fadd_rn(__fmul_rn(__fsub_rn(1.f, fy), p[0]), __fmul_rn(fy, p[ix]));
-                } else {
-                    r = p[0];
-                }
+                r = bilinear_value(p[0], p[dx], p[dy], p[dy + dx], fx, fy);
             }
             out[z] = r;
         }
@@ -523,14 +828,13 @@ static long long clamp_ex(long long low, double v, long long extend, long long h
     return std::max(low, std::min(value, high));
 }
 
-// picks the number of level chunks (gridDim.y) so that small targets still fill the machine
-static int pick_zchunk(size_t nxy, int nz)
+// number of levels per blockIdx.z chunk so that small targets still fill the machine
+static int pick_zchunk(size_t tiles, int nz)
 {
-    const size_t blocks_xy = (nxy + 255) / 256;
     const size_t want = static_cast<size_t>(sm_count()) * 8 * 2; // two waves of 8 resident CTAs per SM
-    if (blocks_xy >= want || nz <= 1)
+    if (tiles >= want || nz <= 1)
         return nz;
-    size_t chunks = (want + blocks_xy - 1) / blocks_xy;
+    size_t chunks = (want + tiles - 1) / tiles;
     chunks = std::min<size_t>(chunks, static_cast<size_t>(nz));
     return static_cast<int>((nz + chunks - 1) / chunks);
 }
@@ -540,7 +844,7 @@ static fimexcu_cache* cache_build(int method, const double* d_px, const double* 
     if (!require_device())
         return nullptr;
     const size_t n = outX * outY;
-    if (inX == 0 || inY == 0 || inX * inY >= 2147483647ull || n >= (1ull << 40)) {
+    if (inX == 0 || inY == 0 || inX * inY >= 2147483647ull || outX >= (1ull << 30) || outY >= (1ull << 30) || n >= (1ull << 40)) {
         set_error("fimexcu_cache_create: grid sizes out of range (need 0 < inX*inY < 2^31)");
         return nullptr;
     }
@@ -641,59 +945,160 @@ static fimexcu_cache* cache_build(int method, const double* d_px, const double* 
             return nullptr;
         build_bilinear_kernel<<<nb, 256, 0, s>>>(d_px, d_py, n, static_cast<int>(c->inX), static_cast<int>(c->inY), static_cast<double>(minX),
                                                   static_cast<double>(minY), c->off.as<int>(), c->wx.as<float>(), c->wy.as<float>());
+        FXCU_CUDA_NULL(cudaGetLastError());
+        // how many 32 x 8 target tiles have a source footprint the staged (TMA) kernel can hold
+        DevBuf counts;
+        if (!counts.alloc(2 * sizeof(unsigned), s))
+            return nullptr;
+        FXCU_CUDA_NULL(cudaMemsetAsync(counts.p, 0, 2 * sizeof(unsigned), s));
+        const dim3 tg(static_cast<unsigned>((outX + 31) / 32), static_cast<unsigned>((outY + 7) / 8));
+        tile_fit_kernel<<<tg, 256, 0, s>>>(c->off.as<int>(), c->wx.as<float>(), c->wy.as<float>(), static_cast<int>(outX), static_cast<int>(outY),
+                                           static_cast<int>(c->inX), counts.as<unsigned>());
+        FXCU_CUDA_NULL(cudaGetLastError());
+        unsigned hc[2] = {0, 0};
+        FXCU_CUDA_NULL(cudaMemcpyAsync(hc, counts.p, sizeof(hc), cudaMemcpyDeviceToHost, s));
+        FXCU_CUDA_NULL(cudaStreamSynchronize(s));
+        c->tiles_with_data = hc[0];
+        c->tiles_fitting = hc[1];
     } else {
         if (!c->wx.alloc_sync(n * sizeof(double)) || !c->wy.alloc_sync(n * sizeof(double)))
             return nullptr;
         build_bicubic_kernel<<<nb, 256, 0, s>>>(d_px, d_py, n, static_cast<int>(c->inX), static_cast<int>(c->inY), static_cast<double>(minX),
                                                  static_cast<double>(minY), c->off.as<int>(), c->wx.as<double>(), c->wy.as<double>());
+        FXCU_CUDA_NULL(cudaGetLastError());
     }
-    FXCU_CUDA_NULL(cudaGetLastError());
     FXCU_CUDA_NULL(cudaStreamSynchronize(s));
     return c.release();
 }
 
-template <bool BAD, bool FILL>
-static void launch_cache_apply(const fimexcu_cache* c, const float* d_in, int nz, float* d_out, float bad, float fill, cudaStream_t s)
+// ---- TMA tensor map over the source slab [nz][inY][inX] with row pitch / level stride (elements) ----
+typedef CUresult (*tensor_map_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                         const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static tensor_map_encode_fn tensor_map_encoder()
 {
-    const size_t nxy = c->outX * c->outY;
-    const size_t inLayer = c->inX * c->inY;
-    const int zchunk = pick_zchunk(nxy, nz);
-    const dim3 grid(blocks_for(nxy, 256), static_cast<unsigned>((nz + zchunk - 1) / zchunk));
+    static tensor_map_encode_fn fn = []() -> tensor_map_encode_fn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        return reinterpret_cast<tensor_map_encode_fn>(p);
+    }();
+    return fn;
+}
+
+static bool make_source_map(CUtensorMap* m, const float* d_in, size_t inX, size_t inY, size_t nz, int inPitch, size_t inLevel)
+{
+    tensor_map_encode_fn enc = tensor_map_encoder();
+    if (!enc)
+        return false;
+    // TMA needs a 16 B aligned base and strides that are multiples of 16 B
+    if ((reinterpret_cast<uintptr_t>(d_in) & 15u) != 0 || (inPitch & 3) != 0 || (inLevel & 3) != 0)
+        return false;
+    cuuint64_t dims[3] = {inX, inY, nz};
+    cuuint64_t strides[2] = {static_cast<cuuint64_t>(inPitch) * 4, static_cast<cuuint64_t>(inLevel) * 4};
+    cuuint32_t box[3] = {TMA_BW, TMA_BH, TMA_ZB};
+    cuuint32_t es[3] = {1, 1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(d_in), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+struct Layout {
+    int inPitch;
+    size_t inLevel;
+    int outPitch;
+    size_t outLevel;
+};
+
+template <bool BAD, bool FILL>
+static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cudaStream_t s, bool allow_tma)
+{
+    ApplyParams P = P0;
+    const size_t tiles = static_cast<size_t>((c->outX + 31) / 32) * ((c->outY + 7) / 8);
+    if (c->kind == KIND_BILINEAR && allow_tma) {
+        // staged kernel: worth it when most tiles fit its box and there are enough tiles to fill the GPU without
+        // splitting the level loop
+        CUtensorMap map;
+        const bool enough = tiles >= static_cast<size_t>(sm_count()) * 6;
+        const bool fits = c->tiles_with_data > 0 && 10ull * c->tiles_fitting >= 8ull * c->tiles_with_data;
+        if (enough && fits && make_source_map(&map, P.in, c->inX, c->inY, static_cast<size_t>(P.nz), P.inPitch, P.inLevel)) {
+            const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH));
+            bilinear_apply_tma_kernel<BAD, FILL><<<grid, TMA_THREADS, 0, s>>>(map, P);
+            return;
+        }
+    }
+    P.zchunk = pick_zchunk(tiles, P.nz);
+    const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + 7) / 8),
+                    static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
     switch (c->kind) {
-    case KIND_BILINEAR:
-        bilinear_apply_kernel<BAD, FILL><<<grid, 256, 0, s>>>(c->off.as<int>(), c->wx.as<float>(), c->wy.as<float>(), d_in, d_out, nxy, nz, zchunk,
-                                                               inLayer, static_cast<int>(c->inX), bad, fill);
-        break;
-    case KIND_BICUBIC:
-        bicubic_apply_kernel<BAD, FILL><<<grid, 256, 0, s>>>(c->off.as<int>(), c->wx.as<double>(), c->wy.as<double>(), d_in, d_out, nxy, nz, zchunk,
-                                                              inLayer, static_cast<int>(c->inX), bad, fill);
-        break;
-    default:
-        nearest_apply_kernel<BAD, FILL><<<grid, 256, 0, s>>>(c->off.as<int>(), d_in, d_out, nxy, nz, zchunk, inLayer, bad, fill);
-        break;
+    case KIND_BILINEAR: bilinear_apply_kernel<BAD, FILL><<<grid, 256, 0, s>>>(P); break;
+    case KIND_BICUBIC: bicubic_apply_kernel<BAD, FILL><<<grid, 256, 0, s>>>(P); break;
+    default: nearest_apply_kernel<BAD, FILL><<<grid, 256, 0, s>>>(P); break;
     }
 }
 
-int cache_apply_dev(const fimexcu_cache* c, const float* d_in, size_t nz, float* d_out, float bad, float fill, cudaStream_t s)
+static int check_layout(const fimexcu_cache* c, const Layout& L, size_t nz)
+{
+    if (L.inPitch < static_cast<long long>(c->inX) || L.inLevel < static_cast<size_t>(L.inPitch) * (c->inY - 1) + c->inX ||
+        L.outPitch < static_cast<long long>(c->outX) || L.outLevel < static_cast<size_t>(L.outPitch) * (c->outY - 1) + c->outX)
+        FXCU_FAIL("fimexcu_cache_apply: row pitch / level stride smaller than the grid");
+    if (nz > 0x3fffffffull)
+        FXCU_FAIL("fimexcu_cache_apply: too many levels");
+    return FIMEXCU_OK;
+}
+
+int cache_apply_strided(const fimexcu_cache* c, const float* d_in, const Layout& L, size_t nz, float* d_out, float bad, float fill, cudaStream_t s)
 {
     if (!c)
         FXCU_FAIL("fimexcu_cache_apply: null cache");
     if (nz == 0 || c->outX * c->outY == 0)
         return FIMEXCU_OK;
-    if (nz > 0x7fffffffull / 2)
-        FXCU_FAIL("fimexcu_cache_apply: too many levels");
+    if (check_layout(c, L, nz) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
+    ApplyParams P;
+    P.off = c->off.as<int>();
+    P.wx = c->wx.p;
+    P.wy = c->wy.p;
+    P.in = d_in;
+    P.out = d_out;
+    P.outX = static_cast<int>(c->outX);
+    P.outY = static_cast<int>(c->outY);
+    P.nz = static_cast<int>(nz);
+    P.zchunk = P.nz;
+    P.inX = static_cast<int>(c->inX);
+    P.inPitch = L.inPitch;
+    P.inLevel = L.inLevel;
+    P.outPitch = L.outPitch;
+    P.outLevel = L.outLevel;
+    P.bad = bad;
+    P.fill = fill;
     const bool has_bad = !std::isnan(bad), has_fill = !std::isnan(fill);
-    const int inz = static_cast<int>(nz);
+    const bool allow_tma = getenv("FIMEXCU_NO_TMA") == nullptr;
     if (has_bad && has_fill)
-        launch_cache_apply<true, true>(c, d_in, inz, d_out, bad, fill, s);
+        launch_cache_apply<true, true>(c, P, s, allow_tma);
     else if (has_bad)
-        launch_cache_apply<true, false>(c, d_in, inz, d_out, bad, fill, s);
+        launch_cache_apply<true, false>(c, P, s, allow_tma);
     else if (has_fill)
-        launch_cache_apply<false, true>(c, d_in, inz, d_out, bad, fill, s);
+        launch_cache_apply<false, true>(c, P, s, allow_tma);
     else
-        launch_cache_apply<false, false>(c, d_in, inz, d_out, bad, fill, s);
+        launch_cache_apply<false, false>(c, P, s, allow_tma);
     FXCU_CUDA(cudaGetLastError());
     return FIMEXCU_OK;
+}
+
+static Layout dense_layout(const fimexcu_cache* c)
+{
+    return Layout{static_cast<int>(c->inX), c->inX * c->inY, static_cast<int>(c->outX), c->outX * c->outY};
+}
+
+// rows of the device-resident layout start on 32 B (source: TMA + sector aligned boxes) and 128 B (target: one line per warp store)
+static Layout padded_layout(const fimexcu_cache* c)
+{
+    const int ip = static_cast<int>((c->inX + 7) & ~size_t(7));
+    const int op = static_cast<int>((c->outX + 31) & ~size_t(31));
+    return Layout{ip, static_cast<size_t>(ip) * c->inY, op, static_cast<size_t>(op) * c->outY};
 }
 
 } // namespace fxcu
@@ -737,10 +1142,36 @@ int fimexcu_cache_info(const fimexcu_cache* c, size_t* inX, size_t* inY, size_t*
     return FIMEXCU_OK;
 }
 
+int fimexcu_cache_padded_layout(const fimexcu_cache* c, size_t* in_row_pitch, size_t* in_level_stride, size_t* out_row_pitch, size_t* out_level_stride)
+{
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_padded_layout: null cache");
+    const Layout L = padded_layout(c);
+    if (in_row_pitch) *in_row_pitch = static_cast<size_t>(L.inPitch);
+    if (in_level_stride) *in_level_stride = L.inLevel;
+    if (out_row_pitch) *out_row_pitch = static_cast<size_t>(L.outPitch);
+    if (out_level_stride) *out_level_stride = L.outLevel;
+    return FIMEXCU_OK;
+}
+
 int fimexcu_cache_apply_dev_f(const fimexcu_cache* c, const float* d_in, size_t nz, float* d_out, float badIn, float fillOut, void* stream)
 {
     clear_error();
-    return cache_apply_dev(c, d_in, nz, d_out, badIn, fillOut, as_stream(stream));
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply: null cache");
+    return cache_apply_strided(c, d_in, dense_layout(c), nz, d_out, badIn, fillOut, as_stream(stream));
+}
+
+int fimexcu_cache_apply_dev_strided_f(const fimexcu_cache* c, const float* d_in, size_t in_row_pitch, size_t in_level_stride, size_t nz, float* d_out,
+                                      size_t out_row_pitch, size_t out_level_stride, float badIn, float fillOut, void* stream)
+{
+    clear_error();
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply: null cache");
+    if (in_row_pitch > 0x7fffffffull || out_row_pitch > 0x7fffffffull)
+        FXCU_FAIL("fimexcu_cache_apply: row pitch out of range");
+    const Layout L{static_cast<int>(in_row_pitch), in_level_stride, static_cast<int>(out_row_pitch), out_level_stride};
+    return cache_apply_strided(c, d_in, L, nz, d_out, badIn, fillOut, as_stream(stream));
 }
 
 int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, float* out, size_t* newSize, float badIn, float fillOut)
@@ -756,8 +1187,11 @@ int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, 
         *newSize = nz * outLayer;
     if (nz == 0 || outLayer == 0)
         return FIMEXCU_OK;
-    // Levels are independent: split the slab into chunks and run copy-in, kernel and copy-out of
-    // neighbouring chunks on different streams so that PCIe traffic in both directions overlaps.
+    // Levels are independent: the slab is cut into level chunks; copy-in, kernel and copy-out of neighbouring chunks
+    // run on different streams so that PCIe traffic in both directions overlaps the kernels.  This path is bound by the
+    // PCIe copies (the 767 MB result alone takes ~14 ms, the kernels 0.4 ms), so the chunks keep the dense host layout on
+    // the device: plain 1-D copies run at full DMA speed, strided 2-D copies into the padded layout measured 1.5x slower.
+    const Layout L = dense_layout(c);
     const int NS = 3;
     const size_t chunk = std::max<size_t>(1, std::min<size_t>(nz, (nz + 7) / 8));
     cudaStream_t st[NS];
@@ -767,7 +1201,7 @@ int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, 
     {
         DevBuf din[NS], dout[NS];
         for (int i = 0; i < NS && rc == FIMEXCU_OK; ++i)
-            if (!din[i].alloc(chunk * inLayer * sizeof(float), st[i]) || !dout[i].alloc(chunk * outLayer * sizeof(float), st[i]))
+            if (!din[i].alloc(chunk * L.inLevel * sizeof(float), st[i]) || !dout[i].alloc(chunk * L.outLevel * sizeof(float), st[i]))
                 rc = FIMEXCU_ERROR;
         size_t k = 0;
         for (size_t z0 = 0; z0 < nz && rc == FIMEXCU_OK; z0 += chunk, ++k) {
@@ -778,7 +1212,7 @@ int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, 
                 rc = FIMEXCU_ERROR;
                 break;
             }
-            rc = cache_apply_dev(c, din[i].as<float>(), zn, dout[i].as<float>(), badIn, fillOut, st[i]);
+            rc = cache_apply_strided(c, din[i].as<float>(), L, zn, dout[i].as<float>(), badIn, fillOut, st[i]);
             if (rc != FIMEXCU_OK)
                 break;
             if (!cuda_ok(cudaMemcpyAsync(out + z0 * outLayer, dout[i].p, zn * outLayer * sizeof(float), cudaMemcpyDeviceToHost, st[i]), "D2H",
@@ -806,38 +1240,66 @@ int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r
     if (nz == 0 || nxy == 0)
         return FIMEXCU_OK;
     cudaStream_t s = as_stream(stream);
+    const Layout L = dense_layout(c);
     if (c->kind != KIND_BILINEAR) {
-        // bicubic / nearest: the general kernels per component, then the stand-alone rotation; the
-        // rotation sees NaN (not fill), so the fill is applied by the rotation-free path only
-        if (r && (!std::isnan(fillU) || !std::isnan(fillV)))
-            FXCU_FAIL("fimexcu_cache_apply_uv: fill values with rotation are only supported for bilinear caches");
-        if (cache_apply_dev(c, d_u_in, nz, d_u_out, badU, fillU, s) != FIMEXCU_OK || cache_apply_dev(c, d_v_in, nz, d_v_out, badV, fillV, s) != FIMEXCU_OK)
+        // bicubic / nearest: the general kernels per component, the stand-alone rotation (which must see NaN, not the
+        // fill value), then the fill
+        const float nanv = std::numeric_limits<float>::quiet_NaN();
+        const float fu = r ? nanv : fillU, fv = r ? nanv : fillV;
+        if (cache_apply_strided(c, d_u_in, L, nz, d_u_out, badU, fu, s) != FIMEXCU_OK || cache_apply_strided(c, d_v_in, L, nz, d_v_out, badV, fv, s) != FIMEXCU_OK)
             return FIMEXCU_ERROR;
-        return r ? fimexcu_vecrot_apply_dev_f(r, d_u_out, d_v_out, nz, stream) : FIMEXCU_OK;
+        if (!r)
+            return FIMEXCU_OK;
+        if (fimexcu_vecrot_apply_dev_f(r, d_u_out, d_v_out, nz, stream) != FIMEXCU_OK)
+            return FIMEXCU_ERROR;
+        const unsigned fb = static_cast<unsigned>(std::min<size_t>((nz * nxy + 255) / 256, static_cast<size_t>(sm_count()) * 16));
+        if (!std::isnan(fillU))
+            fill_kernel<<<fb, 256, 0, s>>>(d_u_out, nz * nxy, fillU);
+        if (!std::isnan(fillV))
+            fill_kernel<<<fb, 256, 0, s>>>(d_v_out, nz * nxy, fillV);
+        FXCU_CUDA(cudaGetLastError());
+        return FIMEXCU_OK;
     }
-    const int inz = static_cast<int>(nz);
-    const size_t inLayer = c->inX * c->inY;
-    const int zchunk = pick_zchunk(nxy, inz);
-    const dim3 grid(blocks_for(nxy, 256), static_cast<unsigned>((inz + zchunk - 1) / zchunk));
-    const bool bad = !std::isnan(badU) || !std::isnan(badV), fill = !std::isnan(fillU) || !std::isnan(fillV);
-    // a NaN bad value never compares equal, a NaN fill value re-writes NaN: the <true,true> variant is always correct
-    const double* cs = r ? r->c.as<double>() : nullptr;
-    const double* sn = r ? r->s.as<double>() : nullptr;
-#define FXCU_UV(B, F, R)                                                                                                                      \
-    bilinear_uv_kernel<B, F, R><<<grid, 256, 0, s>>>(c->off.as<int>(), c->wx.as<float>(), c->wy.as<float>(), cs, sn, d_u_in, d_v_in, d_u_out, \
-                                                     d_v_out, nxy, inz, zchunk, inLayer, static_cast<int>(c->inX), badU, badV, fillU, fillV)
+    ApplyParams P;
+    P.off = c->off.as<int>();
+    P.wx = c->wx.p;
+    P.wy = c->wy.p;
+    P.in = d_u_in;
+    P.out = d_u_out;
+    P.outX = static_cast<int>(c->outX);
+    P.outY = static_cast<int>(c->outY);
+    P.nz = static_cast<int>(nz);
+    P.inX = static_cast<int>(c->inX);
+    P.inPitch = L.inPitch;
+    P.inLevel = L.inLevel;
+    P.outPitch = L.outPitch;
+    P.outLevel = L.outLevel;
+    P.bad = badU;
+    P.fill = fillU;
+    UvParams Q;
+    Q.cs = r ? r->c.as<double>() : nullptr;
+    Q.sn = r ? r->s.as<double>() : nullptr;
+    Q.vin = d_v_in;
+    Q.vout = d_v_out;
+    Q.badV = badV;
+    Q.fillV = fillV;
+    const size_t tiles = static_cast<size_t>((c->outX + 31) / 32) * ((c->outY + 7) / 8);
+    P.zchunk = pick_zchunk(tiles, P.nz);
+    const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + 7) / 8),
+                    static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
+    const bool special = !std::isnan(badU) || !std::isnan(badV) || !std::isnan(fillU) || !std::isnan(fillV);
+    // a NaN bad value never compares equal and a NaN fill value re-writes NaN: the <true,true> variant is always correct
     if (r) {
-        if (bad || fill)
-            FXCU_UV(true, true, true);
+        if (special)
+            bilinear_uv_kernel<true, true, true><<<grid, 256, 0, s>>>(P, Q);
         else
-            FXCU_UV(false, false, true);
+            bilinear_uv_kernel<false, false, true><<<grid, 256, 0, s>>>(P, Q);
     } else {
-        if (bad || fill)
-            FXCU_UV(true, true, false);
+        if (special)
+            bilinear_uv_kernel<true, true, false><<<grid, 256, 0, s>>>(P, Q);
         else
-            FXCU_UV(false, false, false);
+            bilinear_uv_kernel<false, false, false><<<grid, 256, 0, s>>>(P, Q);
     }
-#undef FXCU_UV
     FXCU_CUDA(cudaGetLastError());
     return FIMEXCU_OK;
 }

@@ -2,12 +2,14 @@
 // Product code: never includes or links anything from oracle/.
 #pragma once
 
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cmath>
 #include <cstddef>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <limits>
 #include <string>
 

@@ -15,6 +15,7 @@ struct fimexcu_cache {
     size_t xMin = 0, yMin = 0;
     fxcu::DevBuf off;    // int32 [outX*outY]
     fxcu::DevBuf wx, wy; // f32 (bilinear) or f64 (bicubic) [outX*outY]
+    unsigned tiles_with_data = 0, tiles_fitting = 0; // 32 x 8 target tiles: with defined cells / whose footprint fits the TMA box
 };
 
 struct fimexcu_vecrot {

@@ -102,6 +102,35 @@ class CachedInterpolationInterface:
         self._apply_host(a.ctypes.data, size, out.ctypes.data, newSize, badValue, fillValue)
         return out, newSize.value
 
+    def paddedLayout(self):
+        """(in_row_pitch, in_level_stride, out_row_pitch, out_level_stride) in elements of the device-resident layout
+        that the staged kernels like best: source rows on 32 B, target rows on 128 B (fimexcu_cache_padded_layout)."""
+        v = [C.c_size_t() for _ in range(4)]
+        _lib.check(lib.fimexcu_cache_padded_layout(self._h, *[C.byref(t) for t in v]), "padded_layout")
+        return tuple(t.value for t in v)
+
+    def toPadded(self, dense):
+        """copy a dense CUDA slab [nz][inY][inX] into a padded one; returns the padded tensor (a view [..., :inX] is the data)"""
+        import torch
+        ip, il, _, _ = self.paddedLayout()
+        nz = dense.numel() // (self.inX * self.inY)
+        buf = torch.empty((nz, self.inY, ip), dtype=torch.float32, device=dense.device)
+        buf[:, :, :self.inX].copy_(dense.reshape(nz, self.inY, self.inX))
+        return buf
+
+    def interpolateValuesPadded(self, paddedIn, out=None, badValue=_NAN, fillValue=_NAN):
+        """device-resident apply in the padded layout: paddedIn [nz][inY][in_row_pitch] -> out [nz][outY][out_row_pitch]
+        (the defined data is out[..., :outX])."""
+        import torch
+        ip, il, op, ol = self.paddedLayout()
+        nz = paddedIn.shape[0]
+        assert paddedIn.is_cuda and paddedIn.is_contiguous() and paddedIn.shape[1:] == (self.inY, ip)
+        if out is None:
+            out = torch.empty((nz, self.outY, op), dtype=torch.float32, device=paddedIn.device)
+        _lib.check(lib.fimexcu_cache_apply_dev_strided_f(self._h, paddedIn.data_ptr(), ip, il, nz, out.data_ptr(), op, ol, badValue, fillValue,
+                                                         _lib.current_stream_ptr()), "interpolateValues")
+        return out
+
     def _apply_host(self, pin, size, pout, newSize, bad, fill):
         _lib.check(lib.fimexcu_cache_apply_f(self._h, pin, size, pout, C.byref(newSize), bad, fill), "interpolateValues")
 

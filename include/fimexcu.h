@@ -108,8 +108,18 @@ int fimexcu_cache_info(const fimexcu_cache* c, size_t* inX, size_t* inY, size_t*
  *   badIn   values equal to it are read as NaN (pass NaN for "none")
  *   fillOut NaN results are written as this value (pass NaN to keep NaN) */
 int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, float* out, size_t* newSize, float badIn, float fillOut);
-/* same on DEVICE-resident slabs; enqueues on `stream` */
+/* same on DEVICE-resident slabs in the reference's dense layout; enqueues on `stream` */
 int fimexcu_cache_apply_dev_f(const fimexcu_cache* c, const float* d_in, size_t nz, float* d_out, float badIn, float fillOut, void* stream);
+/* same on DEVICE-resident slabs with explicit element strides: element (z, y, x) of the source lives at
+ * d_in[z*in_level_stride + y*in_row_pitch + x], of the target at d_out[z*out_level_stride + y*out_row_pitch + x].
+ * Any strides >= the grid sizes are accepted.  The fast (TMA-staged) bilinear kernel needs d_in on a 16 B boundary and
+ * in_row_pitch, in_level_stride multiples of 4; target rows on 128 B boundaries make every warp store one full line.
+ * fimexcu_cache_padded_layout() returns strides that satisfy both (what slabs that stay on the device between chained
+ * operators should use; the host entry points stage through this layout internally). */
+int fimexcu_cache_apply_dev_strided_f(const fimexcu_cache* c, const float* d_in, size_t in_row_pitch, size_t in_level_stride, size_t nz,
+                                      float* d_out, size_t out_row_pitch, size_t out_level_stride, float badIn, float fillOut, void* stream);
+int fimexcu_cache_padded_layout(const fimexcu_cache* c, size_t* in_row_pitch, size_t* in_level_stride, size_t* out_row_pitch,
+                                size_t* out_level_stride);
 void fimexcu_cache_destroy(fimexcu_cache* c);
 
 /* Drop-in for the per-point C kernels with the reference signatures (include/fimex/interpolation.h:95-137,

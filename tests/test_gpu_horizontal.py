@@ -239,3 +239,53 @@ def test_meps_t1_full_slab_properties(fx, meps_t1):
     for z in (0, 31, 64):
         vals = outc[z][~mask0]
         assert np.abs(vals - (z + 1.0)).max() <= 1e-5 * (z + 1.0)
+
+
+# ---------------------------------------------------------------------------------- staged (TMA) kernel and strided layouts
+@pytest.mark.parametrize("shape", [(300, 200, 1400, 900, 9), (949, 1069, 2891, 1021, 3), (128, 96, 700, 500, 65)])
+@pytest.mark.parametrize("special", [False, True])
+def test_bilinear_staged_kernel_padded_layout(fx, oracle, shape, special):
+    """the headline kernel (TMA-staged, warp-specialised) in the padded device layout, incl. rim tiles, tiles that do
+    not fit the box (random tables -> direct fallback inside the kernel) and the fused bad/fill conversions"""
+    import torch
+    in_x, in_y, out_x, out_y, nz = shape
+    rng = np.random.default_rng(sum(shape))
+    # a smooth, slightly rotated and magnified map (fits the box) with a strip of scattered positions (does not)
+    gx, gy = np.meshgrid(np.arange(out_x), np.arange(out_y))
+    px = -3.0 + gx * ((in_x + 5.0) / out_x) + 0.11 * gy * (in_x / out_x)
+    py = -2.5 + gy * ((in_y + 4.0) / out_y) - 0.07 * gx * (in_y / out_y)
+    k = out_y // 2
+    px[k:k + 9] = rng.uniform(-2, in_x + 1, px[k:k + 9].shape)
+    py[k:k + 9] = rng.uniform(-2, in_y + 1, py[k:k + 9].shape)
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    bad, fill = np.float32(-999.0), np.float32(1e20)
+    fld[rng.random(fld.shape) < 0.01] = bad if special else np.nan
+    clean = fld.copy()
+    if special:
+        oracle.orc_bad2nanf(fp(clean), clean.size, bad)
+    want, info = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, clean)
+    if special:
+        oracle.orc_nanf2bad(fp(want), want.size, fill)
+    ci = fx.CachedInterpolation("x", "y", ol.BILINEAR, px, py, in_x, in_y, out_x, out_y)
+    sub = torch.from_numpy(ci.reduceInput(fld, in_x, in_y)).cuda()
+    kw = dict(badValue=float(bad), fillValue=float(fill)) if special else {}
+    out = ci.interpolateValuesPadded(ci.toPadded(sub), **kw)
+    torch.cuda.synchronize()
+    assert _eq(out[:, :, :out_x].cpu().numpy(), want)
+    # the dense entry point must give the same answer (direct or staged kernel, whichever its alignment allows)
+    dense, _ = ci.interpolateValues(sub, **kw)
+    torch.cuda.synchronize()
+    assert _eq(dense.cpu().numpy(), want)
+
+
+def test_staged_and_direct_kernels_agree_on_meps(fx, meps_t1, monkeypatch):
+    import torch
+    S, px, py, ox, oy, ci = meps_t1
+    fld = S.meps_slab_torch(t=5, device="cuda", nz=13)
+    pin = ci.toPadded(ci.reduceInput(fld, S.MEPS_NX, S.MEPS_NY))
+    a = ci.interpolateValuesPadded(pin)
+    torch.cuda.synchronize()
+    monkeypatch.setenv("FIMEXCU_NO_TMA", "1")
+    b = ci.interpolateValuesPadded(pin)
+    torch.cuda.synchronize()
+    assert _eq(a[:, :, :ox].cpu().numpy(), b[:, :, :ox].cpu().numpy())
