@@ -60,6 +60,7 @@ SIGNATURES = {
     "fimexcu_cache_apply_uv_dev_f": (C.c_int, [vp, vp, vp, vp, sz, vp, vp] + [C.c_float] * 4 + [vp]),
     "fimexcu_points2position": (C.c_int, [vp, sz, vp, C.c_int, C.c_int]),
     "fimexcu_points2position_dev": (C.c_int, [vp, sz, vp, C.c_int, C.c_int, vp]),
+    "fimexcu_points2position_dev_noalloc": (C.c_int, [vp, sz, vp, C.c_int, C.c_int, vp]),
     "fimexcu_reproject_axes": (C.c_int, [C.c_char_p, C.c_char_p, vp, vp, C.c_int, C.c_int, vp, vp]),
     "fimexcu_reproject_axes_dev": (C.c_int, [C.c_char_p, C.c_char_p, vp, vp, C.c_int, C.c_int, vp, vp, vp]),
     "fimexcu_reproject_values": (C.c_int, [C.c_char_p, C.c_char_p, vp, vp, C.c_int]),

@@ -6,6 +6,7 @@
 // One thread per point; the axis (a few thousand f64) stays in L1/L2.
 #include "fxcu_common.h"
 
+#include <mutex>
 #include <vector>
 
 namespace fxcu {
@@ -102,6 +103,34 @@ int points2position_dev(double* d_points, size_t n, const double* d_axis, const 
     return FIMEXCU_OK;
 }
 
+// ---- scratch for fimexcu_points2position_dev_noalloc: the device copy of the axis lives in a fixed array that is
+// part of the loaded module (one instance per GPU that loads the library, held until the process exits) ----
+constexpr int NOALLOC_MAX_AXIS = FIMEXCU_NOALLOC_MAX_AXIS;
+static __device__ __align__(256) double g_noalloc_axis[NOALLOC_MAX_AXIS];
+
+// In host code `g_noalloc_axis` is only a stand-in for the symbol, not a device address: the address the kernel
+// needs is looked up once per device, with that device current.
+static double* noalloc_axis_address()
+{
+    static std::mutex lock;
+    static double* address[64] = {nullptr};
+    int dev = -1;
+    if (!cuda_ok(cudaGetDevice(&dev), "cudaGetDevice", __FILE__, __LINE__))
+        return nullptr;
+    if (dev < 0 || dev >= 64) {
+        set_error("fimexcu_points2position_dev_noalloc: device ordinal out of range");
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> guard(lock);
+    if (!address[dev]) {
+        double* p = nullptr;
+        if (!cuda_ok(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_axis), "cudaGetSymbolAddress(g_noalloc_axis)", __FILE__, __LINE__))
+            return nullptr;
+        address[dev] = p;
+    }
+    return address[dev];
+}
+
 } // namespace fxcu
 
 using namespace fxcu;
@@ -120,6 +149,33 @@ int fimexcu_points2position_dev(double* d_points, size_t n, const double* axis_h
     FXCU_CUDA(cudaMemcpyAsync(ax.p, axis_host, static_cast<size_t>(num) * sizeof(double), cudaMemcpyHostToDevice, s));
     const int rc = points2position_dev(d_points, n, ax.as<double>(), axis_host, num, axis_type, s);
     FXCU_CUDA(cudaStreamSynchronize(s)); // axis_host may be a temporary of the caller
+    return rc;
+}
+
+int fimexcu_points2position_dev_noalloc(double* d_points, size_t n, const double* axis_host, int num, int axis_type, void* stream)
+{
+    clear_error();
+    if (num > NOALLOC_MAX_AXIS) {
+        char msg[160];
+        std::snprintf(msg, sizeof(msg), "fimexcu_points2position_dev_noalloc: axis has %d values, the fixed scratch holds at most %d "
+                                        "(use fimexcu_points2position_dev, which allocates)", num, NOALLOC_MAX_AXIS);
+        FXCU_FAIL(msg);
+    }
+    if (num < 2)
+        FXCU_FAIL("fimexcu_points2position: axis needs at least 2 values");
+    int dev = 0, major = 0;
+    FXCU_CUDA(cudaGetDevice(&dev));
+    FXCU_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (major != 10)
+        FXCU_FAIL("libfimexcu is built for sm_100a only; the current device is not a compute-capability 10.x GPU");
+    double* d_axis = noalloc_axis_address(); // first call on a device: symbol look-up
+    if (!d_axis)
+        return FIMEXCU_ERROR;
+    cudaStream_t s = as_stream(stream);
+    // every call overwrites the first `num` entries it reads; nothing in the scratch has to start at zero
+    FXCU_CUDA(cudaMemcpyAsync(d_axis, axis_host, static_cast<size_t>(num) * sizeof(double), cudaMemcpyHostToDevice, s));
+    const int rc = points2position_dev(d_points, n, d_axis, axis_host, num, axis_type, s);
+    FXCU_CUDA(cudaStreamSynchronize(s)); // axis_host may be a temporary of the caller; also ends this call's use of the scratch
     return rc;
 }
 

@@ -164,6 +164,20 @@ int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r
  * coordinates -> fractional axis indices, in place.  HOST pointers. */
 int fimexcu_points2position(double* points, size_t n, const double* axis, int num, int axis_type);
 int fimexcu_points2position_dev(double* d_points, size_t n, const double* axis_host, int num, int axis_type, void* stream);
+/* No counterpart in the reference.  Same result as fimexcu_points2position_dev, for callers that must not allocate GPU
+ * memory while they run: a reader chain embedded in a host application that has handed the whole device to its own
+ * memory pool at start-up (an inference or visualisation server with a fixed budget), where cudaMalloc fails, or a
+ * latency-sensitive thread that cannot afford the device-wide synchronisation a cudaMalloc/cudaFree may imply.  The
+ * device copy of the axis, which the other entry point keeps in a freshly allocated buffer, lives here in a fixed
+ * array inside the library image: FIMEXCU_NOALLOC_MAX_AXIS doubles (128 KiB) on every GPU that loads the library,
+ * held until the process exits.  The call allocates nothing (no cudaMalloc/cudaFree, no pool, no torch); the caller
+ * still owns d_points (in/out, device) and axis_host (host).  Longer axes are rejected with FIMEXCU_ERROR.
+ * The first call on each device looks up the array's device address; make that first call before any stream capture
+ * begins.  All calls share the one array and it keeps the previous call's axis: a call overwrites the part it uses
+ * before reading it, and two calls whose GPU work overlaps (different streams or threads) race on it -- serialise
+ * them.  The call returns after `stream` has drained, like fimexcu_points2position_dev. */
+#define FIMEXCU_NOALLOC_MAX_AXIS 16384
+int fimexcu_points2position_dev_noalloc(double* d_points, size_t n, const double* axis_host, int num, int axis_type, void* stream);
 /* Replaces reproject::reproject_axes (include/fimex/reproject.h:211-227, src/reproject.cc:573-587): broadcast the
  * 1-D axes to an ix*iy lattice and transform proj_input -> proj_output (proj4 strings; degrees for geographic
  * CRS as with PROJ >= 6).  Points that cannot be projected become +inf. */
