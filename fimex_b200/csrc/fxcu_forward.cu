@@ -1,0 +1,415 @@
+// fxcu_forward.cu -- forward (scatter / aggregate) interpolation: K11 index build, K12 sum/mean/min/max, K13 median.
+//
+// Reference behaviour restated here (fimex 2.4.1):
+//   CachedForwardInterpolation ctor                 src/CachedForwardInterpolation.cc:133-201
+//   CachedForwardInterpolation::interpolateValues   src/CachedForwardInterpolation.cc:205-224
+//   AggSum / AggMean / AggMin / AggMax / AggMedian   src/CachedForwardInterpolation.cc:63-130
+//   RoundAndClamp                                   src/MathUtils.cc:30-46
+//
+// The reference keeps one std::vector<size_t> of source indices per target cell, filled while walking the source row-major,
+// so every list is ascending in source index and the f32 running sums are taken in that order.  Here the lists are a CSR:
+// a stable radix sort of (target cell, source index) pairs (one-off, CUB) gives the same order; the apply kernel gives one
+// thread one target cell and walks its segment sequentially, so sum and mean are bit-identical to the reference
+// (no parallel re-association), min/max/median trivially so.
+//
+// HBM layout: source [nz][inY][inX] f32 (reduced window), target [nz][outY][outX] f32, CSR segStart int32 [nout+1],
+// segIdx int32 [nvalid].  Algorithmic bytes per source point and level: 4 (value) + 4*N_out/N_in (result) + 8/nz (CSR).
+#include "fxcu_common.h"
+
+#include <cub/device/device_radix_sort.cuh>
+
+#include <algorithm>
+#include <memory>
+#include <vector>
+
+struct fimexcu_forward {
+    int method = 0;
+    int kind = 0; // 0 sum, 1 mean, 2 median, 3 max, 4 min
+    bool undef = false;
+    size_t inX = 0, inY = 0, outX = 0, outY = 0;
+    bool reduced = false;
+    size_t xMin = 0, yMin = 0;
+    size_t maxPointsInIn = 0;
+    size_t nvalid = 0;
+    fxcu::DevBuf segStart; // int32 [nout+1]
+    fxcu::DevBuf segIdx;   // int32 [nvalid]
+};
+
+namespace fxcu {
+
+__device__ __forceinline__ long long fwd_round_and_clamp(double d, long long maxi)
+{
+    const double r = round(d);
+    if (!(r >= 0.0) || r > static_cast<double>(maxi))
+        return -1;
+    return static_cast<long long>(r);
+}
+
+// :141-160 first half: target cell of every source cell (key = nout for "no target"), used source range
+__global__ void __launch_bounds__(256) fwd_target_kernel(const double* __restrict__ px, const double* __restrict__ py, int inX, size_t nin, int outX,
+                                                         int outY, unsigned* __restrict__ key, unsigned* __restrict__ val, int* __restrict__ range)
+{
+    const size_t i = blockIdx.x * 256ull + threadIdx.x;
+    int lox = 0x7fffffff, hix = -1, loy = 0x7fffffff, hiy = -1;
+    if (i < nin) {
+        const long long tx = fwd_round_and_clamp(px[i], outX - 1), ty = fwd_round_and_clamp(py[i], outY - 1);
+        unsigned k = static_cast<unsigned>(outX) * static_cast<unsigned>(outY);
+        if (tx >= 0 && ty >= 0) {
+            k = static_cast<unsigned>(ty) * outX + static_cast<unsigned>(tx);
+            const int iy = static_cast<int>(i / inX), ix = static_cast<int>(i - static_cast<size_t>(iy) * inX);
+            lox = hix = ix;
+            loy = hiy = iy;
+        }
+        key[i] = k;
+        val[i] = static_cast<unsigned>(i);
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        lox = min(lox, __shfl_xor_sync(0xffffffffu, lox, s));
+        hix = max(hix, __shfl_xor_sync(0xffffffffu, hix, s));
+        loy = min(loy, __shfl_xor_sync(0xffffffffu, loy, s));
+        hiy = max(hiy, __shfl_xor_sync(0xffffffffu, hiy, s));
+    }
+    if ((threadIdx.x & 31) == 0 && hix >= 0) {
+        atomicMin(&range[0], lox);
+        atomicMax(&range[1], hix);
+        atomicMin(&range[2], loy);
+        atomicMax(&range[3], hiy);
+    }
+}
+
+// segStart[o] = first sorted position whose key >= o (o = 0..nout); also the longest segment
+__global__ void __launch_bounds__(256) fwd_segments_kernel(const unsigned* __restrict__ sortedKey, size_t n, unsigned nout, int* __restrict__ segStart,
+                                                           int* __restrict__ maxLen)
+{
+    const size_t o = blockIdx.x * 256ull + threadIdx.x;
+    if (o > nout)
+        return;
+    size_t lo = 0, hi = n;
+    while (lo < hi) {
+        const size_t mid = (lo + hi) / 2;
+        if (sortedKey[mid] < o)
+            lo = mid + 1;
+        else
+            hi = mid;
+    }
+    segStart[o] = static_cast<int>(lo);
+    if (o < nout) {
+        size_t e = lo;
+        while (e < n && sortedKey[e] == o)
+            ++e;
+        atomicMax(maxLen, static_cast<int>(e - lo));
+    }
+}
+
+// :177-183: source indices re-expressed in the reduced window
+__global__ void __launch_bounds__(256) fwd_rebase_kernel(const unsigned* __restrict__ sortedVal, size_t nvalid, int inX, int minX, int minY, int redX,
+                                                         int* __restrict__ segIdx)
+{
+    const size_t k = blockIdx.x * 256ull + threadIdx.x;
+    if (k >= nvalid)
+        return;
+    const int i = static_cast<int>(sortedVal[k]);
+    const int iy = i / inX - minY, ix = i % inX - minX;
+    segIdx[k] = iy * redX + ix;
+}
+
+struct FwdParams {
+    const int* segStart;
+    const int* segIdx;
+    const float* in;
+    float* out;
+    size_t nout, inLayer;
+    int nz, zchunk;
+    int kind;
+    bool undef, level_compat;
+    float bad, fill;
+};
+
+__device__ __forceinline__ float fwd_load(const float* p, float bad, bool has_bad)
+{
+    float v = __ldg(p);
+    if (has_bad && v == bad)
+        v = nan_f();
+    return v;
+}
+
+// K12/K13: one thread per target cell, levels z0..z1; the segment is walked in ascending source order
+__global__ void __launch_bounds__(256) fwd_apply_kernel(const FwdParams P)
+{
+    const size_t o = blockIdx.x * 256ull + threadIdx.x;
+    if (o >= P.nout)
+        return;
+    const int z0 = blockIdx.y * P.zchunk, z1 = min(P.nz, z0 + P.zchunk);
+    const int s0 = P.segStart[o], s1 = P.segStart[o + 1];
+    const bool has_bad = !isnan(P.bad), has_fill = !isnan(P.fill);
+    float* po = P.out + static_cast<size_t>(z0) * P.nout + o;
+    float carried = nan_f();
+    for (int z = z0; z < z1; ++z, po += P.nout) {
+        float r;
+        if (P.level_compat && z > z0) {
+            r = carried; // the reference reads input level 0 for every output level (CachedForwardInterpolation.cc:212-221)
+        } else {
+            const float* src = P.in + (P.level_compat ? 0 : static_cast<size_t>(z) * P.inLayer);
+            int count = 0;
+            float val = 0.f;
+            if (P.kind != 2) {
+                for (int k = s0; k < s1; ++k) {
+                    const float f = fwd_load(src + P.segIdx[k], P.bad, has_bad);
+                    if (!P.undef && isnan(f))
+                        continue;
+                    if (P.kind <= 1)
+                        val = __fadd_rn(val, f); // AggSum::push, f32 running sum
+                    else if (P.kind == 3) {
+                        if (count == 0 || f > val)
+                            val = f; // AggMax::push
+                    } else {
+                        if (count == 0 || f < val)
+                            val = f; // AggMin::push
+                    }
+                    ++count;
+                }
+                if (count == 0)
+                    r = nan_f();
+                else if (P.kind == 1)
+                    r = __fdiv_rn(val, static_cast<float>(count)); // val / count, count converted to float (:90)
+                else
+                    r = val;
+            } else {
+                // AggMedian: nth_element at n/2 == element of rank n/2 among the pushed values.  Rank selection without
+                // storage: v has rank k iff #(values < v) <= k < #(values < v) + #(values == v).
+                int n = 0;
+                bool any_nan = false;
+                for (int k = s0; k < s1; ++k) {
+                    const float f = fwd_load(src + P.segIdx[k], P.bad, has_bad);
+                    if (isnan(f)) {
+                        if (P.undef) {
+                            any_nan = true;
+                            ++n;
+                        }
+                    } else {
+                        ++n;
+                    }
+                }
+                r = nan_f();
+                if (n > 0 && !any_nan) { // NaN among the values: unspecified order in the reference, defined as NaN
+                    const int rank = n / 2;
+                    for (int k = s0; k < s1; ++k) {
+                        const float v = fwd_load(src + P.segIdx[k], P.bad, has_bad);
+                        if (isnan(v))
+                            continue;
+                        int less = 0, equal = 0;
+                        for (int j = s0; j < s1; ++j) {
+                            const float w = fwd_load(src + P.segIdx[j], P.bad, has_bad);
+                            less += (w < v) ? 1 : 0;
+                            equal += (w == v) ? 1 : 0;
+                        }
+                        if (less <= rank && rank < less + equal) {
+                            r = v;
+                            break;
+                        }
+                    }
+                }
+            }
+            carried = r;
+        }
+        float w = r;
+        if (has_fill && isnan(w))
+            w = P.fill;
+        __stcs(po, w);
+    }
+}
+
+static int fwd_zchunk(size_t nout, int nz, bool compat)
+{
+    if (compat)
+        return nz; // one computation, nz stores
+    const size_t blocks = (nout + 255) / 256;
+    const size_t want = static_cast<size_t>(sm_count()) * 16;
+    if (blocks >= want || nz <= 1)
+        return nz;
+    size_t chunks = std::min<size_t>((want + blocks - 1) / blocks, static_cast<size_t>(nz));
+    return static_cast<int>((nz + chunks - 1) / chunks);
+}
+
+} // namespace fxcu
+
+using namespace fxcu;
+
+extern "C" {
+
+fimexcu_forward* fimexcu_forward_create(int method, const double* pOnX, const double* pOnY, size_t inX, size_t inY, size_t outX, size_t outY)
+{
+    clear_error();
+    if (!require_device())
+        return nullptr;
+    if (method < FIMEXCU_INTERPOL_FORWARD_SUM || method > FIMEXCU_INTERPOL_FORWARD_UNDEF_MIN) {
+        set_error("unknown forward interpolation method: " + std::to_string(method)); // CachedForwardInterpolation.cc:196
+        return nullptr;
+    }
+    const size_t nin = inX * inY, nout = outX * outY;
+    if (nin == 0 || nout == 0 || nin >= 2147483647ull || nout >= 2147483647ull) {
+        set_error("fimexcu_forward_create: grid sizes out of range (need 0 < size < 2^31)");
+        return nullptr;
+    }
+    std::unique_ptr<fimexcu_forward> f(new fimexcu_forward());
+    f->method = method;
+    f->undef = method >= FIMEXCU_INTERPOL_FORWARD_UNDEF_SUM;
+    switch (method) {
+    case FIMEXCU_INTERPOL_FORWARD_SUM: case FIMEXCU_INTERPOL_FORWARD_UNDEF_SUM: f->kind = 0; break;
+    case FIMEXCU_INTERPOL_FORWARD_MEAN: case FIMEXCU_INTERPOL_FORWARD_UNDEF_MEAN: f->kind = 1; break;
+    case FIMEXCU_INTERPOL_FORWARD_MEDIAN: case FIMEXCU_INTERPOL_FORWARD_UNDEF_MEDIAN: f->kind = 2; break;
+    case FIMEXCU_INTERPOL_FORWARD_MAX: case FIMEXCU_INTERPOL_FORWARD_UNDEF_MAX: f->kind = 3; break;
+    default: f->kind = 4; break;
+    }
+    f->inX = inX;
+    f->inY = inY;
+    f->outX = outX;
+    f->outY = outY;
+    cudaStream_t s = nullptr;
+    DevBuf dx, dy, key, val, keyS, valS, range, maxLen, tmp;
+    if (!dx.alloc(nin * 8, s) || !dy.alloc(nin * 8, s) || !key.alloc(nin * 4, s) || !val.alloc(nin * 4, s) || !keyS.alloc(nin * 4, s) ||
+        !valS.alloc(nin * 4, s) || !range.alloc(4 * sizeof(int), s) || !maxLen.alloc(sizeof(int), s))
+        return nullptr;
+    FXCU_CUDA_NULL(cudaMemcpyAsync(dx.p, pOnX, nin * 8, cudaMemcpyHostToDevice, s));
+    FXCU_CUDA_NULL(cudaMemcpyAsync(dy.p, pOnY, nin * 8, cudaMemcpyHostToDevice, s));
+    const int init[4] = {0x7fffffff, -1, 0x7fffffff, -1};
+    FXCU_CUDA_NULL(cudaMemcpyAsync(range.p, init, sizeof(init), cudaMemcpyHostToDevice, s));
+    FXCU_CUDA_NULL(cudaMemsetAsync(maxLen.p, 0, sizeof(int), s));
+    fwd_target_kernel<<<blocks_for(nin, 256), 256, 0, s>>>(dx.as<double>(), dy.as<double>(), static_cast<int>(inX), nin, static_cast<int>(outX),
+                                                           static_cast<int>(outY), key.as<unsigned>(), val.as<unsigned>(), range.as<int>());
+    FXCU_CUDA_NULL(cudaGetLastError());
+    // stable LSD radix sort by target cell: equal keys keep their ascending source order
+    size_t tmpBytes = 0;
+    int bits = 1;
+    while ((1ull << bits) <= nout)
+        ++bits;
+    FXCU_CUDA_NULL(cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, key.as<unsigned>(), keyS.as<unsigned>(), val.as<unsigned>(), valS.as<unsigned>(),
+                                                   static_cast<int>(nin), 0, bits, s));
+    if (!tmp.alloc(tmpBytes, s))
+        return nullptr;
+    FXCU_CUDA_NULL(cub::DeviceRadixSort::SortPairs(tmp.p, tmpBytes, key.as<unsigned>(), keyS.as<unsigned>(), val.as<unsigned>(), valS.as<unsigned>(),
+                                                   static_cast<int>(nin), 0, bits, s));
+    if (!f->segStart.alloc_sync((nout + 1) * sizeof(int)))
+        return nullptr;
+    fwd_segments_kernel<<<blocks_for(nout + 1, 256), 256, 0, s>>>(keyS.as<unsigned>(), nin, static_cast<unsigned>(nout), f->segStart.as<int>(),
+                                                                  maxLen.as<int>());
+    FXCU_CUDA_NULL(cudaGetLastError());
+    int r[4], ml = 0, nvalid = 0;
+    FXCU_CUDA_NULL(cudaMemcpyAsync(r, range.p, sizeof(r), cudaMemcpyDeviceToHost, s));
+    FXCU_CUDA_NULL(cudaMemcpyAsync(&ml, maxLen.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    FXCU_CUDA_NULL(cudaMemcpyAsync(&nvalid, f->segStart.as<int>() + nout, sizeof(int), cudaMemcpyDeviceToHost, s));
+    FXCU_CUDA_NULL(cudaStreamSynchronize(s));
+    f->maxPointsInIn = static_cast<size_t>(ml);
+    f->nvalid = static_cast<size_t>(nvalid);
+    // CachedForwardInterpolation.cc:165-186
+    size_t minInX = 0, maxInX = 0, minInY = 0, maxInY = 0;
+    if (nvalid > 0) {
+        minInX = static_cast<size_t>(r[0]);
+        maxInX = static_cast<size_t>(r[1]);
+        minInY = static_cast<size_t>(r[2]);
+        maxInY = static_cast<size_t>(r[3]);
+    }
+    const size_t EXT = 2;
+    minInX = (minInX > EXT) ? minInX - EXT : 0;
+    minInY = (minInY > EXT) ? minInY - EXT : 0;
+    maxInX = std::min(inX - 1, maxInX + EXT);
+    maxInY = std::min(inY - 1, maxInY + EXT);
+    int rebX = 0, rebY = 0;
+    size_t redX = inX;
+    if ((minInX > 0 || minInY > 0 || maxInX < inX - 1 || maxInY < inY - 1) && (minInX + 2 * EXT <= maxInX) && (minInY + 2 * EXT <= maxInY)) {
+        redX = maxInX - minInX + 1;
+        f->reduced = true;
+        f->xMin = minInX;
+        f->yMin = minInY;
+        f->inX = redX;
+        f->inY = maxInY - minInY + 1;
+        rebX = static_cast<int>(minInX);
+        rebY = static_cast<int>(minInY);
+    }
+    if (!f->segIdx.alloc_sync(std::max<size_t>(f->nvalid, 1) * sizeof(int)))
+        return nullptr;
+    if (f->nvalid) {
+        fwd_rebase_kernel<<<blocks_for(f->nvalid, 256), 256, 0, s>>>(valS.as<unsigned>(), f->nvalid, static_cast<int>(inX), rebX, rebY,
+                                                                     static_cast<int>(redX), f->segIdx.as<int>());
+        FXCU_CUDA_NULL(cudaGetLastError());
+    }
+    FXCU_CUDA_NULL(cudaStreamSynchronize(s));
+    return f.release();
+}
+
+int fimexcu_forward_info(const fimexcu_forward* f, size_t* inX, size_t* inY, size_t* outX, size_t* outY, int* reduced, size_t* xMin,
+                         size_t* yMin, size_t* maxPointsInIn)
+{
+    if (!f)
+        FXCU_FAIL("fimexcu_forward_info: null handle");
+    if (inX) *inX = f->inX;
+    if (inY) *inY = f->inY;
+    if (outX) *outX = f->outX;
+    if (outY) *outY = f->outY;
+    if (reduced) *reduced = f->reduced ? 1 : 0;
+    if (xMin) *xMin = f->xMin;
+    if (yMin) *yMin = f->yMin;
+    if (maxPointsInIn) *maxPointsInIn = f->maxPointsInIn;
+    return FIMEXCU_OK;
+}
+
+int fimexcu_forward_apply_dev_f(const fimexcu_forward* f, const float* d_in, size_t nz, float* d_out, float badIn, float fillOut,
+                                int level_compat, void* stream)
+{
+    clear_error();
+    if (!f)
+        FXCU_FAIL("fimexcu_forward_apply: null handle");
+    const size_t nout = f->outX * f->outY;
+    if (nz == 0 || nout == 0)
+        return FIMEXCU_OK;
+    if (nz > 0x3fffffffull)
+        FXCU_FAIL("fimexcu_forward_apply: too many levels");
+    FwdParams P;
+    P.segStart = f->segStart.as<int>();
+    P.segIdx = f->segIdx.as<int>();
+    P.in = d_in;
+    P.out = d_out;
+    P.nout = nout;
+    P.inLayer = f->inX * f->inY;
+    P.nz = static_cast<int>(nz);
+    P.zchunk = fwd_zchunk(nout, P.nz, level_compat != 0);
+    P.kind = f->kind;
+    P.undef = f->undef;
+    P.level_compat = level_compat != 0;
+    P.bad = badIn;
+    P.fill = fillOut;
+    const dim3 grid(blocks_for(nout, 256), static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
+    fwd_apply_kernel<<<grid, 256, 0, as_stream(stream)>>>(P);
+    FXCU_CUDA(cudaGetLastError());
+    return FIMEXCU_OK;
+}
+
+int fimexcu_forward_apply_f(const fimexcu_forward* f, const float* in, size_t size, float* out, size_t* newSize, float badIn, float fillOut,
+                            int level_compat)
+{
+    clear_error();
+    if (!f)
+        FXCU_FAIL("fimexcu_forward_apply_f: null handle");
+    if (!require_device())
+        return FIMEXCU_ERROR;
+    const size_t inLayer = f->inX * f->inY, outLayer = f->outX * f->outY;
+    const size_t nz = size / inLayer; // CachedForwardInterpolation.cc:209
+    if (newSize)
+        *newSize = nz * outLayer;
+    if (nz == 0 || outLayer == 0)
+        return FIMEXCU_OK;
+    DevBuf din, dout;
+    if (!din.alloc(nz * inLayer * 4, nullptr) || !dout.alloc(nz * outLayer * 4, nullptr))
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(din.p, in, nz * inLayer * 4, cudaMemcpyHostToDevice, nullptr));
+    if (fimexcu_forward_apply_dev_f(f, din.as<float>(), nz, dout.as<float>(), badIn, fillOut, level_compat, nullptr) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(out, dout.p, nz * outLayer * 4, cudaMemcpyDeviceToHost, nullptr));
+    FXCU_CUDA(cudaStreamSynchronize(nullptr));
+    return FIMEXCU_OK;
+}
+
+void fimexcu_forward_destroy(fimexcu_forward* f) { delete f; }
+
+} // extern "C"

@@ -1,0 +1,116 @@
+"""Host-side mirror of the vertical-interpolation hot loop on top of the C ABI.
+
+  verticalInterpolate        CDMVerticalInterpolator::getLevelDataSlice hot loop (src/CDMVerticalInterpolator.cc:488-561)
+  verticalHybridPressure     same with the hybrid-sigma pressure formed on the fly
+                             (src/coordSys/verticalTransform/HybridSigmaApToPressureConverter.cc:71-100)
+  mifi_get_values_*_f        the two-level kernels of include/fimex/interpolation.h:153-232
+Arrays are [nOuter][nz][nInner] (C order): the CDM shape (x, y, [ensemble], k, t) of a time-step slab has nInner = the product
+of the dimensions faster than the vertical one and nOuter = the product of the slower ones.
+"""
+import numpy as np
+
+from . import _lib
+from ._lib import lib
+
+_NAN = float("nan")
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _opt(a, dtype):
+    return None if a is None else np.ascontiguousarray(a, dtype=dtype)
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data
+
+
+def verticalInterpolate(method, inData, verticalIn, level1=None, verticalOut=None, validMin=None, validMax=None, valid_min=_NAN,
+                        valid_max=_NAN, badValue=_NAN, fillValue=_NAN):
+    """inData, verticalIn: [nOuter][nzi][nInner] f32; level1: fixed target levels (f64) or verticalOut: [nOuter][nzo][nInner] f32.
+    validMin/validMax: per-column f64 [nOuter][nInner] (converter validity range); valid_min/valid_max: the variable's
+    valid range (clamp).  Returns [nOuter][nzo][nInner] f32."""
+    if _is_torch(inData):
+        import torch
+        nO, nzi, nI = inData.shape
+        lv = _opt(level1, np.float64)
+        nzo = lv.size if lv is not None else verticalOut.shape[1]
+        out = torch.empty((nO, nzo, nI), dtype=torch.float32, device=inData.device)
+        _lib.check(lib.fimexcu_vertical_interpolate_dev_f(
+            method, inData.data_ptr(), verticalIn.data_ptr(), nO, nzi, nI, _ptr(lv), None if verticalOut is None else verticalOut.data_ptr(), nzo,
+            None if validMin is None else validMin.data_ptr(), None if validMax is None else validMax.data_ptr(), valid_min, valid_max,
+            badValue, fillValue, out.data_ptr(), _lib.current_stream_ptr()), "verticalInterpolate")
+        return out
+    a, v = _f32(inData), _f32(verticalIn)
+    nO, nzi, nI = a.shape
+    assert v.shape == a.shape
+    lv, vo = _opt(level1, np.float64), _opt(verticalOut, np.float32)
+    nzo = lv.size if lv is not None else vo.shape[1]
+    mn, mx = _opt(validMin, np.float64), _opt(validMax, np.float64)
+    out = np.empty((nO, nzo, nI), dtype=np.float32)
+    _lib.check(lib.fimexcu_vertical_interpolate_f(method, a.ctypes.data, v.ctypes.data, nO, nzi, nI, _ptr(lv), _ptr(vo), nzo, _ptr(mn), _ptr(mx),
+                                                  valid_min, valid_max, badValue, fillValue, out.ctypes.data), "verticalInterpolate")
+    return out
+
+
+def verticalHybridPressure(method, inData, ap, b, ps, level1, ps_scale=1.0, valid_min=_NAN, valid_max=_NAN, badValue=_NAN, fillValue=_NAN):
+    """inData [nOuter][nzi][nInner] f32; ap, b [nzi] f64 (ap in the unit of level1); ps [nOuter or 1][nInner] f32, multiplied by
+    ps_scale (unit conversion); level1 target pressures."""
+    apv, bv, lv = _opt(ap, np.float64), _opt(b, np.float64), _opt(level1, np.float64)
+    if _is_torch(inData):
+        import torch
+        nO, nzi, nI = inData.shape
+        out = torch.empty((nO, lv.size, nI), dtype=torch.float32, device=inData.device)
+        _lib.check(lib.fimexcu_vertical_hybrid_pressure_dev_f(method, inData.data_ptr(), nO, nzi, nI, apv.ctypes.data, bv.ctypes.data, ps.data_ptr(),
+                                                              ps.shape[0], ps_scale, lv.ctypes.data, lv.size, valid_min, valid_max, badValue,
+                                                              fillValue, out.data_ptr(), _lib.current_stream_ptr()), "verticalHybridPressure")
+        return out
+    a, p = _f32(inData), _f32(ps)
+    nO, nzi, nI = a.shape
+    p = p.reshape(-1, nI)
+    out = np.empty((nO, lv.size, nI), dtype=np.float32)
+    _lib.check(lib.fimexcu_vertical_hybrid_pressure_f(method, a.ctypes.data, nO, nzi, nI, apv.ctypes.data, bv.ctypes.data, p.ctypes.data, p.shape[0],
+                                                      ps_scale, lv.ctypes.data, lv.size, valid_min, valid_max, badValue, fillValue, out.ctypes.data),
+               "verticalHybridPressure")
+    return out
+
+
+def _two_level(fn, A, B, a, b, x):
+    A, B = _f32(A).ravel(), _f32(B).ravel()
+    out = np.full(A.shape, 12345, dtype=np.float32)
+    rc = fn(A.ctypes.data, B.ctypes.data, out.ctypes.data, A.size, float(a), float(b), float(x))
+    return out, rc
+
+
+def mifi_get_values_nearest_f(A, B, a, b, x):
+    return _two_level(lib.fimexcu_get_values_nearest_f, A, B, a, b, x)
+
+
+def mifi_get_values_linear_f(A, B, a, b, x):
+    return _two_level(lib.fimexcu_get_values_linear_f, A, B, a, b, x)
+
+
+def mifi_get_values_linear_weak_extrapol_f(A, B, a, b, x):
+    return _two_level(lib.fimexcu_get_values_linear_weak_extrapol_f, A, B, a, b, x)
+
+
+def mifi_get_values_linear_no_extrapol_f(A, B, a, b, x):
+    return _two_level(lib.fimexcu_get_values_linear_no_extrapol_f, A, B, a, b, x)
+
+
+def mifi_get_values_linear_const_extrapol_f(A, B, a, b, x):
+    return _two_level(lib.fimexcu_get_values_linear_const_extrapol_f, A, B, a, b, x)
+
+
+def mifi_get_values_log_f(A, B, a, b, x):
+    return _two_level(lib.fimexcu_get_values_log_f, A, B, a, b, x)
+
+
+def mifi_get_values_log_log_f(A, B, a, b, x):
+    return _two_level(lib.fimexcu_get_values_log_log_f, A, B, a, b, x)

@@ -85,5 +85,37 @@ def main():
     print("wrote reference_small.npz with", len(out), "arrays")
 
 
+
+def vertical_fixtures():
+    """The reference's own expected-output files of its vertical-interpolation shell tests
+    (test/testVerticalInterpolatorSigmaHybridToPressure.sh, test/testVerticalInterpolatorEnsembleSigmaHybridToPressure.sh:
+    fimex --verticalInterpolate.type=pressure --verticalInterpolate.method=log --verticalInterpolate.level1=1000,850,500,300,100,50),
+    NetCDF-3 classic, read with scipy.  Stored: the raw inputs the hot loop sees and the values fimex wrote."""
+    from scipy.io import netcdf_file
+    d = "/root/reference/test/"
+    out = {}
+    fi, fo = netcdf_file(d + "verticalSigmaHybrid.nc", mmap=False), netcdf_file(d + "verticalSigmaHybridPressure.nc", mmap=False)
+    out["sh_ap_pa"] = fi.variables["ap"].data.astype(np.float64)
+    out["sh_b"] = fi.variables["b"].data.astype(np.float64)
+    psv = fi.variables["air_pressure"]
+    out["sh_ps_raw"] = psv.data.astype(np.float32)                     # packed short, unit hPa after scaling
+    out["sh_ps_scale"] = np.float64(psv.scale_factor)
+    out["sh_levels"] = fo.variables["pressure"].data.astype(np.float64)
+    for n in ("air_potential_temperature", "specific_humidity"):
+        out["sh_in_" + n] = fi.variables[n].data.astype(np.float32)    # (time, k, Yc, Xc), _FillValue 9.96921e36
+        out["sh_ex_" + n] = fo.variables[n].data.astype(np.float32)    # (time, pressure, Yc, Xc)
+    fi, fo = netcdf_file(d + "testdata_vertical_ensemble_in.nc", mmap=False), netcdf_file(d + "testdata_vertical_ensemble_ex.nc", mmap=False)
+    out["en_ap_pa"] = fi.variables["ap"].data.astype(np.float64)
+    out["en_b"] = fi.variables["b"].data.astype(np.float64)
+    out["en_ps_pa"] = fi.variables["surface_air_pressure"].data.astype(np.float32)  # (time, height0, ensemble, y, x)
+    out["en_levels"] = fo.variables["pressure"].data.astype(np.float64)
+    for n in ("specific_humidity_ml", "x_wind_ml", "y_wind_ml", "upward_air_velocity_ml"):
+        out["en_in_" + n] = fi.variables[n].data.astype(np.int32)      # packed int32, _FillValue -2147483647: the loop sees the raw numbers as f32
+        out["en_ex_" + n] = fo.variables[n].data.astype(np.int32)      # (time, pressure, ensemble, y, x)
+    np.savez_compressed(os.path.join(HERE, "reference_vertical.npz"), **out)
+    print("wrote reference_vertical.npz with", len(out), "arrays")
+
+
 if __name__ == "__main__":
     main()
+    vertical_fixtures()

@@ -1,0 +1,240 @@
+"""GPU parity tests of the vertical path (K14/K15), the two-level kernels and the forward aggregation (K11-K13),
+through the C ABI.  Checker: oracle/liboracle.so and the committed reference fixtures.
+Bar: bit-exact for every method except the log / log_log weights, which go through the device's f64 log():
+those values are compared within 1e-5 relative (BASELINE.json), their undefined masks bit-exactly."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from oracle_lib import dp, fp
+
+pytestmark = pytest.mark.gpu
+NAN = float("nan")
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _eq(a, b):
+    a, b = np.asarray(a), np.asarray(b)
+    na, nb = np.isnan(a), np.isnan(b)
+    return a.shape == b.shape and np.array_equal(na, nb) and np.array_equal(a[~na], b[~nb])
+
+
+def _close(a, b, rtol=1e-5):
+    a, b = np.asarray(a), np.asarray(b)
+    na, nb = np.isnan(a), np.isnan(b)
+    return a.shape == b.shape and np.array_equal(na, nb) and np.allclose(a[~na], b[~nb], rtol=rtol, atol=0)
+
+
+@pytest.fixture(scope="module")
+def fx():
+    import fimex_b200
+    assert fimex_b200.lib.fimexcu_device_count() >= 1
+    return fimex_b200
+
+
+def _oracle_vertical(method, fld, vc, levels=None, vout=None, vmin=None, vmax=None, valid_min=NAN, valid_max=NAN):
+    """fld, vc: [nO][nzi][nI] -> [nO][nzo][nI] with the oracle (one outer slice at a time)"""
+    o = ol.oracle()
+    nO, nzi, nI = fld.shape
+    nzo = len(levels) if levels is not None else vout.shape[1]
+    out = np.empty((nO, nzo, nI), np.float32)
+    lv = None if levels is None else np.ascontiguousarray(levels, dtype=np.float64)
+    for k in range(nO):
+        f, v = np.ascontiguousarray(fld[k]), np.ascontiguousarray(vc[k])
+        vo = None if vout is None else np.ascontiguousarray(vout[k])
+        mn = None if vmin is None else np.ascontiguousarray(vmin[k])
+        mx = None if vmax is None else np.ascontiguousarray(vmax[k])
+        res = np.empty((nzo, nI), np.float32)
+        rc = o.orc_vertical_interpolate_f(method, fp(f), fp(v), nzi, nI, None if lv is None else dp(lv), None if vo is None else fp(vo), nzo,
+                                          None if mn is None else dp(mn), None if mx is None else dp(mx), valid_min, valid_max, fp(res))
+        assert rc == 1
+        out[k] = res
+    return out
+
+
+def _columns(rng, nO, nzi, nI, kind):
+    if kind == "pressure":  # hybrid-like, decreasing upwards, column dependent
+        ps = rng.uniform(950, 1040, (nO, 1, nI))
+        eta = np.linspace(0.01, 1.0, nzi)[None, :, None]
+        vc = (ps * eta + 5 * (1 - eta)).astype(np.float32)
+    elif kind == "reversed":
+        ps = rng.uniform(950, 1040, (nO, 1, nI))
+        eta = np.linspace(1.0, 0.01, nzi)[None, :, None]
+        vc = (ps * eta).astype(np.float32)
+    else:  # unordered with duplicates and NaN
+        vc = rng.choice(np.arange(1, 40, dtype=np.float32) * 25, (nO, nzi, nI)).astype(np.float32)
+        vc[rng.random(vc.shape) < 0.02] = np.nan
+    fld = rng.normal(280, 20, (nO, nzi, nI)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.03] = np.nan
+    return fld, np.ascontiguousarray(vc)
+
+
+@pytest.mark.parametrize("method", [ol.VINT_LIN, ol.VINT_LOG, ol.VINT_LOGLOG, ol.VINT_NN, ol.VINT_LIN_WEAK, ol.VINT_LIN_NO, ol.VINT_LIN_CONST])
+@pytest.mark.parametrize("kind", ["pressure", "reversed", "unordered"])
+def test_vertical_fixed_levels_vs_oracle(fx, method, kind):
+    from fimex_b200.vertical import verticalInterpolate
+    rng = np.random.default_rng(100 * method + len(kind))
+    nO, nzi, nI = 3, 65, 517
+    fld, vc = _columns(rng, nO, nzi, nI, kind)
+    levels = [1000., 925., 850., 700., 500., 400., 300., 250., 200., 150., 100., 50., 1100., 5., float(vc[0, 0, 0])]
+    want = _oracle_vertical(method, fld, vc, levels=levels)
+    got = verticalInterpolate(method, fld, vc, level1=levels)
+    if method in (ol.VINT_LOG, ol.VINT_LOGLOG):
+        assert _close(got, want)
+    else:
+        assert _eq(got, want)
+    assert np.isnan(want).any() and (~np.isnan(want)).any()
+
+
+def test_vertical_validity_clamp_bad_fill_and_template_axis(fx, oracle):
+    """converter validity range (CDMVerticalInterpolator.cc:505-528), valid_min/valid_max clamp (:551-561), an output vertical
+    coordinate instead of fixed levels (template / to-axis) and the fused bad/fill conversions; device-resident."""
+    import torch
+    from fimex_b200.vertical import verticalInterpolate
+    rng = np.random.default_rng(3)
+    nO, nzi, nI, nzo = 2, 40, 300, 9
+    fld, vc = _columns(rng, nO, nzi, nI, "pressure")
+    vout = np.sort(rng.uniform(20, 1050, (nO, nzo, nI)).astype(np.float32), axis=1)
+    vmin = rng.uniform(0, 200, (nO, nI))
+    vmax = rng.uniform(800, 1100, (nO, nI))
+    bad, fill = np.float32(-999.), np.float32(1e30)
+    raw = fld.copy()
+    raw[np.isnan(raw)] = bad
+    for kw in (dict(vmin=vmin, vmax=vmax), dict(vmin=vmin), dict(vmax=vmax), {}):
+        want = _oracle_vertical(ol.VINT_LIN, fld, vc, vout=vout, valid_min=250., valid_max=300., **kw)
+        oracle.orc_nanf2bad(fp(want), want.size, fill)
+        got = verticalInterpolate(ol.VINT_LIN, torch.from_numpy(raw).cuda(), torch.from_numpy(vc).cuda(), verticalOut=torch.from_numpy(vout).cuda(),
+                                  validMin=torch.from_numpy(kw["vmin"]).cuda() if "vmin" in kw else None,
+                                  validMax=torch.from_numpy(kw["vmax"]).cuda() if "vmax" in kw else None, valid_min=250., valid_max=300.,
+                                  badValue=float(bad), fillValue=float(fill))
+        torch.cuda.synchronize()
+        assert _eq(got.cpu().numpy(), want)
+
+
+def test_vertical_hybrid_pressure_matches_fimex_output_files(fx):
+    """the reference's own expected files (see tests/golden/make_golden.py): pressure formed on the fly from ap, b, ps"""
+    from fimex_b200.vertical import verticalHybridPressure
+    from test_oracle_golden import cdmcmp_close
+    g = np.load(os.path.join(GOLD, "reference_vertical.npz"))
+    lev = g["sh_levels"]
+    bad = 9.96921e36
+    for name in ("air_potential_temperature", "specific_humidity"):
+        v, e = g["sh_in_" + name], g["sh_ex_" + name]
+        nt, nk, ny, nx = v.shape
+        for t in range(nt):
+            out = verticalHybridPressure(ol.VINT_LOG, v[t].reshape(1, nk, ny * nx), g["sh_ap_pa"] * 0.01, g["sh_b"], g["sh_ps_raw"][t].reshape(1, -1),
+                                         lev, ps_scale=float(g["sh_ps_scale"]), badValue=bad, fillValue=bad)
+            assert cdmcmp_close(out[0], e[t].reshape(lev.size, -1)).all(), (name, t)
+    lev = g["en_levels"]
+    for name in ("specific_humidity_ml", "x_wind_ml", "y_wind_ml", "upward_air_velocity_ml"):
+        v, e = g["en_in_" + name], g["en_ex_" + name]
+        nt, nk = v.shape[:2]
+        ncol = int(np.prod(v.shape[2:]))
+        for t in range(nt):
+            out = verticalHybridPressure(ol.VINT_LOG, v[t].reshape(1, nk, ncol).astype(np.float32), g["en_ap_pa"] * 0.01, g["en_b"],
+                                         g["en_ps_pa"][t].reshape(1, ncol), lev, ps_scale=0.01, badValue=-2147483647.0)[0]
+            got = np.where(np.isnan(out), -2147483647, np.sign(out) * np.floor(np.abs(out.astype(np.float64)) + 0.5)).astype(np.int64)
+            exp = e[t].reshape(lev.size, ncol).astype(np.int64)
+            # the packed integers fimex wrote; a 1-ulp difference of a log weight may move a value sitting on .5 by one count
+            assert np.abs(got - exp).max() <= 1 and (got != exp).mean() < 1e-3, (name, t)
+
+
+def test_vertical_hybrid_pressure_vs_oracle_config5_shape(fx):
+    """BASELINE configs[4] layout: (hybrid=65, member, y, x) -> 12 pressure levels, ps broadcast or per member"""
+    from fimex_b200.vertical import verticalHybridPressure
+    rng = np.random.default_rng(12)
+    g = np.load(os.path.join(GOLD, "reference_vertical.npz"))
+    ap, b = g["en_ap_pa"] * 0.01, g["en_b"]
+    nmem, ny, nx = 4, 23, 31
+    nI = nmem * ny * nx
+    levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50], dtype=np.float64)
+    ps = (101325 - 12 * rng.uniform(0, 2500, nI) + rng.normal(0, 300, nI)).astype(np.float32)
+    fld = rng.normal(0, 10, (1, 65, nI)).astype(np.float32)
+    p = (ap[:, None] + b[:, None] * (ps.astype(np.float64) * 0.01)[None, :]).astype(np.float32)[None]
+    want = _oracle_vertical(ol.VINT_LIN, fld, np.ascontiguousarray(p), levels=levels)
+    got = verticalHybridPressure(ol.VINT_LIN, fld, ap, b, ps.reshape(1, nI), levels, ps_scale=0.01)
+    assert _eq(got, want)
+    wantl = _oracle_vertical(ol.VINT_LOG, fld, np.ascontiguousarray(p), levels=levels)
+    gotl = verticalHybridPressure(ol.VINT_LOG, fld, ap, b, ps.reshape(1, nI), levels, ps_scale=0.01)
+    assert _close(gotl, wantl)
+
+
+@pytest.mark.parametrize("name", ["nearest", "linear", "linear_weak_extrapol", "linear_no_extrapol", "linear_const_extrapol", "log", "log_log"])
+def test_two_level_kernels(fx, oracle, name):
+    import fimex_b200.vertical as V
+    rng = np.random.default_rng(7)
+    fo, fg = getattr(oracle, f"orc_get_values_{name}_f"), getattr(V, f"mifi_get_values_{name}_f")
+    n = 1000
+    for _ in range(40):
+        A = rng.normal(size=n).astype(np.float32)
+        B = rng.normal(size=n).astype(np.float32)
+        A[rng.random(n) < 0.1] = np.nan
+        xa, xb = rng.uniform(1, 1000, 2)
+        x = float(rng.choice([xa, xb, rng.uniform(-100, 1500), (xa + xb) / 2]))
+        if rng.random() < 0.1:
+            xb = xa
+        want = np.full(n, 12345, np.float32)
+        rc = fo(fp(A), fp(B), fp(want), n, xa, xb, x)
+        got, rcg = fg(A, B, xa, xb, x)
+        assert rc == rcg and _eq(got, want)
+
+
+# ---------------------------------------------------------------------------------- forward aggregation
+FWD = [("sum", ol.FWD_SUM), ("mean", ol.FWD_MEAN), ("median", ol.FWD_MEDIAN), ("max", ol.FWD_MAX), ("min", ol.FWD_MIN),
+       ("undef_sum", ol.FWD_UNDEF_SUM), ("undef_mean", ol.FWD_UNDEF_MEAN), ("undef_max", ol.FWD_UNDEF_MAX), ("undef_min", ol.FWD_UNDEF_MIN)]
+
+
+@pytest.mark.parametrize("name,method", FWD)
+def test_forward_golden(fx, name, method):
+    g = np.load(os.path.join(GOLD, "reference_small.npz"))
+    in_x, in_y, out_x, out_y, nz = (int(v) for v in g["f_dims"])
+    ci = fx.CachedForwardInterpolation("x", "y", method, g["f_px"], g["f_py"], in_x, in_y, out_x, out_y)
+    out, n = ci.interpolateValues(ci.reduceInput(g["f_field"], in_x, in_y))
+    assert n == nz * out_x * out_y
+    assert _eq(out, g[f"f_{name}_out"])  # the reference's own output (level-0 quirk included)
+
+
+@pytest.mark.parametrize("method", [m for _, m in FWD] + [ol.FWD_UNDEF_MEDIAN])
+@pytest.mark.parametrize("compat", [True, False])
+def test_forward_vs_oracle(fx, method, compat):
+    rng = np.random.default_rng(method)
+    in_x, in_y, out_x, out_y, nz = 203, 157, 41, 33, 4
+    pox = rng.uniform(-3, out_x + 2, in_x * in_y)
+    poy = rng.uniform(-3, out_y + 2, in_x * in_y)
+    pox[:50] = np.round(pox[:50] * 2) / 2
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.1] = np.nan
+    want, info = ol.o_cached_apply(method, pox, poy, in_x, in_y, out_x, out_y, fld, level_bug=1 if compat else 0)
+    ci = fx.CachedForwardInterpolation("x", "y", method, pox, poy, in_x, in_y, out_x, out_y, level_compat=compat)
+    assert (ci.getInX(), ci.getInY(), ci.reducedDomain() is not None) == (info["inX"], info["inY"], info["reduced"])
+    got, _ = ci.interpolateValues(ci.reduceInput(fld, in_x, in_y))
+    assert _eq(got, want)
+    if not compat:
+        assert not _eq(got[0], got[1])
+
+
+def test_forward_reduced_window_bad_fill_and_swath_shape(fx, oracle):
+    """a 2030x1354 swath-sized source onto a small grid: long segments, reduced window, fused bad/fill, device resident"""
+    import torch
+    rng = np.random.default_rng(5)
+    in_x, in_y, out_x, out_y, nz = 1354, 2030, 120, 90, 2
+    gx, gy = np.meshgrid(np.arange(in_x), np.arange(in_y))
+    pox = (gx - 300) * (out_x / 700.0) + rng.normal(0, 0.2, gx.shape)   # only part of the swath hits the target
+    poy = (gy - 500) * (out_y / 900.0) + rng.normal(0, 0.2, gx.shape)
+    bad, fill = np.float32(-1e30), np.float32(9.96921e36)
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.3] = np.nan      # "30 % land-masked"
+    for method in (ol.FWD_MEAN, ol.FWD_MAX, ol.FWD_MEDIAN):
+        want, info = ol.o_cached_apply(method, pox.ravel(), poy.ravel(), in_x, in_y, out_x, out_y, fld, level_bug=0)
+        oracle.orc_nanf2bad(fp(want), want.size, fill)
+        ci = fx.CachedForwardInterpolation("x", "y", method, pox.ravel(), poy.ravel(), in_x, in_y, out_x, out_y, level_compat=False)
+        assert info["reduced"] and ci.reducedDomain() is not None
+        assert (ci.reducedDomain().xMin, ci.reducedDomain().yMin, ci.getInX(), ci.getInY()) == (info["xMin"], info["yMin"], info["inX"], info["inY"])
+        raw = fld.copy()
+        raw[np.isnan(raw)] = bad
+        d_in = torch.from_numpy(ci.reduceInput(raw, in_x, in_y)).cuda()
+        got, _ = ci.interpolateValues(d_in, badValue=float(bad), fillValue=float(fill))
+        torch.cuda.synchronize()
+        assert _eq(got.cpu().numpy(), want)

@@ -186,3 +186,55 @@ def test_hybrid_sigma_pressure_formula(oracle):
     p = np.zeros(3)
     oracle.orc_atmosphere_hybrid_sigma_ap_pressure(3, 101325., dp(ap), dp(b), dp(p))
     np.testing.assert_array_equal(p, ap + b * 101325.)
+
+
+# ---------------------------------------------------------------------------------- the reference's own output files (vertical)
+def _vertical_golden():
+    import os
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_vertical.npz"))
+
+
+def cdmcmp_close(a, b, tol=1e-3):
+    """test/cdmcmp.cc:87-164: |a-b| <= tol*|a| and <= tol*|b| (or equal)"""
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    d = np.abs(a - b)
+    return (a == b) | ((d <= tol * np.abs(a)) & (d <= tol * np.abs(b)))
+
+
+def test_vertical_oracle_reproduces_fimex_output_sigma_hybrid(oracle):
+    """verticalSigmaHybrid.nc -> verticalSigmaHybridPressure.nc (testVerticalInterpolatorSigmaHybridToPressure.sh)"""
+    g = _vertical_golden()
+    ap, b, lev = g["sh_ap_pa"] * 0.01, g["sh_b"], g["sh_levels"]
+    ps = g["sh_ps_raw"].astype(np.float64) * float(g["sh_ps_scale"])  # hPa
+    bad = np.float32(9.96921e36)
+    for name in ("air_potential_temperature", "specific_humidity"):
+        v, e = g["sh_in_" + name], g["sh_ex_" + name]
+        nt, nk, ny, nx = v.shape
+        for t in range(nt):
+            fld = v[t].reshape(nk, ny * nx).copy()
+            oracle.orc_bad2nanf(fp(fld), fld.size, bad)
+            p = np.ascontiguousarray((ap[:, None] + b[:, None] * ps[t].reshape(1, -1)).astype(np.float32))
+            out = np.empty((lev.size, ny * nx), np.float32)
+            assert oracle.orc_vertical_interpolate_f(1, fp(fld), fp(p), nk, ny * nx, dp(lev), None, lev.size, None, None, NAN, NAN, fp(out)) == 1
+            oracle.orc_nanf2bad(fp(out), out.size, bad)
+            assert cdmcmp_close(out, e[t].reshape(lev.size, -1)).all(), (name, t)
+
+
+def test_vertical_oracle_reproduces_fimex_output_ensemble(oracle):
+    """testdata_vertical_ensemble_in.nc -> _ex.nc: (time, hybrid=65, ensemble=3, y, x), packed int32 variables whose raw
+    numbers are interpolated as f32 and written back with lround (DataUtils.h:55-58)."""
+    g = _vertical_golden()
+    ap, b, lev = g["en_ap_pa"] * 0.01, g["en_b"], g["en_levels"]
+    ps = g["en_ps_pa"].astype(np.float64) * 0.01  # Pa -> hPa
+    for name in ("specific_humidity_ml", "x_wind_ml", "y_wind_ml", "upward_air_velocity_ml"):
+        v, e = g["en_in_" + name], g["en_ex_" + name]
+        nt, nk = v.shape[:2]
+        ncol = int(np.prod(v.shape[2:]))
+        for t in range(nt):
+            fld = v[t].reshape(nk, ncol).astype(np.float32)
+            oracle.orc_bad2nanf(fp(fld), fld.size, np.float32(-2147483647))
+            p = np.ascontiguousarray((ap[:, None] + b[:, None] * ps[t].reshape(1, ncol)).astype(np.float32))
+            out = np.empty((lev.size, ncol), np.float32)
+            oracle.orc_vertical_interpolate_f(1, fp(fld), fp(p), nk, ncol, dp(lev), None, lev.size, None, None, NAN, NAN, fp(out))
+            got = np.where(np.isnan(out), -2147483647, np.sign(out) * np.floor(np.abs(out.astype(np.float64)) + 0.5)).astype(np.int64)
+            assert np.array_equal(got, e[t].reshape(lev.size, ncol).astype(np.int64)), (name, t)
