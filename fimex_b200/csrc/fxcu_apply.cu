@@ -839,7 +839,7 @@ static int pick_zchunk(size_t tiles, int nz)
     return static_cast<int>((nz + chunks - 1) / chunks);
 }
 
-static fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, size_t inX, size_t inY, size_t outX, size_t outY, cudaStream_t s)
+fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, size_t inX, size_t inY, size_t outX, size_t outY, cudaStream_t s)
 {
     if (!require_device())
         return nullptr;

@@ -22,3 +22,10 @@ struct fimexcu_vecrot {
     size_t ox = 0, oy = 0;
     fxcu::DevBuf c, s, deg; // f64 [ox*oy] each: cos, sin, angle in degree
 };
+
+namespace fxcu {
+// fxcu_apply.cu: cache construction from DEVICE index tables (K2/K3 tail: reduced domain, table entries)
+fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, size_t inX, size_t inY, size_t outX, size_t outY, cudaStream_t s);
+// fxcu_axes.cu: mifi_points2position on device points with the axis already on the device
+int points2position_dev(double* d_points, size_t n, const double* d_axis, const double* axis_host, int num, int axis_type, cudaStream_t s);
+}

@@ -868,3 +868,168 @@ int orc_vertical_interpolate_f(int method, const float* in, const float* vcoord_
     }
     return ORC_OK;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * src/CDMInterpolator.cc:953-1028 -- coord_kdtree without the tree (see header).
+ * ------------------------------------------------------------------------------------------ */
+#define ORC_D2R 0.017453292519943296 /* deg_to_rad<double>, MathUtils.h:158-162 */
+
+int orc_kdtree_translate(double maxDist_m, double* px, double* py, size_t nPoints, const double* lon, const double* lat, size_t nx, size_t ny,
+                         double* gap)
+{
+    const size_t n = nx * ny;
+    double* c = (double*)malloc((n ? n : 1) * 3 * sizeof(double));
+    for (size_t i = 0; i < n; ++i) {
+        if (!(isnan(lat[i]) || isnan(lon[i]))) {
+            const double la = lat[i] * ORC_D2R, lo = lon[i] * ORC_D2R;
+            c[3 * i] = cos(la) * cos(lo);
+            c[3 * i + 1] = cos(la) * sin(lo);
+            c[3 * i + 2] = sin(la);
+        } else {
+            c[3 * i] = c[3 * i + 1] = c[3 * i + 2] = nan("");
+        }
+    }
+    const double r = maxDist_m / 6371000.;
+    const double r2 = r * r;
+    for (size_t q = 0; q < nPoints; ++q) {
+        const double la = py[q] * ORC_D2R, lo = px[q] * ORC_D2R;
+        const double q0 = cos(la) * cos(lo), q1 = cos(la) * sin(lo), q2 = sin(la);
+        double best = HUGE_VAL, second = HUGE_VAL;
+        size_t bi = (size_t)-1;
+        for (size_t i = 0; i < n; ++i) {
+            const double d0 = q0 - c[3 * i], d1 = q1 - c[3 * i + 1], d2 = q2 - c[3 * i + 2];
+            double d = 0;
+            d += d0 * d0;
+            d += d1 * d1;
+            d += d2 * d2;
+            if (!(d < r2))
+                continue;
+            if (d < best) {
+                second = best;
+                best = d;
+                bi = i;
+            } else if (d < second) {
+                second = d;
+            }
+        }
+        if (gap)
+            gap[q] = second - best;
+        if (bi != (size_t)-1) {
+            px[q] = (double)(bi % nx);
+            py[q] = (double)(bi / nx);
+        } else {
+            px[q] = -1000;
+            py[q] = -1000;
+        }
+    }
+    free(c);
+    return ORC_OK;
+}
+
+/* src/CDMInterpolator.cc:1030-1090 */
+double orc_get_grid_distance(const double* lon, const double* lat, size_t nx, size_t ny)
+{
+    const size_t n = nx * ny;
+    int steps;
+    size_t stepSize;
+    if (n > 1000) {
+        steps = 53;
+        stepSize = n / steps;
+    } else {
+        stepSize = 1;
+        steps = (int)n;
+    }
+    double min_sample = 2;
+    for (int ik = 0; ik < steps; ++ik) {
+        const size_t sp = ik * stepSize;
+        const double lon0 = lon[sp] * ORC_D2R, lat0 = lat[sp] * ORC_D2R;
+        if (isnan(lon0) || isnan(lat0))
+            continue;
+        double best = -2;
+        for (size_t pos = 0; pos < n; ++pos) {
+            if (pos == sp)
+                continue;
+            const double lon1 = lon[pos] * ORC_D2R, lat1 = lat[pos] * ORC_D2R;
+            if (isnan(lon1) || isnan(lat1))
+                continue;
+            const double dlon = lon0 - lon1;
+            const double cd = cos(lat0) * cos(lat1) * cos(dlon) + sin(lat0) * sin(lat1);
+            if (cd > best)
+                best = cd;
+        }
+        if (best < min_sample)
+            min_sample = best;
+    }
+    const double d = acos(min_sample) * 1.414;
+    return d < 3.1415926535897932384626433832795 ? d : 3.1415926535897932384626433832795;
+}
+
+typedef struct { double lat, lon, x, y; } orc_llpoint;
+
+static int orc_cmp_ll(const void* a, const void* b)
+{
+    const double la = ((const orc_llpoint*)a)->lat, lb = ((const orc_llpoint*)b)->lat;
+    return (la > lb) - (la < lb);
+}
+
+/* src/CDMInterpolator.cc:1112-1190 */
+int orc_coordnn_translate(double* px, double* py, size_t nPoints, const double* lon, const double* lat, size_t nx, size_t ny)
+{
+    const double max_grid_d = orc_get_grid_distance(lon, lat, nx, ny);
+    const double min_grid_cos_d = cos(max_grid_d);
+    orc_llpoint* ll = (orc_llpoint*)malloc((nx * ny ? nx * ny : 1) * sizeof(orc_llpoint));
+    size_t m = 0;
+    for (size_t ix = 0; ix < nx; ++ix)
+        for (size_t iy = 0; iy < ny; ++iy) {
+            const size_t pos = ix + iy * nx;
+            if (!(isnan(lon[pos]) || isnan(lat[pos]))) {
+                ll[m].lat = lat[pos] * ORC_D2R;
+                ll[m].lon = lon[pos] * ORC_D2R;
+                ll[m].x = (double)ix;
+                ll[m].y = (double)iy;
+                ++m;
+            }
+        }
+    qsort(ll, m, sizeof(orc_llpoint), orc_cmp_ll);
+    for (size_t q = 0; q < nPoints; ++q) {
+        const double plat = py[q] * ORC_D2R, plon = px[q] * ORC_D2R;
+        double rx = -1., ry = -1.;
+        double min_cos_d = min_grid_cos_d, min_d = acos(min_cos_d);
+        size_t lo = 0, hi = m; /* lower_bound on latitude */
+        while (lo < hi) {
+            const size_t mid = (lo + hi) / 2;
+            if (ll[mid].lat < plat)
+                lo = mid + 1;
+            else
+                hi = mid;
+        }
+        for (size_t it = lo; it < m; ++it) {
+            if (fabs(ll[it].lat - plat) > min_d)
+                break;
+            const double dlon = ll[it].lon - plon;
+            const double cd = cos(ll[it].lat) * cos(plat) * cos(dlon) + sin(ll[it].lat) * sin(plat);
+            if (cd > min_cos_d) {
+                min_cos_d = cd;
+                min_d = acos(min_cos_d);
+                rx = ll[it].x;
+                ry = ll[it].y;
+            }
+        }
+        for (size_t it = lo; it-- > 0;) {
+            if (fabs(ll[it].lat - plat) > min_d)
+                break;
+            const double dlon = ll[it].lon - plon;
+            const double cd = cos(ll[it].lat) * cos(plat) * cos(dlon) + sin(ll[it].lat) * sin(plat);
+            if (cd > min_cos_d) {
+                min_cos_d = cd;
+                min_d = acos(min_cos_d);
+                rx = ll[it].x;
+                ry = ll[it].y;
+            }
+        }
+        px[q] = rx;
+        py[q] = ry;
+    }
+    free(ll);
+    return ORC_OK;
+}

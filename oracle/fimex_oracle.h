@@ -152,6 +152,19 @@ int orc_vertical_interpolate_f(int method, const float* in, const float* vcoord_
                                const float* vcoord_out, size_t nzo, const double* vmin, const double* vmax, double valid_min,
                                double valid_max, float* out);
 
+/* ---- src/CDMInterpolator.cc:953-1028 (coord_kdtree) stated without nanoflann: for each target the source point with the
+ * smallest squared chord distance on the unit sphere, strictly below (maxDist/R)^2; misses give -1000.  Brute force, O(N*M):
+ * small cases only.  Exact-distance ties go to the lower source index here; nanoflann's own choice (tree order) is available
+ * from oracle/_ref (ref_kdtree_translate).  second_best_gap[i] (may be NULL) receives d2(second best) - d2(best), so that tests
+ * can tell genuine ties / near-ties from disagreements. ---- */
+int orc_kdtree_translate(double maxDist_m, double* pointsOnX_deg, double* pointsOnY_deg, size_t nPoints, const double* lon_deg,
+                         const double* lat_deg, size_t nx, size_t ny, double* second_best_gap);
+/* ---- src/CDMInterpolator.cc:1030-1190 (coord_nearestneighbor): getGridDistance + fastTranslatePointsToClosestInputCell,
+ * restated literally (latitude-sorted list, scan up then down).  Misses give -1. ---- */
+double orc_get_grid_distance(const double* lon_deg, const double* lat_deg, size_t nx, size_t ny);
+int orc_coordnn_translate(double* pointsOnX_deg, double* pointsOnY_deg, size_t nPoints, const double* lon_deg, const double* lat_deg, size_t nx,
+                          size_t ny);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1209,6 +1209,8 @@ int miniproj_inv(const miniproj_crs* c, double x, double y, double* lam, double*
 size_t miniproj_transform(const miniproj_crs* src, const miniproj_crs* dst, size_t n, double* x, double* y)
 {
     size_t failed = 0;
+    if (src->kind == MP_LONGLAT && dst->kind == MP_LONGLAT)
+        return 0; /* geographic -> geographic, no datum shift: degrees pass through untouched */
     for (size_t i = 0; i < n; ++i) {
         double lam, phi, ox, oy;
         if (miniproj_inv(src, x[i], y[i], &lam, &phi) || miniproj_fwd(dst, lam, phi, &ox, &oy)) {

@@ -106,6 +106,9 @@ def oracle():
         "orc_atmosphere_hybrid_height": (None, [C.c_size_t, C.c_double, c_double_p, c_double_p, c_double_p]),
         "orc_vertical_interpolate_f": (C.c_int, [C.c_int, c_float_p, c_float_p, C.c_size_t, C.c_size_t, c_double_p, c_float_p, C.c_size_t,
                                                  c_double_p, c_double_p, C.c_double, C.c_double, c_float_p]),
+        "orc_kdtree_translate": (C.c_int, [C.c_double, c_double_p, c_double_p, C.c_size_t, c_double_p, c_double_p, C.c_size_t, C.c_size_t, c_double_p]),
+        "orc_get_grid_distance": (C.c_double, [c_double_p, c_double_p, C.c_size_t, C.c_size_t]),
+        "orc_coordnn_translate": (C.c_int, [c_double_p, c_double_p, C.c_size_t, c_double_p, c_double_p, C.c_size_t, C.c_size_t]),
         "miniproj_transform_str": (C.c_long, [C.c_char_p, C.c_char_p, C.c_size_t, c_double_p, c_double_p, C.c_char_p, C.c_size_t]),
         "orc_reproject_axes": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, C.c_int, C.c_int, c_double_p, c_double_p]),
         "orc_get_vector_reproject_matrix": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, C.c_int, C.c_int, c_double_p]),

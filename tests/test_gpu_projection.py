@@ -1,0 +1,165 @@
+"""GPU tests of the cache build: lattice reprojection (K1), index tables (K2), rotation matrices (K8), through the C ABI.
+
+Checker: oracle/miniproj.c (CPU restatement of the published projection formulas; PARITY UNPINNED against real PROJ,
+see oracle/miniproj.h) and analytic identities.  Tolerances: 1e-6 m / 1e-9 deg on coordinates (device vs glibc libm
+differ in the last bits), 1e-9 cells on index tables, 1e-9 rad on rotation angles."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from oracle_lib import dp
+
+pytestmark = pytest.mark.gpu
+
+PROJS = {
+    "meps": "+proj=lcc +lat_0=63.3 +lon_0=15 +lat_1=63.3 +lat_2=63.3 +no_defs +R=6.371e+06",
+    "arome_arctic": "+proj=lcc +lat_0=77.5 +lon_0=335 +lat_1=77.5 +lat_2=77.5 +no_defs +R=6.371e+06",
+    "lcc_2sp_wgs84": "+proj=lcc +lat_1=60 +lat_2=70 +lat_0=65 +lon_0=10 +x_0=1000 +y_0=-2000 +ellps=WGS84",
+    "norkyst": "+proj=stere +ellps=WGS84 +lat_0=90.0 +lat_ts=60.0 +x_0=3192800 +y_0=1784000 +lon_0=70",
+    "stere_sphere": "+proj=stere +lat_0=90 +lon_0=-32 +lat_ts=60 +ellps=sphere +a=6371000 +e=0",
+    "stere_oblique": "+proj=stere +lat_0=55 +lon_0=12 +R=6371000",
+    "stere_oblique_ell": "+proj=stere +lat_0=55 +lon_0=12 +ellps=GRS80 +k=0.9999",
+    "hirlam": "+proj=ob_tran +o_proj=longlat +lon_0=-40 +o_lat_p=22 +R=6.371e+06 +no_defs",
+    "merc": "+proj=merc +lon_0=5 +lat_ts=60 +ellps=WGS84",
+    "merc_sphere": "+proj=merc +R=6371000",
+    "utm33": "+proj=utm +zone=33 +datum=WGS84 +units=m +no_defs",
+    "tmerc_sphere": "+proj=tmerc +lat_0=60 +lon_0=15 +R=6371000 +k=0.9996",
+    "laea_eu": "+proj=laea +lat_0=52 +lon_0=10 +x_0=4321000 +y_0=3210000 +ellps=GRS80 +units=m",
+    "laea_polar": "+proj=laea +lat_0=90 +lon_0=0 +R=6371000",
+}
+LL = "+proj=latlong +R=6.371e+06 +no_defs"
+LL_WGS = "+proj=latlong +datum=WGS84 +towgs84=0,0,0"
+
+
+@pytest.fixture(scope="module")
+def rp():
+    import fimex_b200
+    assert fimex_b200.lib.fimexcu_device_count() >= 1
+    from fimex_b200 import reproject
+    return reproject
+
+
+def _oracle_transform(src, dst, x, y):
+    xv, yv = np.array(x, dtype=np.float64).ravel().copy(), np.array(y, dtype=np.float64).ravel().copy()
+    err = C.create_string_buffer(200)
+    rc = ol.oracle().miniproj_transform_str(src.encode(), dst.encode(), xv.size, dp(xv), dp(yv), err, 200)
+    assert rc >= 0, err.value
+    return xv, yv
+
+
+@pytest.mark.parametrize("name", sorted(PROJS))
+def test_lonlat_to_projection_and_back(rp, name):
+    rng = np.random.default_rng(abs(hash(name)) % 1000)
+    lon = rng.uniform(-20, 50, 20000)
+    lat = rng.uniform(45, 85, 20000)
+    lon[:5] = [15, 15, 0, 179.9, -179.9]
+    lat[:5] = [63.3, 90, 60, 70, 70]
+    x, y = rp.reproject_values(LL, PROJS[name], lon, lat)
+    wx, wy = _oracle_transform(LL, PROJS[name], lon, lat)
+    fin = np.isfinite(wx)
+    assert np.array_equal(fin, np.isfinite(x))
+    tol = 1e-9 if name == "hirlam" else 1e-6
+    assert np.abs(x[fin] - wx[fin]).max() < tol and np.abs(y[fin] - wy[fin]).max() < tol
+    # and back: round trip to 1e-9 degree
+    lon2, lat2 = rp.reproject_values(PROJS[name], LL, x[fin], y[fin])
+    dlon = (lon2 - lon[fin] + 180) % 360 - 180
+    ok = np.abs(lat[fin]) < 89.999
+    rt = 2e-8 if name == "laea_eu" else 1e-9  # the authalic-latitude series of the ellipsoidal laea is itself good to ~1e-8 deg
+    assert np.abs(dlon[ok]).max() < rt and np.abs(lat2 - lat[fin]).max() < rt
+
+
+def test_known_coordinates(rp):
+    # UTM33 on the central meridian at 60 N: x = 500000, y = 0.9996 * meridian arc (6 654 072.819 m on WGS84)
+    x, y = rp.reproject_values(LL_WGS, PROJS["utm33"], [15.0], [60.0])
+    assert abs(x[0] - 500000.0) < 1e-6 and abs(y[0] - 0.9996 * 6654072.819) < 2e-3
+    # MEPS corners: (0,0) -> 50.32 N 0.28 E, (948,1068) -> 71.58 N 54.24 E
+    from fimex_b200 import synthetic as S
+    lon, lat = rp.reproject_values(S.MEPS_PROJ, LL, [S.MEPS_X0, S.MEPS_X0 + 948 * 2500], [S.MEPS_Y0, S.MEPS_Y0 + 1068 * 2500])
+    assert abs(lat[0] - 50.3196) < 1e-3 and abs(lon[0] - 0.2783) < 1e-3 and abs(lat[1] - 71.5760) < 1e-3 and abs(lon[1] - 54.2413) < 1e-3
+    # sphere -> WGS84 lat/lon is a null datum shift
+    lon, lat = rp.reproject_values(LL, LL_WGS, [12.5], [61.25])
+    assert lon[0] == 12.5 and lat[0] == 61.25
+    # unknown projection -> error with the reference's "Proj error" wording
+    import fimex_b200
+    with pytest.raises(fimex_b200.FimexCudaError, match="Proj error"):
+        rp.reproject_values("+proj=fork +lat_1000=123", LL, [0.0], [0.0])
+
+
+def test_meps_index_tables_built_on_device(rp):
+    """fimexcu_reproject_axes + mifi_points2position against the closed-form table generator and the oracle"""
+    import fimex_b200
+    from fimex_b200 import synthetic as S
+    lon, lat = S.target_axes("T1")
+    x, y = rp.reproject_axes(S.LATLON_PROJ, S.MEPS_PROJ, lon, lat)
+    mx, my = S.meps_axes()
+    px = fimex_b200.mifi_points2position(x, mx, 0)
+    py = fimex_b200.mifi_points2position(y, my, 0)
+    cx, cy, ox, oy = S.meps_index_tables("T1")
+    assert px.shape == (oy, ox)
+    assert np.abs(px - cx).max() < 1e-9 and np.abs(py - cy).max() < 1e-9
+    wx, wy = np.empty(ox * oy), np.empty(ox * oy)
+    ol.oracle().orc_reproject_axes(S.LATLON_PROJ.encode(), S.MEPS_PROJ.encode(), dp(lon), dp(lat), lon.size, lat.size, dp(wx), dp(wy))
+    assert np.abs(x.ravel() - wx).max() < 1e-6 and np.abs(y.ravel() - wy).max() < 1e-6
+
+
+def test_cache_from_projection_equals_cache_from_tables(rp):
+    """the one-call device build gives the same regridded values as tables -> createCachedInterpolation"""
+    import fimex_b200
+    from fimex_b200 import synthetic as S
+    lon, lat = S.target_axes("T2")
+    mx, my = S.meps_axes()
+    ci = rp.cachedInterpolationFromProjection(1, S.LATLON_PROJ, S.MEPS_PROJ, lon, lat, mx, my)
+    cx, cy, ox, oy = S.meps_index_tables("T2")
+    ref = fimex_b200.CachedInterpolation("x", "y", 1, cx, cy, S.MEPS_NX, S.MEPS_NY, ox, oy)
+    assert (ci.getInX(), ci.getInY()) == (ref.getInX(), ref.getInY()) == (505, 642)
+    assert (ci.reducedDomain().xMin, ci.reducedDomain().yMin) == (172, 205)
+    fld = S.meps_slab_numpy(t=1, nz=3)
+    a, _ = ci.interpolateValues(ci.reduceInput(fld, S.MEPS_NX, S.MEPS_NY))
+    b, _ = ref.interpolateValues(ref.reduceInput(fld, S.MEPS_NX, S.MEPS_NY))
+    assert not np.isnan(a).any()
+    assert np.allclose(a, b, rtol=1e-5, atol=0)  # tables agree to 1e-12 cells; weights to 1 ulp of f32
+
+
+@pytest.mark.parametrize("src,dst,kind", [("meps", LL, "deg"), ("meps", "stere_sphere", "m"), ("hirlam", "norkyst", "m"), ("utm33", LL_WGS, "deg"),
+                                          ("norkyst", "meps", "m")])
+def test_vector_reproject_matrix_vs_oracle(rp, src, dst, kind):
+    ps = PROJS[src]
+    pd = PROJS.get(dst, dst)
+    if kind == "deg":
+        ax, ay = np.arange(0., 30., 0.5), np.arange(55., 72., 0.5)
+    else:
+        cx, cy = _oracle_transform(LL, pd, [15.0], [65.0])
+        ax, ay = cx[0] + np.arange(-40, 40) * 10000.0, cy[0] + np.arange(-30, 30) * 10000.0
+    m = rp.get_vector_reproject_matrix(ps, pd, ax, ay)
+    want = np.empty(ax.size * ay.size * 3)
+    assert ol.oracle().orc_get_vector_reproject_matrix(ps.encode(), pd.encode(), dp(ax), dp(ay), ax.size, ay.size, dp(want)) == 0
+    want = want.reshape(ay.size, ax.size, 3)
+    assert np.abs(m[..., 0] - want[..., 0]).max() < 1e-7 and np.abs(m[..., 1] - want[..., 1]).max() < 1e-7
+    d = (m[..., 2] - want[..., 2] + 180) % 360 - 180
+    assert np.abs(d).max() < 1e-5
+    assert np.abs(m[..., 0] ** 2 + m[..., 1] ** 2 - 1).max() < 1e-12
+    # points variant
+    gx, gy = np.meshgrid(ax, ay)
+    mp = rp.get_vector_reproject_matrix_points(ps, pd, 0 if src == "hirlam" else 1, gx, gy)
+    wantp = np.empty(gx.size * 3)
+    assert ol.oracle().orc_get_vector_reproject_matrix_points(ps.encode(), pd.encode(), 0 if src == "hirlam" else 1, dp(np.ascontiguousarray(gx)),
+                                                              dp(np.ascontiguousarray(gy)), ax.size, ay.size, dp(wantp)) == 0
+    dp_ = (mp[..., 2].ravel() - wantp.reshape(-1, 3)[:, 2] + 180) % 360 - 180
+    assert np.abs(dp_).max() < 1e-3
+
+
+def test_rotation_90_degrees_between_polar_stereographic_grids(rp):
+    """test/testInterpolation.cc:387-470: stere lon_0=0 -> lon_0=90 turns (u, v) into (v, -u)"""
+    import fimex_b200
+    a = "+proj=stere +lat_0=90 +lon_0=0 +lat_ts=60 +ellps=sphere +a=6371000 +e=0"
+    b = "+proj=stere +lat_0=90 +lon_0=90 +lat_ts=60 +ellps=sphere +a=6371000 +e=0"
+    ax = np.arange(-5, 6) * 50000.0
+    ay = np.arange(-4, 5) * 50000.0 + 1e6
+    m = rp.get_vector_reproject_matrix(a, b, ax, ay)
+    cvr = fimex_b200.CachedVectorReprojection(m)
+    u = np.full((1, ay.size, ax.size), 3.0, np.float32)
+    v = np.full((1, ay.size, ax.size), -2.0, np.float32)
+    cvr.reprojectValues(u, v)
+    assert np.abs(u - (-2.0)).max() < 1e-4 and np.abs(v - (-3.0)).max() < 1e-4
