@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--target", default="T1", choices=["T1", "T2"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the short measurements of the other kernels of the path")
     return ap.parse_args()
 
 
@@ -185,6 +186,93 @@ def main_reference(args):
     return 0
 
 
+
+# ------------------------------------------------------------------------------------------------ the other kernels of the path
+def secondary_kernels(S, ci, px, py, ox, oy, peak):
+    """Short CUDA-event measurements (3 warm-up + 5 timed launches each) of the remaining SURVEY 8 kernels on BASELINE-shaped
+    inputs, each with its algorithmic bytes against the same measured HBM peak.  Reported under "kernels"."""
+    import torch
+    import fimex_b200
+    from fimex_b200 import _lib, interpolation as I, vertical as V, reproject as RP
+    lib = fimex_b200.lib
+    nz, nan = S.MEPS_NZ, float("nan")
+    stream = _lib.current_stream_ptr()
+    out = {}
+
+    def timed(fn, reps=5):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    def entry(ms, alg_bytes, points, what):
+        gbs = alg_bytes / (ms * 1e-3) / 1e9
+        return {"ms": ms, "Gpoints_per_s": points / (ms * 1e-3) / 1e9, "achieved_GBs": gbs, "frac_of_hbm_peak": gbs / peak,
+                "algorithmic_bytes": alg_bytes, "what": what}
+
+    inx, iny = ci.getInX(), ci.getInY()
+    pts = nz * ox * oy
+    alg = S.bilinear_algorithmic_bytes(inx * iny, ox * oy, nz)
+    src = S.meps_slab_torch(t=7, device="cuda")
+    dst = torch.empty((nz, oy, ox), dtype=torch.float32, device="cuda")
+    for name, method in (("K5_bicubic_apply", 2), ("K6_nearest_apply", 0)):
+        c = fimex_b200.createCachedInterpolation("x", "y", method, px, py, S.MEPS_NX, S.MEPS_NY, ox, oy)
+        sub = c.reduceInput(src, S.MEPS_NX, S.MEPS_NY)
+        ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_dev_f(c._h, sub.data_ptr(), nz, dst.data_ptr(), nan, nan, stream), name))
+        out[name] = entry(ms, alg, pts, "S->T1 slab, dense layout")
+        c.close()
+    # K7: fused u,v interpolation + rotation, and the stand-alone rotation
+    ang = np.random.default_rng(1).uniform(-0.6, 0.6, ox * oy)
+    cvr = I.CachedVectorReprojection(np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy(), ox, oy)
+    dst2 = torch.empty_like(dst)
+    sub = ci.reduceInput(src, S.MEPS_NX, S.MEPS_NY)
+    ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_uv_dev_f(ci._h, cvr._h, sub.data_ptr(), sub.data_ptr(), nz, dst.data_ptr(), dst2.data_ptr(),
+                                                                   nan, nan, nan, nan, stream), "uv"))
+    out["K7_fused_uv_bilinear_rotation"] = entry(ms, 2 * alg + 16.0 * ox * oy, 2 * pts, "u and v of one S->T1 slab in one pass")
+    ms = timed(lambda: _lib.check(lib.fimexcu_vecrot_apply_dev_f(cvr._h, dst.data_ptr(), dst2.data_ptr(), nz, stream), "rot"))
+    out["K7_rotation_alone"] = entry(ms, (16.0 + 16.0 / nz) * pts, 2 * pts, "in-place rotation of u,v [65][1021][2891]")
+    cvr.close()
+    del dst2
+    # K14+K15: hybrid-sigma -> 12 pressure levels, log, 30 members on the T2 grid (configs[4] shape, one time step)
+    g = np.random.default_rng(2)
+    ncol = 30 * 801 * 561
+    eta = np.linspace(0.0, 1.0, 65)
+    ap, b = 100.0 * (1 - eta) * 0.2 * eta * 4 + 0.1, eta ** 1.5  # hPa; smooth hybrid coefficients, model top ~0.1 hPa
+    ps = torch.from_numpy((101325 - 12 * g.uniform(0, 2500, 801 * 561) + g.normal(0, 300, 801 * 561)).astype(np.float32)).cuda()
+    ps = ps.repeat(30).reshape(1, ncol).contiguous()
+    vin = torch.randn((1, 65, ncol), dtype=torch.float32, device="cuda")
+    levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50], dtype=np.float64)
+    ms = timed(lambda: V.verticalHybridPressure(1, vin, ap, b, ps, levels, ps_scale=0.01), reps=3)
+    out["K14_K15_vertical_hybrid_to_pressure_log"] = entry(ms, 312.0 * ncol, 12 * ncol, "65 -> 12 levels, 30 members x 801x561 columns, p formed on the fly")
+    del vin, ps
+    # K12: forward mean, 2030x1354 swath -> 1000x1000 cells, 8 levels (level_compat off: every level aggregated)
+    gx, gy = np.meshgrid(np.arange(1354), np.arange(2030))
+    fwd = I.CachedForwardInterpolation("x", "y", 6, (gx * (1000 / 1354.0)).ravel() - 0.3, (gy * (1000 / 2030.0)).ravel() - 0.3, 1354, 2030, 1000, 1000,
+                                       level_compat=False)
+    fin = torch.randn((8, fwd.getInY(), fwd.getInX()), dtype=torch.float32, device="cuda")
+    fout = torch.empty((8, 1000, 1000), dtype=torch.float32, device="cuda")
+    ms = timed(lambda: _lib.check(lib.fimexcu_forward_apply_dev_f(fwd._h, fin.data_ptr(), 8, fout.data_ptr(), nan, nan, 0, stream), "fwd"))
+    n_in = fwd.getInX() * fwd.getInY()
+    out["K12_forward_mean"] = entry(ms, (4.0 + 4.0 * 1e6 / n_in + 8.0 / 8) * n_in * 8, n_in * 8, "2030x1354 swath -> 1000x1000, 8 levels; points = source points")
+    fwd.close()
+    # K1+K2+K3: cache build from projection strings (one-off; points/s, no roofline)
+    lon, lat = S.target_axes("T1")
+    mx, my = S.meps_axes()
+    t0 = time.perf_counter()
+    c = RP.cachedInterpolationFromProjection(1, S.LATLON_PROJ, S.MEPS_PROJ, lon, lat, mx, my)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    c.close()
+    out["K1_K2_K3_cache_build_from_projection"] = {"ms": dt * 1e3, "Mpoints_per_s": ox * oy / dt / 1e6,
+                                                   "what": "reproject_axes + 2x points2position + reduced domain + tables, 2.95 M targets, wall clock incl. allocations"}
+    return out
+
 # ------------------------------------------------------------------------------------------------ B200 arm
 def main_b200(args):
     import torch
@@ -318,6 +406,15 @@ def main_b200(args):
         except Exception as exc:  # the checker is optional on the GPU box; the GPU numbers stand on their own
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": str(exc)[:200]}
 
+    kernels = None
+    if rank == 0 and world == 1 and not args.no_secondary:
+        del slabs, outs
+        torch.cuda.empty_cache()
+        try:
+            kernels = secondary_kernels(S, ci, px, py, ox, oy, peak)
+        except Exception as exc:
+            kernels = {"error": str(exc)[:300]}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -328,7 +425,7 @@ def main_b200(args):
                        "reduced_source_window": [inx, iny], "sharding": f"independent time-step slabs, {world} rank(s), no collective",
                        "l2": "inputs larger than L2: 3 rotating 264 MB source slabs, 767 MB written per step (L2 126 MB)",
                        "hbm_layout": "dense [z][y][x]" if dense else f"rows padded: source pitch {ip} (32 B), target pitch {op} (128 B)"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "kernels": kernels,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

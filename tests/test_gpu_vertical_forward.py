@@ -78,7 +78,9 @@ def test_vertical_fixed_levels_vs_oracle(fx, method, kind):
     rng = np.random.default_rng(100 * method + len(kind))
     nO, nzi, nI = 3, 65, 517
     fld, vc = _columns(rng, nO, nzi, nI, kind)
-    levels = [1000., 925., 850., 700., 500., 400., 300., 250., 200., 150., 100., 50., 1100., 5., float(vc[0, 0, 0])]
+    levels = [1000., 925., 850., 700., 500., 400., 300., 250., 200., 150., 100., 50., 1100., 5., float(vc[0, 0, 0]), float(vc[0, -1, 0]),
+              float(vc[0, 30, 5]), float(vc[1, 1, 7]), float(vc[2, nzi - 2, 11]), 1e12, -1e12, 3.0e9, 0.0]
+    levels = [v for v in levels if not np.isnan(v)]
     want = _oracle_vertical(method, fld, vc, levels=levels)
     got = verticalInterpolate(method, fld, vc, level1=levels)
     if method in (ol.VINT_LOG, ol.VINT_LOGLOG):
