@@ -1,0 +1,55 @@
+"""The C++ reference-side glue (fimex_b200/host/CudaCachedInterpolation.h: CachedInterpolationInterface subclasses and
+CachedVectorReprojection over the C ABI) driven the way CDMInterpolator::getDataSlice drives the reference classes."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from oracle_lib import dp, fp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "fimex_b200", "host", "host_selftest")
+
+
+def test_glue_compiles_against_the_reference_headers():
+    inc = "/root/reference/include"
+    if not os.path.isdir(inc):
+        pytest.skip("reference headers not present")
+    r = subprocess.run(["g++", "-std=c++20", "-fsyntax-only", "-DFIMEXCU_WITH_FIMEX_HEADERS", "-I" + inc,
+                        os.path.join(ROOT, "fimex_b200", "host", "CudaCachedInterpolation.h")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("method", [ol.BILINEAR, ol.BICUBIC, ol.NEAREST])
+def test_cpp_glue_matches_oracle(tmp_path, method):
+    assert os.path.exists(EXE), "fimex_b200/host/host_selftest not built (python -m fimex_b200.build)"
+    rng = np.random.default_rng(method)
+    in_x, in_y, out_x, out_y, nz = 57, 43, 83, 61, 4
+    # tables that reach all four borders, so the reduced window is the whole grid (offset 0)
+    px = rng.uniform(-2, in_x + 1, out_x * out_y)
+    py = rng.uniform(-2, in_y + 1, out_x * out_y)
+    px[:4], py[:4] = [0.2, in_x - 1.2, 0.2, in_x - 1.2], [0.2, 0.2, in_y - 1.2, in_y - 1.2]
+    strip = (py >= in_y - 0.5) & (py < in_y + 0.5) & ~((np.floor(px) >= 0) & (np.floor(px) + 1 < in_x))
+    py[strip] += 1.0
+    u = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    v = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    u[rng.random(u.shape) < 0.03] = np.nan
+    ang = rng.uniform(-3, 3, out_x * out_y)
+    m3 = np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy()
+    case, res = tmp_path / "case.bin", tmp_path / "res.bin"
+    with open(case, "wb") as f:
+        f.write(np.array([method, in_x, in_y, out_x, out_y, nz], dtype=np.int32).tobytes())
+        for a in (px, py, u, v, m3):
+            f.write(np.ascontiguousarray(a).tobytes())
+    r = subprocess.run([EXE, str(case), str(res)], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    got = np.fromfile(res, dtype=np.float32).reshape(2, nz, out_y, out_x)
+    wu, info = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, u)
+    wv, _ = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, v)
+    assert (info["inX"], info["inY"]) == (in_x, in_y)
+    ol.oracle().orc_vector_reproject_values_by_matrix_f(dp(m3), out_x * out_y, fp(wu), fp(wv), nz)
+    for g, w in ((got[0], wu), (got[1], wv)):
+        assert np.array_equal(np.isnan(g), np.isnan(w)) and np.array_equal(g[~np.isnan(g)], w[~np.isnan(w)])
