@@ -226,6 +226,13 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
         sub = c.reduceInput(src, S.MEPS_NX, S.MEPS_NY)
         ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_dev_f(c._h, sub.data_ptr(), nz, dst.data_ptr(), nan, nan, stream), name))
         out[name] = entry(ms, alg, pts, "S->T1 slab, dense layout")
+        if method == 0:  # nearest also through the staged kernel (padded layout)
+            pin = c.toPadded(sub)
+            ip, il, op, ol_ = c.paddedLayout()
+            pout = torch.empty((nz, oy, op), dtype=torch.float32, device="cuda")
+            ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_dev_strided_f(c._h, pin.data_ptr(), ip, il, nz, pout.data_ptr(), op, ol_, nan, nan, stream), name))
+            out[name + "_padded_staged"] = entry(ms, alg, pts, "S->T1 slab, padded layout, TMA-staged")
+            del pin, pout
         c.close()
     # K7: fused u,v interpolation + rotation, and the stand-alone rotation
     ang = np.random.default_rng(1).uniform(-0.6, 0.6, ox * oy)
@@ -235,6 +242,13 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
     ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_uv_dev_f(ci._h, cvr._h, sub.data_ptr(), sub.data_ptr(), nz, dst.data_ptr(), dst2.data_ptr(),
                                                                    nan, nan, nan, nan, stream), "uv"))
     out["K7_fused_uv_bilinear_rotation"] = entry(ms, 2 * alg + 16.0 * ox * oy, 2 * pts, "u and v of one S->T1 slab in one pass")
+    pin = ci.toPadded(sub)
+    ip, il, op, ol_ = ci.paddedLayout()
+    pu, pv = torch.empty((nz, oy, op), dtype=torch.float32, device="cuda"), torch.empty((nz, oy, op), dtype=torch.float32, device="cuda")
+    ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_uv_dev_strided_f(ci._h, cvr._h, pin.data_ptr(), pin.data_ptr(), ip, il, nz, pu.data_ptr(),
+                                                                           pv.data_ptr(), op, ol_, nan, nan, nan, nan, stream), "uv"))
+    out["K7_fused_uv_bilinear_rotation_padded_staged"] = entry(ms, 2 * alg + 16.0 * ox * oy, 2 * pts, "same, padded layout, TMA-staged")
+    del pin, pu, pv
     ms = timed(lambda: _lib.check(lib.fimexcu_vecrot_apply_dev_f(cvr._h, dst.data_ptr(), dst2.data_ptr(), nz, stream), "rot"))
     out["K7_rotation_alone"] = entry(ms, (16.0 + 16.0 / nz) * pts, 2 * pts, "in-place rotation of u,v [65][1021][2891]")
     cvr.close()
@@ -348,12 +362,12 @@ def main_b200(args):
     my_ms = ms_total / args.steps  # this rank's mean launch duration (one launch per step)
     achieved = alg_bytes / (my_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "kernel": "fxcu::bilinear_apply_tma_kernel" if not os.environ.get("FIMEXCU_NO_TMA") else "fxcu::bilinear_apply_kernel", "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
+                "kernel": "fxcu::staged_apply_tma_kernel<bilinear>" if not os.environ.get("FIMEXCU_NO_TMA") else "fxcu::bilinear_apply_kernel", "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                 "bytes_per_point": alg_bytes / points_per_step}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
         try:
-            roofline["traffic"] = json.load(open(prof)).get("bilinear_apply_tma_kernel_dram_bytes_per_launch")
+            roofline["traffic"] = json.load(open(prof)).get("staged_apply_tma_kernel_dram_bytes_per_launch")
         except Exception:
             pass
 

@@ -58,6 +58,7 @@ SIGNATURES = {
     "fimexcu_vecrot_destroy": (None, [vp]),
     "fimexcu_cache_apply_uv_f": (C.c_int, [vp, vp, vp, vp, sz, vp, vp, c_size_p] + [C.c_float] * 4),
     "fimexcu_cache_apply_uv_dev_f": (C.c_int, [vp, vp, vp, vp, sz, vp, vp] + [C.c_float] * 4 + [vp]),
+    "fimexcu_cache_apply_uv_dev_strided_f": (C.c_int, [vp, vp, vp, vp, sz, sz, sz, vp, vp, sz, sz] + [C.c_float] * 4 + [vp]),
     "fimexcu_points2position": (C.c_int, [vp, sz, vp, C.c_int, C.c_int]),
     "fimexcu_points2position_dev": (C.c_int, [vp, sz, vp, C.c_int, C.c_int, vp]),
     "fimexcu_points2position_dev_noalloc": (C.c_int, [vp, sz, vp, C.c_int, C.c_int, vp]),

@@ -499,8 +499,9 @@ __device__ __forceinline__ float tap(const float* t, int i, float bad)
     return v;
 }
 
-template <bool BAD, bool FILL>
-__global__ void __launch_bounds__(TMA_THREADS, 6) bilinear_apply_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ApplyParams P)
+// NN = true: nearest-neighbour tables (one tap, no weights) through the same pipeline
+template <bool BAD, bool FILL, bool NN>
+__global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ApplyParams P)
 {
     constexpr int STAGE_FLOATS = TMA_BW * TMA_BH * TMA_ZB;
     constexpr int LVL = TMA_BW * TMA_BH;
@@ -520,8 +521,10 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) bilinear_apply_tma_kernel(cons
     if (in_grid) {
         const size_t o = static_cast<size_t>(oy) * P.outX + ox;
         f = P.off[o];
-        fx = static_cast<const float*>(P.wx)[o];
-        fy = static_cast<const float*>(P.wy)[o];
+        if (!NN) {
+            fx = static_cast<const float*>(P.wx)[o];
+            fy = static_cast<const float*>(P.wy)[o];
+        }
     }
     int x0 = 0x3fffffff, y0 = 0x3fffffff, x1 = -1, y1 = -1;
     if (f >= 0) {
@@ -530,7 +533,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) bilinear_apply_tma_kernel(cons
         x1 = x0 + (fx >= 0.f ? 1 : 0);
         y1 = y0 + (fy >= 0.f ? 1 : 0);
     }
-    const bool interior = (f < 0) || (fx >= 0.f && fy >= 0.f);
+    const bool interior = !NN && ((f < 0) || (fx >= 0.f && fy >= 0.f));
     int lox = x0, loy = y0, hix = x1, hiy = y1;
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) {
@@ -606,7 +609,23 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) bilinear_apply_tma_kernel(cons
         return;
     }
     const int r = (f >= 0) ? (y0 - by0) * TMA_BW + (x0 - bx0) : 0;
-    if (all_interior) {
+    if (NN) { // one tap per target cell
+        for (int it = 0; it < niter; ++it) {
+            const int s = it % TMA_STAGES;
+            mbar_wait(&full[s], (it / TMA_STAGES) & 1);
+            const float* t = &tile[s][r];
+#pragma unroll
+            for (int k = 0; k < TMA_ZB; ++k) {
+                const float v = (f >= 0) ? tap<BAD>(t, k * LVL, P.bad) : nan_f();
+                if (in_grid && it * TMA_ZB + k < P.nz)
+                    store_out<FILL>(po + k * P.outLevel, v, P.fill);
+            }
+            po += TMA_ZB * P.outLevel;
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&empty[s]);
+        }
+    } else if (all_interior) {
         // undefined targets carry NaN weights: every product is NaN, no select in the loop
         const float wfx = (f >= 0) ? fx : nan_f(), wfy = (f >= 0) ? fy : nan_f();
         const float omx = __fsub_rn(1.f, wfx), omy = __fsub_rn(1.f, wfy);
@@ -649,6 +668,181 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) bilinear_apply_tma_kernel(cons
     }
 }
 
+// Staged form of the fused vector pass: u and v boxes of the same footprint travel through the same ring (two TMA loads per
+// stage on one mbarrier), consumers interpolate both components, rotate (reproject.cc:488-507) and store.
+constexpr int UV_ZB = 2; // levels per stage (two fields per level)
+struct UvStagedParams {
+    const double* cs;
+    const double* sn;
+    const float* vin;
+    float* vout;
+    float badV, fillV;
+};
+
+template <bool BAD, bool FILL, bool ROT>
+__global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __grid_constant__ CUtensorMap umap, const __grid_constant__ CUtensorMap vmap,
+                                                                       const ApplyParams P, const UvStagedParams Q)
+{
+    constexpr int LVL = TMA_BW * TMA_BH;
+    constexpr int FIELD = LVL * UV_ZB;
+    __shared__ __align__(128) float tile[TMA_STAGES][2 * FIELD];
+    __shared__ __align__(8) uint64_t full[TMA_STAGES];
+    __shared__ __align__(8) uint64_t empty[TMA_STAGES];
+    __shared__ int red[4][TMA_TH];
+    __shared__ int bbox[4];
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const bool consumer = warp < TMA_TH;
+    const int ox = blockIdx.x * 32 + lane, oy = blockIdx.y * TMA_TH + warp;
+    const bool in_grid = consumer && ox < P.outX && oy < P.outY;
+    int f = -1;
+    float fx = -1.f, fy = -1.f;
+    size_t o = 0;
+    if (in_grid) {
+        o = static_cast<size_t>(oy) * P.outX + ox;
+        f = P.off[o];
+        fx = static_cast<const float*>(P.wx)[o];
+        fy = static_cast<const float*>(P.wy)[o];
+    }
+    int x0 = 0x3fffffff, y0 = 0x3fffffff, x1 = -1, y1 = -1;
+    if (f >= 0) {
+        y0 = f / P.inX;
+        x0 = f - y0 * P.inX;
+        x1 = x0 + (fx >= 0.f ? 1 : 0);
+        y1 = y0 + (fy >= 0.f ? 1 : 0);
+    }
+    int lox = x0, loy = y0, hix = x1, hiy = y1;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        lox = min(lox, __shfl_xor_sync(0xffffffffu, lox, s));
+        loy = min(loy, __shfl_xor_sync(0xffffffffu, loy, s));
+        hix = max(hix, __shfl_xor_sync(0xffffffffu, hix, s));
+        hiy = max(hiy, __shfl_xor_sync(0xffffffffu, hiy, s));
+    }
+    if (consumer && lane == 0) {
+        red[0][warp] = lox;
+        red[1][warp] = loy;
+        red[2][warp] = hix;
+        red[3][warp] = hiy;
+    }
+    if (tid == 0) {
+        for (int s = 0; s < TMA_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], TMA_TH);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int a = red[0][0], b = red[1][0], c = red[2][0], d = red[3][0];
+        for (int w = 1; w < TMA_TH; ++w) {
+            a = min(a, red[0][w]);
+            b = min(b, red[1][w]);
+            c = max(c, red[2][w]);
+            d = max(d, red[3][w]);
+        }
+        bbox[0] = a & ~7;
+        bbox[1] = b;
+        bbox[2] = c;
+        bbox[3] = d;
+    }
+    __syncthreads();
+    const int bx0 = bbox[0], by0 = bbox[1], bx1 = bbox[2], by1 = bbox[3];
+    const size_t obase = static_cast<size_t>(oy) * P.outPitch + ox;
+    float* pu = P.out + obase;
+    float* pv = Q.vout + obase;
+    if (bx1 < 0) {
+        if (in_grid)
+            for (int z = 0; z < P.nz; ++z, pu += P.outLevel, pv += P.outLevel) {
+                store_out<FILL>(pu, nan_f(), P.fill);
+                store_out<FILL>(pv, nan_f(), Q.fillV);
+            }
+        return;
+    }
+    double c = 1., s = 0.;
+    if (ROT && in_grid) {
+        c = Q.cs[o];
+        s = Q.sn[o];
+    }
+    const bool staged = (bx1 - bx0 + 1 <= TMA_BW) && (by1 - by0 + 1 <= TMA_BH);
+    const int niter = staged ? (P.nz + UV_ZB - 1) / UV_ZB : 0;
+    if (!consumer) {
+        if (staged && lane == 0) {
+            for (int it = 0; it < niter; ++it) {
+                const int st = it % TMA_STAGES;
+                mbar_wait(&empty[st], ((it / TMA_STAGES) & 1) ^ 1);
+                mbar_expect_tx(&full[st], 2 * FIELD * sizeof(float));
+                tma_load_3d(&tile[st][0], &umap, &full[st], bx0, by0, it * UV_ZB);
+                tma_load_3d(&tile[st][FIELD], &vmap, &full[st], bx0, by0, it * UV_ZB);
+            }
+        }
+        return;
+    }
+    // tap offsets: a switched-off direction aliases the first tap
+    const int dxs = fx >= 0.f ? 1 : 0;
+    if (!staged) { // direct gathers for this tile
+        if (!in_grid)
+            return;
+        if (f < 0) {
+            for (int z = 0; z < P.nz; ++z, pu += P.outLevel, pv += P.outLevel) {
+                store_out<FILL>(pu, nan_f(), P.fill);
+                store_out<FILL>(pv, nan_f(), Q.fillV);
+            }
+            return;
+        }
+        const int dyg = fy >= 0.f ? P.inPitch : 0;
+        const float* qu = P.in + static_cast<size_t>(y0) * P.inPitch + x0;
+        const float* qv2 = Q.vin + static_cast<size_t>(y0) * P.inPitch + x0;
+        for (int z = 0; z < P.nz; ++z, qu += P.inLevel, qv2 += P.inLevel, pu += P.outLevel, pv += P.outLevel) {
+            float u = bilinear_value(load_in<BAD>(qu, P.bad), load_in<BAD>(qu + dxs, P.bad), load_in<BAD>(qu + dyg, P.bad),
+                                     load_in<BAD>(qu + dyg + dxs, P.bad), fx, fy);
+            float v = bilinear_value(load_in<BAD>(qv2, Q.badV), load_in<BAD>(qv2 + dxs, Q.badV), load_in<BAD>(qv2 + dyg, Q.badV),
+                                     load_in<BAD>(qv2 + dyg + dxs, Q.badV), fx, fy);
+            if (ROT) {
+                const double du = static_cast<double>(u), dv = static_cast<double>(v);
+                u = __double2float_rn(__dsub_rn(__dmul_rn(du, c), __dmul_rn(dv, s)));
+                v = __double2float_rn(__dadd_rn(__dmul_rn(du, s), __dmul_rn(dv, c)));
+            }
+            store_out<FILL>(pu, u, P.fill);
+            store_out<FILL>(pv, v, Q.fillV);
+        }
+        return;
+    }
+    const int dys = fy >= 0.f ? TMA_BW : 0;
+    const int r = (f >= 0) ? (y0 - by0) * TMA_BW + (x0 - bx0) : 0;
+    for (int it = 0; it < niter; ++it) {
+        const int st = it % TMA_STAGES;
+        mbar_wait(&full[st], (it / TMA_STAGES) & 1);
+        const float* tu = &tile[st][r];
+        const float* tv = tu + FIELD;
+#pragma unroll
+        for (int k = 0; k < UV_ZB; ++k) {
+            float u = nan_f(), v = nan_f();
+            if (f >= 0) {
+                u = bilinear_value(tap<BAD>(tu, k * LVL, P.bad), tap<BAD>(tu, k * LVL + dxs, P.bad), tap<BAD>(tu, k * LVL + dys, P.bad),
+                                   tap<BAD>(tu, k * LVL + dys + dxs, P.bad), fx, fy);
+                v = bilinear_value(tap<BAD>(tv, k * LVL, Q.badV), tap<BAD>(tv, k * LVL + dxs, Q.badV), tap<BAD>(tv, k * LVL + dys, Q.badV),
+                                   tap<BAD>(tv, k * LVL + dys + dxs, Q.badV), fx, fy);
+                if (ROT) {
+                    const double du = static_cast<double>(u), dv = static_cast<double>(v);
+                    u = __double2float_rn(__dsub_rn(__dmul_rn(du, c), __dmul_rn(dv, s)));
+                    v = __double2float_rn(__dadd_rn(__dmul_rn(du, s), __dmul_rn(dv, c)));
+                }
+            }
+            if (in_grid && it * UV_ZB + k < P.nz) {
+                store_out<FILL>(pu + k * P.outLevel, u, P.fill);
+                store_out<FILL>(pv + k * P.outLevel, v, Q.fillV);
+            }
+        }
+        pu += UV_ZB * P.outLevel;
+        pv += UV_ZB * P.outLevel;
+        __syncwarp();
+        if (lane == 0)
+            mbar_arrive(&empty[st]);
+    }
+}
+
 // fraction of 32 x 8 target tiles whose source footprint fits the staged kernel's box (decides, once per cache,
 // whether the staged kernel is worth launching).  counts[0] = tiles with data, counts[1] = of those, tiles that fit
 __global__ void __launch_bounds__(256) tile_fit_kernel(const int* __restrict__ off, const float* __restrict__ wx, const float* __restrict__ wy, int outX,
@@ -663,8 +857,8 @@ __global__ void __launch_bounds__(256) tile_fit_kernel(const int* __restrict__ o
         if (f >= 0) {
             y0 = f / inX;
             x0 = f - y0 * inX;
-            x1 = x0 + (wx[o] >= 0.f ? 1 : 0);
-            y1 = y0 + (wy[o] >= 0.f ? 1 : 0);
+            x1 = x0 + ((wx && wx[o] >= 0.f) ? 1 : 0);
+            y1 = y0 + ((wy && wy[o] >= 0.f) ? 1 : 0);
         }
     }
 #pragma unroll
@@ -902,6 +1096,21 @@ fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, s
             c->inX = redX;
             c->inY = redY;
         }
+        {
+            DevBuf counts;
+            if (!counts.alloc(2 * sizeof(unsigned), s))
+                return nullptr;
+            FXCU_CUDA_NULL(cudaMemsetAsync(counts.p, 0, 2 * sizeof(unsigned), s));
+            const dim3 tg(static_cast<unsigned>((outX + 31) / 32), static_cast<unsigned>((outY + 7) / 8));
+            tile_fit_kernel<<<tg, 256, 0, s>>>(c->off.as<int>(), nullptr, nullptr, static_cast<int>(outX), static_cast<int>(outY),
+                                               static_cast<int>(c->inX), counts.as<unsigned>());
+            FXCU_CUDA_NULL(cudaGetLastError());
+            unsigned hc[2] = {0, 0};
+            FXCU_CUDA_NULL(cudaMemcpyAsync(hc, counts.p, sizeof(hc), cudaMemcpyDeviceToHost, s));
+            FXCU_CUDA_NULL(cudaStreamSynchronize(s));
+            c->tiles_with_data = hc[0];
+            c->tiles_fitting = hc[1];
+        }
         FXCU_CUDA_NULL(cudaStreamSynchronize(s));
         return c.release();
     }
@@ -989,7 +1198,7 @@ static tensor_map_encode_fn tensor_map_encoder()
     return fn;
 }
 
-static bool make_source_map(CUtensorMap* m, const float* d_in, size_t inX, size_t inY, size_t nz, int inPitch, size_t inLevel)
+static bool make_source_map(CUtensorMap* m, const float* d_in, size_t inX, size_t inY, size_t nz, int inPitch, size_t inLevel, int depth = TMA_ZB)
 {
     tensor_map_encode_fn enc = tensor_map_encoder();
     if (!enc)
@@ -999,7 +1208,7 @@ static bool make_source_map(CUtensorMap* m, const float* d_in, size_t inX, size_
         return false;
     cuuint64_t dims[3] = {inX, inY, nz};
     cuuint64_t strides[2] = {static_cast<cuuint64_t>(inPitch) * 4, static_cast<cuuint64_t>(inLevel) * 4};
-    cuuint32_t box[3] = {TMA_BW, TMA_BH, TMA_ZB};
+    cuuint32_t box[3] = {TMA_BW, TMA_BH, static_cast<cuuint32_t>(depth)};
     cuuint32_t es[3] = {1, 1, 1};
     return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(d_in), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -1017,7 +1226,7 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
 {
     ApplyParams P = P0;
     const size_t tiles = static_cast<size_t>((c->outX + 31) / 32) * ((c->outY + 7) / 8);
-    if (c->kind == KIND_BILINEAR && allow_tma) {
+    if ((c->kind == KIND_BILINEAR || c->kind == KIND_NN) && allow_tma) {
         // staged kernel: worth it when most tiles fit its box and there are enough tiles to fill the GPU without
         // splitting the level loop
         CUtensorMap map;
@@ -1025,7 +1234,10 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
         const bool fits = c->tiles_with_data > 0 && 10ull * c->tiles_fitting >= 8ull * c->tiles_with_data;
         if (enough && fits && make_source_map(&map, P.in, c->inX, c->inY, static_cast<size_t>(P.nz), P.inPitch, P.inLevel)) {
             const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH));
-            bilinear_apply_tma_kernel<BAD, FILL><<<grid, TMA_THREADS, 0, s>>>(map, P);
+            if (c->kind == KIND_NN)
+                staged_apply_tma_kernel<BAD, FILL, true><<<grid, TMA_THREADS, 0, s>>>(map, P);
+            else
+                staged_apply_tma_kernel<BAD, FILL, false><<<grid, TMA_THREADS, 0, s>>>(map, P);
             return;
         }
     }
@@ -1228,10 +1440,9 @@ int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, 
     return rc;
 }
 
-int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* d_u_in, const float* d_v_in, size_t nz,
-                                 float* d_u_out, float* d_v_out, float badU, float badV, float fillU, float fillV, void* stream)
+static int cache_apply_uv_strided(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* d_u_in, const float* d_v_in, const Layout& L, size_t nz,
+                                  float* d_u_out, float* d_v_out, float badU, float badV, float fillU, float fillV, cudaStream_t s)
 {
-    clear_error();
     if (!c)
         FXCU_FAIL("fimexcu_cache_apply_uv: null cache");
     const size_t nxy = c->outX * c->outY;
@@ -1239,18 +1450,21 @@ int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r
         FXCU_FAIL("fimexcu_cache_apply_uv: rotation matrix and cache have different target grids");
     if (nz == 0 || nxy == 0)
         return FIMEXCU_OK;
-    cudaStream_t s = as_stream(stream);
-    const Layout L = dense_layout(c);
+    if (check_layout(c, L, nz) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
     if (c->kind != KIND_BILINEAR) {
         // bicubic / nearest: the general kernels per component, the stand-alone rotation (which must see NaN, not the
-        // fill value), then the fill
+        // fill value), then the fill.  The stand-alone rotation and fill work on dense arrays only.
+        const bool dense_out = static_cast<size_t>(L.outPitch) == c->outX && L.outLevel == nxy;
+        if (r && !dense_out)
+            FXCU_FAIL("fimexcu_cache_apply_uv: rotation of bicubic / nearest results needs the dense target layout");
         const float nanv = std::numeric_limits<float>::quiet_NaN();
         const float fu = r ? nanv : fillU, fv = r ? nanv : fillV;
         if (cache_apply_strided(c, d_u_in, L, nz, d_u_out, badU, fu, s) != FIMEXCU_OK || cache_apply_strided(c, d_v_in, L, nz, d_v_out, badV, fv, s) != FIMEXCU_OK)
             return FIMEXCU_ERROR;
         if (!r)
             return FIMEXCU_OK;
-        if (fimexcu_vecrot_apply_dev_f(r, d_u_out, d_v_out, nz, stream) != FIMEXCU_OK)
+        if (fimexcu_vecrot_apply_dev_f(r, d_u_out, d_v_out, nz, s) != FIMEXCU_OK)
             return FIMEXCU_ERROR;
         const unsigned fb = static_cast<unsigned>(std::min<size_t>((nz * nxy + 255) / 256, static_cast<size_t>(sm_count()) * 16));
         if (!std::isnan(fillU))
@@ -1269,6 +1483,7 @@ int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r
     P.outX = static_cast<int>(c->outX);
     P.outY = static_cast<int>(c->outY);
     P.nz = static_cast<int>(nz);
+    P.zchunk = P.nz;
     P.inX = static_cast<int>(c->inX);
     P.inPitch = L.inPitch;
     P.inLevel = L.inLevel;
@@ -1276,6 +1491,38 @@ int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r
     P.outLevel = L.outLevel;
     P.bad = badU;
     P.fill = fillU;
+    const bool special = !std::isnan(badU) || !std::isnan(badV) || !std::isnan(fillU) || !std::isnan(fillV);
+    const size_t tiles = static_cast<size_t>((c->outX + 31) / 32) * ((c->outY + 7) / 8);
+    // staged (TMA) form when both sources can be described and the tiles fit
+    CUtensorMap umap, vmap;
+    const bool enough = tiles >= static_cast<size_t>(sm_count()) * 5;
+    const bool fits = c->tiles_with_data > 0 && 10ull * c->tiles_fitting >= 8ull * c->tiles_with_data;
+    if (getenv("FIMEXCU_NO_TMA") == nullptr && enough && fits &&
+        make_source_map(&umap, d_u_in, c->inX, c->inY, nz, L.inPitch, L.inLevel, UV_ZB) &&
+        make_source_map(&vmap, d_v_in, c->inX, c->inY, nz, L.inPitch, L.inLevel, UV_ZB)) {
+        UvStagedParams Q;
+        Q.cs = r ? r->c.as<double>() : nullptr;
+        Q.sn = r ? r->s.as<double>() : nullptr;
+        Q.vin = d_v_in;
+        Q.vout = d_v_out;
+        Q.badV = badV;
+        Q.fillV = fillV;
+        const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH));
+        // a NaN bad value never compares equal and a NaN fill value re-writes NaN: the <true,true> variant is always correct
+        if (r) {
+            if (special)
+                staged_uv_tma_kernel<true, true, true><<<grid, TMA_THREADS, 0, s>>>(umap, vmap, P, Q);
+            else
+                staged_uv_tma_kernel<false, false, true><<<grid, TMA_THREADS, 0, s>>>(umap, vmap, P, Q);
+        } else {
+            if (special)
+                staged_uv_tma_kernel<true, true, false><<<grid, TMA_THREADS, 0, s>>>(umap, vmap, P, Q);
+            else
+                staged_uv_tma_kernel<false, false, false><<<grid, TMA_THREADS, 0, s>>>(umap, vmap, P, Q);
+        }
+        FXCU_CUDA(cudaGetLastError());
+        return FIMEXCU_OK;
+    }
     UvParams Q;
     Q.cs = r ? r->c.as<double>() : nullptr;
     Q.sn = r ? r->s.as<double>() : nullptr;
@@ -1283,12 +1530,9 @@ int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r
     Q.vout = d_v_out;
     Q.badV = badV;
     Q.fillV = fillV;
-    const size_t tiles = static_cast<size_t>((c->outX + 31) / 32) * ((c->outY + 7) / 8);
     P.zchunk = pick_zchunk(tiles, P.nz);
     const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + 7) / 8),
                     static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
-    const bool special = !std::isnan(badU) || !std::isnan(badV) || !std::isnan(fillU) || !std::isnan(fillV);
-    // a NaN bad value never compares equal and a NaN fill value re-writes NaN: the <true,true> variant is always correct
     if (r) {
         if (special)
             bilinear_uv_kernel<true, true, true><<<grid, 256, 0, s>>>(P, Q);
@@ -1302,6 +1546,29 @@ int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r
     }
     FXCU_CUDA(cudaGetLastError());
     return FIMEXCU_OK;
+}
+
+int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* d_u_in, const float* d_v_in, size_t nz,
+                                 float* d_u_out, float* d_v_out, float badU, float badV, float fillU, float fillV, void* stream)
+{
+    clear_error();
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply_uv: null cache");
+    return cache_apply_uv_strided(c, r, d_u_in, d_v_in, dense_layout(c), nz, d_u_out, d_v_out, badU, badV, fillU, fillV, as_stream(stream));
+}
+
+int fimexcu_cache_apply_uv_dev_strided_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* d_u_in, const float* d_v_in,
+                                         size_t in_row_pitch, size_t in_level_stride, size_t nz, float* d_u_out, float* d_v_out,
+                                         size_t out_row_pitch, size_t out_level_stride, float badU, float badV, float fillU, float fillV,
+                                         void* stream)
+{
+    clear_error();
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply_uv: null cache");
+    if (in_row_pitch > 0x7fffffffull || out_row_pitch > 0x7fffffffull)
+        FXCU_FAIL("fimexcu_cache_apply_uv: row pitch out of range");
+    const Layout L{static_cast<int>(in_row_pitch), in_level_stride, static_cast<int>(out_row_pitch), out_level_stride};
+    return cache_apply_uv_strided(c, r, d_u_in, d_v_in, L, nz, d_u_out, d_v_out, badU, badV, fillU, fillV, as_stream(stream));
 }
 
 int fimexcu_cache_apply_uv_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* u_in, const float* v_in, size_t size, float* u_out,

@@ -302,6 +302,20 @@ def interpolateVectorValues(ci, cvr, uIn, vIn, badU=_NAN, badV=_NAN, fillU=_NAN,
     return uo, vo
 
 
+def interpolateVectorValuesPadded(ci, cvr, uPadded, vPadded, badU=_NAN, badV=_NAN, fillU=_NAN, fillV=_NAN):
+    """interpolateVectorValues on device slabs in the padded layout of ci.paddedLayout() (the TMA-staged fused kernel);
+    returns (u, v) as [nz][outY][out_row_pitch] tensors."""
+    import torch
+    ip, il, op, ol = ci.paddedLayout()
+    nz = uPadded.shape[0]
+    uo = torch.empty((nz, ci.outY, op), dtype=torch.float32, device=uPadded.device)
+    vo = torch.empty_like(uo)
+    rh = cvr._h if cvr is not None else None
+    _lib.check(lib.fimexcu_cache_apply_uv_dev_strided_f(ci._h, rh, uPadded.data_ptr(), vPadded.data_ptr(), ip, il, nz, uo.data_ptr(), vo.data_ptr(),
+                                                        op, ol, badU, badV, fillU, fillV, _lib.current_stream_ptr()), "interpolateVectorValues")
+    return uo, vo
+
+
 def mifi_points2position(points, axis, axis_type):
     """include/fimex/interpolation.h:76-93: returns the positions (the reference works in place)."""
     ax = _f64(axis).ravel()

@@ -156,6 +156,12 @@ int fimexcu_cache_apply_uv_f(const fimexcu_cache* c, const fimexcu_vecrot* r, co
                              float* v_out, size_t* newSize, float badU, float badV, float fillU, float fillV);
 int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* d_u_in, const float* d_v_in, size_t nz,
                                  float* d_u_out, float* d_v_out, float badU, float badV, float fillU, float fillV, void* stream);
+/* same with explicit element strides for both sources and both targets (see fimexcu_cache_apply_dev_strided_f); with the
+ * padded layout the bilinear case runs as one TMA-staged kernel. */
+int fimexcu_cache_apply_uv_dev_strided_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* d_u_in, const float* d_v_in,
+                                         size_t in_row_pitch, size_t in_level_stride, size_t nz, float* d_u_out, float* d_v_out,
+                                         size_t out_row_pitch, size_t out_level_stride, float badU, float badV, float fillU, float fillV,
+                                         void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * cache build: axes, projections, rotation matrix

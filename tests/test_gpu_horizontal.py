@@ -289,3 +289,69 @@ def test_staged_and_direct_kernels_agree_on_meps(fx, meps_t1, monkeypatch):
     b = ci.interpolateValuesPadded(pin)
     torch.cuda.synchronize()
     assert _eq(a[:, :, :ox].cpu().numpy(), b[:, :, :ox].cpu().numpy())
+
+
+def test_nearest_staged_kernel_padded_layout(fx, oracle):
+    """nearest-neighbour tables through the TMA-staged kernel (padded layout) and the direct kernel (dense layout)"""
+    import torch
+    rng = np.random.default_rng(31)
+    in_x, in_y, out_x, out_y, nz = 300, 200, 1400, 900, 7
+    gx, gy = np.meshgrid(np.arange(out_x), np.arange(out_y))
+    px = -3.0 + gx * ((in_x + 5.0) / out_x) + 0.11 * gy * (in_x / out_x)
+    py = -2.5 + gy * ((in_y + 4.0) / out_y) - 0.07 * gx * (in_y / out_y)
+    k = out_y // 3
+    px[k:k + 9] = rng.uniform(-2, in_x + 1, px[k:k + 9].shape)
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.02] = np.nan
+    want, info = ol.o_cached_apply(ol.NEAREST, px, py, in_x, in_y, out_x, out_y, fld)
+    ci = fx.CachedNNInterpolation("x", "y", px, py, in_x, in_y, out_x, out_y)
+    sub = torch.from_numpy(ci.reduceInput(fld, in_x, in_y)).cuda()
+    out = ci.interpolateValuesPadded(ci.toPadded(sub))
+    torch.cuda.synchronize()
+    assert _eq(out[:, :, :out_x].cpu().numpy(), want)
+    dense, _ = ci.interpolateValues(sub, fillValue=-5.0)
+    w2 = want.copy()
+    w2[np.isnan(w2)] = -5.0
+    assert _eq(dense.cpu().numpy(), w2)
+
+
+@pytest.mark.parametrize("special", [False, True])
+def test_fused_uv_staged_kernel_padded_layout(fx, oracle, special):
+    """u,v interpolation + rotation as one TMA-staged kernel (padded layout) == the three separate reference steps"""
+    import torch
+    from fimex_b200.interpolation import interpolateVectorValuesPadded
+    rng = np.random.default_rng(77)
+    in_x, in_y, out_x, out_y, nz = 300, 200, 1400, 900, 5
+    gx, gy = np.meshgrid(np.arange(out_x), np.arange(out_y))
+    px = -3.0 + gx * ((in_x + 5.0) / out_x) + 0.11 * gy * (in_x / out_x)
+    py = -2.5 + gy * ((in_y + 4.0) / out_y) - 0.07 * gx * (in_y / out_y)
+    k = out_y // 2
+    px[k:k + 9] = rng.uniform(-2, in_x + 1, px[k:k + 9].shape)
+    ang = rng.uniform(-np.pi, np.pi, out_x * out_y)
+    m3 = np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy()
+    u = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    v = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    bad, fill = np.float32(-999.0), np.float32(1e20)
+    u[rng.random(u.shape) < 0.01] = bad if special else np.nan
+    cu, cv = u.copy(), v.copy()
+    if special:
+        oracle.orc_bad2nanf(fp(cu), cu.size, bad)
+    wu, _ = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, cu)
+    wv, _ = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, cv)
+    oracle.orc_vector_reproject_values_by_matrix_f(dp(m3), out_x * out_y, fp(wu), fp(wv), nz)
+    if special:
+        oracle.orc_nanf2bad(fp(wu), wu.size, fill)
+        oracle.orc_nanf2bad(fp(wv), wv.size, fill)
+    ci = fx.CachedInterpolation("x", "y", ol.BILINEAR, px, py, in_x, in_y, out_x, out_y)
+    cvr = fx.CachedVectorReprojection(m3, out_x, out_y)
+    up = ci.toPadded(torch.from_numpy(ci.reduceInput(u, in_x, in_y)).cuda())
+    vp = ci.toPadded(torch.from_numpy(ci.reduceInput(v, in_x, in_y)).cuda())
+    kw = dict(badU=float(bad), badV=float(bad), fillU=float(fill), fillV=float(fill)) if special else {}
+    gu, gv = interpolateVectorValuesPadded(ci, cvr, up, vp, **kw)
+    torch.cuda.synchronize()
+    assert _eq(gu[:, :, :out_x].cpu().numpy(), wu) and _eq(gv[:, :, :out_x].cpu().numpy(), wv)
+    # without rotation
+    gu, gv = interpolateVectorValuesPadded(ci, None, up, vp)
+    wu2, _ = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, u if not special else u)
+    torch.cuda.synchronize()
+    assert _eq(gu[:, :, :out_x].cpu().numpy(), wu2)
