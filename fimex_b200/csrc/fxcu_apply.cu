@@ -1404,14 +1404,16 @@ int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, 
     // PCIe copies (the 767 MB result alone takes ~14 ms, the kernels 0.4 ms), so the chunks keep the dense host layout on
     // the device: plain 1-D copies run at full DMA speed, strided 2-D copies into the padded layout measured 1.5x slower.
     const Layout L = dense_layout(c);
-    const int NS = 3;
-    const size_t chunk = std::max<size_t>(1, std::min<size_t>(nz, (nz + 7) / 8));
-    cudaStream_t st[NS];
+    constexpr int NS_MAX = 8;
+    static const int NS = []() { const char* e = getenv("FIMEXCU_E2E_STREAMS"); const int v = e ? atoi(e) : 3; return std::max(1, std::min(8, v)); }();
+    static const int NCHUNK = []() { const char* e = getenv("FIMEXCU_E2E_CHUNKS"); const int v = e ? atoi(e) : 8; return std::max(1, v); }();
+    const size_t chunk = std::max<size_t>(1, std::min<size_t>(nz, (nz + NCHUNK - 1) / NCHUNK));
+    cudaStream_t st[NS_MAX];
     for (int i = 0; i < NS; ++i)
         FXCU_CUDA(cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking));
     int rc = FIMEXCU_OK;
     {
-        DevBuf din[NS], dout[NS];
+        DevBuf din[NS_MAX], dout[NS_MAX];
         for (int i = 0; i < NS && rc == FIMEXCU_OK; ++i)
             if (!din[i].alloc(chunk * L.inLevel * sizeof(float), st[i]) || !dout[i].alloc(chunk * L.outLevel * sizeof(float), st[i]))
                 rc = FIMEXCU_ERROR;

@@ -116,6 +116,54 @@ def vertical_fixtures():
     print("wrote reference_vertical.npz with", len(out), "arrays")
 
 
+
+def hirlam12_fixture():
+    """BASELINE configs[0]: test/hirlam12.nc (NetCDF-3 classic: time 2, pressure 2, Yc 12, Xc 17; Xc/Yc plain degrees, i.e. a
+    lat/lon source) regridded bilinearly as `fimex --interpolate.method=bilinear --interpolate.projString=...` would, by driving
+    the reference's own objects: reproject_axes (src/reproject.cc over the proj.h shim) -> mifi_points2position ->
+    createCachedInterpolation -> interpolateValues, and for x_wind/y_wind get_vector_reproject_matrix -> reprojectValues."""
+    import ctypes as C
+    from scipy.io import netcdf_file
+    ref = ol.ref()
+    f = netcdf_file("/root/reference/test/hirlam12.nc", mmap=False)
+    xc, yc = f.variables["Xc"].data.astype(np.float64), f.variables["Yc"].data.astype(np.float64)
+    out = {"xc": xc, "yc": yc}
+    fields = {n: f.variables[n].data.astype(np.float32) for n in ("geopotential_height", "air_potential_temperature", "x_wind", "y_wind")}
+    for n, v in fields.items():
+        out["in_" + n] = v  # (time, pressure, Yc, Xc)
+    src = "+proj=latlong +R=6371000 +no_defs"
+    targets = {
+        "latlong": ("+proj=latlong +R=6371000 +no_defs", np.arange(4.9, 6.7001, 0.05), np.arange(61.4, 62.7001, 0.05), 1, 2),
+        "stere": ("+proj=stere +lat_0=90 +lon_0=0 +lat_ts=60 +R=6371000 +no_defs", 295000.0 + 2500.0 * np.arange(50), -3100000.0 + 2500.0 * np.arange(60), 0, 0),
+    }
+    for tag, (proj, ax, ay, xt, yt) in targets.items():
+        ax, ay = np.ascontiguousarray(ax), np.ascontiguousarray(ay)
+        n = ax.size * ay.size
+        px, py = np.empty(n), np.empty(n)
+        assert ref.ref_reproject_axes(proj.encode(), src.encode(), dp(ax), dp(ay), ax.size, ay.size, dp(px), dp(py)) == 0
+        ref.mifi_points2position(dp(px), n, dp(xc), xc.size, 1)  # MIFI_LONGITUDE
+        ref.mifi_points2position(dp(py), n, dp(yc), yc.size, 2)  # MIFI_LATITUDE
+        out[f"{tag}_proj"] = np.frombuffer(proj.encode(), dtype=np.uint8)
+        out[f"{tag}_ax"], out[f"{tag}_ay"], out[f"{tag}_px"], out[f"{tag}_py"] = ax, ay, px, py
+        m = np.empty(n * 3)
+        assert ref.ref_get_vector_reproject_matrix(src.encode(), proj.encode(), dp(ax), dp(ay), ax.size, ay.size, dp(m)) == 0
+        out[f"{tag}_matrix"] = m
+        res = {}
+        for name, v in fields.items():
+            fld = v.reshape(-1, yc.size, xc.size)
+            r, info = ol.r_cached_apply(ol.BILINEAR, px, py, xc.size, yc.size, ax.size, ay.size, fld)
+            res[name] = r
+            out[f"{tag}_info"] = np.array([info["inX"], info["inY"], int(info["reduced"]), info["xMin"], info["yMin"]])
+        u, v = res["x_wind"].copy(), res["y_wind"].copy()
+        ref.ref_vector_reproject_values_by_matrix_f(dp(m), ax.size, ay.size, fp(u), fp(v), u.shape[0])
+        res["x_wind"], res["y_wind"] = u, v
+        for name, r in res.items():
+            out[f"{tag}_ex_{name}"] = r
+    np.savez_compressed(os.path.join(HERE, "reference_hirlam12.npz"), **out)
+    print("wrote reference_hirlam12.npz with", len(out), "arrays")
+
+
 if __name__ == "__main__":
     main()
     vertical_fixtures()
+    hirlam12_fixture()
