@@ -265,6 +265,29 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
     ms = timed(lambda: V.verticalHybridPressure(1, vin, ap, b, ps, levels, ps_scale=0.01), reps=3)
     out["K14_K15_vertical_hybrid_to_pressure_log"] = entry(ms, 312.0 * ncol, 12 * ncol, "65 -> 12 levels, 30 members x 801x561 columns, p formed on the fly")
     del vin, ps
+    # configs[4] second half, chained on the device: bilinear S->T2 of (65 levels x 6 members) and of ps, then hybrid -> 12 pressure levels
+    lon2, lat2 = S.target_axes("T2")
+    px2, py2, ox2, oy2 = S.meps_index_tables("T2")
+    c2 = fimex_b200.CachedInterpolation("x", "y", 1, px2, py2, S.MEPS_NX, S.MEPS_NY, ox2, oy2)
+    nmem = 6
+    ip2, il2, op2, ol2 = c2.paddedLayout()
+    f_in = torch.randn((65 * nmem, c2.getInY(), ip2), dtype=torch.float32, device="cuda")
+    ps_in = 101325.0 + 300.0 * torch.randn((nmem, c2.getInY(), ip2), dtype=torch.float32, device="cuda")
+    f_out = torch.empty((65 * nmem, oy2, op2), dtype=torch.float32, device="cuda")
+    ps_out = torch.empty((nmem, oy2, op2), dtype=torch.float32, device="cuda")
+    n_inner = nmem * oy2 * op2
+
+    def chain():
+        c2.interpolateValuesPadded(f_in, out=f_out)
+        c2.interpolateValuesPadded(ps_in, out=ps_out)
+        return V.verticalHybridPressure(0, f_out.reshape(1, 65, n_inner), ap, b, ps_out.reshape(1, n_inner), levels, ps_scale=0.01)
+    ms = timed(chain, reps=3)
+    alg_h = S.bilinear_algorithmic_bytes(c2.getInX() * c2.getInY(), ox2 * oy2, 65 * nmem) + S.bilinear_algorithmic_bytes(c2.getInX() * c2.getInY(), ox2 * oy2, nmem)
+    alg_v = 312.0 * nmem * ox2 * oy2
+    out["chained_bilinear_T2_then_vertical"] = entry(ms, alg_h + alg_v, 12 * nmem * ox2 * oy2,
+                                                     "configs[4]: 6 members x 65 levels S->T2 (7.13 B/pt) + ps, then 65->12 pressure levels (linear); points = final output values")
+    c2.close()
+    del f_in, ps_in, f_out, ps_out
     # K12: forward mean, 2030x1354 swath -> 1000x1000 cells, 8 levels (level_compat off: every level aggregated)
     gx, gy = np.meshgrid(np.arange(1354), np.arange(2030))
     fwd = I.CachedForwardInterpolation("x", "y", 6, (gx * (1000 / 1354.0)).ravel() - 0.3, (gy * (1000 / 2030.0)).ravel() - 0.3, 1354, 2030, 1000, 1000,

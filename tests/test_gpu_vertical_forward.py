@@ -240,3 +240,41 @@ def test_forward_reduced_window_bad_fill_and_swath_shape(fx, oracle):
         got, _ = ci.interpolateValues(d_in, badValue=float(bad), fillValue=float(fill))
         torch.cuda.synchronize()
         assert _eq(got.cpu().numpy(), want)
+
+
+# ---------------------------------------------------------------------------------- chained horizontal -> vertical (configs[4])
+def test_chained_horizontal_then_vertical_on_device(fx):
+    """BASELINE configs[4], second half: ensemble hybrid-sigma field (hybrid, member, y, x) regridded bilinearly first, then
+    interpolated to pressure levels with the pressure formed from the REGRIDDED surface pressure (the reference's order,
+    fimex.cc:862-863 / SURVEY 3.5).  All slabs stay on the device in the padded layout; the oracle runs the same chain."""
+    import torch
+    from fimex_b200.vertical import verticalHybridPressure
+    rng = np.random.default_rng(42)
+    g = np.load(os.path.join(GOLD, "reference_vertical.npz"))
+    ap, b = g["en_ap_pa"] * 0.01, g["en_b"]
+    nk, nmem, in_x, in_y, out_x, out_y = 65, 3, 90, 70, 217, 153
+    gx, gy = np.meshgrid(np.arange(out_x), np.arange(out_y))
+    px = 2.0 + gx * ((in_x - 5.0) / out_x) + 0.05 * gy * (in_x / out_x)
+    py = 1.5 + gy * ((in_y - 12.0) / out_y) + 0.03 * gx * (in_y / out_x)
+    fld = rng.normal(0, 10, (nk, nmem, in_y, in_x)).astype(np.float32)
+    ps = (101325 - 12 * rng.uniform(0, 2500, (nmem, in_y, in_x)) + rng.normal(0, 300, (nmem, in_y, in_x))).astype(np.float32)
+    levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50], dtype=np.float64)
+    # oracle chain
+    h_f, info = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, fld.reshape(-1, in_y, in_x))
+    h_ps, _ = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, ps)
+    ncol = nmem * out_y * out_x
+    p = (ap[:, None] + b[:, None] * (h_ps.reshape(1, ncol).astype(np.float64) * 0.01)).astype(np.float32)
+    want = _oracle_vertical(ol.VINT_LIN, h_f.reshape(1, nk, ncol), np.ascontiguousarray(p[None]), levels=levels).reshape(12, nmem, out_y, out_x)
+    # device chain
+    ci = fx.CachedInterpolation("x", "y", ol.BILINEAR, px, py, in_x, in_y, out_x, out_y)
+    d_f = ci.toPadded(torch.from_numpy(ci.reduceInput(fld.reshape(-1, in_y, in_x), in_x, in_y)).cuda())
+    d_ps = ci.toPadded(torch.from_numpy(ci.reduceInput(ps, in_x, in_y)).cuda())
+    r_f = ci.interpolateValuesPadded(d_f)      # [65*3][out_y][pitch]
+    r_ps = ci.interpolateValuesPadded(d_ps)    # [3][out_y][pitch]
+    pitch = r_f.shape[2]
+    n_inner = nmem * out_y * pitch
+    out = verticalHybridPressure(ol.VINT_LIN, r_f.reshape(1, nk, n_inner), ap, b, r_ps.reshape(1, n_inner), levels, ps_scale=0.01)
+    torch.cuda.synchronize()
+    got = out.reshape(12, nmem, out_y, pitch)[..., :out_x].cpu().numpy()
+    assert _eq(got, want)
+    assert (~np.isnan(want)).mean() > 0.5
