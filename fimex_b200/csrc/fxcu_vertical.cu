@@ -19,6 +19,8 @@
 #include "fxcu_common.h"
 
 #include <cfloat>
+#include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -37,6 +39,7 @@ struct VertParams {
     double ps_scale;
     size_t nOuter, nzi, nInner, nzo;
     const double* levels;     // [nzo] device, or nullptr
+    int levels_dir;           // fixed levels: +1 non-decreasing, -1 non-increasing (both for one level), 0 unordered or NaN
     int dir_hint;             // hybrid mode: +1 / -1 when every column of the launch is provably strictly monotone, 0 = check per column
     const double* xlog;       // [nzo] device: host-computed log / log-log of the fixed levels (LOG / LOGLOG), or nullptr
     const float* vcoord_out;  // [nOuter][nzo][nInner] or nullptr
@@ -47,16 +50,76 @@ struct VertParams {
     float* out;
 };
 
+// 1/d to ~1e-12 (one Newton step on the hardware's approximation) or to full f64 accuracy (two steps); d normal and positive
+__device__ __forceinline__ double rcp_newton(double d, bool full)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    r = __fma_rn(r, __fma_rn(-d, r, 1.0), r);
+    if (full)
+        r = __fma_rn(r, __fma_rn(-d, r, 1.0), r);
+    return r;
+}
+
+__constant__ double c_inv_odd[12] = {1., 1. / 3, 1. / 5, 1. / 7, 1. / 9, 1. / 11, 1. / 13, 1. / 15, 1. / 17, 1. / 19, 1. / 21, 1. / 23};
+
+// The weight of the LOG method, f = (log x - log a) / (log b - log a) narrowed to f32 (interpolation.c:521-535), without a
+// logarithm: log(x/a) = 2 atanh(s), s = (x - a)/(x + a), as a series that is exact to < 2e-17 relative for |s| < 0.2.  The
+// quotient of the two series is accurate to ~1e-15, an order better than the reference's own difference of rounded logarithms,
+// whose error bound (2^-52 * max|log| * (1 + |f|) / |log b - log a|) is the tolerance below: the fast value is returned only if
+// every real number within that tolerance narrows to the SAME f32 -- then the reference's f is that float.  Otherwise (about
+// once in 10^4 values, or brackets wider than a factor 1.5) the caller evaluates the logarithms.  a, b, x positive, a != b.
+__device__ __forceinline__ bool log_weight_fast(double a, double b, double x, float& f)
+{
+    const double u1 = __dsub_rn(x, a), v1 = __dadd_rn(x, a), u2 = __dsub_rn(b, a), v2 = __dadd_rn(b, a);
+    if (!(fabs(u1) < 0.2 * v1 && fabs(u2) < 0.2 * v2 && v1 < 1e300 && v2 < 1e300 && a > 1e-300 && b > 1e-300))
+        return false;
+    const double s1 = u1 * rcp_newton(v1, false), s2 = u2 * rcp_newton(v2, false);
+    const double z1 = s1 * s1, z2 = s2 * s2;
+    double p1 = c_inv_odd[11], p2 = c_inv_odd[11]; // operands straight from the constant bank: no immediates to materialise
+#pragma unroll
+    for (int i = 10; i >= 0; --i) {
+        p1 = __fma_rn(p1, z1, c_inv_odd[i]);
+        p2 = __fma_rn(p2, z2, c_inv_odd[i]);
+    }
+    const double num = (u1 * v2) * p1, den = (v1 * u2) * p2; // f = num / den; |den| > 0 because a != b
+    if (!(fabs(den) > 1e-280 && fabs(den) < 1e280 && fabs(num) < 1e280))
+        return false;
+    const double ad = fabs(den);
+    double q = fabs(num) * rcp_newton(ad, true);
+    q = __fma_rn(__fma_rn(-ad, q, fabs(num)), rcp_newton(ad, false), q);
+    // |log b - log a| = 2 |s2| p2 >= 2 |s2|; |log| < 105 for f32-born a, b and for a level within a factor 1.5 of them
+    const double tol = (1. + q) * 2e-14 / fabs(s2) + 1e-15 * q;
+    const float lo = __double2float_rn(q - tol), hi = __double2float_rn(q + tol);
+    if (lo != hi)
+        return false;
+    f = ((num < 0) != (den < 0)) ? -lo : lo;
+    return true;
+}
+
 // mifi_get_values_linear_f & friends for n == 1; returns false where the reference leaves the output untouched
 // xlog: log(x) (LOG) or log(log(x + e)) (LOGLOG) computed on the host for fixed target levels, NaN = compute here
 __device__ __forceinline__ float two_level(int method, float A, float B, double a, double b, double x, double xlog)
 {
     if (method == FIMEXCU_VINT_METHOD_NN)
         return A; // interpolation.c:416-425
+    bool have_f = false;
+    float f = 0.f;
     if (method == FIMEXCU_VINT_METHOD_LOG || method == FIMEXCU_VINT_METHOD_LOGLOG) {
         if (a <= 0 || b <= 0 || x <= 0)
             return nan_f(); // reference: MIFI_ERROR, output unwritten
-        if (method == FIMEXCU_VINT_METHOD_LOGLOG) {
+        // the same function of the same argument: exact weights whatever the logarithm's last bit (f == 0 / 1 copy A / B even
+        // next to an undefined value)
+        if (a == b || x == a) {
+            have_f = true;
+            f = 0.f;
+        } else if (x == b) {
+            have_f = true;
+            f = 1.f;
+        } else if (method == FIMEXCU_VINT_METHOD_LOG) {
+            have_f = log_weight_fast(a, b, x, f);
+        }
+        if (!have_f && method == FIMEXCU_VINT_METHOD_LOGLOG) { // log(v + e) > 1 for v > 0: the inner checks cannot fail otherwise
             const double e = 2.7182818284590452354;
             a = log(__dadd_rn(a, e));
             b = log(__dadd_rn(b, e));
@@ -65,11 +128,14 @@ __device__ __forceinline__ float two_level(int method, float A, float B, double 
             if (a <= 0 || b <= 0 || (isnan(xlog) && x <= 0))
                 return nan_f();
         }
-        a = log(a);
-        b = log(b);
-        x = isnan(xlog) ? log(x) : xlog;
+        if (!have_f) {
+            a = log(a);
+            b = log(b);
+            x = isnan(xlog) ? log(x) : xlog;
+        }
     }
-    const float f = (a == b) ? 0.f : __double2float_rn(__ddiv_rn(__dsub_rn(x, a), __dsub_rn(b, a)));
+    if (!have_f)
+        f = (a == b) ? 0.f : __double2float_rn(__ddiv_rn(__dsub_rn(x, a), __dsub_rn(b, a)));
     switch (method) {
     case FIMEXCU_VINT_METHOD_LIN_CONST_EXTRA:
         if (f >= 1.f)
@@ -184,7 +250,12 @@ __device__ __forceinline__ bool find_neighbors_monotone(const Col& c, int n, int
     if (dir > 0 ? x >= cl : x <= cl) {
         // far end: (n-1, n-2), provided the f32 distances of the last two elements are distinguishable (they are unless |x|
         // exceeds 2^24 level spacings; then the reference's tie handling decides and the general scan is used)
-        if (!(fabsf(__fsub_rn(x, cl)) < fabsf(__fsub_rn(x, c(n - 2)))))
+        const float dl = fabsf(__fsub_rn(x, cl)), d2 = fabsf(__fsub_rn(x, c(n - 2)));
+        if (!(dl < d2))
+            return false;
+        // the fallback walks upwards and keeps the FIRST element of a run of equal distances as runner-up: n-2 only if n-3 is
+        // measurably farther
+        if (n >= 3 && !(d2 < fabsf(__fsub_rn(x, c(n - 3)))))
             return false;
         first = n - 1;
         second = n - 2;
@@ -203,6 +274,9 @@ __device__ __forceinline__ bool find_neighbors_monotone(const Col& c, int n, int
     // the reference minimises the ROUNDED differences x - c[k]; they order like the exact ones unless two of them round to the
     // same float -- then leave the decision to the general scan
     if (lo > 0 && __fsub_rn(x, c(lo)) == __fsub_rn(x, c(lo - 1)))
+        return false;
+    // a difference that overflows to FLT_MAX or beyond looks like "no neighbour on this side" to the reference
+    if (!(fabsf(__fsub_rn(x, c(lo))) < FLT_MAX && fabsf(__fsub_rn(x, c(hi))) < FLT_MAX))
         return false;
     if (hi < n - 1 && __fsub_rn(x, c(hi)) == __fsub_rn(x, c(hi + 1)))
         return false;
@@ -234,61 +308,95 @@ struct HybridCol { // p = ap + b*ps formed on the fly: vertical_coordinate_trans
     __device__ __forceinline__ float operator()(int k) const { return __double2float_rn(__dadd_rn(ap[k], __dmul_rn(b[k], ps))); }
 };
 
+// CDMVerticalInterpolator.cc:505-528: is the target level inside the column's [vmin, vmax]?
+__device__ __forceinline__ bool level_in_range(const VertParams& P, double vout, double lo, double hi)
+{
+    if (P.vmin && P.vmax)
+        return (vout >= lo) && (vout <= hi);
+    if (P.vmin)
+        return vout >= lo;
+    if (P.vmax)
+        return vout <= hi;
+    return true;
+}
+
+// what one output value needs besides its column: passed by value to the out-of-line helpers of the sweep kernel
+struct OutCfg {
+    int method;
+    float bad, fill, valid_min, valid_max;
+    size_t nInner;
+};
+__device__ __forceinline__ OutCfg out_cfg(const VertParams& P) { return OutCfg{P.method, P.bad, P.fill, P.valid_min, P.valid_max, P.nInner}; }
+
+// valid_min / valid_max clamp (CDMVerticalInterpolator.cc:551-561; NaN compares false and stays), fill value, streaming store
+__device__ __forceinline__ void store_result(const OutCfg& C, float* dst, float r)
+{
+    if (r < C.valid_min)
+        r = C.valid_min;
+    if (r > C.valid_max)
+        r = C.valid_max;
+    if (!isnan(C.fill) && isnan(r))
+        r = C.fill;
+    __stcs(dst, r);
+}
+
+// the two bracketing levels' values through the two-level kernel
+__device__ __forceinline__ float blend_levels(const OutCfg& C, float A, float B, float a, float b, double vout, double xlog)
+{
+    if (!isnan(C.bad)) {
+        if (A == C.bad)
+            A = nan_f();
+        if (B == C.bad)
+            B = nan_f();
+    }
+    return two_level(C.method, A, B, static_cast<double>(a), static_cast<double>(b), vout, xlog);
+}
+
+// one output value by the reference's neighbour search (dir: +1 / -1 column known strictly monotone, 0 general scan)
+template <class Col>
+__device__ __forceinline__ float general_output(const OutCfg& C, const Col& c, int nzi, int dir, const float* din, double vout, double xlog)
+{
+    int p0, p1;
+    const float xf = __double2float_rn(vout);
+    if (!(dir != 0 && find_neighbors_monotone(c, nzi, dir, xf, p0, p1)))
+        find_neighbors(c, nzi, xf, p0, p1);
+    if (p0 == p1)
+        return nan_f();
+    return blend_levels(C, __ldg(din + static_cast<size_t>(p0) * C.nInner), __ldg(din + static_cast<size_t>(p1) * C.nInner), c(p0), c(p1), vout, xlog);
+}
+
+// +1 strictly increasing, -1 strictly decreasing (both NaN-free), 0 otherwise
+template <class Col>
+__device__ __forceinline__ int column_direction(const Col& c, int nzi)
+{
+    if (nzi < 2)
+        return 0;
+    bool inc = true, dec = true;
+    float prev = c(0);
+    for (int k = 1; k < nzi; ++k) {
+        const float cur = c(k);
+        inc = inc && (cur > prev);
+        dec = dec && (cur < prev);
+        prev = cur;
+    }
+    return inc ? 1 : (dec ? -1 : 0);
+}
+
 template <class Col>
 __device__ __forceinline__ void vertical_column(const VertParams& P, const Col& c, size_t cidx, size_t outer, size_t inner, int dir_known)
 {
     const int nzi = static_cast<int>(P.nzi);
-    // strictly monotone and NaN-free?  (+1 increasing, -1 decreasing, 0 -> general scan)
-    int dir = dir_known;
-    if (dir == 0 && nzi >= 2) {
-        bool inc = true, dec = true;
-        float prev = c(0);
-        for (int k = 1; k < nzi; ++k) {
-            const float cur = c(k);
-            inc = inc && (cur > prev);
-            dec = dec && (cur < prev);
-            prev = cur;
-        }
-        dir = inc ? 1 : (dec ? -1 : 0);
-    }
+    const int dir = dir_known != 0 ? dir_known : column_direction(c, nzi);
     const float* din = P.in + outer * P.nzi * P.nInner + inner;
     float* dout = P.out + outer * P.nzo * P.nInner + inner;
-    const bool has_bad = !isnan(P.bad), has_fill = !isnan(P.fill);
     const double lo = P.vmin ? P.vmin[cidx] : 0., hi = P.vmax ? P.vmax[cidx] : 0.;
+    const OutCfg C = out_cfg(P);
     for (size_t k = 0; k < P.nzo; ++k) {
         const double vout = P.vcoord_out ? static_cast<double>(__ldg(P.vcoord_out + (outer * P.nzo + k) * P.nInner + inner)) : __ldg(P.levels + k);
-        bool range = true; // CDMVerticalInterpolator.cc:505-528
-        if (P.vmin && P.vmax)
-            range = (vout >= lo) && (vout <= hi);
-        else if (P.vmin)
-            range = vout >= lo;
-        else if (P.vmax)
-            range = vout <= hi;
         float r = nan_f();
-        if (range) {
-            int p0, p1;
-            const float xf = __double2float_rn(vout);
-            if (!(dir != 0 && find_neighbors_monotone(c, nzi, dir, xf, p0, p1)))
-                find_neighbors(c, nzi, xf, p0, p1);
-            if (p0 != p1) {
-                float A = __ldg(din + static_cast<size_t>(p0) * P.nInner), B = __ldg(din + static_cast<size_t>(p1) * P.nInner);
-                if (has_bad) {
-                    if (A == P.bad)
-                        A = nan_f();
-                    if (B == P.bad)
-                        B = nan_f();
-                }
-                r = two_level(P.method, A, B, static_cast<double>(c(p0)), static_cast<double>(c(p1)), vout, P.xlog ? __ldg(P.xlog + k) : nan(""));
-            }
-        }
-        // valid_min / valid_max clamp (CDMVerticalInterpolator.cc:551-561); NaN compares false and stays
-        if (r < P.valid_min)
-            r = P.valid_min;
-        if (r > P.valid_max)
-            r = P.valid_max;
-        if (has_fill && isnan(r))
-            r = P.fill;
-        __stcs(dout + k * P.nInner, r);
+        if (level_in_range(P, vout, lo, hi))
+            r = general_output(C, c, nzi, dir, din, vout, P.xlog ? __ldg(P.xlog + k) : nan(""));
+        store_result(C, dout + k * P.nInner, r);
     }
 }
 
@@ -326,6 +434,534 @@ __global__ void __launch_bounds__(VT) vertical_kernel(const VertParams P)
     }
 }
 
+// ---- fast paths for strictly monotone columns and FIXED target levels ------------------------------------------------------------
+// For such a column the reference's search returns (see find_neighbors_monotone), with n(x) = number of elements on the near
+// side of x in column order (c(k) <= x for an increasing, c(k) >= x for a decreasing column) and step = (x == c(0)) ? 0 : n(x):
+//   step == 0      (0,0): nothing to interpolate between;  step == nzi   (nzi-1, nzi-2);  else lo = step-1, hi = step.
+// value_from_step() turns a step into the output value; f32 difference ties and the other corner cases in which the reference's
+// scan is not fully determined by the bracket go to the out-of-line general search (rare).
+template <class Col>
+__device__ __noinline__ float sweep_slow(OutCfg C, Col c, int nzi, int dir, const float* din, double vout, double xlog)
+{
+    return general_output(C, c, nzi, dir, din, vout, xlog);
+}
+
+struct PairCol { // hybrid pressure from interleaved (ap, b) pairs
+    const double2* apb;
+    double ps;
+    __device__ __forceinline__ float operator()(int k) const
+    {
+        const double2 q = apb[k];
+        return __double2float_rn(__dadd_rn(q.x, __dmul_rn(q.y, ps)));
+    }
+};
+
+struct ColumnEnds { // c(0), c(1), c(nzi-1), c(nzi-2), c(nzi-3)
+    float c0, c1, cl, cl2, cl3;
+};
+
+// plo = c(step-1), phi = c(step) for an interior step (ignored otherwise)
+struct GlobalVal { // the column's values where they lie
+    const float* din;
+    size_t nInner;
+    __device__ __forceinline__ float operator()(int k) const { return __ldg(din + static_cast<size_t>(k) * nInner); }
+};
+template <class Col, class Val>
+__device__ __forceinline__ float value_from_step(const OutCfg& C, const Col& c, const Val& val, int nzi, bool inc, const ColumnEnds& E, int step, float x,
+                                                 float plo, float phi, const float* din, double vout, double xlog)
+{
+    bool fast, distinct = true;
+    int first = 0, second = 0;
+    float a = 0.f, b = 0.f;
+    if (step == 0) {
+        distinct = false;
+        fast = (x == E.c0) || fabsf(__fsub_rn(x, E.c0)) < fabsf(__fsub_rn(x, E.c1));
+    } else if (step == nzi) {
+        first = nzi - 1;
+        second = nzi - 2;
+        a = E.cl;
+        b = E.cl2;
+        const float d2 = fabsf(__fsub_rn(x, E.cl2));
+        fast = fabsf(__fsub_rn(x, E.cl)) < d2 && (nzi < 3 || d2 < fabsf(__fsub_rn(x, E.cl3)));
+    } else {
+        const float dlo = __fsub_rn(x, plo), dhi = __fsub_rn(x, phi);
+        fast = fabsf(dlo) < FLT_MAX && fabsf(dhi) < FLT_MAX && (inc || x != plo);
+        if (fast && step > 1)
+            fast = dlo != __fsub_rn(x, c(step - 2));
+        first = inc ? step - 1 : step;
+        second = inc ? step : step - 1;
+        a = inc ? plo : phi;
+        b = inc ? phi : plo;
+    }
+    if (!fast)
+        return sweep_slow(C, c, nzi, inc ? 1 : -1, din, vout, xlog);
+    if (!distinct)
+        return nan_f();
+    return blend_levels(C, val(first), val(second), a, b, vout, xlog);
+}
+
+// every output of a column by the reference's scan (NaN / unordered / single-level columns)
+template <class Col>
+__device__ __forceinline__ void column_by_general_scan(const VertParams& P, const OutCfg& C, const Col& c, int nzi, int nzo, const double* s_xd,
+                                                       const double* s_xl, double rlo, double rhi, const float* din, float* dout)
+{
+    const int dir = column_direction(c, nzi);
+    for (int jj = 0; jj < nzo; ++jj) {
+        const double vout = s_xd[jj];
+        float r = nan_f();
+        if (level_in_range(P, vout, rlo, rhi))
+            r = sweep_slow(C, c, nzi, dir, din, vout, s_xl[jj]);
+        store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
+    }
+}
+
+// Sweep kernel, for target levels that are SORTED (either way).  Phase 1 walks the column once, level by level (uniform,
+// broadcast accesses; an explicit coordinate streams through registers CH levels ahead), and notes for every target level the
+// step at which the walk passes it; monotonicity is verified on the way.  Phase 2 runs over the target levels with all lanes in
+// step.  Shared memory: hybrid (ap, b) pairs, the level list (f64, log, f32 with a NaN sentinel either side), notes [nzo][VT] u16.
+constexpr int CH = 4;
+
+template <bool HYBRID>
+__global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams P)
+{
+    extern __shared__ double smem_d[];
+    const int nzi = static_cast<int>(P.nzi), nzo = static_cast<int>(P.nzo);
+    double2* s_apb = reinterpret_cast<double2*>(smem_d);
+    double* s_xd = smem_d + (HYBRID ? 2 * nzi : 0);
+    double* s_xl = s_xd + nzo;
+    float* s_xf = reinterpret_cast<float*>(s_xl + nzo) + 1; // [-1] and [nzo] are sentinels
+    unsigned short* s_k = reinterpret_cast<unsigned short*>(s_xf + nzo + 1 + (nzo & 1)) + threadIdx.x; // [nzo][VT], this thread's column
+    if (HYBRID) {
+        for (int k = threadIdx.x; k < nzi; k += VT)
+            s_apb[k] = make_double2(P.ap[k], P.b[k]);
+    }
+    for (int k = threadIdx.x; k < nzo; k += VT) {
+        const double x = P.levels[k];
+        s_xd[k] = x;
+        s_xl[k] = P.xlog ? P.xlog[k] : nan("");
+        s_xf[k] = __double2float_rn(x);
+    }
+    if (threadIdx.x == 0) {
+        s_xf[-1] = nan_f();
+        s_xf[nzo] = nan_f();
+    }
+    __syncthreads();
+    const size_t ncol = P.nOuter * P.nInner;
+    const size_t cidx = blockIdx.x * static_cast<size_t>(VT) + threadIdx.x;
+    if (cidx >= ncol)
+        return;
+    const size_t outer = cidx / P.nInner, inner = cidx - outer * P.nInner;
+    const float* din = P.in + outer * P.nzi * P.nInner + inner;
+    float* dout = P.out + outer * P.nzo * P.nInner + inner;
+    const float* gc = HYBRID ? nullptr : P.vcoord_in + outer * P.nzi * P.nInner + inner;
+    double ps = 0.;
+    if (HYBRID)
+        ps = __dmul_rn(static_cast<double>(__ldg(P.ps + (P.nOuterPs == 1 ? 0 : outer) * P.nInner + inner)), P.ps_scale);
+    const PairCol hc{s_apb, ps};
+    const StridedCol sc{gc, static_cast<int>(P.nInner)};
+    auto coord = [&](int k) -> float { return HYBRID ? hc(k) : sc(k); };
+    const OutCfg C = out_cfg(P);
+    const double rlo = P.vmin ? P.vmin[cidx] : 0., rhi = P.vmax ? P.vmax[cidx] : 0.;
+
+    // ---- phase 1: one walk along the column, in the order in which it increases after multiplication by sg ----
+    bool ok = nzi >= 2;
+    ColumnEnds E{};
+    bool inc = false;
+    if (ok) {
+        E.c0 = coord(0);
+        E.c1 = coord(1);
+        inc = E.c1 > E.c0;
+        ok = inc || (E.c1 < E.c0);
+    }
+    if (ok) {
+        const float sg = inc ? 1.f : -1.f; // exact
+        const bool forward = (inc ? 1 : -1) == P.levels_dir || nzo == 1;
+        const int xstep = forward ? 1 : -1, kstep = xstep * VT;
+        const float* xp = s_xf + (forward ? 0 : nzo - 1);
+        unsigned short* kp = s_k + (forward ? 0 : nzo - 1) * VT;
+        float x = __fmul_rn(sg, *xp); // NaN once the list is exhausted
+        auto note = [&](int step) {
+            *kp = static_cast<unsigned short>(step);
+            xp += xstep;
+            kp += kstep;
+            x = __fmul_rn(sg, *xp);
+        };
+        float pm1 = __fmul_rn(sg, E.c0);
+        while (x <= pm1) // at or beyond the end that holds element 0
+            note(0);
+        bool mono = true;
+        if (HYBRID) {
+            for (int k = 1; k < nzi; ++k) {
+                const float pk = __fmul_rn(sg, hc(k));
+                mono = mono && (pk > pm1);
+                while (x < pk) // c(k-1) <= x < c(k) in walk order
+                    note(k);
+                pm1 = pk;
+            }
+        } else {
+            float ccur[CH];
+#pragma unroll
+            for (int i = 0; i < CH; ++i)
+                ccur[i] = (1 + i) < nzi ? __ldg(gc + static_cast<size_t>(1 + i) * P.nInner) : 0.f;
+            for (int base = 1; base < nzi; base += CH) {
+                float cnx[CH];
+#pragma unroll
+                for (int i = 0; i < CH; ++i)
+                    cnx[i] = (base + CH + i) < nzi ? __ldg(gc + static_cast<size_t>(base + CH + i) * P.nInner) : 0.f;
+#pragma unroll
+                for (int i = 0; i < CH; ++i) {
+                    const int k = base + i;
+                    if (k < nzi) {
+                        const float pk = __fmul_rn(sg, ccur[i]);
+                        mono = mono && (pk > pm1);
+                        while (x < pk)
+                            note(k);
+                        pm1 = pk;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < CH; ++i)
+                    ccur[i] = cnx[i];
+            }
+        }
+        ok = mono;
+        if (ok)
+            while (!isnan(x)) // at or beyond the far end
+                note(nzi);
+    }
+    if (!ok) {
+        if (HYBRID)
+            column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, rlo, rhi, din, dout);
+        else
+            column_by_general_scan(P, C, sc, nzi, nzo, s_xd, s_xl, rlo, rhi, din, dout);
+        return;
+    }
+
+    // ---- phase 2: the target levels, all lanes in step ----
+    E.cl = coord(nzi - 1);
+    E.cl2 = coord(nzi - 2);
+    E.cl3 = nzi >= 3 ? coord(nzi - 3) : 0.f;
+    for (int jj = 0; jj < nzo; ++jj) {
+        const double vout = s_xd[jj];
+        float r = nan_f();
+        if (level_in_range(P, vout, rlo, rhi)) {
+            const int step = s_k[jj * VT];
+            float plo = 0.f, phi = 0.f;
+            if (step > 0 && step < nzi) {
+                plo = coord(step - 1);
+                phi = coord(step);
+            }
+            const GlobalVal gv{din, P.nInner};
+            if (HYBRID)
+                r = value_from_step(C, hc, gv, nzi, inc, E, step, s_xf[jj], plo, phi, din, vout, s_xl[jj]);
+            else
+                r = value_from_step(C, sc, gv, nzi, inc, E, step, s_xf[jj], plo, phi, din, vout, s_xl[jj]);
+        }
+        store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
+    }
+}
+
+// ---- hybrid-sigma source, launch-wide table -----------------------------------------------------------------------------------
+// p_k(ps) = ap_k + b_k*ps depends on the column only through ps, so n(x_j) is a step function of ps.  One small kernel proves
+// from the launch's ps range that every column is strictly monotone (as hybrid_direction() does on the host) and tabulates
+// n(x_j) on a ps grid; the main kernel looks its column's bin up, corrects the count by +-1 steps against the exactly evaluated
+// f32 column and emits.  No per-column walk at all: ~100 instructions per output value.  Target levels need not be sorted.
+struct HybridTableHeader {
+    double ps_lo, ps_hi, inv_width; // scaled surface pressure range the table (and the proof) covers
+    int dir, nbins;
+};
+
+__host__ __device__ inline int hybrid_direction(const double* ap, const double* b, size_t nzi, double ps_lo, double ps_hi)
+{
+    // p_{k+1} - p_k is linear in ps: it keeps its sign on [ps_lo, ps_hi] if it has it at both ends; a margin of a few f32 ulps
+    // makes the statement hold for the ROUNDED f32 column the kernels work on
+    if (!(ps_lo <= ps_hi) || !(fabs(ps_lo) <= DBL_MAX) || !(fabs(ps_hi) <= DBL_MAX) || nzi < 2)
+        return 0;
+    bool inc = true, dec = true;
+    for (size_t k = 0; k + 1 < nzi; ++k) {
+        for (int e = 0; e < 2; ++e) {
+            const double ps = e ? ps_hi : ps_lo;
+            const double p0 = ap[k] + b[k] * ps, p1 = ap[k + 1] + b[k + 1] * ps;
+            const double margin = 8.0 * 1.1920929e-7 * fmax(fabs(p0), fabs(p1)) + 1e-30;
+            inc = inc && (p1 - p0 > margin);
+            dec = dec && (p0 - p1 > margin);
+        }
+    }
+    return inc ? 1 : (dec ? -1 : 0);
+}
+
+__device__ __forceinline__ float decode_ordered(int e) { return e >= 0 ? __int_as_float(e) : -__int_as_float(-e); }
+
+// Histogram of the launch's surface pressure by the top bits of its ordered-int encoding (sign, exponent, 2 mantissa bits:
+// quarter-octave bins).  NaN is skipped.  The table covers the populated region around the bulk of the data, so that a few
+// outliers (fill values, uninitialised pad columns) cannot stretch it; columns outside go through the general search.
+constexpr int PS_HIST_BINS = 2048, PS_HIST_SHIFT = 21;
+__device__ __forceinline__ int ps_hist_key(float v)
+{
+    const int bits = __float_as_int(v);
+    const int enc = bits >= 0 ? bits : -(bits & 0x7fffffff);
+    return (enc >> PS_HIST_SHIFT) + PS_HIST_BINS / 2;
+}
+
+__global__ void __launch_bounds__(256) ps_hist_kernel(const float* __restrict__ ps, size_t n, unsigned* __restrict__ hist)
+{
+    __shared__ unsigned sh[PS_HIST_BINS];
+    for (int i = threadIdx.x; i < PS_HIST_BINS; i += 256)
+        sh[i] = 0;
+    __syncthreads();
+    for (size_t base = blockIdx.x * 256ull; base < n; base += 256ull * gridDim.x) { // whole warps stay in step
+        const size_t i = base + threadIdx.x;
+        const float v = i < n ? __ldg(ps + i) : nan_f();
+        const bool valid = !isnan(v);
+        const int key = valid ? ps_hist_key(v) : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, key); // the data sit in a handful of bins: one atomic per bin and warp
+        if (valid && static_cast<int>(threadIdx.x & 31) == __ffs(peers) - 1)
+            atomicAdd(&sh[key], static_cast<unsigned>(__popc(peers)));
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < PS_HIST_BINS; i += 256)
+        if (sh[i])
+            atomicAdd(&hist[i], sh[i]);
+}
+
+__global__ void __launch_bounds__(256) hybrid_table_kernel(const double* __restrict__ ap, const double* __restrict__ b, int nzi,
+                                                           const double* __restrict__ levels, int nzo, const unsigned* __restrict__ hist,
+                                                           double ps_scale, int nbins, HybridTableHeader* __restrict__ hdr,
+                                                           unsigned short* __restrict__ tab)
+{
+    __shared__ unsigned sh[PS_HIST_BINS];
+    __shared__ int s_dir;
+    __shared__ double s_lo, s_w;
+    __shared__ int s_first, s_last;
+    __shared__ unsigned long long s_total;
+    if (threadIdx.x == 0) {
+        s_first = PS_HIST_BINS;
+        s_last = -1;
+        s_total = 0;
+    }
+    __syncthreads();
+    {
+        unsigned long long part = 0;
+        int first = PS_HIST_BINS, last = -1;
+        for (int i = threadIdx.x; i < PS_HIST_BINS; i += 256) {
+            const unsigned c = hist[i];
+            sh[i] = c;
+            if (c) {
+                part += c;
+                first = min(first, i);
+                last = max(last, i);
+            }
+        }
+        if (part) {
+            atomicAdd(&s_total, part);
+            atomicMin(&s_first, first);
+            atomicMax(&s_last, last);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned long long total = s_total;
+        int dir = 0;
+        double lo = 0., hi = 0.;
+        if (total) {
+            // smallest run of bins holding 90 % of the values, then outwards over every neighbouring populated bin
+            const unsigned long long need = total - total / 10;
+            int best_l = s_first, best_r = s_last, l = s_first;
+            unsigned long long acc = 0;
+            for (int r = s_first; r <= s_last; ++r) {
+                acc += sh[r];
+                while (acc - sh[l] >= need) {
+                    acc -= sh[l];
+                    ++l;
+                }
+                if (acc >= need && r - l < best_r - best_l) {
+                    best_l = l;
+                    best_r = r;
+                }
+            }
+            while (best_l > 0 && sh[best_l - 1])
+                --best_l;
+            while (best_r < PS_HIST_BINS - 1 && sh[best_r + 1])
+                ++best_r;
+            // bin edges back to floats: the smallest and the largest encoding of the run
+            const long long e_lo = (static_cast<long long>(best_l) - PS_HIST_BINS / 2) << PS_HIST_SHIFT;
+            const long long e_hi = ((static_cast<long long>(best_r) - PS_HIST_BINS / 2 + 1) << PS_HIST_SHIFT) - 1;
+            const long long cap = 0x7f800000ll;
+            const int i_lo = static_cast<int>(e_lo < -cap ? -cap : e_lo), i_hi = static_cast<int>(e_hi > cap ? cap : e_hi);
+            const double a0 = static_cast<double>(decode_ordered(i_lo)) * ps_scale, a1 = static_cast<double>(decode_ordered(i_hi)) * ps_scale;
+            lo = fmin(a0, a1);
+            hi = fmax(a0, a1);
+            dir = hybrid_direction(ap, b, nzi, lo, hi);
+        }
+        const double w = dir ? (hi - lo) / nbins : 0.;
+        s_dir = dir;
+        s_lo = lo;
+        s_w = w;
+        hdr->ps_lo = lo;
+        hdr->ps_hi = hi;
+        hdr->inv_width = (w > 0 && 1. / w <= DBL_MAX) ? 1. / w : 0.;
+        hdr->dir = dir;
+        hdr->nbins = nbins;
+    }
+    __syncthreads();
+    const int dir = s_dir;
+    for (int idx = threadIdx.x; idx < nzo * nbins; idx += 256) {
+        const int j = idx / nbins, i = idx - j * nbins;
+        int n = 0;
+        if (dir) {
+            const double ps = s_lo + (i + 0.5) * s_w;
+            const float sg = dir > 0 ? 1.f : -1.f;
+            const float x = sg * __double2float_rn(levels[j]);
+            int lo = 0, hi = nzi; // count of k with sg*c(k) <= x: c is increasing in walk order
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                const float v = sg * __double2float_rn(__dadd_rn(ap[mid], __dmul_rn(b[mid], ps)));
+                if (v <= x)
+                    lo = mid + 1;
+                else
+                    hi = mid;
+            }
+            n = lo;
+        }
+        tab[idx] = static_cast<unsigned short>(n);
+    }
+}
+
+constexpr int HT = 128;       // threads (columns) per block of the table kernel's consumer
+constexpr int MAX_ADJUST = 6; // corrections of a looked-up count before the general search takes over
+constexpr int JC = 8;         // target levels per batch: their bracket values travel together
+constexpr unsigned CODE_NAN = 0u, CODE_BLEND = 1u << 14, CODE_SLOW = 2u << 14, CODE_UP = 1u << 13; // | first (13 bits)
+
+// what value_from_step() decides, without fetching anything: NaN / general search / blend(first, first +- 1)
+__device__ __forceinline__ unsigned classify_step(const PairCol& c, int nzi, bool inc, const ColumnEnds& E, int step, float x, float plo, float phi)
+{
+    if (step == 0)
+        return ((x == E.c0) || fabsf(__fsub_rn(x, E.c0)) < fabsf(__fsub_rn(x, E.c1))) ? CODE_NAN : CODE_SLOW;
+    if (step == nzi) {
+        const float d2 = fabsf(__fsub_rn(x, E.cl2));
+        const bool fast = fabsf(__fsub_rn(x, E.cl)) < d2 && (nzi < 3 || d2 < fabsf(__fsub_rn(x, E.cl3)));
+        return fast ? (CODE_BLEND | static_cast<unsigned>(nzi - 1)) : CODE_SLOW; // second = first - 1
+    }
+    const float dlo = __fsub_rn(x, plo), dhi = __fsub_rn(x, phi);
+    bool fast = fabsf(dlo) < FLT_MAX && fabsf(dhi) < FLT_MAX && (inc || x != plo);
+    if (fast && step > 1)
+        fast = dlo != __fsub_rn(x, c(step - 2));
+    if (!fast)
+        return CODE_SLOW;
+    return inc ? (CODE_BLEND | CODE_UP | static_cast<unsigned>(step - 1)) : (CODE_BLEND | static_cast<unsigned>(step));
+}
+
+// Per column: bin of the table, then the target levels in batches of JC.  Pass 1 of a batch finds every level's bracket (table
+// count, corrected against the exactly evaluated f32 column) and sends for the two bracket values with asynchronous copies into
+// shared memory, so that all gathers of a batch are in flight together; pass 2 blends and stores.
+template <int METHOD> // compile-time interpolation method: the other methods' arithmetic is not in the kernel at all
+__global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const VertParams P, const HybridTableHeader* __restrict__ hdr,
+                                                                     const unsigned short* __restrict__ tab)
+{
+    extern __shared__ double smem_d[];
+    const int nzi = static_cast<int>(P.nzi), nzo = static_cast<int>(P.nzo);
+    const int nbins = hdr->nbins, dir = hdr->dir;
+    double2* s_apb = reinterpret_cast<double2*>(smem_d);
+    double* s_xd = smem_d + 2 * nzi;
+    double* s_xl = s_xd + nzo;
+    float* s_xf = reinterpret_cast<float*>(s_xl + nzo);
+    unsigned short* s_tab = reinterpret_cast<unsigned short*>(s_xf + nzo + (nzo & 1));
+    float* s_A = reinterpret_cast<float*>(s_tab + 2 * ((nzo * nbins + 1) / 2)) + threadIdx.x; // [JC][HT]
+    float* s_B = s_A + JC * HT;                                                                // [JC][HT]
+    unsigned short* s_code = reinterpret_cast<unsigned short*>(s_B - threadIdx.x + JC * HT) + threadIdx.x; // [JC][HT]
+    for (int k = threadIdx.x; k < nzi; k += HT)
+        s_apb[k] = make_double2(P.ap[k], P.b[k]);
+    for (int k = threadIdx.x; k < nzo; k += HT) {
+        const double x = P.levels[k];
+        s_xd[k] = x;
+        s_xl[k] = P.xlog ? P.xlog[k] : nan("");
+        s_xf[k] = __double2float_rn(x);
+    }
+    if (dir) {
+        const int words = (nzo * nbins + 1) / 2; // the table buffer is padded to a whole number of 32-bit words
+        for (int i = threadIdx.x; i < words; i += HT)
+            reinterpret_cast<unsigned*>(s_tab)[i] = __ldg(reinterpret_cast<const unsigned*>(tab) + i);
+    }
+    __syncthreads();
+    const size_t ncol = P.nOuter * P.nInner;
+    const size_t cidx = blockIdx.x * static_cast<size_t>(HT) + threadIdx.x;
+    if (cidx >= ncol)
+        return;
+    const size_t outer = cidx / P.nInner, inner = cidx - outer * P.nInner;
+    const float* din = P.in + outer * P.nzi * P.nInner + inner;
+    float* dout = P.out + outer * P.nzo * P.nInner + inner;
+    const double ps = __dmul_rn(static_cast<double>(__ldg(P.ps + (P.nOuterPs == 1 ? 0 : outer) * P.nInner + inner)), P.ps_scale);
+    const PairCol hc{s_apb, ps};
+    OutCfg C = out_cfg(P);
+    C.method = METHOD;
+    if (dir == 0 || !(ps >= hdr->ps_lo && ps <= hdr->ps_hi)) { // no proof for this launch, or a column outside its range (NaN, outlier)
+        column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, 0., 0., din, dout);
+        return;
+    }
+    const bool inc = dir > 0;
+    const float sg = inc ? 1.f : -1.f;
+    ColumnEnds E;
+    E.c0 = hc(0);
+    E.c1 = hc(1);
+    E.cl = hc(nzi - 1);
+    E.cl2 = hc(nzi - 2);
+    E.cl3 = nzi >= 3 ? hc(nzi - 3) : 0.f;
+    const double t = (ps - hdr->ps_lo) * hdr->inv_width;
+    const int bin = min(max(static_cast<int>(t), 0), nbins - 1);
+    const unsigned short* mytab = s_tab + bin;
+    const unsigned sA = static_cast<unsigned>(__cvta_generic_to_shared(s_A)), sB = static_cast<unsigned>(__cvta_generic_to_shared(s_B));
+    for (int j0 = 0; j0 < nzo; j0 += JC) {
+        const int jn = min(JC, nzo - j0);
+        for (int u = 0; u < jn; ++u) {
+            const int jj = j0 + u;
+            const float x = s_xf[jj];
+            const float xs = __fmul_rn(sg, x);
+            int n = mytab[jj * nbins];
+            // n must satisfy (n == 0 || c(n-1) <= x) && (n == nzi || x < c(n)) in walk order; the table is off by a step at
+            // most near a bin's own transitions
+            float plo = n > 0 ? hc(n - 1) : 0.f, phi = n < nzi ? hc(n) : 0.f;
+            int it = 0;
+            while (n > 0 && !(__fmul_rn(sg, plo) <= xs) && it < MAX_ADJUST) {
+                --n;
+                ++it;
+                phi = plo;
+                plo = n > 0 ? hc(n - 1) : 0.f;
+            }
+            while (n < nzi && !(xs < __fmul_rn(sg, phi)) && it < MAX_ADJUST) {
+                ++n;
+                ++it;
+                plo = phi;
+                phi = n < nzi ? hc(n) : 0.f;
+            }
+            unsigned code = CODE_SLOW;
+            if (it < MAX_ADJUST && !isnan(x))
+                code = classify_step(hc, nzi, inc, E, (x == E.c0) ? 0 : n, x, plo, phi);
+            if (code & CODE_BLEND) {
+                const unsigned first = code & 0x1fffu;
+                const float* pa = din + static_cast<size_t>(first) * P.nInner;
+                const float* pb = (code & CODE_UP) ? pa + P.nInner : pa - P.nInner;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sA + u * HT * 4), "l"(pa) : "memory");
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sB + u * HT * 4), "l"(pb) : "memory");
+            }
+            s_code[u * HT] = static_cast<unsigned short>(code);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        for (int u = 0; u < jn; ++u) {
+            const int jj = j0 + u;
+            const unsigned code = s_code[u * HT];
+            float r = nan_f();
+            if (code & CODE_BLEND) {
+                const int first = static_cast<int>(code & 0x1fffu), second = (code & CODE_UP) ? first + 1 : first - 1;
+                r = blend_levels(C, s_A[u * HT], s_B[u * HT], hc(first), hc(second), s_xd[jj], s_xl[jj]);
+            } else if (code & CODE_SLOW) {
+                r = sweep_slow(C, hc, nzi, dir, din, s_xd[jj], s_xl[jj]);
+            }
+            store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
+        }
+    }
+}
+
 // min / max of the surface pressure of a launch (NaN ignored): lets the host prove monotonicity for all columns at once
 __global__ void __launch_bounds__(256) ps_minmax_kernel(const float* __restrict__ ps, size_t n, float* __restrict__ mm)
 {
@@ -346,22 +982,30 @@ __global__ void __launch_bounds__(256) ps_minmax_kernel(const float* __restrict_
     }
 }
 
-// p_k(ps) = ap_k + b_k*ps is linear in ps, so p_{k+1} - p_k keeps its sign on [ps_lo, ps_hi] if it has it at both ends; a margin
-// of a few f32 ulps makes the statement hold for the ROUNDED f32 column the kernel works on.
-static int hybrid_direction(const double* ap, const double* b, size_t nzi, double ps_lo, double ps_hi)
+// sorted fixed levels -> sweep kernel (FIMEXCU_VERTICAL_NO_SWEEP=1 keeps the per-level search kernels, for A/B measurements)
+static size_t sweep_smem(const VertParams& P)
 {
-    if (!(ps_lo <= ps_hi) || !std::isfinite(ps_lo) || !std::isfinite(ps_hi) || nzi < 2)
-        return 0;
-    bool inc = true, dec = true;
-    for (size_t k = 0; k + 1 < nzi; ++k) {
-        for (double ps : {ps_lo, ps_hi}) {
-            const double p0 = ap[k] + b[k] * ps, p1 = ap[k + 1] + b[k + 1] * ps;
-            const double margin = 8.0 * 1.1920929e-7 * std::max(std::fabs(p0), std::fabs(p1)) + 1e-30;
-            inc = inc && (p1 - p0 > margin);
-            dec = dec && (p0 - p1 > margin);
+    return ((P.vcoord_in ? 0 : 2 * P.nzi) + 2 * P.nzo) * sizeof(double) + (P.nzo + 2 + (P.nzo & 1)) * sizeof(float) + P.nzo * VT * sizeof(unsigned short);
+}
+static bool sweep_applies(const VertParams& P)
+{
+    static const bool disabled = std::getenv("FIMEXCU_VERTICAL_NO_SWEEP") != nullptr;
+    return !disabled && P.levels && !P.vcoord_out && P.levels_dir != 0 && P.nzi < 65535 && P.nzo < 65535 && sweep_smem(P) <= 24 * 1024;
+}
+
+// direction of a fixed level list: +1 non-decreasing, -1 non-increasing, 0 unordered / NaN
+static int levels_direction(const double* lv, size_t n)
+{
+    bool up = true, down = true;
+    for (size_t k = 0; k < n; ++k) {
+        if (std::isnan(lv[k]))
+            return 0;
+        if (k) {
+            up = up && lv[k] >= lv[k - 1];
+            down = down && lv[k] <= lv[k - 1];
         }
     }
-    return inc ? 1 : (dec ? -1 : 0);
+    return up ? 1 : (down ? -1 : 0);
 }
 
 static int launch_vertical(const VertParams& P, cudaStream_t s)
@@ -374,6 +1018,15 @@ static int launch_vertical(const VertParams& P, cudaStream_t s)
     if (P.method < 0 || P.method > FIMEXCU_VINT_METHOD_LIN_CONST_EXTRA)
         FXCU_FAIL("fimexcu_vertical: unknown vertical interpolation method");
     const unsigned blocks = static_cast<unsigned>((ncol + VT - 1) / VT);
+    if (sweep_applies(P)) {
+        const size_t smem = sweep_smem(P);
+        if (!P.vcoord_in)
+            vertical_sweep_kernel<true><<<blocks, VT, smem, s>>>(P);
+        else
+            vertical_sweep_kernel<false><<<blocks, VT, smem, s>>>(P);
+        FXCU_CUDA(cudaGetLastError());
+        return FIMEXCU_OK;
+    }
     if (!P.vcoord_in) {
         const size_t smem = 2 * P.nzi * sizeof(double);
         if (smem > 48 * 1024)
@@ -487,6 +1140,7 @@ int fimexcu_vertical_interpolate_dev_f(int method, const float* d_in, const floa
         FXCU_CUDA(cudaMemcpyAsync(lv.p, hl.data(), 2 * nzo * sizeof(double), cudaMemcpyHostToDevice, s));
         FXCU_CUDA(cudaStreamSynchronize(s)); // `hl` is a temporary
         P.levels = lv.as<double>();
+        P.levels_dir = levels_direction(levels_host, nzo);
         if (method == FIMEXCU_VINT_METHOD_LOG || method == FIMEXCU_VINT_METHOD_LOGLOG)
             P.xlog = lv.as<double>() + nzo;
         P.vcoord_out = nullptr;
@@ -586,6 +1240,7 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
     P.ap = coef.as<double>();
     P.b = coef.as<double>() + nzi;
     P.levels = coef.as<double>() + 2 * nzi;
+    P.levels_dir = levels_direction(levels_host, nzo);
     if (method == FIMEXCU_VINT_METHOD_LOG || method == FIMEXCU_VINT_METHOD_LOGLOG)
         P.xlog = coef.as<double>() + 2 * nzi + nzo;
     P.ps = d_ps;
@@ -600,13 +1255,52 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
     P.bad = badIn;
     P.fill = fillOut;
     P.out = d_out;
-    {
+    const size_t ncol = nOuter * nInner, nps = nOuterPs * nInner;
+    static const bool no_table = std::getenv("FIMEXCU_VERTICAL_NO_TABLE") != nullptr;
+    const int nbins = static_cast<int>(std::min<size_t>(512, std::max<size_t>(8, 2048 / std::max<size_t>(nzo, 1))));
+    const size_t tab_words = (nzo * nbins + 1) / 2;
+    const size_t tab_smem = (2 * nzi + 2 * nzo) * sizeof(double) + (nzo + (nzo & 1)) * sizeof(float) + tab_words * 4 +
+                            JC * HT * (2 * sizeof(float) + sizeof(unsigned short));
+    const int init[2] = {0x7f800000, static_cast<int>(0x80800000u)}; // +inf / "-inf" in the ordered-int encoding
+    if (!no_table && ncol && nzo && nzi >= 1 && nzi < 8192 && nzo < 65535 && tab_smem <= 26 * 1024) {
+        // launch-wide table path: ps range -> monotonicity proof + table (device side, no host round trip) -> consumer kernel
+        DevBuf scratch;
+        const size_t hdr_off = PS_HIST_BINS * sizeof(unsigned), tab_off = hdr_off + sizeof(HybridTableHeader);
+        if (!scratch.alloc(tab_off + tab_words * 4, s))
+            return FIMEXCU_ERROR;
+        char* base = static_cast<char*>(scratch.p);
+        FXCU_CUDA(cudaMemsetAsync(base, 0, hdr_off, s));
+        if (nps)
+            ps_hist_kernel<<<static_cast<unsigned>(std::min<size_t>((nps + 255) / 256, static_cast<size_t>(sm_count()) * 8)), 256, 0, s>>>(
+                d_ps, nps, reinterpret_cast<unsigned*>(base));
+        hybrid_table_kernel<<<1, 256, 0, s>>>(P.ap, P.b, static_cast<int>(nzi), P.levels, static_cast<int>(nzo), reinterpret_cast<const unsigned*>(base),
+                                               ps_scale, nbins, reinterpret_cast<HybridTableHeader*>(base + hdr_off),
+                                               reinterpret_cast<unsigned short*>(base + tab_off));
+        const unsigned blocks = static_cast<unsigned>((ncol + HT - 1) / HT);
+        const HybridTableHeader* hdr = reinterpret_cast<const HybridTableHeader*>(base + hdr_off);
+        const unsigned short* tab = reinterpret_cast<const unsigned short*>(base + tab_off);
+        switch (method) {
+#define FXCU_TABLE_CASE(M) \
+    case M: vertical_hybrid_table_kernel<M><<<blocks, HT, tab_smem, s>>>(P, hdr, tab); break;
+            FXCU_TABLE_CASE(FIMEXCU_VINT_METHOD_LIN)
+            FXCU_TABLE_CASE(FIMEXCU_VINT_METHOD_LOG)
+            FXCU_TABLE_CASE(FIMEXCU_VINT_METHOD_LOGLOG)
+            FXCU_TABLE_CASE(FIMEXCU_VINT_METHOD_NN)
+            FXCU_TABLE_CASE(FIMEXCU_VINT_METHOD_LIN_WEAK_EXTRA)
+            FXCU_TABLE_CASE(FIMEXCU_VINT_METHOD_LIN_NO_EXTRA)
+            FXCU_TABLE_CASE(FIMEXCU_VINT_METHOD_LIN_CONST_EXTRA)
+#undef FXCU_TABLE_CASE
+        default: FXCU_FAIL("fimexcu_vertical_hybrid_pressure: unknown vertical interpolation method");
+        }
+        FXCU_CUDA(cudaGetLastError());
+        FXCU_CUDA(cudaStreamSynchronize(s)); // `h` is a temporary
+        return FIMEXCU_OK;
+    }
+    if (!sweep_applies(P)) { // the per-level search kernel profits from a launch-wide monotonicity proof
         DevBuf mm;
         if (!mm.alloc(2 * sizeof(float), s))
             return FIMEXCU_ERROR;
-        const int init[2] = {0x7f800000, static_cast<int>(0x80800000u)}; // +inf / "-inf" in the ordered-int encoding
         FXCU_CUDA(cudaMemcpyAsync(mm.p, init, sizeof(init), cudaMemcpyHostToDevice, s));
-        const size_t nps = nOuterPs * nInner;
         if (nps)
             ps_minmax_kernel<<<static_cast<unsigned>(std::min<size_t>((nps + 255) / 256, 2048)), 256, 0, s>>>(d_ps, nps, mm.as<float>());
         FXCU_CUDA(cudaGetLastError());

@@ -278,3 +278,117 @@ def test_chained_horizontal_then_vertical_on_device(fx):
     got = out.reshape(12, nmem, out_y, pitch)[..., :out_x].cpu().numpy()
     assert _eq(got, want)
     assert (~np.isnan(want)).mean() > 0.5
+
+
+# ---------------------------------------------------------------------------------- sweep kernel (sorted fixed levels)
+def _sorted_level_list(vc, order):
+    lv = [1000., 925., 850., 700., 500., 400., 300., 250., 200., 150., 100., 50., 1100., 5., 1e12, -1e12, 3.0e9, 0.0, 512.0, 512.0]
+    picks = [vc[0, 0, 0], vc[0, -1, 0], vc[0, vc.shape[1] // 2, 5 % vc.shape[2]], vc[-1, min(1, vc.shape[1] - 1), 7 % vc.shape[2]],
+             vc[-1, max(vc.shape[1] - 2, 0), 11 % vc.shape[2]]]
+    lv += [float(v) for v in picks if not np.isnan(v)]
+    lv += [float(np.nextafter(np.float32(v), np.float32(np.inf))) for v in picks[:2] if not np.isnan(v)]
+    lv = sorted(lv)
+    return lv if order == "up" else lv[::-1]
+
+
+@pytest.mark.parametrize("method", [ol.VINT_LIN, ol.VINT_LOG, ol.VINT_NN, ol.VINT_LIN_WEAK, ol.VINT_LIN_CONST])
+@pytest.mark.parametrize("kind", ["pressure", "reversed", "unordered", "mixed", "ties"])
+@pytest.mark.parametrize("order", ["up", "down"])
+def test_vertical_sweep_sorted_levels_vs_oracle(fx, method, kind, order):
+    """sorted target levels take the one-pass sweep kernel: every bracket must be the reference search's, including levels equal to
+    a column element, beyond either end, f32 difference ties (-> per-output general path) and non-monotone / NaN columns (-> whole
+    column by the general scan)"""
+    from fimex_b200.vertical import verticalInterpolate
+    rng = np.random.default_rng(1000 * method + 10 * len(kind) + len(order))
+    nO, nzi, nI = 2, 65, 389
+    if kind == "mixed":
+        fld, vc = _columns(rng, nO, nzi, nI, "pressure")
+        _, vr = _columns(rng, nO, nzi, nI, "reversed")
+        _, vu = _columns(rng, nO, nzi, nI, "unordered")
+        sel = rng.integers(0, 4, (nO, 1, nI))
+        vc = np.where(sel == 1, vr, np.where(sel == 2, vu, vc))
+        eq = sel[:, 0, :] == 3  # strictly monotone except one repeated element
+        vc[:, 40, :] = np.where(eq, vc[:, 39, :], vc[:, 40, :])
+        vc[0, 64, 3] = np.nan
+        vc[1, 0, 4] = np.nan
+        vc = np.ascontiguousarray(vc.astype(np.float32))
+    elif kind == "ties":  # spacing of a few ulps on a large offset: differences to far levels round to the same float
+        fld, _ = _columns(rng, nO, nzi, nI, "pressure")
+        step = rng.choice([8.0, 16.0, -8.0], (nO, 1, nI))
+        vc = np.ascontiguousarray((1.0e8 + step * np.arange(nzi)[None, :, None]).astype(np.float32))
+    else:
+        fld, vc = _columns(rng, nO, nzi, nI, kind)
+    levels = _sorted_level_list(vc, order)
+    if kind == "ties":
+        levels = sorted(levels + [1.0e8, 1.0e8 + 16, 1.0e8 + 20, 1.0e8 - 300, 1.0e8 + 8 * 64, 1.0e8 + 8 * 64 + 4, 2.0e8, 1.7e15], reverse=(order == "down"))
+    want = _oracle_vertical(method, fld, vc, levels=levels)
+    got = verticalInterpolate(method, fld, vc, level1=levels)
+    if method == ol.VINT_LOG:
+        assert _close(got, want)
+    else:
+        assert _eq(got, want)
+
+
+@pytest.mark.parametrize("nzi", [1, 2, 3, 5])
+def test_vertical_sweep_short_columns_and_validity(fx, nzi):
+    import torch
+    from fimex_b200.vertical import verticalInterpolate
+    rng = np.random.default_rng(nzi)
+    nO, nI = 2, 130
+    fld, vc = _columns(rng, nO, nzi, nI, "pressure" if nzi % 2 else "reversed")
+    levels = sorted([float(vc[0, 0, 0]), float(vc[1, -1, 3]), 1200., 1., 500., 700., 900.])
+    vmin, vmax = rng.uniform(0, 600, (nO, nI)), rng.uniform(650, 1300, (nO, nI))
+    for kw in (dict(vmin=vmin, vmax=vmax), dict(vmax=vmax), {}):
+        want = _oracle_vertical(ol.VINT_LIN, fld, vc, levels=levels, valid_min=260., valid_max=300., **kw)
+        got = verticalInterpolate(ol.VINT_LIN, torch.from_numpy(fld).cuda(), torch.from_numpy(vc).cuda(), level1=levels,
+                                  validMin=torch.from_numpy(kw["vmin"]).cuda() if "vmin" in kw else None,
+                                  validMax=torch.from_numpy(kw["vmax"]).cuda() if "vmax" in kw else None, valid_min=260., valid_max=300.)
+        torch.cuda.synchronize()
+        assert _eq(got.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("order", ["up", "down"])
+def test_vertical_sweep_hybrid_nan_ps_and_level_order(fx, order):
+    from fimex_b200.vertical import verticalHybridPressure
+    rng = np.random.default_rng(77)
+    g = np.load(os.path.join(GOLD, "reference_vertical.npz"))
+    ap, b = g["en_ap_pa"] * 0.01, g["en_b"]
+    nI = 1500
+    levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50, 1, 0.001, 1100], dtype=np.float64)
+    levels = np.sort(levels) if order == "up" else np.sort(levels)[::-1].copy()
+    ps = (101325 - 12 * rng.uniform(0, 2500, nI) + rng.normal(0, 300, nI)).astype(np.float32)
+    ps[::97] = np.nan
+    ps[5] = 0.0
+    ps[6] = -500.0
+    fld = rng.normal(0, 10, (1, 65, nI)).astype(np.float32)
+    p = (ap[:, None] + b[:, None] * (ps.astype(np.float64) * 0.01)[None, :]).astype(np.float32)[None]
+    for m in (ol.VINT_LIN, ol.VINT_LOG, ol.VINT_LOGLOG):
+        want = _oracle_vertical(m, fld, np.ascontiguousarray(p), levels=levels)
+        got = verticalHybridPressure(m, fld, ap, b, ps.reshape(1, nI), levels, ps_scale=0.01)
+        assert (_eq if m == ol.VINT_LIN else _close)(got, want), m
+
+
+def test_vertical_hybrid_outlier_surface_pressure(fx):
+    """fill-like and garbage surface pressures (1e30, 0, negative, inf, NaN) in a few columns: those columns follow the reference's
+    general scan, all others are unaffected"""
+    from fimex_b200.vertical import verticalHybridPressure
+    rng = np.random.default_rng(9)
+    g = np.load(os.path.join(GOLD, "reference_vertical.npz"))
+    ap, b = g["en_ap_pa"] * 0.01, g["en_b"]
+    nI = 6000
+    levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50], dtype=np.float64)
+    ps = (101325 - 12 * rng.uniform(0, 2500, nI) + rng.normal(0, 300, nI)).astype(np.float32)
+    ps[::50] = np.float32(1e30)
+    ps[7::61] = 0.0
+    ps[11::67] = -3.0e4
+    ps[13::71] = np.inf
+    ps[17::73] = np.nan
+    ps[19::79] = np.float32(9.96921e36)
+    ps[23::83] = np.float32(55000.0)  # an isolated but valid value
+    fld = rng.normal(0, 10, (1, 65, nI)).astype(np.float32)
+    with np.errstate(all="ignore"):
+        p = (ap[:, None] + b[:, None] * (ps.astype(np.float64) * 0.01)[None, :]).astype(np.float32)[None]
+    for m in (ol.VINT_LIN, ol.VINT_LOG):
+        want = _oracle_vertical(m, fld, np.ascontiguousarray(p), levels=levels)
+        got = verticalHybridPressure(m, fld, ap, b, ps.reshape(1, nI), levels, ps_scale=0.01)
+        assert (_eq if m == ol.VINT_LIN else _close)(got, want), m
