@@ -429,6 +429,36 @@ def main_b200(args):
                "call": "fimexcu_cache_apply_f (host pointers, pinned; H2D + kernel + D2H pipelined over level chunks)"}
         lib.fimexcu_host_free(h_in)
         lib.fimexcu_host_free(h_out)
+        # the same slab as a packed CDM_SHORT variable: raw int16 in, int16 out, unpack / pack fused in the kernel
+        try:
+            p_in = lib.fimexcu_host_alloc(n_in * 2)
+            p_out = lib.fimexcu_host_alloc(points_per_step * 2)
+            if not p_in or not p_out:
+                raise RuntimeError("pinned allocation failed: " + _lib.last_error())
+            raw = torch.randint(-30000, 30000, (n_in,), dtype=torch.int16, device="cuda")
+            _lib.check(lib.fimexcu_memcpy_d2h(p_in, raw.data_ptr(), n_in * 2), "d2h")
+            del raw
+
+            def packed_step():
+                _lib.check(lib.fimexcu_cache_apply_i16(ci._h, p_in, n_in, p_out, C.byref(new_size), -32767.0), "apply_i16")
+
+            packed_step()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                packed_step()
+            torch.cuda.synchronize()
+            dtp = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(dtp, op=dist.ReduceOp.MAX)
+            launches += (e2e_steps + 1) * chunks
+            e2e["packed_i16"] = {"value": world * points_per_step / float(dtp.item()) / 1e9, "unit": UNIT, "h2d_bytes_per_step": n_in * 2,
+                                 "d2h_bytes_per_step": points_per_step * 2, "ms_per_step": float(dtp.item()) * 1e3,
+                                 "call": "fimexcu_cache_apply_i16 (CDM_SHORT slab: raw int16 in and out, fill <-> NaN and lround fused)"}
+            lib.fimexcu_host_free(p_in)
+            lib.fimexcu_host_free(p_out)
+        except Exception as exc:
+            e2e["packed_i16"] = {"error": str(exc)[:200]}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

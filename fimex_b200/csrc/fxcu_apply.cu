@@ -24,6 +24,8 @@
 #include "fxcu_handles.h"
 
 #include <algorithm>
+#include <cstdint>
+#include <cstring>
 #include <memory>
 #include <vector>
 
@@ -257,8 +259,8 @@ struct ApplyParams {
     const int* off;
     const void* wx;
     const void* wy;
-    const float* in;
-    float* out;
+    const void* in; // f32, or i16 for the packed kernels
+    void* out;
     int outX, outY, nz, zchunk;
     int inX;       // row length the table offsets refer to (the cache's reduced window)
     int inPitch;   // elements between source rows
@@ -283,6 +285,36 @@ __device__ __forceinline__ void store_out(float* __restrict__ p, float v, float 
     if (FILL && isnan(v)) // mifi_nanf2bad, interpolation.c:1074-1082
         v = fill;
     __stcs(p, v); // written once, never re-read by this kernel: keep L2 for the source planes
+}
+
+// Packed 16-bit slabs, the way CDMInterpolator::getDataSlice treats a `short` variable (CDMInterpolator.cc:140-151): the RAW
+// values are cast to float (Data::asFloat), the variable's fill value becomes NaN (mifi_bad2nanf), and the result goes back
+// through ScaleValue<float,short>(NaN, 1, 0, fill, 1, 0) (DataUtils.h:38-60): NaN -> (short)fill, else
+// static_cast<short>(int(lround(double(v)))) (MathUtils.h:40-96) -- half away from zero, wrapping like the C casts.
+// `bad` carries float(fill) on the way in and the bit pattern of short(fill) on the way out.
+template <bool BAD>
+__device__ __forceinline__ float load_in(const short* __restrict__ p, float bad)
+{
+    float v = static_cast<float>(__ldg(p));
+    if (v == bad)
+        v = nan_f();
+    return v;
+}
+
+__device__ __forceinline__ short pack_i16(float v, float fill_bits)
+{
+    if (isnan(v))
+        return static_cast<short>(__float_as_int(fill_bits));
+    float t = truncf(v);
+    if (fabsf(__fsub_rn(v, t)) >= 0.5f) // v - trunc(v) is exact
+        t = __fadd_rn(t, copysignf(1.f, v));
+    return static_cast<short>(static_cast<int>(__float2ll_rz(t)));
+}
+
+template <bool FILL>
+__device__ __forceinline__ void store_out(short* __restrict__ p, float v, float fill_bits)
+{
+    *p = pack_i16(v, fill_bits);
 }
 
 // thread -> target cell of a 32 x 8 tile; returns false outside the grid
@@ -324,7 +356,7 @@ __device__ __forceinline__ float bilinear_value(float s00, float s01, float s10,
 // K4, direct-gather form.  One thread per target cell of a 32 x 8 tile, blockIdx.z selects a chunk of levels; the
 // table entry stays in registers for all its levels.  Used for small grids, for sources TMA cannot describe
 // (unaligned base or pitch) and for tiles whose source footprint does not fit the staged kernel's box.
-template <bool BAD, bool FILL>
+template <bool BAD, bool FILL, class T = float>
 __global__ void __launch_bounds__(256) bilinear_apply_kernel(const ApplyParams P)
 {
     int ox, oy;
@@ -335,13 +367,13 @@ __global__ void __launch_bounds__(256) bilinear_apply_kernel(const ApplyParams P
     const int z1 = min(P.nz, z0 + P.zchunk);
     const int f = P.off[o];
     const float fx = static_cast<const float*>(P.wx)[o], fy = static_cast<const float*>(P.wy)[o];
-    float* po = P.out + static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
+    T* po = static_cast<T*>(P.out) + static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
     if (f < 0) {
         for (int z = z0; z < z1; ++z, po += P.outLevel)
             store_out<FILL>(po, nan_f(), P.fill);
         return;
     }
-    const float* p = P.in + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
+    const T* p = static_cast<const T*>(P.in) + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
     const int inX = P.inPitch;
     if (fx >= 0.f && fy >= 0.f) {
         const float omx = __fsub_rn(1.f, fx), omy = __fsub_rn(1.f, fy);
@@ -374,7 +406,7 @@ __global__ void __launch_bounds__(256) bilinear_apply_kernel(const ApplyParams P
 
 // K5.  Same mapping; 16 taps, weights in f64, the four column sums added into the f32 result one at a
 // time (interpolation.c:388-406).
-template <bool BAD, bool FILL>
+template <bool BAD, bool FILL, class T = float>
 __global__ void __launch_bounds__(256) bicubic_apply_kernel(const ApplyParams P)
 {
     int ox, oy;
@@ -384,7 +416,7 @@ __global__ void __launch_bounds__(256) bicubic_apply_kernel(const ApplyParams P)
     const int z0 = blockIdx.z * P.zchunk;
     const int z1 = min(P.nz, z0 + P.zchunk);
     const int f = P.off[o];
-    float* po = P.out + static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
+    T* po = static_cast<T*>(P.out) + static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
     if (f < 0) {
         for (int z = z0; z < z1; ++z, po += P.outLevel)
             store_out<FILL>(po, nan_f(), P.fill);
@@ -393,7 +425,7 @@ __global__ void __launch_bounds__(256) bicubic_apply_kernel(const ApplyParams P)
     double wxv[4], wyv[4];
     cubic_weights(static_cast<const double*>(P.wx)[o], wxv);
     cubic_weights(static_cast<const double*>(P.wy)[o], wyv);
-    const float* p = P.in + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
+    const T* p = static_cast<const T*>(P.in) + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
     const int inX = P.inPitch;
     for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel) {
         float v[4][4];
@@ -416,7 +448,7 @@ __global__ void __launch_bounds__(256) bicubic_apply_kernel(const ApplyParams P)
 }
 
 // K6.  Pure gather.
-template <bool BAD, bool FILL>
+template <bool BAD, bool FILL, class T = float>
 __global__ void __launch_bounds__(256) nearest_apply_kernel(const ApplyParams P)
 {
     int ox, oy;
@@ -426,13 +458,13 @@ __global__ void __launch_bounds__(256) nearest_apply_kernel(const ApplyParams P)
     const int z0 = blockIdx.z * P.zchunk;
     const int z1 = min(P.nz, z0 + P.zchunk);
     const int f = P.off[o];
-    float* po = P.out + static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
+    T* po = static_cast<T*>(P.out) + static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
     if (f < 0) {
         for (int z = z0; z < z1; ++z, po += P.outLevel)
             store_out<FILL>(po, nan_f(), P.fill);
         return;
     }
-    const float* p = P.in + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
+    const T* p = static_cast<const T*>(P.in) + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
 #pragma unroll 4
     for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel)
         store_out<FILL>(po, load_in<BAD>(p, P.bad), P.fill);
@@ -571,7 +603,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
     }
     __syncthreads();
     const int bx0 = bbox[0], by0 = bbox[1], bx1 = bbox[2], by1 = bbox[3];
-    float* po = P.out + static_cast<size_t>(oy) * P.outPitch + ox;
+    float* po = static_cast<float*>(P.out) + static_cast<size_t>(oy) * P.outPitch + ox;
     if (bx1 < 0) { // nothing defined in this tile
         if (in_grid)
             for (int z = 0; z < P.nz; ++z, po += P.outLevel)
@@ -587,7 +619,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
             return;
         }
         const int dxg = fx >= 0.f ? 1 : 0, dyg = fy >= 0.f ? P.inPitch : 0;
-        const float* p = P.in + static_cast<size_t>(y0) * P.inPitch + x0;
+        const float* p = static_cast<const float*>(P.in) + static_cast<size_t>(y0) * P.inPitch + x0;
 #pragma unroll 4
         for (int z = 0; z < P.nz; ++z, p += P.inLevel, po += P.outLevel)
             store_out<FILL>(po, bilinear_value(load_in<BAD>(p, P.bad), load_in<BAD>(p + dxg, P.bad), load_in<BAD>(p + dyg, P.bad),
@@ -750,7 +782,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
     __syncthreads();
     const int bx0 = bbox[0], by0 = bbox[1], bx1 = bbox[2], by1 = bbox[3];
     const size_t obase = static_cast<size_t>(oy) * P.outPitch + ox;
-    float* pu = P.out + obase;
+    float* pu = static_cast<float*>(P.out) + obase;
     float* pv = Q.vout + obase;
     if (bx1 < 0) {
         if (in_grid)
@@ -792,7 +824,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
             return;
         }
         const int dyg = fy >= 0.f ? P.inPitch : 0;
-        const float* qu = P.in + static_cast<size_t>(y0) * P.inPitch + x0;
+        const float* qu = static_cast<const float*>(P.in) + static_cast<size_t>(y0) * P.inPitch + x0;
         const float* qv2 = Q.vin + static_cast<size_t>(y0) * P.inPitch + x0;
         for (int z = 0; z < P.nz; ++z, qu += P.inLevel, qv2 += P.inLevel, pu += P.outLevel, pv += P.outLevel) {
             float u = bilinear_value(load_in<BAD>(qu, P.bad), load_in<BAD>(qu + dxs, P.bad), load_in<BAD>(qu + dyg, P.bad),
@@ -916,7 +948,7 @@ __global__ void __launch_bounds__(256) bilinear_uv_kernel(const ApplyParams P, c
     const int f = P.off[o];
     const float fx = static_cast<const float*>(P.wx)[o], fy = static_cast<const float*>(P.wy)[o];
     const size_t obase = static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
-    float* pu = P.out + obase;
+    float* pu = static_cast<float*>(P.out) + obase;
     float* pv = Q.vout + obase;
     if (f < 0) {
         for (int z = z0; z < z1; ++z, pu += P.outLevel, pv += P.outLevel) {
@@ -934,7 +966,7 @@ __global__ void __launch_bounds__(256) bilinear_uv_kernel(const ApplyParams P, c
     const int dx = fx >= 0.f ? 1 : 0;
     const int dy = fy >= 0.f ? P.inPitch : 0;
     const size_t ibase = static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
-    const float* qu = P.in + ibase;
+    const float* qu = static_cast<const float*>(P.in) + ibase;
     const float* qv = Q.vin + ibase;
 #pragma unroll 2
     for (int z = z0; z < z1; ++z, qu += P.inLevel, qv += P.inLevel, pu += P.outLevel, pv += P.outLevel) {
@@ -1232,7 +1264,7 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
         CUtensorMap map;
         const bool enough = tiles >= static_cast<size_t>(sm_count()) * 6;
         const bool fits = c->tiles_with_data > 0 && 10ull * c->tiles_fitting >= 8ull * c->tiles_with_data;
-        if (enough && fits && make_source_map(&map, P.in, c->inX, c->inY, static_cast<size_t>(P.nz), P.inPitch, P.inLevel)) {
+        if (enough && fits && make_source_map(&map, static_cast<const float*>(P.in), c->inX, c->inY, static_cast<size_t>(P.nz), P.inPitch, P.inLevel)) {
             const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH));
             if (c->kind == KIND_NN)
                 staged_apply_tma_kernel<BAD, FILL, true><<<grid, TMA_THREADS, 0, s>>>(map, P);
@@ -1300,6 +1332,45 @@ int cache_apply_strided(const fimexcu_cache* c, const float* d_in, const Layout&
     return FIMEXCU_OK;
 }
 
+// packed 16-bit slabs (see load_in / pack_i16): direct-gather kernels on the raw values, fill <-> NaN fused on both sides
+int cache_apply_strided_i16(const fimexcu_cache* c, const short* d_in, const Layout& L, size_t nz, short* d_out, double badValue, cudaStream_t s)
+{
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply_i16: null cache");
+    if (nz == 0 || c->outX * c->outY == 0)
+        return FIMEXCU_OK;
+    if (check_layout(c, L, nz) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
+    ApplyParams P;
+    P.off = c->off.as<int>();
+    P.wx = c->wx.p;
+    P.wy = c->wy.p;
+    P.in = d_in;
+    P.out = d_out;
+    P.outX = static_cast<int>(c->outX);
+    P.outY = static_cast<int>(c->outY);
+    P.nz = static_cast<int>(nz);
+    P.inX = static_cast<int>(c->inX);
+    P.inPitch = L.inPitch;
+    P.inLevel = L.inLevel;
+    P.outPitch = L.outPitch;
+    P.outLevel = L.outLevel;
+    P.bad = static_cast<float>(badValue); // mifi_bad2nanf's float parameter (CDMInterpolator.cc:143)
+    const int fill_bits = static_cast<short>(badValue); // ScaleValue's newFill_ = static_cast<short>(newFill) (DataUtils.h:49)
+    std::memcpy(&P.fill, &fill_bits, sizeof(float));
+    const size_t tiles = static_cast<size_t>((c->outX + 31) / 32) * ((c->outY + 7) / 8);
+    P.zchunk = pick_zchunk(tiles, P.nz);
+    const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + 7) / 8),
+                    static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
+    switch (c->kind) {
+    case KIND_BILINEAR: bilinear_apply_kernel<true, true, short><<<grid, 256, 0, s>>>(P); break;
+    case KIND_BICUBIC: bicubic_apply_kernel<true, true, short><<<grid, 256, 0, s>>>(P); break;
+    default: nearest_apply_kernel<true, true, short><<<grid, 256, 0, s>>>(P); break;
+    }
+    FXCU_CUDA(cudaGetLastError());
+    return FIMEXCU_OK;
+}
+
 static Layout dense_layout(const fimexcu_cache* c)
 {
     return Layout{static_cast<int>(c->inX), c->inX * c->inY, static_cast<int>(c->outX), c->outX * c->outY};
@@ -1312,6 +1383,64 @@ static Layout padded_layout(const fimexcu_cache* c)
     const int op = static_cast<int>((c->outX + 31) & ~size_t(31));
     return Layout{ip, static_cast<size_t>(ip) * c->inY, op, static_cast<size_t>(op) * c->outY};
 }
+
+// host slab -> host slab through the device; T = float or short, `apply` = the strided device apply for that element type
+template <class T, class ApplyFn>
+static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T* out, size_t* newSize, ApplyFn apply)
+{
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply_f: null cache");
+    if (!require_device())
+        return FIMEXCU_ERROR;
+    const size_t inLayer = c->inX * c->inY, outLayer = c->outX * c->outY;
+    const size_t nz = size / inLayer; // CachedInterpolation.cc:176
+    if (newSize)
+        *newSize = nz * outLayer;
+    if (nz == 0 || outLayer == 0)
+        return FIMEXCU_OK;
+    // Levels are independent: the slab is cut into level chunks; copy-in, kernel and copy-out of neighbouring chunks
+    // run on different streams so that PCIe traffic in both directions overlaps the kernels.  This path is bound by the
+    // PCIe copies (the 767 MB result alone takes ~14 ms, the kernels 0.4 ms), so the chunks keep the dense host layout on
+    // the device: plain 1-D copies run at full DMA speed, strided 2-D copies into the padded layout measured 1.5x slower.
+    const Layout L = dense_layout(c);
+    constexpr int NS_MAX = 8;
+    static const int NS = []() { const char* e = getenv("FIMEXCU_E2E_STREAMS"); const int v = e ? atoi(e) : 3; return std::max(1, std::min(8, v)); }();
+    static const int NCHUNK = []() { const char* e = getenv("FIMEXCU_E2E_CHUNKS"); const int v = e ? atoi(e) : 8; return std::max(1, v); }();
+    const size_t chunk = std::max<size_t>(1, std::min<size_t>(nz, (nz + NCHUNK - 1) / NCHUNK));
+    cudaStream_t st[NS_MAX];
+    for (int i = 0; i < NS; ++i)
+        FXCU_CUDA(cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking));
+    int rc = FIMEXCU_OK;
+    {
+        DevBuf din[NS_MAX], dout[NS_MAX];
+        for (int i = 0; i < NS && rc == FIMEXCU_OK; ++i)
+            if (!din[i].alloc(chunk * L.inLevel * sizeof(T), st[i]) || !dout[i].alloc(chunk * L.outLevel * sizeof(T), st[i]))
+                rc = FIMEXCU_ERROR;
+        size_t k = 0;
+        for (size_t z0 = 0; z0 < nz && rc == FIMEXCU_OK; z0 += chunk, ++k) {
+            const size_t zn = std::min(chunk, nz - z0);
+            const int i = static_cast<int>(k % NS);
+            if (!cuda_ok(cudaMemcpyAsync(din[i].p, in + z0 * inLayer, zn * inLayer * sizeof(T), cudaMemcpyHostToDevice, st[i]), "H2D", __FILE__,
+                         __LINE__)) {
+                rc = FIMEXCU_ERROR;
+                break;
+            }
+            rc = apply(din[i].template as<T>(), L, zn, dout[i].template as<T>(), st[i]);
+            if (rc != FIMEXCU_OK)
+                break;
+            if (!cuda_ok(cudaMemcpyAsync(out + z0 * outLayer, dout[i].p, zn * outLayer * sizeof(T), cudaMemcpyDeviceToHost, st[i]), "D2H",
+                         __FILE__, __LINE__))
+                rc = FIMEXCU_ERROR;
+        }
+        for (int i = 0; i < NS; ++i)
+            if (!cuda_ok(cudaStreamSynchronize(st[i]), "cudaStreamSynchronize", __FILE__, __LINE__))
+                rc = FIMEXCU_ERROR;
+    }
+    for (int i = 0; i < NS; ++i)
+        cudaStreamDestroy(st[i]);
+    return rc;
+}
+
 
 } // namespace fxcu
 
@@ -1389,57 +1518,25 @@ int fimexcu_cache_apply_dev_strided_f(const fimexcu_cache* c, const float* d_in,
 int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, float* out, size_t* newSize, float badIn, float fillOut)
 {
     clear_error();
+    return cache_apply_host<float>(c, in, size, out, newSize, [&](const float* di, const Layout& L, size_t zn, float* dout, cudaStream_t st) {
+        return cache_apply_strided(c, di, L, zn, dout, badIn, fillOut, st);
+    });
+}
+
+int fimexcu_cache_apply_i16(const fimexcu_cache* c, const int16_t* in, size_t size, int16_t* out, size_t* newSize, double badValue)
+{
+    clear_error();
+    return cache_apply_host<short>(c, in, size, out, newSize, [&](const short* di, const Layout& L, size_t zn, short* dout, cudaStream_t st) {
+        return cache_apply_strided_i16(c, di, L, zn, dout, badValue, st);
+    });
+}
+
+int fimexcu_cache_apply_dev_i16(const fimexcu_cache* c, const int16_t* d_in, size_t nz, int16_t* d_out, double badValue, void* stream)
+{
+    clear_error();
     if (!c)
-        FXCU_FAIL("fimexcu_cache_apply_f: null cache");
-    if (!require_device())
-        return FIMEXCU_ERROR;
-    const size_t inLayer = c->inX * c->inY, outLayer = c->outX * c->outY;
-    const size_t nz = size / inLayer; // CachedInterpolation.cc:176
-    if (newSize)
-        *newSize = nz * outLayer;
-    if (nz == 0 || outLayer == 0)
-        return FIMEXCU_OK;
-    // Levels are independent: the slab is cut into level chunks; copy-in, kernel and copy-out of neighbouring chunks
-    // run on different streams so that PCIe traffic in both directions overlaps the kernels.  This path is bound by the
-    // PCIe copies (the 767 MB result alone takes ~14 ms, the kernels 0.4 ms), so the chunks keep the dense host layout on
-    // the device: plain 1-D copies run at full DMA speed, strided 2-D copies into the padded layout measured 1.5x slower.
-    const Layout L = dense_layout(c);
-    constexpr int NS_MAX = 8;
-    static const int NS = []() { const char* e = getenv("FIMEXCU_E2E_STREAMS"); const int v = e ? atoi(e) : 3; return std::max(1, std::min(8, v)); }();
-    static const int NCHUNK = []() { const char* e = getenv("FIMEXCU_E2E_CHUNKS"); const int v = e ? atoi(e) : 8; return std::max(1, v); }();
-    const size_t chunk = std::max<size_t>(1, std::min<size_t>(nz, (nz + NCHUNK - 1) / NCHUNK));
-    cudaStream_t st[NS_MAX];
-    for (int i = 0; i < NS; ++i)
-        FXCU_CUDA(cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking));
-    int rc = FIMEXCU_OK;
-    {
-        DevBuf din[NS_MAX], dout[NS_MAX];
-        for (int i = 0; i < NS && rc == FIMEXCU_OK; ++i)
-            if (!din[i].alloc(chunk * L.inLevel * sizeof(float), st[i]) || !dout[i].alloc(chunk * L.outLevel * sizeof(float), st[i]))
-                rc = FIMEXCU_ERROR;
-        size_t k = 0;
-        for (size_t z0 = 0; z0 < nz && rc == FIMEXCU_OK; z0 += chunk, ++k) {
-            const size_t zn = std::min(chunk, nz - z0);
-            const int i = static_cast<int>(k % NS);
-            if (!cuda_ok(cudaMemcpyAsync(din[i].p, in + z0 * inLayer, zn * inLayer * sizeof(float), cudaMemcpyHostToDevice, st[i]), "H2D", __FILE__,
-                         __LINE__)) {
-                rc = FIMEXCU_ERROR;
-                break;
-            }
-            rc = cache_apply_strided(c, din[i].as<float>(), L, zn, dout[i].as<float>(), badIn, fillOut, st[i]);
-            if (rc != FIMEXCU_OK)
-                break;
-            if (!cuda_ok(cudaMemcpyAsync(out + z0 * outLayer, dout[i].p, zn * outLayer * sizeof(float), cudaMemcpyDeviceToHost, st[i]), "D2H",
-                         __FILE__, __LINE__))
-                rc = FIMEXCU_ERROR;
-        }
-        for (int i = 0; i < NS; ++i)
-            if (!cuda_ok(cudaStreamSynchronize(st[i]), "cudaStreamSynchronize", __FILE__, __LINE__))
-                rc = FIMEXCU_ERROR;
-    }
-    for (int i = 0; i < NS; ++i)
-        cudaStreamDestroy(st[i]);
-    return rc;
+        FXCU_FAIL("fimexcu_cache_apply_dev_i16: null cache");
+    return cache_apply_strided_i16(c, d_in, dense_layout(c), nz, d_out, badValue, as_stream(stream));
 }
 
 static int cache_apply_uv_strided(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* d_u_in, const float* d_v_in, const Layout& L, size_t nz,

@@ -102,6 +102,28 @@ class CachedInterpolationInterface:
         self._apply_host(a.ctypes.data, size, out.ctypes.data, newSize, badValue, fillValue)
         return out, newSize.value
 
+    def interpolateValuesPacked(self, inData, badValue):
+        """CDMInterpolator::getDataSlice for a CDM_SHORT variable around the cached interpolation (CDMInterpolator.cc:140-151):
+        inData [nz][inY][inX] int16 RAW packed values, badValue = the variable's _FillValue; returns int16 [nz][outY][outX].
+        numpy array: host path (2 bytes per value over PCIe each way); CUDA torch int16 tensor: device path."""
+        if self._h is None:
+            raise FimexCudaError("cache was destroyed")
+        if _is_torch(inData):
+            import torch
+            if not inData.is_cuda or inData.dtype != torch.int16 or not inData.is_contiguous():
+                raise FimexCudaError("device path needs a contiguous int16 CUDA tensor")
+            nz = inData.numel() // (self.inX * self.inY)
+            out = torch.empty((nz, self.outY, self.outX), dtype=torch.int16, device=inData.device)
+            _lib.check(lib.fimexcu_cache_apply_dev_i16(self._h, inData.data_ptr(), nz, out.data_ptr(), float(badValue), _lib.current_stream_ptr()),
+                       "cache_apply_dev_i16")
+            return out
+        a = np.ascontiguousarray(inData, dtype=np.int16)
+        nz = a.size // (self.inX * self.inY)
+        out = np.empty((nz, self.outY, self.outX), dtype=np.int16)
+        newSize = C.c_size_t()
+        _lib.check(lib.fimexcu_cache_apply_i16(self._h, a.ctypes.data, a.size, out.ctypes.data, C.byref(newSize), float(badValue)), "cache_apply_i16")
+        return out
+
     def paddedLayout(self):
         """(in_row_pitch, in_level_stride, out_row_pitch, out_level_stride) in elements of the device-resident layout
         that the staged kernels like best: source rows on 32 B, target rows on 128 B (fimexcu_cache_padded_layout)."""
@@ -214,6 +236,9 @@ class CachedForwardInterpolation(CachedInterpolationInterface):
         self.inX, self.inY, self.outX, self.outY = (t.value for t in v)
         self.maxPointsInIn = mp.value
         self._reduced = ReducedInterpolationDomain(self._xDimName, self._yDimName, xm.value, ym.value) if red.value else None
+
+    def interpolateValuesPacked(self, inData, badValue):
+        raise FimexCudaError("packed slabs are not supported by the forward aggregation")
 
     def _apply_host(self, pin, size, pout, newSize, bad, fill):
         _lib.check(lib.fimexcu_forward_apply_f(self._h, pin, size, pout, C.byref(newSize), bad, fill, self.level_compat), "interpolateValues")

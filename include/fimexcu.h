@@ -21,6 +21,7 @@
 #define FIMEXCU_H
 
 #include <stddef.h>
+#include <stdint.h>
 
 #ifdef __cplusplus
 extern "C" {
@@ -120,6 +121,17 @@ int fimexcu_cache_apply_dev_strided_f(const fimexcu_cache* c, const float* d_in,
                                       float* d_out, size_t out_row_pitch, size_t out_level_stride, float badIn, float fillOut, void* stream);
 int fimexcu_cache_padded_layout(const fimexcu_cache* c, size_t* in_row_pitch, size_t* in_level_stride, size_t* out_row_pitch,
                                 size_t* out_level_stride);
+/* Packed 16-bit slabs (slab feed / sink with fused unpack and pack).  Replaces, for a CDM_SHORT variable,
+ * the whole of CDMInterpolator::getDataSlice around the cached interpolation (src/CDMInterpolator.cc:140-151, 188-260):
+ *   data2InterpolationArray   Data::asFloat() of the RAW packed values, mifi_bad2nanf(badValue)
+ *   interpolateValues         as fimexcu_cache_apply_f
+ *   interpolationArray2Data   convertDataType(NaN,1,0, CDM_SHORT, badValue,1,0) = ScaleValue<float,short>
+ *                             (include/fimex/DataUtils.h:38-60): NaN -> (short)badValue, else
+ *                             static_cast<short>(int(lround(double(v)))) (include/fimex/MathUtils.h:40-96)
+ * so only 2 bytes per value cross PCIe and HBM in either direction.  badValue = the variable's _FillValue
+ * (CDM::getFillValue), used for both sides like the reference.  Layouts as fimexcu_cache_apply_f / _dev_f with int16 elements. */
+int fimexcu_cache_apply_i16(const fimexcu_cache* c, const int16_t* in, size_t size, int16_t* out, size_t* newSize, double badValue);
+int fimexcu_cache_apply_dev_i16(const fimexcu_cache* c, const int16_t* d_in, size_t nz, int16_t* d_out, double badValue, void* stream);
 void fimexcu_cache_destroy(fimexcu_cache* c);
 
 /* Drop-in for the per-point C kernels with the reference signatures (include/fimex/interpolation.h:95-137,

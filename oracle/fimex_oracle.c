@@ -373,6 +373,45 @@ void orc_nanf2bad(float* v, size_t n, float bad)
             v[i] = bad;
 }
 
+/* src/CDMInterpolator.cc:140-145 */
+void orc_i16_to_interpolation_array(const short* in, size_t n, double badValue, float* out)
+{
+    size_t i;
+    for (i = 0; i < n; ++i)
+        out[i] = (float)in[i]; /* data_caster<float,short>: static_cast, no rounding involved */
+    orc_bad2nanf(out, n, (float)badValue); /* the double fill value narrows at the call (interpolation.h:310) */
+}
+
+/* src/CDMInterpolator.cc:147-151 */
+void orc_interpolation_array_to_i16(const float* in, size_t n, double badValue, short* out)
+{
+    /* ScaleValue<float,short>(oldFill = NaN, 1, 0, newFill = badValue, 1, 0): oldScale/newScale = 1, (oldOffset-newOffset)/newScale = 0 */
+    const short newFill = (short)badValue;
+    size_t i;
+    for (i = 0; i < n; ++i) {
+        const float v = in[i];
+        if (v != v) { /* in == NaN is never true; mifi_isnan(in) is */
+            out[i] = newFill;
+        } else {
+            const double d = 1.0 * v + 0.0;
+            const int r = (int)lround(d); /* MathUtils.h:40-43: int round(double) { return ::lround(num); } */
+            out[i] = (short)r;            /* data_rounder: static_cast<OUT>(round(in)) */
+        }
+    }
+}
+
+/* src/CDMReader.cc:177-192 + Data::asFloat() */
+void orc_i16_scaled_to_float(const short* in, size_t n, double fill, double scale, double offset, float* out)
+{
+    const short oldFill = (short)fill;
+    const double a = scale / 1.0, b = (offset - 0.0) / 1.0;
+    size_t i;
+    for (i = 0; i < n; ++i) {
+        const double d = (in[i] == oldFill) ? NAN : a * in[i] + b;
+        out[i] = (float)d;
+    }
+}
+
 /* ------------------------------------------------------------------------------------------
  * src/MathUtils.cc:30-46 -- round half away from zero, then range test.  The reference converts
  * the rounded double to size_t first (negative -> huge -> invalid, -0.0 -> 0 -> valid, NaN -> invalid

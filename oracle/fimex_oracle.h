@@ -78,6 +78,16 @@ int orc_get_values_log_f(const float* a, const float* b, float* out, size_t n, d
 int orc_get_values_log_log_f(const float* a, const float* b, float* out, size_t n, double xa, double xb, double x);               /* :534-546 */
 void orc_bad2nanf(float* v, size_t n, float bad); /* :1064-1072 */
 void orc_nanf2bad(float* v, size_t n, float bad); /* :1074-1082 */
+/* packed CDM_SHORT slabs around the interpolation, src/CDMInterpolator.cc:140-151:
+ *   orc_i16_to_interpolation_array  Data::asFloat() (data_caster<float,short>, include/fimex/MathUtils.h:60-96) + mifi_bad2nanf
+ *   orc_interpolation_array_to_i16  convertDataType(NaN,1,0,CDM_SHORT,badValue,1,0) -> ScaleValue<float,short>
+ *                                   (include/fimex/DataUtils.h:38-60, src/DataImpl.h:296-307): NaN -> (short)badValue, else
+ *                                   (short)(int)lround(1.0*v + 0.0) */
+void orc_i16_to_interpolation_array(const short* in, size_t n, double badValue, float* out);
+void orc_interpolation_array_to_i16(const float* in, size_t n, double badValue, short* out);
+/* getScaledDataSlice of a CDM_SHORT variable as the vertical converters see it (src/CDMReader.cc:177-192 ->
+ * ScaleValue<short,double>(fill, scale, offset, NaN, 1, 0), then Data::asFloat()) */
+void orc_i16_scaled_to_float(const short* in, size_t n, double fill, double scale, double offset, float* out);
 
 /* ---- src/MathUtils.cc:30-46 : RoundAndClamp ---- */
 size_t orc_round_and_clamp(double d, size_t mini, size_t maxi, size_t invalid);

@@ -4,6 +4,7 @@
 // The mifi_* C functions of src/interpolation.c are exported by the same library as they are.
 #include "CachedForwardInterpolation.h"
 #include "fimex/CachedInterpolation.h"
+#include "fimex/DataUtils.h"
 #include "fimex/FindNeighborElements.h"
 #include "fimex/MathUtils.h"
 #include "fimex/SharedArray.h"
@@ -12,6 +13,7 @@
 #include "leap_iterator.h"
 #include "nanoflann/nanoflann.hpp"
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstring>
@@ -253,6 +255,27 @@ int ref_reproject_f(int method, const char* proj_in, const float* infield, const
     } catch (...) {
         return -1;
     }
+}
+
+// The reference's own conversion templates for a CDM_SHORT variable around the interpolation, instantiated exactly as
+// CDMInterpolator.cc:140-151 / DataImpl.h:296-307 / CDMReader.cc:177-192 instantiate them (header-only code of the reference).
+void ref_i16_to_interpolation_array(const short* in, size_t n, double badValue, float* out)
+{
+    std::transform(in, in + n, out, MetNoFimex::data_caster<float, short>()); // Data::asFloat -> ArrayTypeConverter<float,short>
+    mifi_bad2nanf(out, out + n, badValue);
+}
+
+void ref_interpolation_array_to_i16(const float* in, size_t n, double badValue, short* out)
+{
+    MetNoFimex::ScaleValue<float, short> sv(MIFI_UNDEFINED_F, 1., 0., badValue, 1., 0.);
+    std::transform(in, in + n, out, sv);
+}
+
+void ref_i16_scaled_to_float(const short* in, size_t n, double fill, double scale, double offset, float* out)
+{
+    MetNoFimex::ScaleValue<short, double> sv(fill, scale, offset, MIFI_UNDEFINED_D, 1., 0.);
+    for (size_t i = 0; i < n; ++i)
+        out[i] = MetNoFimex::data_caster<float, double>()(sv(in[i]));
 }
 
 } // extern "C"

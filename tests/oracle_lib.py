@@ -85,6 +85,9 @@ def oracle():
         "orc_get_values_log_log_f": (C.c_int, two_level),
         "orc_bad2nanf": (None, [c_float_p, C.c_size_t, C.c_float]),
         "orc_nanf2bad": (None, [c_float_p, C.c_size_t, C.c_float]),
+        "orc_i16_to_interpolation_array": (None, [C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
+        "orc_interpolation_array_to_i16": (None, [c_float_p, C.c_size_t, C.c_double, C.c_void_p]),
+        "orc_i16_scaled_to_float": (None, [C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
         "orc_round_and_clamp": (C.c_size_t, [C.c_double, C.c_size_t, C.c_size_t, C.c_size_t]),
         "orc_cached_interp_create": (C.POINTER(_CachedInterp), [C.c_int, c_double_p, c_double_p] + [C.c_size_t] * 4),
         "orc_cached_interp_apply": (C.c_int, [C.POINTER(_CachedInterp), c_float_p, C.c_size_t, c_float_p]),
@@ -145,6 +148,9 @@ def ref(omp=False):
         "ref_cache_apply_seconds": (C.c_double, [C.c_void_p, c_float_p, C.c_size_t, C.c_int]),
         "ref_cache_destroy": (None, [C.c_void_p]),
         "ref_round_and_clamp": (C.c_size_t, [C.c_double, C.c_size_t, C.c_size_t, C.c_size_t]),
+        "ref_i16_to_interpolation_array": (None, [C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
+        "ref_interpolation_array_to_i16": (None, [c_float_p, C.c_size_t, C.c_double, C.c_void_p]),
+        "ref_i16_scaled_to_float": (None, [C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
         "ref_find_closest_neighbor_distinct_elements": (None, [c_float_p, C.c_size_t, C.c_long, C.c_double, C.POINTER(C.c_long), C.POINTER(C.c_long)]),
         "ref_find_closest_distinct_elements": (None, [c_float_p, C.c_size_t, C.c_long, C.c_double, C.POINTER(C.c_long), C.POINTER(C.c_long)]),
         "ref_kdtree_translate": (C.c_int, [C.c_double, c_double_p, c_double_p, C.c_size_t, c_double_p, c_double_p, C.c_size_t, C.c_size_t]),
@@ -233,3 +239,16 @@ def r_cached_apply(method, px, py, in_x, in_y, out_x, out_y, field, omp=False):
     lib.ref_cache_destroy(h)
     assert rc == 0
     return out, info
+
+
+def o_packed_apply(method, px, py, inX, inY, outX, outY, raw, badValue):
+    """CDMInterpolator::getDataSlice for a CDM_SHORT variable with the oracle: raw int16 [nz][inY][inX] -> int16 [nz][outY][outX]"""
+    o = oracle()
+    raw = np.ascontiguousarray(raw, dtype=np.int16)
+    f = np.empty(raw.shape, np.float32)
+    o.orc_i16_to_interpolation_array(raw.ctypes.data, raw.size, float(badValue), fp(f))
+    res, _ = o_cached_apply(method, px, py, inX, inY, outX, outY, f)
+    res = np.ascontiguousarray(res, dtype=np.float32)
+    out = np.empty(res.shape, np.int16)
+    o.orc_interpolation_array_to_i16(fp(res), res.size, float(badValue), out.ctypes.data)
+    return out

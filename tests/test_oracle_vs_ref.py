@@ -204,3 +204,35 @@ def test_reproject_matrix_restatement_matches_reference_logic(oracle, ref):
     oracle.orc_reproject_axes(ll, lcc, dp(lon), dp(lat), lon.size, lat.size, dp(ox_), dp(oy_))
     ref.ref_reproject_axes(ll, lcc, dp(lon), dp(lat), lon.size, lat.size, dp(rx_), dp(ry_))
     assert _eq(ox_, rx_) and _eq(oy_, ry_)
+
+
+def test_packed_short_conversions_match_reference(oracle, ref):
+    """the conversions CDMInterpolator::getDataSlice wraps around the interpolation for a CDM_SHORT variable, and the scaled read of
+    the vertical converters: the restatement against the reference's own header templates (ScaleValue, data_caster)"""
+    rng = np.random.default_rng(5)
+    n = 200000
+    for bad in (-32767.0, 9999.0, 1.0e10, -32768.0):
+        raw = rng.integers(-32768, 32768, n).astype(np.int16)
+        raw[::17] = np.int16(bad) if abs(bad) < 32768 else 123
+        a, b = np.empty(n, np.float32), np.empty(n, np.float32)
+        oracle.orc_i16_to_interpolation_array(raw.ctypes.data, n, bad, fp(a))
+        ref.ref_i16_to_interpolation_array(raw.ctypes.data, n, bad, fp(b))
+        assert np.array_equal(a, b, equal_nan=True)
+        v = rng.uniform(-40000, 40000, n).astype(np.float32)
+        v[:5000] = np.round(v[:5000]) + np.float32(0.5)           # ties: half away from zero
+        v[5000:6000] = np.float32(0.49999997) * rng.choice([-1, 1], 1000)
+        v[6000:7000] = rng.uniform(-3e9, 3e9, 1000).astype(np.float32)  # beyond short and int: the C casts wrap
+        v[7000:8000] = np.nan
+        v[8000] = -0.0
+        c, d = np.empty(n, np.int16), np.empty(n, np.int16)
+        oracle.orc_interpolation_array_to_i16(fp(v), n, bad, c.ctypes.data)
+        ref.ref_interpolation_array_to_i16(fp(v), n, bad, d.ctypes.data)
+        assert np.array_equal(c, d)
+    for fill, scale, offset in ((-32767.0, 0.01, 273.15), (9999.0, 1.0, 0.0), (-32768.0, 1e-3, -5.0)):
+        raw = rng.integers(-32768, 32768, n).astype(np.int16)
+        raw[::13] = np.int16(fill)
+        a, b = np.empty(n, np.float32), np.empty(n, np.float32)
+        oracle.orc_i16_scaled_to_float(raw.ctypes.data, n, fill, scale, offset, fp(a))
+        ref.ref_i16_scaled_to_float(raw.ctypes.data, n, fill, scale, offset, fp(b))
+        assert np.array_equal(a, b, equal_nan=True)
+        assert np.isnan(a[::13]).all()
