@@ -288,6 +288,21 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
                                                      "configs[4]: 6 members x 65 levels S->T2 (7.13 B/pt) + ps, then 65->12 pressure levels (linear); points = final output values")
     c2.close()
     del f_in, ps_in, f_out, ps_out
+    # vertical coordinate converters (8(f) rank 2): hypsometric integration to altitude, 65 levels, with humidity
+    ncol_v = 6 * 801 * 561
+    p_f = (torch.linspace(0.998, 0.01, 65, device="cuda")[None, :, None] * (950.0 + 60.0 * torch.rand((1, 1, ncol_v), device="cuda"))).contiguous()
+    sap_f = (p_f[:, 0, :] / 0.998).contiguous()
+    sgp_f = 20000.0 * torch.rand((1, ncol_v), device="cuda")
+    t_f = 220.0 + 80.0 * torch.rand((1, 65, ncol_v), device="cuda")
+    q_f = 0.02 * torch.rand((1, 65, ncol_v), device="cuda")
+    ms = timed(lambda: V.pressureIntegrationAltitude(p_f, sap_f, sgp_f, t_f, q_f, start_high_p=1), reps=5)
+    out["vcoord_pressure_integration_altitude"] = entry(ms, (8.0 + 4.0 * 65 * 4) * ncol_v, 65 * ncol_v,
+                                                        "hypsometric integration, 65 levels, p + T + q read, altitude written: 1048 B per column")
+    lev_ms = timed(lambda: V.verticalLevelField(V.VCOORD_HYBRID_SIGMA_AP, ap, b, 0.0, sap_f, surface_scale=1.0, post=V.VPOST_STANDARD_ALTITUDE,
+                                                topography=sgp_f[0], topography_factor=-1.0 / 9.80665), reps=5)
+    out["vcoord_hybrid_pressure_to_height_field"] = entry(lev_ms, (8.0 + 4.0 * 65) * ncol_v, 65 * ncol_v,
+                                                          "hybrid pressure -> standard altitude -> minus topography, one pass, 65 levels: 268 B per column")
+    del p_f, sap_f, sgp_f, t_f, q_f
     # K12: forward mean, 2030x1354 swath -> 1000x1000 cells, 8 levels (level_compat off: every level aggregated)
     gx, gy = np.meshgrid(np.arange(1354), np.arange(2030))
     fwd = I.CachedForwardInterpolation("x", "y", 6, (gx * (1000 / 1354.0)).ravel() - 0.3, (gy * (1000 / 2030.0)).ravel() - 0.3, 1354, 2030, 1000, 1000,

@@ -114,3 +114,71 @@ def mifi_get_values_log_f(A, B, a, b, x):
 
 def mifi_get_values_log_log_f(A, B, a, b, x):
     return _two_level(lib.fimexcu_get_values_log_log_f, A, B, a, b, x)
+
+
+# ---- vertical coordinate converters (device-resident; src/coordSys/verticalTransform/*) ----
+VCOORD_HYBRID_SIGMA_AP, VCOORD_HYBRID_SIGMA, VCOORD_SIGMA, VCOORD_LN_PRESSURE, VCOORD_HYBRID_HEIGHT, VCOORD_OCEAN_S_G1, VCOORD_OCEAN_S_G2 = range(7)
+VPOST_NONE, VPOST_STANDARD_ALTITUDE, VPOST_STANDARD_PRESSURE = range(3)
+
+
+def _dev(a):
+    """numpy -> CUDA tensor (the converters only exist on the device: there is no CPU path)"""
+    import torch
+    if a is None:
+        return None
+    if _is_torch(a):
+        if not a.is_cuda or a.dtype != torch.float32 or not a.is_contiguous():
+            raise _lib.FimexCudaError("needs a contiguous float32 CUDA tensor")
+        return a
+    return torch.from_numpy(_f32(a)).cuda()
+
+
+def _dptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def verticalLevelField(kind, a, b, scalar, surface, nz=None, surface_scale=1.0, eta=None, post=VPOST_NONE, topography=None, topography_factor=0.0,
+                       nOuter=None, nInner=None):
+    """The converter chain  level formula -> standard-atmosphere step -> +- topography  as one device pass.
+    a, b: per-level terms (f64, host); surface: [nOuterS][nInner] f32 (ps / orography / depth) or None for ln_pressure (then give
+    nOuter, nInner); returns a CUDA tensor [nOuter][nz][nInner] f32 that can be passed as verticalIn / verticalOut."""
+    import torch
+    av, bv = _opt(a, np.float64), _opt(b, np.float64)
+    nz = av.size if nz is None else nz
+    s, e, t = _dev(surface), _dev(eta), _dev(topography)
+    if s is not None:
+        s = s.reshape(-1, s.shape[-1])
+        nOuterS, nI = s.shape
+        nO = nOuterS if nOuter is None else nOuter
+    else:
+        nOuterS, nO, nI = 1, nOuter, nInner
+    out = torch.empty((nO, nz, nI), dtype=torch.float32, device="cuda")
+    _lib.check(lib.fimexcu_vcoord_levels_dev_f(kind, av.ctypes.data, _ptr(bv), float(scalar), _dptr(s), nOuterS, float(surface_scale), _dptr(e), post,
+                                               _dptr(t), float(topography_factor), nO, nz, nI, out.data_ptr(), _lib.current_stream_ptr()),
+               "verticalLevelField")
+    return out
+
+
+def verticalStandardAtmosphere(post, field):
+    """pressure [hPa] -> standard altitude or altitude [m] -> standard pressure on a device field"""
+    import torch
+    f = _dev(field)
+    out = torch.empty_like(f)
+    _lib.check(lib.fimexcu_vcoord_transform_dev_f(post, f.data_ptr(), f.numel(), out.data_ptr(), _lib.current_stream_ptr()), "verticalStandardAtmosphere")
+    return out
+
+
+def pressureIntegrationAltitude(pressure, surfacePressure, surfaceGeopotential, airTemperature, specificHumidity=None, sap_scale=1.0, sgp_scale=1.0,
+                                start_high_p=-1, topography=None, topography_factor=0.0):
+    """PressureIntegrationToAltitudeConverter::getDataSlice on the device: pressure / airTemperature / specificHumidity
+    [nOuter][nz][nInner] f32, surface fields [nOuterS][nInner]; returns the altitude of every level (CUDA tensor)."""
+    import torch
+    p, T, q = _dev(pressure), _dev(airTemperature), _dev(specificHumidity)
+    sap, sgp, t = _dev(surfacePressure), _dev(surfaceGeopotential), _dev(topography)
+    nO, nz, nI = p.shape
+    sap, sgp = sap.reshape(-1, nI), sgp.reshape(-1, nI)
+    out = torch.empty_like(p)
+    _lib.check(lib.fimexcu_vcoord_pressure_integration_dev_f(p.data_ptr(), sap.data_ptr(), float(sap_scale), sgp.data_ptr(), float(sgp_scale), T.data_ptr(),
+                                                             _dptr(q), nO, sap.shape[0], nz, nI, int(start_high_p), _dptr(t), float(topography_factor),
+                                                             out.data_ptr(), _lib.current_stream_ptr()), "pressureIntegrationAltitude")
+    return out

@@ -291,6 +291,45 @@ int fimexcu_get_values_linear_const_extrapol_f(const float* infieldA, const floa
 int fimexcu_get_values_log_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
 int fimexcu_get_values_log_log_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
 
+/* ---- vertical coordinate converters -----------------------------------------------------------------------
+ * The fields CDMVerticalInterpolator asks its ToVLevelConverter / VerticalConverter chain for (src/CDMVerticalInterpolator.cc:
+ * 380-470), produced on the device so that they feed fimexcu_vertical_interpolate_dev_f as d_vcoord_in / d_vcoord_out without
+ * leaving HBM.  The reference's converters hand doubles to one another and the interpolator narrows the last array with
+ * Data::asFloat(); here a chain  level formula -> standard-atmosphere step -> +- topography  is ONE pass in f64 with one f32 store.
+ * Fields: f32 [nOuter][nz][nInner]; surface fields f32 [nOuterS][nInner], nOuterS = 1 or nOuter; topography f32 [nInner]. */
+enum fimexcu_vcoord_kind {
+    FIMEXCU_VCOORD_HYBRID_SIGMA_AP = 0, /* p = ap + b*ps          mifi_atmosphere_hybrid_sigma_ap_pressure (vertical_coordinate_transformations.c:64-70), HybridSigmaApToPressureConverter.cc:71-100 */
+    FIMEXCU_VCOORD_HYBRID_SIGMA = 1,    /* p = a*p0 + b*ps        mifi_atmosphere_hybrid_sigma_pressure (:56-62), HybridSigmaToPressureConverter.cc:65-90; scalar = p0 */
+    FIMEXCU_VCOORD_SIGMA = 2,           /* p = ptop + sigma*(ps - ptop)  mifi_atmosphere_sigma_pressure (:37-44), SigmaToPressureConverter.cc:50-72; a = sigma, scalar = ptop */
+    FIMEXCU_VCOORD_LN_PRESSURE = 3,     /* p = p0*exp(-lev)       mifi_atmosphere_ln_pressure (:29-35), LnPressureToPressureConverter.cc:50-72; a = lev, scalar = p0, no surface field */
+    FIMEXCU_VCOORD_HYBRID_HEIGHT = 4,   /* h = a + b*orog         mifi_atmosphere_hybrid_height (:72-78) */
+    FIMEXCU_VCOORD_OCEAN_S_G1 = 5,      /* depth = -z, mifi_ocean_s_g1_z (:166-174), OceanSCoordinateGToDepthConverter.cc:64-107; a = s, b = C, scalar = depth_c, surf = depth, eta optional */
+    FIMEXCU_VCOORD_OCEAN_S_G2 = 6       /* depth = -z, mifi_ocean_s_g2_z (:175-183) */
+};
+enum fimexcu_vcoord_post {
+    FIMEXCU_VPOST_NONE = 0,
+    FIMEXCU_VPOST_STANDARD_ALTITUDE = 1, /* pressure [hPa] -> altitude: mifi_barometric_standard_altitude (:110-113), PressureToStandardAltitudeConverter.cc:62-71 */
+    FIMEXCU_VPOST_STANDARD_PRESSURE = 2  /* altitude [m] -> pressure: mifi_barometric_standard_pressure (:95-99), AltitudeStandardToPressureConverter.cc:62-71 */
+};
+/* a_host, b_host: the per-level terms [nz] (HOST); d_surf is multiplied by surf_scale in f64 (the linear unit conversion of
+ * getScaledDataSliceInUnit, e.g. Pa -> hPa); d_topo / topo_factor: AltitudeHeightConverter::getDataSlice
+ * (AltitudeHeightConverter.cc:110-131): value + topo_factor*topo with topo_factor = +-1 (surface altitude) or +-1/g (geopotential);
+ * NULL = no such step. */
+int fimexcu_vcoord_levels_dev_f(int kind, const double* a_host, const double* b_host, double scalar, const float* d_surf, size_t nOuterS,
+                                double surf_scale, const float* d_eta, int post, const float* d_topo, double topo_factor, size_t nOuter, size_t nz,
+                                size_t nInner, float* d_out, void* stream);
+/* the standard-atmosphere step alone on a device field (when the converter's input is a data variable) */
+int fimexcu_vcoord_transform_dev_f(int post, const float* d_in, size_t n, float* d_out, void* stream);
+/* Replaces PressureIntegrationToAltitudeConverter::getDataSlice (PressureIntegrationToAltitudeConverter.cc:114-247): hypsometric
+ * integration from the surface upwards, a += mifi_barometric_layer_thickness(p_low, p_high, Tv) with
+ * Tv = mifi_virtual_temperature(q, T) when d_shum is given (vertical_coordinate_transformations.c:115-118, 161-164).
+ * d_p [hPa], d_airt [K], d_shum [1] are [nOuter][nz][nInner]; d_sap*sap_scale [hPa] and d_sgp*sgp_scale [m^2/s^2] are surface
+ * fields.  start_high_p: 1 = level 0 is the lowest level, 0 = the last level is, -1 = decide like the reference from the first
+ * column whose first and last pressure are positive (error if there is none).  d_topo / topo_factor as above. */
+int fimexcu_vcoord_pressure_integration_dev_f(const float* d_p, const float* d_sap, double sap_scale, const float* d_sgp, double sgp_scale,
+                                              const float* d_airt, const float* d_shum, size_t nOuter, size_t nOuterS, size_t nz, size_t nInner,
+                                              int start_high_p, const float* d_topo, double topo_factor, float* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

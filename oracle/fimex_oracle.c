@@ -1072,3 +1072,122 @@ int orc_coordnn_translate(double* px, double* py, size_t nPoints, const double* 
     free(ll);
     return ORC_OK;
 }
+
+/* ---- vertical coordinate converters ---------------------------------------------------------------------------------------- */
+#define ORC_GAS_CONSTANT 8.31432        /* mifi_constants.h:241 */
+#define ORC_EARTH_GRAVITY 9.80665       /* :235 */
+#define ORC_MOLAR_MASS_DRY_AIR 0.0289644 /* :238 */
+static const double ORC_BAROMETRIC_FACTOR = ORC_GAS_CONSTANT / (ORC_EARTH_GRAVITY * ORC_MOLAR_MASS_DRY_AIR); /* v_c_t.c:80-81 */
+static const double ORC_Z_MOL_WEIGHT_RATIO = .60771704180064308681;                                          /* :84 */
+
+float orc_virtual_temperature(float spec_humidity, float T) { return (1 + ORC_Z_MOL_WEIGHT_RATIO * spec_humidity) * T; }
+
+float orc_barometric_layer_thickness(float p_low_alti, float p_high_alti, float T)
+{
+    return log(p_low_alti / p_high_alti) * T * ORC_BAROMETRIC_FACTOR;
+}
+
+static double orc_vpost(int post, double v)
+{
+    if (post == ORC_VPOST_STANDARD_ALTITUDE) { /* mifi_barometric_height(n, 1013.25, p, 288.15, .), :101-113 */
+        const double K = -ORC_BAROMETRIC_FACTOR * 288.15;
+        return K * log(v / 1013.25);
+    }
+    if (post == ORC_VPOST_STANDARD_PRESSURE) { /* mifi_barometric_pressure(n, 1013.25, h, 288.15, .), :86-99 */
+        const double Cc = -1 / (ORC_BAROMETRIC_FACTOR * 288.15);
+        return 1013.25 * exp(Cc * v);
+    }
+    return v;
+}
+
+int orc_vcoord_levels_f(int kind, const double* a, const double* b, double scalar, const float* surf, size_t nOuterS, double surf_scale,
+                        const float* eta, int post, const float* topo, double topo_factor, size_t nOuter, size_t nz, size_t nInner, float* out)
+{
+    size_t o, k, i;
+    if (kind < 0 || kind > ORC_VCOORD_OCEAN_S_G2 || !(nOuterS == 1 || nOuterS == nOuter))
+        return 0;
+    for (o = 0; o < nOuter; ++o)
+        for (k = 0; k < nz; ++k)
+            for (i = 0; i < nInner; ++i) {
+                const size_t si = (nOuterS == 1 ? 0 : o) * nInner + i;
+                const double s = surf ? surf_scale * surf[si] : 0.; /* ScaleValue: oldScale * in (+ 0), DataUtils.h:57 */
+                double v;
+                switch (kind) {
+                case ORC_VCOORD_HYBRID_SIGMA_AP: v = a[k] + (b[k] * s); break;            /* v_c_t.c:64-70 */
+                case ORC_VCOORD_HYBRID_SIGMA: v = (a[k] * scalar) + (b[k] * s); break;   /* :56-62 */
+                case ORC_VCOORD_SIGMA: { const double pDiff = (s - scalar); v = scalar + a[k] * pDiff; break; } /* :37-44 */
+                case ORC_VCOORD_LN_PRESSURE: v = scalar * exp(-a[k]); break;              /* :29-35 */
+                case ORC_VCOORD_HYBRID_HEIGHT: v = a[k] + (b[k] * s); break;              /* :72-78 */
+                case ORC_VCOORD_OCEAN_S_G1: {                                            /* :166-174 */
+                    const double zeta = eta ? (double)eta[si] : 0., h_inv = 1 / s;
+                    const double S = scalar * a[k] + (s - scalar) * b[k];
+                    v = -(S + zeta * (1 + S * h_inv)); /* positive down, OceanSCoordinateGToDepthConverter.cc:100-101 */
+                    break;
+                }
+                default: {                                                               /* :175-183 */
+                    const double zeta = eta ? (double)eta[si] : 0., hph_c_inv = 1 / (s + scalar);
+                    const double S = hph_c_inv * (scalar * a[k] + s * b[k]);
+                    v = -(zeta + (zeta + s) * S);
+                    break;
+                }
+                }
+                v = orc_vpost(post, v);
+                if (topo)
+                    v = v + topo_factor * topo[i]; /* AltitudeHeightConverter.cc:125-127 */
+                out[(o * nz + k) * nInner + i] = (float)v;
+            }
+    return 1;
+}
+
+void orc_vcoord_transform_f(int post, const float* in, size_t n, float* out)
+{
+    size_t i;
+    for (i = 0; i < n; ++i)
+        out[i] = (float)orc_vpost(post, (double)in[i]);
+}
+
+int orc_vcoord_pressure_integration_f(const float* p, const float* sap, double sap_scale, const float* sgp, double sgp_scale, const float* airt,
+                                      const float* shum, size_t nOuter, size_t nOuterS, size_t nz, size_t nInner, int start_high_p,
+                                      const float* topo, double topo_factor, float* out)
+{
+    size_t o, i, n;
+    if (!(nOuterS == 1 || nOuterS == nOuter) || nz == 0)
+        return 0;
+    if (start_high_p < 0) { /* PressureIntegrationToAltitudeConverter.cc:141-164: first column with positive ends decides */
+        int have = 0;
+        for (o = 0; o < nOuter && !have; ++o)
+            for (i = 0; i < nInner && !have; ++i) {
+                const float p_first = p[(o * nz) * nInner + i], p_last = p[(o * nz + nz - 1) * nInner + i];
+                if (p_first > 0 && p_last > 0) {
+                    start_high_p = (p_first > p_last);
+                    have = 1;
+                }
+            }
+        if (!have)
+            return 0;
+    }
+    for (o = 0; o < nOuter; ++o)
+        for (i = 0; i < nInner; ++i) { /* :225-246 */
+            const size_t si = (nOuterS == 1 ? 0 : o) * nInner + i;
+            const float sgp_v = (float)(sgp_scale * sgp[si]), sap_v = (float)(sap_scale * sap[si]); /* VarFloat: asFloat of the scaled double */
+            double a = sgp_v / ORC_EARTH_GRAVITY;
+            float p_low_alti = sap_v;
+            for (n = 0; n < nz; ++n) {
+                const size_t iz = start_high_p ? n : nz - 1 - n;
+                const size_t idx = (o * nz + iz) * nInner + i;
+                const float p_high_alti = p[idx];
+                float Tv = airt[idx];
+                double lt, v;
+                if (shum)
+                    Tv = orc_virtual_temperature(shum[idx], Tv);
+                lt = orc_barometric_layer_thickness(p_low_alti, p_high_alti, Tv);
+                a += lt;
+                v = a;
+                if (topo)
+                    v = v + topo_factor * topo[i];
+                out[idx] = (float)v;
+                p_low_alti = p_high_alti;
+            }
+        }
+    return 1;
+}

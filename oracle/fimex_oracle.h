@@ -179,3 +179,30 @@ int orc_coordnn_translate(double* pointsOnX_deg, double* pointsOnY_deg, size_t n
 }
 #endif
 #endif
+
+/* ---- vertical coordinate converters -------------------------------------------------------------------
+ * Restated from src/vertical_coordinate_transformations.c:29-183 and the converter classes under
+ * src/coordSys/verticalTransform/ (HybridSigmaApToPressureConverter.cc:71-100, HybridSigmaToPressureConverter.cc:65-90,
+ * SigmaToPressureConverter.cc:50-72, LnPressureToPressureConverter.cc:50-72, AtmosphereHybridHeight / mifi_atmosphere_hybrid_height,
+ * OceanSCoordinateGToDepthConverter.cc:64-107, PressureToStandardAltitudeConverter.cc:62-71,
+ * AltitudeStandardToPressureConverter.cc:62-71, AltitudeHeightConverter.cc:110-131,
+ * PressureIntegrationToAltitudeConverter.cc:114-247).  The converters hand DOUBLES to one another; the vertical interpolator
+ * narrows the final field with Data::asFloat() (CDMVerticalInterpolator.cc:483).  Fields: [nOuter][nz][nInner], surface fields
+ * [nOuterS][nInner] with nOuterS = 1 or nOuter. */
+enum { ORC_VCOORD_HYBRID_SIGMA_AP = 0, ORC_VCOORD_HYBRID_SIGMA = 1, ORC_VCOORD_SIGMA = 2, ORC_VCOORD_LN_PRESSURE = 3,
+       ORC_VCOORD_HYBRID_HEIGHT = 4, ORC_VCOORD_OCEAN_S_G1 = 5, ORC_VCOORD_OCEAN_S_G2 = 6 };
+enum { ORC_VPOST_NONE = 0, ORC_VPOST_STANDARD_ALTITUDE = 1, ORC_VPOST_STANDARD_PRESSURE = 2 };
+/* a, b: per-level terms (ap|a|sigma|lev|a|s and b|b|-|-|b|C); scalar: p0 | ptop | depth_c; surf: ps | orog | depth (scaled by
+ * surf_scale in double, like getScaledDataSliceInUnit); eta: ocean zeta or NULL; post: standard-atmosphere step on the double;
+ * topo: AltitudeHeightConverter's term (NULL = none), added as topo_factor * topo in double */
+int orc_vcoord_levels_f(int kind, const double* a, const double* b, double scalar, const float* surf, size_t nOuterS, double surf_scale,
+                        const float* eta, int post, const float* topo, double topo_factor, size_t nOuter, size_t nz, size_t nInner, float* out);
+/* hypsometric integration from the surface upwards; start_high_p: 1 level 0 is the lowest, 0 the last level is, -1 decide
+ * like the reference from the first column whose first and last pressure are positive (returns 0 if there is none) */
+int orc_vcoord_pressure_integration_f(const float* p, const float* sap, double sap_scale, const float* sgp, double sgp_scale, const float* airt,
+                                      const float* shum, size_t nOuter, size_t nOuterS, size_t nz, size_t nInner, int start_high_p,
+                                      const float* topo, double topo_factor, float* out);
+/* stand-alone standard-atmosphere step on a field (f32 in, double arithmetic, f32 out) */
+void orc_vcoord_transform_f(int post, const float* in, size_t n, float* out);
+float orc_virtual_temperature(float spec_humidity, float T);                       /* vertical_coordinate_transformations.c:115-118 */
+float orc_barometric_layer_thickness(float p_low_alti, float p_high_alti, float T); /* :161-164 */

@@ -85,6 +85,13 @@ def oracle():
         "orc_get_values_log_log_f": (C.c_int, two_level),
         "orc_bad2nanf": (None, [c_float_p, C.c_size_t, C.c_float]),
         "orc_nanf2bad": (None, [c_float_p, C.c_size_t, C.c_float]),
+        "orc_vcoord_levels_f": (C.c_int, [C.c_int, c_double_p, c_double_p, C.c_double, c_float_p, C.c_size_t, C.c_double, c_float_p, C.c_int, c_float_p,
+                                         C.c_double, C.c_size_t, C.c_size_t, C.c_size_t, c_float_p]),
+        "orc_vcoord_pressure_integration_f": (C.c_int, [c_float_p, c_float_p, C.c_double, c_float_p, C.c_double, c_float_p, c_float_p, C.c_size_t,
+                                                       C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, c_float_p, C.c_double, c_float_p]),
+        "orc_vcoord_transform_f": (None, [C.c_int, c_float_p, C.c_size_t, c_float_p]),
+        "orc_virtual_temperature": (C.c_float, [C.c_float, C.c_float]),
+        "orc_barometric_layer_thickness": (C.c_float, [C.c_float, C.c_float, C.c_float]),
         "orc_i16_to_interpolation_array": (None, [C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
         "orc_interpolation_array_to_i16": (None, [c_float_p, C.c_size_t, C.c_double, C.c_void_p]),
         "orc_i16_scaled_to_float": (None, [C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
@@ -174,6 +181,16 @@ def ref(omp=False):
         "mifi_get_values_log_log_f": (C.c_int, two_level),
         "mifi_string_to_interpolation_method": (C.c_int, [C.c_char_p]),
         "mifi_atmosphere_hybrid_sigma_ap_pressure": (C.c_int, [C.c_size_t, C.c_double, c_double_p, c_double_p, c_double_p]),
+        "mifi_atmosphere_hybrid_sigma_pressure": (C.c_int, [C.c_size_t, C.c_double, C.c_double, c_double_p, c_double_p, c_double_p]),
+        "mifi_atmosphere_sigma_pressure": (C.c_int, [C.c_size_t, C.c_double, C.c_double, c_double_p, c_double_p]),
+        "mifi_atmosphere_ln_pressure": (C.c_int, [C.c_size_t, C.c_double, c_double_p, c_double_p]),
+        "mifi_atmosphere_hybrid_height": (C.c_int, [C.c_size_t, C.c_double, c_double_p, c_double_p, c_double_p]),
+        "mifi_ocean_s_g1_z": (C.c_int, [C.c_size_t, C.c_double, C.c_double, C.c_double, c_double_p, c_double_p, c_double_p]),
+        "mifi_ocean_s_g2_z": (C.c_int, [C.c_size_t, C.c_double, C.c_double, C.c_double, c_double_p, c_double_p, c_double_p]),
+        "mifi_barometric_standard_altitude": (C.c_int, [C.c_size_t, c_double_p, c_double_p]),
+        "mifi_barometric_standard_pressure": (C.c_int, [C.c_size_t, c_double_p, c_double_p]),
+        "mifi_virtual_temperature": (C.c_float, [C.c_float, C.c_float]),
+        "mifi_barometric_layer_thickness": (C.c_float, [C.c_float, C.c_float, C.c_float]),
     }
     for name, (res, args) in sig.items():
         f = getattr(lib, name)

@@ -236,3 +236,100 @@ def test_packed_short_conversions_match_reference(oracle, ref):
         ref.ref_i16_scaled_to_float(raw.ctypes.data, n, fill, scale, offset, fp(b))
         assert np.array_equal(a, b, equal_nan=True)
         assert np.isnan(a[::13]).all()
+
+
+def _fpn(a):
+    return None if a is None else fp(a)
+
+
+def test_vertical_converters_match_reference_functions(oracle, ref):
+    """the converter restatement against the reference's own C functions (src/vertical_coordinate_transformations.c, compiled
+    into oracle/_ref), composed per column the way the converter classes call them"""
+    rng = np.random.default_rng(8)
+    nz, nI = 23, 57
+    a = np.sort(rng.uniform(0, 300, nz))
+    b = np.sort(rng.uniform(0, 1, nz))
+    ps = rng.uniform(60000, 104000, (2, nI)).astype(np.float32)
+    orog = rng.uniform(0, 2500, (1, nI)).astype(np.float32)
+    depth = rng.uniform(5, 4000, (1, nI)).astype(np.float32)
+    eta = rng.normal(0, 0.5, (1, nI)).astype(np.float32)
+    topo = rng.uniform(0, 2000, nI).astype(np.float32)
+    sC = -np.sort(rng.uniform(0, 1, nz))[::-1].copy()
+    cases = [
+        (ol_k.HYBRID_SIGMA_AP, a, b, 0.0, ps, 0.01, None, lambda s, z: _call(ref.mifi_atmosphere_hybrid_sigma_ap_pressure, nz, s, a, b)),
+        (ol_k.HYBRID_SIGMA, a / 1000, b, 1000.0, ps, 0.01, None, lambda s, z: _call(ref.mifi_atmosphere_hybrid_sigma_pressure, nz, 1000.0, s, a / 1000, b)),
+        (ol_k.SIGMA, b, None, 10.0, ps, 0.01, None, lambda s, z: _call(ref.mifi_atmosphere_sigma_pressure, nz, 10.0, s, b)),
+        (ol_k.LN_PRESSURE, a / 50, None, 1000.0, None, 1.0, None, lambda s, z: _call(ref.mifi_atmosphere_ln_pressure, nz, 1000.0, a / 50)),
+        (ol_k.HYBRID_HEIGHT, a * 100, b, 0.0, orog, 1.0, None, lambda s, z: _call(ref.mifi_atmosphere_hybrid_height, nz, s, a * 100, b)),
+        (ol_k.OCEAN_S_G1, sC, sC * 0.7, 10.0, depth, 1.0, eta, lambda s, z: -_call(ref.mifi_ocean_s_g1_z, nz, s, 10.0, z, sC, sC * 0.7)),
+        (ol_k.OCEAN_S_G2, sC, sC * 0.7, 10.0, depth, 1.0, eta, lambda s, z: -_call(ref.mifi_ocean_s_g2_z, nz, s, 10.0, z, sC, sC * 0.7)),
+    ]
+    for kind, ka, kb, scalar, surf, scale, e, column in cases:
+        for post, factor, tp in ((0, 0.0, None), (1, -1.0, topo), (2, 1.0 / 9.80665, topo)):
+            nO = 2 if surf is ps else 1
+            out = np.empty((nO, nz, nI), np.float32)
+            kbb = ka if kb is None else kb
+            rc = oracle.orc_vcoord_levels_f(kind, dp(np.ascontiguousarray(ka)), dp(np.ascontiguousarray(kbb)), scalar, _fpn(surf), nO if surf is not None else 1,
+                                            scale, _fpn(e), post, _fpn(tp), factor, nO, nz, nI, fp(out))
+            assert rc == 1
+            want = np.empty((nO, nz, nI), np.float64)
+            for o in range(nO):
+                for i in range(nI):
+                    s = scale * float(surf[o, i]) if surf is not None else 0.0
+                    col = column(s, float(e[0, i]) if e is not None else 0.0)
+                    if post == 1:
+                        col = _call(ref.mifi_barometric_standard_altitude, nz, col)
+                    elif post == 2:
+                        col = _call(ref.mifi_barometric_standard_pressure, nz, col)
+                    if tp is not None:
+                        col = col + factor * float(tp[i])
+                    want[o, :, i] = col
+            with np.errstate(all="ignore"):
+                assert np.array_equal(out, want.astype(np.float32), equal_nan=True), (kind, post)
+    # building blocks of the hypsometric integration
+    q, T = rng.uniform(0, 0.02, 1000).astype(np.float32), rng.uniform(200, 310, 1000).astype(np.float32)
+    pl, ph = rng.uniform(100, 1050, 1000).astype(np.float32), rng.uniform(100, 1050, 1000).astype(np.float32)
+    for k in range(1000):
+        assert oracle.orc_virtual_temperature(q[k], T[k]) == ref.mifi_virtual_temperature(q[k], T[k])
+        assert oracle.orc_barometric_layer_thickness(pl[k], ph[k], T[k]) == ref.mifi_barometric_layer_thickness(pl[k], ph[k], T[k])
+
+
+def _call(fn, n, *args):
+    """call a mifi_* column function: scalars stay, arrays become double pointers, the last argument is the output"""
+    out = np.empty(n, np.float64)
+    conv = [dp(np.ascontiguousarray(x, dtype=np.float64)) if isinstance(x, np.ndarray) else x for x in args]
+    fn(n, *conv, dp(out))
+    return out
+
+
+class ol_k:
+    HYBRID_SIGMA_AP, HYBRID_SIGMA, SIGMA, LN_PRESSURE, HYBRID_HEIGHT, OCEAN_S_G1, OCEAN_S_G2 = range(7)
+
+
+def test_pressure_integration_restatement_against_python_loop(oracle, ref):
+    """PressureIntegrationToAltitudeConverter.cc:225-246 replayed in Python over the reference's two float functions"""
+    rng = np.random.default_rng(4)
+    nz, nI = 17, 29
+    for start_high in (1, 0, -1):
+        eta = np.linspace(1.0, 0.02, nz) if start_high != 0 else np.linspace(0.02, 1.0, nz)
+        sap = rng.uniform(700, 1040, (1, nI)).astype(np.float32)
+        p = (eta[:, None] * sap[0][None, :]).astype(np.float32)[None] * np.float32(0.999)
+        sgp = rng.uniform(0, 20000, (1, nI)).astype(np.float32)
+        T = rng.uniform(210, 300, (1, nz, nI)).astype(np.float32)
+        q = rng.uniform(0, 0.02, (1, nz, nI)).astype(np.float32)
+        for hum in (q, None):
+            out = np.empty((1, nz, nI), np.float32)
+            assert oracle.orc_vcoord_pressure_integration_f(fp(p), fp(sap), 1.0, fp(sgp), 1.0, fp(T), _fpn(hum), 1, 1, nz, nI, start_high, None, 0.0,
+                                                            fp(out)) == 1
+            want = np.empty((nz, nI), np.float64)
+            high = bool(p[0, 0, 0] > p[0, -1, 0])
+            for i in range(nI):
+                acc = float(sgp[0, i]) / 9.80665
+                p_low = sap[0, i]
+                for n in range(nz):
+                    iz = n if high else nz - 1 - n
+                    tv = T[0, iz, i] if hum is None else ref.mifi_virtual_temperature(q[0, iz, i], T[0, iz, i])
+                    acc += float(ref.mifi_barometric_layer_thickness(p_low, p[0, iz, i], tv))
+                    want[iz, i] = acc
+                    p_low = p[0, iz, i]
+            assert np.array_equal(out[0], want.astype(np.float32))
