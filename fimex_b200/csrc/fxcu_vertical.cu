@@ -1068,12 +1068,10 @@ __global__ void __launch_bounds__(256) lin_kernel(const float* __restrict__ A, c
         out[i] = __fadd_rn(A[i], __fmul_rn(f, __fsub_rn(B[i], A[i])));
 }
 
-// kind: 0 linear, 1 weak, 2 no, 3 const.  Decides on the host exactly like the reference which of copy-A / copy-B / blend / NaN applies.
-static int two_level_host(int kind, const float* A, const float* B, float* out, size_t n, double a, double b, double x)
+// kind: 0 linear, 1 weak, 2 no, 3 const.  Decides on the host exactly like the reference which of copy-A / copy-B / blend / NaN
+// applies; device pointers, enqueued on `s`
+static int two_level_dev(int kind, const float* dA, const float* dB, float* dO, size_t n, double a, double b, double x, cudaStream_t s)
 {
-    clear_error();
-    if (!require_device())
-        return FIMEXCU_ERROR;
     const float f = (a == b) ? 0.f : static_cast<float>((x - a) / (b - a));
     int action; // 0 copy A, 1 copy B, 2 blend, 3 NaN
     if (kind == 3)
@@ -1091,20 +1089,76 @@ static int two_level_host(int kind, const float* A, const float* B, float* out, 
     if (n == 0)
         return FIMEXCU_OK;
     const size_t bytes = n * sizeof(float);
+    const unsigned blocks = static_cast<unsigned>(std::min<size_t>((n + 255) / 256, static_cast<size_t>(sm_count()) * 16));
+    switch (action) {
+    case 0:
+        if (dO != dA)
+            FXCU_CUDA(cudaMemcpyAsync(dO, dA, bytes, cudaMemcpyDeviceToDevice, s));
+        break;
+    case 1:
+        if (dO != dB)
+            FXCU_CUDA(cudaMemcpyAsync(dO, dB, bytes, cudaMemcpyDeviceToDevice, s));
+        break;
+    case 2: lin_kernel<<<blocks, 256, 0, s>>>(dA, dB, dO, n, f); break;
+    default: FXCU_CUDA(cudaMemsetAsync(dO, 0xff, bytes, s)); break; // all-ones is a quiet NaN
+    }
+    FXCU_CUDA(cudaGetLastError());
+    return FIMEXCU_OK;
+}
+
+// vertical-interpolation method -> (kind, transformed coordinates) of the reference's seven two-level functions
+// (interpolation.c:416-546); returns false (error set) where the reference returns MIFI_ERROR and leaves the output untouched
+static bool two_level_plan(int method, double& a, double& b, double& x, int& kind)
+{
+    switch (method) {
+    case FIMEXCU_VINT_METHOD_NN: kind = 3; a = 0.; b = 1.; x = -1.; return true; // f < 0 with the "const" rule: copy A
+    case FIMEXCU_VINT_METHOD_LIN: kind = 0; return true;
+    case FIMEXCU_VINT_METHOD_LIN_WEAK_EXTRA: kind = 1; return true;
+    case FIMEXCU_VINT_METHOD_LIN_NO_EXTRA: kind = 2; return true;
+    case FIMEXCU_VINT_METHOD_LIN_CONST_EXTRA: kind = 3; return true;
+    case FIMEXCU_VINT_METHOD_LOGLOG:
+        if (a <= 0 || b <= 0 || x <= 0) {
+            set_error("mifi_get_values_log_log_f: non-positive coordinate");
+            return false;
+        }
+        a = std::log(a + 2.7182818284590452354);
+        b = std::log(b + 2.7182818284590452354);
+        x = std::log(x + 2.7182818284590452354);
+        // fall through: mifi_get_values_log_log_f calls mifi_get_values_log_f (interpolation.c:537-546)
+    case FIMEXCU_VINT_METHOD_LOG:
+        if (a <= 0 || b <= 0 || x <= 0) {
+            set_error("mifi_get_values_log_f: non-positive coordinate");
+            return false; // output untouched, like interpolation.c:524-526
+        }
+        // the three logarithms are host-side scalars (as in the reference); the field arithmetic runs on the device
+        a = std::log(a);
+        b = std::log(b);
+        x = std::log(x);
+        kind = 0;
+        return true;
+    default: set_error("fimexcu_get_values_two_level: unknown method"); return false;
+    }
+}
+
+static int two_level_host(int method, const float* A, const float* B, float* out, size_t n, double a, double b, double x)
+{
+    clear_error();
+    if (!require_device())
+        return FIMEXCU_ERROR;
+    int kind = 0;
+    if (!two_level_plan(method, a, b, x, kind))
+        return FIMEXCU_ERROR;
+    if (n == 0)
+        return FIMEXCU_OK;
+    const size_t bytes = n * sizeof(float);
     DevBuf dA, dB, dO;
     if (!dA.alloc(bytes, nullptr) || !dB.alloc(bytes, nullptr) || !dO.alloc(bytes, nullptr))
         return FIMEXCU_ERROR;
     // the product has no CPU path: even the plain copies travel through the device
     FXCU_CUDA(cudaMemcpyAsync(dA.p, A, bytes, cudaMemcpyHostToDevice, nullptr));
     FXCU_CUDA(cudaMemcpyAsync(dB.p, B, bytes, cudaMemcpyHostToDevice, nullptr));
-    const unsigned blocks = static_cast<unsigned>(std::min<size_t>((n + 255) / 256, static_cast<size_t>(sm_count()) * 16));
-    switch (action) {
-    case 0: FXCU_CUDA(cudaMemcpyAsync(dO.p, dA.p, bytes, cudaMemcpyDeviceToDevice, nullptr)); break;
-    case 1: FXCU_CUDA(cudaMemcpyAsync(dO.p, dB.p, bytes, cudaMemcpyDeviceToDevice, nullptr)); break;
-    case 2: lin_kernel<<<blocks, 256>>>(dA.as<float>(), dB.as<float>(), dO.as<float>(), n, f); break;
-    default: FXCU_CUDA(cudaMemsetAsync(dO.p, 0xff, bytes, nullptr)); break; // all-ones is a quiet NaN
-    }
-    FXCU_CUDA(cudaGetLastError());
+    if (two_level_dev(kind, dA.as<float>(), dB.as<float>(), dO.as<float>(), n, a, b, x, nullptr) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
     FXCU_CUDA(cudaMemcpyAsync(out, dO.p, bytes, cudaMemcpyDeviceToHost, nullptr));
     FXCU_CUDA(cudaStreamSynchronize(nullptr));
     return FIMEXCU_OK;
@@ -1346,48 +1400,49 @@ int fimexcu_vertical_hybrid_pressure_f(int method, const float* in, size_t nOute
 
 int fimexcu_get_values_nearest_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x)
 {
-    (void)a; (void)b; (void)x;
-    return two_level_host(3, infieldA, infieldB, outfield, n, 0., 1., -1.); // f < 0 with the "const" rule: copy A
+    return two_level_host(FIMEXCU_VINT_METHOD_NN, infieldA, infieldB, outfield, n, a, b, x);
 }
 
 int fimexcu_get_values_linear_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x)
 {
-    return two_level_host(0, infieldA, infieldB, outfield, n, a, b, x);
+    return two_level_host(FIMEXCU_VINT_METHOD_LIN, infieldA, infieldB, outfield, n, a, b, x);
 }
 
 int fimexcu_get_values_linear_weak_extrapol_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x)
 {
-    return two_level_host(1, infieldA, infieldB, outfield, n, a, b, x);
+    return two_level_host(FIMEXCU_VINT_METHOD_LIN_WEAK_EXTRA, infieldA, infieldB, outfield, n, a, b, x);
 }
 
 int fimexcu_get_values_linear_no_extrapol_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x)
 {
-    return two_level_host(2, infieldA, infieldB, outfield, n, a, b, x);
+    return two_level_host(FIMEXCU_VINT_METHOD_LIN_NO_EXTRA, infieldA, infieldB, outfield, n, a, b, x);
 }
 
 int fimexcu_get_values_linear_const_extrapol_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x)
 {
-    return two_level_host(3, infieldA, infieldB, outfield, n, a, b, x);
+    return two_level_host(FIMEXCU_VINT_METHOD_LIN_CONST_EXTRA, infieldA, infieldB, outfield, n, a, b, x);
 }
 
 int fimexcu_get_values_log_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x)
 {
-    if (a <= 0 || b <= 0 || x <= 0) {
-        set_error("mifi_get_values_log_f: non-positive coordinate");
-        return FIMEXCU_ERROR; // output untouched, like interpolation.c:524-526
-    }
-    // the three logarithms are host-side scalars (as in the reference); the field arithmetic runs on the device
-    return two_level_host(0, infieldA, infieldB, outfield, n, std::log(a), std::log(b), std::log(x));
+    return two_level_host(FIMEXCU_VINT_METHOD_LOG, infieldA, infieldB, outfield, n, a, b, x);
 }
 
 int fimexcu_get_values_log_log_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x)
 {
-    if (a <= 0 || b <= 0 || x <= 0) {
-        set_error("mifi_get_values_log_log_f: non-positive coordinate");
+    return two_level_host(FIMEXCU_VINT_METHOD_LOGLOG, infieldA, infieldB, outfield, n, a, b, x);
+}
+
+int fimexcu_get_values_two_level_dev_f(int method, const float* d_A, const float* d_B, float* d_out, size_t n, double a, double b, double x,
+                                       void* stream)
+{
+    clear_error();
+    if (!require_device())
         return FIMEXCU_ERROR;
-    }
-    const double e = 2.7182818284590452354;
-    return fimexcu_get_values_log_f(infieldA, infieldB, outfield, n, std::log(a + e), std::log(b + e), std::log(x + e));
+    int kind = 0;
+    if (!two_level_plan(method, a, b, x, kind))
+        return FIMEXCU_ERROR;
+    return two_level_dev(kind, d_A, d_B, d_out, n, a, b, x, as_stream(stream));
 }
 
 } // extern "C"

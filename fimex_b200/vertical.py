@@ -182,3 +182,16 @@ def pressureIntegrationAltitude(pressure, surfacePressure, surfaceGeopotential, 
                                                              _dptr(q), nO, sap.shape[0], nz, nI, int(start_high_p), _dptr(t), float(topography_factor),
                                                              out.data_ptr(), _lib.current_stream_ptr()), "pressureIntegrationAltitude")
     return out
+
+
+def timeInterpolateSlabs(sliceA, sliceB, tA, tB, t, method=4):
+    """CDMTimeInterpolator::getDataSlice between two device-resident time slices (src/CDMTimeInterpolator.cc:117-131): the
+    two-level kernel selected by `method` (default linear_weak_extrapol like the reference) over whole slabs; CUDA tensors."""
+    import torch
+    a, b = _dev(sliceA), _dev(sliceB)
+    if a.numel() != b.numel():
+        raise _lib.FimexCudaError("got slices with different size")
+    out = torch.empty_like(a)
+    _lib.check(lib.fimexcu_get_values_two_level_dev_f(method, a.data_ptr(), b.data_ptr(), out.data_ptr(), a.numel(), float(tA), float(tB), float(t),
+                                                      _lib.current_stream_ptr()), "timeInterpolateSlabs")
+    return out

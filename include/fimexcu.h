@@ -290,6 +290,12 @@ int fimexcu_get_values_linear_no_extrapol_f(const float* infieldA, const float* 
 int fimexcu_get_values_linear_const_extrapol_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
 int fimexcu_get_values_log_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
 int fimexcu_get_values_log_log_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);
+/* The same seven functions on DEVICE-resident slabs, selected by `method` (FIMEXCU_VINT_METHOD_*), enqueued on `stream`: what
+ * CDMTimeInterpolator::getDataSlice does between two time slices (src/CDMTimeInterpolator.cc:127:
+ * mifi_get_values_linear_weak_extrapol_f(d1, d2, out, size, t1, t2, t)) for slabs that stay on the device.
+ * d_out may alias d_A or d_B. */
+int fimexcu_get_values_two_level_dev_f(int method, const float* d_A, const float* d_B, float* d_out, size_t n, double a, double b, double x,
+                                       void* stream);
 
 /* ---- vertical coordinate converters -----------------------------------------------------------------------
  * The fields CDMVerticalInterpolator asks its ToVLevelConverter / VerticalConverter chain for (src/CDMVerticalInterpolator.cc:

@@ -392,3 +392,35 @@ def test_vertical_hybrid_outlier_surface_pressure(fx):
         want = _oracle_vertical(m, fld, np.ascontiguousarray(p), levels=levels)
         got = verticalHybridPressure(m, fld, ap, b, ps.reshape(1, nI), levels, ps_scale=0.01)
         assert (_eq if m == ol.VINT_LIN else _close)(got, want), m
+
+
+@pytest.mark.parametrize("name,method", [("nearest", ol.VINT_NN), ("linear", ol.VINT_LIN), ("linear_weak_extrapol", ol.VINT_LIN_WEAK),
+                                         ("linear_no_extrapol", ol.VINT_LIN_NO), ("linear_const_extrapol", ol.VINT_LIN_CONST), ("log", ol.VINT_LOG),
+                                         ("log_log", ol.VINT_LOGLOG)])
+def test_two_level_kernels_on_device_slabs(fx, oracle, name, method):
+    """CDMTimeInterpolator's use of the two-level kernels (CDMTimeInterpolator.cc:127) on slabs that stay on the device"""
+    import torch
+    from fimex_b200.vertical import timeInterpolateSlabs
+    rng = np.random.default_rng(method)
+    n = 100003
+    A = rng.normal(280, 10, n).astype(np.float32)
+    B = rng.normal(280, 10, n).astype(np.float32)
+    A[::101] = np.nan
+    B[::103] = np.nan
+    fn = getattr(oracle, "orc_get_values_" + name + "_f")
+    dA, dB = torch.from_numpy(A).cuda(), torch.from_numpy(B).cuda()
+    for a, b, x in ((3.0, 9.0, 4.5), (3.0, 9.0, 3.0), (3.0, 9.0, 9.0), (3.0, 9.0, 20.0), (3.0, 9.0, 0.5), (5.0, 5.0, 5.0), (9.0, 3.0, 13.0)):
+        want = np.full(n, -7.0, np.float32)
+        rc = fn(fp(A), fp(B), fp(want), n, a, b, x)
+        assert rc == 1
+        got = timeInterpolateSlabs(dA, dB, a, b, x, method=method)
+        torch.cuda.synchronize()
+        assert _eq(got.cpu().numpy(), want), (name, a, b, x)
+    # in place on the first slab, like a caller that reuses its buffer
+    want = np.empty(n, np.float32)
+    fn(fp(A), fp(B), fp(want), n, 3.0, 9.0, 4.5)
+    from fimex_b200 import _lib
+    dC = dA.clone()
+    _lib.check(_lib.lib.fimexcu_get_values_two_level_dev_f(method, dC.data_ptr(), dB.data_ptr(), dC.data_ptr(), n, 3.0, 9.0, 4.5, _lib.current_stream_ptr()), "x")
+    torch.cuda.synchronize()
+    assert _eq(dC.cpu().numpy(), want)
