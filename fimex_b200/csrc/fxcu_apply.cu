@@ -268,6 +268,7 @@ struct ApplyParams {
     int outPitch;  // elements between target rows
     size_t outLevel; // elements between target levels
     float bad, fill;
+    const int4* tile_meta; // per 32 x 8 target tile, see fimexcu_cache (staged kernels only)
 };
 
 template <bool BAD>
@@ -482,7 +483,7 @@ __global__ void __launch_bounds__(256) nearest_apply_kernel(const ApplyParams P)
 constexpr int TMA_BW = 32;    // box width  (source columns): one shared-memory row == 32 banks
 constexpr int TMA_BH = 16;    // box height (source rows)
 constexpr int TMA_ZB = 4;     // levels per stage
-constexpr int TMA_STAGES = 3; // ring depth
+constexpr int TMA_STAGES = 4; // ring depth (32 KB per CTA, 6 CTAs per SM)
 constexpr int TMA_TH = 8;     // consumer warps == tile rows
 constexpr int TMA_THREADS = 32 * TMA_TH + 32;
 
@@ -540,14 +541,15 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
     __shared__ __align__(128) float tile[TMA_STAGES][STAGE_FLOATS];
     __shared__ __align__(8) uint64_t full[TMA_STAGES];
     __shared__ __align__(8) uint64_t empty[TMA_STAGES];
-    __shared__ int red[4][TMA_TH];
-    __shared__ int bbox[4];
-
+    static_assert(TMA_TH == 8, "tile_fit_kernel describes 32 x 8 tiles");
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const bool consumer = warp < TMA_TH;
     const int ox = blockIdx.x * 32 + lane, oy = blockIdx.y * TMA_TH + warp;
     const bool in_grid = consumer && ox < P.outX && oy < P.outY;
+    // the tile's box and path come from the cache (computed once at build time): the producer can start streaming before a
+    // single table entry of this tile has arrived, and no reduction over the tile is needed here
+    const int4 meta = __ldg(P.tile_meta + blockIdx.y * gridDim.x + blockIdx.x);
     int f = -1;
     float fx = -1.f, fy = -1.f;
     if (in_grid) {
@@ -558,28 +560,6 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
             fy = static_cast<const float*>(P.wy)[o];
         }
     }
-    int x0 = 0x3fffffff, y0 = 0x3fffffff, x1 = -1, y1 = -1;
-    if (f >= 0) {
-        y0 = f / P.inX;
-        x0 = f - y0 * P.inX;
-        x1 = x0 + (fx >= 0.f ? 1 : 0);
-        y1 = y0 + (fy >= 0.f ? 1 : 0);
-    }
-    const bool interior = !NN && ((f < 0) || (fx >= 0.f && fy >= 0.f));
-    int lox = x0, loy = y0, hix = x1, hiy = y1;
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        lox = min(lox, __shfl_xor_sync(0xffffffffu, lox, s));
-        loy = min(loy, __shfl_xor_sync(0xffffffffu, loy, s));
-        hix = max(hix, __shfl_xor_sync(0xffffffffu, hix, s));
-        hiy = max(hiy, __shfl_xor_sync(0xffffffffu, hiy, s));
-    }
-    if (consumer && lane == 0) {
-        red[0][warp] = lox;
-        red[1][warp] = loy;
-        red[2][warp] = hix;
-        red[3][warp] = hiy;
-    }
     if (tid == 0) {
         for (int s = 0; s < TMA_STAGES; ++s) {
             mbar_init(&full[s], 1);
@@ -587,30 +567,18 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    const int all_interior = __syncthreads_and(interior ? 1 : 0);
-    if (tid == 0) {
-        int a = red[0][0], b = red[1][0], c = red[2][0], d = red[3][0];
-        for (int w = 1; w < TMA_TH; ++w) {
-            a = min(a, red[0][w]);
-            b = min(b, red[1][w]);
-            c = max(c, red[2][w]);
-            d = max(d, red[3][w]);
-        }
-        bbox[0] = a & ~7; // box starts on a 32 B sector
-        bbox[1] = b;
-        bbox[2] = c;
-        bbox[3] = d;
-    }
     __syncthreads();
-    const int bx0 = bbox[0], by0 = bbox[1], bx1 = bbox[2], by1 = bbox[3];
+    const int bx0 = meta.x, by0 = meta.y;
+    const bool all_interior = (meta.z & TILE_ALL_INTERIOR) != 0;
     float* po = static_cast<float*>(P.out) + static_cast<size_t>(oy) * P.outPitch + ox;
-    if (bx1 < 0) { // nothing defined in this tile
+    if (!(meta.z & TILE_HAS_DATA)) { // nothing defined in this tile
         if (in_grid)
             for (int z = 0; z < P.nz; ++z, po += P.outLevel)
                 store_out<FILL>(po, nan_f(), P.fill);
         return;
     }
-    if (!((bx1 - bx0 + 1 <= TMA_BW) && (by1 - by0 + 1 <= TMA_BH))) { // footprint too large: direct gathers
+    const int y0 = (f >= 0) ? f / P.inX : 0, x0 = (f >= 0) ? f - y0 * P.inX : 0;
+    if (!(meta.z & TILE_FITS)) { // footprint too large: direct gathers
         if (!in_grid)
             return;
         if (f < 0) {
@@ -702,7 +670,8 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
 
 // Staged form of the fused vector pass: u and v boxes of the same footprint travel through the same ring (two TMA loads per
 // stage on one mbarrier), consumers interpolate both components, rotate (reproject.cc:488-507) and store.
-constexpr int UV_ZB = 2; // levels per stage (two fields per level)
+constexpr int UV_ZB = 2;     // levels per stage (two fields per level)
+constexpr int UV_STAGES = 3; // ring depth
 struct UvStagedParams {
     const double* cs;
     const double* sn;
@@ -717,9 +686,9 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
 {
     constexpr int LVL = TMA_BW * TMA_BH;
     constexpr int FIELD = LVL * UV_ZB;
-    __shared__ __align__(128) float tile[TMA_STAGES][2 * FIELD];
-    __shared__ __align__(8) uint64_t full[TMA_STAGES];
-    __shared__ __align__(8) uint64_t empty[TMA_STAGES];
+    __shared__ __align__(128) float tile[UV_STAGES][2 * FIELD];
+    __shared__ __align__(8) uint64_t full[UV_STAGES];
+    __shared__ __align__(8) uint64_t empty[UV_STAGES];
     __shared__ int red[4][TMA_TH];
     __shared__ int bbox[4];
 
@@ -759,7 +728,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
         red[3][warp] = hiy;
     }
     if (tid == 0) {
-        for (int s = 0; s < TMA_STAGES; ++s) {
+        for (int s = 0; s < UV_STAGES; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], TMA_TH);
         }
@@ -802,8 +771,8 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
     if (!consumer) {
         if (staged && lane == 0) {
             for (int it = 0; it < niter; ++it) {
-                const int st = it % TMA_STAGES;
-                mbar_wait(&empty[st], ((it / TMA_STAGES) & 1) ^ 1);
+                const int st = it % UV_STAGES;
+                mbar_wait(&empty[st], ((it / UV_STAGES) & 1) ^ 1);
                 mbar_expect_tx(&full[st], 2 * FIELD * sizeof(float));
                 tma_load_3d(&tile[st][0], &umap, &full[st], bx0, by0, it * UV_ZB);
                 tma_load_3d(&tile[st][FIELD], &vmap, &full[st], bx0, by0, it * UV_ZB);
@@ -844,8 +813,8 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
     const int dys = fy >= 0.f ? TMA_BW : 0;
     const int r = (f >= 0) ? (y0 - by0) * TMA_BW + (x0 - bx0) : 0;
     for (int it = 0; it < niter; ++it) {
-        const int st = it % TMA_STAGES;
-        mbar_wait(&full[st], (it / TMA_STAGES) & 1);
+        const int st = it % UV_STAGES;
+        mbar_wait(&full[st], (it / UV_STAGES) & 1);
         const float* tu = &tile[st][r];
         const float* tv = tu + FIELD;
 #pragma unroll
@@ -878,21 +847,25 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
 // fraction of 32 x 8 target tiles whose source footprint fits the staged kernel's box (decides, once per cache,
 // whether the staged kernel is worth launching).  counts[0] = tiles with data, counts[1] = of those, tiles that fit
 __global__ void __launch_bounds__(256) tile_fit_kernel(const int* __restrict__ off, const float* __restrict__ wx, const float* __restrict__ wy, int outX,
-                                                       int outY, int inX, unsigned* __restrict__ counts)
+                                                       int outY, int inX, unsigned* __restrict__ counts, int4* __restrict__ meta)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ox = blockIdx.x * 32 + lane, oy = blockIdx.y * 8 + warp;
     int x0 = 0x3fffffff, y0 = 0x3fffffff, x1 = -1, y1 = -1;
+    bool interior = wx != nullptr; // undefined cells and cells outside the grid do not spoil a tile's fast path
     if (ox < outX && oy < outY) {
         const size_t o = static_cast<size_t>(oy) * outX + ox;
         const int f = off[o];
         if (f >= 0) {
             y0 = f / inX;
             x0 = f - y0 * inX;
-            x1 = x0 + ((wx && wx[o] >= 0.f) ? 1 : 0);
-            y1 = y0 + ((wy && wy[o] >= 0.f) ? 1 : 0);
+            const bool ex = wx && wx[o] >= 0.f, ey = wy && wy[o] >= 0.f;
+            x1 = x0 + (ex ? 1 : 0);
+            y1 = y0 + (ey ? 1 : 0);
+            interior = ex && ey;
         }
     }
+    const int all_interior = __syncthreads_and(interior ? 1 : 0);
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) {
         x0 = min(x0, __shfl_xor_sync(0xffffffffu, x0, s));
@@ -915,11 +888,16 @@ __global__ void __launch_bounds__(256) tile_fit_kernel(const int* __restrict__ o
             x1 = max(x1, red[2][w]);
             y1 = max(y1, red[3][w]);
         }
+        int flags = all_interior ? TILE_ALL_INTERIOR : 0;
         if (x1 >= 0) {
+            flags |= TILE_HAS_DATA;
             atomicAdd(&counts[0], 1u);
-            if ((x1 - (x0 & ~7) + 1 <= TMA_BW) && (y1 - y0 + 1 <= TMA_BH))
+            if ((x1 - (x0 & ~7) + 1 <= TMA_BW) && (y1 - y0 + 1 <= TMA_BH)) {
+                flags |= TILE_FITS;
                 atomicAdd(&counts[1], 1u);
+            }
         }
+        meta[blockIdx.y * gridDim.x + blockIdx.x] = make_int4(x0 & ~7, y0, flags, 0); // box starts on a 32 B sector
     }
 }
 
@@ -1134,8 +1112,10 @@ fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, s
                 return nullptr;
             FXCU_CUDA_NULL(cudaMemsetAsync(counts.p, 0, 2 * sizeof(unsigned), s));
             const dim3 tg(static_cast<unsigned>((outX + 31) / 32), static_cast<unsigned>((outY + 7) / 8));
+            if (!c->tile_meta.alloc_sync(static_cast<size_t>(tg.x) * tg.y * sizeof(int4)))
+                return nullptr;
             tile_fit_kernel<<<tg, 256, 0, s>>>(c->off.as<int>(), nullptr, nullptr, static_cast<int>(outX), static_cast<int>(outY),
-                                               static_cast<int>(c->inX), counts.as<unsigned>());
+                                               static_cast<int>(c->inX), counts.as<unsigned>(), c->tile_meta.as<int4>());
             FXCU_CUDA_NULL(cudaGetLastError());
             unsigned hc[2] = {0, 0};
             FXCU_CUDA_NULL(cudaMemcpyAsync(hc, counts.p, sizeof(hc), cudaMemcpyDeviceToHost, s));
@@ -1193,8 +1173,10 @@ fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, s
             return nullptr;
         FXCU_CUDA_NULL(cudaMemsetAsync(counts.p, 0, 2 * sizeof(unsigned), s));
         const dim3 tg(static_cast<unsigned>((outX + 31) / 32), static_cast<unsigned>((outY + 7) / 8));
+        if (!c->tile_meta.alloc_sync(static_cast<size_t>(tg.x) * tg.y * sizeof(int4)))
+            return nullptr;
         tile_fit_kernel<<<tg, 256, 0, s>>>(c->off.as<int>(), c->wx.as<float>(), c->wy.as<float>(), static_cast<int>(outX), static_cast<int>(outY),
-                                           static_cast<int>(c->inX), counts.as<unsigned>());
+                                           static_cast<int>(c->inX), counts.as<unsigned>(), c->tile_meta.as<int4>());
         FXCU_CUDA_NULL(cudaGetLastError());
         unsigned hc[2] = {0, 0};
         FXCU_CUDA_NULL(cudaMemcpyAsync(hc, counts.p, sizeof(hc), cudaMemcpyDeviceToHost, s));
@@ -1305,6 +1287,7 @@ int cache_apply_strided(const fimexcu_cache* c, const float* d_in, const Layout&
     P.off = c->off.as<int>();
     P.wx = c->wx.p;
     P.wy = c->wy.p;
+    P.tile_meta = c->tile_meta.as<int4>();
     P.in = d_in;
     P.out = d_out;
     P.outX = static_cast<int>(c->outX);
@@ -1345,6 +1328,7 @@ int cache_apply_strided_i16(const fimexcu_cache* c, const short* d_in, const Lay
     P.off = c->off.as<int>();
     P.wx = c->wx.p;
     P.wy = c->wy.p;
+    P.tile_meta = c->tile_meta.as<int4>();
     P.in = d_in;
     P.out = d_out;
     P.outX = static_cast<int>(c->outX);
@@ -1577,6 +1561,7 @@ static int cache_apply_uv_strided(const fimexcu_cache* c, const fimexcu_vecrot* 
     P.off = c->off.as<int>();
     P.wx = c->wx.p;
     P.wy = c->wy.p;
+    P.tile_meta = c->tile_meta.as<int4>();
     P.in = d_u_in;
     P.out = d_u_out;
     P.outX = static_cast<int>(c->outX);

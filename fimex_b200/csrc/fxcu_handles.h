@@ -4,6 +4,8 @@
 
 namespace fxcu {
 enum CacheKind { KIND_BILINEAR = 0, KIND_BICUBIC = 1, KIND_NN = 2 };
+// what the staged kernels need to know about a target tile before any of its table entries has arrived
+enum TileFlags { TILE_HAS_DATA = 1, TILE_FITS = 2, TILE_ALL_INTERIOR = 4 };
 }
 
 struct fimexcu_cache {
@@ -16,6 +18,7 @@ struct fimexcu_cache {
     fxcu::DevBuf off;    // int32 [outX*outY]
     fxcu::DevBuf wx, wy; // f32 (bilinear) or f64 (bicubic) [outX*outY]
     unsigned tiles_with_data = 0, tiles_fitting = 0; // 32 x 8 target tiles: with defined cells / whose footprint fits the TMA box
+    fxcu::DevBuf tile_meta; // int4 per 32 x 8 target tile (row-major over tiles): {box x0 (sector aligned), box y0, TILE_* flags, 0}
 };
 
 struct fimexcu_vecrot {
