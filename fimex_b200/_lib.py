@@ -48,6 +48,9 @@ SIGNATURES = {
     "fimexcu_vcoord_transform_dev_f": (C.c_int, [C.c_int, vp, sz, vp, vp]),
     "fimexcu_get_values_two_level_dev_f": (C.c_int, [C.c_int, vp, vp, vp, sz, C.c_double, C.c_double, C.c_double, vp]),
     "fimexcu_vcoord_pressure_integration_dev_f": (C.c_int, [vp, vp, C.c_double, vp, C.c_double, vp, vp, sz, sz, sz, sz, C.c_int, vp, C.c_double, vp, vp]),
+    "fimexcu_unpack_dev_f": (C.c_int, [C.c_int, vp, sz, C.c_double, vp, vp]),
+    "fimexcu_unpack_scaled_dev_f": (C.c_int, [C.c_int, vp, sz, C.c_double, C.c_double, C.c_double, vp, vp]),
+    "fimexcu_pack_dev_f": (C.c_int, [C.c_int, vp, sz, C.c_double, vp, vp]),
     "fimexcu_cache_apply_i16": (C.c_int, [vp, vp, sz, vp, c_size_p, C.c_double]),
     "fimexcu_cache_apply_dev_i16": (C.c_int, [vp, vp, sz, vp, C.c_double, vp]),
     "fimexcu_cache_padded_layout": (C.c_int, [vp, c_size_p, c_size_p, c_size_p, c_size_p]),

@@ -1267,6 +1267,10 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
 
 static int check_layout(const fimexcu_cache* c, const Layout& L, size_t nz)
 {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev != c->device) // the tables live in that device's memory
+        FXCU_FAIL("fimexcu_cache_apply: the cache was built on device " + std::to_string(c->device) + ", the current device is " +
+                  std::to_string(dev) + " (call fimexcu_set_device first)");
     if (L.inPitch < static_cast<long long>(c->inX) || L.inLevel < static_cast<size_t>(L.inPitch) * (c->inY - 1) + c->inX ||
         L.outPitch < static_cast<long long>(c->outX) || L.outLevel < static_cast<size_t>(L.outPitch) * (c->outY - 1) + c->outX)
         FXCU_FAIL("fimexcu_cache_apply: row pitch / level stride smaller than the grid");

@@ -134,6 +134,23 @@ int fimexcu_cache_apply_i16(const fimexcu_cache* c, const int16_t* in, size_t si
 int fimexcu_cache_apply_dev_i16(const fimexcu_cache* c, const int16_t* d_in, size_t nz, int16_t* d_out, double badValue, void* stream);
 void fimexcu_cache_destroy(fimexcu_cache* c);
 
+/* Slab feed / sink for packed integer variables as stand-alone device passes, so that packed slabs cross
+ * PCIe in their file type and any operator of the path can be chained on the device in f32:
+ *   fimexcu_unpack_dev_f         data2InterpolationArray (src/CDMInterpolator.cc:140-145): Data::asFloat() of the raw values, fill -> NaN
+ *   fimexcu_unpack_scaled_dev_f  getScaledDataSlice (src/CDMReader.cc:177-192): fill -> NaN, scale*v + offset in f64, narrowed like Data::asFloat()
+ *   fimexcu_pack_dev_f           interpolationArray2Data (src/CDMInterpolator.cc:147-151): NaN -> fill, lround, the C casts of ScaleValue<float,T> */
+enum fimexcu_dtype {
+    FIMEXCU_DTYPE_I8 = 0,  /* CDM_CHAR (NC_BYTE) */
+    FIMEXCU_DTYPE_I16 = 1, /* CDM_SHORT */
+    FIMEXCU_DTYPE_I32 = 2, /* CDM_INT */
+    FIMEXCU_DTYPE_U8 = 3,  /* CDM_UCHAR */
+    FIMEXCU_DTYPE_U16 = 4, /* CDM_USHORT */
+    FIMEXCU_DTYPE_U32 = 5  /* CDM_UINT */
+};
+int fimexcu_unpack_dev_f(int dtype, const void* d_in, size_t n, double badValue, float* d_out, void* stream);
+int fimexcu_unpack_scaled_dev_f(int dtype, const void* d_in, size_t n, double fill, double scale, double offset, float* d_out, void* stream);
+int fimexcu_pack_dev_f(int dtype, const float* d_in, size_t n, double badValue, void* d_out, void* stream);
+
 /* Drop-in for the per-point C kernels with the reference signatures (include/fimex/interpolation.h:95-137,
  * src/interpolation.c:251-414): one (x, y) position over iz levels.  infield/outvalues are HOST pointers.
  * Provided for callers of the uncached path (reproject::reproject_f, src/reproject.cc:266-295); one launch

@@ -1191,3 +1191,82 @@ int orc_vcoord_pressure_integration_f(const float* p, const float* sap, double s
         }
     return 1;
 }
+
+/* ---- packed integer slabs, generic over the CDM integer types ---- */
+#define ORC_PACK_FUNCS(NAME, T)                                                                                          \
+    static void orc_unpack_##NAME(const T* in, size_t n, double badValue, float* out)                                    \
+    {                                                                                                                    \
+        size_t i;                                                                                                        \
+        for (i = 0; i < n; ++i)                                                                                          \
+            out[i] = (float)in[i];                                                                                       \
+        orc_bad2nanf(out, n, (float)badValue);                                                                           \
+    }                                                                                                                    \
+    static void orc_unpack_scaled_##NAME(const T* in, size_t n, double fill, double scale, double offset, float* out)    \
+    {                                                                                                                    \
+        const T oldFill = (T)fill;                                                                                       \
+        const double a = scale / 1.0, b = (offset - 0.0) / 1.0;                                                          \
+        size_t i;                                                                                                        \
+        for (i = 0; i < n; ++i) {                                                                                        \
+            const double d = (in[i] == oldFill) ? NAN : a * in[i] + b;                                                   \
+            out[i] = (float)d;                                                                                           \
+        }                                                                                                                \
+    }                                                                                                                    \
+    static void orc_pack_##NAME(const float* in, size_t n, double badValue, T* out)                                      \
+    {                                                                                                                    \
+        const T newFill = (T)badValue;                                                                                   \
+        size_t i;                                                                                                        \
+        for (i = 0; i < n; ++i) {                                                                                        \
+            const float v = in[i];                                                                                       \
+            if (v != v) {                                                                                                \
+                out[i] = newFill;                                                                                        \
+            } else {                                                                                                     \
+                const int r = (int)lround(1.0 * v + 0.0);                                                                \
+                out[i] = (T)r;                                                                                           \
+            }                                                                                                            \
+        }                                                                                                                \
+    }
+ORC_PACK_FUNCS(i8, signed char)
+ORC_PACK_FUNCS(i16, short)
+ORC_PACK_FUNCS(i32, int)
+ORC_PACK_FUNCS(u8, unsigned char)
+ORC_PACK_FUNCS(u16, unsigned short)
+ORC_PACK_FUNCS(u32, unsigned int)
+
+int orc_unpack_f(int dtype, const void* in, size_t n, double badValue, float* out)
+{
+    switch (dtype) {
+    case 0: orc_unpack_i8((const signed char*)in, n, badValue, out); return 1;
+    case 1: orc_unpack_i16((const short*)in, n, badValue, out); return 1;
+    case 2: orc_unpack_i32((const int*)in, n, badValue, out); return 1;
+    case 3: orc_unpack_u8((const unsigned char*)in, n, badValue, out); return 1;
+    case 4: orc_unpack_u16((const unsigned short*)in, n, badValue, out); return 1;
+    case 5: orc_unpack_u32((const unsigned int*)in, n, badValue, out); return 1;
+    default: return 0;
+    }
+}
+
+int orc_unpack_scaled_f(int dtype, const void* in, size_t n, double fill, double scale, double offset, float* out)
+{
+    switch (dtype) {
+    case 0: orc_unpack_scaled_i8((const signed char*)in, n, fill, scale, offset, out); return 1;
+    case 1: orc_unpack_scaled_i16((const short*)in, n, fill, scale, offset, out); return 1;
+    case 2: orc_unpack_scaled_i32((const int*)in, n, fill, scale, offset, out); return 1;
+    case 3: orc_unpack_scaled_u8((const unsigned char*)in, n, fill, scale, offset, out); return 1;
+    case 4: orc_unpack_scaled_u16((const unsigned short*)in, n, fill, scale, offset, out); return 1;
+    case 5: orc_unpack_scaled_u32((const unsigned int*)in, n, fill, scale, offset, out); return 1;
+    default: return 0;
+    }
+}
+
+int orc_pack_f(int dtype, const float* in, size_t n, double badValue, void* out)
+{
+    switch (dtype) {
+    case 0: orc_pack_i8(in, n, badValue, (signed char*)out); return 1;
+    case 1: orc_pack_i16(in, n, badValue, (short*)out); return 1;
+    case 2: orc_pack_i32(in, n, badValue, (int*)out); return 1;
+    case 3: orc_pack_u8(in, n, badValue, (unsigned char*)out); return 1;
+    case 4: orc_pack_u16(in, n, badValue, (unsigned short*)out); return 1;
+    case 5: orc_pack_u32(in, n, badValue, (unsigned int*)out); return 1;
+    default: return 0;
+    }
+}

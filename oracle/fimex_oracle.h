@@ -206,3 +206,9 @@ int orc_vcoord_pressure_integration_f(const float* p, const float* sap, double s
 void orc_vcoord_transform_f(int post, const float* in, size_t n, float* out);
 float orc_virtual_temperature(float spec_humidity, float T);                       /* vertical_coordinate_transformations.c:115-118 */
 float orc_barometric_layer_thickness(float p_low_alti, float p_high_alti, float T); /* :161-164 */
+
+/* ---- packed integer slabs, any CDM integer type (see orc_i16_* above for the citations); dtype as enum fimexcu_dtype:
+ * 0 CDM_CHAR (signed char), 1 CDM_SHORT, 2 CDM_INT, 3 CDM_UCHAR, 4 CDM_USHORT, 5 CDM_UINT */
+int orc_unpack_f(int dtype, const void* in, size_t n, double badValue, float* out);
+int orc_unpack_scaled_f(int dtype, const void* in, size_t n, double fill, double scale, double offset, float* out);
+int orc_pack_f(int dtype, const float* in, size_t n, double badValue, void* out);

@@ -63,6 +63,29 @@ struct Cloud {
 };
 } // namespace
 
+// generic over the CDM integer types; dtype as enum fimexcu_dtype (CDM_CHAR is `char`, include/fimex/CDMDataType.h:34-46)
+namespace {
+template <class T> void ref_unpack_t(const void* in, size_t n, double bad, float* out)
+{
+    const T* p = static_cast<const T*>(in);
+    std::transform(p, p + n, out, MetNoFimex::data_caster<float, T>());
+    mifi_bad2nanf(out, out + n, bad);
+}
+template <class T> void ref_unpack_scaled_t(const void* in, size_t n, double fill, double scale, double offset, float* out)
+{
+    const T* p = static_cast<const T*>(in);
+    MetNoFimex::ScaleValue<T, double> sv(fill, scale, offset, MIFI_UNDEFINED_D, 1., 0.);
+    for (size_t i = 0; i < n; ++i)
+        out[i] = MetNoFimex::data_caster<float, double>()(sv(p[i]));
+}
+template <class T> void ref_pack_t(const float* in, size_t n, double bad, void* out)
+{
+    MetNoFimex::ScaleValue<float, T> sv(MIFI_UNDEFINED_F, 1., 0., bad, 1., 0.);
+    std::transform(in, in + n, static_cast<T*>(out), sv);
+}
+} // namespace
+
+
 extern "C" {
 
 int ref_num_threads(void)
@@ -276,6 +299,45 @@ void ref_i16_scaled_to_float(const short* in, size_t n, double fill, double scal
     MetNoFimex::ScaleValue<short, double> sv(fill, scale, offset, MIFI_UNDEFINED_D, 1., 0.);
     for (size_t i = 0; i < n; ++i)
         out[i] = MetNoFimex::data_caster<float, double>()(sv(in[i]));
+}
+
+int ref_unpack_f(int dtype, const void* in, size_t n, double bad, float* out)
+{
+    switch (dtype) {
+    case 0: ref_unpack_t<char>(in, n, bad, out); return 1;
+    case 1: ref_unpack_t<short>(in, n, bad, out); return 1;
+    case 2: ref_unpack_t<int>(in, n, bad, out); return 1;
+    case 3: ref_unpack_t<unsigned char>(in, n, bad, out); return 1;
+    case 4: ref_unpack_t<unsigned short>(in, n, bad, out); return 1;
+    case 5: ref_unpack_t<unsigned int>(in, n, bad, out); return 1;
+    default: return 0;
+    }
+}
+
+int ref_unpack_scaled_f(int dtype, const void* in, size_t n, double fill, double scale, double offset, float* out)
+{
+    switch (dtype) {
+    case 0: ref_unpack_scaled_t<char>(in, n, fill, scale, offset, out); return 1;
+    case 1: ref_unpack_scaled_t<short>(in, n, fill, scale, offset, out); return 1;
+    case 2: ref_unpack_scaled_t<int>(in, n, fill, scale, offset, out); return 1;
+    case 3: ref_unpack_scaled_t<unsigned char>(in, n, fill, scale, offset, out); return 1;
+    case 4: ref_unpack_scaled_t<unsigned short>(in, n, fill, scale, offset, out); return 1;
+    case 5: ref_unpack_scaled_t<unsigned int>(in, n, fill, scale, offset, out); return 1;
+    default: return 0;
+    }
+}
+
+int ref_pack_f(int dtype, const float* in, size_t n, double bad, void* out)
+{
+    switch (dtype) {
+    case 0: ref_pack_t<char>(in, n, bad, out); return 1;
+    case 1: ref_pack_t<short>(in, n, bad, out); return 1;
+    case 2: ref_pack_t<int>(in, n, bad, out); return 1;
+    case 3: ref_pack_t<unsigned char>(in, n, bad, out); return 1;
+    case 4: ref_pack_t<unsigned short>(in, n, bad, out); return 1;
+    case 5: ref_pack_t<unsigned int>(in, n, bad, out); return 1;
+    default: return 0;
+    }
 }
 
 } // extern "C"

@@ -92,6 +92,9 @@ def oracle():
         "orc_vcoord_transform_f": (None, [C.c_int, c_float_p, C.c_size_t, c_float_p]),
         "orc_virtual_temperature": (C.c_float, [C.c_float, C.c_float]),
         "orc_barometric_layer_thickness": (C.c_float, [C.c_float, C.c_float, C.c_float]),
+        "orc_unpack_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
+        "orc_unpack_scaled_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
+        "orc_pack_f": (C.c_int, [C.c_int, c_float_p, C.c_size_t, C.c_double, C.c_void_p]),
         "orc_i16_to_interpolation_array": (None, [C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
         "orc_interpolation_array_to_i16": (None, [c_float_p, C.c_size_t, C.c_double, C.c_void_p]),
         "orc_i16_scaled_to_float": (None, [C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
@@ -155,6 +158,9 @@ def ref(omp=False):
         "ref_cache_apply_seconds": (C.c_double, [C.c_void_p, c_float_p, C.c_size_t, C.c_int]),
         "ref_cache_destroy": (None, [C.c_void_p]),
         "ref_round_and_clamp": (C.c_size_t, [C.c_double, C.c_size_t, C.c_size_t, C.c_size_t]),
+        "ref_unpack_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
+        "ref_unpack_scaled_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
+        "ref_pack_f": (C.c_int, [C.c_int, c_float_p, C.c_size_t, C.c_double, C.c_void_p]),
         "ref_i16_to_interpolation_array": (None, [C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
         "ref_interpolation_array_to_i16": (None, [c_float_p, C.c_size_t, C.c_double, C.c_void_p]),
         "ref_i16_scaled_to_float": (None, [C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
@@ -269,3 +275,6 @@ def o_packed_apply(method, px, py, inX, inY, outX, outY, raw, badValue):
     out = np.empty(res.shape, np.int16)
     o.orc_interpolation_array_to_i16(fp(res), res.size, float(badValue), out.ctypes.data)
     return out
+
+
+PACKED_DTYPES = {0: np.int8, 1: np.int16, 2: np.int32, 3: np.uint8, 4: np.uint16, 5: np.uint32}

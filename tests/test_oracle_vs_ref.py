@@ -333,3 +333,33 @@ def test_pressure_integration_restatement_against_python_loop(oracle, ref):
                     want[iz, i] = acc
                     p_low = p[0, iz, i]
             assert np.array_equal(out[0], want.astype(np.float32))
+
+
+@pytest.mark.parametrize("dtype", sorted(ol.PACKED_DTYPES))
+def test_packed_conversions_all_types_match_reference(oracle, ref, dtype):
+    """data2InterpolationArray / getScaledDataSlice / interpolationArray2Data for every CDM integer type, against the reference's
+    header templates instantiated for that type"""
+    rng = np.random.default_rng(dtype)
+    T = ol.PACKED_DTYPES[dtype]
+    info = np.iinfo(T)
+    n = 100000
+    raw = rng.integers(info.min, int(info.max) + 1, n, dtype=np.int64).astype(T)
+    for bad in (float(info.min), float(info.max), 17.0, 1.0e30, -1.0e10):
+        fillv = np.array([bad]).astype(np.float64)
+        if info.min <= bad <= info.max:
+            raw[::19] = T(bad)
+        a, b = np.empty(n, np.float32), np.empty(n, np.float32)
+        assert oracle.orc_unpack_f(dtype, raw.ctypes.data, n, bad, fp(a)) == 1 and ref.ref_unpack_f(dtype, raw.ctypes.data, n, bad, fp(b)) == 1
+        assert np.array_equal(a, b, equal_nan=True)
+        if info.min <= bad <= info.max:  # casting an out-of-range double to the integer type is undefined in the reference
+            assert oracle.orc_unpack_scaled_f(dtype, raw.ctypes.data, n, bad, 0.01, 273.15, fp(a)) == 1
+            assert ref.ref_unpack_scaled_f(dtype, raw.ctypes.data, n, bad, 0.01, 273.15, fp(b)) == 1
+            assert np.array_equal(a, b, equal_nan=True)
+            span = float(info.max) - float(info.min)
+            v = rng.uniform(info.min - 0.1 * span, info.max + 0.1 * span, n).astype(np.float32)
+            v[:4000] = np.round(v[:4000]) + np.float32(0.5)
+            v[4000:5000] = np.nan
+            v[5000:5100] = rng.uniform(-2e9, 2e9, 100).astype(np.float32)
+            c, d = np.empty(n, T), np.empty(n, T)
+            assert oracle.orc_pack_f(dtype, fp(v), n, bad, c.ctypes.data) == 1 and ref.ref_pack_f(dtype, fp(v), n, bad, d.ctypes.data) == 1
+            assert np.array_equal(c, d)
