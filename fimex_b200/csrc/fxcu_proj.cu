@@ -322,4 +322,41 @@ fimexcu_cache* fimexcu_cache_create_from_projection(int method, const char* proj
     return cache_build(method, px.as<double>(), py.as<double>(), inX, inY, outX, outY, nullptr);
 }
 
+fimexcu_cache* fimexcu_cache_create_from_points(int method, const char* proj_points, const char* proj_org, const double* x_points,
+                                                const double* y_points, size_t outX, size_t outY, const double* org_x_axis,
+                                                const double* org_y_axis, size_t inX, size_t inY, int org_x_axis_type, int org_y_axis_type)
+{
+    clear_error();
+    if (!require_device())
+        return nullptr;
+    Crs points, source;
+    if (!parse_pair(proj_points, proj_org, points, source))
+        return nullptr;
+    if (outX == 0 || outY == 0 || inX < 2 || inY < 2 || outX > 0x3fffffff || outY > 0x3fffffff || inX > 0x3fffffff || inY > 0x3fffffff) {
+        set_error("fimexcu_cache_create_from_points: sizes out of range");
+        return nullptr;
+    }
+    if (!x_points || !y_points || !org_x_axis || !org_y_axis) {
+        set_error("fimexcu_cache_create_from_points: null argument");
+        return nullptr;
+    }
+    const size_t n = outX * outY;
+    DevBuf px, py, axes;
+    if (!px.alloc(n * 8, nullptr) || !py.alloc(n * 8, nullptr) || !axes.alloc((inX + inY) * 8, nullptr))
+        return nullptr;
+    FXCU_CUDA_NULL(cudaMemcpyAsync(px.p, x_points, n * 8, cudaMemcpyHostToDevice, nullptr));
+    FXCU_CUDA_NULL(cudaMemcpyAsync(py.p, y_points, n * 8, cudaMemcpyHostToDevice, nullptr));
+    // CDMInterpolator.cc:1647: the template's / list's points expressed in the source CRS
+    transform_kernel<<<blocks_for(n, 256), 256>>>(points, source, n, px.as<double>(), py.as<double>());
+    FXCU_CUDA_NULL(cudaGetLastError());
+    // :1659-1660: coordinates -> fractional indices on the source axes
+    FXCU_CUDA_NULL(cudaMemcpy(axes.p, org_x_axis, inX * 8, cudaMemcpyHostToDevice));
+    FXCU_CUDA_NULL(cudaMemcpy(axes.as<double>() + inX, org_y_axis, inY * 8, cudaMemcpyHostToDevice));
+    if (points2position_dev(px.as<double>(), n, axes.as<double>(), org_x_axis, static_cast<int>(inX), org_x_axis_type, nullptr) != FIMEXCU_OK ||
+        points2position_dev(py.as<double>(), n, axes.as<double>() + inX, org_y_axis, static_cast<int>(inY), org_y_axis_type, nullptr) != FIMEXCU_OK)
+        return nullptr;
+    // :1665: createCachedInterpolation
+    return cache_build(method, px.as<double>(), py.as<double>(), inX, inY, outX, outY, nullptr);
+}
+
 } // extern "C"

@@ -59,3 +59,27 @@ def cachedInterpolationFromProjection(method, proj_input, org_proj, out_x_axis, 
     ci._h = _lib.check_handle(h, "changeProjectionByProjectionParameters")
     ci._read_info()
     return ci
+
+
+LAT_LON_PROJSTR = "+proj=latlong +datum=WGS84 +towgs84=0,0,0 +no_defs"  # MIFI_WGS84_LATLON_PROJ4 (include/fimex/mifi_constants.h)
+
+
+def cachedInterpolationForPoints(method, org_proj, lonVals, latVals, org_x_axis, org_y_axis, org_x_axis_type=0, org_y_axis_type=0, out_shape=None,
+                                 proj_points=LAT_LON_PROJSTR):
+    """CDMInterpolator::changeProjection(method, lonVals, latVals) / ...ToLatLonTemplate / ...ToCrossSections
+    (src/CDMInterpolator.cc:457-490, 1580-1666): the target is a list of points in degrees; out_shape = (outY, outX) for a 2-D
+    template, default a single row of len(lonVals) points."""
+    from .interpolation import CachedInterpolationInterface
+    lon, lat = _f64(lonVals).ravel(), _f64(latVals).ravel()
+    if lon.size != lat.size:
+        raise _lib.FimexCudaError("number of longitude and latitude values differs")
+    oy, ox = (1, lon.size) if out_shape is None else out_shape
+    if ox * oy != lon.size:
+        raise _lib.FimexCudaError("out_shape does not match the number of points")
+    ix, iy = _f64(org_x_axis).ravel(), _f64(org_y_axis).ravel()
+    h = lib.fimexcu_cache_create_from_points(method, proj_points.encode(), org_proj.encode(), lon.ctypes.data, lat.ctypes.data, ox, oy, ix.ctypes.data,
+                                             iy.ctypes.data, ix.size, iy.size, org_x_axis_type, org_y_axis_type)
+    ci = CachedInterpolationInterface("x", "y")
+    ci._h = _lib.check_handle(h, "changeProjectionToLatLonTemplate")
+    ci._read_info()
+    return ci

@@ -238,6 +238,15 @@ fimexcu_cache* fimexcu_cache_create_from_projection(int method, const char* proj
                                                     const double* org_x_axis, const double* org_y_axis, size_t inX, size_t inY,
                                                     int org_x_axis_type, int org_y_axis_type);
 
+/* The numeric part of CDMInterpolator::changeProjectionByProjectionParametersToLatLonTemplate (src/CDMInterpolator.cc:1636-1666):
+ * the target is a LIST of points (outX*outY of them: a 2-D lat/lon template, a point list with outY = 1, or the sampled lines
+ * of changeProjectionToCrossSections, :492-613) given in proj_points (the reference passes "+proj=latlong +datum=WGS84" and
+ * degrees): reproject_values(points -> source CRS) + 2 x points2position + cache construction, all on the device
+ * (SURVEY 8(f) rank 4). */
+fimexcu_cache* fimexcu_cache_create_from_points(int method, const char* proj_points, const char* proj_org, const double* x_points,
+                                                const double* y_points, size_t outX, size_t outY, const double* org_x_axis,
+                                                const double* org_y_axis, size_t inX, size_t inY, int org_x_axis_type, int org_y_axis_type);
+
 /* ------------------------------------------------------------------------------------------------
  * coordinate-based nearest neighbour (curvilinear sources)
  * ---------------------------------------------------------------------------------------------- */

@@ -202,3 +202,36 @@ def test_config0_hirlam12_end_to_end(rp, tag):
         assert np.array_equal(np.isnan(got)[:, ~strip], np.isnan(want)[:, ~strip])
         k = ~np.isnan(want) & ~strip[None]
         assert np.allclose(got[k], want[k], rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("method", [ol.BILINEAR, ol.BICUBIC, ol.NEAREST])
+def test_point_list_and_cross_section_extraction(rp, method):
+    """CDMInterpolator::changeProjection(method, lonVals, latVals) / ...ToLatLonTemplate / ...ToCrossSections
+    (src/CDMInterpolator.cc:457-613, 1580-1666): a list of lon/lat points (here: two great-circle-ish sections sampled like
+    the reference does, plus isolated stations, some outside the domain) as the target of the cached interpolation, built on
+    the device in one call and compared with oracle transform -> points2position -> cached apply."""
+    from fimex_b200 import synthetic as S
+    rng = np.random.default_rng(method)
+    lon = np.concatenate([np.linspace(5.0, 25.0, 301), np.linspace(-20.0, 60.0, 257), rng.uniform(-30, 70, 200)])
+    lat = np.concatenate([np.linspace(58.0, 70.5, 301), np.linspace(48.0, 76.0, 257), rng.uniform(45, 80, 200)])
+    mx, my = S.meps_axes()
+    ci = rp.cachedInterpolationForPoints(method, S.MEPS_PROJ, lon, lat, mx, my)
+    assert (ci.getOutX(), ci.getOutY()) == (lon.size, 1)
+    x, y = _oracle_transform(rp.LAT_LON_PROJSTR, S.MEPS_PROJ, lon, lat)
+    o = ol.oracle()
+    o.orc_points2position(dp(x), x.size, dp(mx), mx.size, ol.PROJ_AXIS)
+    o.orc_points2position(dp(y), y.size, dp(my), my.size, ol.PROJ_AXIS)
+    fld = S.meps_slab_numpy(t=2, nz=4)
+    want, info = ol.o_cached_apply(method, x, y, S.MEPS_NX, S.MEPS_NY, lon.size, 1, fld)
+    got, _ = ci.interpolateValues(ci.reduceInput(fld, S.MEPS_NX, S.MEPS_NY))
+    assert np.array_equal(np.isnan(got), np.isnan(want)) and np.isnan(want).any() and (~np.isnan(want)).any()
+    ok = ~np.isnan(want)
+    if method == ol.NEAREST:
+        assert (got[ok] != want[ok]).mean() < 1e-3  # a cell boundary hit to 1e-12 cells may round the other way
+    else:
+        assert np.allclose(got[ok], want[ok], rtol=1e-5, atol=1e-4)
+    # a 2-D lat/lon template is the same call with a shape
+    ci2 = rp.cachedInterpolationForPoints(method, S.MEPS_PROJ, lon[:600], lat[:600], mx, my, out_shape=(20, 30))
+    got2, _ = ci2.interpolateValues(ci2.reduceInput(fld, S.MEPS_NX, S.MEPS_NY))
+    ok2 = ~np.isnan(got2.reshape(4, -1))
+    assert got2.shape == (4, 20, 30) and np.allclose(got2.reshape(4, -1)[ok2], got[:, 0, :600][ok2], rtol=1e-6)
