@@ -362,3 +362,27 @@ def mifi_get_values(method, infield, x, y):
           MIFI_INTERPOL_BICUBIC: lib.fimexcu_get_values_bicubic_f}[method]
     _lib.check(fn(a.ctypes.data, out.ctypes.data, float(x), float(y), ix, iy, iz), "mifi_get_values")
     return out
+
+
+def mifi_fill2d_f(field, relaxCrit=0.01, corrEff=1.6, maxLoop=100):
+    """mifi_fill2d_f / InterpolatorFill2d (include/fimex/interpolation.h:253, src/CDMInterpolator.cc:76-80): undefined cells of every
+    [ny][nx] level of `field` ([..., ny, nx]) are filled by Laplace relaxation.  numpy array: returns (filled copy, nChanged per level);
+    CUDA float32 tensor: filled IN PLACE on the device, returns (field, nChanged per level)."""
+    if _is_torch(field):
+        import torch
+        if not field.is_cuda or field.dtype != torch.float32 or not field.is_contiguous():
+            raise FimexCudaError("device path needs a contiguous float32 CUDA tensor")
+        ny, nx = field.shape[-2:]
+        nz = field.numel() // (nx * ny) if nx * ny else 0
+        cnt = (C.c_size_t * max(nz, 1))()
+        _lib.check(lib.fimexcu_fill2d_dev_f(nx, ny, nz, field.data_ptr(), relaxCrit, corrEff, maxLoop, cnt, _lib.current_stream_ptr()), "mifi_fill2d_f")
+        return field, list(cnt)[:nz]
+    a = np.array(field, dtype=np.float32, order="C", copy=True)
+    ny, nx = a.shape[-2:]
+    lev = a.reshape(-1, ny, nx)
+    counts = []
+    for k in range(lev.shape[0]):
+        n = C.c_size_t()
+        _lib.check(lib.fimexcu_fill2d_f(nx, ny, lev[k].ctypes.data, relaxCrit, corrEff, maxLoop, C.byref(n)), "mifi_fill2d_f")
+        counts.append(n.value)
+    return a, counts

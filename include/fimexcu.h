@@ -323,6 +323,17 @@ int fimexcu_get_values_log_log_f(const float* infieldA, const float* infieldB, f
 int fimexcu_get_values_two_level_dev_f(int method, const float* d_A, const float* d_B, float* d_out, size_t n, double a, double b, double x,
                                        void* stream);
 
+/* ---- fill2d pre / post-process -----------------------------------------------------------------------------
+ * Drop-in for mifi_fill2d_f (include/fimex/interpolation.h:253, src/interpolation.c:548-678), the `fill2d(relaxCrit, corrEff,
+ * maxLoop)` process that CDMInterpolator::getDataSlice runs level by level before / after the interpolation
+ * (src/CDMInterpolator.cc:76-80, 163-186): undefined cells are filled by Laplace relaxation.  Bit-exact: the sequential
+ * Gauss-Seidel sweeps run as a wavefront over anti-diagonals with several sweeps in flight (same dependency graph).
+ * HOST field [ny][nx] in place; *nChanged = number of undefined cells found. */
+int fimexcu_fill2d_f(size_t nx, size_t ny, float* field, float relaxCrit, float corrEff, size_t maxLoop, size_t* nChanged);
+/* the same for nz DEVICE-resident levels [nz][ny][nx] at once (processArray_'s loop over levels); nChanged_host: [nz] or NULL */
+int fimexcu_fill2d_dev_f(size_t nx, size_t ny, size_t nz, float* d_field, float relaxCrit, float corrEff, size_t maxLoop, size_t* nChanged_host,
+                         void* stream);
+
 /* ---- vertical coordinate converters -----------------------------------------------------------------------
  * The fields CDMVerticalInterpolator asks its ToVLevelConverter / VerticalConverter chain for (src/CDMVerticalInterpolator.cc:
  * 380-470), produced on the device so that they feed fimexcu_vertical_interpolate_dev_f as d_vcoord_in / d_vcoord_out without

@@ -1270,3 +1270,73 @@ int orc_pack_f(int dtype, const float* in, size_t n, double badValue, void* out)
     default: return 0;
     }
 }
+
+/* src/interpolation.c:548-678 */
+int orc_fill2d_f(size_t nx, size_t ny, float* field, float relaxCrit, float corrEff, size_t maxLoop, size_t* nChanged)
+{
+    const size_t total = nx * ny;
+    size_t i, x, y, n, nUnchanged;
+    double sum = 0, average, stddev = 0, crit;
+    float *w, *e;
+    if (total == 0)
+        return 1;
+    *nChanged = 0;
+    for (i = 0; i < total; ++i) { /* :556-563 */
+        if (isnan(field[i]))
+            (*nChanged)++;
+        else
+            sum += field[i];
+    }
+    nUnchanged = total - *nChanged;
+    if (nUnchanged == 0 || *nChanged == 0)
+        return 1;
+    w = (float*)malloc(total * sizeof(float));
+    e = (float*)malloc(total * sizeof(float));
+    average = sum / nUnchanged; /* :580 */
+    for (i = 0; i < total; ++i) { /* :586-596 */
+        if (isnan(field[i])) {
+            w[i] = 1.;
+            field[i] = average;
+        } else {
+            stddev += fabs(field[i] - average);
+            w[i] = 0.;
+        }
+    }
+    stddev /= nUnchanged;
+    crit = relaxCrit * stddev;
+    for (y = 1; y + 1 < ny; y++) /* :608-612 */
+        for (x = 1; x + 1 < nx; x++)
+            w[y * nx + x] *= corrEff;
+    for (n = 0; n < maxLoop; n++) { /* :621-669 */
+        for (y = 1; y + 1 < ny; y++)
+            for (x = 1; x + 1 < nx; x++) {
+                float* f = &field[y * nx + x];
+                e[y * nx + x] = (*(f + 1) + *(f - 1) + *(f + nx) + *(f - nx)) * 0.25 - *f;
+                (*f) += e[y * nx + x] * w[y * nx + x];
+            }
+        if ((n < (maxLoop - 5)) && (n % 10 == 0)) { /* size_t arithmetic: maxLoop < 5 wraps, as in the reference */
+            const float crtest = crit * corrEff;
+            size_t nbad = 0;
+            for (y = 1; y + 1 < ny && !nbad; y++)
+                for (x = 1; x + 1 < nx; x++)
+                    if (fabs(e[y * nx + x] * w[y * nx + x]) > crtest)
+                        nbad = 1;
+            if (nbad == 0) {
+                free(e);
+                free(w);
+                return 1;
+            }
+        }
+        for (y = 1; y + 1 < ny; y++) { /* :660-663 */
+            field[y * nx + 0] += (field[y * nx + 1] - field[y * nx + 0]) * w[y * nx + 0];
+            field[y * nx + (nx - 1)] += (field[y * nx + (nx - 2)] - field[y * nx + (nx - 1)]) * w[y * nx + (nx - 1)];
+        }
+        for (x = 0; x < nx; x++) { /* :664-667 */
+            field[0 * nx + x] += (field[1 * nx + x] - field[0 * nx + x]) * w[0 * nx + x];
+            field[(ny - 1) * nx + x] += (field[(ny - 2) * nx + x] - field[(ny - 1) * nx + x]) * w[(ny - 1) * nx + x];
+        }
+    }
+    free(e);
+    free(w);
+    return 1;
+}

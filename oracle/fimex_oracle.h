@@ -212,3 +212,8 @@ float orc_barometric_layer_thickness(float p_low_alti, float p_high_alti, float 
 int orc_unpack_f(int dtype, const void* in, size_t n, double badValue, float* out);
 int orc_unpack_scaled_f(int dtype, const void* in, size_t n, double fill, double scale, double offset, float* out);
 int orc_pack_f(int dtype, const float* in, size_t n, double badValue, void* out);
+
+/* mifi_fill2d_f (src/interpolation.c:548-678): undefined cells replaced by the solution of a Laplace relaxation (sequential
+ * Gauss-Seidel sweeps in row-major order with over-relaxation corrEff, borders extrapolated after every sweep, convergence
+ * tested after sweeps 0, 10, 20, ... below maxLoop-5).  In place; *nChanged = number of undefined cells found. */
+int orc_fill2d_f(size_t nx, size_t ny, float* field, float relaxCrit, float corrEff, size_t maxLoop, size_t* nChanged);

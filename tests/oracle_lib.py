@@ -92,6 +92,7 @@ def oracle():
         "orc_vcoord_transform_f": (None, [C.c_int, c_float_p, C.c_size_t, c_float_p]),
         "orc_virtual_temperature": (C.c_float, [C.c_float, C.c_float]),
         "orc_barometric_layer_thickness": (C.c_float, [C.c_float, C.c_float, C.c_float]),
+        "orc_fill2d_f": (C.c_int, [C.c_size_t, C.c_size_t, c_float_p, C.c_float, C.c_float, C.c_size_t, c_size_p]),
         "orc_unpack_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
         "orc_unpack_scaled_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
         "orc_pack_f": (C.c_int, [C.c_int, c_float_p, C.c_size_t, C.c_double, C.c_void_p]),
@@ -158,6 +159,7 @@ def ref(omp=False):
         "ref_cache_apply_seconds": (C.c_double, [C.c_void_p, c_float_p, C.c_size_t, C.c_int]),
         "ref_cache_destroy": (None, [C.c_void_p]),
         "ref_round_and_clamp": (C.c_size_t, [C.c_double, C.c_size_t, C.c_size_t, C.c_size_t]),
+        "mifi_fill2d_f": (C.c_int, [C.c_size_t, C.c_size_t, c_float_p, C.c_float, C.c_float, C.c_size_t, c_size_p]),
         "ref_unpack_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
         "ref_unpack_scaled_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
         "ref_pack_f": (C.c_int, [C.c_int, c_float_p, C.c_size_t, C.c_double, C.c_void_p]),

@@ -363,3 +363,26 @@ def test_packed_conversions_all_types_match_reference(oracle, ref, dtype):
             c, d = np.empty(n, T), np.empty(n, T)
             assert oracle.orc_pack_f(dtype, fp(v), n, bad, c.ctypes.data) == 1 and ref.ref_pack_f(dtype, fp(v), n, bad, d.ctypes.data) == 1
             assert np.array_equal(c, d)
+
+
+def _blob_field(rng, ny, nx, frac=0.15):
+    yy, xx = np.meshgrid(np.arange(ny), np.arange(nx), indexing="ij")
+    f = (280 + 15 * np.sin(xx / 9.0) * np.cos(yy / 7.0) + rng.normal(0, 1, (ny, nx))).astype(np.float32)
+    for _ in range(max(1, int(frac * nx * ny / 60))):
+        cy, cx, r = rng.integers(0, ny), rng.integers(0, nx), rng.integers(2, 7)
+        f[(yy - cy) ** 2 + (xx - cx) ** 2 <= r * r] = np.nan
+    return f
+
+
+@pytest.mark.parametrize("nx,ny,maxloop", [(61, 47, 100), (33, 80, 7), (20, 20, 3), (90, 12, 31)])
+def test_fill2d_restatement_matches_reference(oracle, ref, nx, ny, maxloop):
+    rng = np.random.default_rng(nx * ny + maxloop)
+    f = _blob_field(rng, ny, nx)
+    f[0, :5] = np.nan  # undefined cells on the border and in a corner
+    f[-1, -1] = np.nan
+    a, b = f.copy(), f.copy()
+    na, nb = C.c_size_t(), C.c_size_t()
+    assert oracle.orc_fill2d_f(nx, ny, fp(a), 0.01, 1.6, maxloop, C.byref(na)) == 1
+    ref.mifi_fill2d_f(nx, ny, fp(b), 0.01, 1.6, maxloop, C.byref(nb))
+    assert na.value == nb.value == int(np.isnan(f).sum())
+    assert np.array_equal(a, b) and not np.isnan(a).any()
