@@ -15,9 +15,9 @@
 // CTA that owns the level.  One CTA per level (levels are independent, processArray_ runs them in an OpenMP loop).  The sweeps
 // work on a diagonal-major copy of the level (cell (x,y) stored at [x+y][x]): an anti-diagonal and its four neighbour
 // diagonals are then contiguous rows, every warp access one line (in the row-major layout every lane hits its own sector and
-// the step is bound by the L1 tag stage: 13 us per step against 1.5 us); the ~150 KB a step touches stay in L1 / L2.  The two double-precision sums of the set-up (mean, mean absolute deviation) are added in
-// the reference's sequential order by one thread from shared-memory stages filled by the others: their roundings decide the
-// result, so the order cannot be changed.
+// the step is bound by the L1 tag stage: 13 us per step against 5.7 us); the ~150 KB a step touches stay in L1 / L2.
+// The two double-precision sums of the set-up (mean, mean absolute deviation) are added in the reference's sequential order by
+// one thread from shared-memory stages filled by the others: their roundings decide the result, so the order cannot be changed.
 #include "fxcu_common.h"
 
 #include <vector>

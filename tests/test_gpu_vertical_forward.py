@@ -424,3 +424,40 @@ def test_two_level_kernels_on_device_slabs(fx, oracle, name, method):
     _lib.check(_lib.lib.fimexcu_get_values_two_level_dev_f(method, dC.data_ptr(), dB.data_ptr(), dC.data_ptr(), n, 3.0, 9.0, 4.5, _lib.current_stream_ptr()), "x")
     torch.cuda.synchronize()
     assert _eq(dC.cpu().numpy(), want)
+
+
+def test_config5_full_size_properties(fx):
+    """BASELINE configs[4] at full horizontal size (65 hybrid levels x 4 members x 1069 x 949 -> 12 pressure levels, log): a field
+    that is linear in log(p) must come back as the same line evaluated at the target pressures (1e-5 relative, the tolerance of
+    BASELINE.json), levels below the surface follow the reference's extrapolation from the two lowest levels, and a random sample
+    of columns equals the oracle."""
+    import torch
+    from fimex_b200.vertical import verticalHybridPressure
+    from fimex_b200 import synthetic as S
+    g = np.load(os.path.join(GOLD, "reference_vertical.npz"))
+    ap, b = g["en_ap_pa"] * 0.01, g["en_b"]
+    nmem, ny, nx = 4, S.MEPS_NY, S.MEPS_NX
+    nI = nmem * ny * nx
+    levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50], dtype=np.float64)
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    yy = torch.arange(ny, device="cuda", dtype=torch.float32)[:, None]
+    xx = torch.arange(nx, device="cuda", dtype=torch.float32)[None, :]
+    h = 1250.0 * (1 + torch.sin(xx / 97.0) * torch.cos(yy / 131.0))  # smooth orography 0..2500 m
+    ps = (101325.0 - 12.0 * h)[None].repeat(nmem, 1, 1) + 300.0 * torch.randn((nmem, ny, nx), device="cuda", generator=gen)
+    ps = ps.reshape(1, nI).contiguous()
+    p = (torch.from_numpy(ap).cuda()[:, None] + torch.from_numpy(b).cuda()[:, None] * (ps.double() * 0.01)).float()  # [65][nI], the f32 column
+    alpha, beta = 250.0, 7.5
+    fld = (alpha + beta * torch.log(p.double())).float().reshape(1, 65, nI).contiguous()
+    out = verticalHybridPressure(ol.VINT_LOG, fld, ap, b, ps, levels, ps_scale=0.01)
+    torch.cuda.synchronize()
+    want = torch.from_numpy(alpha + beta * np.log(levels)).cuda().float()[None, :, None].expand(1, 12, nI)
+    # the first hybrid level of this fixture is the constant 10 hPa, so every target level lies inside or below the column
+    assert not torch.isnan(out).any()
+    rel = ((out - want).abs() / want.abs()).max().item()
+    assert rel < 1e-5, rel
+    # random sample of columns against the oracle (bit-exact masks, 1e-5 relative values)
+    idx = torch.randint(0, nI, (4000,), device="cuda", generator=gen)
+    f_s = fld[0][:, idx].cpu().numpy()[None]
+    p_s = p[:, idx].cpu().numpy()[None]
+    w = _oracle_vertical(ol.VINT_LOG, np.ascontiguousarray(f_s), np.ascontiguousarray(p_s), levels=levels)
+    assert _close(out[0][:, idx].cpu().numpy()[None], w)
