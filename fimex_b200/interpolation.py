@@ -79,6 +79,17 @@ class CachedInterpolationInterface:
         sub = a[:, r.yMin:r.yMin + self.inY, r.xMin:r.xMin + self.inX]
         return sub.contiguous() if _is_torch(sub) else np.ascontiguousarray(sub)
 
+    def sliceOutput(self, out, xStart=0, xSize=None, yStart=0, ySize=None):
+        """What getOutputDataSlice() (src/CachedInterpolation.cc:113-130) hands the caller: the requested x/y sub-window of the
+        full interpolated slab [.., outY, outX]; the other dimensions were already cut by getInputDataSlice()."""
+        a = out.reshape(-1, self.outY, self.outX)
+        xSize = self.outX - xStart if xSize is None else xSize
+        ySize = self.outY - yStart if ySize is None else ySize
+        if xStart + xSize > self.outX or yStart + ySize > self.outY:
+            raise FimexCudaError("requested output window lies outside the target grid")
+        sub = a[:, yStart:yStart + ySize, xStart:xStart + xSize]
+        return sub.contiguous() if _is_torch(sub) else np.ascontiguousarray(sub)
+
     def interpolateValues(self, inData, size=None, badValue=_NAN, fillValue=_NAN):
         """interpolateValues(inData, size, newSize) -> (outData, newSize).
         inData: [nz][inY][inX] f32 (numpy: host path; CUDA torch tensor: device path).  badValue/fillValue
