@@ -50,6 +50,9 @@ SIGNATURES = {
     "fimexcu_vcoord_pressure_integration_dev_f": (C.c_int, [vp, vp, C.c_double, vp, C.c_double, vp, vp, sz, sz, sz, sz, C.c_int, vp, C.c_double, vp, vp]),
     "fimexcu_fill2d_f": (C.c_int, [sz, sz, vp, C.c_float, C.c_float, sz, c_size_p]),
     "fimexcu_fill2d_dev_f": (C.c_int, [sz, sz, sz, vp, C.c_float, C.c_float, sz, vp, vp]),
+    "fimexcu_creepfill2d_f": (C.c_int, [sz, sz, vp, C.c_ushort, C.c_char, c_size_p]),
+    "fimexcu_creepfillval2d_f": (C.c_int, [sz, sz, vp, C.c_float, C.c_ushort, C.c_char, c_size_p]),
+    "fimexcu_creepfill2d_dev_f": (C.c_int, [sz, sz, sz, vp, C.c_int, C.c_float, C.c_ushort, C.c_char, vp, vp]),
     "fimexcu_unpack_dev_f": (C.c_int, [C.c_int, vp, sz, C.c_double, vp, vp]),
     "fimexcu_unpack_scaled_dev_f": (C.c_int, [C.c_int, vp, sz, C.c_double, C.c_double, C.c_double, vp, vp]),
     "fimexcu_pack_dev_f": (C.c_int, [C.c_int, vp, sz, C.c_double, vp, vp]),

@@ -218,6 +218,194 @@ __global__ void __launch_bounds__(FT) fill2d_kernel(const Fill2dParams P)
     }
 }
 
+// ---- creepfill (src/interpolation.c:680-810) ------------------------------------------------------------------------------------
+// Same wavefront as fill2d (a cell sees the west / north neighbours of this sweep, the east / south ones of the previous sweep;
+// here that includes the neighbours' WEIGHTS, which a fill switches from 0 to 1).  The reference stops after the first sweep that
+// changes nothing; such a sweep leaves a fixed point, so running the rest of a group of sweeps is harmless, and the group's
+// last sweep tells whether to go on.  Border cells are not touched by the sweeps.
+struct CreepParams {
+    float* field;       // [nz][ny][nx], in place
+    float* sf;          // diagonal-major scratch, see Fill2dParams
+    signed char* sw;    // weights: 0 undefined, setWeight defined, 1 filled
+    unsigned short* sr; // how often a cell was filled (defined cells start at `repeat`)
+    int nx, ny;
+    size_t level, slevel;
+    int use_mean;       // creepfill2d: first guess = field mean; creepfillval2d: defaultVal
+    float defaultVal;
+    unsigned short repeat;
+    signed char setWeight;
+    unsigned long long* nChanged;
+};
+
+// field[i] += field[j]*w[j]; field[i] /= (1 + w[j])  (:758-779), one application
+__device__ __forceinline__ float creep_border_step(float fi, float fj, int wj)
+{
+    return __fdiv_rn(__fadd_rn(fi, __fmul_rn(fj, static_cast<float>(wj))), static_cast<float>(1 + wj));
+}
+
+__global__ void __launch_bounds__(FT) creepfill_kernel(const CreepParams P)
+{
+    __shared__ double stage[FCHUNK];
+    __shared__ float s_default;
+    __shared__ unsigned long long s_nchg;
+    const int nx = P.nx, ny = P.ny, tid = threadIdx.x;
+    const size_t total = static_cast<size_t>(nx) * ny;
+    float* f = P.field + blockIdx.x * P.level;
+    float* sf = P.sf + blockIdx.x * P.slevel;
+    signed char* sw = P.sw + blockIdx.x * P.slevel;
+    unsigned short* sr = P.sr + blockIdx.x * P.slevel;
+    auto sk = [nx](int x, int y) { return static_cast<size_t>(x + y) * nx + x; };
+    const int repeat = P.repeat;
+
+    unsigned long long mine = 0;
+    for (size_t i = tid; i < total; i += FT)
+        mine += isnan(f[i]) ? 1u : 0u;
+    if (tid == 0)
+        s_nchg = 0;
+    __syncthreads();
+    if (mine)
+        atomicAdd(&s_nchg, mine);
+    __syncthreads();
+    const unsigned long long nChanged = s_nchg, nUnchanged = total - nChanged;
+    if (tid == 0)
+        P.nChanged[blockIdx.x] = nChanged;
+    if (nUnchanged == 0 || nChanged == 0)
+        return; // :687-690, :791
+    if (P.use_mean) { // float average = sum / nUnchanged with the f64 sum in index order (:783-794)
+        const double sum = sequential_sum(total, stage, [&](size_t i) {
+            const float v = f[i];
+            return isnan(v) ? 0. : static_cast<double>(v);
+        });
+        if (tid == 0)
+            s_default = __double2float_rn(__ddiv_rn(sum, static_cast<double>(nUnchanged)));
+    } else if (tid == 0) {
+        s_default = P.defaultVal;
+    }
+    __syncthreads();
+    const float first_guess = s_default;
+    for (size_t i = tid; i < total; i += FT) { // :703-715
+        const int y = static_cast<int>(i / nx), x = static_cast<int>(i - static_cast<size_t>(y) * nx);
+        const float v = f[i];
+        const bool undef = isnan(v);
+        sf[sk(x, y)] = undef ? first_guess : v;
+        sw[sk(x, y)] = undef ? static_cast<signed char>(0) : P.setWeight;
+        sr[sk(x, y)] = undef ? static_cast<unsigned short>(0) : P.repeat;
+    }
+    __syncthreads();
+
+    // ---- sweeps (:724-754) ----
+    unsigned long long l = 0;
+    while (l < nUnchanged) {
+        const int G = static_cast<int>(min(static_cast<unsigned long long>(GMAX), nUnchanged - l));
+        int changed = 0;
+        const int tmax = (nx + ny - 4) + 2 * (G - 1);
+        for (int t = 2; t <= tmax; ++t) {
+            for (int x0 = tid; x0 < nx; x0 += FT) {
+#pragma unroll
+                for (int g = 0; g < GMAX; ++g) {
+                    const int d = t - 2 * g;
+                    const int x = max(1, d - (ny - 2)) + x0;
+                    if (g < G && d >= 2 && x <= min(nx - 2, d - 1)) {
+                        const size_t i = static_cast<size_t>(d) * nx + x;
+                        if (sr[i] < repeat) {
+                            const int wE = sw[i + nx + 1], wW = sw[i - nx - 1], wS = sw[i + nx], wN = sw[i - nx];
+                            const size_t wsum = static_cast<size_t>(static_cast<long long>(wE + wW + wS + wN)); // int sum -> size_t, as in C
+                            if (wsum != 0) {
+                                const float nb = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(static_cast<float>(wE), sf[i + nx + 1]),
+                                                                               __fmul_rn(static_cast<float>(wW), sf[i - nx - 1])),
+                                                                     __fmul_rn(static_cast<float>(wS), sf[i + nx])),
+                                                           __fmul_rn(static_cast<float>(wN), sf[i - nx]));
+                                sf[i] = __fdiv_rn(__fadd_rn(sf[i], nb), static_cast<float>(1 + wsum));
+                                sw[i] = 1;
+                                sr[i] = static_cast<unsigned short>(sr[i] + 1);
+                                if (g == G - 1)
+                                    changed = 1;
+                            }
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        l += G;
+        if (!__syncthreads_or(changed))
+            break;
+    }
+
+    // ---- borders (:756-781): `repeat` rounds of columns, then rows; an undefined border cell (r == 0 < repeat) is pulled towards
+    // its inner neighbour every round.  The corners read a border cell of the same round, so their thread replays that cell.
+    if (repeat > 0) {
+        const int last = ny - 1;
+        float corner = 0.f;
+        bool corner_set = false;
+        if (tid < 4) {
+            const int cx = (tid & 1) ? nx - 1 : 0, cy = (tid & 2) ? last : 0; // the corner
+            const int by = (tid & 2) ? last - 1 : 1;                            // its column neighbour (cx, by): a west / east border cell
+            const int ix = (tid & 1) ? nx - 2 : 1;                              // that cell's inner neighbour (ix, by)
+            if (sr[sk(cx, cy)] < repeat) {
+                float fb = sf[sk(cx, by)];
+                int wb = sw[sk(cx, by)];
+                const bool b_undef = sr[sk(cx, by)] < repeat;
+                const float fi = sf[sk(ix, by)];
+                const int wi = sw[sk(ix, by)];
+                corner = sf[sk(cx, cy)];
+                for (int r = 0; r < repeat; ++r) {
+                    if (b_undef) { // the column loop of this round comes first (:757-768)
+                        fb = creep_border_step(fb, fi, wi);
+                        wb = 1;
+                    }
+                    corner = creep_border_step(corner, fb, wb);
+                }
+                corner_set = true;
+            }
+        }
+        __syncthreads(); // the corners have read their neighbours' first-guess values
+        if (corner_set)
+            sf[sk((tid & 1) ? nx - 1 : 0, (tid & 2) ? last : 0)] = corner;
+        for (int y = 1 + tid; y < ny - 1; y += FT) {
+            if (sr[sk(0, y)] < repeat) {
+                float v = sf[sk(0, y)];
+                const float fi = sf[sk(1, y)];
+                const int wi = sw[sk(1, y)];
+                for (int r = 0; r < repeat; ++r)
+                    v = creep_border_step(v, fi, wi);
+                sf[sk(0, y)] = v;
+            }
+            if (sr[sk(nx - 1, y)] < repeat) {
+                float v = sf[sk(nx - 1, y)];
+                const float fi = sf[sk(nx - 2, y)];
+                const int wi = sw[sk(nx - 2, y)];
+                for (int r = 0; r < repeat; ++r)
+                    v = creep_border_step(v, fi, wi);
+                sf[sk(nx - 1, y)] = v;
+            }
+        }
+        for (int x = 1 + tid; x < nx - 1; x += FT) {
+            if (sr[sk(x, 0)] < repeat) {
+                float v = sf[sk(x, 0)];
+                const float fi = sf[sk(x, 1)];
+                const int wi = sw[sk(x, 1)];
+                for (int r = 0; r < repeat; ++r)
+                    v = creep_border_step(v, fi, wi);
+                sf[sk(x, 0)] = v;
+            }
+            if (sr[sk(x, last)] < repeat) {
+                float v = sf[sk(x, last)];
+                const float fi = sf[sk(x, last - 1)];
+                const int wi = sw[sk(x, last - 1)];
+                for (int r = 0; r < repeat; ++r)
+                    v = creep_border_step(v, fi, wi);
+                sf[sk(x, last)] = v;
+            }
+        }
+        __syncthreads();
+    }
+    for (size_t i = tid; i < total; i += FT) {
+        const int y = static_cast<int>(i / nx), x = static_cast<int>(i - static_cast<size_t>(y) * nx);
+        f[i] = sf[sk(x, y)];
+    }
+}
+
 } // namespace fxcu
 
 using namespace fxcu;
@@ -287,6 +475,85 @@ int fimexcu_fill2d_f(size_t nx, size_t ny, float* field, float relaxCrit, float 
     if (nChanged)
         *nChanged = changed;
     return FIMEXCU_OK;
+}
+
+int fimexcu_creepfill2d_dev_f(size_t nx, size_t ny, size_t nz, float* d_field, int use_mean, float defaultVal, unsigned short repeat, char setWeight,
+                              size_t* nChanged_host, void* stream)
+{
+    clear_error();
+    if (!require_device())
+        return FIMEXCU_ERROR;
+    if (nx * ny == 0 || nz == 0)
+        return FIMEXCU_OK;
+    if (nx < 3 || ny < 3 || nx > 0x3fffffff || ny > 0x3fffffff || nx * ny > 0x7fffffffull)
+        FXCU_FAIL("fimexcu_creepfill2d: the grid must be at least 3 x 3 and smaller than 2^31 cells");
+    if (nz > 0x7fffffffull)
+        FXCU_FAIL("fimexcu_creepfill2d: too many levels");
+    if (!d_field)
+        FXCU_FAIL("fimexcu_creepfill2d: null field");
+    cudaStream_t s = as_stream(stream);
+    DevBuf sf, sw, sr, cnt;
+    const size_t slevel = (nx + ny - 1) * nx;
+    if (!sf.alloc(slevel * nz * sizeof(float), s) || !sw.alloc(slevel * nz, s) || !sr.alloc(slevel * nz * sizeof(unsigned short), s) ||
+        !cnt.alloc(nz * sizeof(unsigned long long), s))
+        return FIMEXCU_ERROR;
+    CreepParams P{};
+    P.field = d_field;
+    P.sf = sf.as<float>();
+    P.sw = sw.as<signed char>();
+    P.sr = sr.as<unsigned short>();
+    P.nx = static_cast<int>(nx);
+    P.ny = static_cast<int>(ny);
+    P.level = nx * ny;
+    P.slevel = slevel;
+    P.use_mean = use_mean ? 1 : 0;
+    P.defaultVal = defaultVal;
+    P.repeat = repeat;
+    P.setWeight = static_cast<signed char>(setWeight);
+    P.nChanged = cnt.as<unsigned long long>();
+    creepfill_kernel<<<static_cast<unsigned>(nz), FT, 0, s>>>(P);
+    FXCU_CUDA(cudaGetLastError());
+    if (nChanged_host) {
+        std::vector<unsigned long long> h(nz);
+        FXCU_CUDA(cudaMemcpyAsync(h.data(), cnt.p, nz * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+        FXCU_CUDA(cudaStreamSynchronize(s));
+        for (size_t k = 0; k < nz; ++k)
+            nChanged_host[k] = static_cast<size_t>(h[k]);
+    }
+    return FIMEXCU_OK;
+}
+
+static int creepfill_host(size_t nx, size_t ny, float* field, int use_mean, float defaultVal, unsigned short repeat, char setWeight, size_t* nChanged)
+{
+    if (!require_device())
+        return FIMEXCU_ERROR;
+    if (nx * ny == 0)
+        return FIMEXCU_OK;
+    const size_t bytes = nx * ny * sizeof(float);
+    DevBuf d;
+    if (!d.alloc(bytes, nullptr))
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(d.p, field, bytes, cudaMemcpyHostToDevice, nullptr));
+    size_t changed = 0;
+    if (fimexcu_creepfill2d_dev_f(nx, ny, 1, d.as<float>(), use_mean, defaultVal, repeat, setWeight, &changed, nullptr) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(field, d.p, bytes, cudaMemcpyDeviceToHost, nullptr));
+    FXCU_CUDA(cudaStreamSynchronize(nullptr));
+    if (nChanged)
+        *nChanged = changed;
+    return FIMEXCU_OK;
+}
+
+int fimexcu_creepfill2d_f(size_t nx, size_t ny, float* field, unsigned short repeat, char setWeight, size_t* nChanged)
+{
+    clear_error();
+    return creepfill_host(nx, ny, field, 1, 0.f, repeat, setWeight, nChanged);
+}
+
+int fimexcu_creepfillval2d_f(size_t nx, size_t ny, float* field, float defaultVal, unsigned short repeat, char setWeight, size_t* nChanged)
+{
+    clear_error();
+    return creepfill_host(nx, ny, field, 0, defaultVal, repeat, setWeight, nChanged);
 }
 
 } // extern "C"

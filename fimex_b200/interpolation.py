@@ -397,3 +397,34 @@ def mifi_fill2d_f(field, relaxCrit=0.01, corrEff=1.6, maxLoop=100):
         _lib.check(lib.fimexcu_fill2d_f(nx, ny, lev[k].ctypes.data, relaxCrit, corrEff, maxLoop, C.byref(n)), "mifi_fill2d_f")
         counts.append(n.value)
     return a, counts
+
+
+def mifi_creepfill2d_f(field, repeat=20, setWeight=2, defaultValue=None):
+    """mifi_creepfill2d_f (defaultValue None: first guess = the level's mean) / mifi_creepfillval2d_f
+    (include/fimex/interpolation.h:275, 298; InterpolatorCreepFill2d / InterpolatorCreepFillVal2d, src/CDMInterpolator.cc:82-92) on every
+    [ny][nx] level of `field`.  numpy array: returns (filled copy, nChanged per level); CUDA float32 tensor: filled in place."""
+    use_mean = 1 if defaultValue is None else 0
+    dv = 0.0 if defaultValue is None else float(defaultValue)
+    w = bytes([setWeight & 0xff])
+    if _is_torch(field):
+        import torch
+        if not field.is_cuda or field.dtype != torch.float32 or not field.is_contiguous():
+            raise FimexCudaError("device path needs a contiguous float32 CUDA tensor")
+        ny, nx = field.shape[-2:]
+        nz = field.numel() // (nx * ny) if nx * ny else 0
+        cnt = (C.c_size_t * max(nz, 1))()
+        _lib.check(lib.fimexcu_creepfill2d_dev_f(nx, ny, nz, field.data_ptr(), use_mean, dv, repeat, w, cnt, _lib.current_stream_ptr()),
+                   "mifi_creepfill2d_f")
+        return field, list(cnt)[:nz]
+    a = np.array(field, dtype=np.float32, order="C", copy=True)
+    ny, nx = a.shape[-2:]
+    lev = a.reshape(-1, ny, nx)
+    counts = []
+    for k in range(lev.shape[0]):
+        n = C.c_size_t()
+        if use_mean:
+            _lib.check(lib.fimexcu_creepfill2d_f(nx, ny, lev[k].ctypes.data, repeat, w, C.byref(n)), "mifi_creepfill2d_f")
+        else:
+            _lib.check(lib.fimexcu_creepfillval2d_f(nx, ny, lev[k].ctypes.data, dv, repeat, w, C.byref(n)), "mifi_creepfillval2d_f")
+        counts.append(n.value)
+    return a, counts

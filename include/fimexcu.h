@@ -334,6 +334,15 @@ int fimexcu_fill2d_f(size_t nx, size_t ny, float* field, float relaxCrit, float 
 int fimexcu_fill2d_dev_f(size_t nx, size_t ny, size_t nz, float* d_field, float relaxCrit, float corrEff, size_t maxLoop, size_t* nChanged_host,
                          void* stream);
 
+/* Drop-ins for mifi_creepfill2d_f / mifi_creepfillval2d_f (include/fimex/interpolation.h:275, 298, src/interpolation.c:680-810),
+ * the `creepfill2d(repeat, setWeight)` / `creepfillval2d(repeat, setWeight, defaultValue)` processes
+ * (src/CDMInterpolator.cc:82-92).  Bit-exact, same wavefront form as fill2d.  HOST field [ny][nx] in place. */
+int fimexcu_creepfill2d_f(size_t nx, size_t ny, float* field, unsigned short repeat, char setWeight, size_t* nChanged);
+int fimexcu_creepfillval2d_f(size_t nx, size_t ny, float* field, float defaultVal, unsigned short repeat, char setWeight, size_t* nChanged);
+/* nz DEVICE-resident levels at once; use_mean != 0: creepfill2d (first guess = the level's mean), else creepfillval2d(defaultVal) */
+int fimexcu_creepfill2d_dev_f(size_t nx, size_t ny, size_t nz, float* d_field, int use_mean, float defaultVal, unsigned short repeat, char setWeight,
+                              size_t* nChanged_host, void* stream);
+
 /* ---- vertical coordinate converters -----------------------------------------------------------------------
  * The fields CDMVerticalInterpolator asks its ToVLevelConverter / VerticalConverter chain for (src/CDMVerticalInterpolator.cc:
  * 380-470), produced on the device so that they feed fimexcu_vertical_interpolate_dev_f as d_vcoord_in / d_vcoord_out without

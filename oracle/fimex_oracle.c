@@ -1340,3 +1340,117 @@ int orc_fill2d_f(size_t nx, size_t ny, float* field, float relaxCrit, float corr
     free(w);
     return 1;
 }
+
+/* src/interpolation.c:680-775 */
+static int orc_creepfill_impl(size_t nx, size_t ny, float* field, float defaultVal, unsigned short repeat, char setWeight, size_t nChanged)
+{
+    const size_t total = nx * ny;
+    size_t i, x, y, l, nUnchanged, changedInLoop;
+    char* w;
+    unsigned short* r;
+    if (total == 0)
+        return 1;
+    nUnchanged = total - nChanged;
+    if (nUnchanged == 0 || nChanged == 0)
+        return 1;
+    w = (char*)malloc(total);
+    r = (unsigned short*)malloc(total * sizeof(unsigned short));
+    for (i = 0; i < total; ++i) { /* :703-715 */
+        if (isnan(field[i])) {
+            w[i] = 0;
+            r[i] = 0;
+            field[i] = defaultVal;
+        } else {
+            w[i] = setWeight;
+            r[i] = repeat;
+        }
+    }
+    l = 0;
+    changedInLoop = 1;
+    while ((changedInLoop > 0) && (l < nUnchanged)) { /* :724-754 */
+        changedInLoop = 0;
+        l++;
+        for (y = 1; y + 1 < ny; y++)
+            for (x = 1; x + 1 < nx; x++) {
+                float* f = &field[y * nx + x];
+                unsigned short* rr = &r[y * nx + x];
+                char* ww = &w[y * nx + x];
+                if (*rr < repeat) {
+                    size_t wFieldSum = *(ww + 1) + *(ww - 1) + *(ww + nx) + *(ww - nx);
+                    if (wFieldSum != 0) {
+                        (*f) += *(ww + 1) * *(f + 1) + *(ww - 1) * *(f - 1) + *(ww + nx) * *(f + nx) + *(ww - nx) * *(f - nx);
+                        (*f) /= (1 + wFieldSum);
+                        (*ww) = 1;
+                        (*rr)++;
+                        changedInLoop++;
+                    }
+                }
+            }
+    }
+    for (l = 0; l < repeat; l++) { /* :756-781 */
+        for (y = 1; y + 1 < ny; y++) {
+            if (r[y * nx + 0] < repeat) {
+                field[y * nx + 0] += field[y * nx + 1] * w[y * nx + 1];
+                field[y * nx + 0] /= (1 + w[y * nx + 1]);
+                w[y * nx + 0] = 1;
+            }
+            if (r[y * nx + (nx - 1)] < repeat) {
+                field[y * nx + (nx - 1)] += field[y * nx + (nx - 2)] * w[y * nx + (nx - 2)];
+                field[y * nx + (nx - 1)] /= (1 + w[y * nx + (nx - 2)]);
+                w[y * nx + (nx - 1)] = 1;
+            }
+        }
+        for (x = 0; x < nx; x++) {
+            if (r[0 * nx + x] < repeat) {
+                field[0 * nx + x] += field[1 * nx + x] * w[1 * nx + x];
+                field[0 * nx + x] /= (1 + w[1 * nx + x]);
+                w[0 * nx + x] = 1;
+            }
+            if (r[(ny - 1) * nx + x] < repeat) {
+                field[(ny - 1) * nx + x] += field[(ny - 2) * nx + x] * w[(ny - 2) * nx + x];
+                field[(ny - 1) * nx + x] /= (1 + w[(ny - 2) * nx + x]);
+                w[(ny - 1) * nx + x] = 1;
+            }
+        }
+    }
+    free(r);
+    free(w);
+    return 1;
+}
+
+/* :777-797 */
+int orc_creepfill2d_f(size_t nx, size_t ny, float* field, unsigned short repeat, char setWeight, size_t* nChanged)
+{
+    const size_t total = nx * ny;
+    size_t i, nUnchanged;
+    double sum = 0;
+    float average;
+    if (total == 0)
+        return 1;
+    *nChanged = 0;
+    for (i = 0; i < total; ++i) {
+        if (isnan(field[i]))
+            (*nChanged)++;
+        else
+            sum += field[i];
+    }
+    nUnchanged = total - *nChanged;
+    if (nUnchanged == 0)
+        return 1;
+    average = sum / nUnchanged;
+    return orc_creepfill_impl(nx, ny, field, average, repeat, setWeight, *nChanged);
+}
+
+/* :799-810 */
+int orc_creepfillval2d_f(size_t nx, size_t ny, float* field, float defaultVal, unsigned short repeat, char setWeight, size_t* nChanged)
+{
+    const size_t total = nx * ny;
+    size_t i;
+    if (total == 0)
+        return 1;
+    *nChanged = 0;
+    for (i = 0; i < total; ++i)
+        if (isnan(field[i]))
+            (*nChanged)++;
+    return orc_creepfill_impl(nx, ny, field, defaultVal, repeat, setWeight, *nChanged);
+}

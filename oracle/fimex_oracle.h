@@ -217,3 +217,10 @@ int orc_pack_f(int dtype, const float* in, size_t n, double badValue, void* out)
  * Gauss-Seidel sweeps in row-major order with over-relaxation corrEff, borders extrapolated after every sweep, convergence
  * tested after sweeps 0, 10, 20, ... below maxLoop-5).  In place; *nChanged = number of undefined cells found. */
 int orc_fill2d_f(size_t nx, size_t ny, float* field, float relaxCrit, float corrEff, size_t maxLoop, size_t* nChanged);
+
+/* mifi_creepfill2d_f / mifi_creepfillval2d_f (src/interpolation.c:680-810): undefined cells take the weighted mean of their
+ * defined 4-neighbours and their own first guess (field mean resp. defaultVal), sweep after sweep in row-major order (a cell
+ * filled in this sweep already counts for its east and south neighbours), every cell at most `repeat` times, until a sweep
+ * changes nothing; borders afterwards from their inner neighbours. */
+int orc_creepfill2d_f(size_t nx, size_t ny, float* field, unsigned short repeat, char setWeight, size_t* nChanged);
+int orc_creepfillval2d_f(size_t nx, size_t ny, float* field, float defaultVal, unsigned short repeat, char setWeight, size_t* nChanged);

@@ -93,6 +93,8 @@ def oracle():
         "orc_virtual_temperature": (C.c_float, [C.c_float, C.c_float]),
         "orc_barometric_layer_thickness": (C.c_float, [C.c_float, C.c_float, C.c_float]),
         "orc_fill2d_f": (C.c_int, [C.c_size_t, C.c_size_t, c_float_p, C.c_float, C.c_float, C.c_size_t, c_size_p]),
+        "orc_creepfill2d_f": (C.c_int, [C.c_size_t, C.c_size_t, c_float_p, C.c_ushort, C.c_char, c_size_p]),
+        "orc_creepfillval2d_f": (C.c_int, [C.c_size_t, C.c_size_t, c_float_p, C.c_float, C.c_ushort, C.c_char, c_size_p]),
         "orc_unpack_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
         "orc_unpack_scaled_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
         "orc_pack_f": (C.c_int, [C.c_int, c_float_p, C.c_size_t, C.c_double, C.c_void_p]),
@@ -160,6 +162,8 @@ def ref(omp=False):
         "ref_cache_destroy": (None, [C.c_void_p]),
         "ref_round_and_clamp": (C.c_size_t, [C.c_double, C.c_size_t, C.c_size_t, C.c_size_t]),
         "mifi_fill2d_f": (C.c_int, [C.c_size_t, C.c_size_t, c_float_p, C.c_float, C.c_float, C.c_size_t, c_size_p]),
+        "mifi_creepfill2d_f": (C.c_int, [C.c_size_t, C.c_size_t, c_float_p, C.c_ushort, C.c_char, c_size_p]),
+        "mifi_creepfillval2d_f": (C.c_int, [C.c_size_t, C.c_size_t, c_float_p, C.c_float, C.c_ushort, C.c_char, c_size_p]),
         "ref_unpack_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, c_float_p]),
         "ref_unpack_scaled_f": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_double, c_float_p]),
         "ref_pack_f": (C.c_int, [C.c_int, c_float_p, C.c_size_t, C.c_double, C.c_void_p]),

@@ -77,3 +77,52 @@ def test_fill2d_many_levels_on_device_and_trivial_levels(fx):
 def test_fill2d_rejects_degenerate_grids(fx):
     with pytest.raises(Exception):
         fx.mifi_fill2d_f(np.full((2, 40), np.nan, np.float32))
+
+
+def _oracle_creep(f, repeat, weight, default=None):
+    a = f.copy()
+    n = C.c_size_t()
+    w = bytes([weight])
+    if default is None:
+        assert ol.oracle().orc_creepfill2d_f(f.shape[1], f.shape[0], fp(a), repeat, w, C.byref(n)) == 1
+    else:
+        assert ol.oracle().orc_creepfillval2d_f(f.shape[1], f.shape[0], fp(a), default, repeat, w, C.byref(n)) == 1
+    return a, n.value
+
+
+@pytest.mark.parametrize("nx,ny,repeat,weight", [(61, 47, 20, 2), (33, 80, 1, 1), (20, 20, 5, 2), (90, 12, 20, 4), (3, 3, 3, 2), (128, 97, 20, 2),
+                                                  (75, 64, 0, 2), (1100, 37, 7, 3)])
+@pytest.mark.parametrize("default", [None, 271.5])
+def test_creepfill_vs_oracle(fx, nx, ny, repeat, weight, default):
+    rng = np.random.default_rng(nx * ny + repeat)
+    f = _blob_field(rng, ny, nx, frac=0.3)
+    f[0, :5] = np.nan
+    f[-1, -1] = np.nan
+    f[ny // 2, 0] = np.nan
+    f[1, 0] = np.nan
+    f[-2, -1] = np.nan
+    if nx * ny == 9:
+        f = rng.normal(280, 5, (3, 3)).astype(np.float32)
+        f[1, 1] = f[0, 0] = f[1, 0] = np.nan
+    want, nwant = _oracle_creep(f, repeat, weight, default)
+    got, counts = fx.mifi_creepfill2d_f(f, repeat, weight, default)
+    assert counts == [nwant] and np.array_equal(got, want, equal_nan=True)
+
+
+def test_creepfill_many_levels_on_device(fx):
+    import torch
+    rng = np.random.default_rng(14)
+    nz, ny, nx = 6, 59, 83
+    fld = np.stack([_blob_field(rng, ny, nx, frac=0.1 + 0.08 * k) for k in range(nz)])
+    fld[2] = np.nan
+    fld[3] = np.float32(5.0)
+    fld[4, 10:50, 20:70] = np.nan
+    fld[5, :, :30] = np.nan  # everything west of a line: the fill creeps a long way, border cells included
+    want = np.empty_like(fld)
+    nwant = []
+    for k in range(nz):
+        want[k], n = _oracle_creep(fld[k], 20, 2)
+        nwant.append(n)
+    out, counts = fx.mifi_creepfill2d_f(torch.from_numpy(fld).cuda(), 20, 2)
+    torch.cuda.synchronize()
+    assert counts == nwant and np.array_equal(out.cpu().numpy(), want, equal_nan=True)

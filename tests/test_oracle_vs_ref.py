@@ -386,3 +386,28 @@ def test_fill2d_restatement_matches_reference(oracle, ref, nx, ny, maxloop):
     ref.mifi_fill2d_f(nx, ny, fp(b), 0.01, 1.6, maxloop, C.byref(nb))
     assert na.value == nb.value == int(np.isnan(f).sum())
     assert np.array_equal(a, b) and not np.isnan(a).any()
+
+
+@pytest.mark.parametrize("nx,ny,repeat,weight", [(61, 47, 20, 2), (33, 80, 1, 1), (20, 20, 5, 2), (90, 12, 20, 4), (3, 3, 3, 2)])
+def test_creepfill_restatement_matches_reference(oracle, ref, nx, ny, repeat, weight):
+    rng = np.random.default_rng(nx * ny + repeat)
+    f = _blob_field(rng, ny, nx, frac=0.3)
+    f[0, :5] = np.nan
+    f[-1, -1] = np.nan
+    f[ny // 2, 0] = np.nan
+    f[1, 0] = np.nan
+    if nx * ny == 9:
+        f = rng.normal(280, 5, (3, 3)).astype(np.float32)
+        f[1, 1] = f[0, 0] = f[1, 0] = np.nan
+    w = bytes([weight])
+    for kind in ("mean", "val"):
+        a, b = f.copy(), f.copy()
+        na, nb = C.c_size_t(), C.c_size_t()
+        if kind == "mean":
+            assert oracle.orc_creepfill2d_f(nx, ny, fp(a), repeat, w, C.byref(na)) == 1
+            ref.mifi_creepfill2d_f(nx, ny, fp(b), repeat, w, C.byref(nb))
+        else:
+            assert oracle.orc_creepfillval2d_f(nx, ny, fp(a), 271.5, repeat, w, C.byref(na)) == 1
+            ref.mifi_creepfillval2d_f(nx, ny, fp(b), 271.5, repeat, w, C.byref(nb))
+        assert na.value == nb.value == int(np.isnan(f).sum())
+        assert np.array_equal(a, b) and not np.isnan(a).any()
