@@ -5,10 +5,12 @@
 //   include/fimex/CDMException.h:36-41          CDMException : std::runtime_error
 //   include/fimex/CachedInterpolation.h:42-112  ReducedInterpolationDomain, CachedInterpolationInterface (without the CDM slicing helpers)
 //   include/fimex/reproject.h:34-47             reproject::Matrix
+//   include/fimex/CDMInterpolator.h:45-52       InterpolatorProcess2d
 // Define FIMEXCU_WITH_FIMEX_HEADERS to compile against the real headers instead.
 #pragma once
 #ifdef FIMEXCU_WITH_FIMEX_HEADERS
 #include "fimex/CDMException.h"
+#include "fimex/CDMInterpolator.h"
 #include "fimex/CachedInterpolation.h"
 #include "fimex/CachedVectorReprojection.h"
 #include "fimex/SharedArray.h"
@@ -56,6 +58,12 @@ protected:
     ReducedInterpolationDomain_p reducedDomain_;
 };
 typedef std::shared_ptr<CachedInterpolationInterface> CachedInterpolationInterface_p;
+
+class InterpolatorProcess2d {
+public:
+    virtual void operator()(float* array, size_t nx, size_t ny) = 0;
+    virtual ~InterpolatorProcess2d() {}
+};
 
 namespace reproject {
 struct Matrix {

@@ -3,6 +3,7 @@
 // (tests/test_gpu_host_cpp.py), writes the results next to it; the driver compares them with the oracle.
 //   file layout (little endian): int32 method, inX, inY, outX, outY, nz; f64 px[out], py[out]; f32 u[nz*in], v[nz*in]; f64 matrix[out*3]
 #include "CudaCachedInterpolation.h"
+#include "CudaInterpolatorProcess2d.h"
 
 #include <cstdint>
 #include <cstdio>
@@ -13,8 +14,53 @@ using namespace MetNoFimex;
 
 static bool read_all(FILE* f, void* p, size_t bytes) { return bytes == 0 || fread(p, 1, bytes, f) == bytes; }
 
+// host_selftest fill case.bin result.bin -- the fill functors the way processArray_ drives them (src/CDMInterpolator.cc:163-186):
+//   case: int32 kind (0 fill2d, 1 creepfill2d, 2 creepfillval2d), nx, ny, nz; f32 p0, p1, p2; f32 field[nz*ny*nx]
+//         fill2d: p0 relaxCrit, p1 corrEff, p2 maxLoop; creepfill: p0 repeat, p1 setWeight, p2 defaultValue
+//   result: field after operator() level by level, then field after processSlab()
+static int fill_mode(const char* in_path, const char* out_path)
+{
+    FILE* f = fopen(in_path, "rb");
+    if (!f)
+        return 2;
+    int32_t hdr[4];
+    float p[3];
+    if (!read_all(f, hdr, sizeof(hdr)) || !read_all(f, p, sizeof(p)))
+        return 2;
+    const size_t nx = hdr[1], ny = hdr[2], nz = hdr[3], n = nx * ny * nz;
+    std::vector<float> a(n), b;
+    if (!read_all(f, a.data(), n * 4))
+        return 2;
+    fclose(f);
+    b = a;
+    try {
+        std::shared_ptr<CudaInterpolatorProcess2d> proc;
+        if (hdr[0] == 0)
+            proc = std::make_shared<CudaInterpolatorFill2d>(p[0], p[1], static_cast<size_t>(p[2]));
+        else if (hdr[0] == 1)
+            proc = std::make_shared<CudaInterpolatorCreepFill2d>(static_cast<unsigned short>(p[0]), static_cast<char>(p[1]));
+        else
+            proc = std::make_shared<CudaInterpolatorCreepFillVal2d>(static_cast<unsigned short>(p[0]), static_cast<char>(p[1]), p[2]);
+        InterpolatorProcess2d& base = *proc; // the reference holds them as InterpolatorProcess2d_p
+        for (size_t z = 0; z < nz; ++z)
+            base(a.data() + z * nx * ny, nx, ny);
+        proc->processSlab(b.data(), n, nx, ny);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "exception: %s\n", e.what());
+        return 6;
+    }
+    FILE* o = fopen(out_path, "wb");
+    fwrite(a.data(), 4, n, o);
+    fwrite(b.data(), 4, n, o);
+    fclose(o);
+    printf("host_selftest fill ok\n");
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
+    if (argc == 4 && std::strcmp(argv[1], "fill") == 0)
+        return fill_mode(argv[2], argv[3]);
     if (argc != 3) {
         fprintf(stderr, "usage: host_selftest case.bin result.bin\n");
         return 2;

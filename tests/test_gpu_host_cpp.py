@@ -53,3 +53,48 @@ def test_cpp_glue_matches_oracle(tmp_path, method):
     ol.oracle().orc_vector_reproject_values_by_matrix_f(dp(m3), out_x * out_y, fp(wu), fp(wv), nz)
     for g, w in ((got[0], wu), (got[1], wv)):
         assert np.array_equal(np.isnan(g), np.isnan(w)) and np.array_equal(g[~np.isnan(g)], w[~np.isnan(w)])
+
+
+def test_process_glue_compiles_against_the_reference_headers():
+    inc = "/root/reference/include"
+    if not os.path.isdir(inc):
+        pytest.skip("reference headers not present")
+    r = subprocess.run(["g++", "-std=c++20", "-fsyntax-only", "-DFIMEXCU_WITH_FIMEX_HEADERS", "-I" + inc, "-I" + os.path.join(ROOT, "include"),
+                        "-x", "c++", os.path.join(ROOT, "fimex_b200", "host", "CudaInterpolatorProcess2d.h")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,params", [(0, (0.01, 1.6, 100)), (1, (20, 2, 0)), (2, (5, 3, 271.5))])
+def test_cpp_fill_functors_match_oracle(tmp_path, kind, params):
+    """InterpolatorFill2d / InterpolatorCreepFill2d / InterpolatorCreepFillVal2d over the C ABI, level by level (operator()) and
+    as one slab (processArray_), against the oracle restatements"""
+    import ctypes as C
+    assert os.path.exists(EXE)
+    rng = np.random.default_rng(kind)
+    nz, ny, nx = 3, 41, 67
+    yy, xx = np.meshgrid(np.arange(ny), np.arange(nx), indexing="ij")
+    fld = (280 + 10 * np.sin(xx / 9.0) * np.cos(yy / 7.0))[None].repeat(nz, 0).astype(np.float32) + rng.normal(0, 1, (nz, ny, nx)).astype(np.float32)
+    for k in range(nz):
+        for _ in range(6):
+            cy, cx, r = rng.integers(0, ny), rng.integers(0, nx), rng.integers(2, 7)
+            fld[k][(yy - cy) ** 2 + (xx - cx) ** 2 <= r * r] = np.nan
+    want = fld.copy()
+    o = ol.oracle()
+    for k in range(nz):
+        n = C.c_size_t()
+        if kind == 0:
+            o.orc_fill2d_f(nx, ny, fp(want[k]), params[0], params[1], int(params[2]), C.byref(n))
+        elif kind == 1:
+            o.orc_creepfill2d_f(nx, ny, fp(want[k]), int(params[0]), bytes([int(params[1])]), C.byref(n))
+        else:
+            o.orc_creepfillval2d_f(nx, ny, fp(want[k]), params[2], int(params[0]), bytes([int(params[1])]), C.byref(n))
+    case, res = tmp_path / "fill.bin", tmp_path / "fill_out.bin"
+    with open(case, "wb") as f:
+        np.array([kind, nx, ny, nz], dtype=np.int32).tofile(f)
+        np.array(params, dtype=np.float32).tofile(f)
+        fld.tofile(f)
+    r = subprocess.run([EXE, "fill", str(case), str(res)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    out = np.fromfile(res, dtype=np.float32).reshape(2, nz, ny, nx)
+    assert np.array_equal(out[0], want) and np.array_equal(out[1], want)
