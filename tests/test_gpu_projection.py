@@ -235,3 +235,27 @@ def test_point_list_and_cross_section_extraction(rp, method):
     got2, _ = ci2.interpolateValues(ci2.reduceInput(fld, S.MEPS_NX, S.MEPS_NY))
     ok2 = ~np.isnan(got2.reshape(4, -1))
     assert got2.shape == (4, 20, 30) and np.allclose(got2.reshape(4, -1)[ok2], got[:, 0, :600][ok2], rtol=1e-6)
+
+
+def test_device_resident_reprojection_entry_points(rp):
+    """fimexcu_reproject_axes_dev / fimexcu_reproject_values_dev / fimexcu_synchronize: the same numbers as the host-pointer entry
+    points, with the results left on the device"""
+    import torch
+    from fimex_b200 import _lib, synthetic as S
+    lib = _lib.lib
+    lon, lat = S.target_axes("T2")
+    x, y = rp.reproject_axes(S.LATLON_PROJ, S.MEPS_PROJ, lon, lat)
+    dx = torch.empty((lat.size, lon.size), dtype=torch.float64, device="cuda")
+    dy = torch.empty_like(dx)
+    _lib.check(lib.fimexcu_reproject_axes_dev(S.LATLON_PROJ.encode(), S.MEPS_PROJ.encode(), lon.ctypes.data, lat.ctypes.data, lon.size, lat.size,
+                                              dx.data_ptr(), dy.data_ptr(), _lib.current_stream_ptr()), "reproject_axes_dev")
+    _lib.check(lib.fimexcu_synchronize(), "synchronize")
+    assert np.array_equal(dx.cpu().numpy(), x) and np.array_equal(dy.cpu().numpy(), y)
+    # points back to lon/lat on the device, in place
+    _lib.check(lib.fimexcu_reproject_values_dev(S.MEPS_PROJ.encode(), S.LATLON_PROJ.encode(), dx.data_ptr(), dy.data_ptr(), dx.numel(),
+                                                _lib.current_stream_ptr()), "reproject_values_dev")
+    _lib.check(lib.fimexcu_synchronize(), "synchronize")
+    bx, by = rp.reproject_values(S.MEPS_PROJ, S.LATLON_PROJ, x.ravel().copy(), y.ravel().copy())
+    assert np.array_equal(dx.cpu().numpy().ravel(), bx) and np.array_equal(dy.cpu().numpy().ravel(), by)
+    lon2, lat2 = np.meshgrid(lon, lat)
+    assert np.abs(dx.cpu().numpy() - lon2).max() < 1e-9 and np.abs(dy.cpu().numpy() - lat2).max() < 1e-9
