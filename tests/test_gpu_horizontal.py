@@ -404,3 +404,41 @@ def test_packed_i16_rounding_and_wrap(fx):
         ci = fx.createCachedInterpolation("x", "y", method, px, py, in_x, in_y, out_x, out_y)
         got = ci.interpolateValuesPacked(ci.reduceInput(raw, in_x, in_y), 9999.0)
         assert np.array_equal(got, want), method
+
+
+def test_concurrent_host_threads_share_a_cache(fx):
+    """The reference calls getDataSlice from OpenMP threads (src/io/netcdf/NetCDF_CDMWriter.cc:599-618): several host threads
+    use ONE cache at the same time through the host-pointer entry points (ctypes releases the GIL); every thread must get the
+    bit-exact result and its own error state."""
+    import threading
+    rng = np.random.default_rng(99)
+    in_x, in_y, out_x, out_y, nz = 101, 87, 203, 167, 6
+    px, py = _tables(rng, in_x, in_y, out_x * out_y)
+    ci = fx.createCachedInterpolation("x", "y", ol.BILINEAR, px, py, in_x, in_y, out_x, out_y)
+    fields = [rng.normal(size=(nz, in_y, in_x)).astype(np.float32) for _ in range(6)]
+    wants = [ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, f)[0] for f in fields]
+    results, errors = [None] * len(fields), []
+
+    def work(k):
+        try:
+            for _ in range(5):
+                out, _ = ci.interpolateValues(ci.reduceInput(fields[k], in_x, in_y))
+                packed = ci.interpolateValuesPacked(np.zeros((1, ci.getInY(), ci.getInX()), np.int16), -32767.0)
+                assert packed.shape == (1, out_y, out_x)
+            results[k] = out
+            if k == 0:  # an error raised in one thread must not leak into the others' error state
+                try:
+                    fx.createCachedInterpolation("x", "y", 99, px, py, in_x, in_y, out_x, out_y)
+                except Exception as exc:
+                    assert "unknown interpolation" in str(exc)
+        except Exception as exc:  # noqa: BLE001
+            errors.append((k, repr(exc)))
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(len(fields))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for k in range(len(fields)):
+        assert _eq(results[k], wants[k]), k
