@@ -115,6 +115,39 @@ __global__ void __launch_bounds__(256) vcoord_transform_kernel(int post, const f
         out[i] = __double2float_rn(standard_step(post, static_cast<double>(in[i])));
 }
 
+__constant__ double c_atanh_odd[12] = {1., 1. / 3, 1. / 5, 1. / 7, 1. / 9, 1. / 11, 1. / 13, 1. / 15, 1. / 17, 1. / 19, 1. / 21, 1. / 23};
+
+// mifi_barometric_layer_thickness (v_c_t.c:161-164): (float)(log((double)(p_low / p_high)) * T * BAROMETRIC_FACTOR).  For layer
+// ratios within a factor 1.5 the logarithm is evaluated as 2 atanh((r-1)/(r+1)) (series exact to < 2e-17 relative for |s| < 0.2,
+// a third of the instructions of log()); the result is taken only if every real number within 1e-15 relative -- more than the
+// error of either evaluation -- narrows to the same f32, otherwise (and for thicker layers) log() is called.
+__device__ __forceinline__ float layer_thickness(float p_low, float p_high, float Tv)
+{
+    const double r = static_cast<double>(__fdiv_rn(p_low, p_high));
+    const double T = static_cast<double>(Tv);
+    if (r > 0.667 && r < 1.5) {
+        const double den = __dadd_rn(r, 1.);
+        double q;
+        asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(q) : "d"(den));
+        q = __fma_rn(q, __fma_rn(-den, q, 1.0), q);
+        q = __fma_rn(q, __fma_rn(-den, q, 1.0), q);
+        const double num = __dsub_rn(r, 1.); // exact (Sterbenz)
+        double sv = num * q;
+        sv = __fma_rn(__fma_rn(-den, sv, num), q, sv); // one correction: s to ~1 ulp
+        const double z = sv * sv;
+        double pl = c_atanh_odd[11];
+#pragma unroll
+        for (int i = 10; i >= 0; --i)
+            pl = __fma_rn(pl, z, c_atanh_odd[i]);
+        const double lg = 2. * sv * pl;
+        const double m = __dmul_rn(__dmul_rn(lg, T), BAROMETRIC_FACTOR);
+        const float lo = __double2float_rn(m * (1. - 1e-15)), hi = __double2float_rn(m * (1. + 1e-15));
+        if (lo == hi)
+            return lo;
+    }
+    return __double2float_rn(__dmul_rn(__dmul_rn(log(r), T), BAROMETRIC_FACTOR));
+}
+
 // first column (in the reference's loop order) whose first and last pressure are positive decides the direction of ALL
 // columns (PressureIntegrationToAltitudeConverter.cc:141-164): dirflag[0] = its index (atomicMin), resolved by the consumer
 __global__ void __launch_bounds__(256) vcoord_direction_kernel(const float* __restrict__ p, size_t nOuter, size_t nz, size_t nInner,
@@ -210,9 +243,7 @@ __global__ void __launch_bounds__(128) vcoord_integration_kernel(const Integrati
                 float Tv = bt[i];
                 if (pq) // mifi_virtual_temperature: (1 + Z*q) * T in double, returned as float
                     Tv = __double2float_rn(__dmul_rn(__dadd_rn(1., __dmul_rn(Z_MOL_WEIGHT_RATIO, static_cast<double>(bq[i]))), static_cast<double>(Tv)));
-                // mifi_barometric_layer_thickness: log(float ratio) * T * BAROMETRIC_FACTOR in double, returned as float
-                const double lg = log(static_cast<double>(__fdiv_rn(p_low, p_high)));
-                const float lt = __double2float_rn(__dmul_rn(__dmul_rn(lg, static_cast<double>(Tv)), BAROMETRIC_FACTOR));
+                const float lt = layer_thickness(p_low, p_high, Tv);
                 a = __dadd_rn(a, static_cast<double>(lt));
                 __stcs(po + n * step, __double2float_rn(P.topo ? __dadd_rn(a, tp) : a));
                 p_low = p_high;
