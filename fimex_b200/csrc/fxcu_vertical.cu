@@ -520,6 +520,7 @@ __device__ __forceinline__ void column_by_general_scan(const VertParams& P, cons
 // step at which the walk passes it; monotonicity is verified on the way.  Phase 2 runs over the target levels with all lanes in
 // step.  Shared memory: hybrid (ap, b) pairs, the level list (f64, log, f32 with a NaN sentinel either side), notes [nzo][VT] u16.
 constexpr int CH = 4;
+constexpr int SJC = 8; // explicit coordinate: target levels per gather batch
 
 template <bool HYBRID>
 __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams P)
@@ -641,23 +642,85 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
     E.cl = coord(nzi - 1);
     E.cl2 = coord(nzi - 2);
     E.cl3 = nzi >= 3 ? coord(nzi - 3) : 0.f;
-    for (int jj = 0; jj < nzo; ++jj) {
-        const double vout = s_xd[jj];
-        float r = nan_f();
-        if (level_in_range(P, vout, rlo, rhi)) {
-            const int step = s_k[jj * VT];
-            float plo = 0.f, phi = 0.f;
-            if (step > 0 && step < nzi) {
-                plo = coord(step - 1);
-                phi = coord(step);
+    if (HYBRID) {
+        for (int jj = 0; jj < nzo; ++jj) {
+            const double vout = s_xd[jj];
+            float r = nan_f();
+            if (level_in_range(P, vout, rlo, rhi)) {
+                const int step = s_k[jj * VT];
+                float plo = 0.f, phi = 0.f;
+                if (step > 0 && step < nzi) {
+                    plo = hc(step - 1);
+                    phi = hc(step);
+                }
+                r = value_from_step(C, hc, GlobalVal{din, P.nInner}, nzi, inc, E, step, s_xf[jj], plo, phi, din, vout, s_xl[jj]);
             }
-            const GlobalVal gv{din, P.nInner};
-            if (HYBRID)
-                r = value_from_step(C, hc, gv, nzi, inc, E, step, s_xf[jj], plo, phi, din, vout, s_xl[jj]);
-            else
-                r = value_from_step(C, sc, gv, nzi, inc, E, step, s_xf[jj], plo, phi, din, vout, s_xl[jj]);
+            store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
         }
-        store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
+        return;
+    }
+    // explicit coordinate: the three coordinates and two values a level needs are known from its step alone, so a batch of
+    // levels sends for all of them at once (cp.async into shared memory) before any is used
+    float* s_g = reinterpret_cast<float*>(s_k - threadIdx.x + static_cast<size_t>(nzo) * VT) + threadIdx.x; // [5][SJC][VT]
+    const unsigned g0 = static_cast<unsigned>(__cvta_generic_to_shared(s_g));
+    auto send = [&](int slot, int u, const float* src) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(g0 + static_cast<unsigned>((slot * SJC + u) * VT * 4)), "l"(src) : "memory");
+    };
+    auto got = [&](int slot, int u) { return s_g[(slot * SJC + u) * VT]; };
+    for (int j0 = 0; j0 < nzo; j0 += SJC) {
+        const int jn = min(SJC, nzo - j0);
+        for (int u = 0; u < jn; ++u) {
+            const int step = s_k[(j0 + u) * VT];
+            if (step > 0 && step < nzi) {
+                send(0, u, gc + static_cast<size_t>(max(step - 2, 0)) * P.nInner);
+                send(1, u, gc + static_cast<size_t>(step - 1) * P.nInner);
+                send(2, u, gc + static_cast<size_t>(step) * P.nInner);
+                send(3, u, din + static_cast<size_t>(step - 1) * P.nInner);
+                send(4, u, din + static_cast<size_t>(step) * P.nInner);
+            } else if (step == nzi) {
+                send(3, u, din + static_cast<size_t>(nzi - 1) * P.nInner);
+                send(4, u, din + static_cast<size_t>(nzi - 2) * P.nInner);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        for (int u = 0; u < jn; ++u) {
+            const int jj = j0 + u;
+            const double vout = s_xd[jj], xlog = s_xl[jj];
+            float r = nan_f();
+            if (level_in_range(P, vout, rlo, rhi)) {
+                const int step = s_k[jj * VT];
+                const float x = s_xf[jj];
+                bool fast, distinct = true;
+                float A = 0.f, B = 0.f, a = 0.f, b = 0.f;
+                if (step == 0) { // see value_from_step
+                    distinct = false;
+                    fast = (x == E.c0) || fabsf(__fsub_rn(x, E.c0)) < fabsf(__fsub_rn(x, E.c1));
+                } else if (step == nzi) {
+                    A = got(3, u);
+                    B = got(4, u);
+                    a = E.cl;
+                    b = E.cl2;
+                    const float d2 = fabsf(__fsub_rn(x, E.cl2));
+                    fast = fabsf(__fsub_rn(x, E.cl)) < d2 && (nzi < 3 || d2 < fabsf(__fsub_rn(x, E.cl3)));
+                } else {
+                    const float plo = got(1, u), phi = got(2, u);
+                    const float dlo = __fsub_rn(x, plo), dhi = __fsub_rn(x, phi);
+                    fast = fabsf(dlo) < FLT_MAX && fabsf(dhi) < FLT_MAX && (inc || x != plo);
+                    if (fast && step > 1)
+                        fast = dlo != __fsub_rn(x, got(0, u));
+                    A = inc ? got(3, u) : got(4, u);
+                    B = inc ? got(4, u) : got(3, u);
+                    a = inc ? plo : phi;
+                    b = inc ? phi : plo;
+                }
+                if (!fast)
+                    r = sweep_slow(C, sc, nzi, inc ? 1 : -1, din, vout, xlog);
+                else if (distinct)
+                    r = blend_levels(C, A, B, a, b, vout, xlog);
+            }
+            store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
+        }
     }
 }
 
@@ -985,12 +1048,13 @@ __global__ void __launch_bounds__(256) ps_minmax_kernel(const float* __restrict_
 // sorted fixed levels -> sweep kernel (FIMEXCU_VERTICAL_NO_SWEEP=1 keeps the per-level search kernels, for A/B measurements)
 static size_t sweep_smem(const VertParams& P)
 {
-    return ((P.vcoord_in ? 0 : 2 * P.nzi) + 2 * P.nzo) * sizeof(double) + (P.nzo + 2 + (P.nzo & 1)) * sizeof(float) + P.nzo * VT * sizeof(unsigned short);
+    return ((P.vcoord_in ? 0 : 2 * P.nzi) + 2 * P.nzo) * sizeof(double) + (P.nzo + 2 + (P.nzo & 1)) * sizeof(float) +
+           (P.nzo + (P.nzo & 1)) * VT * sizeof(unsigned short) + (P.vcoord_in ? 5 * SJC * VT * sizeof(float) : 0);
 }
 static bool sweep_applies(const VertParams& P)
 {
     static const bool disabled = std::getenv("FIMEXCU_VERTICAL_NO_SWEEP") != nullptr;
-    return !disabled && P.levels && !P.vcoord_out && P.levels_dir != 0 && P.nzi < 65535 && P.nzo < 65535 && sweep_smem(P) <= 24 * 1024;
+    return !disabled && P.levels && !P.vcoord_out && P.levels_dir != 0 && P.nzi < 65535 && P.nzo < 65535 && sweep_smem(P) <= 40 * 1024;
 }
 
 // direction of a fixed level list: +1 non-decreasing, -1 non-increasing, 0 unordered / NaN
