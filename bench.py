@@ -111,6 +111,29 @@ def workload(target):
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
+def cpu_vertical_port(ncol=60000):
+    """configs[4] on the CPU: the oracle's restatement of CDMVerticalInterpolator::getLevelDataSlice (the reference's loop is not
+    OpenMP-parallel) on a bounded sample of columns, 65 hybrid levels -> 12 pressure levels, log.  Part of the cpu_baseline leg."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    rng = np.random.default_rng(1)
+    g = np.load(os.path.join(ROOT, "tests", "golden", "reference_vertical.npz"))
+    ap, b = g["en_ap_pa"] * 0.01, g["en_b"]
+    levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50], dtype=np.float64)
+    ps = (101325 - 12 * rng.uniform(0, 2500, ncol) + rng.normal(0, 300, ncol)).astype(np.float32)
+    fld = rng.normal(0, 10, (65, ncol)).astype(np.float32)
+    t0 = time.perf_counter()
+    p = np.ascontiguousarray((ap[:, None] + b[:, None] * (ps.astype(np.float64) * 0.01)[None, :]).astype(np.float32))  # the converter's part
+    out = np.empty((12, ncol), np.float32)
+    rc = ol.oracle().orc_vertical_interpolate_f(ol.VINT_LOG, ol.fp(fld), ol.fp(p), 65, ncol, ol.dp(levels), None, 12, None, None, float("nan"),
+                                                float("nan"), ol.fp(out))
+    dt = time.perf_counter() - t0
+    if rc != 1:
+        raise RuntimeError("oracle vertical interpolation failed")
+    return {"value": 12 * ncol / dt / 1e9, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"{ncol} columns, 65 hybrid levels -> 12 pressure levels, log (oracle restatement of getLevelDataSlice + hybrid pressure)"}
+
+
 def cpu_reference(px, py, S, ox, oy, budget_s=12.0, max_levels=None):
     """Times CachedInterpolation::interpolateValues of the reference (oracle/_ref, built with OpenMP = the reference's
     ENABLE_FIMEX_OMP) on a bounded number of levels of the same slab.  Falls back to the scalar oracle port."""
@@ -485,6 +508,10 @@ def main_b200(args):
             cpu = {"value": levels * ox * oy / dt / 1e9, "unit": UNIT, "cores": ref["threads"], "kind": ref["kind"],
                    "sample": f"{levels} of {nz} levels of one S->{args.target} slab x{reps} "
                              f"(CachedInterpolation::interpolateValues, {ref['threads']} OpenMP threads)"}
+            try:
+                cpu["vertical_hybrid_to_pressure_log"] = cpu_vertical_port()
+            except Exception as exc:
+                cpu["vertical_hybrid_to_pressure_log"] = {"error": str(exc)[:200]}
         except Exception as exc:  # the checker is optional on the GPU box; the GPU numbers stand on their own
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": str(exc)[:200]}
 
