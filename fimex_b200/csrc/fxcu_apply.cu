@@ -1394,10 +1394,22 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
     constexpr int NS_MAX = 8;
     static const int NS = []() { const char* e = getenv("FIMEXCU_E2E_STREAMS"); const int v = e ? atoi(e) : 3; return std::max(1, std::min(8, v)); }();
     static const int NCHUNK = []() { const char* e = getenv("FIMEXCU_E2E_CHUNKS"); const int v = e ? atoi(e) : 8; return std::max(1, v); }();
-    const size_t chunk = std::max<size_t>(1, std::min<size_t>(nz, (nz + NCHUNK - 1) / NCHUNK));
-    cudaStream_t st[NS_MAX];
-    for (int i = 0; i < NS; ++i)
-        FXCU_CUDA(cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking));
+    // small slabs are latency-bound: one chunk per 16 MB of traffic (at most NCHUNK), and the streams are kept per host thread
+    // and device instead of being created for every call
+    const size_t traffic = nz * (inLayer + outLayer) * sizeof(T);
+    const size_t nchunk = std::max<size_t>(1, std::min<size_t>(static_cast<size_t>(NCHUNK), traffic / (16u << 20)));
+    const size_t chunk = std::max<size_t>(1, std::min<size_t>(nz, (nz + nchunk - 1) / nchunk));
+    struct ThreadStreams {
+        int device = -1;
+        cudaStream_t st[NS_MAX] = {};
+    };
+    thread_local ThreadStreams pool; // never destroyed: the context may be gone when a thread exits
+    if (pool.device != c->device) {
+        for (int i = 0; i < NS_MAX; ++i)
+            FXCU_CUDA(cudaStreamCreateWithFlags(&pool.st[i], cudaStreamNonBlocking));
+        pool.device = c->device;
+    }
+    cudaStream_t* st = pool.st;
     int rc = FIMEXCU_OK;
     {
         DevBuf din[NS_MAX], dout[NS_MAX];
@@ -1424,8 +1436,6 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
             if (!cuda_ok(cudaStreamSynchronize(st[i]), "cudaStreamSynchronize", __FILE__, __LINE__))
                 rc = FIMEXCU_ERROR;
     }
-    for (int i = 0; i < NS; ++i)
-        cudaStreamDestroy(st[i]);
     return rc;
 }
 
