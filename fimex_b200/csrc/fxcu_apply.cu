@@ -405,6 +405,29 @@ __global__ void __launch_bounds__(256) bilinear_apply_kernel(const ApplyParams P
     }
 }
 
+// 16 taps around p (tap (x0-1, y0-1)), weights in f64, the four column sums added into the f32 result one at a time
+// (interpolation.c:388-406)
+template <bool BAD, class T>
+__device__ __forceinline__ float bicubic_sample(const T* __restrict__ p, int pitch, const double wxv[4], const double wyv[4], float bad)
+{
+    float v[4][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            v[j][i] = load_in<BAD>(p + j * pitch + i, bad);
+    float acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        double col = 0.;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            col = __dadd_rn(col, __dmul_rn(wxv[i], static_cast<double>(v[j][i])));
+        acc = __double2float_rn(__dadd_rn(static_cast<double>(acc), __dmul_rn(col, wyv[j])));
+    }
+    return acc;
+}
+
 // K5.  Same mapping; 16 taps, weights in f64, the four column sums added into the f32 result one at a
 // time (interpolation.c:388-406).
 template <bool BAD, bool FILL, class T = float>
@@ -428,24 +451,8 @@ __global__ void __launch_bounds__(256) bicubic_apply_kernel(const ApplyParams P)
     cubic_weights(static_cast<const double*>(P.wy)[o], wyv);
     const T* p = static_cast<const T*>(P.in) + static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
     const int inX = P.inPitch;
-    for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel) {
-        float v[4][4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                v[j][i] = load_in<BAD>(p + j * inX + i, P.bad);
-        float acc = 0.f;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            double col = 0.;
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                col = __dadd_rn(col, __dmul_rn(wxv[i], static_cast<double>(v[j][i])));
-            acc = __double2float_rn(__dadd_rn(static_cast<double>(acc), __dmul_rn(col, wyv[j])));
-        }
-        store_out<FILL>(po, acc, P.fill);
-    }
+    for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel)
+        store_out<FILL>(po, bicubic_sample<BAD>(p, inX, wxv, wyv, P.bad), P.fill);
 }
 
 // K6.  Pure gather.
@@ -964,13 +971,60 @@ __global__ void __launch_bounds__(256) bilinear_uv_kernel(const ApplyParams P, c
     }
 }
 
-// NaN -> fill over a dense array (used where the fill cannot be fused: bicubic/nearest u,v with rotation)
-__global__ void __launch_bounds__(256) fill_kernel(float* __restrict__ a, size_t n, float fill)
+// K7 for bicubic and nearest-neighbour tables: both components sampled and rotated in one pass (the reference runs
+// interpolateValues twice and then reprojectValues over both results, src/CDMInterpolator.cc:232-259)
+template <bool CUBIC, bool ROT>
+__global__ void __launch_bounds__(256) sampled_uv_kernel(const ApplyParams P, const UvParams Q)
 {
-    for (size_t i = blockIdx.x * 256ull + threadIdx.x; i < n; i += 256ull * gridDim.x)
-        if (isnan(a[i]))
-            a[i] = fill;
+    int ox, oy;
+    if (!tile_cell(P, ox, oy))
+        return;
+    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const int z0 = blockIdx.z * P.zchunk;
+    const int z1 = min(P.nz, z0 + P.zchunk);
+    const int f = P.off[o];
+    const size_t obase = static_cast<size_t>(z0) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
+    float* pu = static_cast<float*>(P.out) + obase;
+    float* pv = Q.vout + obase;
+    if (f < 0) {
+        for (int z = z0; z < z1; ++z, pu += P.outLevel, pv += P.outLevel) {
+            store_out<true>(pu, nan_f(), P.fill);
+            store_out<true>(pv, nan_f(), Q.fillV);
+        }
+        return;
+    }
+    double c = 1., s = 0.;
+    if (ROT) {
+        c = Q.cs[o];
+        s = Q.sn[o];
+    }
+    double wxv[4], wyv[4];
+    if (CUBIC) {
+        cubic_weights(static_cast<const double*>(P.wx)[o], wxv);
+        cubic_weights(static_cast<const double*>(P.wy)[o], wyv);
+    }
+    const size_t ibase = static_cast<size_t>(z0) * P.inLevel + source_offset(P, f);
+    const float* qu = static_cast<const float*>(P.in) + ibase;
+    const float* qv = Q.vin + ibase;
+    for (int z = z0; z < z1; ++z, qu += P.inLevel, qv += P.inLevel, pu += P.outLevel, pv += P.outLevel) {
+        float u, v;
+        if (CUBIC) {
+            u = bicubic_sample<true>(qu, P.inPitch, wxv, wyv, P.bad);
+            v = bicubic_sample<true>(qv, P.inPitch, wxv, wyv, Q.badV);
+        } else {
+            u = load_in<true>(qu, P.bad);
+            v = load_in<true>(qv, Q.badV);
+        }
+        if (ROT) {
+            const double du = static_cast<double>(u), dv = static_cast<double>(v);
+            u = __double2float_rn(__dsub_rn(__dmul_rn(du, c), __dmul_rn(dv, s)));
+            v = __double2float_rn(__dadd_rn(__dmul_rn(du, s), __dmul_rn(dv, c)));
+        }
+        store_out<true>(pu, u, P.fill);
+        store_out<true>(pv, v, Q.fillV);
+    }
 }
+
 
 // single-position variants with the reference signatures (one launch; levels across threads)
 __global__ void point_kernel(int method, const float* __restrict__ in, float* __restrict__ out, double x, double y, int ix, int iy, int iz)
@@ -1549,25 +1603,46 @@ static int cache_apply_uv_strided(const fimexcu_cache* c, const fimexcu_vecrot* 
         return FIMEXCU_OK;
     if (check_layout(c, L, nz) != FIMEXCU_OK)
         return FIMEXCU_ERROR;
-    if (c->kind != KIND_BILINEAR) {
-        // bicubic / nearest: the general kernels per component, the stand-alone rotation (which must see NaN, not the
-        // fill value), then the fill.  The stand-alone rotation and fill work on dense arrays only.
-        const bool dense_out = static_cast<size_t>(L.outPitch) == c->outX && L.outLevel == nxy;
-        if (r && !dense_out)
-            FXCU_FAIL("fimexcu_cache_apply_uv: rotation of bicubic / nearest results needs the dense target layout");
-        const float nanv = std::numeric_limits<float>::quiet_NaN();
-        const float fu = r ? nanv : fillU, fv = r ? nanv : fillV;
-        if (cache_apply_strided(c, d_u_in, L, nz, d_u_out, badU, fu, s) != FIMEXCU_OK || cache_apply_strided(c, d_v_in, L, nz, d_v_out, badV, fv, s) != FIMEXCU_OK)
-            return FIMEXCU_ERROR;
-        if (!r)
-            return FIMEXCU_OK;
-        if (fimexcu_vecrot_apply_dev_f(r, d_u_out, d_v_out, nz, s) != FIMEXCU_OK)
-            return FIMEXCU_ERROR;
-        const unsigned fb = static_cast<unsigned>(std::min<size_t>((nz * nxy + 255) / 256, static_cast<size_t>(sm_count()) * 16));
-        if (!std::isnan(fillU))
-            fill_kernel<<<fb, 256, 0, s>>>(d_u_out, nz * nxy, fillU);
-        if (!std::isnan(fillV))
-            fill_kernel<<<fb, 256, 0, s>>>(d_v_out, nz * nxy, fillV);
+    if (c->kind != KIND_BILINEAR) { // bicubic / nearest: one fused pass (a NaN bad / fill value switches the conversion off by itself)
+        ApplyParams P;
+        P.off = c->off.as<int>();
+        P.wx = c->wx.p;
+        P.wy = c->wy.p;
+        P.tile_meta = nullptr;
+        P.in = d_u_in;
+        P.out = d_u_out;
+        P.outX = static_cast<int>(c->outX);
+        P.outY = static_cast<int>(c->outY);
+        P.nz = static_cast<int>(nz);
+        P.inX = static_cast<int>(c->inX);
+        P.inPitch = L.inPitch;
+        P.inLevel = L.inLevel;
+        P.outPitch = L.outPitch;
+        P.outLevel = L.outLevel;
+        P.bad = badU;
+        P.fill = fillU;
+        UvParams Q;
+        Q.cs = r ? r->c.as<double>() : nullptr;
+        Q.sn = r ? r->s.as<double>() : nullptr;
+        Q.vin = d_v_in;
+        Q.vout = d_v_out;
+        Q.badV = badV;
+        Q.fillV = fillV;
+        const size_t tiles = static_cast<size_t>((c->outX + 31) / 32) * ((c->outY + 7) / 8);
+        P.zchunk = pick_zchunk(tiles, P.nz);
+        const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + 7) / 8),
+                        static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
+        if (c->kind == KIND_BICUBIC) {
+            if (r)
+                sampled_uv_kernel<true, true><<<grid, 256, 0, s>>>(P, Q);
+            else
+                sampled_uv_kernel<true, false><<<grid, 256, 0, s>>>(P, Q);
+        } else {
+            if (r)
+                sampled_uv_kernel<false, true><<<grid, 256, 0, s>>>(P, Q);
+            else
+                sampled_uv_kernel<false, false><<<grid, 256, 0, s>>>(P, Q);
+        }
         FXCU_CUDA(cudaGetLastError());
         return FIMEXCU_OK;
     }

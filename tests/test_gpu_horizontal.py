@@ -442,3 +442,39 @@ def test_concurrent_host_threads_share_a_cache(fx):
     assert not errors, errors
     for k in range(len(fields)):
         assert _eq(results[k], wants[k]), k
+
+
+@pytest.mark.parametrize("method", [ol.BICUBIC, ol.NEAREST])
+@pytest.mark.parametrize("rotate", [True, False])
+def test_fused_uv_bicubic_nearest_bad_fill_padded(fx, oracle, method, rotate):
+    """bicubic / nearest wind pairs in one fused pass with bad -> NaN on load and NaN -> fill AFTER the rotation (which must see NaN,
+    not the fill value), in the padded device layout and in the dense one"""
+    import torch
+    from fimex_b200.interpolation import interpolateVectorValues, interpolateVectorValuesPadded
+    rng = np.random.default_rng(5 + method)
+    in_x, in_y, out_x, out_y, nz = 70, 50, 131, 97, 5
+    ang = rng.uniform(-np.pi, np.pi, out_x * out_y)
+    m3 = np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy()
+    px, py = _tables(rng, in_x, in_y, out_x * out_y)
+    bad_u, bad_v, fill_u, fill_v = np.float32(-999.0), np.float32(-888.0), np.float32(1e30), np.float32(-1e30)
+    u = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    v = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    un, vn = u.copy(), v.copy()
+    mu, mv = rng.random(u.shape) < 0.02, rng.random(v.shape) < 0.02
+    un[mu], vn[mv] = np.nan, np.nan
+    u[mu], v[mv] = bad_u, bad_v
+    wu, _ = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, un)
+    wv, _ = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, vn)
+    if rotate:
+        oracle.orc_vector_reproject_values_by_matrix_f(dp(m3), out_x * out_y, fp(wu), fp(wv), nz)
+    oracle.orc_nanf2bad(fp(wu), wu.size, fill_u)
+    oracle.orc_nanf2bad(fp(wv), wv.size, fill_v)
+    ci = fx.createCachedInterpolation("x", "y", method, px, py, in_x, in_y, out_x, out_y)
+    cvr = fx.CachedVectorReprojection(m3, out_x, out_y) if rotate else None
+    ru, rv = ci.reduceInput(u, in_x, in_y), ci.reduceInput(v, in_x, in_y)
+    gu, gv = interpolateVectorValues(ci, cvr, ru, rv, float(bad_u), float(bad_v), float(fill_u), float(fill_v))
+    assert _eq(gu, wu) and _eq(gv, wv)
+    du, dv = ci.toPadded(torch.from_numpy(ru).cuda()), ci.toPadded(torch.from_numpy(rv).cuda())
+    pu, pv = interpolateVectorValuesPadded(ci, cvr, du, dv, float(bad_u), float(bad_v), float(fill_u), float(fill_v))
+    torch.cuda.synchronize()
+    assert _eq(pu[..., :out_x].cpu().numpy(), wu) and _eq(pv[..., :out_x].cpu().numpy(), wv)
