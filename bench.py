@@ -300,6 +300,10 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
     ps_out = torch.empty((nmem, oy2, op2), dtype=torch.float32, device="cuda")
     n_inner = nmem * oy2 * op2
 
+    ms = timed(lambda: c2.interpolateValuesPadded(f_in, out=f_out), reps=5)
+    out["K4_bilinear_T2_padded_staged"] = entry(ms, S.bilinear_algorithmic_bytes(c2.getInX() * c2.getInY(), ox2 * oy2, 65 * nmem), 65 * nmem * ox2 * oy2,
+                                                "S->T2 (interior target, reduced source window 505x642, 7.13 B/pt), 390 levels per launch")
+
     def chain():
         c2.interpolateValuesPadded(f_in, out=f_out)
         c2.interpolateValuesPadded(ps_in, out=ps_out)

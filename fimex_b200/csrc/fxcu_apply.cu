@@ -577,10 +577,13 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
     __syncthreads();
     const int bx0 = meta.x, by0 = meta.y;
     const bool all_interior = (meta.z & TILE_ALL_INTERIOR) != 0;
-    float* po = static_cast<float*>(P.out) + static_cast<size_t>(oy) * P.outPitch + ox;
+    // blockIdx.z selects a chunk of levels (a multiple of TMA_ZB): few tiles x many levels would otherwise leave the last wave
+    // of CTAs mostly empty
+    const int zb = blockIdx.z * P.zchunk, nzc = min(P.nz, zb + P.zchunk) - zb;
+    float* po = static_cast<float*>(P.out) + static_cast<size_t>(zb) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
     if (!(meta.z & TILE_HAS_DATA)) { // nothing defined in this tile
         if (in_grid)
-            for (int z = 0; z < P.nz; ++z, po += P.outLevel)
+            for (int z = 0; z < nzc; ++z, po += P.outLevel)
                 store_out<FILL>(po, nan_f(), P.fill);
         return;
     }
@@ -589,28 +592,28 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
         if (!in_grid)
             return;
         if (f < 0) {
-            for (int z = 0; z < P.nz; ++z, po += P.outLevel)
+            for (int z = 0; z < nzc; ++z, po += P.outLevel)
                 store_out<FILL>(po, nan_f(), P.fill);
             return;
         }
         const int dxg = fx >= 0.f ? 1 : 0, dyg = fy >= 0.f ? P.inPitch : 0;
-        const float* p = static_cast<const float*>(P.in) + static_cast<size_t>(y0) * P.inPitch + x0;
+        const float* p = static_cast<const float*>(P.in) + static_cast<size_t>(zb) * P.inLevel + static_cast<size_t>(y0) * P.inPitch + x0;
 #pragma unroll 4
-        for (int z = 0; z < P.nz; ++z, p += P.inLevel, po += P.outLevel)
+        for (int z = 0; z < nzc; ++z, p += P.inLevel, po += P.outLevel)
             store_out<FILL>(po, bilinear_value(load_in<BAD>(p, P.bad), load_in<BAD>(p + dxg, P.bad), load_in<BAD>(p + dyg, P.bad),
                                                load_in<BAD>(p + dyg + dxg, P.bad), fx, fy),
                             P.fill);
         return;
     }
     constexpr unsigned BYTES = STAGE_FLOATS * sizeof(float);
-    const int niter = (P.nz + TMA_ZB - 1) / TMA_ZB;
+    const int niter = (nzc + TMA_ZB - 1) / TMA_ZB;
     if (!consumer) { // producer warp: one lane keeps the ring full
         if (lane == 0) {
             for (int it = 0; it < niter; ++it) {
                 const int s = it % TMA_STAGES;
                 mbar_wait(&empty[s], ((it / TMA_STAGES) & 1) ^ 1); // passes at once the first time round
                 mbar_expect_tx(&full[s], BYTES);
-                tma_load_3d(&tile[s][0], &tmap, &full[s], bx0, by0, it * TMA_ZB);
+                tma_load_3d(&tile[s][0], &tmap, &full[s], bx0, by0, zb + it * TMA_ZB);
             }
         }
         return;
@@ -624,7 +627,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
 #pragma unroll
             for (int k = 0; k < TMA_ZB; ++k) {
                 const float v = (f >= 0) ? tap<BAD>(t, k * LVL, P.bad) : nan_f();
-                if (in_grid && it * TMA_ZB + k < P.nz)
+                if (in_grid && it * TMA_ZB + k < nzc)
                     store_out<FILL>(po + k * P.outLevel, v, P.fill);
             }
             po += TMA_ZB * P.outLevel;
@@ -644,7 +647,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
             for (int k = 0; k < TMA_ZB; ++k) {
                 const float v = blend4(tap<BAD>(t, k * LVL, P.bad), tap<BAD>(t, k * LVL + 1, P.bad), tap<BAD>(t, k * LVL + TMA_BW, P.bad),
                                        tap<BAD>(t, k * LVL + TMA_BW + 1, P.bad), wfx, wfy, omx, omy);
-                if (in_grid && it * TMA_ZB + k < P.nz)
+                if (in_grid && it * TMA_ZB + k < nzc)
                     store_out<FILL>(po + k * P.outLevel, v, P.fill);
             }
             po += TMA_ZB * P.outLevel;
@@ -664,7 +667,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
                 if (f >= 0)
                     v = bilinear_value(tap<BAD>(t, k * LVL, P.bad), tap<BAD>(t, k * LVL + dxs, P.bad), tap<BAD>(t, k * LVL + dys, P.bad),
                                        tap<BAD>(t, k * LVL + dys + dxs, P.bad), fx, fy);
-                if (in_grid && it * TMA_ZB + k < P.nz)
+                if (in_grid && it * TMA_ZB + k < nzc)
                     store_out<FILL>(po + k * P.outLevel, v, P.fill);
             }
             po += TMA_ZB * P.outLevel;
@@ -757,12 +760,13 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
     }
     __syncthreads();
     const int bx0 = bbox[0], by0 = bbox[1], bx1 = bbox[2], by1 = bbox[3];
-    const size_t obase = static_cast<size_t>(oy) * P.outPitch + ox;
+    const int zb = blockIdx.z * P.zchunk, nzc = min(P.nz, zb + P.zchunk) - zb; // this CTA's chunk of levels (a multiple of UV_ZB)
+    const size_t obase = static_cast<size_t>(zb) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
     float* pu = static_cast<float*>(P.out) + obase;
     float* pv = Q.vout + obase;
     if (bx1 < 0) {
         if (in_grid)
-            for (int z = 0; z < P.nz; ++z, pu += P.outLevel, pv += P.outLevel) {
+            for (int z = 0; z < nzc; ++z, pu += P.outLevel, pv += P.outLevel) {
                 store_out<FILL>(pu, nan_f(), P.fill);
                 store_out<FILL>(pv, nan_f(), Q.fillV);
             }
@@ -774,15 +778,15 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
         s = Q.sn[o];
     }
     const bool staged = (bx1 - bx0 + 1 <= TMA_BW) && (by1 - by0 + 1 <= TMA_BH);
-    const int niter = staged ? (P.nz + UV_ZB - 1) / UV_ZB : 0;
+    const int niter = staged ? (nzc + UV_ZB - 1) / UV_ZB : 0;
     if (!consumer) {
         if (staged && lane == 0) {
             for (int it = 0; it < niter; ++it) {
                 const int st = it % UV_STAGES;
                 mbar_wait(&empty[st], ((it / UV_STAGES) & 1) ^ 1);
                 mbar_expect_tx(&full[st], 2 * FIELD * sizeof(float));
-                tma_load_3d(&tile[st][0], &umap, &full[st], bx0, by0, it * UV_ZB);
-                tma_load_3d(&tile[st][FIELD], &vmap, &full[st], bx0, by0, it * UV_ZB);
+                tma_load_3d(&tile[st][0], &umap, &full[st], bx0, by0, zb + it * UV_ZB);
+                tma_load_3d(&tile[st][FIELD], &vmap, &full[st], bx0, by0, zb + it * UV_ZB);
             }
         }
         return;
@@ -793,16 +797,16 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
         if (!in_grid)
             return;
         if (f < 0) {
-            for (int z = 0; z < P.nz; ++z, pu += P.outLevel, pv += P.outLevel) {
+            for (int z = 0; z < nzc; ++z, pu += P.outLevel, pv += P.outLevel) {
                 store_out<FILL>(pu, nan_f(), P.fill);
                 store_out<FILL>(pv, nan_f(), Q.fillV);
             }
             return;
         }
         const int dyg = fy >= 0.f ? P.inPitch : 0;
-        const float* qu = static_cast<const float*>(P.in) + static_cast<size_t>(y0) * P.inPitch + x0;
-        const float* qv2 = Q.vin + static_cast<size_t>(y0) * P.inPitch + x0;
-        for (int z = 0; z < P.nz; ++z, qu += P.inLevel, qv2 += P.inLevel, pu += P.outLevel, pv += P.outLevel) {
+        const float* qu = static_cast<const float*>(P.in) + static_cast<size_t>(zb) * P.inLevel + static_cast<size_t>(y0) * P.inPitch + x0;
+        const float* qv2 = Q.vin + static_cast<size_t>(zb) * P.inLevel + static_cast<size_t>(y0) * P.inPitch + x0;
+        for (int z = 0; z < nzc; ++z, qu += P.inLevel, qv2 += P.inLevel, pu += P.outLevel, pv += P.outLevel) {
             float u = bilinear_value(load_in<BAD>(qu, P.bad), load_in<BAD>(qu + dxs, P.bad), load_in<BAD>(qu + dyg, P.bad),
                                      load_in<BAD>(qu + dyg + dxs, P.bad), fx, fy);
             float v = bilinear_value(load_in<BAD>(qv2, Q.badV), load_in<BAD>(qv2 + dxs, Q.badV), load_in<BAD>(qv2 + dyg, Q.badV),
@@ -838,7 +842,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
                     v = __double2float_rn(__dadd_rn(__dmul_rn(du, s), __dmul_rn(dv, c)));
                 }
             }
-            if (in_grid && it * UV_ZB + k < P.nz) {
+            if (in_grid && it * UV_ZB + k < nzc) {
                 store_out<FILL>(pu + k * P.outLevel, u, P.fill);
                 store_out<FILL>(pv + k * P.outLevel, v, Q.fillV);
             }
@@ -1301,7 +1305,13 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
         const bool enough = tiles >= static_cast<size_t>(sm_count()) * 6;
         const bool fits = c->tiles_with_data > 0 && 10ull * c->tiles_fitting >= 8ull * c->tiles_with_data;
         if (enough && fits && make_source_map(&map, static_cast<const float*>(P.in), c->inX, c->inY, static_cast<size_t>(P.nz), P.inPitch, P.inLevel)) {
-            const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH));
+            // at least ~8 waves of CTAs (6 per SM): split the levels when the tiles alone are too few
+            const size_t slots = static_cast<size_t>(sm_count()) * 6;
+            size_t zsplit = std::max<size_t>(1, (8 * slots + tiles - 1) / tiles); // 16 / 24 waves measured slower on T1
+            zsplit = std::min<size_t>(zsplit, std::max<size_t>(1, static_cast<size_t>(P.nz) / (4 * TMA_ZB)));
+            P.zchunk = static_cast<int>(((static_cast<size_t>(P.nz) + zsplit - 1) / zsplit + TMA_ZB - 1) / TMA_ZB * TMA_ZB);
+            const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH),
+                            static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
             if (c->kind == KIND_NN)
                 staged_apply_tma_kernel<BAD, FILL, true><<<grid, TMA_THREADS, 0, s>>>(map, P);
             else
@@ -1680,7 +1690,12 @@ static int cache_apply_uv_strided(const fimexcu_cache* c, const fimexcu_vecrot* 
         Q.vout = d_v_out;
         Q.badV = badV;
         Q.fillV = fillV;
-        const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH));
+        const size_t slots = static_cast<size_t>(sm_count()) * 5; // see launch_cache_apply
+        size_t zsplit = std::max<size_t>(1, (8 * slots + tiles - 1) / tiles);
+        zsplit = std::min<size_t>(zsplit, std::max<size_t>(1, nz / (4 * UV_ZB)));
+        P.zchunk = static_cast<int>(((nz + zsplit - 1) / zsplit + UV_ZB - 1) / UV_ZB * UV_ZB);
+        const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH),
+                        static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
         // a NaN bad value never compares equal and a NaN fill value re-writes NaN: the <true,true> variant is always correct
         if (r) {
             if (special)
