@@ -1188,7 +1188,7 @@ static bool two_level_plan(int method, double& a, double& b, double& x, int& kin
         a = std::log(a + 2.7182818284590452354);
         b = std::log(b + 2.7182818284590452354);
         x = std::log(x + 2.7182818284590452354);
-        // fall through: mifi_get_values_log_log_f calls mifi_get_values_log_f (interpolation.c:537-546)
+        [[fallthrough]]; // mifi_get_values_log_log_f calls mifi_get_values_log_f (interpolation.c:537-546)
     case FIMEXCU_VINT_METHOD_LOG:
         if (a <= 0 || b <= 0 || x <= 0) {
             set_error("mifi_get_values_log_f: non-positive coordinate");

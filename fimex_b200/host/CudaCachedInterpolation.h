@@ -51,7 +51,7 @@ public:
     // shared_array's deleter returns it to the pinned allocator, so callers see an ordinary shared_array<float>.
     shared_array<float> interpolateValues(shared_array<float> inData, size_t size, size_t& newSize) const override
     {
-        const size_t nz = (inX * inY) ? size / (inX * inY) : 0;
+        const size_t nz = (inX * inY != 0) ? size / (inX * inY) : 0;
         newSize = nz * outX * outY;
         float* raw = static_cast<float*>(fimexcu_host_alloc((newSize ? newSize : 1) * sizeof(float)));
         if (!raw)
@@ -87,7 +87,7 @@ public:
     ~CudaCachedForwardInterpolation() override { fimexcu_forward_destroy(h_); }
     shared_array<float> interpolateValues(shared_array<float> inData, size_t size, size_t& newSize) const override
     {
-        const size_t nz = (inX * inY) ? size / (inX * inY) : 0;
+        const size_t nz = (inX * inY != 0) ? size / (inX * inY) : 0;
         newSize = nz * outX * outY;
         auto out = make_shared_array<float>(newSize ? newSize : 1);
         if (fimexcu_forward_apply_f(h_, inData.get(), size, out.get(), &newSize, NAN, NAN, compat_ ? 1 : 0) != FIMEXCU_OK)

@@ -1016,7 +1016,7 @@ int orc_coordnn_translate(double* px, double* py, size_t nPoints, const double* 
 {
     const double max_grid_d = orc_get_grid_distance(lon, lat, nx, ny);
     const double min_grid_cos_d = cos(max_grid_d);
-    orc_llpoint* ll = (orc_llpoint*)malloc((nx * ny ? nx * ny : 1) * sizeof(orc_llpoint));
+    orc_llpoint* ll = (orc_llpoint*)malloc((nx * ny != 0 ? nx * ny : 1) * sizeof(orc_llpoint));
     size_t m = 0;
     for (size_t ix = 0; ix < nx; ++ix)
         for (size_t iy = 0; iy < ny; ++iy) {
