@@ -85,6 +85,7 @@ SIGNATURES = {
     "fimexcu_cache_create_from_projection": (vp, [C.c_int, C.c_char_p, C.c_char_p, vp, vp, sz, sz, vp, vp, sz, sz, C.c_int, C.c_int]),
     "fimexcu_cache_create_from_points": (vp, [C.c_int, C.c_char_p, C.c_char_p, vp, vp, sz, sz, vp, vp, sz, sz, C.c_int, C.c_int]),
     "fimexcu_kdtree_translate": (C.c_int, [C.c_double, vp, vp, sz, vp, vp, sz, sz]),
+    "fimexcu_kdtree_translate_mode": (C.c_int, [C.c_double, vp, vp, sz, vp, vp, sz, sz, C.c_int]),
     "fimexcu_coordnn_translate": (C.c_int, [vp, vp, sz, vp, vp, sz, sz]),
     "fimexcu_forward_create": (vp, [C.c_int, vp, vp, sz, sz, sz, sz]),
     "fimexcu_forward_info": (C.c_int, [vp, c_size_p, c_size_p, c_size_p, c_size_p, c_int_p, c_size_p, c_size_p, c_size_p]),

@@ -20,6 +20,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC",
+    "-Xcompiler", "-ffp-contract=off",  # host code too (the coordinate searches redo reference arithmetic with the host's libm)
     "--fmad=false",  # the reference's x86-64 build rounds every product and sum separately
 ]
 

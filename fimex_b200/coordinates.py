@@ -10,14 +10,15 @@ def _f64(a):
     return np.ascontiguousarray(a, dtype=np.float64)
 
 
-def flannTranslatePointsToClosestInputCell(maxDist, pointsOnXAxis, pointsOnYAxis, lonVals, latVals):
+def flannTranslatePointsToClosestInputCell(maxDist, pointsOnXAxis, pointsOnYAxis, lonVals, latVals, nanoflann_compat=True):
     """coord_kdtree: target lon/lat (degrees) -> source (ix, iy) as doubles, -1000 where nothing lies within maxDist metres.
-    lonVals/latVals: [orgYDimSize][orgXDimSize]."""
+    lonVals/latVals: [orgYDimSize][orgXDimSize].  nanoflann_compat=True: the reference's result, tie order and NaN-cloud losses
+    included; False: true nearest point, NaN source points left out, lower index on ties."""
     lon, lat = _f64(lonVals), _f64(latVals)
     ny, nx = lon.shape
     px, py = np.array(pointsOnXAxis, dtype=np.float64).ravel().copy(), np.array(pointsOnYAxis, dtype=np.float64).ravel().copy()
-    _lib.check(lib.fimexcu_kdtree_translate(float(maxDist), px.ctypes.data, py.ctypes.data, px.size, lon.ctypes.data, lat.ctypes.data, nx, ny),
-               "flannTranslatePointsToClosestInputCell")
+    _lib.check(lib.fimexcu_kdtree_translate_mode(float(maxDist), px.ctypes.data, py.ctypes.data, px.size, lon.ctypes.data, lat.ctypes.data, nx, ny,
+                                                 1 if nanoflann_compat else 0), "flannTranslatePointsToClosestInputCell")
     return px.reshape(np.shape(pointsOnXAxis)), py.reshape(np.shape(pointsOnYAxis))
 
 

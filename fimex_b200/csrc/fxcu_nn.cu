@@ -11,13 +11,18 @@
 // great-circle angle, strictly above cos(ROI) (coord_nearestneighbor).  The GPU gets there with a uniform 3-D hash grid over
 // the unit sphere instead of a kd-tree: cell edge >= search radius, source points sorted by cell key (radix sort), each query
 // scans the 27 cells around it.  Distances use the reference's operation order with separately rounded f64 operations.
-// Exact ties (duplicated source positions, e.g. wrap columns) are decided by the lower source index for K9 -- the reference's
-// choice depends on nanoflann's tree layout -- and by the reference's scan order (larger-or-equal latitude first) for K10.
+// K9 through this file is the nanoflann_compat = 0 form only (true nearest point, NaN points skipped, lower source index on exact
+// ties); the reference-identical form walks a clone of nanoflann's tree (fxcu_kdtree.cu).  K10 here is reference-identical: the
+// device search is final only where its best candidate is clear of the runner-up and of the ROI threshold by more than the
+// difference between the device's and glibc's sin/cos; the remaining targets (near ties, exact ties between duplicated
+// positions, targets at the edge of the ROI) are decided by the reference's own latitude-sorted scan on the host (fxcu_llscan.h).
 #include "fxcu_common.h"
+#include "fxcu_llscan.h"
 
 #include <cub/device/device_radix_sort.cuh>
 
 #include <algorithm>
+#include <thread>
 #include <vector>
 
 namespace fxcu {
@@ -124,9 +129,19 @@ __global__ void __launch_bounds__(128) nn_kdtree_kernel(double* __restrict__ qlo
     }
 }
 
-// getGridDistance (CDMInterpolator.cc:1030-1090): per sample, the largest cosine to any other valid point
+// getGridDistance (CDMInterpolator.cc:1030-1090): per sample, the largest cosine to any other valid point -- in device
+// arithmetic; the second pass lists every point within NOISE of that maximum so that the host can take the maximum of the
+// glibc-evaluated cosines over them (llscan::exact_sample_cos), which is the reference's number
+constexpr int SAMPLE_CAND_CAP = 256;
+
+__device__ __forceinline__ double sample_cos(double c0, double s0, double lon0, double lat1, double lon1)
+{
+    const double dlon = __dsub_rn(lon0, lon1);
+    return __dadd_rn(__dmul_rn(__dmul_rn(c0, cos(lat1)), cos(dlon)), __dmul_rn(s0, sin(lat1)));
+}
+
 __global__ void __launch_bounds__(256) nn_sample_kernel(const double* __restrict__ latr, const double* __restrict__ lonr, size_t n, size_t stepSize,
-                                                        double* __restrict__ sample_cos)
+                                                        double* __restrict__ sample_cos_out)
 {
     const size_t samplePos = blockIdx.x * stepSize;
     const double lat0 = latr[samplePos], lon0 = lonr[samplePos];
@@ -139,8 +154,7 @@ __global__ void __launch_bounds__(256) nn_sample_kernel(const double* __restrict
             const double lat1 = latr[p], lon1 = lonr[p];
             if (isnan(lat1) || isnan(lon1))
                 continue;
-            const double dlon = __dsub_rn(lon0, lon1);
-            const double cd = __dadd_rn(__dmul_rn(__dmul_rn(c0, cos(lat1)), cos(dlon)), __dmul_rn(s0, sin(lat1)));
+            const double cd = sample_cos(c0, s0, lon0, lat1, lon1);
             if (cd > best)
                 best = cd;
         }
@@ -159,14 +173,39 @@ __global__ void __launch_bounds__(256) nn_sample_kernel(const double* __restrict
         __syncthreads();
     }
     if (threadIdx.x == 0)
-        sample_cos[blockIdx.x] = isnan(best) ? nan("") : red[0];
+        sample_cos_out[blockIdx.x] = isnan(best) ? nan("") : red[0];
 }
 
-// K10: fastTranslatePointsToClosestInputCell (:1137-1186): largest cos_d strictly above cos(ROI); on exact ties the scan order
-// of the reference decides: entries with lat >= p.lat in ascending latitude first, then those below in descending latitude.
+__global__ void __launch_bounds__(256) nn_sample_collect_kernel(const double* __restrict__ latr, const double* __restrict__ lonr, size_t n,
+                                                                size_t stepSize, const double* __restrict__ sample_max, double noise,
+                                                                unsigned* __restrict__ cand, unsigned* __restrict__ ncand)
+{
+    const size_t samplePos = blockIdx.x * stepSize;
+    const double lat0 = latr[samplePos], lon0 = lonr[samplePos];
+    const double top = sample_max[blockIdx.x];
+    if (isnan(lat0) || isnan(lon0) || isnan(top))
+        return;
+    const double c0 = cos(lat0), s0 = sin(lat0);
+    for (size_t p = threadIdx.x; p < n; p += 256) {
+        if (p == samplePos)
+            continue;
+        const double lat1 = latr[p], lon1 = lonr[p];
+        if (isnan(lat1) || isnan(lon1))
+            continue;
+        if (sample_cos(c0, s0, lon0, lat1, lon1) >= top - noise) {
+            const unsigned slot = atomicAdd(&ncand[blockIdx.x], 1u);
+            if (slot < SAMPLE_CAND_CAP)
+                cand[blockIdx.x * SAMPLE_CAND_CAP + slot] = static_cast<unsigned>(p);
+        }
+    }
+}
+
+// K10: fastTranslatePointsToClosestInputCell (:1137-1186) in device arithmetic: the largest cos_d, its runner-up, and the
+// verdict -- a clear winner above the ROI threshold, a clear miss, or "let the host scan decide" (see the file header)
 __global__ void __launch_bounds__(128) nn_coord_kernel(double* __restrict__ qlon, double* __restrict__ qlat, size_t nq, const double* __restrict__ latr,
                                                        const double* __restrict__ lonr, const unsigned long long* __restrict__ keys,
-                                                       const unsigned* __restrict__ vals, size_t n, SphereGrid g, double min_grid_cos_d, int nx)
+                                                       const unsigned* __restrict__ vals, size_t n, SphereGrid g, double min_grid_cos_d, double noise,
+                                                       int nx, unsigned* __restrict__ redo, unsigned* __restrict__ nredo)
 {
     const size_t i = blockIdx.x * 128ull + threadIdx.x;
     if (i >= nq)
@@ -174,7 +213,7 @@ __global__ void __launch_bounds__(128) nn_coord_kernel(double* __restrict__ qlon
     const double plat = __dmul_rn(qlat[i], NN_D2R), plon = __dmul_rn(qlon[i], NN_D2R);
     const double cpl = cos(plat), spl = sin(plat);
     const double q0 = __dmul_rn(cpl, cos(plon)), q1 = __dmul_rn(cpl, sin(plon)), q2 = spl;
-    double best = min_grid_cos_d, best_lat = 0.;
+    double best = -INFINITY, second = -INFINITY;
     unsigned best_idx = 0xffffffffu;
     if (isfinite(q0) && isfinite(q1) && isfinite(q2)) {
         const int cx = grid_coord(q0, g), cy = grid_coord(q1, g), cz = grid_coord(q2, g);
@@ -186,30 +225,24 @@ __global__ void __launch_bounds__(128) nn_coord_kernel(double* __restrict__ qlon
                     const double slat = latr[s];
                     const double dlon = __dsub_rn(lonr[s], plon);
                     const double cd = __dadd_rn(__dmul_rn(__dmul_rn(cos(slat), cpl), cos(dlon)), __dmul_rn(sin(slat), spl));
-                    bool take = cd > best;
-                    if (!take && cd == best && best_idx != 0xffffffffu) {
-                        const bool s_up = slat >= plat, b_up = best_lat >= plat;
-                        if (s_up != b_up)
-                            take = s_up;
-                        else if (slat != best_lat)
-                            take = s_up ? (slat < best_lat) : (slat > best_lat);
-                        else
-                            take = s < best_idx;
-                    }
-                    if (take) {
+                    if (cd > best) {
+                        second = best;
                         best = cd;
                         best_idx = s;
-                        best_lat = slat;
+                    } else if (cd > second) {
+                        second = cd;
                     }
                 }
             }
     }
-    if (best_idx != 0xffffffffu) {
+    if (best_idx == 0xffffffffu || best < min_grid_cos_d - noise) {
+        qlon[i] = -1.;
+        qlat[i] = -1.;
+    } else if (best > min_grid_cos_d + noise && best - second > noise) {
         qlon[i] = static_cast<double>(best_idx % nx);
         qlat[i] = static_cast<double>(best_idx / nx);
     } else {
-        qlon[i] = -1.;
-        qlat[i] = -1.;
+        redo[atomicAdd(nredo, 1u)] = static_cast<unsigned>(i); // qlon/qlat keep the target's coordinates for the host
     }
 }
 
@@ -251,21 +284,13 @@ static int build_cloud(Cloud& c, const double* lon_host, const double* lat_host,
 
 } // namespace fxcu
 
-using namespace fxcu;
+namespace fxcu {
 
-extern "C" {
-
-int fimexcu_kdtree_translate(double maxDist, double* pointsOnXAxis, double* pointsOnYAxis, size_t pointsSize, const double* lonVals,
-                             const double* latVals, size_t orgXDimSize, size_t orgYDimSize)
+// K9 without the tree (nanoflann_compat = 0 of fimexcu_kdtree_translate_mode; argument checks are the caller's)
+int kdtree_translate_grid(double maxDist, double* pointsOnXAxis, double* pointsOnYAxis, size_t pointsSize, const double* lonVals, const double* latVals,
+                          size_t orgXDimSize, size_t orgYDimSize)
 {
-    clear_error();
-    if (!require_device())
-        return FIMEXCU_ERROR;
     const size_t n = orgXDimSize * orgYDimSize;
-    if (n == 0 || n >= 2147483647ull)
-        FXCU_FAIL("fimexcu_kdtree_translate: source grid size out of range");
-    if (!(maxDist > 0))
-        FXCU_FAIL("fimexcu_kdtree_translate: maxDist must be positive"); // assert(maxDist != 0), CDMInterpolator.cc:961
     if (pointsSize == 0)
         return FIMEXCU_OK;
     const double r = maxDist / NN_EARTH_RADIUS_M; // all calculations on the unit sphere (:964)
@@ -288,6 +313,12 @@ int fimexcu_kdtree_translate(double maxDist, double* pointsOnXAxis, double* poin
     return FIMEXCU_OK;
 }
 
+} // namespace fxcu
+
+using namespace fxcu;
+
+extern "C" {
+
 int fimexcu_coordnn_translate(double* pointsOnXAxis, double* pointsOnYAxis, size_t pointsSize, const double* lonVals, const double* latVals,
                               size_t orgXDimSize, size_t orgYDimSize)
 {
@@ -297,57 +328,128 @@ int fimexcu_coordnn_translate(double* pointsOnXAxis, double* pointsOnYAxis, size
     const size_t n = orgXDimSize * orgYDimSize;
     if (n == 0 || n >= 2147483647ull)
         FXCU_FAIL("fimexcu_coordnn_translate: source grid size out of range");
-    // 1. ROI of the input data (getGridDistance): the cloud for that step needs no grid yet (chord 2 -> one cell)
-    Cloud c0;
-    if (build_cloud(c0, lonVals, latVals, n, 2.0) != FIMEXCU_OK)
-        return FIMEXCU_ERROR;
-    int steps;
-    size_t stepSize;
-    if (n > 1000) {
-        steps = 53; // "unusual grid-dimension" (:1040)
-        stepSize = n / steps;
-    } else {
-        stepSize = 1;
-        steps = static_cast<int>(n);
-    }
-    DevBuf sc;
-    if (!sc.alloc(steps * sizeof(double), nullptr))
-        return FIMEXCU_ERROR;
-    nn_sample_kernel<<<steps, 256>>>(c0.latr.as<double>(), c0.lonr.as<double>(), n, stepSize, sc.as<double>());
-    FXCU_CUDA(cudaGetLastError());
-    std::vector<double> samples(steps);
-    FXCU_CUDA(cudaMemcpy(samples.data(), sc.p, steps * sizeof(double), cudaMemcpyDeviceToHost));
-    double min_cos = 2.;
-    bool any = false;
-    for (double v : samples)
-        if (!std::isnan(v)) {
-            any = true;
-            min_cos = std::min(min_cos, v);
+    if (pointsSize >= 0xffffffffull)
+        FXCU_FAIL("fimexcu_coordnn_translate: too many target points");
+    try {
+        // the reference's latitude-sorted list (std::sort + glibc sin/cos) is prepared on the host cores while the GPU searches
+        llscan::SortedCloud sorted;
+        struct Joiner {
+            std::thread t;
+            ~Joiner()
+            {
+                if (t.joinable())
+                    t.join();
+            }
+        } sorter{std::thread([&]() { llscan::build(sorted, lonVals, latVals, orgXDimSize, orgYDimSize); })};
+
+        // 1. ROI of the input data (getGridDistance): the cloud for that step needs no grid yet (chord 2 -> one cell)
+        Cloud c0;
+        if (build_cloud(c0, lonVals, latVals, n, 2.0) != FIMEXCU_OK)
+            return FIMEXCU_ERROR;
+        int steps;
+        size_t stepSize;
+        if (n > 1000) {
+            steps = 53; // "unusual grid-dimension" (:1040)
+            stepSize = n / steps;
+        } else {
+            stepSize = 1;
+            steps = static_cast<int>(n);
         }
-    if (!any)
-        FXCU_FAIL("fimexcu_coordnn_translate: no valid sample point to estimate the grid distance");
-    const double PI = 3.1415926535897932384626433832795;
-    const double max_grid_d = std::min(std::acos(std::max(-1.0, std::min(1.0, min_cos))) * 1.414, PI); // :1088-1089
-    const double min_grid_cos_d = std::cos(max_grid_d);
-    if (pointsSize == 0)
+        DevBuf sc, cand, ncand;
+        if (!sc.alloc(steps * sizeof(double), nullptr) || !cand.alloc(size_t(steps) * SAMPLE_CAND_CAP * 4, nullptr) || !ncand.alloc(size_t(steps) * 4, nullptr))
+            return FIMEXCU_ERROR;
+        FXCU_CUDA(cudaMemsetAsync(ncand.p, 0, size_t(steps) * 4, nullptr));
+        nn_sample_kernel<<<steps, 256>>>(c0.latr.as<double>(), c0.lonr.as<double>(), n, stepSize, sc.as<double>());
+        FXCU_CUDA(cudaGetLastError());
+        nn_sample_collect_kernel<<<steps, 256>>>(c0.latr.as<double>(), c0.lonr.as<double>(), n, stepSize, sc.as<double>(), llscan::NOISE,
+                                                 cand.as<unsigned>(), ncand.as<unsigned>());
+        FXCU_CUDA(cudaGetLastError());
+        std::vector<double> devMax(steps);
+        std::vector<unsigned> hCand(size_t(steps) * SAMPLE_CAND_CAP), hCount(steps);
+        FXCU_CUDA(cudaMemcpy(devMax.data(), sc.p, steps * sizeof(double), cudaMemcpyDeviceToHost));
+        FXCU_CUDA(cudaMemcpy(hCand.data(), cand.p, hCand.size() * 4, cudaMemcpyDeviceToHost));
+        FXCU_CUDA(cudaMemcpy(hCount.data(), ncand.p, size_t(steps) * 4, cudaMemcpyDeviceToHost));
+        // the samples in glibc arithmetic: largest cosine over the listed candidates (or over everything, should a sample sit in
+        // a heap of more than SAMPLE_CAND_CAP near-equidistant points)
+        double min_cos = 0.;
+        bool any = false;
+        for (int ik = 0; ik < steps; ++ik) {
+            const size_t samplePos = ik * stepSize;
+            if (std::isnan(lonVals[samplePos] * llscan::D2R) || std::isnan(latVals[samplePos] * llscan::D2R))
+                continue; // :1053
+            double v;
+            if (hCount[ik] <= SAMPLE_CAND_CAP) {
+                v = llscan::exact_sample_cos(latVals[samplePos], lonVals[samplePos], lonVals, latVals, &hCand[size_t(ik) * SAMPLE_CAND_CAP], hCount[ik]);
+            } else {
+                std::vector<unsigned> all;
+                all.reserve(n);
+                for (size_t ix = 0; ix < orgXDimSize; ++ix)
+                    for (size_t iy = 0; iy < orgYDimSize; ++iy) {
+                        const size_t pos = ix + iy * orgXDimSize;
+                        if (pos != samplePos && !(std::isnan(lonVals[pos]) || std::isnan(latVals[pos])))
+                            all.push_back(static_cast<unsigned>(pos));
+                    }
+                v = llscan::exact_sample_cos(latVals[samplePos], lonVals[samplePos], lonVals, latVals, all.data(), all.size());
+            }
+            if (!any || v < min_cos)
+                min_cos = v;
+            any = true;
+        }
+        if (!any)
+            FXCU_FAIL("fimexcu_coordnn_translate: no valid sample point to estimate the grid distance"); // the reference dereferences end() here
+        const double MIFI_PI_D = 3.1415926535897932384626433832795;
+        const double grid_d = std::acos(min_cos) * 1.414;                                  // :1088
+        const double max_grid_d = (MIFI_PI_D < grid_d) ? MIFI_PI_D : grid_d;              // std::min(max_grid_d, MIFI_PI), :1089
+        const double min_grid_cos_d = std::cos(max_grid_d);
+        if (pointsSize == 0)
+            return FIMEXCU_OK;
+        if (std::isnan(min_grid_cos_d)) {
+            // a lone source point (or coincident sample pairs whose cosine rounds above 1) gives acos() = NaN in the reference:
+            // no cosine is greater than NaN, every target stays at its initial (-1, -1)
+            for (size_t i = 0; i < pointsSize; ++i)
+                pointsOnXAxis[i] = pointsOnYAxis[i] = -1.;
+            return FIMEXCU_OK;
+        }
+        // 2. the search, on a grid whose cells are as wide as the largest admissible chord
+        Cloud c;
+        if (build_cloud(c, lonVals, latVals, n, 2.0 * std::sin(max_grid_d / 2.0)) != FIMEXCU_OK)
+            return FIMEXCU_ERROR;
+        DevBuf qx, qy, redo, nredo;
+        if (!qx.alloc(pointsSize * 8, nullptr) || !qy.alloc(pointsSize * 8, nullptr) || !redo.alloc(pointsSize * 4, nullptr) || !nredo.alloc(4, nullptr))
+            return FIMEXCU_ERROR;
+        FXCU_CUDA(cudaMemcpyAsync(qx.p, pointsOnXAxis, pointsSize * 8, cudaMemcpyHostToDevice, nullptr));
+        FXCU_CUDA(cudaMemcpyAsync(qy.p, pointsOnYAxis, pointsSize * 8, cudaMemcpyHostToDevice, nullptr));
+        FXCU_CUDA(cudaMemsetAsync(nredo.p, 0, 4, nullptr));
+        nn_coord_kernel<<<blocks_for(pointsSize, 128), 128>>>(qx.as<double>(), qy.as<double>(), pointsSize, c.latr.as<double>(), c.lonr.as<double>(),
+                                                              c.keyS.as<unsigned long long>(), c.valS.as<unsigned>(), n, c.g, min_grid_cos_d,
+                                                              llscan::NOISE, static_cast<int>(orgXDimSize), redo.as<unsigned>(), nredo.as<unsigned>());
+        FXCU_CUDA(cudaGetLastError());
+        unsigned hRedo = 0;
+        FXCU_CUDA(cudaMemcpyAsync(&hRedo, nredo.p, 4, cudaMemcpyDeviceToHost, nullptr));
+        FXCU_CUDA(cudaMemcpyAsync(pointsOnXAxis, qx.p, pointsSize * 8, cudaMemcpyDeviceToHost, nullptr));
+        FXCU_CUDA(cudaMemcpyAsync(pointsOnYAxis, qy.p, pointsSize * 8, cudaMemcpyDeviceToHost, nullptr));
+        FXCU_CUDA(cudaStreamSynchronize(nullptr));
+        sorter.t.join();
+        if (hRedo) {
+            std::vector<unsigned> list(hRedo);
+            FXCU_CUDA(cudaMemcpy(list.data(), redo.p, size_t(hRedo) * 4, cudaMemcpyDeviceToHost));
+            parallel_ranges(hRedo, 16, [&](size_t a, size_t b) {
+                for (size_t k = a; k < b; ++k) {
+                    const size_t i = list[k]; // pointsOn?Axis[i] still hold the target's lon / lat
+                    const long pos = llscan::scan(sorted, pointsOnXAxis[i], pointsOnYAxis[i], min_grid_cos_d);
+                    if (pos >= 0) {
+                        pointsOnXAxis[i] = static_cast<double>(size_t(pos) % orgXDimSize);
+                        pointsOnYAxis[i] = static_cast<double>(size_t(pos) / orgXDimSize);
+                    } else {
+                        pointsOnXAxis[i] = pointsOnYAxis[i] = -1.;
+                    }
+                }
+            });
+        }
         return FIMEXCU_OK;
-    // 2. the search, on a grid whose cells are as wide as the largest admissible chord
-    Cloud c;
-    if (build_cloud(c, lonVals, latVals, n, 2.0 * std::sin(max_grid_d / 2.0)) != FIMEXCU_OK)
-        return FIMEXCU_ERROR;
-    DevBuf qx, qy;
-    if (!qx.alloc(pointsSize * 8, nullptr) || !qy.alloc(pointsSize * 8, nullptr))
-        return FIMEXCU_ERROR;
-    FXCU_CUDA(cudaMemcpyAsync(qx.p, pointsOnXAxis, pointsSize * 8, cudaMemcpyHostToDevice, nullptr));
-    FXCU_CUDA(cudaMemcpyAsync(qy.p, pointsOnYAxis, pointsSize * 8, cudaMemcpyHostToDevice, nullptr));
-    nn_coord_kernel<<<blocks_for(pointsSize, 128), 128>>>(qx.as<double>(), qy.as<double>(), pointsSize, c.latr.as<double>(), c.lonr.as<double>(),
-                                                          c.keyS.as<unsigned long long>(), c.valS.as<unsigned>(), n, c.g, min_grid_cos_d,
-                                                          static_cast<int>(orgXDimSize));
-    FXCU_CUDA(cudaGetLastError());
-    FXCU_CUDA(cudaMemcpyAsync(pointsOnXAxis, qx.p, pointsSize * 8, cudaMemcpyDeviceToHost, nullptr));
-    FXCU_CUDA(cudaMemcpyAsync(pointsOnYAxis, qy.p, pointsSize * 8, cudaMemcpyDeviceToHost, nullptr));
-    FXCU_CUDA(cudaStreamSynchronize(nullptr));
-    return FIMEXCU_OK;
+    } catch (const std::exception& e) {
+        FXCU_FAIL(std::string("fimexcu_coordnn_translate: ") + e.what());
+    }
 }
 
 } // extern "C"

@@ -252,10 +252,22 @@ fimexcu_cache* fimexcu_cache_create_from_points(int method, const char* proj_poi
  * ---------------------------------------------------------------------------------------------- */
 /* Replaces flannTranslatePointsToClosestInputCell (src/CDMInterpolator.cc:953-1028; nanoflann radiusSearch, first
  * sorted match).  pointsOnXAxis/pointsOnYAxis: in = target lon/lat in degrees, out = source (ix, iy) as doubles,
- * or -1000 when nothing lies within maxDist (metres on the R=6371000 sphere).  HOST pointers. */
+ * or -1000 when nothing lies within maxDist (metres on the R=6371000 sphere).  HOST pointers.
+ * Result identical to the reference's, including what follows from nanoflann's tree layout (include/nanoflann/nanoflann.hpp
+ * :1053-1237, :1263-1310) and libstdc++'s std::sort (:972): which of several exactly equidistant source points wins, and which
+ * matches are lost when the cloud holds NaN coordinates (the reference keeps them in the tree, CDMInterpolator.cc:982-986).
+ * Unit-sphere coordinates come from the host's libm, the tree is built on the host cores, the walk runs on the GPU. */
 int fimexcu_kdtree_translate(double maxDist, double* pointsOnXAxis, double* pointsOnYAxis, size_t pointsSize, const double* lonVals,
                              const double* latVals, size_t orgXDimSize, size_t orgYDimSize);
-/* Replaces fastTranslatePointsToClosestInputCell + getGridDistance (CDMInterpolator.cc:1030-1190): misses give -1. */
+/* Same with a switch, like level_compat of the forward cache: nanoflann_compat = 1 is fimexcu_kdtree_translate;
+ * nanoflann_compat = 0 is the corrected behaviour -- source points with NaN coordinates are left out, so that every target gets
+ * its true nearest source point within maxDist, and exact ties go to the lower source index (tree-free search on the GPU). */
+int fimexcu_kdtree_translate_mode(double maxDist, double* pointsOnXAxis, double* pointsOnYAxis, size_t pointsSize, const double* lonVals,
+                                  const double* latVals, size_t orgXDimSize, size_t orgYDimSize, int nanoflann_compat);
+/* Replaces fastTranslatePointsToClosestInputCell + getGridDistance (CDMInterpolator.cc:1030-1190): misses give -1.
+ * Result identical to the reference's: the GPU search decides every target whose best candidate is clear of the runner-up and of
+ * the ROI threshold by more than the device/glibc sin-cos noise (1e-13 in the cosine); the others (near and exact ties, ROI edge)
+ * are decided by the reference's own latitude-sorted scan on the host, on a list ordered by this libstdc++'s std::sort. */
 int fimexcu_coordnn_translate(double* pointsOnXAxis, double* pointsOnYAxis, size_t pointsSize, const double* lonVals, const double* latVals,
                               size_t orgXDimSize, size_t orgYDimSize);
 

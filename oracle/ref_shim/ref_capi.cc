@@ -225,6 +225,105 @@ int ref_kdtree_translate(double maxDist_m, double* pointsOnX_deg, double* points
     return 0;
 }
 
+// coord_nearestneighbor: fastTranslatePointsToClosestInputCell + getGridDistance (CDMInterpolator.cc:1030-1190) also sit in the
+// anonymous namespace of the translation unit that cannot be linked here.  Restated on the SAME library calls the reference
+// makes -- std::sort on a 4-double record compared by latitude only (not stable: the order of equal latitudes is libstdc++'s
+// introsort's), std::lower_bound, std::min_element, glibc sin/cos/acos -- so that the tie order is the reference's.
+namespace {
+struct LatLonRecord {
+    double lat, lon, x, y; // radians, radians, source ix, source iy
+    bool operator<(const LatLonRecord& o) const { return lat < o.lat; }
+};
+} // namespace
+
+double ref_grid_distance(const double* lon_deg, const double* lat_deg, size_t nx, size_t ny)
+{
+    std::vector<double> samples;
+    int steps;
+    size_t stepSize;
+    if (nx * ny > 1000) {
+        steps = 53;
+        stepSize = nx * ny / steps;
+    } else {
+        stepSize = 1;
+        steps = static_cast<int>(nx * ny);
+    }
+    for (int ik = 0; ik < steps; ++ik) {
+        const size_t samplePos = ik * stepSize;
+        const double lon0 = deg_to_rad(lon_deg[samplePos]), lat0 = deg_to_rad(lat_deg[samplePos]);
+        if (std::isnan(lon0) || std::isnan(lat0))
+            continue;
+        double largest = -2;
+        for (size_t ix = 0; ix < nx; ++ix)
+            for (size_t iy = 0; iy < ny; ++iy) {
+                const size_t pos = ix + iy * nx;
+                if (pos == samplePos)
+                    continue;
+                const double lon1 = deg_to_rad(lon_deg[pos]), lat1 = deg_to_rad(lat_deg[pos]);
+                if (std::isnan(lon1) || std::isnan(lat1))
+                    continue;
+                const double dlon = lon0 - lon1;
+                const double cos_d = cos(lat0) * cos(lat1) * cos(dlon) + sin(lat0) * sin(lat1);
+                if (cos_d > largest)
+                    largest = cos_d;
+            }
+        samples.push_back(largest);
+    }
+    const double d = acos(*std::min_element(samples.begin(), samples.end())) * 1.414;
+    return std::min(d, MIFI_PI);
+}
+
+int ref_coordnn_translate(double* pointsOnX_deg, double* pointsOnY_deg, size_t nPoints, const double* lon_deg, const double* lat_deg, size_t nx, size_t ny)
+{
+    const double roi = ref_grid_distance(lon_deg, lat_deg, nx, ny);
+    const double roi_cos = cos(roi);
+    std::vector<LatLonRecord> recs;
+    recs.reserve(nx * ny);
+    for (size_t ix = 0; ix < nx; ++ix)
+        for (size_t iy = 0; iy < ny; ++iy) {
+            const size_t pos = ix + iy * nx;
+            if (!(std::isnan(lon_deg[pos]) || std::isnan(lat_deg[pos])))
+                recs.push_back(LatLonRecord{deg_to_rad(lat_deg[pos]), deg_to_rad(lon_deg[pos]), double(ix), double(iy)});
+        }
+    std::sort(recs.begin(), recs.end());
+#pragma omp parallel for
+    for (long i = 0; i < static_cast<long>(nPoints); ++i) {
+        LatLonRecord p{deg_to_rad(pointsOnY_deg[i]), deg_to_rad(pointsOnX_deg[i]), -1., -1.};
+        double best_cos = roi_cos, best_d = acos(best_cos);
+        auto up = std::lower_bound(recs.begin(), recs.end(), p);
+        auto down = up;
+        while (up != recs.end()) {
+            if (fabs(up->lat - p.lat) > best_d)
+                break;
+            const double dlon = up->lon - p.lon;
+            const double cos_d = cos(up->lat) * cos(p.lat) * cos(dlon) + sin(up->lat) * sin(p.lat);
+            if (cos_d > best_cos) {
+                best_cos = cos_d;
+                best_d = acos(best_cos);
+                p.x = up->x;
+                p.y = up->y;
+            }
+            ++up;
+        }
+        while (down != recs.begin()) {
+            --down;
+            if (fabs(down->lat - p.lat) > best_d)
+                break;
+            const double dlon = down->lon - p.lon;
+            const double cos_d = cos(down->lat) * cos(p.lat) * cos(dlon) + sin(down->lat) * sin(p.lat);
+            if (cos_d > best_cos) {
+                best_cos = cos_d;
+                best_d = acos(best_cos);
+                p.x = down->x;
+                p.y = down->y;
+            }
+        }
+        pointsOnY_deg[i] = p.y;
+        pointsOnX_deg[i] = p.x;
+    }
+    return 0;
+}
+
 // ---- src/reproject.cc driven through its public functions (PROJ replaced by ref_shim/proj.h) ----
 int ref_reproject_axes(const char* proj_in, const char* proj_out, const double* in_x, const double* in_y, int ix, int iy, double* out_x, double* out_y)
 {

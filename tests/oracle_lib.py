@@ -13,6 +13,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
+HERE = os.path.dirname(os.path.abspath(__file__))
 
 c_double_p = C.POINTER(C.c_double)
 c_float_p = C.POINTER(C.c_float)
@@ -173,6 +174,8 @@ def ref(omp=False):
         "ref_find_closest_neighbor_distinct_elements": (None, [c_float_p, C.c_size_t, C.c_long, C.c_double, C.POINTER(C.c_long), C.POINTER(C.c_long)]),
         "ref_find_closest_distinct_elements": (None, [c_float_p, C.c_size_t, C.c_long, C.c_double, C.POINTER(C.c_long), C.POINTER(C.c_long)]),
         "ref_kdtree_translate": (C.c_int, [C.c_double, c_double_p, c_double_p, C.c_size_t, c_double_p, c_double_p, C.c_size_t, C.c_size_t]),
+        "ref_coordnn_translate": (C.c_int, [c_double_p, c_double_p, C.c_size_t, c_double_p, c_double_p, C.c_size_t, C.c_size_t]),
+        "ref_grid_distance": (C.c_double, [c_double_p, c_double_p, C.c_size_t, C.c_size_t]),
         "ref_vector_reproject_values_by_matrix_f": (None, [c_double_p, C.c_int, C.c_int, c_float_p, c_float_p, C.c_int]),
         "ref_vector_reproject_direction_by_matrix_f": (None, [c_double_p, C.c_int, C.c_int, c_float_p, C.c_int]),
         "ref_reproject_axes": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, C.c_int, C.c_int, c_double_p, c_double_p]),
@@ -284,3 +287,29 @@ def o_packed_apply(method, px, py, inX, inY, outX, outY, raw, badValue):
 
 
 PACKED_DTYPES = {0: np.int8, 1: np.int16, 2: np.int32, 3: np.uint8, 4: np.uint16, 5: np.uint32}
+
+
+# ---------------------------------------------------------------- CPU harnesses over the product's host-only headers
+_native = {}
+
+
+def native(name):
+    """tests/native/<name>.cc -> lib<name>.so (g++; built on first use).  These drive the HOST-side logic of libfimexcu's
+    coordinate searches (fimex_b200/csrc/fxcu_kdclone.h, fxcu_llscan.h) so that it can be tested without a GPU."""
+    if name in _native:
+        return _native[name]
+    src = os.path.join(HERE, "native", name + ".cc")
+    so = os.path.join(HERE, "native", "lib" + name + ".so")
+    deps = [src] + [os.path.join(ROOT, "fimex_b200", "csrc", h) for h in ("fxcu_kdclone.h", "fxcu_llscan.h", "fxcu_hostpar.h")]
+    if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
+        subprocess.run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-pthread", "-o", so, src], check=True)
+    lib = C.CDLL(so)
+    if name == "kdclone_host":
+        lib.kdclone_translate_host.restype = C.c_int
+        lib.kdclone_translate_host.argtypes = [C.c_double, c_double_p, c_double_p, C.c_size_t, c_double_p, c_double_p, C.c_size_t, C.c_size_t, C.c_uint,
+                                               C.c_char_p, C.c_size_t]
+    elif name == "llscan_host":
+        lib.llscan_translate_host.restype = C.c_int
+        lib.llscan_translate_host.argtypes = [c_double_p, c_double_p, C.c_size_t, c_double_p, c_double_p, C.c_size_t, C.c_size_t, C.c_double]
+    _native[name] = lib
+    return lib

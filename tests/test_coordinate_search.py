@@ -1,9 +1,14 @@
 """Coordinate-based nearest neighbour (coord_kdtree K9, coord_nearestneighbor K10).
 
-CPU part: the tree-free restatement in oracle/ against the reference's vendored nanoflann (oracle/_ref).
-GPU part: libfimexcu against both.  Bar: identical source cell for every target, except targets whose best and second-best
-candidates are closer together than the sin/cos rounding noise (|d2 gap| <= 1e-12 relative: the device's and glibc's sin/cos
-differ in the last bit) and exact-distance ties between duplicated source positions, where the chosen duplicate may differ."""
+Bar: the source cell of EVERY target equals the reference's -- np.array_equal, no tolerance, no whitelist -- including what follows
+from nanoflann's tree layout (which of several exactly equidistant duplicates wins; which matches a cloud with NaN coordinates
+loses) and from the reference's latitude-sorted scan order.  Checkers: the reference's vendored nanoflann driven as
+CDMInterpolator.cc:953-1028 drives it (oracle/_ref: ref_kdtree_translate) and its coord_nearestneighbor scan restated on the same
+libstdc++ calls (ref_coordnn_translate).
+CPU part: the host-side logic of the product (tree build + walk, sorted scan; tests/native harnesses) and the tree-free oracle.
+GPU part: libfimexcu through the C ABI."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -54,99 +59,186 @@ def test_oracle_kdtree_restatement_matches_nanoflann(oracle, ref):
     assert ((bx == -1000) & (ax >= 0)).sum() > 100 and not ((ax == -1000) & (bx >= 0)).any()
 
 
-def _same_cells(gx, gy, wx, wy, lon, lat, ambiguous):
-    diff = (gx != wx) | (gy != wy)
-    bad = diff & ~ambiguous
-    if bad.any():
-        # duplicates: a different index at the very same position is fine
-        ok = np.zeros(bad.sum(), bool)
-        for k, i in enumerate(np.flatnonzero(bad)):
-            if gx[i] >= 0 and wx[i] >= 0:
-                a, b = (int(gy[i]), int(gx[i])), (int(wy[i]), int(wx[i]))
-                ok[k] = lon[a] == lon[b] and lat[a] == lat[b]
-        return ok.all()
-    return True
+# ---------------------------------------------------------------- CPU: the product's host-side logic against the reference
+CLOUDS = ["plain", "edge_nan", "edge_nan_wrap", "scatter_nan", "first_nan", "heavy_nan", "rounded_dups", "one_position"]
+
+
+def cloud(rng, nx, ny, kind):
+    lon, lat = swath(rng, nx, ny, nan_frac=0.005 if kind.startswith("edge_nan") else 0.0, wrap_column=kind.endswith("wrap"))
+    if kind == "scatter_nan":
+        lat[rng.random(lat.shape) < 0.05] = np.nan
+    elif kind == "first_nan":  # the bounding box of the whole tree starts from point 0 (nanoflann.hpp:1020-1039)
+        lat[0, 0] = np.nan
+    elif kind == "heavy_nan":
+        lon[rng.random(lat.shape) < 0.4] = np.nan
+        lat[0, 0] = np.nan
+    elif kind == "rounded_dups":  # many exactly equal positions: ties everywhere, more than 16 matches per target
+        lat[:], lon[:] = np.round(lat), np.round(lon)
+    elif kind == "one_position":
+        lat[:], lon[:] = 60.0, 10.0
+    return lon, lat
+
+
+def cloud_targets(rng, n, kind):
+    qx, qy = targets(rng, n)
+    if kind in ("rounded_dups", "one_position"):
+        qx, qy = np.round(qx * 2) / 2, np.round(qy * 2) / 2  # exactly between duplicates
+    return qx, qy
+
+
+@pytest.mark.parametrize("kind", CLOUDS)
+def test_host_tree_clone_equals_nanoflann(ref, kind):
+    """fxcu_kdclone.h (build + walk + std::sort) against the reference's nanoflann, every target, sequential and threaded build"""
+    lib = ol.native("kdclone_host")
+    rng = np.random.default_rng(CLOUDS.index(kind))
+    nx, ny = 61, 83
+    lon, lat = cloud(rng, nx, ny, kind)
+    qx, qy = cloud_targets(rng, 4000, kind)
+    for maxdist, threads in ((60000.0, 1), (400000.0, 1), (60000.0, 8)):
+        ax, ay, err = qx.copy(), qy.copy(), C.create_string_buffer(512)
+        assert lib.kdclone_translate_host(maxdist, dp(ax), dp(ay), ax.size, dp(lon), dp(lat), nx, ny, threads, err, 512) == 0, err.value
+        bx, by = qx.copy(), qy.copy()
+        assert ref.ref_kdtree_translate(maxdist, dp(bx), dp(by), bx.size, dp(lon), dp(lat), nx, ny) == 0
+        assert np.array_equal(ax, bx) and np.array_equal(ay, by)
+        assert (bx >= 0).any()
+
+
+def test_host_tree_clone_threaded_build_large(ref):
+    lib = ol.native("kdclone_host")
+    rng = np.random.default_rng(77)
+    nx, ny = 403, 335  # > 65536 points: the threaded build really forks
+    lon, lat = cloud(rng, nx, ny, "edge_nan_wrap")
+    qx, qy = targets(rng, 20000)
+    ax, ay, err = qx.copy(), qy.copy(), C.create_string_buffer(512)
+    assert lib.kdclone_translate_host(20000.0, dp(ax), dp(ay), ax.size, dp(lon), dp(lat), nx, ny, 8, err, 512) == 0, err.value
+    bx, by = qx.copy(), qy.copy()
+    ref.ref_kdtree_translate(20000.0, dp(bx), dp(by), bx.size, dp(lon), dp(lat), nx, ny)
+    assert np.array_equal(ax, bx) and np.array_equal(ay, by) and (bx >= 0).sum() > 1000
+
+
+@pytest.mark.parametrize("kind", ["plain", "edge_nan_wrap", "scatter_nan", "rounded_dups"])
+def test_host_sorted_scan_equals_reference(ref, kind):
+    """fxcu_llscan.h (compact keys, dot-product shortcut) against the scan restated on the reference's own library calls"""
+    lib = ol.native("llscan_host")
+    rng = np.random.default_rng(20 + CLOUDS.index(kind))
+    nx, ny = 97, 71
+    lon, lat = cloud(rng, nx, ny, kind)
+    if kind == "rounded_dups":
+        lon, lat = swath(rng, nx, ny, nan_frac=0.0)
+        lat[:], lon[:] = np.round(lat * 2) / 2, np.round(lon * 2) / 2
+    qx, qy = cloud_targets(rng, 6000, kind)
+    roi = ref.ref_grid_distance(dp(lon), dp(lat), nx, ny)
+    ax, ay = qx.copy(), qy.copy()
+    lib.llscan_translate_host(dp(ax), dp(ay), ax.size, dp(lon), dp(lat), nx, ny, roi)
+    bx, by = qx.copy(), qy.copy()
+    ref.ref_coordnn_translate(dp(bx), dp(by), bx.size, dp(lon), dp(lat), nx, ny)
+    assert np.array_equal(ax, bx) and np.array_equal(ay, by)
+    assert (bx >= 0).any() and (bx == -1).any()
+
+
+# ---------------------------------------------------------------- GPU: libfimexcu through the C ABI
+def _ref_or_skip():
+    r = ol.ref(omp=True)
+    if r is None:
+        pytest.skip("oracle/_ref not built")
+    return r
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("wrap", [False, True])
-def test_gpu_kdtree_matches_reference(wrap):
+@pytest.mark.parametrize("kind", CLOUDS)
+def test_gpu_kdtree_equals_nanoflann(kind):
     import fimex_b200
     from fimex_b200.coordinates import flannTranslatePointsToClosestInputCell as gpu
     assert fimex_b200.lib.fimexcu_device_count() >= 1
-    rng = np.random.default_rng(9)
+    r = _ref_or_skip()
+    rng = np.random.default_rng(100 + CLOUDS.index(kind))
     nx, ny = 203, 135
-    lon, lat = swath(rng, nx, ny, nan_frac=0.0, wrap_column=wrap)
-    qx, qy = targets(rng, 30000)
-    qx[:50], qy[:50] = lon[10, 20:70], lat[10, 20:70]  # exact hits
-    for maxdist in (3000.0, 15000.0):
+    lon, lat = cloud(rng, nx, ny, kind)
+    qx, qy = cloud_targets(rng, 30000, kind)
+    ok = ~np.isnan(lat[10, 20:70])
+    qx[:50][ok], qy[:50][ok] = lon[10, 20:70][ok], lat[10, 20:70][ok]  # exact hits
+    qx[50], qy[51] = np.nan, np.nan                                    # NaN targets find nothing
+    for maxdist in (3000.0, 15000.0, 150000.0):                        # the last: far more than 16 matches per target
         gx, gy = gpu(maxdist, qx, qy, lon, lat)
-        wx, wy, gap = qx.copy(), qy.copy(), np.empty(qx.size)
-        ol.oracle().orc_kdtree_translate(maxdist, dp(wx), dp(wy), wx.size, dp(lon), dp(lat), nx, ny, dp(gap))
-        r2 = (maxdist / 6371000.0) ** 2
-        assert _same_cells(gx, gy, wx, wy, lon, lat, ambiguous=np.abs(gap) <= 1e-12 * r2 + 1e-28)
-        assert ((gx == wx) & (gy == wy)).mean() > 0.9999
-        r = ol.ref()
-        if r is not None and not wrap:  # nanoflann itself (tie order of duplicates is its own)
-            bx, by = qx.copy(), qy.copy()
-            r.ref_kdtree_translate(maxdist, dp(bx), dp(by), bx.size, dp(lon), dp(lat), nx, ny)
-            assert ((gx == bx) & (gy == by)).mean() > 0.9999
-        assert (gx == -1000).any() and (gx >= 0).any()
-    # NaN source coordinates are skipped, everything else still found (brute-force restatement as the checker)
-    lon2, lat2 = swath(rng, nx, ny, nan_frac=0.01)
-    assert np.isnan(lat2).any()
-    gx, gy = gpu(15000.0, qx, qy, lon2, lat2)
-    wx, wy, gap = qx.copy(), qy.copy(), np.empty(qx.size)
-    ol.oracle().orc_kdtree_translate(15000.0, dp(wx), dp(wy), wx.size, dp(lon2), dp(lat2), nx, ny, dp(gap))
-    assert _same_cells(gx, gy, wx, wy, lon2, lat2, ambiguous=np.abs(gap) <= 1e-12 * (15000.0 / 6371000.0) ** 2 + 1e-28)
+        bx, by = qx.copy(), qy.copy()
+        r.ref_kdtree_translate(maxdist, dp(bx), dp(by), bx.size, dp(lon), dp(lat), nx, ny)
+        assert np.array_equal(gx, bx) and np.array_equal(gy, by)
+        assert gx[50] == -1000 and gx[51] == -1000
+    assert (bx >= 0).any()
 
 
 @pytest.mark.gpu
-def test_gpu_kdtree_config4_size():
-    """2030x1354 swath -> 0.025 deg grid, radius = target spacing: every match is within the radius and is the nearest
-    (checked against a brute-force subset), NaN source coordinates are never matched"""
+def test_gpu_kdtree_config4_as_written():
+    """2030x1354 swath, 0.5 % NaN coordinates at the edges, one duplicated wrap column (exact ties),
+    radius = target spacing of a 0.025 deg grid: every target equals nanoflann's answer"""
     from fimex_b200.coordinates import flannTranslatePointsToClosestInputCell as gpu
+    r = _ref_or_skip()
     rng = np.random.default_rng(2)
     nx, ny = 1354, 2030
-    lon, lat = swath(rng, nx, ny)
-    tlon, tlat = np.meshgrid(np.arange(0, 20, 0.025), np.arange(58, 70, 0.025))
+    lon, lat = swath(rng, nx, ny, nan_frac=0.005, wrap_column=True)
+    assert np.isnan(lat).any()
+    # the grid covers the swath's western edge, where the NaN coordinates and the duplicated column (0 == nx-1) lie
+    tlon, tlat = np.meshgrid(np.arange(-18, 2, 0.025), np.arange(53, 65, 0.025))
     maxdist = 0.025 * np.pi / 180 * 6371000.0
     gx, gy = gpu(maxdist, tlon, tlat, lon, lat)
-    hit = gx >= 0
-    assert hit.mean() > 0.3 and (gx[~hit] == -1000).all()
-    iy, ix = gy[hit].astype(int), gx[hit].astype(int)
-    assert not np.isnan(lat[iy, ix]).any()
-
-    def xyz(lo, la):
-        lo, la = np.radians(lo), np.radians(la)
-        return np.stack([np.cos(la) * np.cos(lo), np.cos(la) * np.sin(lo), np.sin(la)], -1)
-    d = np.linalg.norm(xyz(tlon[hit], tlat[hit]) - xyz(lon[iy, ix], lat[iy, ix]), axis=-1)
-    assert (d < maxdist / 6371000.0).all()
-    sel = rng.choice(tlon.size, 300, replace=False)
-    wx, wy = tlon.ravel()[sel].copy(), tlat.ravel()[sel].copy()
-    gap = np.empty(sel.size)
-    ol.oracle().orc_kdtree_translate(maxdist, dp(wx), dp(wy), wx.size, dp(lon), dp(lat), nx, ny, dp(gap))
-    amb = np.abs(gap) <= 1e-12 * (maxdist / 6371000.0) ** 2
-    assert (((gx.ravel()[sel] == wx) & (gy.ravel()[sel] == wy)) | amb).all()
+    bx, by = tlon.ravel().copy(), tlat.ravel().copy()
+    r.ref_kdtree_translate(maxdist, dp(bx), dp(by), bx.size, dp(lon), dp(lat), nx, ny)
+    assert np.array_equal(gx.ravel(), bx) and np.array_equal(gy.ravel(), by)
+    hit = bx >= 0
+    assert hit.mean() > 0.2 and (bx[~hit] == -1000).all()
+    # the duplicated column is really exercised: targets whose winner sits on column 0 or on its copy
+    assert ((bx == 0) | (bx == nx - 1)).sum() > 100
 
 
 @pytest.mark.gpu
-def test_gpu_coord_nearestneighbor_matches_oracle():
+def test_gpu_kdtree_corrected_mode(oracle):
+    """nanoflann_compat=0: NaN source points are left out and every target gets its true nearest point (the tree-free oracle),
+    which the reference does not deliver on such clouds"""
+    from fimex_b200.coordinates import flannTranslatePointsToClosestInputCell as gpu
+    rng = np.random.default_rng(9)
+    nx, ny = 203, 135
+    lon, lat = swath(rng, nx, ny, nan_frac=0.01)
+    assert np.isnan(lat).any()
+    qx, qy = targets(rng, 30000)
+    gx, gy = gpu(15000.0, qx, qy, lon, lat, nanoflann_compat=False)
+    wx, wy, gap = qx.copy(), qy.copy(), np.empty(qx.size)
+    oracle.orc_kdtree_translate(15000.0, dp(wx), dp(wy), wx.size, dp(lon), dp(lat), nx, ny, dp(gap))
+    clear = np.abs(gap) > 1e-12 * (15000.0 / 6371000.0) ** 2 + 1e-28  # this mode uses the device's sin/cos
+    assert np.array_equal(gx[clear], wx[clear]) and np.array_equal(gy[clear], wy[clear])
+    assert clear.mean() > 0.999 and (wx >= 0).sum() > 1000
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["plain", "edge_nan_wrap", "scatter_nan", "rounded_dups"])
+def test_gpu_coord_nearestneighbor_equals_reference(kind):
     from fimex_b200.coordinates import fastTranslatePointsToClosestInputCell as gpu
-    rng = np.random.default_rng(11)
+    r = _ref_or_skip()
+    rng = np.random.default_rng(200 + CLOUDS.index(kind))
     nx, ny = 151, 97
-    lon, lat = swath(rng, nx, ny)
-    qx, qy = targets(rng, 20000)
+    lon, lat = cloud(rng, nx, ny, kind)
+    if kind == "rounded_dups":
+        lon, lat = swath(rng, nx, ny, nan_frac=0.0)
+        lat[:], lon[:] = np.round(lat * 2) / 2, np.round(lon * 2) / 2
+    qx, qy = cloud_targets(rng, 20000, kind)
+    qx[:40], qy[:40] = lon[5, 10:50], lat[5, 10:50]
+    qx[41] = np.nan
     gx, gy = gpu(qx, qy, lon, lat)
-    wx, wy = qx.copy(), qy.copy()
-    ol.oracle().orc_coordnn_translate(dp(wx), dp(wy), wx.size, dp(lon), dp(lat), nx, ny)
-    same = (gx == wx) & (gy == wy)
-    assert same.mean() > 0.9995  # cos_d near-ties at the sin/cos rounding level may pick the other of two equidistant cells
-    assert (wx == -1).any() and (wx >= 0).any() and np.array_equal(gx == -1, wx == -1) or same.mean() > 0.9999
-    # where they differ, the two candidates are equally far from the target to within 1e-12
-    for i in np.flatnonzero(~same)[:20]:
-        def cosd(ix, iy):
-            a, b = np.radians(lat[int(iy), int(ix)]), np.radians(qy[i])
-            return np.cos(a) * np.cos(b) * np.cos(np.radians(lon[int(iy), int(ix)] - qx[i])) + np.sin(a) * np.sin(b)
-        if gx[i] >= 0 and wx[i] >= 0:
-            assert abs(cosd(gx[i], gy[i]) - cosd(wx[i], wy[i])) < 1e-12
+    bx, by = qx.copy(), qy.copy()
+    r.ref_coordnn_translate(dp(bx), dp(by), bx.size, dp(lon), dp(lat), nx, ny)
+    assert np.array_equal(gx, bx) and np.array_equal(gy, by)
+    assert (bx == -1).any() and (bx >= 0).any()
+
+
+@pytest.mark.gpu
+def test_gpu_coord_nearestneighbor_config4_as_written():
+    from fimex_b200.coordinates import fastTranslatePointsToClosestInputCell as gpu
+    r = _ref_or_skip()
+    rng = np.random.default_rng(3)
+    nx, ny = 1354, 2030
+    lon, lat = swath(rng, nx, ny, nan_frac=0.005, wrap_column=True)
+    tlon, tlat = np.meshgrid(np.arange(-18, 2, 0.05), np.arange(53, 65, 0.05))
+    gx, gy = gpu(tlon, tlat, lon, lat)
+    bx, by = tlon.ravel().copy(), tlat.ravel().copy()
+    r.ref_coordnn_translate(dp(bx), dp(by), bx.size, dp(lon), dp(lat), nx, ny)
+    assert np.array_equal(gx.ravel(), bx) and np.array_equal(gy.ravel(), by)
+    assert (bx >= 0).mean() > 0.2 and ((bx == 0) | (bx == nx - 1)).sum() > 100
