@@ -43,6 +43,12 @@ SIGNATURES = {
     "fimexcu_cache_info": (C.c_int, [vp, c_size_p, c_size_p, c_size_p, c_size_p, c_int_p, c_size_p, c_size_p]),
     "fimexcu_cache_apply_f": (C.c_int, [vp, vp, sz, vp, c_size_p, C.c_float, C.c_float]),
     "fimexcu_cache_apply_dev_f": (C.c_int, [vp, vp, sz, vp, C.c_float, C.c_float, vp]),
+    "fimexcu_cache_apply_window_f": (C.c_int, [vp, vp, sz, sz, sz, sz, sz, vp, c_size_p, C.c_float, C.c_float]),
+    "fimexcu_cache_apply_window_dev_f": (C.c_int, [vp, vp, sz, sz, sz, sz, sz, vp, C.c_float, C.c_float, vp]),
+    "fimexcu_cache_replicate": (C.c_int, [vp, C.c_int, c_int_p]),
+    "fimexcu_vecrot_replicate": (C.c_int, [vp, C.c_int, c_int_p]),
+    "fimexcu_set_staged_kernels": (None, [C.c_int]),
+    "fimexcu_host_pool_trim": (None, []),
     "fimexcu_cache_apply_dev_strided_f": (C.c_int, [vp, vp, sz, sz, sz, vp, sz, sz, C.c_float, C.c_float, vp]),
     "fimexcu_vcoord_levels_dev_f": (C.c_int, [C.c_int, vp, vp, C.c_double, vp, sz, C.c_double, vp, C.c_int, vp, C.c_double, sz, sz, sz, vp, vp]),
     "fimexcu_vcoord_transform_dev_f": (C.c_int, [C.c_int, vp, sz, vp, vp]),

@@ -76,7 +76,7 @@ def build_host_selftest(force=False):
     exe = os.path.join(host, "host_selftest")
     deps = [os.path.join(host, f) for f in ("host_selftest.cc", "CudaCachedInterpolation.h", "CudaInterpolatorProcess2d.h", "fimex_stand_in.h")] + [LIB]
     if force or _stale(exe, deps):
-        cmd = ["g++", "-std=c++17", "-O2", "-o", exe, os.path.join(host, "host_selftest.cc"), "-L" + HERE, "-lfimexcu", "-Wl,-rpath,$ORIGIN/.."]
+        cmd = ["g++", "-std=c++17", "-O2", "-pthread", "-o", exe, os.path.join(host, "host_selftest.cc"), "-L" + HERE, "-lfimexcu", "-Wl,-rpath,$ORIGIN/.."]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("g++ failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)

@@ -22,8 +22,10 @@
 // rounded separately; the kernels use the _rn intrinsics (never contracted by nvcc) and reproduce the
 // reference's results bit for bit.
 #include "fxcu_handles.h"
+#include "fxcu_hostpar.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cstdint>
 #include <cstring>
 #include <memory>
@@ -269,6 +271,9 @@ struct ApplyParams {
     size_t outLevel; // elements between target levels
     float bad, fill;
     const int4* tile_meta; // per 32 x 8 target tile, see fimexcu_cache (staged kernels only)
+    // direct-gather kernels only: outX x outY may be a window of the target grid (getOutputDataSlice, CachedInterpolation.cc:113-130);
+    // tabX = 0 means the whole grid, else the tables' row length with the window starting at (winX0, winY0)
+    int tabX = 0, winX0 = 0, winY0 = 0;
 };
 
 template <bool BAD>
@@ -318,12 +323,19 @@ __device__ __forceinline__ void store_out(short* __restrict__ p, float v, float 
     *p = pack_i16(v, fill_bits);
 }
 
-// thread -> target cell of a 32 x 8 tile; returns false outside the grid
+// thread -> target cell of a 32 x 8 tile; returns false outside the grid (or the requested window of it)
 __device__ __forceinline__ bool tile_cell(const ApplyParams& P, int& ox, int& oy)
 {
     ox = blockIdx.x * 32 + (threadIdx.x & 31);
     oy = blockIdx.y * 8 + (threadIdx.x >> 5);
     return ox < P.outX && oy < P.outY;
+}
+// index of that cell in the cache's tables
+__device__ __forceinline__ size_t table_index(const ApplyParams& P, int ox, int oy)
+{
+    if (P.tabX == 0)
+        return static_cast<size_t>(oy) * P.outX + ox;
+    return static_cast<size_t>(oy + P.winY0) * P.tabX + (ox + P.winX0);
 }
 
 // table offset (relative to a dense inX-wide level) -> offset in the pitched source level
@@ -363,7 +375,7 @@ __global__ void __launch_bounds__(256) bilinear_apply_kernel(const ApplyParams P
     int ox, oy;
     if (!tile_cell(P, ox, oy))
         return;
-    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const size_t o = table_index(P, ox, oy);
     const int z0 = blockIdx.z * P.zchunk;
     const int z1 = min(P.nz, z0 + P.zchunk);
     const int f = P.off[o];
@@ -436,7 +448,7 @@ __global__ void __launch_bounds__(256) bicubic_apply_kernel(const ApplyParams P)
     int ox, oy;
     if (!tile_cell(P, ox, oy))
         return;
-    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const size_t o = table_index(P, ox, oy);
     const int z0 = blockIdx.z * P.zchunk;
     const int z1 = min(P.nz, z0 + P.zchunk);
     const int f = P.off[o];
@@ -462,7 +474,7 @@ __global__ void __launch_bounds__(256) nearest_apply_kernel(const ApplyParams P)
     int ox, oy;
     if (!tile_cell(P, ox, oy))
         return;
-    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const size_t o = table_index(P, ox, oy);
     const int z0 = blockIdx.z * P.zchunk;
     const int z1 = min(P.nz, z0 + P.zchunk);
     const int f = P.off[o];
@@ -931,7 +943,7 @@ __global__ void __launch_bounds__(256) bilinear_uv_kernel(const ApplyParams P, c
     int ox, oy;
     if (!tile_cell(P, ox, oy))
         return;
-    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const size_t o = table_index(P, ox, oy);
     const int z0 = blockIdx.z * P.zchunk;
     const int z1 = min(P.nz, z0 + P.zchunk);
     const int f = P.off[o];
@@ -983,7 +995,7 @@ __global__ void __launch_bounds__(256) sampled_uv_kernel(const ApplyParams P, co
     int ox, oy;
     if (!tile_cell(P, ox, oy))
         return;
-    const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+    const size_t o = table_index(P, ox, oy);
     const int z0 = blockIdx.z * P.zchunk;
     const int z1 = min(P.nz, z0 + P.zchunk);
     const int f = P.off[o];
@@ -1286,6 +1298,16 @@ static bool make_source_map(CUtensorMap* m, const float* d_in, size_t inX, size_
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// A/B switch between the staged (TMA) and the direct-gather kernels: the environment variable
+// FIMEXCU_NO_TMA is read once per process; fimexcu_set_staged_kernels() overrides it at run time
+static std::atomic<int> g_tma_override{-1};
+static bool tma_allowed()
+{
+    static const bool env = getenv("FIMEXCU_NO_TMA") == nullptr;
+    const int o = g_tma_override.load(std::memory_order_relaxed);
+    return o < 0 ? env : o != 0;
+}
+
 struct Layout {
     int inPitch;
     size_t inLevel;
@@ -1297,8 +1319,8 @@ template <bool BAD, bool FILL>
 static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cudaStream_t s, bool allow_tma)
 {
     ApplyParams P = P0;
-    const size_t tiles = static_cast<size_t>((c->outX + 31) / 32) * ((c->outY + 7) / 8);
-    if ((c->kind == KIND_BILINEAR || c->kind == KIND_NN) && allow_tma) {
+    const size_t tiles = static_cast<size_t>((P.outX + 31) / 32) * ((P.outY + 7) / 8);
+    if ((c->kind == KIND_BILINEAR || c->kind == KIND_NN) && allow_tma && P.tabX == 0) {
         // staged kernel: worth it when most tiles fit its box and there are enough tiles to fill the GPU without
         // splitting the level loop
         CUtensorMap map;
@@ -1320,7 +1342,7 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
         }
     }
     P.zchunk = pick_zchunk(tiles, P.nz);
-    const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + 7) / 8),
+    const dim3 grid(static_cast<unsigned>((P.outX + 31) / 32), static_cast<unsigned>((P.outY + 7) / 8),
                     static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
     switch (c->kind) {
     case KIND_BILINEAR: bilinear_apply_kernel<BAD, FILL><<<grid, 256, 0, s>>>(P); break;
@@ -1343,13 +1365,19 @@ static int check_layout(const fimexcu_cache* c, const Layout& L, size_t nz)
     return FIMEXCU_OK;
 }
 
-int cache_apply_strided(const fimexcu_cache* c, const float* d_in, const Layout& L, size_t nz, float* d_out, float bad, float fill, cudaStream_t s)
+// a window of the target grid (getOutputDataSlice, CachedInterpolation.cc:113-130); xSize == 0: the whole grid
+struct Window {
+    size_t xStart = 0, xSize = 0, yStart = 0, ySize = 0;
+};
+
+int cache_apply_strided(const fimexcu_cache* c, const float* d_in, const Layout& L, size_t nz, float* d_out, float bad, float fill, cudaStream_t s,
+                        const Window& w = Window())
 {
     if (!c)
         FXCU_FAIL("fimexcu_cache_apply: null cache");
     if (nz == 0 || c->outX * c->outY == 0)
         return FIMEXCU_OK;
-    if (check_layout(c, L, nz) != FIMEXCU_OK)
+    if (w.xSize == 0 && check_layout(c, L, nz) != FIMEXCU_OK)
         return FIMEXCU_ERROR;
     ApplyParams P;
     P.off = c->off.as<int>();
@@ -1369,8 +1397,15 @@ int cache_apply_strided(const fimexcu_cache* c, const float* d_in, const Layout&
     P.outLevel = L.outLevel;
     P.bad = bad;
     P.fill = fill;
+    if (w.xSize != 0) {
+        P.tabX = static_cast<int>(c->outX);
+        P.winX0 = static_cast<int>(w.xStart);
+        P.winY0 = static_cast<int>(w.yStart);
+        P.outX = static_cast<int>(w.xSize);
+        P.outY = static_cast<int>(w.ySize);
+    }
     const bool has_bad = !std::isnan(bad), has_fill = !std::isnan(fill);
-    const bool allow_tma = getenv("FIMEXCU_NO_TMA") == nullptr;
+    const bool allow_tma = tma_allowed();
     if (has_bad && has_fill)
         launch_cache_apply<true, true>(c, P, s, allow_tma);
     else if (has_bad)
@@ -1436,14 +1471,62 @@ static Layout padded_layout(const fimexcu_cache* c)
     return Layout{ip, static_cast<size_t>(ip) * c->inY, op, static_cast<size_t>(op) * c->outY};
 }
 
-// host slab -> host slab through the device; T = float or short, `apply` = the strided device apply for that element type
+// streams of the host-pointer entry points: kept per host thread AND per device (a thread of the reference's OpenMP writer
+// loop may serve different devices over its life), created on first use, never destroyed (the context may be gone at thread exit)
+constexpr int NS_MAX = 8;
+struct ThreadStreams {
+    bool ready = false;
+    cudaStream_t st[NS_MAX] = {};
+    cudaEvent_t h2d[NS_MAX] = {}; // "the host-to-device copy of this stream's current chunk is done"
+};
+static ThreadStreams* thread_streams(int device)
+{
+    thread_local ThreadStreams pools[64];
+    if (device < 0 || device >= 64) {
+        set_error("device ordinal out of range");
+        return nullptr;
+    }
+    ThreadStreams& p = pools[device];
+    if (!p.ready) {
+        cudaStream_t made[NS_MAX] = {};
+        for (int i = 0; i < NS_MAX; ++i)
+            if (!cuda_ok(cudaStreamCreateWithFlags(&made[i], cudaStreamNonBlocking), "cudaStreamCreateWithFlags", __FILE__, __LINE__)) {
+                for (int k = 0; k < i; ++k)
+                    cudaStreamDestroy(made[k]);
+                return nullptr;
+            }
+        for (int i = 0; i < NS_MAX; ++i) {
+            p.st[i] = made[i];
+            if (!cuda_ok(cudaEventCreateWithFlags(&p.h2d[i], cudaEventDisableTiming), "cudaEventCreateWithFlags", __FILE__, __LINE__))
+                return nullptr;
+        }
+        p.ready = true;
+    }
+    return &p;
+}
+
+static int e2e_streams()
+{
+    static const int v = []() { const char* e = getenv("FIMEXCU_E2E_STREAMS"); const int n = e ? atoi(e) : 3; return std::max(1, std::min(NS_MAX, n)); }();
+    return v;
+}
+static int e2e_chunks()
+{
+    static const int v = []() { const char* e = getenv("FIMEXCU_E2E_CHUNKS"); const int n = e ? atoi(e) : 8; return std::max(1, n); }();
+    return v;
+}
+
+// pageable <-> pinned copies of one level chunk on the host cores (a single memcpy thread runs at a fraction of PCIe speed)
+static void host_copy(void* dst, const void* src, size_t bytes)
+{
+    parallel_ranges(bytes, size_t(4) << 20, [&](size_t a, size_t b) { std::memcpy(static_cast<char*>(dst) + a, static_cast<const char*>(src) + a, b - a); });
+}
+
+// host slab -> host slab through the device; T = float or short, `apply` = the strided device apply for that element type.
+// c is the table set on the CURRENT device.
 template <class T, class ApplyFn>
 static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T* out, size_t* newSize, ApplyFn apply)
 {
-    if (!c)
-        FXCU_FAIL("fimexcu_cache_apply_f: null cache");
-    if (!require_device())
-        return FIMEXCU_ERROR;
     const size_t inLayer = c->inX * c->inY, outLayer = c->outX * c->outY;
     const size_t nz = size / inLayer; // CachedInterpolation.cc:176
     if (newSize)
@@ -1455,54 +1538,85 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
     // PCIe copies (the 767 MB result alone takes ~14 ms, the kernels 0.4 ms), so the chunks keep the dense host layout on
     // the device: plain 1-D copies run at full DMA speed, strided 2-D copies into the padded layout measured 1.5x slower.
     const Layout L = dense_layout(c);
-    constexpr int NS_MAX = 8;
-    static const int NS = []() { const char* e = getenv("FIMEXCU_E2E_STREAMS"); const int v = e ? atoi(e) : 3; return std::max(1, std::min(8, v)); }();
-    static const int NCHUNK = []() { const char* e = getenv("FIMEXCU_E2E_CHUNKS"); const int v = e ? atoi(e) : 8; return std::max(1, v); }();
-    // small slabs are latency-bound: one chunk per 16 MB of traffic (at most NCHUNK), and the streams are kept per host thread
-    // and device instead of being created for every call
+    const int NS = e2e_streams();
+    // small slabs are latency-bound: one chunk per 16 MB of traffic (at most FIMEXCU_E2E_CHUNKS)
     const size_t traffic = nz * (inLayer + outLayer) * sizeof(T);
-    const size_t nchunk = std::max<size_t>(1, std::min<size_t>(static_cast<size_t>(NCHUNK), traffic / (16u << 20)));
+    const size_t nchunk = std::max<size_t>(1, std::min<size_t>(static_cast<size_t>(e2e_chunks()), traffic / (16u << 20)));
     const size_t chunk = std::max<size_t>(1, std::min<size_t>(nz, (nz + nchunk - 1) / nchunk));
-    struct ThreadStreams {
-        int device = -1;
-        cudaStream_t st[NS_MAX] = {};
+    ThreadStreams* ts = thread_streams(c->device);
+    if (!ts)
+        return FIMEXCU_ERROR;
+    cudaStream_t* st = ts->st;
+    // The reference hands ordinary `new float[]` memory (include/fimex/SharedArray.h:42-48).  The DMA engines cannot read or
+    // write pageable memory: such a slab goes through pinned bounce buffers from the library's pool, one per stream, filled /
+    // drained by the host cores while the neighbouring chunk is on the bus.
+    const bool bounce_in = is_pageable_host(in), bounce_out = is_pageable_host(out);
+    struct Pinned {
+        void* p = nullptr;
+        ~Pinned() { host_pool_free(p); }
     };
-    thread_local ThreadStreams pool; // never destroyed: the context may be gone when a thread exits
-    if (pool.device != c->device) {
-        for (int i = 0; i < NS_MAX; ++i)
-            FXCU_CUDA(cudaStreamCreateWithFlags(&pool.st[i], cudaStreamNonBlocking));
-        pool.device = c->device;
-    }
-    cudaStream_t* st = pool.st;
+    Pinned hin[NS_MAX], hout[NS_MAX];
+    struct Pending { // a chunk whose result still sits in hout[i]
+        bool live = false;
+        size_t z0 = 0, zn = 0;
+    } pend[NS_MAX];
     int rc = FIMEXCU_OK;
     {
         DevBuf din[NS_MAX], dout[NS_MAX];
-        for (int i = 0; i < NS && rc == FIMEXCU_OK; ++i)
+        for (int i = 0; i < NS && rc == FIMEXCU_OK; ++i) {
             if (!din[i].alloc(chunk * L.inLevel * sizeof(T), st[i]) || !dout[i].alloc(chunk * L.outLevel * sizeof(T), st[i]))
                 rc = FIMEXCU_ERROR;
+            if (rc == FIMEXCU_OK && bounce_in && !(hin[i].p = host_pool_alloc(chunk * inLayer * sizeof(T))))
+                rc = FIMEXCU_ERROR;
+            if (rc == FIMEXCU_OK && bounce_out && !(hout[i].p = host_pool_alloc(chunk * outLayer * sizeof(T))))
+                rc = FIMEXCU_ERROR;
+        }
+        auto drain = [&](int i) { // wait for stream i; move a finished bounced result to the caller's array
+            if (!cuda_ok(cudaStreamSynchronize(st[i]), "cudaStreamSynchronize", __FILE__, __LINE__))
+                rc = FIMEXCU_ERROR;
+            if (pend[i].live && rc == FIMEXCU_OK)
+                host_copy(out + pend[i].z0 * outLayer, hout[i].p, pend[i].zn * outLayer * sizeof(T));
+            pend[i].live = false;
+        };
         size_t k = 0;
         for (size_t z0 = 0; z0 < nz && rc == FIMEXCU_OK; z0 += chunk, ++k) {
             const size_t zn = std::min(chunk, nz - z0);
             const int i = static_cast<int>(k % NS);
-            if (!cuda_ok(cudaMemcpyAsync(din[i].p, in + z0 * inLayer, zn * inLayer * sizeof(T), cudaMemcpyHostToDevice, st[i]), "H2D", __FILE__,
-                         __LINE__)) {
+            const T* src = in + z0 * inLayer;
+            if (k >= static_cast<size_t>(NS)) { // the bounce buffers of this stream must be free again
+                if (bounce_out)
+                    drain(i);
+                else if (bounce_in && !cuda_ok(cudaEventSynchronize(ts->h2d[i]), "cudaEventSynchronize", __FILE__, __LINE__))
+                    rc = FIMEXCU_ERROR;
+                if (rc != FIMEXCU_OK)
+                    break;
+            }
+            if (bounce_in) {
+                host_copy(hin[i].p, src, zn * inLayer * sizeof(T));
+                src = static_cast<const T*>(hin[i].p);
+            }
+            if (!cuda_ok(cudaMemcpyAsync(din[i].p, src, zn * inLayer * sizeof(T), cudaMemcpyHostToDevice, st[i]), "H2D", __FILE__, __LINE__) ||
+                (bounce_in && !cuda_ok(cudaEventRecord(ts->h2d[i], st[i]), "cudaEventRecord", __FILE__, __LINE__))) {
                 rc = FIMEXCU_ERROR;
                 break;
             }
             rc = apply(din[i].template as<T>(), L, zn, dout[i].template as<T>(), st[i]);
             if (rc != FIMEXCU_OK)
                 break;
-            if (!cuda_ok(cudaMemcpyAsync(out + z0 * outLayer, dout[i].p, zn * outLayer * sizeof(T), cudaMemcpyDeviceToHost, st[i]), "D2H",
-                         __FILE__, __LINE__))
+            T* dst = bounce_out ? static_cast<T*>(hout[i].p) : out + z0 * outLayer;
+            if (!cuda_ok(cudaMemcpyAsync(dst, dout[i].p, zn * outLayer * sizeof(T), cudaMemcpyDeviceToHost, st[i]), "D2H", __FILE__, __LINE__))
                 rc = FIMEXCU_ERROR;
+            if (bounce_out) {
+                pend[i].live = true;
+                pend[i].z0 = z0;
+                pend[i].zn = zn;
+            }
         }
         for (int i = 0; i < NS; ++i)
-            if (!cuda_ok(cudaStreamSynchronize(st[i]), "cudaStreamSynchronize", __FILE__, __LINE__))
-                rc = FIMEXCU_ERROR;
+            drain(i);
     }
     return rc;
 }
-
 
 } // namespace fxcu
 
@@ -1562,6 +1676,8 @@ int fimexcu_cache_apply_dev_f(const fimexcu_cache* c, const float* d_in, size_t 
     clear_error();
     if (!c)
         FXCU_FAIL("fimexcu_cache_apply: null cache");
+    if (!(c = on_current_device(c, "fimexcu_cache_apply")))
+        return FIMEXCU_ERROR;
     return cache_apply_strided(c, d_in, dense_layout(c), nz, d_out, badIn, fillOut, as_stream(stream));
 }
 
@@ -1573,13 +1689,71 @@ int fimexcu_cache_apply_dev_strided_f(const fimexcu_cache* c, const float* d_in,
         FXCU_FAIL("fimexcu_cache_apply: null cache");
     if (in_row_pitch > 0x7fffffffull || out_row_pitch > 0x7fffffffull)
         FXCU_FAIL("fimexcu_cache_apply: row pitch out of range");
+    if (!(c = on_current_device(c, "fimexcu_cache_apply")))
+        return FIMEXCU_ERROR;
     const Layout L{static_cast<int>(in_row_pitch), in_level_stride, static_cast<int>(out_row_pitch), out_level_stride};
     return cache_apply_strided(c, d_in, L, nz, d_out, badIn, fillOut, as_stream(stream));
+}
+
+static int check_window(const fimexcu_cache* c, const Layout& L, size_t nz, size_t xStart, size_t xSize, size_t yStart, size_t ySize)
+{
+    if (xSize == 0 || ySize == 0 || xStart + xSize > c->outX || yStart + ySize > c->outY)
+        FXCU_FAIL("fimexcu_cache_apply_window: the window must be a non-empty part of the target grid");
+    const Layout full{L.inPitch, L.inLevel, static_cast<int>(c->outX), c->outX * c->outY}; // the source side is checked as usual
+    return check_layout(c, full, nz);
+}
+
+int fimexcu_cache_apply_window_dev_f(const fimexcu_cache* c, const float* d_in, size_t nz, size_t xStart, size_t xSize, size_t yStart, size_t ySize,
+                                     float* d_out, float badIn, float fillOut, void* stream)
+{
+    clear_error();
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply_window: null cache");
+    if (!(c = on_current_device(c, "fimexcu_cache_apply_window")))
+        return FIMEXCU_ERROR;
+    Layout L = dense_layout(c);
+    if (check_window(c, L, nz, xStart, xSize, yStart, ySize) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
+    L.outPitch = static_cast<int>(xSize);
+    L.outLevel = xSize * ySize;
+    return cache_apply_strided(c, d_in, L, nz, d_out, badIn, fillOut, as_stream(stream), Window{xStart, xSize, yStart, ySize});
+}
+
+int fimexcu_cache_apply_window_f(const fimexcu_cache* c, const float* in, size_t size, size_t xStart, size_t xSize, size_t yStart, size_t ySize, float* out,
+                                 size_t* newSize, float badIn, float fillOut)
+{
+    clear_error();
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply_window: null cache");
+    if (!require_device() || !(c = on_current_device(c, "fimexcu_cache_apply_window")))
+        return FIMEXCU_ERROR;
+    const size_t inLayer = c->inX * c->inY;
+    const size_t nz = size / inLayer;
+    if (newSize)
+        *newSize = nz * xSize * ySize;
+    if (check_window(c, dense_layout(c), nz, xStart, xSize, yStart, ySize) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
+    if (nz == 0)
+        return FIMEXCU_OK;
+    DevBuf din, dout;
+    const size_t ib = nz * inLayer * sizeof(float), ob = nz * xSize * ySize * sizeof(float);
+    if (!din.alloc(ib, nullptr) || !dout.alloc(ob, nullptr))
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(din.p, in, ib, cudaMemcpyHostToDevice, nullptr));
+    if (fimexcu_cache_apply_window_dev_f(c, din.as<float>(), nz, xStart, xSize, yStart, ySize, dout.as<float>(), badIn, fillOut, nullptr) != FIMEXCU_OK)
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpyAsync(out, dout.p, ob, cudaMemcpyDeviceToHost, nullptr));
+    FXCU_CUDA(cudaStreamSynchronize(nullptr));
+    return FIMEXCU_OK;
 }
 
 int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, float* out, size_t* newSize, float badIn, float fillOut)
 {
     clear_error();
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply_f: null cache");
+    if (!require_device() || !(c = on_current_device(c, "fimexcu_cache_apply_f")))
+        return FIMEXCU_ERROR;
     return cache_apply_host<float>(c, in, size, out, newSize, [&](const float* di, const Layout& L, size_t zn, float* dout, cudaStream_t st) {
         return cache_apply_strided(c, di, L, zn, dout, badIn, fillOut, st);
     });
@@ -1588,6 +1762,10 @@ int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, 
 int fimexcu_cache_apply_i16(const fimexcu_cache* c, const int16_t* in, size_t size, int16_t* out, size_t* newSize, double badValue)
 {
     clear_error();
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_apply_i16: null cache");
+    if (!require_device() || !(c = on_current_device(c, "fimexcu_cache_apply_i16")))
+        return FIMEXCU_ERROR;
     return cache_apply_host<short>(c, in, size, out, newSize, [&](const short* di, const Layout& L, size_t zn, short* dout, cudaStream_t st) {
         return cache_apply_strided_i16(c, di, L, zn, dout, badValue, st);
     });
@@ -1598,6 +1776,8 @@ int fimexcu_cache_apply_dev_i16(const fimexcu_cache* c, const int16_t* d_in, siz
     clear_error();
     if (!c)
         FXCU_FAIL("fimexcu_cache_apply_dev_i16: null cache");
+    if (!(c = on_current_device(c, "fimexcu_cache_apply_dev_i16")))
+        return FIMEXCU_ERROR;
     return cache_apply_strided_i16(c, d_in, dense_layout(c), nz, d_out, badValue, as_stream(stream));
 }
 
@@ -1606,6 +1786,8 @@ static int cache_apply_uv_strided(const fimexcu_cache* c, const fimexcu_vecrot* 
 {
     if (!c)
         FXCU_FAIL("fimexcu_cache_apply_uv: null cache");
+    if (!(c = on_current_device(c, "fimexcu_cache_apply_uv")) || (r && !(r = on_current_device(r, "fimexcu_cache_apply_uv (rotation matrix)"))))
+        return FIMEXCU_ERROR;
     const size_t nxy = c->outX * c->outY;
     if (r && r->ox * r->oy != nxy)
         FXCU_FAIL("fimexcu_cache_apply_uv: rotation matrix and cache have different target grids");
@@ -1680,7 +1862,7 @@ static int cache_apply_uv_strided(const fimexcu_cache* c, const fimexcu_vecrot* 
     CUtensorMap umap, vmap;
     const bool enough = tiles >= static_cast<size_t>(sm_count()) * 5;
     const bool fits = c->tiles_with_data > 0 && 10ull * c->tiles_fitting >= 8ull * c->tiles_with_data;
-    if (getenv("FIMEXCU_NO_TMA") == nullptr && enough && fits &&
+    if (tma_allowed() && enough && fits &&
         make_source_map(&umap, d_u_in, c->inX, c->inY, nz, L.inPitch, L.inLevel, UV_ZB) &&
         make_source_map(&vmap, d_v_in, c->inX, c->inY, nz, L.inPitch, L.inLevel, UV_ZB)) {
         UvStagedParams Q;
@@ -1765,7 +1947,7 @@ int fimexcu_cache_apply_uv_f(const fimexcu_cache* c, const fimexcu_vecrot* r, co
     clear_error();
     if (!c)
         FXCU_FAIL("fimexcu_cache_apply_uv_f: null cache");
-    if (!require_device())
+    if (!require_device() || !(c = on_current_device(c, "fimexcu_cache_apply_uv_f")))
         return FIMEXCU_ERROR;
     const size_t inLayer = c->inX * c->inY, outLayer = c->outX * c->outY;
     const size_t nz = size / inLayer;
@@ -1789,6 +1971,58 @@ int fimexcu_cache_apply_uv_f(const fimexcu_cache* c, const fimexcu_vecrot* r, co
 }
 
 void fimexcu_cache_destroy(fimexcu_cache* c) { delete c; }
+
+void fimexcu_set_staged_kernels(int mode) { g_tma_override.store(mode < 0 ? -1 : (mode ? 1 : 0), std::memory_order_relaxed); }
+
+int fimexcu_cache_replicate(fimexcu_cache* c, int n_devices, const int* device_ids)
+{
+    clear_error();
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_replicate: null cache");
+    if (n_devices < 0 || (n_devices > 0 && !device_ids))
+        FXCU_FAIL("fimexcu_cache_replicate: bad device list");
+    int before = -1;
+    FXCU_CUDA(cudaGetDevice(&before));
+    int rc = FIMEXCU_OK;
+    for (int k = 0; k < n_devices && rc == FIMEXCU_OK; ++k) {
+        const int d = device_ids[k];
+        if (d < 0 || d >= 64) {
+            set_error("fimexcu_cache_replicate: device ordinal out of range");
+            rc = FIMEXCU_ERROR;
+            break;
+        }
+        if (d == c->device || (static_cast<size_t>(d) < c->replicas.size() && c->replicas[d]))
+            continue;
+        if (!cuda_ok(cudaSetDevice(d), "cudaSetDevice", __FILE__, __LINE__) || !require_device()) {
+            rc = FIMEXCU_ERROR;
+            break;
+        }
+        std::unique_ptr<fimexcu_cache> r(new fimexcu_cache());
+        r->method = c->method;
+        r->kind = c->kind;
+        r->device = d;
+        r->inX = c->inX;
+        r->inY = c->inY;
+        r->outX = c->outX;
+        r->outY = c->outY;
+        r->reduced = c->reduced;
+        r->xMin = c->xMin;
+        r->yMin = c->yMin;
+        r->tiles_with_data = c->tiles_with_data;
+        r->tiles_fitting = c->tiles_fitting;
+        if (!replicate_buf(r->off, d, c->off, c->device, nullptr) || !replicate_buf(r->wx, d, c->wx, c->device, nullptr) ||
+            !replicate_buf(r->wy, d, c->wy, c->device, nullptr) || !replicate_buf(r->tile_meta, d, c->tile_meta, c->device, nullptr) ||
+            !cuda_ok(cudaStreamSynchronize(nullptr), "cudaStreamSynchronize", __FILE__, __LINE__)) {
+            rc = FIMEXCU_ERROR;
+            break;
+        }
+        if (c->replicas.size() <= static_cast<size_t>(d))
+            c->replicas.resize(d + 1, nullptr);
+        c->replicas[d] = r.release();
+    }
+    cudaSetDevice(before);
+    return rc;
+}
 
 static int point_values(int method, const float* infield, float* outvalues, double x, double y, int ix, int iy, int iz)
 {

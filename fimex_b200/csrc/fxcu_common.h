@@ -46,10 +46,12 @@ int sm_count();
 
 inline cudaStream_t as_stream(void* s) { return static_cast<cudaStream_t>(s); }
 
-// stream-ordered scratch allocation (cudaMallocAsync from the device's default pool, whose release
-// threshold is raised once so that repeated calls do not return memory to the OS)
+// stream-ordered scratch allocation from a pool that belongs to this library (one per device, created on first use; it keeps
+// up to FIMEXCU_DEVICE_POOL_KEEP_MB, default 2048, of freed memory for the next call -- the device's default pool and its
+// settings, which the host application may share, are left alone)
 struct DevBuf {
     void* p = nullptr;
+    size_t bytes = 0;
     cudaStream_t stream = nullptr;
     bool async = false;
     DevBuf() = default;
@@ -61,6 +63,12 @@ struct DevBuf {
     void release();
     template <typename T> T* as() const { return static_cast<T*>(p); }
 };
+
+// pinned host memory from the library's pool (fimexcu_host_alloc / fimexcu_host_free)
+void* host_pool_alloc(size_t bytes);
+void host_pool_free(void* p);
+// true when p is ordinary pageable host memory (not pinned / registered / managed / device)
+bool is_pageable_host(const void* p);
 
 // grid size for a grid-stride / one-shot kernel over n items with `threads` per block
 inline unsigned blocks_for(size_t n, unsigned threads) { return static_cast<unsigned>((n + threads - 1) / threads); }

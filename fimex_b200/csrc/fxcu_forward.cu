@@ -31,6 +31,7 @@ struct fimexcu_forward {
     size_t xMin = 0, yMin = 0;
     size_t maxPointsInIn = 0;
     size_t nvalid = 0;
+    int device = 0;        // where the tables live
     fxcu::DevBuf segStart; // int32 [nout+1]
     fxcu::DevBuf segIdx;   // int32 [nvalid]
 };
@@ -254,6 +255,7 @@ fimexcu_forward* fimexcu_forward_create(int method, const double* pOnX, const do
     }
     std::unique_ptr<fimexcu_forward> f(new fimexcu_forward());
     f->method = method;
+    FXCU_CUDA_NULL(cudaGetDevice(&f->device));
     f->undef = method >= FIMEXCU_INTERPOL_FORWARD_UNDEF_SUM;
     switch (method) {
     case FIMEXCU_INTERPOL_FORWARD_SUM: case FIMEXCU_INTERPOL_FORWARD_UNDEF_SUM: f->kind = 0; break;
@@ -360,6 +362,10 @@ int fimexcu_forward_apply_dev_f(const fimexcu_forward* f, const float* d_in, siz
     clear_error();
     if (!f)
         FXCU_FAIL("fimexcu_forward_apply: null handle");
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev != f->device) // the segment tables live in that device's memory
+        FXCU_FAIL("fimexcu_forward_apply: the handle was built on device " + std::to_string(f->device) + ", the current device is " +
+                  std::to_string(dev) + " (call fimexcu_set_device first)");
     const size_t nout = f->outX * f->outY;
     if (nz == 0 || nout == 0)
         return FIMEXCU_OK;

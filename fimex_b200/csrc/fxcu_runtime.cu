@@ -1,13 +1,137 @@
 // fxcu_runtime.cu -- error state, device selection and memory helpers of the C ABI (include/fimexcu.h, "runtime").
 #include "fxcu_common.h"
 
+#include <map>
 #include <mutex>
+#include <unordered_map>
 
 namespace fxcu {
 
 namespace {
 thread_local std::string g_last_error;
-std::once_flag g_pool_once[64];
+constexpr int MAX_DEVICES = 64;
+std::once_flag g_pool_once[MAX_DEVICES];
+cudaMemPool_t g_pool[MAX_DEVICES] = {};
+
+// the library's own stream-ordered pool on `dev` (nullptr: creation failed, callers fall back to the default pool)
+cudaMemPool_t device_pool(int dev)
+{
+    if (dev < 0 || dev >= MAX_DEVICES)
+        return nullptr;
+    std::call_once(g_pool_once[dev], [dev]() {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        cudaMemPool_t pool = nullptr;
+        if (cudaMemPoolCreate(&pool, &props) == cudaSuccess) {
+            const char* e = getenv("FIMEXCU_DEVICE_POOL_KEEP_MB");
+            unsigned long long keep = (e ? strtoull(e, nullptr, 10) : 2048ull) << 20;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            g_pool[dev] = pool;
+        }
+        cudaGetLastError();
+    });
+    return g_pool[dev];
+}
+
+// ---- pinned host pool: size classes, free lists; cudaFreeHost never runs on the hot path ----
+struct HostPool {
+    std::mutex m;
+    std::unordered_map<void*, size_t> live;  // handed out: pointer -> class size
+    std::multimap<size_t, void*> idle;       // class size -> pointer
+    size_t idle_bytes = 0;
+    size_t max_idle = []() {
+        const char* e = getenv("FIMEXCU_HOST_POOL_KEEP_MB");
+        return static_cast<size_t>(e ? strtoull(e, nullptr, 10) : 8192ull) << 20;
+    }();
+};
+HostPool& host_pool()
+{
+    static HostPool* p = new HostPool; // never destroyed: the CUDA context may be gone at static destruction time
+    return *p;
+}
+size_t host_class(size_t bytes)
+{
+    if (bytes <= (1u << 20)) {
+        size_t c = 4096;
+        while (c < bytes)
+            c <<= 1;
+        return c;
+    }
+    const size_t step = 2u << 20; // 2 MiB steps above 1 MiB: slabs of one variable land in the same class call after call
+    return (bytes + step - 1) / step * step;
+}
+} // namespace
+
+void* host_pool_alloc(size_t bytes)
+{
+    HostPool& hp = host_pool();
+    const size_t cls = host_class(bytes ? bytes : 1);
+    {
+        std::lock_guard<std::mutex> g(hp.m);
+        auto it = hp.idle.lower_bound(cls);
+        if (it != hp.idle.end() && it->first <= cls + cls / 8) {
+            void* p = it->second;
+            hp.live[p] = it->first;
+            hp.idle_bytes -= it->first;
+            hp.idle.erase(it);
+            return p;
+        }
+    }
+    void* p = nullptr;
+    // portable: one process may drive several devices from its host threads
+    if (!cuda_ok(cudaHostAlloc(&p, cls, cudaHostAllocPortable), "cudaHostAlloc", __FILE__, __LINE__))
+        return nullptr;
+    std::lock_guard<std::mutex> g(hp.m);
+    hp.live[p] = cls;
+    return p;
+}
+
+void host_pool_free(void* p)
+{
+    if (!p)
+        return;
+    HostPool& hp = host_pool();
+    size_t cls = 0;
+    {
+        std::lock_guard<std::mutex> g(hp.m);
+        auto it = hp.live.find(p);
+        if (it == hp.live.end())
+            return; // not ours (or freed twice): leave it alone
+        cls = it->second;
+        hp.live.erase(it);
+        if (hp.idle_bytes + cls <= hp.max_idle) {
+            hp.idle.emplace(cls, p);
+            hp.idle_bytes += cls;
+            return;
+        }
+    }
+    cudaFreeHost(p);
+}
+
+static void host_pool_trim()
+{
+    HostPool& hp = host_pool();
+    std::multimap<size_t, void*> drop;
+    {
+        std::lock_guard<std::mutex> g(hp.m);
+        drop.swap(hp.idle);
+        hp.idle_bytes = 0;
+    }
+    for (auto& kv : drop)
+        cudaFreeHost(kv.second);
+}
+
+bool is_pageable_host(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return true;
+    }
+    return a.type == cudaMemoryTypeUnregistered;
 }
 
 void set_error(const std::string& msg) { g_last_error = msg; }
@@ -40,16 +164,7 @@ bool require_device()
         cudaGetLastError();
         return false;
     }
-    if (dev >= 0 && dev < 64) {
-        std::call_once(g_pool_once[dev], [dev]() {
-            cudaMemPool_t pool;
-            if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-                unsigned long long keep = ~0ull;
-                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-            }
-            cudaGetLastError();
-        });
-    }
+    device_pool(dev);
     return true;
 }
 
@@ -68,6 +183,12 @@ bool DevBuf::alloc(size_t bytes, cudaStream_t s)
         bytes = 16;
     stream = s;
     async = true;
+    this->bytes = bytes;
+    int dev = -1;
+    cudaGetDevice(&dev);
+    cudaMemPool_t pool = device_pool(dev);
+    if (pool)
+        return cuda_ok(cudaMallocFromPoolAsync(&p, bytes, pool, s), "cudaMallocFromPoolAsync", __FILE__, __LINE__);
     return cuda_ok(cudaMallocAsync(&p, bytes, s), "cudaMallocAsync", __FILE__, __LINE__);
 }
 
@@ -77,6 +198,7 @@ bool DevBuf::alloc_sync(size_t bytes)
     if (bytes == 0)
         bytes = 16;
     async = false;
+    this->bytes = bytes;
     return cuda_ok(cudaMalloc(&p, bytes), "cudaMalloc", __FILE__, __LINE__);
 }
 
@@ -89,6 +211,7 @@ void DevBuf::release()
     else
         cudaFree(p);
     p = nullptr;
+    bytes = 0;
 }
 
 } // namespace fxcu
@@ -121,18 +244,14 @@ int fimexcu_set_device(int ordinal)
 
 void* fimexcu_host_alloc(size_t bytes)
 {
-    void* p = nullptr;
     if (!fxcu::require_device())
         return nullptr;
-    FXCU_CUDA_NULL(cudaMallocHost(&p, bytes ? bytes : 1));
-    return p;
+    return fxcu::host_pool_alloc(bytes);
 }
 
-void fimexcu_host_free(void* p)
-{
-    if (p)
-        cudaFreeHost(p);
-}
+void fimexcu_host_free(void* p) { fxcu::host_pool_free(p); }
+
+void fimexcu_host_pool_trim(void) { fxcu::host_pool_trim(); }
 
 void* fimexcu_dev_alloc(size_t bytes)
 {

@@ -86,6 +86,7 @@ static fimexcu_vecrot* vecrot_build(const double* d_m3, size_t ox, size_t oy, cu
     std::unique_ptr<fimexcu_vecrot> r(new fimexcu_vecrot());
     r->ox = ox;
     r->oy = oy;
+    FXCU_CUDA_NULL(cudaGetDevice(&r->device));
     const size_t n = ox * oy;
     if (!r->c.alloc_sync(n * sizeof(double)) || !r->s.alloc_sync(n * sizeof(double)) || !r->deg.alloc_sync(n * sizeof(double)))
         return nullptr;
@@ -129,6 +130,8 @@ int fimexcu_vecrot_apply_dev_f(const fimexcu_vecrot* r, float* d_u, float* d_v, 
     clear_error();
     if (!r)
         FXCU_FAIL("fimexcu_vecrot_apply: null handle");
+    if (!(r = on_current_device(r, "fimexcu_vecrot_apply")))
+        return FIMEXCU_ERROR;
     const size_t layer = r->ox * r->oy;
     if (layer == 0 || nz == 0)
         return FIMEXCU_OK;
@@ -172,6 +175,8 @@ int fimexcu_vecrot_direction_dev_f(const fimexcu_vecrot* r, float* d_angles, siz
     clear_error();
     if (!r)
         FXCU_FAIL("fimexcu_vecrot_direction: null handle");
+    if (!(r = on_current_device(r, "fimexcu_vecrot_direction")))
+        return FIMEXCU_ERROR;
     const size_t layer = r->ox * r->oy;
     if (layer == 0 || nz == 0)
         return FIMEXCU_OK;
@@ -209,5 +214,45 @@ int fimexcu_vecrot_direction_f(const fimexcu_vecrot* r, float* angles, size_t si
 }
 
 void fimexcu_vecrot_destroy(fimexcu_vecrot* r) { delete r; }
+
+int fimexcu_vecrot_replicate(fimexcu_vecrot* v, int n_devices, const int* device_ids)
+{
+    clear_error();
+    if (!v)
+        FXCU_FAIL("fimexcu_vecrot_replicate: null handle");
+    if (n_devices < 0 || (n_devices > 0 && !device_ids))
+        FXCU_FAIL("fimexcu_vecrot_replicate: bad device list");
+    int before = -1;
+    FXCU_CUDA(cudaGetDevice(&before));
+    int rc = FIMEXCU_OK;
+    for (int k = 0; k < n_devices && rc == FIMEXCU_OK; ++k) {
+        const int d = device_ids[k];
+        if (d < 0 || d >= 64) {
+            set_error("fimexcu_vecrot_replicate: device ordinal out of range");
+            rc = FIMEXCU_ERROR;
+            break;
+        }
+        if (d == v->device || (static_cast<size_t>(d) < v->replicas.size() && v->replicas[d]))
+            continue;
+        if (!cuda_ok(cudaSetDevice(d), "cudaSetDevice", __FILE__, __LINE__) || !require_device()) {
+            rc = FIMEXCU_ERROR;
+            break;
+        }
+        std::unique_ptr<fimexcu_vecrot> r(new fimexcu_vecrot());
+        r->ox = v->ox;
+        r->oy = v->oy;
+        r->device = d;
+        if (!replicate_buf(r->c, d, v->c, v->device, nullptr) || !replicate_buf(r->s, d, v->s, v->device, nullptr) ||
+            !replicate_buf(r->deg, d, v->deg, v->device, nullptr) || !cuda_ok(cudaStreamSynchronize(nullptr), "cudaStreamSynchronize", __FILE__, __LINE__)) {
+            rc = FIMEXCU_ERROR;
+            break;
+        }
+        if (v->replicas.size() <= static_cast<size_t>(d))
+            v->replicas.resize(d + 1, nullptr);
+        v->replicas[d] = r.release();
+    }
+    cudaSetDevice(before);
+    return rc;
+}
 
 } // extern "C"

@@ -8,6 +8,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 using namespace MetNoFimex;
@@ -57,10 +58,77 @@ static int fill_mode(const char* in_path, const char* out_path)
     return 0;
 }
 
+// host_selftest threads N case.bin result.bin -- the writer's loop in miniature (src/io/netcdf/NetCDF_CDMWriter.cc:599-618):
+// ONE cache object, N host threads pulling different slabs through interpolateValues at the same time (each thread gets its GPU
+// from cuda_glue::bind_thread(); with one GPU they share it).  Case file as below with nz = levels per slab and u holding
+// nslabs = (file size) slabs back to back: int32 method,inX,inY,outX,outY,nz,nslabs; f64 px,py; f32 slabs[nslabs][nz*in].
+// result: all regridded slabs in order, then int32 device ordinal used for each slab.
+static int threads_mode(int nthreads, const char* in_path, const char* out_path)
+{
+    FILE* f = fopen(in_path, "rb");
+    if (!f)
+        return 2;
+    int32_t hdr[7];
+    if (!read_all(f, hdr, sizeof(hdr)))
+        return 2;
+    const int method = hdr[0];
+    const size_t inX = hdr[1], inY = hdr[2], outX = hdr[3], outY = hdr[4], nz = hdr[5], nslabs = hdr[6];
+    const size_t nout = outX * outY, nin = inX * inY;
+    auto px = make_shared_array<double>(nout), py = make_shared_array<double>(nout);
+    if (!read_all(f, px.get(), nout * 8) || !read_all(f, py.get(), nout * 8))
+        return 2;
+    std::vector<shared_array<float>> slabs(nslabs), results(nslabs);
+    for (size_t k = 0; k < nslabs; ++k) {
+        slabs[k] = make_shared_array<float>(nz * nin); // pageable, like the upstream reader's arrays
+        if (!read_all(f, slabs[k].get(), nz * nin * 4))
+            return 2;
+    }
+    fclose(f);
+    std::vector<int32_t> device_of(nslabs, -1);
+    std::vector<std::string> errors(nthreads);
+    try {
+        CachedInterpolationInterface_p ci = createCudaCachedInterpolation("x", "y", method, px, py, inX, inY, outX, outY);
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nthreads; ++t)
+            pool.emplace_back([&, t]() {
+                try {
+                    for (size_t k = t; k < nslabs; k += nthreads) { // static schedule, like the reference's omp for
+                        size_t newSize = 0;
+                        results[k] = ci->interpolateValues(slabs[k], nz * nin, newSize);
+                        device_of[k] = cuda_glue::bind_thread();
+                        if (newSize != nz * nout)
+                            errors[t] = "wrong newSize";
+                    }
+                } catch (const std::exception& e) {
+                    errors[t] = e.what();
+                }
+            });
+        for (auto& th : pool)
+            th.join();
+    } catch (const std::exception& e) {
+        fprintf(stderr, "exception: %s\n", e.what());
+        return 6;
+    }
+    for (const std::string& e : errors)
+        if (!e.empty()) {
+            fprintf(stderr, "thread error: %s\n", e.c_str());
+            return 7;
+        }
+    FILE* o = fopen(out_path, "wb");
+    for (size_t k = 0; k < nslabs; ++k)
+        fwrite(results[k].get(), 4, nz * nout, o);
+    fwrite(device_of.data(), 4, nslabs, o);
+    fclose(o);
+    printf("host_selftest threads ok (%zu devices)\n", cuda_glue::devices().size());
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
     if (argc == 4 && std::strcmp(argv[1], "fill") == 0)
         return fill_mode(argv[2], argv[3]);
+    if (argc == 5 && std::strcmp(argv[1], "threads") == 0)
+        return threads_mode(std::atoi(argv[2]), argv[3], argv[4]);
     if (argc != 3) {
         fprintf(stderr, "usage: host_selftest case.bin result.bin\n");
         return 2;

@@ -113,6 +113,36 @@ class CachedInterpolationInterface:
         self._apply_host(a.ctypes.data, size, out.ctypes.data, newSize, badValue, fillValue)
         return out, newSize.value
 
+    def interpolateValuesWindow(self, inData, xStart, xSize, yStart, ySize, badValue=_NAN, fillValue=_NAN):
+        """interpolateValues + getOutputDataSlice (src/CachedInterpolation.cc:113-130) for a caller that wants only the cells
+        [yStart, yStart+ySize) x [xStart, xStart+xSize) of the target grid: only those are computed and copied back.
+        Returns [nz][ySize][xSize] (numpy in -> numpy out, CUDA tensor in -> CUDA tensor out)."""
+        if self._h is None:
+            raise FimexCudaError("cache was destroyed")
+        if _is_torch(inData):
+            import torch
+            if not inData.is_cuda or inData.dtype != torch.float32 or not inData.is_contiguous():
+                raise FimexCudaError("device path needs a contiguous float32 CUDA tensor")
+            nz = inData.numel() // (self.inX * self.inY)
+            out = torch.empty((nz, ySize, xSize), dtype=torch.float32, device=inData.device)
+            _lib.check(lib.fimexcu_cache_apply_window_dev_f(self._h, inData.data_ptr(), nz, xStart, xSize, yStart, ySize, out.data_ptr(), badValue, fillValue,
+                                                            _lib.current_stream_ptr()), "interpolateValuesWindow")
+            return out
+        a = np.ascontiguousarray(inData, dtype=np.float32)
+        nz = a.size // (self.inX * self.inY)
+        out = np.empty((nz, ySize, xSize), dtype=np.float32)
+        newSize = C.c_size_t()
+        _lib.check(lib.fimexcu_cache_apply_window_f(self._h, a.ctypes.data, a.size, xStart, xSize, yStart, ySize, out.ctypes.data, C.byref(newSize),
+                                                    badValue, fillValue), "interpolateValuesWindow")
+        assert newSize.value == out.size
+        return out
+
+    def replicate(self, devices):
+        """copy the tables to the listed device ordinals: host threads bound to different GPUs then share this one object, as the
+        reference's OpenMP writer threads share one CachedInterpolation (src/io/netcdf/NetCDF_CDMWriter.cc:599-618)"""
+        ids = (C.c_int * len(devices))(*devices)
+        _lib.check(lib.fimexcu_cache_replicate(self._h, len(devices), ids), "replicate")
+
     def interpolateValuesPacked(self, inData, badValue):
         """CDMInterpolator::getDataSlice for a CDM_SHORT variable around the cached interpolation (CDMInterpolator.cc:140-151):
         inData [nz][inY][inX] int16 RAW packed values, badValue = the variable's _FillValue; returns int16 [nz][outY][outX].
@@ -292,6 +322,11 @@ class CachedVectorReprojection:
         assert uValues.dtype == np.float32 and vValues.dtype == np.float32 and uValues.flags.c_contiguous and vValues.flags.c_contiguous
         size = uValues.size if size is None else size
         _lib.check(lib.fimexcu_vecrot_apply_f(self._h, uValues.ctypes.data, vValues.ctypes.data, size), "reprojectValues")
+
+    def replicate(self, devices):
+        """the matrix on every listed device (see CachedInterpolationInterface.replicate)"""
+        ids = (C.c_int * len(devices))(*devices)
+        _lib.check(lib.fimexcu_vecrot_replicate(self._h, len(devices), ids), "replicate")
 
     def reprojectDirectionValues(self, angles, size=None):
         """src/CachedVectorReprojection.cc:50-54"""

@@ -73,9 +73,15 @@ int fimexcu_device_count(void);
 /* make device `ordinal` current for the calling thread (one process or thread per GPU). */
 int fimexcu_set_device(int ordinal);
 /* pinned host memory for slabs (so the host<->device copies of the *_f entry points run at full PCIe
- * speed); plays the part of make_shared_array<float>() in include/fimex/SharedArray.h:42-48. */
+ * speed); plays the part of make_shared_array<float>() in include/fimex/SharedArray.h:42-48.  The reference allocates a fresh
+ * result array in every interpolateValues() (src/CachedInterpolation.cc:177); pinning 767 MB per call would cost more than
+ * the regridding, so the memory comes from a pool: fimexcu_host_free() parks the block in a size-class free list (up to
+ * FIMEXCU_HOST_POOL_KEEP_MB, default 8192, stay parked) and the next fimexcu_host_alloc() of that class takes it back without
+ * a driver call.  Blocks are portable (usable with every device of the process).  Thread safe. */
 void* fimexcu_host_alloc(size_t bytes);
 void fimexcu_host_free(void* p);
+/* give the parked blocks back to the operating system */
+void fimexcu_host_pool_trim(void);
 /* plain device memory for callers that keep slabs resident between chained operators */
 void* fimexcu_dev_alloc(size_t bytes);
 void fimexcu_dev_free(void* p);
@@ -109,6 +115,16 @@ int fimexcu_cache_info(const fimexcu_cache* c, size_t* inX, size_t* inY, size_t*
  *   badIn   values equal to it are read as NaN (pass NaN for "none")
  *   fillOut NaN results are written as this value (pass NaN to keep NaN) */
 int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, float* out, size_t* newSize, float badIn, float fillOut);
+/* `in` / `out` of the host entry points may be ordinary pageable memory (the reference hands `new float[]` arrays,
+ * include/fimex/SharedArray.h:42-48): such a slab is moved through pinned bounce buffers of the pool above by the host cores,
+ * chunk by chunk, overlapped with the DMA of the neighbouring chunk.  Pinned memory (fimexcu_host_alloc) skips that step. */
+/* interpolateValues() followed by getOutputDataSlice() (src/CachedInterpolation.cc:113-130) for callers that asked for a
+ * sub-window of the target grid (cross-sections, point lists, tiled writers): only the cells [yStart, yStart+ySize) x
+ * [xStart, xStart+xSize) are computed and copied back; out is [nz][ySize][xSize], *newSize = nz*xSize*ySize. */
+int fimexcu_cache_apply_window_f(const fimexcu_cache* c, const float* in, size_t size, size_t xStart, size_t xSize, size_t yStart, size_t ySize,
+                                 float* out, size_t* newSize, float badIn, float fillOut);
+int fimexcu_cache_apply_window_dev_f(const fimexcu_cache* c, const float* d_in, size_t nz, size_t xStart, size_t xSize, size_t yStart, size_t ySize,
+                                     float* d_out, float badIn, float fillOut, void* stream);
 /* same on DEVICE-resident slabs in the reference's dense layout; enqueues on `stream` */
 int fimexcu_cache_apply_dev_f(const fimexcu_cache* c, const float* d_in, size_t nz, float* d_out, float badIn, float fillOut, void* stream);
 /* same on DEVICE-resident slabs with explicit element strides: element (z, y, x) of the source lives at
@@ -116,7 +132,9 @@ int fimexcu_cache_apply_dev_f(const fimexcu_cache* c, const float* d_in, size_t 
  * Any strides >= the grid sizes are accepted.  The fast (TMA-staged) bilinear kernel needs d_in on a 16 B boundary and
  * in_row_pitch, in_level_stride multiples of 4; target rows on 128 B boundaries make every warp store one full line.
  * fimexcu_cache_padded_layout() returns strides that satisfy both (what slabs that stay on the device between chained
- * operators should use; the host entry points stage through this layout internally). */
+ * operators should use).  The host entry points (*_f, *_i16) do NOT go through this layout: they are bound by the PCIe copies,
+ * plain 1-D copies of the dense host layout run at full DMA speed and strided copies into padded rows do not, so their level
+ * chunks keep the dense layout on the device. */
 int fimexcu_cache_apply_dev_strided_f(const fimexcu_cache* c, const float* d_in, size_t in_row_pitch, size_t in_level_stride, size_t nz,
                                       float* d_out, size_t out_row_pitch, size_t out_level_stride, float badIn, float fillOut, void* stream);
 int fimexcu_cache_padded_layout(const fimexcu_cache* c, size_t* in_row_pitch, size_t* in_level_stride, size_t* out_row_pitch,
@@ -133,6 +151,18 @@ int fimexcu_cache_padded_layout(const fimexcu_cache* c, size_t* in_row_pitch, si
 int fimexcu_cache_apply_i16(const fimexcu_cache* c, const int16_t* in, size_t size, int16_t* out, size_t* newSize, double badValue);
 int fimexcu_cache_apply_dev_i16(const fimexcu_cache* c, const int16_t* d_in, size_t nz, int16_t* d_out, double badValue, void* stream);
 void fimexcu_cache_destroy(fimexcu_cache* c);
+/* One cache for all GPUs of the process.  The reference is ONE process whose writer threads call getDataSlice concurrently
+ * (#pragma omp parallel for over the unlimited dimension, src/io/netcdf/NetCDF_CDMWriter.cc:599-618), all through the same
+ * CachedInterpolation object.  fimexcu_cache_replicate() copies the handle's tables (and tile metadata) from the device they
+ * were built on to every listed device (device-to-device copies; about 35 MB for the 2.95 M-cell bilinear T1 tables); from then on
+ * every apply entry point uses the copy that lives on the CALLING THREAD's current device (fimexcu_set_device), so host threads
+ * bound to different GPUs share one handle.  Devices already covered are skipped; the copies die with the handle.  Not thread
+ * safe against concurrent applies on the same handle: replicate once, right after the cache is built. */
+int fimexcu_cache_replicate(fimexcu_cache* c, int n_devices, const int* device_ids);
+/* A/B switch between the staged (TMA) and the direct-gather apply kernels, for measurements and tests: 1 = staged kernels where they
+ * apply (default), 0 = direct kernels only, -1 = back to the default (which the environment variable FIMEXCU_NO_TMA, read once per
+ * process, can set to 0).  No counterpart in the reference. */
+void fimexcu_set_staged_kernels(int mode);
 
 /* Slab feed / sink for packed integer variables as stand-alone device passes, so that packed slabs cross
  * PCIe in their file type and any operator of the path can be chained on the device in f32:
@@ -178,6 +208,8 @@ int fimexcu_vecrot_apply_dev_f(const fimexcu_vecrot* r, float* d_u, float* d_v, 
 int fimexcu_vecrot_direction_f(const fimexcu_vecrot* r, float* angles, size_t size);
 int fimexcu_vecrot_direction_dev_f(const fimexcu_vecrot* r, float* d_angles, size_t nz, void* stream);
 void fimexcu_vecrot_destroy(fimexcu_vecrot* r);
+/* the rotation matrix on every listed device, like fimexcu_cache_replicate (CachedVectorReprojection is shared by the writer threads too) */
+int fimexcu_vecrot_replicate(fimexcu_vecrot* r, int n_devices, const int* device_ids);
 /* The vector branch of CDMInterpolator::getDataSlice (src/CDMInterpolator.cc:232-259) as ONE pass:
  * interpolate u and v with the same cache and rotate them, instead of the reference's two
  * interpolateValues() calls per component plus reprojectValues().  r may be NULL (no rotation). */

@@ -203,7 +203,7 @@ def test_gpu_kdtree_corrected_mode(oracle):
     gx, gy = gpu(15000.0, qx, qy, lon, lat, nanoflann_compat=False)
     wx, wy, gap = qx.copy(), qy.copy(), np.empty(qx.size)
     oracle.orc_kdtree_translate(15000.0, dp(wx), dp(wy), wx.size, dp(lon), dp(lat), nx, ny, dp(gap))
-    clear = np.abs(gap) > 1e-12 * (15000.0 / 6371000.0) ** 2 + 1e-28  # this mode uses the device's sin/cos
+    clear = ~(np.abs(gap) <= 1e-12 * (15000.0 / 6371000.0) ** 2 + 1e-28)  # this mode uses the device's sin/cos; misses have no gap
     assert np.array_equal(gx[clear], wx[clear]) and np.array_equal(gy[clear], wy[clear])
     assert clear.mean() > 0.999 and (wx >= 0).sum() > 1000
 

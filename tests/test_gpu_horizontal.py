@@ -278,17 +278,49 @@ def test_bilinear_staged_kernel_padded_layout(fx, oracle, shape, special):
     assert _eq(dense.cpu().numpy(), want)
 
 
-def test_staged_and_direct_kernels_agree_on_meps(fx, meps_t1, monkeypatch):
+def test_staged_and_direct_kernels_agree_on_meps(fx, meps_t1):
     import torch
     S, px, py, ox, oy, ci = meps_t1
     fld = S.meps_slab_torch(t=5, device="cuda", nz=13)
     pin = ci.toPadded(ci.reduceInput(fld, S.MEPS_NX, S.MEPS_NY))
     a = ci.interpolateValuesPadded(pin)
     torch.cuda.synchronize()
-    monkeypatch.setenv("FIMEXCU_NO_TMA", "1")
-    b = ci.interpolateValuesPadded(pin)
-    torch.cuda.synchronize()
+    fx.lib.fimexcu_set_staged_kernels(0)  # direct-gather kernels only
+    try:
+        b = ci.interpolateValuesPadded(pin)
+        torch.cuda.synchronize()
+    finally:
+        fx.lib.fimexcu_set_staged_kernels(-1)
     assert _eq(a[:, :, :ox].cpu().numpy(), b[:, :, :ox].cpu().numpy())
+
+
+@pytest.mark.parametrize("method", [ol.BILINEAR, ol.BICUBIC, ol.NEAREST])
+def test_output_window_equals_slice_of_full_result(fx, method):
+    """getOutputDataSlice (CachedInterpolation.cc:113-130): sliceOutput() of the full result and the windowed apply (which computes
+    and copies only the window) give the same cells as the oracle's full result cut the same way -- host and device forms"""
+    import torch
+    rng = np.random.default_rng(300 + method)
+    in_x, in_y, out_x, out_y, nz = 90, 70, 233, 151, 5
+    px, py = _tables(rng, in_x, in_y, out_x * out_y)
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.03] = np.nan
+    want, _ = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, fld)
+    ci = fx.createCachedInterpolation("x", "y", method, px, py, in_x, in_y, out_x, out_y)
+    sub = ci.reduceInput(fld, in_x, in_y)
+    full, _ = ci.interpolateValues(sub)
+    for (x0, xs, y0, ys) in [(0, out_x, 0, out_y), (17, 64, 9, 40), (200, 33, 150, 1), (5, 1, 0, out_y), (232, 1, 150, 1)]:
+        w = want[:, y0:y0 + ys, x0:x0 + xs]
+        assert _eq(ci.sliceOutput(full, x0, xs, y0, ys), w)
+        assert _eq(ci.interpolateValuesWindow(sub, x0, xs, y0, ys), w)
+        d = ci.interpolateValuesWindow(torch.from_numpy(sub).cuda(), x0, xs, y0, ys, fillValue=-7.0)
+        torch.cuda.synchronize()
+        wf = w.copy()
+        wf[np.isnan(wf)] = -7.0
+        assert _eq(d.cpu().numpy(), wf)
+    with pytest.raises(fx.FimexCudaError):
+        ci.interpolateValuesWindow(sub, 200, 64, 0, 10)   # reaches beyond the grid
+    with pytest.raises(fx.FimexCudaError):
+        ci.sliceOutput(full, 0, out_x + 1, 0, 1)
 
 
 def test_nearest_staged_kernel_padded_layout(fx, oracle):

@@ -55,6 +55,41 @@ def test_cpp_glue_matches_oracle(tmp_path, method):
         assert np.array_equal(np.isnan(g), np.isnan(w)) and np.array_equal(g[~np.isnan(g)], w[~np.isnan(w)])
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("method", [ol.BILINEAR, ol.NEAREST])
+def test_cpp_glue_one_cache_many_writer_threads(tmp_path, method):
+    """The reference's process model (src/io/netcdf/NetCDF_CDMWriter.cc:599-618): ONE cache object, several host threads
+    calling interpolateValues concurrently with different (pageable) slabs.  Each thread is bound to a GPU round robin over all
+    devices of the box (tables replicated by fimexcu_cache_replicate); with a single GPU the threads share it.  Every slab must
+    equal the oracle, whichever device regridded it."""
+    import fimex_b200
+    rng = np.random.default_rng(40 + method)
+    in_x, in_y, out_x, out_y, nz, nslabs, nthreads = 120, 90, 331, 207, 6, 11, 5
+    px = rng.uniform(-2, in_x + 1, out_x * out_y)
+    py = rng.uniform(-2, in_y + 1, out_x * out_y)
+    px[:4], py[:4] = [0.2, in_x - 1.2, 0.2, in_x - 1.2], [0.2, 0.2, in_y - 1.2, in_y - 1.2]
+    strip = (py >= in_y - 0.5) & (py < in_y + 0.5) & ~((np.floor(px) >= 0) & (np.floor(px) + 1 < in_x))
+    py[strip] += 1.0
+    slabs = rng.normal(size=(nslabs, nz, in_y, in_x)).astype(np.float32)
+    slabs[rng.random(slabs.shape) < 0.02] = np.nan
+    case, res = tmp_path / "case.bin", tmp_path / "res.bin"
+    with open(case, "wb") as f:
+        f.write(np.array([method, in_x, in_y, out_x, out_y, nz, nslabs], dtype=np.int32).tobytes())
+        for a in (px, py, slabs):
+            f.write(np.ascontiguousarray(a).tobytes())
+    r = subprocess.run([EXE, "threads", str(nthreads), str(case), str(res)], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    raw = np.fromfile(res, dtype=np.float32)
+    n = nslabs * nz * out_y * out_x
+    got = raw[:n].reshape(nslabs, nz, out_y, out_x)
+    dev = raw[n:].view(np.int32)
+    for k in range(nslabs):
+        w, _ = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, slabs[k])
+        assert np.array_equal(np.isnan(got[k]), np.isnan(w)) and np.array_equal(got[k][~np.isnan(w)], w[~np.isnan(w)]), k
+    ndev = fimex_b200.lib.fimexcu_device_count()
+    assert len(set(dev.tolist())) == min(ndev, nthreads)  # every GPU of the box (up to the thread count) took part
+
+
 def test_process_glue_compiles_against_the_reference_headers():
     inc = "/root/reference/include"
     if not os.path.isdir(inc):

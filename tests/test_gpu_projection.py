@@ -51,7 +51,7 @@ def _oracle_transform(src, dst, x, y):
 
 @pytest.mark.parametrize("name", sorted(PROJS))
 def test_lonlat_to_projection_and_back(rp, name):
-    rng = np.random.default_rng(abs(hash(name)) % 1000)
+    rng = np.random.default_rng(1000 + sorted(PROJS).index(name))  # fixed per projection (hash() varies with PYTHONHASHSEED)
     lon = rng.uniform(-20, 50, 20000)
     lat = rng.uniform(45, 85, 20000)
     lon[:5] = [15, 15, 0, 179.9, -179.9]
@@ -85,6 +85,14 @@ def test_known_coordinates(rp):
     import fimex_b200
     with pytest.raises(fimex_b200.FimexCudaError, match="Proj error"):
         rp.reproject_values("+proj=fork +lat_1000=123", LL, [0.0], [0.0])
+    # parameters whose effect is not implemented (datum shift, grid shift, prime meridian, axis order, unknown keys) are errors,
+    # never silently dropped; their identity forms are accepted
+    for bad in ("+proj=longlat +ellps=bessel +towgs84=565.4,50.3,465.6", "+proj=longlat +ellps=clrk66 +nadgrids=conus", "+proj=longlat +a=6371000 +pm=paris",
+                "+proj=longlat +R=6371000 +axis=neu", "+proj=longlat +datum=potsdam", "+proj=stere +lat_0=90 +R=6371000 +lon_wrap=180"):
+        with pytest.raises(fimex_b200.FimexCudaError, match="unsupported"):
+            rp.reproject_values(bad, LL, [10.0], [60.0])
+    lon, lat = rp.reproject_values("+proj=longlat +R=6371000 +towgs84=0,0,0,0,0,0,0 +nadgrids=@null +pm=greenwich +axis=enu +no_defs +type=crs", LL, [12.5], [61.25])
+    assert lon[0] == 12.5 and lat[0] == 61.25
 
 
 def test_meps_index_tables_built_on_device(rp):
