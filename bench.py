@@ -263,11 +263,11 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
     alg = S.bilinear_algorithmic_bytes(inx * iny, ox * oy, nz)
     src = S.meps_slab_torch(t=7, device="cuda")
     dst = torch.empty((nz, oy, ox), dtype=torch.float32, device="cuda")
-    for name, method in (("K5_bicubic_apply", 2), ("K6_nearest_apply", 0)):
+    for name, method in (("K4_bilinear_apply_dense", 1), ("K5_bicubic_apply", 2), ("K6_nearest_apply", 0)):
         c = fimex_b200.createCachedInterpolation("x", "y", method, px, py, S.MEPS_NX, S.MEPS_NY, ox, oy)
         sub = c.reduceInput(src, S.MEPS_NX, S.MEPS_NY)
         ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_dev_f(c._h, sub.data_ptr(), nz, dst.data_ptr(), nan, nan, stream), name))
-        out[name] = entry(ms, alg, pts, "S->T1 slab, dense layout")
+        out[name] = entry(ms, alg, pts, "S->T1 slab, the reference's dense layout (row pitch 949: no tensor map possible)")
         if method == 0:  # nearest also through the staged kernel (padded layout)
             pin = c.toPadded(sub)
             ip, il, op, ol_ = c.paddedLayout()

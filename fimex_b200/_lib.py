@@ -87,6 +87,7 @@ SIGNATURES = {
     "fimexcu_reproject_values": (C.c_int, [C.c_char_p, C.c_char_p, vp, vp, C.c_int]),
     "fimexcu_reproject_values_dev": (C.c_int, [C.c_char_p, C.c_char_p, vp, vp, sz, vp]),
     "fimexcu_get_vector_reproject_matrix": (C.c_int, [C.c_char_p, C.c_char_p, vp, vp, C.c_int, C.c_int, vp]),
+    "fimexcu_get_vector_reproject_matrix_field": (C.c_int, [C.c_char_p, C.c_char_p, vp, vp, C.c_int, C.c_int, vp]),
     "fimexcu_get_vector_reproject_matrix_points": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, vp, vp, C.c_int, C.c_int, vp]),
     "fimexcu_cache_create_from_projection": (vp, [C.c_int, C.c_char_p, C.c_char_p, vp, vp, sz, sz, vp, vp, sz, sz, C.c_int, C.c_int]),
     "fimexcu_cache_create_from_points": (vp, [C.c_int, C.c_char_p, C.c_char_p, vp, vp, sz, sz, vp, vp, sz, sz, C.c_int, C.c_int]),

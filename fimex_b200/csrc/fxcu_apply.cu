@@ -1519,7 +1519,9 @@ static int e2e_chunks()
 // pageable <-> pinned copies of one level chunk on the host cores (a single memcpy thread runs at a fraction of PCIe speed)
 static void host_copy(void* dst, const void* src, size_t bytes)
 {
-    parallel_ranges(bytes, size_t(4) << 20, [&](size_t a, size_t b) { std::memcpy(static_cast<char*>(dst) + a, static_cast<const char*>(src) + a, b - a); });
+    static const size_t threads = []() { const char* e = getenv("FIMEXCU_E2E_COPY_THREADS"); const int n = e ? atoi(e) : 4; return static_cast<size_t>(std::max(1, std::min(64, n))); }();
+    const size_t grain = std::max<size_t>(size_t(1) << 20, (bytes + threads - 1) / threads);
+    parallel_ranges(bytes, grain, [&](size_t a, size_t b) { std::memcpy(static_cast<char*>(dst) + a, static_cast<const char*>(src) + a, b - a); });
 }
 
 // host slab -> host slab through the device; T = float or short, `apply` = the strided device apply for that element type.

@@ -132,6 +132,42 @@ static int matrix_from_dev_points(const Crs& src, const Crs& dst, const double* 
     return FIMEXCU_OK;
 }
 
+// get_vector_reproject_matrix_proj (reproject.cc:363-397): delta = 0.1 % of the source spacing, sampled at two places, then the
+// per-point angles (:310-357).  All four arrays on the device, ox*oy entries, row-major.
+static int matrix_proj(const Crs& src, const Crs& dst, const double* d_in_x, const double* d_in_y, const double* d_out_x, const double* d_out_y, int ox,
+                       int oy, double* matrix3_host)
+{
+    const size_t n = static_cast<size_t>(ox) * oy;
+    auto at = [&](size_t idx) {
+        double v = 0;
+        cudaMemcpy(&v, d_in_x + idx, sizeof(double), cudaMemcpyDeviceToHost);
+        return v;
+    };
+    const double dflt = 1e-3;
+    double delta;
+    if (ox > 1) {
+        if (oy > 1) {
+            delta = dflt * (at(static_cast<size_t>(ox) + 1) - at(0));
+            const size_t ox2 = ox / 2, oy2 = oy / 2;
+            const double d2 = dflt * (at((oy2 + 1) * ox + (ox2 + 1)) - at(oy2 * ox + ox2));
+            delta += d2;
+            delta /= 2;
+        } else {
+            delta = dflt * (at(1) - at(0));
+        }
+    } else {
+        if (oy > 1) {
+            delta = dflt * (at(static_cast<size_t>(ox)) - at(0));
+        } else {
+            const double v0 = at(0);
+            delta = (v0 > 1) ? (v0 * dflt) : dflt;
+        }
+    }
+    if (std::fabs(delta) < 1e-9)
+        delta = dflt;
+    return matrix_from_dev_points(src, dst, d_in_x, d_in_y, d_out_x, d_out_y, delta, delta, n, matrix3_host);
+}
+
 } // namespace fxcu
 
 using namespace fxcu;
@@ -234,35 +270,31 @@ int fimexcu_get_vector_reproject_matrix(const char* proj_input, const char* proj
         FXCU_CUDA(cudaMemcpy(outx.p, hx.data(), n * 8, cudaMemcpyHostToDevice));
         FXCU_CUDA(cudaMemcpy(outy.p, hy.data(), n * 8, cudaMemcpyHostToDevice));
     }
-    // delta: 0.1 % of the source spacing, sampled at two places (reproject.cc:363-397)
-    auto at = [&](size_t idx) {
-        double v = 0;
-        cudaMemcpy(&v, inx.as<double>() + idx, sizeof(double), cudaMemcpyDeviceToHost);
-        return v;
-    };
-    const double dflt = 1e-3;
-    double delta;
-    if (ox > 1) {
-        if (oy > 1) {
-            delta = dflt * (at(static_cast<size_t>(ox) + 1) - at(0));
-            const size_t ox2 = ox / 2, oy2 = oy / 2;
-            const double d2 = dflt * (at((oy2 + 1) * ox + (ox2 + 1)) - at(oy2 * ox + ox2));
-            delta += d2;
-            delta /= 2;
-        } else {
-            delta = dflt * (at(1) - at(0));
-        }
-    } else {
-        if (oy > 1) {
-            delta = dflt * (at(static_cast<size_t>(ox)) - at(0));
-        } else {
-            const double v0 = at(0);
-            delta = (v0 > 1) ? (v0 * dflt) : dflt;
-        }
-    }
-    if (std::fabs(delta) < 1e-9)
-        delta = dflt;
-    return matrix_from_dev_points(src, dst, inx.as<double>(), iny.as<double>(), outx.as<double>(), outy.as<double>(), delta, delta, n, matrix3);
+    return matrix_proj(src, dst, inx.as<double>(), iny.as<double>(), outx.as<double>(), outy.as<double>(), ox, oy, matrix3);
+}
+
+int fimexcu_get_vector_reproject_matrix_field(const char* proj_input, const char* proj_output, const double* in_x_field, const double* in_y_field, int ox,
+                                              int oy, double* matrix3)
+{
+    clear_error();
+    if (!require_device())
+        return FIMEXCU_ERROR;
+    Crs src, dst;
+    if (!parse_pair(proj_input, proj_output, src, dst))
+        return FIMEXCU_ERROR;
+    if (ox <= 0 || oy <= 0)
+        return FIMEXCU_OK;
+    const size_t n = static_cast<size_t>(ox) * oy;
+    DevBuf inx, iny, outx, outy;
+    if (!inx.alloc(n * 8, nullptr) || !iny.alloc(n * 8, nullptr) || !outx.alloc(n * 8, nullptr) || !outy.alloc(n * 8, nullptr))
+        return FIMEXCU_ERROR;
+    FXCU_CUDA(cudaMemcpy(inx.p, in_x_field, n * 8, cudaMemcpyHostToDevice));
+    FXCU_CUDA(cudaMemcpy(iny.p, in_y_field, n * 8, cudaMemcpyHostToDevice));
+    FXCU_CUDA(cudaMemcpy(outx.p, inx.p, n * 8, cudaMemcpyDeviceToDevice));
+    FXCU_CUDA(cudaMemcpy(outy.p, iny.p, n * 8, cudaMemcpyDeviceToDevice));
+    transform_kernel<<<blocks_for(n, 256), 256>>>(src, dst, n, outx.as<double>(), outy.as<double>()); // c2c.fwd (reproject.cc:459)
+    FXCU_CUDA(cudaGetLastError());
+    return matrix_proj(src, dst, inx.as<double>(), iny.as<double>(), outx.as<double>(), outy.as<double>(), ox, oy, matrix3);
 }
 
 int fimexcu_get_vector_reproject_matrix_points(const char* proj_input, const char* proj_output, int inputIsMetric, const double* out_x_points,

@@ -36,6 +36,16 @@ def get_vector_reproject_matrix(proj_input, proj_output, out_x_axis, out_y_axis)
     return m
 
 
+def get_vector_reproject_matrix_field(proj_input, proj_output, in_x_field, in_y_field):
+    """reproject::get_vector_reproject_matrix_field (src/reproject.cc:449-461); fields are [oy][ox] positions in the input projection."""
+    fx, fy = _f64(in_x_field), _f64(in_y_field)
+    oy, ox = fx.shape
+    m = np.empty((oy, ox, 3), dtype=np.float64)
+    _lib.check(lib.fimexcu_get_vector_reproject_matrix_field(proj_input.encode(), proj_output.encode(), fx.ctypes.data, fy.ctypes.data, ox, oy,
+                                                             m.ctypes.data), "get_vector_reproject_matrix_field")
+    return m
+
+
 def get_vector_reproject_matrix_points(proj_input, proj_output, inputIsMetric, out_x_points, out_y_points):
     """reproject::get_vector_reproject_matrix_points (src/reproject.cc:432-447); points are [oy][ox] arrays."""
     px, py = _f64(out_x_points), _f64(out_y_points)

@@ -259,6 +259,11 @@ int fimexcu_reproject_values_dev(const char* proj_input, const char* proj_output
  * :310-357).  matrix3: ox*oy*3 doubles out. */
 int fimexcu_get_vector_reproject_matrix(const char* proj_input, const char* proj_output, const double* out_x_axis, const double* out_y_axis, int ox,
                                         int oy, double* matrix3);
+/* Replaces reproject::get_vector_reproject_matrix_field (reproject.h:165-178, reproject.cc:449-461): the grid keeps its cells, only
+ * the direction of the vectors changes (rotation of model winds to true north in CDMProcessor, src/CDMProcessor.cc:149);
+ * in_x_field / in_y_field: ox*oy positions in the input projection (HOST). */
+int fimexcu_get_vector_reproject_matrix_field(const char* proj_input, const char* proj_output, const double* in_x_field, const double* in_y_field, int ox,
+                                              int oy, double* matrix3);
 /* Replaces reproject::get_vector_reproject_matrix_points (reproject.h:177-193, reproject.cc:432-447). */
 int fimexcu_get_vector_reproject_matrix_points(const char* proj_input, const char* proj_output, int inputIsMetric, const double* out_x_points,
                                                const double* out_y_points, int ox, int oy, double* matrix3);

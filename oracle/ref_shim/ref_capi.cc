@@ -347,6 +347,30 @@ int ref_get_vector_reproject_matrix(const char* proj_in, const char* proj_out, c
     }
 }
 
+int ref_get_vector_reproject_matrix_field(const char* proj_in, const char* proj_out, const double* in_x_field, const double* in_y_field, int ox, int oy,
+                                          double* matrix3)
+{
+    try {
+        auto m = reproject::get_vector_reproject_matrix_field(proj_in, proj_out, in_x_field, in_y_field, ox, oy);
+        std::memcpy(matrix3, m->mtx(), sizeof(double) * 3 * ox * oy);
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
+// reproject::vector_reproject_values_f (reproject.cc:532-540): matrix from the axes + rotation, as the reference's tests call it
+int ref_vector_reproject_values_f(const char* proj_in, const char* proj_out, float* u, float* v, const double* out_x_axis, const double* out_y_axis,
+                                  int out_x_axis_type, int out_y_axis_type, int ox, int oy, int oz)
+{
+    try {
+        reproject::vector_reproject_values_f(proj_in, proj_out, u, v, out_x_axis, out_y_axis, out_x_axis_type, out_y_axis_type, ox, oy, oz);
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
 namespace {
 reproject::Matrix_cp borrow_matrix(const double* matrix3, int ox, int oy)
 {

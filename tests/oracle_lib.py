@@ -180,6 +180,9 @@ def ref(omp=False):
         "ref_vector_reproject_direction_by_matrix_f": (None, [c_double_p, C.c_int, C.c_int, c_float_p, C.c_int]),
         "ref_reproject_axes": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, C.c_int, C.c_int, c_double_p, c_double_p]),
         "ref_get_vector_reproject_matrix": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, C.c_int, C.c_int, c_double_p]),
+        "ref_get_vector_reproject_matrix_field": (C.c_int, [C.c_char_p, C.c_char_p, c_double_p, c_double_p, C.c_int, C.c_int, c_double_p]),
+        "ref_vector_reproject_values_f": (C.c_int, [C.c_char_p, C.c_char_p, c_float_p, c_float_p, c_double_p, c_double_p, C.c_int, C.c_int, C.c_int,
+                                                    C.c_int, C.c_int]),
         "ref_reproject_f": (C.c_int, [C.c_int, C.c_char_p, c_float_p, c_double_p, c_double_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p,
                                       c_float_p, c_double_p, c_double_p, C.c_int, C.c_int, C.c_int, C.c_int]),
         # the reference's own extern "C" kernels (src/interpolation.c), exported as they are
