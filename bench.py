@@ -268,12 +268,18 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
         sub = c.reduceInput(src, S.MEPS_NX, S.MEPS_NY)
         ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_dev_f(c._h, sub.data_ptr(), nz, dst.data_ptr(), nan, nan, stream), name))
         out[name] = entry(ms, alg, pts, "S->T1 slab, the reference's dense layout (row pitch 949: no tensor map possible)")
-        if method == 0:  # nearest also through the staged kernel (padded layout)
+        if method in (0, 2):  # nearest and bicubic also through the staged kernels (padded layout)
             pin = c.toPadded(sub)
             ip, il, op, ol_ = c.paddedLayout()
             pout = torch.empty((nz, oy, op), dtype=torch.float32, device="cuda")
             ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_dev_strided_f(c._h, pin.data_ptr(), ip, il, nz, pout.data_ptr(), op, ol_, nan, nan, stream), name))
-            out[name + "_padded_staged"] = entry(ms, alg, pts, "S->T1 slab, padded layout, TMA-staged")
+            out[name + "_padded_staged"] = entry(ms, alg, pts, "S->T1 slab, padded layout, TMA-staged" +
+                                                 (" (bit-exact: the direct kernel; 40 separately rounded FP64 operations per value bound any bit-exact form at 0.41 ms = 40 %)" if method == 2 else ""))
+            if method == 2:
+                c.setFastBicubic(True)
+                ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_dev_strided_f(c._h, pin.data_ptr(), ip, il, nz, pout.data_ptr(), op, ol_, nan, nan, stream), name))
+                out[name + "_padded_staged_f32"] = entry(ms, alg, pts, "same, opt-in f32 FMA arithmetic (1e-5 contract, identical undefined mask)")
+                c.setFastBicubic(False)
             del pin, pout
         c.close()
     # K7: fused u,v interpolation + rotation, and the stand-alone rotation
@@ -349,16 +355,22 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
     out["vcoord_hybrid_pressure_to_height_field"] = entry(lev_ms, (8.0 + 4.0 * 65) * ncol_v, 65 * ncol_v,
                                                           "hybrid pressure -> standard altitude -> minus topography, one pass, 65 levels: 268 B per column")
     del p_f, sap_f, sgp_f, t_f, q_f
-    # K12: forward mean, 2030x1354 swath -> 1000x1000 cells, 8 levels (level_compat off: every level aggregated)
+    # K12 / K13: forward aggregation of the 2030x1354 swath, 8 levels (level_compat off: every level aggregated), onto a 1000x1000 grid
+    # (configs[3]-like, 2.7 sources per cell) and onto a coarse 100x68 grid (20:1 in each direction, ~400 sources per cell)
     gx, gy = np.meshgrid(np.arange(1354), np.arange(2030))
-    fwd = I.CachedForwardInterpolation("x", "y", 6, (gx * (1000 / 1354.0)).ravel() - 0.3, (gy * (1000 / 2030.0)).ravel() - 0.3, 1354, 2030, 1000, 1000,
-                                       level_compat=False)
-    fin = torch.randn((8, fwd.getInY(), fwd.getInX()), dtype=torch.float32, device="cuda")
-    fout = torch.empty((8, 1000, 1000), dtype=torch.float32, device="cuda")
-    ms = timed(lambda: _lib.check(lib.fimexcu_forward_apply_dev_f(fwd._h, fin.data_ptr(), 8, fout.data_ptr(), nan, nan, 0, stream), "fwd"))
-    n_in = fwd.getInX() * fwd.getInY()
-    out["K12_forward_mean"] = entry(ms, (4.0 + 4.0 * 1e6 / n_in + 8.0 / 8) * n_in * 8, n_in * 8, "2030x1354 swath -> 1000x1000, 8 levels; points = source points")
-    fwd.close()
+    fin = None
+    for tag, (tox, toy) in (("", (1000, 1000)), ("_coarse_20to1", (68, 100))):
+        for name, method in (("K12_forward_mean", 6), ("K12_forward_max", 8), ("K13_forward_median", 7)):
+            fwd = I.CachedForwardInterpolation("x", "y", method, (gx * (tox / 1354.0)).ravel() - 0.3, (gy * (toy / 2030.0)).ravel() - 0.3, 1354, 2030, tox, toy,
+                                               level_compat=False)
+            if fin is None or fin.shape[1:] != (fwd.getInY(), fwd.getInX()):
+                fin = torch.randn((8, fwd.getInY(), fwd.getInX()), dtype=torch.float32, device="cuda")
+            fout = torch.empty((8, toy, tox), dtype=torch.float32, device="cuda")
+            ms = timed(lambda: _lib.check(lib.fimexcu_forward_apply_dev_f(fwd._h, fin.data_ptr(), 8, fout.data_ptr(), nan, nan, 0, stream), "fwd"))
+            n_in = fwd.getInX() * fwd.getInY()
+            out[name + tag] = entry(ms, (4.0 + 4.0 * tox * toy / n_in + 8.0 / 8) * n_in * 8, n_in * 8,
+                                    f"2030x1354 swath -> {tox}x{toy}, 8 levels; points = source points")
+            fwd.close()
     # K1+K2+K3: cache build from projection strings (one-off; points/s, no roofline)
     lon, lat = S.target_axes("T1")
     mx, my = S.meps_axes()

@@ -48,6 +48,7 @@ SIGNATURES = {
     "fimexcu_cache_replicate": (C.c_int, [vp, C.c_int, c_int_p]),
     "fimexcu_vecrot_replicate": (C.c_int, [vp, C.c_int, c_int_p]),
     "fimexcu_set_staged_kernels": (None, [C.c_int]),
+    "fimexcu_cache_set_fast_bicubic": (C.c_int, [vp, C.c_int]),
     "fimexcu_host_pool_trim": (None, []),
     "fimexcu_cache_apply_dev_strided_f": (C.c_int, [vp, vp, sz, sz, sz, vp, sz, sz, C.c_float, C.c_float, vp]),
     "fimexcu_vcoord_levels_dev_f": (C.c_int, [C.c_int, vp, vp, C.c_double, vp, sz, C.c_double, vp, C.c_int, vp, C.c_double, sz, sz, sz, vp, vp]),

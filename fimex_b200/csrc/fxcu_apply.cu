@@ -505,6 +505,10 @@ constexpr int TMA_ZB = 4;     // levels per stage
 constexpr int TMA_STAGES = 4; // ring depth (32 KB per CTA, 6 CTAs per SM)
 constexpr int TMA_TH = 8;     // consumer warps == tile rows
 constexpr int TMA_THREADS = 32 * TMA_TH + 32;
+// staged bicubic: 4 x 4 footprints need 3 more rows and columns than the bilinear box offers
+constexpr int CUB_BH = 20;    // box height
+constexpr int CUB_ZB = 4;     // levels per stage (10 KB)
+constexpr int CUB_STAGES = 3;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count)
@@ -690,6 +694,125 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
     }
 }
 
+// K5, staged form, opt-in arithmetic (fimexcu_cache_set_fast_bicubic).  Same ring as K4 with a 32 x 20 box (4 x 4 footprints).
+// What bounds the reference's arithmetic on this machine is not memory: per value it is 16 f64 products + 16 f64 sums (the column
+// sums XMF) and 4 + 4 more for the row combination, each rounded on its own (interpolation.c:395-406) = 40 FP64 operations --
+// 0.41 ms per S->T1 slab at 64 FP64 lanes per SM and clock, so 40 % of the HBM roofline is the ceiling of ANY bit-exact form -- plus
+// 16 f32->f64 widenings of the taps: on the conversion (XU) pipe in the direct kernel (87 % busy, profiles/r1_bicubic_ncu_raw.txt:
+// 0.73 ms), or, tried in round 2, once per staged value into an f64 copy of the box in shared memory, where the 8-byte taps then
+// cost two shared-memory wavefronts each (0.89 ms: slower, not kept; profiles/r2_kernel_variants.md).  The bit-exact bicubic
+// therefore stays with the direct kernel.  This kernel is the variant inside BASELINE.json's 1e-5: weights narrowed to f32, 20
+// fused multiply-adds per value straight from the f32 box; 16 four-byte taps per value make it shared-memory-bound (one wavefront
+// per tap and warp: 0.33 ms per slab).  Undefined masks are identical to the reference's (NaN and Inf taps poison both forms alike).
+template <bool BAD, bool FILL>
+__global__ void __launch_bounds__(TMA_THREADS, 5) staged_bicubic_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ApplyParams P)
+{
+    constexpr int LVL = TMA_BW * CUB_BH;
+    constexpr int STAGE_FLOATS = LVL * CUB_ZB;
+    __shared__ __align__(128) float raw[CUB_STAGES][STAGE_FLOATS];
+    __shared__ __align__(8) uint64_t full[CUB_STAGES];
+    __shared__ __align__(8) uint64_t empty[CUB_STAGES];
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const bool consumer = warp < TMA_TH;
+    const int ox = blockIdx.x * 32 + lane, oy = blockIdx.y * TMA_TH + warp;
+    const bool in_grid = consumer && ox < P.outX && oy < P.outY;
+    const int4 meta = __ldg(P.tile_meta + blockIdx.y * gridDim.x + blockIdx.x);
+    int f = -1;
+    double fxd = 0., fyd = 0.;
+    if (in_grid) {
+        const size_t o = static_cast<size_t>(oy) * P.outX + ox;
+        f = P.off[o];
+        if (f >= 0) {
+            fxd = static_cast<const double*>(P.wx)[o];
+            fyd = static_cast<const double*>(P.wy)[o];
+        }
+    }
+    if (tid == 0) {
+        for (int s = 0; s < CUB_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], TMA_TH);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int bx0 = meta.x, by0 = meta.y;
+    const int zb = blockIdx.z * P.zchunk, nzc = min(P.nz, zb + P.zchunk) - zb;
+    float* po = static_cast<float*>(P.out) + static_cast<size_t>(zb) * P.outLevel + static_cast<size_t>(oy) * P.outPitch + ox;
+    float wxf[4], wyf[4];
+    {
+        double wxv[4], wyv[4];
+        cubic_weights(fxd, wxv);
+        cubic_weights(fyd, wyv);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            wxf[i] = static_cast<float>(wxv[i]);
+            wyf[i] = static_cast<float>(wyv[i]);
+        }
+    }
+    const int y0 = (f >= 0) ? f / P.inX : by0, x0 = (f >= 0) ? f - y0 * P.inX : bx0;
+    if (!(meta.z & TILE_HAS_DATA) || !(meta.z & TILE_FITS)) { // nothing defined, or a footprint beyond the box: no staging
+        if (!in_grid)
+            return;
+        if (f < 0) {
+            for (int z = 0; z < nzc; ++z, po += P.outLevel)
+                store_out<FILL>(po, nan_f(), P.fill);
+            return;
+        }
+        const float* p = static_cast<const float*>(P.in) + static_cast<size_t>(zb) * P.inLevel + static_cast<size_t>(y0) * P.inPitch + x0;
+        for (int z = 0; z < nzc; ++z, p += P.inLevel, po += P.outLevel) {
+            float acc = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float col = __fmul_rn(wxf[0], load_in<BAD>(p + j * P.inPitch, P.bad));
+#pragma unroll
+                for (int i = 1; i < 4; ++i)
+                    col = __fmaf_rn(wxf[i], load_in<BAD>(p + j * P.inPitch + i, P.bad), col);
+                acc = __fmaf_rn(col, wyf[j], acc);
+            }
+            store_out<FILL>(po, acc, P.fill);
+        }
+        return;
+    }
+    constexpr unsigned BYTES = STAGE_FLOATS * sizeof(float);
+    const int niter = (nzc + CUB_ZB - 1) / CUB_ZB;
+    if (!consumer) {
+        if (lane == 0) {
+            for (int it = 0; it < niter; ++it) {
+                const int s = it % CUB_STAGES;
+                mbar_wait(&empty[s], ((it / CUB_STAGES) & 1) ^ 1);
+                mbar_expect_tx(&full[s], BYTES);
+                tma_load_3d(&raw[s][0], &tmap, &full[s], bx0, by0, zb + it * CUB_ZB);
+            }
+        }
+        return;
+    }
+    const int r = (y0 - by0) * TMA_BW + (x0 - bx0);
+    for (int it = 0; it < niter; ++it) {
+        const int s = it % CUB_STAGES;
+        mbar_wait(&full[s], (it / CUB_STAGES) & 1);
+#pragma unroll
+        for (int k = 0; k < CUB_ZB; ++k) {
+            const float* t = &raw[s][k * LVL + r];
+            float acc = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float col = __fmul_rn(wxf[0], tap<BAD>(t, j * TMA_BW, P.bad));
+#pragma unroll
+                for (int i = 1; i < 4; ++i)
+                    col = __fmaf_rn(wxf[i], tap<BAD>(t, j * TMA_BW + i, P.bad), col);
+                acc = __fmaf_rn(col, wyf[j], acc);
+            }
+            if (in_grid && it * CUB_ZB + k < nzc)
+                store_out<FILL>(po + k * P.outLevel, f >= 0 ? acc : nan_f(), P.fill);
+        }
+        po += CUB_ZB * P.outLevel;
+        __syncwarp();
+        if (lane == 0)
+            mbar_arrive(&empty[s]);
+    }
+}
+
 // Staged form of the fused vector pass: u and v boxes of the same footprint travel through the same ring (two TMA loads per
 // stage on one mbarrier), consumers interpolate both components, rotate (reproject.cc:488-507) and store.
 constexpr int UV_ZB = 2;     // levels per stage (two fields per level)
@@ -869,8 +992,9 @@ __global__ void __launch_bounds__(TMA_THREADS, 5) staged_uv_tma_kernel(const __g
 
 // fraction of 32 x 8 target tiles whose source footprint fits the staged kernel's box (decides, once per cache,
 // whether the staged kernel is worth launching).  counts[0] = tiles with data, counts[1] = of those, tiles that fit
+// cubic = true: `off` is the tap (x0-1, y0-1) of a 4 x 4 footprint (bicubic tables), box height CUB_BH
 __global__ void __launch_bounds__(256) tile_fit_kernel(const int* __restrict__ off, const float* __restrict__ wx, const float* __restrict__ wy, int outX,
-                                                       int outY, int inX, unsigned* __restrict__ counts, int4* __restrict__ meta)
+                                                       int outY, int inX, unsigned* __restrict__ counts, int4* __restrict__ meta, bool cubic = false)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ox = blockIdx.x * 32 + lane, oy = blockIdx.y * 8 + warp;
@@ -882,9 +1006,9 @@ __global__ void __launch_bounds__(256) tile_fit_kernel(const int* __restrict__ o
         if (f >= 0) {
             y0 = f / inX;
             x0 = f - y0 * inX;
-            const bool ex = wx && wx[o] >= 0.f, ey = wy && wy[o] >= 0.f;
-            x1 = x0 + (ex ? 1 : 0);
-            y1 = y0 + (ey ? 1 : 0);
+            const bool ex = cubic || (wx && wx[o] >= 0.f), ey = cubic || (wy && wy[o] >= 0.f);
+            x1 = x0 + (cubic ? 3 : (ex ? 1 : 0));
+            y1 = y0 + (cubic ? 3 : (ey ? 1 : 0));
             interior = ex && ey;
         }
     }
@@ -915,7 +1039,7 @@ __global__ void __launch_bounds__(256) tile_fit_kernel(const int* __restrict__ o
         if (x1 >= 0) {
             flags |= TILE_HAS_DATA;
             atomicAdd(&counts[0], 1u);
-            if ((x1 - (x0 & ~7) + 1 <= TMA_BW) && (y1 - y0 + 1 <= TMA_BH)) {
+            if ((x1 - (x0 & ~7) + 1 <= TMA_BW) && (y1 - y0 + 1 <= (cubic ? CUB_BH : TMA_BH))) {
                 flags |= TILE_FITS;
                 atomicAdd(&counts[1], 1u);
             }
@@ -1259,6 +1383,22 @@ fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, s
         build_bicubic_kernel<<<nb, 256, 0, s>>>(d_px, d_py, n, static_cast<int>(c->inX), static_cast<int>(c->inY), static_cast<double>(minX),
                                                  static_cast<double>(minY), c->off.as<int>(), c->wx.as<double>(), c->wy.as<double>());
         FXCU_CUDA_NULL(cudaGetLastError());
+        // 32 x 8 target tiles whose 4 x 4 footprints fit the staged bicubic kernel's 32 x 20 box
+        DevBuf counts;
+        if (!counts.alloc(2 * sizeof(unsigned), s))
+            return nullptr;
+        FXCU_CUDA_NULL(cudaMemsetAsync(counts.p, 0, 2 * sizeof(unsigned), s));
+        const dim3 tg(static_cast<unsigned>((outX + 31) / 32), static_cast<unsigned>((outY + 7) / 8));
+        if (!c->tile_meta.alloc_sync(static_cast<size_t>(tg.x) * tg.y * sizeof(int4)))
+            return nullptr;
+        tile_fit_kernel<<<tg, 256, 0, s>>>(c->off.as<int>(), nullptr, nullptr, static_cast<int>(outX), static_cast<int>(outY), static_cast<int>(c->inX),
+                                           counts.as<unsigned>(), c->tile_meta.as<int4>(), true);
+        FXCU_CUDA_NULL(cudaGetLastError());
+        unsigned hc[2] = {0, 0};
+        FXCU_CUDA_NULL(cudaMemcpyAsync(hc, counts.p, sizeof(hc), cudaMemcpyDeviceToHost, s));
+        FXCU_CUDA_NULL(cudaStreamSynchronize(s));
+        c->tiles_with_data = hc[0];
+        c->tiles_fitting = hc[1];
     }
     FXCU_CUDA_NULL(cudaStreamSynchronize(s));
     return c.release();
@@ -1282,7 +1422,8 @@ static tensor_map_encode_fn tensor_map_encoder()
     return fn;
 }
 
-static bool make_source_map(CUtensorMap* m, const float* d_in, size_t inX, size_t inY, size_t nz, int inPitch, size_t inLevel, int depth = TMA_ZB)
+static bool make_source_map(CUtensorMap* m, const float* d_in, size_t inX, size_t inY, size_t nz, int inPitch, size_t inLevel, int depth = TMA_ZB,
+                            int height = TMA_BH)
 {
     tensor_map_encode_fn enc = tensor_map_encoder();
     if (!enc)
@@ -1292,7 +1433,7 @@ static bool make_source_map(CUtensorMap* m, const float* d_in, size_t inX, size_
         return false;
     cuuint64_t dims[3] = {inX, inY, nz};
     cuuint64_t strides[2] = {static_cast<cuuint64_t>(inPitch) * 4, static_cast<cuuint64_t>(inLevel) * 4};
-    cuuint32_t box[3] = {TMA_BW, TMA_BH, static_cast<cuuint32_t>(depth)};
+    cuuint32_t box[3] = {TMA_BW, static_cast<cuuint32_t>(height), static_cast<cuuint32_t>(depth)};
     cuuint32_t es[3] = {1, 1, 1};
     return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(d_in), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -1338,6 +1479,22 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
                 staged_apply_tma_kernel<BAD, FILL, true><<<grid, TMA_THREADS, 0, s>>>(map, P);
             else
                 staged_apply_tma_kernel<BAD, FILL, false><<<grid, TMA_THREADS, 0, s>>>(map, P);
+            return;
+        }
+    }
+    if (c->kind == KIND_BICUBIC && c->fast_bicubic && allow_tma && P.tabX == 0 && c->tile_meta.p) {
+        CUtensorMap map;
+        const bool enough = tiles >= static_cast<size_t>(sm_count()) * 3;
+        const bool fits = c->tiles_with_data > 0 && 10ull * c->tiles_fitting >= 8ull * c->tiles_with_data;
+        if (enough && fits &&
+            make_source_map(&map, static_cast<const float*>(P.in), c->inX, c->inY, static_cast<size_t>(P.nz), P.inPitch, P.inLevel, CUB_ZB, CUB_BH)) {
+            const size_t slots = static_cast<size_t>(sm_count()) * 5;
+            size_t zsplit = std::max<size_t>(1, (8 * slots + tiles - 1) / tiles);
+            zsplit = std::min<size_t>(zsplit, std::max<size_t>(1, static_cast<size_t>(P.nz) / (4 * CUB_ZB)));
+            P.zchunk = static_cast<int>(((static_cast<size_t>(P.nz) + zsplit - 1) / zsplit + CUB_ZB - 1) / CUB_ZB * CUB_ZB);
+            const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH),
+                            static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
+            staged_bicubic_tma_kernel<BAD, FILL><<<grid, TMA_THREADS, 0, s>>>(map, P);
             return;
         }
     }
@@ -1974,6 +2131,18 @@ int fimexcu_cache_apply_uv_f(const fimexcu_cache* c, const fimexcu_vecrot* r, co
 
 void fimexcu_cache_destroy(fimexcu_cache* c) { delete c; }
 
+int fimexcu_cache_set_fast_bicubic(fimexcu_cache* c, int on)
+{
+    clear_error();
+    if (!c)
+        FXCU_FAIL("fimexcu_cache_set_fast_bicubic: null cache");
+    c->fast_bicubic = on != 0;
+    for (fimexcu_cache* r : c->replicas)
+        if (r)
+            r->fast_bicubic = on != 0;
+    return FIMEXCU_OK;
+}
+
 void fimexcu_set_staged_kernels(int mode) { g_tma_override.store(mode < 0 ? -1 : (mode ? 1 : 0), std::memory_order_relaxed); }
 
 int fimexcu_cache_replicate(fimexcu_cache* c, int n_devices, const int* device_ids)
@@ -2010,6 +2179,7 @@ int fimexcu_cache_replicate(fimexcu_cache* c, int n_devices, const int* device_i
         r->reduced = c->reduced;
         r->xMin = c->xMin;
         r->yMin = c->yMin;
+        r->fast_bicubic = c->fast_bicubic;
         r->tiles_with_data = c->tiles_with_data;
         r->tiles_fitting = c->tiles_fitting;
         if (!replicate_buf(r->off, d, c->off, c->device, nullptr) || !replicate_buf(r->wx, d, c->wx, c->device, nullptr) ||

@@ -221,6 +221,315 @@ __global__ void __launch_bounds__(256) fwd_apply_kernel(const FwdParams P)
     }
 }
 
+// ---- round-2 forms of the apply -----------------------------------------------------------------------------------------------
+// Sum / mean / min / max, thread per target cell, the sources in the OUTER loop and a block of ZB levels in registers: the segment's
+// source indices are read once per level block instead of once per level, and ZB independent gathers are in flight per source.
+// Every level's values are still pushed in ascending source order, so the f32 running sums are the reference's bit for bit
+// (CachedForwardInterpolation.cc:79-86, 143-158).
+template <int KIND, bool UNDEF, int ZB>
+__global__ void __launch_bounds__(256) fwd_reduce_kernel(const FwdParams P)
+{
+    const size_t o = blockIdx.x * 256ull + threadIdx.x;
+    if (o >= P.nout)
+        return;
+    const int z0 = blockIdx.y * P.zchunk, z1 = min(P.nz, z0 + P.zchunk);
+    const int s0 = P.segStart[o], s1 = P.segStart[o + 1];
+    const bool has_bad = !isnan(P.bad), has_fill = !isnan(P.fill);
+    for (int zb = z0; zb < z1; zb += ZB) {
+        const int nk = min(ZB, z1 - zb);
+        const float* src = P.in + static_cast<size_t>(zb) * P.inLayer;
+        float val[ZB];
+        int cnt[ZB];
+#pragma unroll
+        for (int q = 0; q < ZB; ++q) {
+            val[q] = 0.f;
+            cnt[q] = 0;
+        }
+        auto push = [&](const float (&f)[ZB]) {
+#pragma unroll
+            for (int q = 0; q < ZB; ++q) {
+                if (!UNDEF && isnan(f[q]))
+                    continue;
+                if (KIND <= 1)
+                    val[q] = __fadd_rn(val[q], f[q]); // AggSum::push
+                else if (KIND == 3) {
+                    if (cnt[q] == 0 || f[q] > val[q])
+                        val[q] = f[q]; // AggMax::push
+                } else {
+                    if (cnt[q] == 0 || f[q] < val[q])
+                        val[q] = f[q]; // AggMin::push
+                }
+                ++cnt[q];
+            }
+        };
+        int k = s0;
+        for (; k + 2 <= s1; k += 2) { // two sources at a time: their index loads, then all their gathers, are in flight together
+            const float* p0 = src + P.segIdx[k];
+            const float* p1 = src + P.segIdx[k + 1];
+            float f0[ZB], f1[ZB];
+#pragma unroll
+            for (int q = 0; q < ZB; ++q) {
+                f0[q] = q < nk ? fwd_load(p0 + static_cast<size_t>(q) * P.inLayer, P.bad, has_bad) : nan_f();
+                f1[q] = q < nk ? fwd_load(p1 + static_cast<size_t>(q) * P.inLayer, P.bad, has_bad) : nan_f();
+            }
+            push(f0);
+            push(f1);
+        }
+        if (k < s1) {
+            const float* p = src + P.segIdx[k];
+            float f[ZB];
+#pragma unroll
+            for (int q = 0; q < ZB; ++q)
+                f[q] = q < nk ? fwd_load(p + static_cast<size_t>(q) * P.inLayer, P.bad, has_bad) : nan_f();
+            push(f);
+        }
+#pragma unroll
+        for (int q = 0; q < ZB; ++q) {
+            if (q >= nk)
+                break;
+            float r = nan_f();
+            if (cnt[q] != 0)
+                r = KIND == 1 ? __fdiv_rn(val[q], static_cast<float>(cnt[q])) : val[q]; // mean: val / count (:90)
+            if (has_fill && isnan(r))
+                r = P.fill;
+            __stcs(P.out + static_cast<size_t>(zb + q) * P.nout + o, r);
+        }
+    }
+}
+
+// Min / max without the undef flavour do not depend on the order of the values: long segments (coarse targets: hundreds of sources
+// per cell) are taken by a whole warp -- lanes stride over the segment, so a warp reads runs of consecutive source cells instead of
+// 32 cells that lie a target-cell width apart -- and combined with shuffles.  One warp per target cell, ZB levels per pass.
+template <bool MAX, int ZB>
+__global__ void __launch_bounds__(256) fwd_minmax_warp_kernel(const FwdParams P)
+{
+    const size_t o = (blockIdx.x * 256ull + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (o >= P.nout)
+        return;
+    const int z0 = blockIdx.y * P.zchunk, z1 = min(P.nz, z0 + P.zchunk);
+    const int s0 = P.segStart[o], s1 = P.segStart[o + 1];
+    const bool has_bad = !isnan(P.bad), has_fill = !isnan(P.fill);
+    for (int zb = z0; zb < z1; zb += ZB) {
+        const int nk = min(ZB, z1 - zb);
+        const float* src = P.in + static_cast<size_t>(zb) * P.inLayer;
+        float val[ZB];
+#pragma unroll
+        for (int q = 0; q < ZB; ++q)
+            val[q] = nan_f(); // NaN = nothing pushed yet
+        for (int k = s0 + lane; k < s1; k += 32) {
+            const float* p = src + P.segIdx[k];
+#pragma unroll
+            for (int q = 0; q < ZB; ++q) {
+                if (q < nk) {
+                    const float f = fwd_load(p + static_cast<size_t>(q) * P.inLayer, P.bad, has_bad);
+                    if (!isnan(f) && (isnan(val[q]) || (MAX ? f > val[q] : f < val[q])))
+                        val[q] = f;
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < ZB; ++q) {
+#pragma unroll
+            for (int sft = 16; sft > 0; sft >>= 1) {
+                const float other = __shfl_xor_sync(0xffffffffu, val[q], sft);
+                if (!isnan(other) && (isnan(val[q]) || (MAX ? other > val[q] : other < val[q])))
+                    val[q] = other;
+            }
+            if (lane == 0 && q < nk) {
+                float r = val[q];
+                if (has_fill && isnan(r))
+                    r = P.fill;
+                __stcs(P.out + static_cast<size_t>(zb + q) * P.nout + o, r);
+            }
+        }
+    }
+}
+
+// Median (AggMedian: nth_element at n/2, CachedForwardInterpolation.cc:113-130): the element of rank n/2 among the pushed values.
+// The segment's values of one level are loaded ONCE: up to MED_LOCAL of them into a per-thread array, where the rank is found by
+// counting (v has rank r iff #less <= r < #less + #equal); longer segments by a radix selection on the ordered bit pattern of the
+// floats, most significant bit first (32 sweeps over the segment, each a sequential re-read that stays in L1/L2) -- O(32 n)
+// instead of the O(n^2) loads of round 1.
+constexpr int MED_LOCAL = 32;
+__device__ __forceinline__ unsigned ordered_bits(float v)
+{
+    const unsigned b = __float_as_uint(v);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+template <bool UNDEF>
+__global__ void __launch_bounds__(128) fwd_median_kernel(const FwdParams P)
+{
+    const size_t o = blockIdx.x * 128ull + threadIdx.x;
+    if (o >= P.nout)
+        return;
+    const int z0 = blockIdx.y * P.zchunk, z1 = min(P.nz, z0 + P.zchunk);
+    const int s0 = P.segStart[o], s1 = P.segStart[o + 1];
+    const bool has_bad = !isnan(P.bad), has_fill = !isnan(P.fill);
+    float v[MED_LOCAL];
+    for (int z = z0; z < z1; ++z) {
+        const float* src = P.in + static_cast<size_t>(z) * P.inLayer;
+        float r = nan_f();
+        int n = 0;
+        bool any_nan = false;
+        if (s1 - s0 <= MED_LOCAL) {
+            for (int k = s0; k < s1; ++k) {
+                const float f = fwd_load(src + P.segIdx[k], P.bad, has_bad);
+                if (isnan(f)) {
+                    any_nan = any_nan || UNDEF;
+                    n += UNDEF ? 1 : 0;
+                } else {
+                    v[n++] = f;
+                }
+            }
+            if (n > 0 && !any_nan) { // NaN among the values: unspecified order in the reference, defined as NaN
+                const int rank = n / 2;
+                for (int i = 0; i < n; ++i) {
+                    int less = 0, equal = 0;
+                    for (int j = 0; j < n; ++j) {
+                        less += (v[j] < v[i]) ? 1 : 0;
+                        equal += (v[j] == v[i]) ? 1 : 0;
+                    }
+                    if (less <= rank && rank < less + equal) {
+                        r = v[i];
+                        break;
+                    }
+                }
+            }
+        } else {
+            for (int k = s0; k < s1; ++k) {
+                const float f = fwd_load(src + P.segIdx[k], P.bad, has_bad);
+                if (isnan(f))
+                    any_nan = any_nan || UNDEF;
+                else
+                    ++n;
+            }
+            if (n > 0 && !any_nan) {
+                // -0.0 and +0.0 compare equal in nth_element but differ as bit patterns: they are made one key (+0.0's)
+                int rank = n / 2;
+                unsigned prefix = 0, mask = 0;
+                for (int bit = 31; bit >= 0; --bit) {
+                    const unsigned m2 = mask | (1u << bit);
+                    int zeros = 0;
+                    for (int k = s0; k < s1; ++k) {
+                        float f = fwd_load(src + P.segIdx[k], P.bad, has_bad);
+                        if (isnan(f))
+                            continue;
+                        if (f == 0.f)
+                            f = 0.f;
+                        const unsigned key = ordered_bits(f);
+                        zeros += ((key & m2) == prefix) ? 1 : 0; // matches the prefix so far and has a 0 in this bit
+                    }
+                    if (rank >= zeros) {
+                        rank -= zeros;
+                        prefix |= 1u << bit;
+                    }
+                    mask = m2;
+                }
+                const unsigned b = (prefix & 0x80000000u) ? (prefix & 0x7fffffffu) : ~prefix;
+                r = __uint_as_float(b);
+                // the reference returns one of the pushed values: give -0.0 back if the rank falls on a -0.0 and no +0.0 was pushed
+                if (r == 0.f) {
+                    bool pos = false, neg = false;
+                    for (int k = s0; k < s1; ++k) {
+                        const float f = fwd_load(src + P.segIdx[k], P.bad, has_bad);
+                        if (f == 0.f) {
+                            pos = pos || !signbit(f);
+                            neg = neg || signbit(f);
+                        }
+                    }
+                    r = (neg && !pos) ? -0.f : 0.f;
+                }
+            }
+        }
+        if (has_fill && isnan(r))
+            r = P.fill;
+        __stcs(P.out + static_cast<size_t>(z) * P.nout + o, r);
+    }
+}
+
+// Median of long segments: one warp per target cell.  The level's values are gathered once, lanes striding over the segment, into
+// the warp's slice of shared memory (segments beyond MED_WARP_CAP values are swept from global memory instead); the element of rank
+// n/2 is found by the same most-significant-bit-first radix selection as above, each of the 32 passes counting with all lanes and
+// one warp reduction.
+constexpr int MED_WARP_CAP = 1024;
+template <bool UNDEF>
+__global__ void __launch_bounds__(256) fwd_median_warp_kernel(const FwdParams P)
+{
+    __shared__ float buf[8][MED_WARP_CAP];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t o = blockIdx.x * 8ull + warp;
+    if (o >= P.nout)
+        return;
+    const int z0 = blockIdx.y * P.zchunk, z1 = min(P.nz, z0 + P.zchunk);
+    const int s0 = P.segStart[o], s1 = P.segStart[o + 1];
+    const int len = s1 - s0;
+    const bool staged = len <= MED_WARP_CAP;
+    const bool has_bad = !isnan(P.bad), has_fill = !isnan(P.fill);
+    float* mine = buf[warp];
+    for (int z = z0; z < z1; ++z) {
+        const float* src = P.in + static_cast<size_t>(z) * P.inLayer;
+        int n = 0, nans = 0, negz = 0, posz = 0;
+        for (int k = lane; k < len; k += 32) {
+            float f = fwd_load(src + P.segIdx[s0 + k], P.bad, has_bad);
+            if (isnan(f)) {
+                ++nans;
+            } else {
+                ++n;
+                if (f == 0.f) {
+                    negz += signbit(f) ? 1 : 0;
+                    posz += signbit(f) ? 0 : 1;
+                    f = 0.f; // -0.0 and +0.0 are one key
+                }
+            }
+            if (staged)
+                mine[k] = f;
+        }
+#pragma unroll
+        for (int sft = 16; sft > 0; sft >>= 1) {
+            n += __shfl_xor_sync(0xffffffffu, n, sft);
+            nans += __shfl_xor_sync(0xffffffffu, nans, sft);
+            negz += __shfl_xor_sync(0xffffffffu, negz, sft);
+            posz += __shfl_xor_sync(0xffffffffu, posz, sft);
+        }
+        __syncwarp();
+        float r = nan_f();
+        if (n > 0 && !(UNDEF && nans > 0)) { // NaN among the values (undef flavour): unspecified order in the reference, NaN here
+            int rank = n / 2;
+            unsigned prefix = 0, mask = 0;
+            for (int bit = 31; bit >= 0; --bit) {
+                const unsigned m2 = mask | (1u << bit);
+                int zeros = 0;
+                for (int k = lane; k < len; k += 32) {
+                    float f = staged ? mine[k] : fwd_load(src + P.segIdx[s0 + k], P.bad, has_bad);
+                    if (isnan(f))
+                        continue;
+                    if (f == 0.f)
+                        f = 0.f;
+                    zeros += ((ordered_bits(f) & m2) == prefix) ? 1 : 0;
+                }
+#pragma unroll
+                for (int sft = 16; sft > 0; sft >>= 1)
+                    zeros += __shfl_xor_sync(0xffffffffu, zeros, sft);
+                if (rank >= zeros) {
+                    rank -= zeros;
+                    prefix |= 1u << bit;
+                }
+                mask = m2;
+            }
+            r = __uint_as_float((prefix & 0x80000000u) ? (prefix & 0x7fffffffu) : ~prefix);
+            if (r == 0.f)
+                r = (negz > 0 && posz == 0) ? -0.f : 0.f;
+        }
+        __syncwarp();
+        if (lane == 0) {
+            if (has_fill && isnan(r))
+                r = P.fill;
+            __stcs(P.out + static_cast<size_t>(z) * P.nout + o, r);
+        }
+    }
+}
+
 static int fwd_zchunk(size_t nout, int nz, bool compat)
 {
     if (compat)
@@ -229,7 +538,8 @@ static int fwd_zchunk(size_t nout, int nz, bool compat)
     const size_t want = static_cast<size_t>(sm_count()) * 16;
     if (blocks >= want || nz <= 1)
         return nz;
-    size_t chunks = std::min<size_t>((want + blocks - 1) / blocks, static_cast<size_t>(nz));
+    // few target cells: split the levels over blockIdx.y until the machine is full (level blocks of the kernels shrink with it)
+    const size_t chunks = std::min<size_t>((want + blocks - 1) / blocks, static_cast<size_t>(nz));
     return static_cast<int>((nz + chunks - 1) / chunks);
 }
 
@@ -385,8 +695,47 @@ int fimexcu_forward_apply_dev_f(const fimexcu_forward* f, const float* d_in, siz
     P.level_compat = level_compat != 0;
     P.bad = badIn;
     P.fill = fillOut;
+    cudaStream_t st = as_stream(stream);
+    if (P.level_compat) {
+        // the reference's level-0 quirk: one aggregation, nz stores (fwd_apply_kernel carries the value from level to level)
+        const dim3 grid(blocks_for(nout, 256), 1);
+        fwd_apply_kernel<<<grid, 256, 0, st>>>(P);
+        FXCU_CUDA(cudaGetLastError());
+        return FIMEXCU_OK;
+    }
+    constexpr int ZB = 8;
     const dim3 grid(blocks_for(nout, 256), static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
-    fwd_apply_kernel<<<grid, 256, 0, as_stream(stream)>>>(P);
+    const double mean_len = static_cast<double>(f->nvalid) / static_cast<double>(nout);
+    if (f->kind == 2 && mean_len >= 24.) {
+        const dim3 gw(blocks_for(nout, 8), grid.y);
+        if (f->undef)
+            fwd_median_warp_kernel<true><<<gw, 256, 0, st>>>(P);
+        else
+            fwd_median_warp_kernel<false><<<gw, 256, 0, st>>>(P);
+    } else if (f->kind == 2) {
+        const dim3 g2(blocks_for(nout, 128), grid.y);
+        if (f->undef)
+            fwd_median_kernel<true><<<g2, 128, 0, st>>>(P);
+        else
+            fwd_median_kernel<false><<<g2, 128, 0, st>>>(P);
+    } else if ((f->kind == 3 || f->kind == 4) && !f->undef && mean_len >= 48.) {
+        const dim3 gw(blocks_for(nout * 32, 256), grid.y);
+        if (f->kind == 3)
+            fwd_minmax_warp_kernel<true, 4><<<gw, 256, 0, st>>>(P);
+        else
+            fwd_minmax_warp_kernel<false, 4><<<gw, 256, 0, st>>>(P);
+    } else {
+        switch (f->kind * 2 + (f->undef ? 1 : 0)) {
+        case 0: fwd_reduce_kernel<0, false, ZB><<<grid, 256, 0, st>>>(P); break;
+        case 1: fwd_reduce_kernel<0, true, ZB><<<grid, 256, 0, st>>>(P); break;
+        case 2: fwd_reduce_kernel<1, false, ZB><<<grid, 256, 0, st>>>(P); break;
+        case 3: fwd_reduce_kernel<1, true, ZB><<<grid, 256, 0, st>>>(P); break;
+        case 6: fwd_reduce_kernel<3, false, ZB><<<grid, 256, 0, st>>>(P); break;
+        case 7: fwd_reduce_kernel<3, true, ZB><<<grid, 256, 0, st>>>(P); break;
+        case 8: fwd_reduce_kernel<4, false, ZB><<<grid, 256, 0, st>>>(P); break;
+        default: fwd_reduce_kernel<4, true, ZB><<<grid, 256, 0, st>>>(P); break;
+        }
+    }
     FXCU_CUDA(cudaGetLastError());
     return FIMEXCU_OK;
 }

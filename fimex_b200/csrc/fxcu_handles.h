@@ -17,6 +17,7 @@ struct fimexcu_cache {
     size_t inX = 0, inY = 0, outX = 0, outY = 0; // inX/inY: the (possibly reduced) source window
     bool reduced = false;
     size_t xMin = 0, yMin = 0;
+    bool fast_bicubic = false; // fimexcu_cache_set_fast_bicubic: f32 FMA arithmetic in the staged bicubic kernel (1e-5 contract) instead of the reference's rounding chain
     fxcu::DevBuf off;    // int32 [outX*outY]
     fxcu::DevBuf wx, wy; // f32 (bilinear) or f64 (bicubic) [outX*outY]
     unsigned tiles_with_data = 0, tiles_fitting = 0; // 32 x 8 target tiles: with defined cells / whose footprint fits the TMA box

@@ -137,6 +137,10 @@ class CachedInterpolationInterface:
         assert newSize.value == out.size
         return out
 
+    def setFastBicubic(self, on=True):
+        """opt-in f32 FMA arithmetic of the staged bicubic kernel (1e-5 contract instead of bit-exact); see fimexcu_cache_set_fast_bicubic"""
+        _lib.check(lib.fimexcu_cache_set_fast_bicubic(self._h, 1 if on else 0), "set_fast_bicubic")
+
     def replicate(self, devices):
         """copy the tables to the listed device ordinals: host threads bound to different GPUs then share this one object, as the
         reference's OpenMP writer threads share one CachedInterpolation (src/io/netcdf/NetCDF_CDMWriter.cc:599-618)"""

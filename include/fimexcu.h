@@ -159,6 +159,13 @@ void fimexcu_cache_destroy(fimexcu_cache* c);
  * bound to different GPUs share one handle.  Devices already covered are skipped; the copies die with the handle.  Not thread
  * safe against concurrent applies on the same handle: replicate once, right after the cache is built. */
 int fimexcu_cache_replicate(fimexcu_cache* c, int n_devices, const int* device_ids);
+/* Opt-in arithmetic for bicubic caches on device-resident padded slabs (the staged kernel): on = 1 computes the 4 x 4 convolution
+ * with the weights narrowed to f32 and 20 fused multiply-adds per value instead of the reference's chain of 40 separately rounded
+ * f64 operations with an f32 accumulator (src/interpolation.c:388-406), which the FP64 pipe bounds at 40 % of the HBM roofline
+ * (the bit-exact form runs at 23 %, this one at ~40 %).
+ * Results then agree with the reference within BASELINE.json's 1e-5 (relative to the largest tap) instead of bit for bit;
+ * undefined masks stay identical.  Default 0 (bit-exact).  No counterpart in the reference. */
+int fimexcu_cache_set_fast_bicubic(fimexcu_cache* c, int on);
 /* A/B switch between the staged (TMA) and the direct-gather apply kernels, for measurements and tests: 1 = staged kernels where they
  * apply (default), 0 = direct kernels only, -1 = back to the default (which the environment variable FIMEXCU_NO_TMA, read once per
  * process, can set to 0).  No counterpart in the reference. */

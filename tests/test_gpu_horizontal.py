@@ -323,6 +323,48 @@ def test_output_window_equals_slice_of_full_result(fx, method):
         ci.sliceOutput(full, 0, out_x + 1, 0, 1)
 
 
+@pytest.mark.parametrize("shape", [(300, 200, 1400, 900, 9), (128, 96, 700, 500, 65)])
+@pytest.mark.parametrize("special", [False, True])
+def test_bicubic_staged_kernel_padded_layout(fx, oracle, shape, special):
+    """bicubic on padded device slabs: bit-exact (direct kernel) incl. the fused bad/fill conversions; the opt-in f32 variant (staged
+    kernel, 32 x 20 TMA box, tiles that do not fit included): same undefined mask, values within 1e-5 of the largest tap"""
+    import torch
+    in_x, in_y, out_x, out_y, nz = shape
+    rng = np.random.default_rng(sum(shape) + 1)
+    gx, gy = np.meshgrid(np.arange(out_x), np.arange(out_y))
+    px = -3.0 + gx * ((in_x + 5.0) / out_x) + 0.11 * gy * (in_x / out_x)
+    py = -2.5 + gy * ((in_y + 4.0) / out_y) - 0.07 * gx * (in_y / out_y)
+    k = out_y // 2
+    px[k:k + 9] = rng.uniform(-2, in_x + 1, px[k:k + 9].shape)
+    py[k:k + 9] = rng.uniform(-2, in_y + 1, py[k:k + 9].shape)
+    fld = rng.normal(280, 10, size=(nz, in_y, in_x)).astype(np.float32)
+    bad, fill = np.float32(-999.0), np.float32(1e20)
+    fld[rng.random(fld.shape) < 0.01] = bad if special else np.nan
+    clean = fld.copy()
+    if special:
+        oracle.orc_bad2nanf(fp(clean), clean.size, bad)
+    want, info = ol.o_cached_apply(ol.BICUBIC, px, py, in_x, in_y, out_x, out_y, clean)
+    wf = want.copy()
+    if special:
+        oracle.orc_nanf2bad(fp(wf), wf.size, fill)
+    ci = fx.createCachedInterpolation("x", "y", ol.BICUBIC, px, py, in_x, in_y, out_x, out_y)
+    sub = torch.from_numpy(ci.reduceInput(fld, in_x, in_y)).cuda()
+    kw = dict(badValue=float(bad), fillValue=float(fill)) if special else {}
+    pin = ci.toPadded(sub)
+    out = ci.interpolateValuesPadded(pin, **kw)
+    torch.cuda.synchronize()
+    assert _eq(out[:, :, :out_x].cpu().numpy(), wf)
+    assert (~np.isnan(want)).mean() > 0.5
+    ci.setFastBicubic(True)
+    fast = ci.interpolateValuesPadded(pin)[:, :, :out_x].cpu().numpy() if not special else None
+    ci.setFastBicubic(False)
+    if fast is not None:
+        assert np.array_equal(np.isnan(fast), np.isnan(want))
+        ok = ~np.isnan(want)
+        assert np.abs(fast[ok] - want[ok]).max() <= 1e-5 * np.nanmax(np.abs(clean))
+        assert not np.array_equal(fast[ok], want[ok])  # it really is the other arithmetic
+
+
 def test_nearest_staged_kernel_padded_layout(fx, oracle):
     """nearest-neighbour tables through the TMA-staged kernel (padded layout) and the direct kernel (dense layout)"""
     import torch
