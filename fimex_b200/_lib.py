@@ -37,6 +37,9 @@ SIGNATURES = {
     "fimexcu_dev_free": (None, [vp]),
     "fimexcu_memcpy_h2d": (C.c_int, [vp, vp, sz]),
     "fimexcu_memcpy_d2h": (C.c_int, [vp, vp, sz]),
+    "fimexcu_memcpy_d2d": (C.c_int, [vp, vp, sz]),
+    "fimexcu_memcpy2d_h2d": (C.c_int, [vp, sz, vp, sz, sz, sz, sz, sz]),
+    "fimexcu_memcpy2d_d2h": (C.c_int, [vp, sz, vp, sz, sz, sz, sz, sz]),
     "fimexcu_synchronize": (C.c_int, []),
     "fimexcu_cache_create": (vp, [C.c_int, vp, vp, sz, sz, sz, sz]),
     "fimexcu_cache_create_dev": (vp, [C.c_int, vp, vp, sz, sz, sz, sz, vp]),

@@ -74,7 +74,7 @@ def build_host_selftest(force=False):
     """g++ build of the C++ reference-side glue self-test (fimex_b200/host); returns the binary path."""
     host = os.path.join(HERE, "host")
     exe = os.path.join(host, "host_selftest")
-    deps = [os.path.join(host, f) for f in ("host_selftest.cc", "CudaCachedInterpolation.h", "CudaInterpolatorProcess2d.h", "fimex_stand_in.h")] + [LIB]
+    deps = [os.path.join(host, f) for f in ("host_selftest.cc", "CudaCachedInterpolation.h", "CudaInterpolatorProcess2d.h", "CudaSlab.h", "fimex_stand_in.h")] + [LIB]
     if force or _stale(exe, deps):
         cmd = ["g++", "-std=c++17", "-O2", "-pthread", "-o", exe, os.path.join(host, "host_selftest.cc"), "-L" + HERE, "-lfimexcu", "-Wl,-rpath,$ORIGIN/.."]
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -274,10 +274,43 @@ int fimexcu_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes)
     return FIMEXCU_OK;
 }
 
+int fimexcu_memcpy_d2d(void* dst_dev, const void* src_dev, size_t bytes)
+{
+    FXCU_CUDA(cudaMemcpy(dst_dev, src_dev, bytes, cudaMemcpyDeviceToDevice));
+    return FIMEXCU_OK;
+}
+
 int fimexcu_memcpy_d2h(void* dst_host, const void* src_dev, size_t bytes)
 {
     FXCU_CUDA(cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost));
     return FIMEXCU_OK;
+}
+
+// dense host [nz][ny][row] <-> pitched device slab: one 2-D copy when the levels follow each other at the row pitch, else one per level
+static int copy_slab(void* dst, size_t dpitch, size_t dlevel, const void* src, size_t spitch, size_t slevel, size_t width, size_t ny, size_t nz,
+                     cudaMemcpyKind kind)
+{
+    if (width == 0 || ny == 0 || nz == 0)
+        return FIMEXCU_OK;
+    if (dlevel == dpitch * ny && slevel == spitch * ny) {
+        FXCU_CUDA(cudaMemcpy2D(dst, dpitch, src, spitch, width, ny * nz, kind));
+        return FIMEXCU_OK;
+    }
+    for (size_t z = 0; z < nz; ++z)
+        FXCU_CUDA(cudaMemcpy2D(static_cast<char*>(dst) + z * dlevel, dpitch, static_cast<const char*>(src) + z * slevel, spitch, width, ny, kind));
+    return FIMEXCU_OK;
+}
+
+int fimexcu_memcpy2d_h2d(void* dst_dev, size_t dst_pitch_bytes, const void* src_host, size_t src_pitch_bytes, size_t width_bytes, size_t ny, size_t nz,
+                         size_t dst_level_bytes)
+{
+    return copy_slab(dst_dev, dst_pitch_bytes, dst_level_bytes, src_host, src_pitch_bytes, src_pitch_bytes * ny, width_bytes, ny, nz, cudaMemcpyHostToDevice);
+}
+
+int fimexcu_memcpy2d_d2h(void* dst_host, size_t dst_pitch_bytes, const void* src_dev, size_t src_pitch_bytes, size_t width_bytes, size_t ny, size_t nz,
+                         size_t src_level_bytes)
+{
+    return copy_slab(dst_host, dst_pitch_bytes, dst_pitch_bytes * ny, src_dev, src_pitch_bytes, src_level_bytes, width_bytes, ny, nz, cudaMemcpyDeviceToHost);
 }
 
 int fimexcu_synchronize(void)

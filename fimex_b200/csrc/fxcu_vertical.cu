@@ -76,11 +76,22 @@ __device__ __forceinline__ bool log_weight_fast(double a, double b, double x, fl
         return false;
     const double s1 = u1 * rcp_newton(v1, false), s2 = u2 * rcp_newton(v2, false);
     const double z1 = s1 * s1, z2 = s2 * s2;
-    double p1 = c_inv_odd[11], p2 = c_inv_odd[11]; // operands straight from the constant bank: no immediates to materialise
+    double p1, p2; // operands straight from the constant bank: no immediates to materialise
+    if (z1 < 0.004 && z2 < 0.004) {
+        // brackets within a factor 1.13 (the bulk of a 65-level hybrid column): z^7 / 15 < 1.1e-18, seven terms are as exact as twelve
+        p1 = p2 = c_inv_odd[6];
 #pragma unroll
-    for (int i = 10; i >= 0; --i) {
-        p1 = __fma_rn(p1, z1, c_inv_odd[i]);
-        p2 = __fma_rn(p2, z2, c_inv_odd[i]);
+        for (int i = 5; i >= 0; --i) {
+            p1 = __fma_rn(p1, z1, c_inv_odd[i]);
+            p2 = __fma_rn(p2, z2, c_inv_odd[i]);
+        }
+    } else {
+        p1 = p2 = c_inv_odd[11];
+#pragma unroll
+        for (int i = 10; i >= 0; --i) {
+            p1 = __fma_rn(p1, z1, c_inv_odd[i]);
+            p2 = __fma_rn(p2, z2, c_inv_odd[i]);
+        }
     }
     const double num = (u1 * v2) * p1, den = (v1 * u2) * p2; // f = num / den; |den| > 0 because a != b
     if (!(fabs(den) > 1e-280 && fabs(den) < 1e280 && fabs(num) < 1e280))
@@ -931,7 +942,9 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
     unsigned short* s_tab = reinterpret_cast<unsigned short*>(s_xf + nzo + (nzo & 1));
     float* s_A = reinterpret_cast<float*>(s_tab + 2 * ((nzo * nbins + 1) / 2)) + threadIdx.x; // [JC][HT]
     float* s_B = s_A + JC * HT;                                                                // [JC][HT]
-    unsigned short* s_code = reinterpret_cast<unsigned short*>(s_B - threadIdx.x + JC * HT) + threadIdx.x; // [JC][HT]
+    float* s_ca = s_B + JC * HT;                                                               // [JC][HT] coordinate of `first`
+    float* s_cb = s_ca + JC * HT;                                                              // [JC][HT] coordinate of `second`
+    unsigned short* s_code = reinterpret_cast<unsigned short*>(s_cb - threadIdx.x + JC * HT) + threadIdx.x; // [JC][HT]
     for (int k = threadIdx.x; k < nzi; k += HT)
         s_apb[k] = make_double2(P.ap[k], P.b[k]);
     for (int k = threadIdx.x; k < nzo; k += HT) {
@@ -1003,6 +1016,10 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
                 const unsigned first = code & 0x1fffu;
                 const float* pa = din + static_cast<size_t>(first) * P.nInner;
                 const float* pb = (code & CODE_UP) ? pa + P.nInner : pa - P.nInner;
+                // the coordinates of (first, second) are at hand: interior step -> (plo, phi) in walk order, far end -> the column's last two
+                const bool far_end = first == static_cast<unsigned>(nzi - 1) && !(code & CODE_UP) && n == nzi;
+                s_ca[u * HT] = far_end ? E.cl : ((code & CODE_UP) ? plo : phi);
+                s_cb[u * HT] = far_end ? E.cl2 : ((code & CODE_UP) ? phi : plo);
                 asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sA + u * HT * 4), "l"(pa) : "memory");
                 asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sB + u * HT * 4), "l"(pb) : "memory");
             }
@@ -1015,8 +1032,7 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
             const unsigned code = s_code[u * HT];
             float r = nan_f();
             if (code & CODE_BLEND) {
-                const int first = static_cast<int>(code & 0x1fffu), second = (code & CODE_UP) ? first + 1 : first - 1;
-                r = blend_levels(C, s_A[u * HT], s_B[u * HT], hc(first), hc(second), s_xd[jj], s_xl[jj]);
+                r = blend_levels(C, s_A[u * HT], s_B[u * HT], s_ca[u * HT], s_cb[u * HT], s_xd[jj], s_xl[jj]);
             } else if (code & CODE_SLOW) {
                 r = sweep_slow(C, hc, nzi, dir, din, s_xd[jj], s_xl[jj]);
             }
@@ -1378,9 +1394,9 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
     const int nbins = static_cast<int>(std::min<size_t>(512, std::max<size_t>(8, 2048 / std::max<size_t>(nzo, 1))));
     const size_t tab_words = (nzo * nbins + 1) / 2;
     const size_t tab_smem = (2 * nzi + 2 * nzo) * sizeof(double) + (nzo + (nzo & 1)) * sizeof(float) + tab_words * 4 +
-                            JC * HT * (2 * sizeof(float) + sizeof(unsigned short));
+                            JC * HT * (4 * sizeof(float) + sizeof(unsigned short));
     const int init[2] = {0x7f800000, static_cast<int>(0x80800000u)}; // +inf / "-inf" in the ordered-int encoding
-    if (!no_table && ncol && nzo && nzi >= 1 && nzi < 8192 && nzo < 65535 && tab_smem <= 26 * 1024) {
+    if (!no_table && ncol && nzo && nzi >= 1 && nzi < 8192 && nzo < 65535 && tab_smem <= 28 * 1024) {
         // launch-wide table path: ps range -> monotonicity proof + table (device side, no host round trip) -> consumer kernel
         DevBuf scratch;
         const size_t hdr_off = PS_HIST_BINS * sizeof(unsigned), tab_off = hdr_off + sizeof(HybridTableHeader);

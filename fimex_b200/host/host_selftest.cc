@@ -4,6 +4,7 @@
 //   file layout (little endian): int32 method, inX, inY, outX, outY, nz; f64 px[out], py[out]; f32 u[nz*in], v[nz*in]; f64 matrix[out*3]
 #include "CudaCachedInterpolation.h"
 #include "CudaInterpolatorProcess2d.h"
+#include "CudaSlab.h"
 
 #include <cstdint>
 #include <cstdio>
@@ -123,8 +124,75 @@ static int threads_mode(int nthreads, const char* in_path, const char* out_path)
     return 0;
 }
 
+// host_selftest chain case.bin result.bin -- BASELINE configs[4] as a device-resident reader chain (CudaSlab.h): the ensemble field
+// (hybrid, member, y, x) arrives as a PACKED short slab, is unpacked, regridded bilinearly (staged kernel, padded layout), the
+// surface pressure is regridded the same way, the vertical interpolation to fixed pressure levels runs with the pressure formed from
+// the REGRIDDED ps, the wind pair goes through the fused rotation -- and only the final results come back to the host.
+//   case: int32 method(vertical), inX, inY, outX, outY, nLev, nMem, nOut; f64 px[out], py[out]; i16 field[nLev*nMem*in]; f64 fill;
+//         f32 ps[nMem*in]; f64 ap[nLev], b[nLev], levels[nOut]; f64 matrix[out*3]
+//   result: f32 vertical[nOut*nMem*out]; f32 u[nMem*out], v[nMem*out] (the rotated regridded ps / first level pair, as a K7 check)
+static int chain_mode(const char* in_path, const char* out_path)
+{
+    FILE* f = fopen(in_path, "rb");
+    if (!f)
+        return 2;
+    int32_t hdr[8];
+    if (!read_all(f, hdr, sizeof(hdr)))
+        return 2;
+    const int vmethod = hdr[0];
+    const size_t inX = hdr[1], inY = hdr[2], outX = hdr[3], outY = hdr[4], nLev = hdr[5], nMem = hdr[6], nOut = hdr[7];
+    const size_t nout = outX * outY, nin = inX * inY;
+    auto px = make_shared_array<double>(nout), py = make_shared_array<double>(nout);
+    auto raw = make_shared_array<short>(nLev * nMem * nin);
+    auto ps = make_shared_array<float>(nMem * nin);
+    double fill = 0;
+    std::vector<double> ap(nLev), b(nLev), levels(nOut);
+    auto m = std::make_shared<reproject::Matrix>(static_cast<int>(outX), static_cast<int>(outY));
+    if (!read_all(f, px.get(), nout * 8) || !read_all(f, py.get(), nout * 8) || !read_all(f, raw.get(), nLev * nMem * nin * 2) || !read_all(f, &fill, 8) ||
+        !read_all(f, ps.get(), nMem * nin * 4) || !read_all(f, ap.data(), nLev * 8) || !read_all(f, b.data(), nLev * 8) ||
+        !read_all(f, levels.data(), nOut * 8) || !read_all(f, m->mtx(), nout * 3 * 8))
+        return 2;
+    fclose(f);
+    try {
+        CudaCachedInterpolation ci("x", "y", FIMEXCU_INTERPOL_BILINEAR, px, py, inX, inY, outX, outY);
+        if (ci.getInX() != inX || ci.getInY() != inY)
+            return 4; // the driver passes full-window tables
+        size_t ip, il, op, ol;
+        fimexcu_cache_padded_layout(ci.handle(), &ip, &il, &op, &ol);
+        // reader side: the packed field crosses PCIe as shorts, straight into the padded layout
+        CudaSlab_p packed = CudaSlab::upload(raw, nLev * nMem, inY, inX, ip, il);
+        CudaSlab_p field = unpackSlab(*packed, fill);
+        packed.reset();
+        CudaSlab_p psIn = uploadInterpolationInput(ci, ps, nMem * nin);
+        // horizontal, then vertical with the pressure from the regridded ps (fimex.cc:862-863)
+        CudaSlab_p hField = interpolateSlab(ci, *field);
+        CudaSlab_p hPs = interpolateSlab(ci, *psIn);
+        CudaSlab_p vert = cudaVerticalToFixedLevels(vmethod, *hField, nLev, ap, b, *hPs, 0.01, levels);
+        // fused vector pass on two device slabs (ps and the first level of the field stand in for a wind pair)
+        CudaCachedVectorReprojection cvr(m);
+        CudaSlab_p firstLevel = CudaSlab::allocate(CudaSlab::FLOAT, nMem, inY, inX, ip, il);
+        if (fimexcu_memcpy_d2d(firstLevel->devicePtr(), field->devicePtr(), nMem * il * sizeof(float)) != FIMEXCU_OK)
+            return 5;
+        auto uv = interpolateVectorSlabs(ci, cvr, *psIn, *firstLevel);
+        // writer side
+        shared_array<float> hv = vert->asFloat(), hu = uv.first->asFloat(), hvv = uv.second->asFloat();
+        FILE* o = fopen(out_path, "wb");
+        fwrite(hv.get(), 4, vert->size(), o);
+        fwrite(hu.get(), 4, uv.first->size(), o);
+        fwrite(hvv.get(), 4, uv.second->size(), o);
+        fclose(o);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "exception: %s\n", e.what());
+        return 6;
+    }
+    printf("host_selftest chain ok\n");
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
+    if (argc == 4 && std::strcmp(argv[1], "chain") == 0)
+        return chain_mode(argv[2], argv[3]);
     if (argc == 4 && std::strcmp(argv[1], "fill") == 0)
         return fill_mode(argv[2], argv[3]);
     if (argc == 5 && std::strcmp(argv[1], "threads") == 0)

@@ -87,6 +87,13 @@ void* fimexcu_dev_alloc(size_t bytes);
 void fimexcu_dev_free(void* p);
 int fimexcu_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes);
 int fimexcu_memcpy_d2h(void* dst_host, const void* src_dev, size_t bytes);
+int fimexcu_memcpy_d2d(void* dst_dev, const void* src_dev, size_t bytes);
+/* dense host slab [nz][ny][width] <-> device slab with a row pitch and a level stride (bytes): how a slab enters / leaves the padded
+ * device layout of fimexcu_cache_padded_layout at the ends of a device-resident reader chain (fimex_b200/host/CudaSlab.h) */
+int fimexcu_memcpy2d_h2d(void* dst_dev, size_t dst_pitch_bytes, const void* src_host, size_t src_pitch_bytes, size_t width_bytes, size_t ny, size_t nz,
+                         size_t dst_level_bytes);
+int fimexcu_memcpy2d_d2h(void* dst_host, size_t dst_pitch_bytes, const void* src_dev, size_t src_pitch_bytes, size_t width_bytes, size_t ny, size_t nz,
+                         size_t src_level_bytes);
 int fimexcu_synchronize(void);
 
 /* ------------------------------------------------------------------------------------------------

@@ -90,6 +90,72 @@ def test_cpp_glue_one_cache_many_writer_threads(tmp_path, method):
     assert len(set(dev.tolist())) == min(ndev, nthreads)  # every GPU of the box (up to the thread count) took part
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("vmethod", [ol.VINT_LIN, ol.VINT_LOG])
+def test_cpp_device_slab_chain(tmp_path, vmethod):
+    """fimex_b200/host/CudaSlab.h: BASELINE configs[4] as a device-resident reader chain -- packed short field up, unpack,
+    bilinear S->T (staged kernel, padded layout), ps the same way, hybrid -> pressure levels with the pressure from the REGRIDDED
+    ps, fused wind rotation, results down -- against the oracle chain, every value."""
+    import os as _os
+    rng = np.random.default_rng(50 + vmethod)
+    g = np.load(_os.path.join(ROOT, "tests", "golden", "reference_vertical.npz"))
+    ap, b = g["en_ap_pa"] * 0.01, g["en_b"]
+    nlev, nmem, in_x, in_y, out_x, out_y = 65, 2, 300, 200, 1400, 900   # 1232 target tiles: the staged kernels run
+    gx, gy = np.meshgrid(np.arange(out_x), np.arange(out_y))
+    px = -3.0 + gx * ((in_x + 5.0) / out_x) + 0.11 * gy * (in_x / out_x)
+    py = -2.5 + gy * ((in_y + 4.0) / out_y) - 0.07 * gx * (in_y / out_y)
+    fill = -32767.0
+    raw = rng.integers(-3000, 3000, (nlev * nmem, in_y, in_x)).astype(np.int16)
+    raw[rng.random(raw.shape) < 0.01] = int(fill)
+    ps = (101325 - 12 * rng.uniform(0, 2500, (nmem, in_y, in_x)) + rng.normal(0, 300, (nmem, in_y, in_x))).astype(np.float32)
+    levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50], dtype=np.float64)
+    ang = rng.uniform(-3, 3, out_x * out_y)
+    m3 = np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy()
+    case, res = tmp_path / "case.bin", tmp_path / "res.bin"
+    with open(case, "wb") as f:
+        f.write(np.array([vmethod, in_x, in_y, out_x, out_y, nlev, nmem, levels.size], dtype=np.int32).tobytes())
+        f.write(px.tobytes()); f.write(py.tobytes()); f.write(raw.tobytes()); f.write(np.array([fill]).tobytes())
+        f.write(ps.tobytes()); f.write(ap.astype(np.float64).tobytes()); f.write(b.astype(np.float64).tobytes()); f.write(levels.tobytes())
+        f.write(m3.tobytes())
+    r = subprocess.run([EXE, "chain", str(case), str(res)], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    out = np.fromfile(res, dtype=np.float32)
+    ncol = nmem * out_y * out_x
+    got_v = out[:levels.size * ncol].reshape(levels.size, ncol)
+    got_u = out[levels.size * ncol:levels.size * ncol + ncol].reshape(nmem, out_y, out_x)
+    got_w = out[levels.size * ncol + ncol:].reshape(nmem, out_y, out_x)
+    # oracle chain: unpack (asFloat + bad2nan), bilinear, pressure from the regridded ps, vertical
+    o = ol.oracle()
+    fld = np.empty(raw.shape, np.float32)
+    o.orc_i16_to_interpolation_array(raw.ctypes.data, raw.size, fill, fp(fld))
+    h_f, _ = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, fld)
+    h_ps, _ = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, ps)
+    p = np.ascontiguousarray((ap[:, None] + b[:, None] * (h_ps.reshape(1, ncol).astype(np.float64) * 0.01)).astype(np.float32))
+    want = np.empty((levels.size, ncol), np.float32)
+    hf2 = np.ascontiguousarray(h_f.reshape(nlev, ncol))
+    assert o.orc_vertical_interpolate_f(vmethod, fp(hf2), fp(p), nlev, ncol, dp(levels), None, levels.size, None, None, float("nan"), float("nan"),
+                                        fp(want)) == 1
+    assert np.array_equal(np.isnan(got_v), np.isnan(want))
+    k = ~np.isnan(want)
+    if vmethod == ol.VINT_LIN:
+        assert np.array_equal(got_v[k], want[k])
+    else:
+        assert (np.abs(got_v[k] - want[k]) <= 1e-5 * np.abs(want[k])).all() and (got_v[k] == want[k]).mean() > 0.999
+    wu, wv = h_ps.copy(), np.ascontiguousarray(h_f[:nmem])
+    o.orc_vector_reproject_values_by_matrix_f(dp(m3), out_x * out_y, fp(wu), fp(wv), nmem)
+    for gch, w in ((got_u, wu), (got_w, wv)):
+        assert np.array_equal(np.isnan(gch), np.isnan(w)) and np.array_equal(gch[~np.isnan(w)], w[~np.isnan(w)])
+
+
+def test_slab_glue_compiles_against_the_reference_headers():
+    inc = "/root/reference/include"
+    if not os.path.isdir(inc):
+        pytest.skip("reference headers not present")
+    r = subprocess.run(["g++", "-std=c++20", "-fsyntax-only", "-DFIMEXCU_WITH_FIMEX_HEADERS", "-I" + inc, "-x", "c++",
+                        os.path.join(ROOT, "fimex_b200", "host", "CudaSlab.h")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
 def test_process_glue_compiles_against_the_reference_headers():
     inc = "/root/reference/include"
     if not os.path.isdir(inc):
