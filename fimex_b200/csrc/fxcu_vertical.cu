@@ -72,7 +72,9 @@ __constant__ double c_inv_odd[12] = {1., 1. / 3, 1. / 5, 1. / 7, 1. / 9, 1. / 11
 __device__ __forceinline__ bool log_weight_fast(double a, double b, double x, float& f)
 {
     const double u1 = __dsub_rn(x, a), v1 = __dadd_rn(x, a), u2 = __dsub_rn(b, a), v2 = __dadd_rn(b, a);
-    if (!(fabs(u1) < 0.2 * v1 && fabs(u2) < 0.2 * v2 && v1 < 1e300 && v2 < 1e300 && a > 1e-300 && b > 1e-300))
+    // a and b were born as positive finite f32 (callers test a, b, x > 0), so only the level x can be out of the range in which the
+    // products below stay clear of f64 overflow and underflow: v1 < 1e100 bounds x; an infinite a or b fails the ratio tests
+    if (!(fabs(u1) < 0.2 * v1 && fabs(u2) < 0.2 * v2 && v1 < 1e100))
         return false;
     const double s1 = u1 * rcp_newton(v1, false), s2 = u2 * rcp_newton(v2, false);
     const double z1 = s1 * s1, z2 = s2 * s2;
@@ -94,13 +96,16 @@ __device__ __forceinline__ bool log_weight_fast(double a, double b, double x, fl
         }
     }
     const double num = (u1 * v2) * p1, den = (v1 * u2) * p2; // f = num / den; |den| > 0 because a != b
-    if (!(fabs(den) > 1e-280 && fabs(den) < 1e280 && fabs(num) < 1e280))
-        return false;
+    // magnitudes: |u|, v within [1e-45, 1e100] * f32 range, p within [1, 1.02]: |num|, |den| lie in [1e-90, 1e140], no range test needed
     const double ad = fabs(den);
-    double q = fabs(num) * rcp_newton(ad, true);
-    q = __fma_rn(__fma_rn(-ad, q, fabs(num)), rcp_newton(ad, false), q);
+    const double rd = rcp_newton(ad, true);
+    double q = fabs(num) * rd;
+    q = __fma_rn(__fma_rn(-ad, q, fabs(num)), rd, q); // one correction step with the residual
     // |log b - log a| = 2 |s2| p2 >= 2 |s2|; |log| < 105 for f32-born a, b and for a level within a factor 1.5 of them
-    const double tol = (1. + q) * 2e-14 / fabs(s2) + 1e-15 * q;
+    // the bound only has to be an upper one: the division by |s2| is a multiplication by a reciprocal rounded up by 1e-6
+    double rs2;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rs2) : "d"(fabs(s2)));
+    const double tol = (1. + q) * (2.0001e-14 * rs2) + 1e-15 * q;
     const float lo = __double2float_rn(q - tol), hi = __double2float_rn(q + tol);
     if (lo != hi)
         return false;
