@@ -44,10 +44,40 @@ struct VcoordParams {
     float* out;
 };
 
-__device__ __forceinline__ double standard_step(int post, double v)
+// Natural logarithm for the standard-atmosphere step, whose result is narrowed to f32 (the contract of that step is 2 f32 ulps:
+// the device's own log already differs from glibc's in the last f64 bit).  Table form: x = 2^e * m, m in [1, 2); c = the centre of
+// m's 1/128 interval, r = m/c - 1 (|r| < 2^-8), log x = e ln2 + log c + (r - r^2/2 + r^3/3 - r^4/4 + r^5/5), error < 1e-15: a table
+// look-up and 10 FP64 operations instead of the ~45 of log().  tab[i] = (1/c_i, log c_i), 128 entries in shared memory.
+// Zero, negative, subnormal, infinite and NaN arguments go to log().
+__device__ __forceinline__ void log_table_fill(double2* tab, int tid, int nthreads)
+{
+    for (int i = tid; i < 128; i += nthreads) {
+        const double c = 1.0 + (i + 0.5) / 128.0;
+        tab[i] = make_double2(1.0 / c, log(c));
+    }
+}
+__device__ __forceinline__ double log_table(const double2* tab, double x)
+{
+    const long long bits = __double_as_longlong(x);
+    const int ex = static_cast<int>(bits >> 52); // sign and biased exponent
+    if (ex <= 0 || ex >= 0x7ff)
+        return log(x);
+    const double m = __longlong_as_double((bits & 0x000fffffffffffffll) | 0x3ff0000000000000ll);
+    const double2 t = tab[static_cast<int>(bits >> 45) & 127];
+    const double r = __fma_rn(m, t.x, -1.0);
+    double p = __fma_rn(r, 0.2, -0.25);
+    p = __fma_rn(p, r, 1.0 / 3);
+    p = __fma_rn(p, r, -0.5);
+    p = __fma_rn(p * r, r, r);
+    return __fma_rn(static_cast<double>(ex - 1023), 0.693147180559945309417232, t.y + p);
+}
+
+__device__ __forceinline__ double standard_step(int post, double v, const double2* logtab = nullptr)
 {
     if (post == FIMEXCU_VPOST_STANDARD_ALTITUDE) { // mifi_barometric_height(n, 1013.25, p, 288.15, .)
         const double K = -BAROMETRIC_FACTOR * 288.15;
+        if (logtab) // log(v / 1013.25) = log v - log 1013.25
+            return __dmul_rn(K, log_table(logtab, v) - 6.920918265508418);
         return __dmul_rn(K, log(__ddiv_rn(v, 1013.25)));
     }
     if (post == FIMEXCU_VPOST_STANDARD_PRESSURE) { // mifi_barometric_pressure(n, 1013.25, h, 288.15, .)
@@ -61,11 +91,14 @@ __device__ __forceinline__ double standard_step(int post, double v)
 __global__ void __launch_bounds__(256) vcoord_levels_kernel(const VcoordParams P)
 {
     extern __shared__ double s_ab[]; // a[nz], b[nz]
+    __shared__ double2 s_log[128];
     const int nz = static_cast<int>(P.nz);
     for (int k = threadIdx.x; k < nz; k += 256) {
         s_ab[k] = P.a[k];
         s_ab[nz + k] = P.b ? P.b[k] : 0.;
     }
+    if (P.post == FIMEXCU_VPOST_STANDARD_ALTITUDE)
+        log_table_fill(s_log, threadIdx.x, 256);
     __syncthreads();
     const size_t ncol = P.nOuter * P.nInner;
     const size_t cidx = blockIdx.x * 256ull + threadIdx.x;
@@ -102,7 +135,7 @@ __global__ void __launch_bounds__(256) vcoord_levels_kernel(const VcoordParams P
             break;
         }
         }
-        v = standard_step(P.post, v);
+        v = standard_step(P.post, v, s_log);
         if (P.topo)
             v = __dadd_rn(v, tp);
         __stcs(po, __double2float_rn(v));
