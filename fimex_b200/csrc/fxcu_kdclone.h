@@ -22,10 +22,13 @@
 #include <cmath>
 #include <cstdint>
 #include <future>
+#include <limits>
 #include <mutex>
 #include <string>
 #include <utility>
 #include <vector>
+
+#include "fxcu_hostpar.h"
 
 namespace fxcu {
 namespace kdclone {
@@ -86,9 +89,42 @@ struct Builder {
             error = what;
     }
 
-    // :1103-1112 for all three dimensions in one sweep (each dimension's result is what the reference's separate sweep gives)
+    // :1103-1112 for all three dimensions in one sweep (each dimension's result is what the reference's separate sweep gives).
+    // The sequential rule "start from entry 0, replace on v < min / v > max" means: NaN if entry 0 is NaN (no comparison ever
+    // succeeds), else the extreme of the non-NaN entries -- which is what the chunked form computes for large ranges.
     void minmax3(size_t first, size_t count, double mn[3], double mx[3]) const
     {
+        if (count >= (size_t(1) << 19) && parDepth > 0) {
+            const size_t parts = 16, step = (count + parts - 1) / parts;
+            double pmn[16][3], pmx[16][3];
+            parallel_ranges(parts, 1, [&](size_t a, size_t b) {
+                for (size_t c = a; c < b; ++c) {
+                    const size_t lo = first + c * step, hi = std::min(first + count, lo + step);
+                    for (int d = 0; d < 3; ++d) {
+                        pmn[c][d] = std::numeric_limits<double>::infinity();
+                        pmx[c][d] = -std::numeric_limits<double>::infinity();
+                    }
+                    for (size_t i = lo; i < hi; ++i)
+                        for (int d = 0; d < 3; ++d) {
+                            const double v = at(i, d);
+                            if (v < pmn[c][d])
+                                pmn[c][d] = v;
+                            if (v > pmx[c][d])
+                                pmx[c][d] = v;
+                        }
+                }
+            });
+            for (int d = 0; d < 3; ++d) {
+                mn[d] = mx[d] = at(first, d);
+                for (size_t c = 0; c < parts; ++c) {
+                    if (pmn[c][d] < mn[d])
+                        mn[d] = pmn[c][d];
+                    if (pmx[c][d] > mx[d])
+                        mx[d] = pmx[c][d];
+                }
+            }
+            return;
+        }
         for (int d = 0; d < 3; ++d)
             mn[d] = mx[d] = at(first, d);
         for (size_t i = first + 1; i < first + count; ++i)
@@ -236,31 +272,22 @@ struct Builder {
 
 } // namespace detail
 
-// xyz: 3 doubles per source point in source order (NaN triples for points without coordinates).  threads <= 1: sequential.
-inline void build(Tree& t, const double* xyz, size_t n, unsigned threads)
+// Core: t.pts holds the cloud in source order (3 doubles per point, NaN triples for points without coordinates), t.vind has n
+// entries.  Returns false when the build met an empty range while running threaded: the caller must restore t.pts to source order
+// and call again with threads = 1 (only the sequential order defines what such a range reads).
+inline bool build_in_place(Tree& t, unsigned threads)
 {
+    const size_t n = t.vind.size();
     t.error.clear();
     t.nodes.clear();
-    t.vind.resize(n);
-    t.pts.assign(xyz, xyz + 3 * n);
-    for (size_t i = 0; i < n; ++i)
-        t.vind[i] = static_cast<uint32_t>(i);
     if (n == 0) {
         t.error = "coord_kdtree: empty source cloud";
-        return;
+        return true;
     }
-    // :1020-1039
-    for (int d = 0; d < 3; ++d)
-        t.rootBox.lo[d] = t.rootBox.hi[d] = xyz[d];
-    for (size_t k = 1; k < n; ++k)
-        for (int d = 0; d < 3; ++d) {
-            const double v = xyz[3 * k + d];
-            if (v < t.rootBox.lo[d])
-                t.rootBox.lo[d] = v;
-            if (v > t.rootBox.hi[d])
-                t.rootBox.hi[d] = v;
-        }
-    const Box firstBox = t.rootBox;
+    parallel_ranges(n, 1 << 18, [&](size_t a, size_t b) {
+        for (size_t i = a; i < b; ++i)
+            t.vind[i] = static_cast<uint32_t>(i);
+    });
     detail::Builder b;
     b.n = static_cast<uint32_t>(n);
     b.vind = t.vind.data();
@@ -268,15 +295,14 @@ inline void build(Tree& t, const double* xyz, size_t n, unsigned threads)
     b.parDepth = 0;
     for (unsigned c = 1; c < threads; c *= 2)
         ++b.parDepth;
+    // :1020-1039 (the same rule as minmax3)
+    b.minmax3(0, n, t.rootBox.lo, t.rootBox.hi);
     detail::Ctx main;
     b.divide(main, 0, static_cast<uint32_t>(n), t.rootBox, 0);
     if (b.sawEmptyRange && b.parDepth > 0) {
-        // degenerate (NaN-bent) tree: redo it in the reference's own order
         for (detail::Ctx* c : b.tasks)
             delete c;
-        t.rootBox = firstBox;
-        build(t, xyz, n, 1);
-        return;
+        return false; // degenerate (NaN-bent) tree: to be redone in the reference's own order
     }
     // flatten: the main context first, then the sub-contexts; references between contexts become global ids
     std::vector<size_t> offset(b.tasks.size());
@@ -302,6 +328,18 @@ inline void build(Tree& t, const double* xyz, size_t n, unsigned threads)
     }
     t.root = 0;
     t.error = b.error;
+    return true;
+}
+
+// xyz: 3 doubles per source point in source order (NaN triples for points without coordinates).  threads <= 1: sequential.
+inline void build(Tree& t, const double* xyz, size_t n, unsigned threads)
+{
+    t.vind.resize(n);
+    t.pts.assign(xyz, xyz + 3 * n);
+    if (!build_in_place(t, threads)) {
+        t.pts.assign(xyz, xyz + 3 * n);
+        build_in_place(t, 1);
+    }
 }
 
 // :1239-1256

@@ -152,8 +152,9 @@ int kdtree_translate_clone(double maxDist, double* px, double* py, size_t nq, co
 
     // the targets' coordinates are formed while the tree is being built
     std::vector<double> qxyz(3 * nq);
-    std::vector<double> xyz(3 * n);
     kdclone::Tree tree;
+    tree.vind.resize(n);
+    tree.pts.resize(3 * n); // the cloud is written straight into the tree's point array and permuted there
     {
         struct Joiner {
             std::thread t;
@@ -163,8 +164,12 @@ int kdtree_translate_clone(double maxDist, double* px, double* py, size_t nq, co
                     t.join();
             }
         } targets{std::thread([&]() { parallel_ranges(nq, 1 << 16, [&](size_t a, size_t b) { kdclone::sphere_xyz(px, py, a, b, false, qxyz.data()); }); })};
-        parallel_ranges(n, 1 << 16, [&](size_t a, size_t b) { kdclone::sphere_xyz(lon, lat, a, b, true, xyz.data()); });
-        kdclone::build(tree, xyz.data(), n, std::min(hw, 32u));
+        auto fill = [&]() { parallel_ranges(n, 1 << 16, [&](size_t a, size_t b) { kdclone::sphere_xyz(lon, lat, a, b, true, tree.pts.data()); }); };
+        fill();
+        if (!kdclone::build_in_place(tree, std::min(hw, 32u))) {
+            fill();
+            kdclone::build_in_place(tree, 1);
+        }
     }
     if (!tree.error.empty())
         FXCU_FAIL(tree.error);
