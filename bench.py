@@ -312,7 +312,17 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
     levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50], dtype=np.float64)
     ms = timed(lambda: V.verticalHybridPressure(1, vin, ap, b, ps, levels, ps_scale=0.01), reps=3)
     out["K14_K15_vertical_hybrid_to_pressure_log"] = entry(ms, 312.0 * ncol, 12 * ncol, "65 -> 12 levels, 30 members x 801x561 columns, p formed on the fly")
-    del vin, ps
+    ms = timed(lambda: V.verticalHybridPressure(0, vin, ap, b, ps, levels, ps_scale=0.01), reps=3)
+    out["K14_K15_vertical_hybrid_to_pressure_linear"] = entry(ms, 312.0 * ncol, 12 * ncol, "same, method linear")
+    # explicit vertical coordinate (a materialised pressure field, as for non-hybrid sources): the one-pass sweep kernel; the
+    # coordinate is read too: 4*65 more bytes per column
+    ncol_e = 10 * 801 * 561
+    p_e = (torch.from_numpy(ap).cuda().float()[None, :, None] + torch.from_numpy(b).cuda().float()[None, :, None] * (ps[:, None, :ncol_e] * 0.01)).contiguous()
+    vin_e = vin[:, :, :ncol_e].contiguous()
+    ms = timed(lambda: V.verticalInterpolate(1, vin_e, p_e, level1=levels), reps=3)
+    out["K15_vertical_explicit_coordinate_sweep_log"] = entry(ms, (312.0 + 260.0) * ncol_e, 12 * ncol_e,
+                                                               "65 -> 12 levels, 10 members x 801x561 columns, coordinate field read: 572 B per column")
+    del vin, ps, p_e, vin_e
     # configs[4] second half, chained on the device: bilinear S->T2 of (65 levels x 6 members) and of ps, then hybrid -> 12 pressure levels
     lon2, lat2 = S.target_axes("T2")
     px2, py2, ox2, oy2 = S.meps_index_tables("T2")

@@ -19,6 +19,7 @@
 // own consecutive inner indices.  Algorithmic bytes per column: level formulas 4 (surface) + 4*nz (out); hypsometric
 // integration 8 (sap, sgp) + 4*nz*(p, T[, q]) + 4*nz (out).
 #include "fxcu_common.h"
+#include "fxcu_logtable.h"
 
 #include <cmath>
 #include <vector>
@@ -44,34 +45,8 @@ struct VcoordParams {
     float* out;
 };
 
-// Natural logarithm for the standard-atmosphere step, whose result is narrowed to f32 (the contract of that step is 2 f32 ulps:
-// the device's own log already differs from glibc's in the last f64 bit).  Table form: x = 2^e * m, m in [1, 2); c = the centre of
-// m's 1/128 interval, r = m/c - 1 (|r| < 2^-8), log x = e ln2 + log c + (r - r^2/2 + r^3/3 - r^4/4 + r^5/5), error < 1e-15: a table
-// look-up and 10 FP64 operations instead of the ~45 of log().  tab[i] = (1/c_i, log c_i), 128 entries in shared memory.
-// Zero, negative, subnormal, infinite and NaN arguments go to log().
-__device__ __forceinline__ void log_table_fill(double2* tab, int tid, int nthreads)
-{
-    for (int i = tid; i < 128; i += nthreads) {
-        const double c = 1.0 + (i + 0.5) / 128.0;
-        tab[i] = make_double2(1.0 / c, log(c));
-    }
-}
-__device__ __forceinline__ double log_table(const double2* tab, double x)
-{
-    const long long bits = __double_as_longlong(x);
-    const int ex = static_cast<int>(bits >> 52); // sign and biased exponent
-    if (ex <= 0 || ex >= 0x7ff)
-        return log(x);
-    const double m = __longlong_as_double((bits & 0x000fffffffffffffll) | 0x3ff0000000000000ll);
-    const double2 t = tab[static_cast<int>(bits >> 45) & 127];
-    const double r = __fma_rn(m, t.x, -1.0);
-    double p = __fma_rn(r, 0.2, -0.25);
-    p = __fma_rn(p, r, 1.0 / 3);
-    p = __fma_rn(p, r, -0.5);
-    p = __fma_rn(p * r, r, r);
-    return __fma_rn(static_cast<double>(ex - 1023), 0.693147180559945309417232, t.y + p);
-}
-
+// the standard-atmosphere step narrows its result to f32 (contract: 2 f32 ulps; the device's own log already differs from glibc's in
+// the last f64 bit), so its logarithm is the table form of fxcu_logtable.h
 __device__ __forceinline__ double standard_step(int post, double v, const double2* logtab = nullptr)
 {
     if (post == FIMEXCU_VPOST_STANDARD_ALTITUDE) { // mifi_barometric_height(n, 1013.25, p, 288.15, .)

@@ -17,11 +17,13 @@
 // methods call the device's log(), which may differ from glibc's in the last bit of the f64 result; after the narrowing to the
 // f32 factor this shows, rarely, as a 1-ulp difference of the weight (parity within 1e-5 relative; all other methods bit-exact).
 #include "fxcu_common.h"
+#include "fxcu_logtable.h"
 
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 namespace fxcu {
@@ -48,6 +50,7 @@ struct VertParams {
     float valid_min, valid_max; // NaN = none (already narrowed like CDMVerticalInterpolator.cc:553,558)
     float bad, fill;
     float* out;
+    const double2* logtab; // 128-entry logarithm table in device memory (fxcu_logtable.h), made once per device
 };
 
 // 1/d to ~1e-12 (one Newton step on the hardware's approximation) or to full f64 accuracy (two steps); d normal and positive
@@ -106,6 +109,29 @@ __device__ __forceinline__ bool log_weight_fast(double a, double b, double x, fl
     double rs2;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rs2) : "d"(fabs(s2)));
     const double tol = (1. + q) * (2.0001e-14 * rs2) + 1e-15 * q;
+    const float lo = __double2float_rn(q - tol), hi = __double2float_rn(q + tol);
+    if (lo != hi)
+        return false;
+    f = ((num < 0) != (den < 0)) ? -lo : lo;
+    return true;
+}
+
+// The same weight from table logarithms (fxcu_logtable.h) when log(x) is at hand (fixed target levels: computed by the host's
+// libm, i.e. the reference's own number): f = (log x - log a) / (log b - log a) with two 10-operation logarithms and one
+// reciprocal.  Each table logarithm is within 2e-15 of the true one, the reference's rounded logarithms within 2^-53 |log| (< 1.2e-14
+// for any f32-born argument), so the quotient is within (1 + |f|) * 4e-14 / |log b - log a| of the reference's f64 quotient; it is
+// returned only if every real number in that interval narrows to the SAME f32.  a, b positive f32-born, a != b.
+__device__ __forceinline__ bool log_weight_table(const double2* tab, float a, float b, double xlog, float& f)
+{
+    const double la = log_table_f32(tab, a), lb = log_table_f32(tab, b);
+    const double num = xlog - la, den = lb - la;
+    const double ad = fabs(den);
+    if (!(ad > 1e-12 && ad < 1e3 && fabs(num) < 1e6)) // brackets closer than the table's error, or junk: let the caller decide
+        return false;
+    const double rd = rcp_newton(ad, true);
+    double q = fabs(num) * rd;
+    q = __fma_rn(__fma_rn(-ad, q, fabs(num)), rd, q);
+    const double tol = (1. + q) * (4.0001e-14 * rd) + 1e-15 * q;
     const float lo = __double2float_rn(q - tol), hi = __double2float_rn(q + tol);
     if (lo != hi)
         return false;
@@ -341,8 +367,9 @@ struct OutCfg {
     int method;
     float bad, fill, valid_min, valid_max;
     size_t nInner;
+    const double2* logtab; // shared-memory logarithm table of the kernel (fxcu_logtable.h), or nullptr
 };
-__device__ __forceinline__ OutCfg out_cfg(const VertParams& P) { return OutCfg{P.method, P.bad, P.fill, P.valid_min, P.valid_max, P.nInner}; }
+__device__ __forceinline__ OutCfg out_cfg(const VertParams& P) { return OutCfg{P.method, P.bad, P.fill, P.valid_min, P.valid_max, P.nInner, nullptr}; }
 
 // valid_min / valid_max clamp (CDMVerticalInterpolator.cc:551-561; NaN compares false and stays), fill value, streaming store
 __device__ __forceinline__ void store_result(const OutCfg& C, float* dst, float r)
@@ -364,6 +391,19 @@ __device__ __forceinline__ float blend_levels(const OutCfg& C, float A, float B,
             A = nan_f();
         if (B == C.bad)
             B = nan_f();
+    }
+    if (C.logtab && C.method == FIMEXCU_VINT_METHOD_LOG && !isnan(xlog) && a > 0.f && b > 0.f && a != b) {
+        // fixed target level with its host-computed logarithm, f32 bracket: table logarithms (the exact-weight cases x == a / x == b
+        // are the quotient's own 0 and 1 only approximately, so they stay with two_level)
+        float f;
+        const double ad = static_cast<double>(a), bd = static_cast<double>(b);
+        if (vout > 0 && vout != ad && vout != bd && log_weight_table(C.logtab, a, b, xlog, f)) {
+            if (f == 0.f)
+                return A; // interpolation.c:442-447
+            if (f == 1.f)
+                return B;
+            return __fadd_rn(A, __fmul_rn(f, __fsub_rn(B, A)));
+        }
     }
     return two_level(C.method, A, B, static_cast<double>(a), static_cast<double>(b), vout, xlog);
 }
@@ -950,6 +990,10 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
     float* s_ca = s_B + JC * HT;                                                               // [JC][HT] coordinate of `first`
     float* s_cb = s_ca + JC * HT;                                                              // [JC][HT] coordinate of `second`
     unsigned short* s_code = reinterpret_cast<unsigned short*>(s_cb - threadIdx.x + JC * HT) + threadIdx.x; // [JC][HT]
+    __shared__ double2 s_log[METHOD == FIMEXCU_VINT_METHOD_LOG ? 128 : 1];
+    if (METHOD == FIMEXCU_VINT_METHOD_LOG)
+        for (int i = threadIdx.x; i < 128; i += HT)
+            s_log[i] = P.logtab[i]; // made once per device (log_table_device)
     for (int k = threadIdx.x; k < nzi; k += HT)
         s_apb[k] = make_double2(P.ap[k], P.b[k]);
     for (int k = threadIdx.x; k < nzo; k += HT) {
@@ -975,6 +1019,7 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
     const PairCol hc{s_apb, ps};
     OutCfg C = out_cfg(P);
     C.method = METHOD;
+    C.logtab = METHOD == FIMEXCU_VINT_METHOD_LOG ? s_log : nullptr;
     if (dir == 0 || !(ps >= hdr->ps_lo && ps <= hdr->ps_hi)) { // no proof for this launch, or a column outside its range (NaN, outlier)
         column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, 0., 0., din, dout);
         return;
@@ -1091,6 +1136,33 @@ static int levels_direction(const double* lv, size_t n)
         }
     }
     return up ? 1 : (down ? -1 : 0);
+}
+
+// the 128-entry logarithm table of fxcu_logtable.h in device memory: made once per device from the host's libm, never freed
+static const double2* log_table_device()
+{
+    static std::mutex mu;
+    static double2* tabs[64] = {};
+    int dev = -1;
+    if (!cuda_ok(cudaGetDevice(&dev), "cudaGetDevice", __FILE__, __LINE__) || dev < 0 || dev >= 64)
+        return nullptr;
+    std::lock_guard<std::mutex> g(mu);
+    if (!tabs[dev]) {
+        double2 h[128];
+        for (int i = 0; i < 128; ++i) {
+            const double c = 1.0 + (i + 0.5) / 128.0;
+            h[i] = make_double2(1.0 / c, std::log(c));
+        }
+        double2* d = nullptr;
+        if (!cuda_ok(cudaMalloc(&d, sizeof(h)), "cudaMalloc", __FILE__, __LINE__))
+            return nullptr;
+        if (!cuda_ok(cudaMemcpy(d, h, sizeof(h), cudaMemcpyHostToDevice), "cudaMemcpy", __FILE__, __LINE__)) {
+            cudaFree(d);
+            return nullptr;
+        }
+        tabs[dev] = d;
+    }
+    return tabs[dev];
 }
 
 static int launch_vertical(const VertParams& P, cudaStream_t s)
@@ -1394,6 +1466,9 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
     P.bad = badIn;
     P.fill = fillOut;
     P.out = d_out;
+    P.logtab = method == FIMEXCU_VINT_METHOD_LOG ? log_table_device() : nullptr;
+    if (method == FIMEXCU_VINT_METHOD_LOG && !P.logtab)
+        return FIMEXCU_ERROR;
     const size_t ncol = nOuter * nInner, nps = nOuterPs * nInner;
     static const bool no_table = std::getenv("FIMEXCU_VERTICAL_NO_TABLE") != nullptr;
     const int nbins = static_cast<int>(std::min<size_t>(512, std::max<size_t>(8, 2048 / std::max<size_t>(nzo, 1))));
