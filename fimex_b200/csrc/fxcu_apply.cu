@@ -655,10 +655,20 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
         // undefined targets carry NaN weights: every product is NaN, no select in the loop
         const float wfx = (f >= 0) ? fx : nan_f(), wfy = (f >= 0) ? fy : nan_f();
         const float omx = __fsub_rn(1.f, wfx), omy = __fsub_rn(1.f, wfy);
+        // tiles that lie wholly inside the target grid store whole stages without a test per level
+        const bool whole_tile = blockIdx.x * 32 + 32 <= P.outX && blockIdx.y * TMA_TH + TMA_TH <= P.outY;
         for (int it = 0; it < niter; ++it) {
             const int s = it % TMA_STAGES;
             mbar_wait(&full[s], (it / TMA_STAGES) & 1);
             const float* t = &tile[s][r];
+            if (whole_tile && (it + 1) * TMA_ZB <= nzc) {
+#pragma unroll
+                for (int k = 0; k < TMA_ZB; ++k)
+                    store_out<FILL>(po + k * P.outLevel,
+                                    blend4(tap<BAD>(t, k * LVL, P.bad), tap<BAD>(t, k * LVL + 1, P.bad), tap<BAD>(t, k * LVL + TMA_BW, P.bad),
+                                           tap<BAD>(t, k * LVL + TMA_BW + 1, P.bad), wfx, wfy, omx, omy),
+                                    P.fill);
+            } else
 #pragma unroll
             for (int k = 0; k < TMA_ZB; ++k) {
                 const float v = blend4(tap<BAD>(t, k * LVL, P.bad), tap<BAD>(t, k * LVL + 1, P.bad), tap<BAD>(t, k * LVL + TMA_BW, P.bad),
