@@ -383,16 +383,24 @@ __device__ __forceinline__ void store_result(const OutCfg& C, float* dst, float 
     __stcs(dst, r);
 }
 
+// out-of-line copy for the rare cases the table kernel's LOG path hands back (keeps its unrolled column loop small)
+__device__ __noinline__ float two_level_out_of_line(int method, float A, float B, double a, double b, double x, double xlog)
+{
+    return two_level(method, A, B, a, b, x, xlog);
+}
+
 // the two bracketing levels' values through the two-level kernel
+template <int METHOD = -1> // >= 0: the method as a compile-time constant (the other methods' arithmetic drops out of the caller)
 __device__ __forceinline__ float blend_levels(const OutCfg& C, float A, float B, float a, float b, double vout, double xlog)
 {
+    const int method = METHOD >= 0 ? METHOD : C.method;
     if (!isnan(C.bad)) {
         if (A == C.bad)
             A = nan_f();
         if (B == C.bad)
             B = nan_f();
     }
-    if (C.logtab && C.method == FIMEXCU_VINT_METHOD_LOG && !isnan(xlog) && a > 0.f && b > 0.f && a != b) {
+    if (C.logtab && method == FIMEXCU_VINT_METHOD_LOG && !isnan(xlog) && a > 0.f && b > 0.f && a != b) {
         // fixed target level with its host-computed logarithm, f32 bracket: table logarithms (the exact-weight cases x == a / x == b
         // are the quotient's own 0 and 1 only approximately, so they stay with two_level)
         float f;
@@ -405,7 +413,9 @@ __device__ __forceinline__ float blend_levels(const OutCfg& C, float A, float B,
             return __fadd_rn(A, __fmul_rn(f, __fsub_rn(B, A)));
         }
     }
-    return two_level(C.method, A, B, static_cast<double>(a), static_cast<double>(b), vout, xlog);
+    if (C.logtab)
+        return two_level_out_of_line(method, A, B, static_cast<double>(a), static_cast<double>(b), vout, xlog);
+    return two_level(method, A, B, static_cast<double>(a), static_cast<double>(b), vout, xlog);
 }
 
 // one output value by the reference's neighbour search (dir: +1 / -1 column known strictly monotone, 0 general scan)
@@ -948,7 +958,6 @@ __global__ void __launch_bounds__(256) hybrid_table_kernel(const double* __restr
 
 constexpr int HT = 128;       // threads (columns) per block of the table kernel's consumer
 constexpr int MAX_ADJUST = 6; // corrections of a looked-up count before the general search takes over
-constexpr int JC = 8;         // target levels per batch: their bracket values travel together
 constexpr unsigned CODE_NAN = 0u, CODE_BLEND = 1u << 14, CODE_SLOW = 2u << 14, CODE_UP = 1u << 13; // | first (13 bits)
 
 // what value_from_step() decides, without fetching anything: NaN / general search / blend(first, first +- 1)
@@ -970,9 +979,100 @@ __device__ __forceinline__ unsigned classify_step(const PairCol& c, int nzi, boo
     return inc ? (CODE_BLEND | CODE_UP | static_cast<unsigned>(step - 1)) : (CODE_BLEND | static_cast<unsigned>(step));
 }
 
-// Per column: bin of the table, then the target levels in batches of JC.  Pass 1 of a batch finds every level's bracket (table
-// count, corrected against the exactly evaluated f32 column) and sends for the two bracket values with asynchronous copies into
-// shared memory, so that all gathers of a batch are in flight together; pass 2 blends and stores.
+// The table kernel's column loop.  Per target level: the table's count m for the column's ps bin, the two f32 column values around
+// it, ONE correction step against them (the table is off by a step at most next to a bin's own transitions; the value fetched for
+// the correction doubles as the tie guard's c(step-2)), the decision of classify_step() inlined for the two cases that make up the
+// bulk -- an interior bracket and the extrapolation beyond the column's last level -- and the two bracket values fetched with plain
+// loads.  LG levels are handled together in straight-line code so that their 2 * LG gathers are in flight at once.  Everything
+// else (level before or equal to the first element, f32 difference ties, a second correction step, NaN levels) goes to the
+// out-of-line general search, which decides by the reference's own scan.
+constexpr int LG = 2;
+
+template <int METHOD, bool INC>
+__device__ __forceinline__ void table_column(const VertParams& P, const OutCfg& C, const PairCol& hc, int nzi, int nzo, int nbins, int dir,
+                                             const unsigned short* mytab, const float* s_xf, const double* s_xd, const double* s_xl,
+                                             const float* __restrict__ din, float* __restrict__ dout)
+{
+    const float c0 = hc(0), cl = hc(nzi - 1), cl2 = hc(nzi - 2), cl3 = nzi >= 3 ? hc(nzi - 3) : 0.f;
+    for (int j0 = 0; j0 < nzo; j0 += LG) {
+        float A[LG], B[LG], ca[LG], cb[LG];
+        bool slow[LG];
+#pragma unroll
+        for (int u = 0; u < LG; ++u) {
+            const int jj = min(j0 + u, nzo - 1); // a short last group repeats its last level (stores are skipped below)
+            const float x = s_xf[jj];
+            const int m = min(max(static_cast<int>(mytab[jj * nbins]), 1), nzi - 1);
+            float plo = hc(m - 1), phi = hc(m);
+            const bool down = INC ? x < plo : x > plo;      // x lies before c(m-1) in walk order
+            const bool up = INC ? !(x < phi) : !(x > phi);  // x lies at or after c(m) (also true for NaN: sent to the general search)
+            const int e = up ? m + 1 : m - 2;
+            const float ce = hc(min(max(e, 0), nzi - 1));
+            int step = m;
+            float guard = ce;      // c(step - 2)
+            bool have_guard = true; // false: c(step - 2) is not at hand
+            if (up) {
+                step = m + 1;
+                guard = plo;
+                plo = phi;
+                phi = ce;
+            } else if (down) {
+                step = m - 1;
+                phi = plo;
+                plo = ce;
+                have_guard = false;
+            }
+            bool ok = !isnan(x) && x != c0 && step >= 1;
+            int first, second;
+            float a, b;
+            if (step >= nzi) { // beyond the last element (classify_step, step == nzi)
+                const float d2 = fabsf(__fsub_rn(x, cl2));
+                ok = ok && step == nzi && fabsf(__fsub_rn(x, cl)) < d2 && (nzi < 3 || d2 < fabsf(__fsub_rn(x, cl3)));
+                first = nzi - 1;
+                second = nzi - 2;
+                a = cl;
+                b = cl2;
+            } else {
+                const float dlo = __fsub_rn(x, plo), dhi = __fsub_rn(x, phi);
+                // the (possibly corrected) bracket must hold x: c(step-1) <= x < c(step) in walk order
+                ok = ok && (INC ? (plo <= x && x < phi) : (plo >= x && x > phi));
+                ok = ok && fabsf(dlo) < FLT_MAX && fabsf(dhi) < FLT_MAX && (INC || x != plo);
+                if (step > 1) {
+                    // rounded differences to c(step-1) and c(step-2) must differ; without c(step-2) at hand: they do whenever
+                    // |x - c(step-1)| < |c(step-1)| / 8, because c(step-2) is at least one f32 spacing of c(step-1) away
+                    if (have_guard)
+                        ok = ok && dlo != __fsub_rn(x, guard);
+                    else
+                        ok = ok && fabsf(dlo) < 0.125f * fabsf(plo);
+                }
+                first = INC ? step - 1 : step;
+                second = INC ? step : step - 1;
+                a = INC ? plo : phi;
+                b = INC ? phi : plo;
+            }
+            first = ok ? first : 0;
+            second = ok ? second : 0;
+            A[u] = __ldg(din + static_cast<size_t>(first) * P.nInner);
+            B[u] = __ldg(din + static_cast<size_t>(second) * P.nInner);
+            ca[u] = a;
+            cb[u] = b;
+            slow[u] = !ok;
+        }
+#pragma unroll
+        for (int u = 0; u < LG; ++u) {
+            const int jj = j0 + u;
+            if (jj < nzo) {
+                float r;
+                if (slow[u])
+                    r = sweep_slow(C, hc, nzi, dir, din, s_xd[jj], s_xl[jj]);
+                else
+                    r = blend_levels<METHOD>(C, A[u], B[u], ca[u], cb[u], s_xd[jj], s_xl[jj]);
+                store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
+            }
+        }
+    }
+}
+
+// Per column: bin of the table, then table_column() over the target levels.
 template <int METHOD> // compile-time interpolation method: the other methods' arithmetic is not in the kernel at all
 __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const VertParams P, const HybridTableHeader* __restrict__ hdr,
                                                                      const unsigned short* __restrict__ tab)
@@ -985,11 +1085,6 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
     double* s_xl = s_xd + nzo;
     float* s_xf = reinterpret_cast<float*>(s_xl + nzo);
     unsigned short* s_tab = reinterpret_cast<unsigned short*>(s_xf + nzo + (nzo & 1));
-    float* s_A = reinterpret_cast<float*>(s_tab + 2 * ((nzo * nbins + 1) / 2)) + threadIdx.x; // [JC][HT]
-    float* s_B = s_A + JC * HT;                                                                // [JC][HT]
-    float* s_ca = s_B + JC * HT;                                                               // [JC][HT] coordinate of `first`
-    float* s_cb = s_ca + JC * HT;                                                              // [JC][HT] coordinate of `second`
-    unsigned short* s_code = reinterpret_cast<unsigned short*>(s_cb - threadIdx.x + JC * HT) + threadIdx.x; // [JC][HT]
     __shared__ double2 s_log[METHOD == FIMEXCU_VINT_METHOD_LOG ? 128 : 1];
     if (METHOD == FIMEXCU_VINT_METHOD_LOG)
         for (int i = threadIdx.x; i < 128; i += HT)
@@ -1024,71 +1119,12 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
         column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, 0., 0., din, dout);
         return;
     }
-    const bool inc = dir > 0;
-    const float sg = inc ? 1.f : -1.f;
-    ColumnEnds E;
-    E.c0 = hc(0);
-    E.c1 = hc(1);
-    E.cl = hc(nzi - 1);
-    E.cl2 = hc(nzi - 2);
-    E.cl3 = nzi >= 3 ? hc(nzi - 3) : 0.f;
     const double t = (ps - hdr->ps_lo) * hdr->inv_width;
     const int bin = min(max(static_cast<int>(t), 0), nbins - 1);
-    const unsigned short* mytab = s_tab + bin;
-    const unsigned sA = static_cast<unsigned>(__cvta_generic_to_shared(s_A)), sB = static_cast<unsigned>(__cvta_generic_to_shared(s_B));
-    for (int j0 = 0; j0 < nzo; j0 += JC) {
-        const int jn = min(JC, nzo - j0);
-        for (int u = 0; u < jn; ++u) {
-            const int jj = j0 + u;
-            const float x = s_xf[jj];
-            const float xs = __fmul_rn(sg, x);
-            int n = mytab[jj * nbins];
-            // n must satisfy (n == 0 || c(n-1) <= x) && (n == nzi || x < c(n)) in walk order; the table is off by a step at
-            // most near a bin's own transitions
-            float plo = n > 0 ? hc(n - 1) : 0.f, phi = n < nzi ? hc(n) : 0.f;
-            int it = 0;
-            while (n > 0 && !(__fmul_rn(sg, plo) <= xs) && it < MAX_ADJUST) {
-                --n;
-                ++it;
-                phi = plo;
-                plo = n > 0 ? hc(n - 1) : 0.f;
-            }
-            while (n < nzi && !(xs < __fmul_rn(sg, phi)) && it < MAX_ADJUST) {
-                ++n;
-                ++it;
-                plo = phi;
-                phi = n < nzi ? hc(n) : 0.f;
-            }
-            unsigned code = CODE_SLOW;
-            if (it < MAX_ADJUST && !isnan(x))
-                code = classify_step(hc, nzi, inc, E, (x == E.c0) ? 0 : n, x, plo, phi);
-            if (code & CODE_BLEND) {
-                const unsigned first = code & 0x1fffu;
-                const float* pa = din + static_cast<size_t>(first) * P.nInner;
-                const float* pb = (code & CODE_UP) ? pa + P.nInner : pa - P.nInner;
-                // the coordinates of (first, second) are at hand: interior step -> (plo, phi) in walk order, far end -> the column's last two
-                const bool far_end = first == static_cast<unsigned>(nzi - 1) && !(code & CODE_UP) && n == nzi;
-                s_ca[u * HT] = far_end ? E.cl : ((code & CODE_UP) ? plo : phi);
-                s_cb[u * HT] = far_end ? E.cl2 : ((code & CODE_UP) ? phi : plo);
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sA + u * HT * 4), "l"(pa) : "memory");
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sB + u * HT * 4), "l"(pb) : "memory");
-            }
-            s_code[u * HT] = static_cast<unsigned short>(code);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        asm volatile("cp.async.wait_all;" ::: "memory");
-        for (int u = 0; u < jn; ++u) {
-            const int jj = j0 + u;
-            const unsigned code = s_code[u * HT];
-            float r = nan_f();
-            if (code & CODE_BLEND) {
-                r = blend_levels(C, s_A[u * HT], s_B[u * HT], s_ca[u * HT], s_cb[u * HT], s_xd[jj], s_xl[jj]);
-            } else if (code & CODE_SLOW) {
-                r = sweep_slow(C, hc, nzi, dir, din, s_xd[jj], s_xl[jj]);
-            }
-            store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
-        }
-    }
+    if (dir > 0)
+        table_column<METHOD, true>(P, C, hc, nzi, nzo, nbins, dir, s_tab + bin, s_xf, s_xd, s_xl, din, dout);
+    else
+        table_column<METHOD, false>(P, C, hc, nzi, nzo, nbins, dir, s_tab + bin, s_xf, s_xd, s_xl, din, dout);
 }
 
 // min / max of the surface pressure of a launch (NaN ignored): lets the host prove monotonicity for all columns at once
@@ -1473,8 +1509,7 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
     static const bool no_table = std::getenv("FIMEXCU_VERTICAL_NO_TABLE") != nullptr;
     const int nbins = static_cast<int>(std::min<size_t>(512, std::max<size_t>(8, 2048 / std::max<size_t>(nzo, 1))));
     const size_t tab_words = (nzo * nbins + 1) / 2;
-    const size_t tab_smem = (2 * nzi + 2 * nzo) * sizeof(double) + (nzo + (nzo & 1)) * sizeof(float) + tab_words * 4 +
-                            JC * HT * (4 * sizeof(float) + sizeof(unsigned short));
+    const size_t tab_smem = (2 * nzi + 2 * nzo) * sizeof(double) + (nzo + (nzo & 1)) * sizeof(float) + tab_words * 4;
     const int init[2] = {0x7f800000, static_cast<int>(0x80800000u)}; // +inf / "-inf" in the ordered-int encoding
     if (!no_table && ncol && nzo && nzi >= 1 && nzi < 8192 && nzo < 65535 && tab_smem <= 28 * 1024) {
         // launch-wide table path: ps range -> monotonicity proof + table (device side, no host round trip) -> consumer kernel
