@@ -591,6 +591,46 @@ def main_b200(args):
             job["e2e"] = {"value": S.MEPS_NT * points_per_step / wall / 1e9, "unit": UNIT, "ms": wall * 1e3,
                           "what": f"plug-in call sequence per slab; slowest rank's mean slab time over {n_job} of its slabs x its {max(counts)} slabs"}
 
+        # the reference's own process model on the same N GPUs: ONE process (rank 0; the other ranks wait), one cache handle whose
+        # tables are replicated onto every GPU (fimexcu_cache_replicate), N host threads -- the writer's OpenMP threads -- each bound
+        # to a GPU and pulling slabs t, t + N, ... through the plug-in call sequence
+        if world > 1 and not args.no_e2e:
+            barrier()
+            if rank == 0:
+                try:
+                    ci.replicate(list(range(world)))
+                    per_thread = 4
+                    errs = []
+
+                    def writer(d):
+                        try:
+                            _lib.check(lib.fimexcu_set_device(d), "set_device")
+                            ns = C.c_size_t()
+                            for _ in range(per_thread + 1 if d == 0 else per_thread):
+                                h_out = lib.fimexcu_host_alloc(out_bytes)
+                                _lib.check(lib.fimexcu_cache_apply_f(ci._h, pageable_in.ctypes.data, n_in, h_out, C.byref(ns), nanf, nanf), "apply_f")
+                                lib.fimexcu_host_free(h_out)
+                        except Exception as exc:  # noqa: BLE001
+                            errs.append(repr(exc))
+
+                    for timed_round in (False, True):  # first round warms the pools and streams of every (thread, device)
+                        ths = [threading.Thread(target=writer, args=(d,)) for d in range(world)]
+                        t0 = time.perf_counter()
+                        for th in ths:
+                            th.start()
+                        for th in ths:
+                            th.join()
+                        wall_sp = time.perf_counter() - t0
+                    _lib.check(lib.fimexcu_set_device(local), "set_device")
+                    n_sp = world * per_thread + 1
+                    job["single_process"] = ({"error": errs[0][:200]} if errs else
+                                             {"value": n_sp * points_per_step / wall_sp / 1e9, "unit": UNIT, "ms": wall_sp * 1e3, "slabs": n_sp,
+                                              "what": f"one process, one replicated cache handle, {world} host threads bound to {world} GPUs, plug-in call "
+                                                      f"sequence; {n_sp} slabs dealt t % N (thread 0 carries one more)"})
+                except Exception as exc:  # noqa: BLE001
+                    job["single_process"] = {"error": str(exc)[:200]}
+            barrier()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
