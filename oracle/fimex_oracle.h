@@ -11,8 +11,9 @@
  *   (2) the reference itself, compiled from its own sources into oracle/_ref/libfimexref.so
  *       (oracle/Makefile), on seeded random inputs.
  * Projection arithmetic (oracle/miniproj.c) restates the published PROJ / Snyder formulas; PROJ
- * itself is not vendored in the reference, so that one part is "parity unpinned" against real
- * PROJ and pinned by analytic identities instead (see miniproj.h).
+ * itself is not vendored in the reference; that part is pinned against the PROJ-generated
+ * longitude/latitude fields of the reference's fixtures for ob_tran / lcc / stere on the sphere
+ * (tests/test_proj_pins.py) and by analytic identities for the rest (see miniproj.h).
  *
  * Arithmetic is written so that gcc on x86-64 (SSE2, no FMA contraction: build with
  * -ffp-contract=off) produces the same bits as the reference built with its default flags.

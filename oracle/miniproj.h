@@ -8,11 +8,14 @@
  * published algorithms PROJ implements (Snyder, "Map Projections - A Working Manual", USGS PP 1395; PROJ's
  * documented lcc / stere / merc / ob_tran / tmerc(Poder-Engsager) / laea operations).
  *
- * PARITY UNPINNED against real PROJ: the reference has no test that fixes reproject_axes output
- * numerically (test/testInterpolation.cc:260-272 only checks "> 89").  What pins this file instead:
- * round trips fwd(inv(x)) <= 1e-9 deg / 1e-6 m, closed-form corner coordinates of the MEPS grid, the
- * EMEP cell test of test/testInterpolation.cc:274-385 and the 90/180 degree rotation tests (:387-628),
- * all replayed in tests/test_oracle_proj.py.
+ * PINNED against real PROJ output for ob_tran, lcc (sphere) and polar stere (sphere): the reference's NetCDF
+ * fixtures store PROJ-generated longitude/latitude fields for six projected grids; tests/test_proj_pins.py
+ * reproduces them to 3e-14 degree in both directions (fixture tests/golden/reference_proj_pins.npz).
+ * PARITY UNPINNED for the ellipsoidal forms, merc, tmerc/utm and laea: the reference has no test that fixes
+ * reproject_axes output numerically (test/testInterpolation.cc:260-272 only checks "> 89") and no fixture
+ * with those projections.  They are pinned by round trips fwd(inv(x)) <= 1e-9 deg / 1e-6 m, closed-form
+ * corner coordinates of the MEPS grid, the EMEP cell test of test/testInterpolation.cc:274-385 and the
+ * 90/180 degree rotation tests (:387-628), all replayed in tests/test_oracle_proj.py.
  *
  * Transform semantics (crs -> crs): source inverse projection to geographic lon/lat on the source
  * figure, NO datum shift (what proj4's pj_transform does for an unknown datum and PROJ >= 6 does as a

@@ -1,7 +1,7 @@
 """GPU tests of the cache build: lattice reprojection (K1), index tables (K2), rotation matrices (K8), through the C ABI.
 
-Checker: oracle/miniproj.c (CPU restatement of the published projection formulas; PARITY UNPINNED against real PROJ,
-see oracle/miniproj.h) and analytic identities.  Tolerances: 1e-6 m / 1e-9 deg on coordinates (device vs glibc libm
+Checker: oracle/miniproj.c (CPU restatement of the published projection formulas; pinned against stored PROJ output for
+ob_tran / lcc / stere on the sphere in tests/test_proj_pins.py, unpinned for the other forms, see oracle/miniproj.h) and analytic identities.  Tolerances: 1e-6 m / 1e-9 deg on coordinates (device vs glibc libm
 differ in the last bits), 1e-9 cells on index tables, 1e-9 rad on rotation angles."""
 import ctypes as C
 

@@ -1,5 +1,5 @@
 """Pins oracle/miniproj.c, the CPU restatement of the projections (PROJ itself is not in the reference tree and not in this
-image: "parity unpinned" against real PROJ).  Pins used instead: round trips, closed-form / published coordinates, and the
+image; its stored output for ob_tran / lcc / stere on the sphere is pinned in tests/test_proj_pins.py).  Pins here: round trips, closed-form / published coordinates, and the
 reference's own PROJ-dependent unit tests replayed through its unmodified src/reproject.cc compiled over the proj.h shim
 (test/testInterpolation.cc:274-470)."""
 import ctypes as C

@@ -11,8 +11,8 @@ mini-PROJ (oracle/_ref); GPU: the product's device projections through the C ABI
         reference only checks that they parse -- here each gets an explicit forward pin for (10 E, 60 N) and the inverse back, the
         expected numbers coming from the published closed forms (Snyder 1987: 15-1..15-4 lcc, 21-33..21-34 + 15-9 polar stere;
         the pole rotation of ob_tran) evaluated independently in numpy below -- NOT from PROJ, which no test here can run.
-Beyond these pins the projection rows (reproject_axes, reproject_values, get_vector_reproject_matrix*) stay
-"parity unpinned" against PROJ itself; see DESIGN.md section 2.
+PROJ's own numbers for ob_tran / lcc / stere on the sphere are pinned separately, from the lon/lat fields stored in the reference's
+fixtures (tests/test_proj_pins.py); see DESIGN.md section 2 for what remains unpinned.
 """
 import ctypes as C
 import math
