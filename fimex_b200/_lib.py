@@ -69,6 +69,7 @@ SIGNATURES = {
     "fimexcu_cache_apply_i16": (C.c_int, [vp, vp, sz, vp, c_size_p, C.c_double]),
     "fimexcu_cache_apply_dev_i16": (C.c_int, [vp, vp, sz, vp, C.c_double, vp]),
     "fimexcu_cache_padded_layout": (C.c_int, [vp, c_size_p, c_size_p, c_size_p, c_size_p]),
+    "fimexcu_cache_row_bands": (C.c_int, [vp, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_double)]),
     "fimexcu_cache_destroy": (None, [vp]),
     "fimexcu_get_values_f": (C.c_int, _point),
     "fimexcu_get_values_bilinear_f": (C.c_int, _point),

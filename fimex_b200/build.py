@@ -41,7 +41,7 @@ def _stale(target, deps):
 
 def build_library(force=False, verbose=False):
     sources = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
-    headers = sorted(glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh")) +
+    headers = sorted(glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "*.inc")) +
                      glob.glob(os.path.join(HERE, "..", "include", "*.h")))
     os.makedirs(OBJ, exist_ok=True)
     nvcc = _nvcc()

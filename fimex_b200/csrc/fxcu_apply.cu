@@ -26,9 +26,15 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <cstdio>
 #include <cstdint>
 #include <cstring>
+#include <limits>
+#include <emmintrin.h>
+#include <functional>
 #include <memory>
+#include <thread>
 #include <vector>
 
 namespace fxcu {
@@ -1247,6 +1253,96 @@ static int pick_zchunk(size_t tiles, int nz)
     return static_cast<int>((nz + chunks - 1) / chunks);
 }
 
+// per target row: first and one-past-last column whose table entry is defined (lo >= hi: none)
+__global__ void __launch_bounds__(128) row_span_kernel(const int* __restrict__ off, int outX, int2* __restrict__ span)
+{
+    const int* row = off + static_cast<size_t>(blockIdx.x) * outX;
+    int lo = outX, hi = 0;
+    for (int x = threadIdx.x; x < outX; x += 128)
+        if (__ldg(row + x) >= 0) {
+            lo = min(lo, x);
+            hi = max(hi, x + 1);
+        }
+    __shared__ int s_lo, s_hi;
+    if (threadIdx.x == 0) {
+        s_lo = outX;
+        s_hi = 0;
+    }
+    __syncthreads();
+    if (lo < hi) {
+        atomicMin(&s_lo, lo);
+        atomicMax(&s_hi, hi);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        span[blockIdx.x] = make_int2(s_lo, s_hi);
+}
+
+// Row bands of a finished table (fimexcu_cache::bands): the per-row spans from the device, merged on the host into at most
+// MAX_BANDS bands, always joining the two neighbours whose common rectangle adds the least area.
+constexpr size_t MAX_BANDS = 24;
+static bool build_row_bands(fimexcu_cache* c, cudaStream_t s)
+{
+    const size_t outX = c->outX, outY = c->outY;
+    c->bands.clear();
+    c->band_fraction = 1.0;
+    if (outX == 0 || outY == 0 || outY > (1u << 20))
+        return true;
+    DevBuf dspan;
+    if (!dspan.alloc(outY * sizeof(int2), s))
+        return false;
+    row_span_kernel<<<static_cast<unsigned>(outY), 128, 0, s>>>(c->off.as<int>(), static_cast<int>(outX), dspan.as<int2>());
+    std::vector<int2> span(outY);
+    if (!cuda_ok(cudaGetLastError(), "row_span_kernel", __FILE__, __LINE__) ||
+        !cuda_ok(cudaMemcpyAsync(span.data(), dspan.p, outY * sizeof(int2), cudaMemcpyDeviceToHost, s), "cudaMemcpyAsync", __FILE__, __LINE__) ||
+        !cuda_ok(cudaStreamSynchronize(s), "cudaStreamSynchronize", __FILE__, __LINE__))
+        return false;
+    typedef fimexcu_cache::RowBand Band;
+    auto join = [](const Band& a, const Band& b) {
+        Band r{a.y0, b.y1, 0, 0};
+        if (a.x0 >= a.x1) {
+            r.x0 = b.x0;
+            r.x1 = b.x1;
+        } else if (b.x0 >= b.x1) {
+            r.x0 = a.x0;
+            r.x1 = a.x1;
+        } else {
+            r.x0 = std::min(a.x0, b.x0);
+            r.x1 = std::max(a.x1, b.x1);
+        }
+        return r;
+    };
+    auto area = [](const Band& b) { return static_cast<long long>(b.y1 - b.y0) * std::max(0, b.x1 - b.x0); };
+    // start from blocks of rows (at most 512 of them), then merge greedily
+    std::vector<Band> bands;
+    const size_t block = (outY + 511) / 512;
+    for (size_t y0 = 0; y0 < outY; y0 += block) {
+        Band b{static_cast<int>(y0), static_cast<int>(y0), 0, 0};
+        for (size_t y = y0; y < std::min(outY, y0 + block); ++y)
+            b = join(b, Band{static_cast<int>(y), static_cast<int>(y + 1), span[y].x, std::max(span[y].x, span[y].y)});
+        bands.push_back(b);
+    }
+    while (bands.size() > MAX_BANDS) {
+        size_t best = 0;
+        long long best_cost = -1;
+        for (size_t i = 0; i + 1 < bands.size(); ++i) {
+            const long long cost = area(join(bands[i], bands[i + 1])) - area(bands[i]) - area(bands[i + 1]);
+            if (best_cost < 0 || cost < best_cost) {
+                best_cost = cost;
+                best = i;
+            }
+        }
+        bands[best] = join(bands[best], bands[best + 1]);
+        bands.erase(bands.begin() + static_cast<long>(best) + 1);
+    }
+    long long total = 0;
+    for (const Band& b : bands)
+        total += area(b);
+    c->band_fraction = static_cast<double>(total) / (static_cast<double>(outX) * static_cast<double>(outY));
+    c->bands = std::move(bands);
+    return true;
+}
+
 fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, size_t inX, size_t inY, size_t outX, size_t outY, cudaStream_t s)
 {
     if (!require_device())
@@ -1328,6 +1424,8 @@ fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, s
             c->tiles_fitting = hc[1];
         }
         FXCU_CUDA_NULL(cudaStreamSynchronize(s));
+        if (!build_row_bands(c.get(), s))
+            return nullptr;
         return c.release();
     }
 
@@ -1411,6 +1509,8 @@ fimexcu_cache* cache_build(int method, const double* d_px, const double* d_py, s
         c->tiles_fitting = hc[1];
     }
     FXCU_CUDA_NULL(cudaStreamSynchronize(s));
+    if (!build_row_bands(c.get(), s))
+        return nullptr;
     return c.release();
 }
 
@@ -1683,18 +1783,117 @@ static int e2e_chunks()
     return v;
 }
 
+static size_t e2e_copy_threads()
+{
+    static const size_t v = []() { const char* e = getenv("FIMEXCU_E2E_COPY_THREADS"); const int n = e ? atoi(e) : 4; return static_cast<size_t>(std::max(1, std::min(64, n))); }();
+    return v;
+}
+static size_t e2e_fill_threads()
+{
+    static const size_t v = []() { const char* e = getenv("FIMEXCU_E2E_FILL_THREADS"); const int n = e ? atoi(e) : 4; return static_cast<size_t>(std::max(1, std::min(64, n))); }();
+    return v;
+}
+// FIMEXCU_E2E_TRACE=1: one line per host-pointer call on stderr with where its wall time went (for integrators: which of the
+// host copy, the PCIe queue and the margin fill bounds a slab on their machine)
+static bool e2e_trace()
+{
+    static const bool v = []() { const char* e = getenv("FIMEXCU_E2E_TRACE"); return e && atoi(e) != 0; }();
+    return v;
+}
+struct E2ETrace {
+    typedef std::chrono::steady_clock clock;
+    bool on = e2e_trace();
+    clock::time_point t0 = clock::now();
+    double copy_in = 0, wait = 0, enqueue = 0, drain = 0, fill = 0;
+    static double ms(clock::time_point a, clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); }
+    template <class F> void timed(double& acc, F&& f)
+    {
+        if (!on) {
+            f();
+            return;
+        }
+        const clock::time_point a = clock::now();
+        f();
+        acc += ms(a, clock::now());
+    }
+    void report(size_t nz, bool banded, bool bounce_in, bool bounce_out) const
+    {
+        if (on)
+            fprintf(stderr, "fimexcu e2e: %zu levels%s%s%s: total %.2f ms = host copy-in %.2f + waits for buffers %.2f + enqueue %.2f + drain %.2f (margin fill, concurrent: %.2f)\n",
+                    nz, banded ? ", row bands" : "", bounce_in ? ", pageable in" : "", bounce_out ? ", pageable out" : "", ms(t0, clock::now()), copy_in, wait, enqueue, drain,
+                    fill);
+    }
+};
+
+static bool e2e_bands() // FIMEXCU_E2E_BANDS=0: copy whole result slabs back (for measurements)
+{
+    static const bool v = []() { const char* e = getenv("FIMEXCU_E2E_BANDS"); return !(e && atoi(e) == 0); }();
+    return v;
+}
+
+// n copies of v at p: ordinary stores up to the first 64-byte boundary and after the last one, streaming stores for the whole lines
+// in between (written once, not read by this library: an ordinary store would first pull every line into the cache).  Streaming
+// stores to PART of a line, or mixed with ordinary stores to the same line, run four times slower (profiles/exp/hostcopy_probe.cu).
+template <class T> static void fill_lines(T* p, size_t n, T v)
+{
+    static_assert(sizeof(T) == 4 || sizeof(T) == 2, "float or short");
+    while (n && (reinterpret_cast<uintptr_t>(p) & 63u)) {
+        *p++ = v;
+        --n;
+    }
+    constexpr size_t PER = 64 / sizeof(T);
+    if (n >= PER) {
+        alignas(16) T pat[16 / sizeof(T)];
+        for (T& e : pat)
+            e = v;
+        const __m128i q = _mm_load_si128(reinterpret_cast<const __m128i*>(pat));
+        for (; n >= PER; n -= PER, p += PER) {
+            __m128i* line = reinterpret_cast<__m128i*>(p);
+            _mm_stream_si128(line, q);
+            _mm_stream_si128(line + 1, q);
+            _mm_stream_si128(line + 2, q);
+            _mm_stream_si128(line + 3, q);
+        }
+    }
+    while (n) {
+        *p++ = v;
+        --n;
+    }
+}
+
+// the same for a copy: a result span leaves the pinned bounce buffer for the caller's array, whole destination lines streamed
+static void copy_lines(void* dst_, const void* src_, size_t bytes)
+{
+    char* dst = static_cast<char*>(dst_);
+    const char* src = static_cast<const char*>(src_);
+    const size_t head = std::min<size_t>(bytes, (64 - (reinterpret_cast<uintptr_t>(dst) & 63u)) & 63u);
+    std::memcpy(dst, src, head);
+    dst += head;
+    src += head;
+    bytes -= head;
+    for (; bytes >= 64; bytes -= 64, dst += 64, src += 64) {
+        const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src)), b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src) + 1);
+        const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src) + 2), d = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src) + 3);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst), a);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst) + 1, b);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst) + 2, c);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst) + 3, d);
+    }
+    std::memcpy(dst, src, bytes);
+}
+
 // pageable <-> pinned copies of one level chunk on the host cores (a single memcpy thread runs at a fraction of PCIe speed)
 static void host_copy(void* dst, const void* src, size_t bytes)
 {
-    static const size_t threads = []() { const char* e = getenv("FIMEXCU_E2E_COPY_THREADS"); const int n = e ? atoi(e) : 4; return static_cast<size_t>(std::max(1, std::min(64, n))); }();
+    const size_t threads = e2e_copy_threads();
     const size_t grain = std::max<size_t>(size_t(1) << 20, (bytes + threads - 1) / threads);
     parallel_ranges(bytes, grain, [&](size_t a, size_t b) { std::memcpy(static_cast<char*>(dst) + a, static_cast<const char*>(src) + a, b - a); });
 }
 
-// host slab -> host slab through the device; T = float or short, `apply` = the strided device apply for that element type.
-// c is the table set on the CURRENT device.
+// host slab -> host slab through the device; T = float or short, `apply` = the strided device apply for that element type,
+// `undef` = what that apply stores where the table has no source cell.  c is the table set on the CURRENT device.
 template <class T, class ApplyFn>
-static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T* out, size_t* newSize, ApplyFn apply)
+static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T* out, size_t* newSize, T undef, ApplyFn apply)
 {
     const size_t inLayer = c->inX * c->inY, outLayer = c->outX * c->outY;
     const size_t nz = size / inLayer; // CachedInterpolation.cc:176
@@ -1720,6 +1919,57 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
     // write pageable memory: such a slab goes through pinned bounce buffers from the library's pool, one per stream, filled /
     // drained by the host cores while the neighbouring chunk is on the bus.
     const bool bounce_in = is_pageable_host(in), bounce_out = is_pageable_host(out);
+    // Only the row bands of the table that can hold data cross the bus (pitched device->host copies run at the speed of plain
+    // ones: profiles/exp/d2h_probe.cu); the rest of the result is the undefined value, written by host cores meanwhile.
+    const bool banded = e2e_bands() && !c->bands.empty() && c->band_fraction < 0.9 && nz * outLayer * sizeof(T) >= (size_t(8) << 20);
+    const size_t outX = c->outX, outY = c->outY;
+    E2ETrace trace;
+    std::thread filler;
+    std::function<void()> start_filler;
+    std::vector<int> row_x0, row_x1; // per target row: the span that is copied back (empty: x0 == x1 == 0)
+    if (banded) {
+        row_x0.assign(outY, 0);
+        row_x1.assign(outY, 0);
+        for (const fimexcu_cache::RowBand& B : c->bands)
+            if (B.x0 < B.x1)
+                for (int y = B.y0; y < B.y1; ++y) {
+                    row_x0[static_cast<size_t>(y)] = B.x0;
+                    row_x1[static_cast<size_t>(y)] = B.x1;
+                }
+        // everything between the spans, as runs that continue across row ends (the right margin of a row and the left margin of
+        // the next one are one piece of memory); each thread takes a range of (level, row) pairs
+        start_filler = [&]() {
+          filler = std::thread([&]() {
+            const E2ETrace::clock::time_point f0 = E2ETrace::clock::now();
+            parallel_ranges(nz * outY, 256, [&](size_t a, size_t b) {
+                T* run = out + a * outX; // start of the current undefined run
+                for (size_t k = a; k < b; ++k) {
+                    const size_t y = k % outY;
+                    T* row = out + k * outX;
+                    if (row_x0[y] < row_x1[y]) {
+                        fill_lines(run, static_cast<size_t>(row + row_x0[y] - run), undef);
+                        run = row + row_x1[y];
+                    }
+                }
+                fill_lines(run, static_cast<size_t>(out + b * outX - run), undef);
+                _mm_sfence();
+            }, e2e_fill_threads());
+            trace.fill = E2ETrace::ms(f0, E2ETrace::clock::now());
+          });
+        };
+        // a pageable input keeps the host cores busy with its bounce copies until the last chunk is queued, and those copies are
+        // what the device waits for: the margins are then written afterwards, while the queue drains
+        if (!bounce_in)
+            start_filler();
+    }
+    struct JoinOnExit {
+        std::thread& t;
+        ~JoinOnExit()
+        {
+            if (t.joinable())
+                t.join();
+        }
+    } join_filler{filler};
     struct Pinned {
         void* p = nullptr;
         ~Pinned() { host_pool_free(p); }
@@ -1740,11 +1990,45 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
             if (rc == FIMEXCU_OK && bounce_out && !(hout[i].p = host_pool_alloc(chunk * outLayer * sizeof(T))))
                 rc = FIMEXCU_ERROR;
         }
+        // device result of a chunk -> host (the caller's array or this stream's bounce buffer, same dense layout)
+        auto copy_back = [&](int i, T* dst, size_t zn) {
+            if (!banded)
+                return cuda_ok(cudaMemcpyAsync(dst, dout[i].p, zn * outLayer * sizeof(T), cudaMemcpyDeviceToHost, st[i]), "D2H", __FILE__, __LINE__);
+            for (const fimexcu_cache::RowBand& B : c->bands) {
+                if (B.x0 >= B.x1)
+                    continue;
+                cudaMemcpy3DParms p = {};
+                p.srcPtr = make_cudaPitchedPtr(dout[i].p, outX * sizeof(T), outX * sizeof(T), outY);
+                p.dstPtr = make_cudaPitchedPtr(dst, outX * sizeof(T), outX * sizeof(T), outY);
+                p.srcPos = make_cudaPos(static_cast<size_t>(B.x0) * sizeof(T), static_cast<size_t>(B.y0), 0);
+                p.dstPos = p.srcPos;
+                p.extent = make_cudaExtent(static_cast<size_t>(B.x1 - B.x0) * sizeof(T), static_cast<size_t>(B.y1 - B.y0), zn);
+                p.kind = cudaMemcpyDeviceToHost;
+                if (!cuda_ok(cudaMemcpy3DAsync(&p, st[i]), "D2H (row band)", __FILE__, __LINE__))
+                    return false;
+            }
+            return true;
+        };
         auto drain = [&](int i) { // wait for stream i; move a finished bounced result to the caller's array
             if (!cuda_ok(cudaStreamSynchronize(st[i]), "cudaStreamSynchronize", __FILE__, __LINE__))
                 rc = FIMEXCU_ERROR;
-            if (pend[i].live && rc == FIMEXCU_OK)
-                host_copy(out + pend[i].z0 * outLayer, hout[i].p, pend[i].zn * outLayer * sizeof(T));
+            if (pend[i].live && rc == FIMEXCU_OK) {
+                T* dst = out + pend[i].z0 * outLayer;
+                const T* src = static_cast<const T*>(hout[i].p);
+                if (!banded)
+                    host_copy(dst, src, pend[i].zn * outLayer * sizeof(T));
+                else
+                    parallel_ranges(pend[i].zn * outY, 64, [&](size_t a, size_t b) {
+                        for (size_t k = a; k < b; ++k) {
+                            const size_t y = k % outY;
+                            if (row_x0[y] < row_x1[y]) {
+                                const size_t o = k * outX + static_cast<size_t>(row_x0[y]);
+                                copy_lines(dst + o, src + o, static_cast<size_t>(row_x1[y] - row_x0[y]) * sizeof(T));
+                            }
+                        }
+                        _mm_sfence();
+                    }, e2e_copy_threads());
+            }
             pend[i].live = false;
         };
         size_t k = 0;
@@ -1753,17 +2037,20 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
             const int i = static_cast<int>(k % NS);
             const T* src = in + z0 * inLayer;
             if (k >= static_cast<size_t>(NS)) { // the bounce buffers of this stream must be free again
-                if (bounce_out)
-                    drain(i);
-                else if (bounce_in && !cuda_ok(cudaEventSynchronize(ts->h2d[i]), "cudaEventSynchronize", __FILE__, __LINE__))
-                    rc = FIMEXCU_ERROR;
+                trace.timed(trace.wait, [&]() {
+                    if (bounce_out)
+                        drain(i);
+                    else if (bounce_in && !cuda_ok(cudaEventSynchronize(ts->h2d[i]), "cudaEventSynchronize", __FILE__, __LINE__))
+                        rc = FIMEXCU_ERROR;
+                });
                 if (rc != FIMEXCU_OK)
                     break;
             }
             if (bounce_in) {
-                host_copy(hin[i].p, src, zn * inLayer * sizeof(T));
+                trace.timed(trace.copy_in, [&]() { host_copy(hin[i].p, src, zn * inLayer * sizeof(T)); });
                 src = static_cast<const T*>(hin[i].p);
             }
+            const E2ETrace::clock::time_point e0 = trace.on ? E2ETrace::clock::now() : E2ETrace::clock::time_point();
             if (!cuda_ok(cudaMemcpyAsync(din[i].p, src, zn * inLayer * sizeof(T), cudaMemcpyHostToDevice, st[i]), "H2D", __FILE__, __LINE__) ||
                 (bounce_in && !cuda_ok(cudaEventRecord(ts->h2d[i], st[i]), "cudaEventRecord", __FILE__, __LINE__))) {
                 rc = FIMEXCU_ERROR;
@@ -1772,18 +2059,26 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
             rc = apply(din[i].template as<T>(), L, zn, dout[i].template as<T>(), st[i]);
             if (rc != FIMEXCU_OK)
                 break;
-            T* dst = bounce_out ? static_cast<T*>(hout[i].p) : out + z0 * outLayer;
-            if (!cuda_ok(cudaMemcpyAsync(dst, dout[i].p, zn * outLayer * sizeof(T), cudaMemcpyDeviceToHost, st[i]), "D2H", __FILE__, __LINE__))
+            if (!copy_back(i, bounce_out ? static_cast<T*>(hout[i].p) : out + z0 * outLayer, zn))
                 rc = FIMEXCU_ERROR;
             if (bounce_out) {
                 pend[i].live = true;
                 pend[i].z0 = z0;
                 pend[i].zn = zn;
             }
+            if (trace.on)
+                trace.enqueue += E2ETrace::ms(e0, E2ETrace::clock::now());
         }
-        for (int i = 0; i < NS; ++i)
-            drain(i);
+        if (banded && bounce_in)
+            start_filler();
+        trace.timed(trace.drain, [&]() {
+            for (int i = 0; i < NS; ++i)
+                drain(i);
+        });
     }
+    if (filler.joinable())
+        filler.join();
+    trace.report(nz, banded, bounce_in, bounce_out);
     return rc;
 }
 
@@ -1838,6 +2133,23 @@ int fimexcu_cache_padded_layout(const fimexcu_cache* c, size_t* in_row_pitch, si
     if (out_row_pitch) *out_row_pitch = static_cast<size_t>(L.outPitch);
     if (out_level_stride) *out_level_stride = L.outLevel;
     return FIMEXCU_OK;
+}
+
+int fimexcu_cache_row_bands(const fimexcu_cache* c, int* bands4, int max_bands, double* fraction)
+{
+    clear_error();
+    if (!c)
+        return 0;
+    if (fraction)
+        *fraction = c->band_fraction;
+    const int n = static_cast<int>(c->bands.size());
+    for (int k = 0; bands4 && k < n && k < max_bands; ++k) {
+        bands4[4 * k] = c->bands[k].y0;
+        bands4[4 * k + 1] = c->bands[k].y1;
+        bands4[4 * k + 2] = c->bands[k].x0;
+        bands4[4 * k + 3] = c->bands[k].x1;
+    }
+    return n;
 }
 
 int fimexcu_cache_apply_dev_f(const fimexcu_cache* c, const float* d_in, size_t nz, float* d_out, float badIn, float fillOut, void* stream)
@@ -1923,7 +2235,8 @@ int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, 
         FXCU_FAIL("fimexcu_cache_apply_f: null cache");
     if (!require_device() || !(c = on_current_device(c, "fimexcu_cache_apply_f")))
         return FIMEXCU_ERROR;
-    return cache_apply_host<float>(c, in, size, out, newSize, [&](const float* di, const Layout& L, size_t zn, float* dout, cudaStream_t st) {
+    const float undef = std::isnan(fillOut) ? std::numeric_limits<float>::quiet_NaN() : fillOut; // store_out<FILL>(nan_f(), fill)
+    return cache_apply_host<float>(c, in, size, out, newSize, undef, [&](const float* di, const Layout& L, size_t zn, float* dout, cudaStream_t st) {
         return cache_apply_strided(c, di, L, zn, dout, badIn, fillOut, st);
     });
 }
@@ -1935,7 +2248,8 @@ int fimexcu_cache_apply_i16(const fimexcu_cache* c, const int16_t* in, size_t si
         FXCU_FAIL("fimexcu_cache_apply_i16: null cache");
     if (!require_device() || !(c = on_current_device(c, "fimexcu_cache_apply_i16")))
         return FIMEXCU_ERROR;
-    return cache_apply_host<short>(c, in, size, out, newSize, [&](const short* di, const Layout& L, size_t zn, short* dout, cudaStream_t st) {
+    const short undef = static_cast<short>(badValue); // pack_i16(NaN): ScaleValue's newFill_ (DataUtils.h:49)
+    return cache_apply_host<short>(c, in, size, out, newSize, undef, [&](const short* di, const Layout& L, size_t zn, short* dout, cudaStream_t st) {
         return cache_apply_strided_i16(c, di, L, zn, dout, badValue, st);
     });
 }
@@ -2192,6 +2506,8 @@ int fimexcu_cache_replicate(fimexcu_cache* c, int n_devices, const int* device_i
         r->fast_bicubic = c->fast_bicubic;
         r->tiles_with_data = c->tiles_with_data;
         r->tiles_fitting = c->tiles_fitting;
+        r->bands = c->bands;
+        r->band_fraction = c->band_fraction;
         if (!replicate_buf(r->off, d, c->off, c->device, nullptr) || !replicate_buf(r->wx, d, c->wx, c->device, nullptr) ||
             !replicate_buf(r->wy, d, c->wy, c->device, nullptr) || !replicate_buf(r->tile_meta, d, c->tile_meta, c->device, nullptr) ||
             !cuda_ok(cudaStreamSynchronize(nullptr), "cudaStreamSynchronize", __FILE__, __LINE__)) {

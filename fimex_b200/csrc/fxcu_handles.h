@@ -22,6 +22,14 @@ struct fimexcu_cache {
     fxcu::DevBuf wx, wy; // f32 (bilinear) or f64 (bicubic) [outX*outY]
     unsigned tiles_with_data = 0, tiles_fitting = 0; // 32 x 8 target tiles: with defined cells / whose footprint fits the TMA box
     fxcu::DevBuf tile_meta; // int4 per 32 x 8 target tile (row-major over tiles): {box x0 (sector aligned), box y0, TILE_* flags, 0}
+    // Where a result can hold data at all: target rows grouped into a few bands, each with the column span [x0, x1) outside which
+    // every row of the band is undefined whatever the input (table entry -1).  The host entry points bring back only these
+    // rectangles and write the undefined value into the rest on the host (S->T1: 36.6 % of the target lies outside the source).
+    struct RowBand {
+        int y0, y1, x0, x1; // rows [y0, y1), columns [x0, x1); x0 == x1: no row of the band holds data
+    };
+    std::vector<RowBand> bands;  // covers [0, outY) in order; empty: not analysed (treat everything as possibly defined)
+    double band_fraction = 1.0;  // area of the bands' rectangles / area of the target
     // copies of the tables on other devices (fimexcu_cache_replicate), indexed by device ordinal; owned by this handle
     std::vector<fimexcu_cache*> replicas;
     ~fimexcu_cache()

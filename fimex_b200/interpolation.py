@@ -176,6 +176,14 @@ class CachedInterpolationInterface:
         _lib.check(lib.fimexcu_cache_padded_layout(self._h, *[C.byref(t) for t in v]), "padded_layout")
         return tuple(t.value for t in v)
 
+    def rowBands(self):
+        """([(y0, y1, x0, x1), ...], fraction): the bands of target rows with the column span outside which the result is undefined
+        whatever the input; only these rectangles are copied back by the host entry points (fimexcu_cache_row_bands)"""
+        buf = (C.c_int * (4 * 64))()
+        frac = C.c_double(1.0)
+        n = lib.fimexcu_cache_row_bands(self._h, buf, 64, C.byref(frac))
+        return [tuple(buf[4 * k:4 * k + 4]) for k in range(n)], frac.value
+
     def toPadded(self, dense):
         """copy a dense CUDA slab [nz][inY][inX] into a padded one; returns the padded tensor (a view [..., :inX] is the data)"""
         import torch

@@ -552,3 +552,63 @@ def test_fused_uv_bicubic_nearest_bad_fill_padded(fx, oracle, method, rotate):
     pu, pv = interpolateVectorValuesPadded(ci, cvr, du, dv, float(bad_u), float(bad_v), float(fill_u), float(fill_v))
     torch.cuda.synchronize()
     assert _eq(pu[..., :out_x].cpu().numpy(), wu) and _eq(pv[..., :out_x].cpu().numpy(), wv)
+
+
+# ---------------------------------------------------------------------------------- host results: only the row bands that can hold data
+@pytest.mark.parametrize("method", [ol.BILINEAR, ol.BICUBIC, ol.NEAREST])
+@pytest.mark.parametrize("fill", [float("nan"), -999.5])
+def test_host_result_comes_back_in_row_bands(fx, method, fill):
+    """A target much larger than the source, rotated against it: the defined part of every target row is a different span.  The
+    host entry point copies back only the bands' rectangles and writes the undefined value elsewhere on the host
+    (fimexcu_cache_row_bands); the result must be the reference's, cell for cell, for pageable and for pinned result arrays."""
+    rng = np.random.default_rng(400 + method)
+    in_x, in_y, out_x, out_y, nz = 120, 90, 1100, 700, 5   # 15.4 MB result: above the 8 MB threshold of the banded copy
+    gx, gy = np.meshgrid(np.arange(out_x, dtype=np.float64), np.arange(out_y, dtype=np.float64))
+    ang = np.radians(24.0)
+    cx, cy = out_x / 2.0, out_y / 2.0
+    px = in_x / 2.0 + 0.16 * (np.cos(ang) * (gx - cx) - np.sin(ang) * (gy - cy))
+    py = in_y / 2.0 + 0.16 * (np.sin(ang) * (gx - cx) + np.cos(ang) * (gy - cy)) + 2e-5 * (gx - cx) ** 2
+    fld = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.02] = np.nan
+    ci = fx.createCachedInterpolation("x", "y", method, px, py, in_x, in_y, out_x, out_y)
+    bands, frac = ci.rowBands()
+    assert 1 <= len(bands) <= 24 and frac < 0.9, (len(bands), frac)
+    assert bands[0][0] == 0 and bands[-1][1] == out_y and all(a[1] == b[0] for a, b in zip(bands, bands[1:]))
+    want, _ = ol.o_cached_apply(method, px, py, in_x, in_y, out_x, out_y, fld)
+    if not np.isnan(fill):
+        want = np.where(np.isnan(want), np.float32(fill), want)
+    # every cell outside the bands must be undefined in the reference's result too
+    mask = np.zeros((out_y, out_x), bool)
+    for y0, y1, x0, x1 in bands:
+        mask[y0:y1, x0:x1] = x0 < x1
+    outside = want[:, ~mask]
+    assert np.isnan(outside).all() if np.isnan(fill) else (outside == np.float32(fill)).all()
+    sub = ci.reduceInput(fld, in_x, in_y)
+    got, _ = ci.interpolateValues(sub, fillValue=fill)          # pageable in, pageable out
+    assert _eq(got.reshape(want.shape), want)
+    lib = fx.lib
+    h_out = lib.fimexcu_host_alloc(want.size * 4)
+    assert h_out
+    C.memset(h_out, 0x5a, want.size * 4)                         # stale content must not survive anywhere
+    new = C.c_size_t()
+    fx._lib.check(lib.fimexcu_cache_apply_f(ci._h, sub.ctypes.data, sub.size, h_out, C.byref(new), float("nan"), fill), "apply")
+    a = np.frombuffer((C.c_float * want.size).from_address(h_out), dtype=np.float32).reshape(want.shape)
+    assert new.value == want.size and _eq(a, want)
+    lib.fimexcu_host_free(h_out)
+
+
+def test_host_packed_result_comes_back_in_row_bands(fx):
+    rng = np.random.default_rng(77)
+    in_x, in_y, out_x, out_y, nz = 120, 90, 1500, 900, 4       # 10.8 MB of int16
+    gx, gy = np.meshgrid(np.arange(out_x, dtype=np.float64), np.arange(out_y, dtype=np.float64))
+    px = -40.0 + 0.14 * gx + 0.03 * gy
+    py = -30.0 + 0.17 * gy - 0.02 * gx
+    bad = -32767.0
+    raw = rng.integers(-30000, 30000, (nz, in_y, in_x)).astype(np.int16)
+    raw[rng.random(raw.shape) < 0.03] = np.int16(bad)
+    ci = fx.createCachedInterpolation("x", "y", ol.BILINEAR, px, py, in_x, in_y, out_x, out_y)
+    bands, frac = ci.rowBands()
+    assert bands and frac < 0.9
+    want = ol.o_packed_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, raw, bad)
+    got = ci.interpolateValuesPacked(ci.reduceInput(raw, in_x, in_y), bad)
+    assert got.dtype == np.int16 and np.array_equal(got, want)
