@@ -37,10 +37,11 @@ __device__ __forceinline__ double log_table(const double2* tab, double x)
 
 // the same for an argument that was born as a positive, normal f32 (a coordinate column narrowed by Data::asFloat()): everything
 // comes from the 32-bit pattern -- no 64-bit shifts; the caller guarantees 0 < a < inf, subnormals go to log()
-__device__ __forceinline__ double log_table_f32(const double2* tab, float a)
+// NORMAL: the caller has already established that a is a positive normal number
+template <bool NORMAL = false> __device__ __forceinline__ double log_table_f32(const double2* tab, float a)
 {
     const unsigned bits = __float_as_uint(a);
-    if (bits - 0x00800000u >= 0x7f000000u) // zero, subnormal, negative, inf, NaN
+    if (!NORMAL && bits - 0x00800000u >= 0x7f000000u) // zero, subnormal, negative, inf, NaN
         return log(static_cast<double>(a));
     const unsigned mant = bits & 0x007fffffu;
     const double m = __hiloint2double(static_cast<int>(0x3ff00000u | (mant >> 3)), static_cast<int>(mant << 29)); // 1.mant, exact

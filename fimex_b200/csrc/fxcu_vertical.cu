@@ -121,17 +121,20 @@ __device__ __forceinline__ bool log_weight_fast(double a, double b, double x, fl
 // reciprocal.  Each table logarithm is within 2e-15 of the true one, the reference's rounded logarithms within 2^-53 |log| (< 1.2e-14
 // for any f32-born argument), so the quotient is within (1 + |f|) * 4e-14 / |log b - log a| of the reference's f64 quotient; it is
 // returned only if every real number in that interval narrows to the SAME f32.  a, b positive f32-born, a != b.
-__device__ __forceinline__ bool log_weight_table(const double2* tab, float a, float b, double xlog, float& f)
+// NORMAL: a and b are known to be positive normal numbers (their logarithms then differ by less than 178 in magnitude).
+template <bool NORMAL = false> __device__ __forceinline__ bool log_weight_table(const double2* tab, float a, float b, double xlog, float& f)
 {
-    const double la = log_table_f32(tab, a), lb = log_table_f32(tab, b);
+    const double la = log_table_f32<NORMAL>(tab, a), lb = log_table_f32<NORMAL>(tab, b);
     const double num = xlog - la, den = lb - la;
     const double ad = fabs(den);
-    if (!(ad > 1e-12 && ad < 1e3 && fabs(num) < 1e6)) // brackets closer than the table's error, or junk: let the caller decide
+    if (!(ad > 1e-12 && (NORMAL || ad < 1e3) && fabs(num) < 1e6)) // brackets closer than the table's error, or junk: let the caller decide
         return false;
-    const double rd = rcp_newton(ad, true);
+    double rd; // the hardware's reciprocal (relative error < 2^-23); the quotient gets a correction step, which squares that error
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rd) : "d"(ad));
     double q = fabs(num) * rd;
-    q = __fma_rn(__fma_rn(-ad, q, fabs(num)), rd, q);
-    const double tol = (1. + q) * (4.0001e-14 * rd) + 1e-15 * q;
+    q = __fma_rn(__fma_rn(-ad, q, fabs(num)), rd, q);          // relative error < 2^-46 + 2^-52
+    const double k = __fma_rn(rd, 4.0002e-14, 3e-14);          // (1 + q) k >= (1 + q) 4.0001e-14 / |den| + (1e-15 + 2^-45) q
+    const double tol = __fma_rn(q, k, k);
     const float lo = __double2float_rn(q - tol), hi = __double2float_rn(q + tol);
     if (lo != hi)
         return false;
@@ -390,7 +393,9 @@ __device__ __noinline__ float two_level_out_of_line(int method, float A, float B
 }
 
 // the two bracketing levels' values through the two-level kernel
-template <int METHOD = -1> // >= 0: the method as a compile-time constant (the other methods' arithmetic drops out of the caller)
+// TRUSTED (table kernel): the caller has established, for the LOG method, that the level is positive with a host-computed logarithm,
+// that a and b are positive normal numbers and that the level's f32 value differs from both (so the level itself does too)
+template <int METHOD = -1, bool TRUSTED = false> // METHOD >= 0: compile-time constant (the other methods' arithmetic drops out of the caller)
 __device__ __forceinline__ float blend_levels(const OutCfg& C, float A, float B, float a, float b, double vout, double xlog)
 {
     const int method = METHOD >= 0 ? METHOD : C.method;
@@ -400,12 +405,12 @@ __device__ __forceinline__ float blend_levels(const OutCfg& C, float A, float B,
         if (B == C.bad)
             B = nan_f();
     }
-    if (C.logtab && method == FIMEXCU_VINT_METHOD_LOG && !isnan(xlog) && a > 0.f && b > 0.f && a != b) {
+    if (C.logtab && method == FIMEXCU_VINT_METHOD_LOG && (TRUSTED || (!isnan(xlog) && a > 0.f && b > 0.f && a != b))) {
         // fixed target level with its host-computed logarithm, f32 bracket: table logarithms (the exact-weight cases x == a / x == b
         // are the quotient's own 0 and 1 only approximately, so they stay with two_level)
         float f;
         const double ad = static_cast<double>(a), bd = static_cast<double>(b);
-        if (vout > 0 && vout != ad && vout != bd && log_weight_table(C.logtab, a, b, xlog, f)) {
+        if ((TRUSTED || (vout > 0 && vout != ad && vout != bd)) && log_weight_table<TRUSTED>(C.logtab, a, b, xlog, f)) {
             if (f == 0.f)
                 return A; // interpolation.c:442-447
             if (f == 1.f)
@@ -957,6 +962,7 @@ __global__ void __launch_bounds__(256) hybrid_table_kernel(const double* __restr
 }
 
 constexpr int HT = 128;       // threads (columns) per block of the table kernel's consumer
+constexpr int HT_CHUNKS = 4;  // runs of HT columns one block works through with the same staged tables
 constexpr int MAX_ADJUST = 6; // corrections of a looked-up count before the general search takes over
 constexpr unsigned CODE_NAN = 0u, CODE_BLEND = 1u << 14, CODE_SLOW = 2u << 14, CODE_UP = 1u << 13; // | first (13 bits)
 
@@ -986,90 +992,107 @@ __device__ __forceinline__ unsigned classify_step(const PairCol& c, int nzi, boo
 // loads.  LG levels are handled together in straight-line code so that their 2 * LG gathers are in flight at once.  Everything
 // else (level before or equal to the first element, f32 difference ties, a second correction step, NaN levels) goes to the
 // out-of-line general search, which decides by the reference's own scan.
-constexpr int LG = 2;
+constexpr int LG = 4;
+
+// per-column constants of table_column()
+struct TableColumn {
+    float c0, cl3;      // first element, third from the end (0 for nzi < 3)
+    unsigned stride;    // nInner (the launch guarantees nzi * nInner and nzo * nInner < 2^31: 32-bit offsets)
+    bool plain;         // no valid range, no fill value: results are stored as they are
+};
+
+// LG target levels starting at j0 (FULL: all of them exist; otherwise the group is cut at nzo).  Straight-line code: the bracket
+// decision is all predicate logic and selects, so that the 2 * LG gathers are in flight together.
+template <int METHOD, bool INC, bool FULL>
+__device__ __forceinline__ void table_group(const OutCfg& C, const TableColumn& T, const PairCol& hc, int nzi, int nzo, int nbins, int dir, int j0,
+                                            const unsigned short* mytab, const float* s_xf, const double* s_xd, const double* s_xl,
+                                            const float* __restrict__ din, float* __restrict__ dout_j0)
+{
+    constexpr bool LOGM = METHOD == FIMEXCU_VINT_METHOD_LOG;
+    float A[LG], B[LG], ca[LG], cb[LG];
+    bool slow[LG];
+#pragma unroll
+    for (int u = 0; u < LG; ++u) {
+        const int jj = FULL ? j0 + u : min(j0 + u, nzo - 1); // a short last group repeats its last level (stores are skipped below)
+        const float x = s_xf[jj];
+        const int m = mytab[jj * nbins]; // clamped to [1, nzi - 1] when the table was staged
+        const float pm1 = hc(m - 1), pm = hc(m);
+        const bool up = INC ? !(x < pm) : !(x > pm);             // x lies at or after c(m) (also true for NaN: sent to the general search)
+        const bool down = !up && (INC ? x < pm1 : x > pm1);      // x lies before c(m-1) in walk order
+        const float ce = hc(min(max(up ? m + 1 : m - 2, 0), nzi - 1));
+        // one correction step: the bracket c(step-1), c(step) and, unless the step went down, c(step-2)
+        const int step = m + (up ? 1 : 0) - (down ? 1 : 0);
+        const float plo = up ? pm : (down ? ce : pm1);
+        const float phi = up ? ce : (down ? pm1 : pm);
+        const float guard = up ? pm1 : ce;
+        const float dlo = __fsub_rn(x, plo), dhi = __fsub_rn(x, phi), dg = __fsub_rn(x, guard);
+        // interior: the bracket must hold x (c(step-1) <= x < c(step) in walk order), the differences must be finite, and the rounded
+        // differences to c(step-1) and c(step-2) must differ -- without c(step-2) at hand they do whenever |x - c(step-1)| <
+        // |c(step-1)| / 8, because c(step-2) is at least one f32 spacing of c(step-1) away
+        bool ok_in = INC ? (plo <= x && x < phi) : (plo > x && x > phi);
+        ok_in = ok_in && fabsf(dlo) < FLT_MAX && fabsf(dhi) < FLT_MAX;
+        const bool tie_free = down ? fabsf(dlo) < 0.125f * fabsf(plo) : dlo != dg;
+        ok_in = ok_in && (step <= 1 || tie_free);
+        // beyond the last element (step == nzi, reached only by a step up from m == nzi - 1: plo = c(nzi-1), guard = c(nzi-2))
+        const bool far = step >= nzi;
+        const bool ok_far = fabsf(dlo) < fabsf(dg) && (nzi < 3 || fabsf(dg) < fabsf(__fsub_rn(x, T.cl3)));
+        bool ok = !isnan(x) && x != T.c0 && step >= 1 && (far ? ok_far : ok_in);
+        const float a = (INC || far) ? plo : phi;
+        const float b = far ? guard : (INC ? phi : plo);
+        if (LOGM)
+            ok = ok && x != a && x != b; // an exact hit has the weight 0 or 1 exactly: not the table quotient's business
+        int first = (INC || far) ? step - 1 : step;
+        int second = far ? step - 2 : (INC ? step : step - 1);
+        first = ok ? first : 0;
+        second = ok ? second : 0;
+        A[u] = __ldg(din + static_cast<unsigned>(first) * T.stride);
+        B[u] = __ldg(din + static_cast<unsigned>(second) * T.stride);
+        ca[u] = a;
+        cb[u] = b;
+        slow[u] = !ok;
+    }
+#pragma unroll
+    for (int u = 0; u < LG; ++u) {
+        const int jj = j0 + u;
+        if (FULL || jj < nzo) {
+            float r;
+            if (slow[u])
+                r = sweep_slow(C, hc, nzi, dir, din, s_xd[jj], s_xl[jj]);
+            else
+                r = blend_levels<METHOD, LOGM>(C, A[u], B[u], ca[u], cb[u], s_xd[jj], s_xl[jj]);
+            float* dst = dout_j0 + static_cast<unsigned>(u) * T.stride;
+            if (T.plain)
+                __stcs(dst, r);
+            else
+                store_result(C, dst, r);
+        }
+    }
+}
 
 template <int METHOD, bool INC>
 __device__ __forceinline__ void table_column(const VertParams& P, const OutCfg& C, const PairCol& hc, int nzi, int nzo, int nbins, int dir,
                                              const unsigned short* mytab, const float* s_xf, const double* s_xd, const double* s_xl,
                                              const float* __restrict__ din, float* __restrict__ dout)
 {
-    const float c0 = hc(0), cl = hc(nzi - 1), cl2 = hc(nzi - 2), cl3 = nzi >= 3 ? hc(nzi - 3) : 0.f;
-    for (int j0 = 0; j0 < nzo; j0 += LG) {
-        float A[LG], B[LG], ca[LG], cb[LG];
-        bool slow[LG];
-#pragma unroll
-        for (int u = 0; u < LG; ++u) {
-            const int jj = min(j0 + u, nzo - 1); // a short last group repeats its last level (stores are skipped below)
-            const float x = s_xf[jj];
-            const int m = min(max(static_cast<int>(mytab[jj * nbins]), 1), nzi - 1);
-            float plo = hc(m - 1), phi = hc(m);
-            const bool down = INC ? x < plo : x > plo;      // x lies before c(m-1) in walk order
-            const bool up = INC ? !(x < phi) : !(x > phi);  // x lies at or after c(m) (also true for NaN: sent to the general search)
-            const int e = up ? m + 1 : m - 2;
-            const float ce = hc(min(max(e, 0), nzi - 1));
-            int step = m;
-            float guard = ce;      // c(step - 2)
-            bool have_guard = true; // false: c(step - 2) is not at hand
-            if (up) {
-                step = m + 1;
-                guard = plo;
-                plo = phi;
-                phi = ce;
-            } else if (down) {
-                step = m - 1;
-                phi = plo;
-                plo = ce;
-                have_guard = false;
-            }
-            bool ok = !isnan(x) && x != c0 && step >= 1;
-            int first, second;
-            float a, b;
-            if (step >= nzi) { // beyond the last element (classify_step, step == nzi)
-                const float d2 = fabsf(__fsub_rn(x, cl2));
-                ok = ok && step == nzi && fabsf(__fsub_rn(x, cl)) < d2 && (nzi < 3 || d2 < fabsf(__fsub_rn(x, cl3)));
-                first = nzi - 1;
-                second = nzi - 2;
-                a = cl;
-                b = cl2;
-            } else {
-                const float dlo = __fsub_rn(x, plo), dhi = __fsub_rn(x, phi);
-                // the (possibly corrected) bracket must hold x: c(step-1) <= x < c(step) in walk order
-                ok = ok && (INC ? (plo <= x && x < phi) : (plo >= x && x > phi));
-                ok = ok && fabsf(dlo) < FLT_MAX && fabsf(dhi) < FLT_MAX && (INC || x != plo);
-                if (step > 1) {
-                    // rounded differences to c(step-1) and c(step-2) must differ; without c(step-2) at hand: they do whenever
-                    // |x - c(step-1)| < |c(step-1)| / 8, because c(step-2) is at least one f32 spacing of c(step-1) away
-                    if (have_guard)
-                        ok = ok && dlo != __fsub_rn(x, guard);
-                    else
-                        ok = ok && fabsf(dlo) < 0.125f * fabsf(plo);
-                }
-                first = INC ? step - 1 : step;
-                second = INC ? step : step - 1;
-                a = INC ? plo : phi;
-                b = INC ? phi : plo;
-            }
-            first = ok ? first : 0;
-            second = ok ? second : 0;
-            A[u] = __ldg(din + static_cast<size_t>(first) * P.nInner);
-            B[u] = __ldg(din + static_cast<size_t>(second) * P.nInner);
-            ca[u] = a;
-            cb[u] = b;
-            slow[u] = !ok;
-        }
-#pragma unroll
-        for (int u = 0; u < LG; ++u) {
-            const int jj = j0 + u;
-            if (jj < nzo) {
-                float r;
-                if (slow[u])
-                    r = sweep_slow(C, hc, nzi, dir, din, s_xd[jj], s_xl[jj]);
-                else
-                    r = blend_levels<METHOD>(C, A[u], B[u], ca[u], cb[u], s_xd[jj], s_xl[jj]);
-                store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
-            }
+    TableColumn T;
+    T.c0 = hc(0);
+    T.cl3 = nzi >= 3 ? hc(nzi - 3) : 0.f;
+    T.stride = static_cast<unsigned>(P.nInner);
+    T.plain = isnan(C.valid_min) && isnan(C.valid_max) && isnan(C.fill);
+    if (METHOD == FIMEXCU_VINT_METHOD_LOG) {
+        // the column is strictly monotone (the launch's proof), so every element lies between its ends: if both are positive normal
+        // numbers, all are, and the per-level tests of the logarithm drop out (blend_levels<.., TRUSTED>)
+        const unsigned b0 = __float_as_uint(T.c0), b1 = __float_as_uint(hc(nzi - 1));
+        if (b0 - 0x00800000u >= 0x7f000000u || b1 - 0x00800000u >= 0x7f000000u) {
+            column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, 0., 0., din, dout);
+            return;
         }
     }
+    int j0 = 0;
+    for (; j0 + LG <= nzo; j0 += LG, dout += LG * T.stride)
+        table_group<METHOD, INC, true>(C, T, hc, nzi, nzo, nbins, dir, j0, mytab, s_xf, s_xd, s_xl, din, dout);
+    if (j0 < nzo)
+        table_group<METHOD, INC, false>(C, T, hc, nzi, nzo, nbins, dir, j0, mytab, s_xf, s_xd, s_xl, din, dout);
 }
 
 // Per column: bin of the table, then table_column() over the target levels.
@@ -1093,38 +1116,45 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
         s_apb[k] = make_double2(P.ap[k], P.b[k]);
     for (int k = threadIdx.x; k < nzo; k += HT) {
         const double x = P.levels[k];
+        const double xl = P.xlog ? P.xlog[k] : nan("");
         s_xd[k] = x;
-        s_xl[k] = P.xlog ? P.xlog[k] : nan("");
-        s_xf[k] = __double2float_rn(x);
+        s_xl[k] = xl;
+        // LOG: a level without a usable host logarithm (non-positive, NaN) is marked NaN here, which sends it to the general search
+        s_xf[k] = (METHOD == FIMEXCU_VINT_METHOD_LOG && !(x > 0. && !isnan(xl))) ? nan_f() : __double2float_rn(x);
     }
     if (dir) {
         const int words = (nzo * nbins + 1) / 2; // the table buffer is padded to a whole number of 32-bit words
+        const unsigned lo2 = 0x00010001u, hi2 = static_cast<unsigned>(nzi - 1) * 0x00010001u; // counts clamped to [1, nzi - 1] once, here
         for (int i = threadIdx.x; i < words; i += HT)
-            reinterpret_cast<unsigned*>(s_tab)[i] = __ldg(reinterpret_cast<const unsigned*>(tab) + i);
+            reinterpret_cast<unsigned*>(s_tab)[i] = __vminu2(__vmaxu2(__ldg(reinterpret_cast<const unsigned*>(tab) + i), lo2), hi2);
     }
     __syncthreads();
-    const size_t ncol = P.nOuter * P.nInner;
-    const size_t cidx = blockIdx.x * static_cast<size_t>(HT) + threadIdx.x;
-    if (cidx >= ncol)
-        return;
-    const size_t outer = cidx / P.nInner, inner = cidx - outer * P.nInner;
-    const float* din = P.in + outer * P.nzi * P.nInner + inner;
-    float* dout = P.out + outer * P.nzo * P.nInner + inner;
-    const double ps = __dmul_rn(static_cast<double>(__ldg(P.ps + (P.nOuterPs == 1 ? 0 : outer) * P.nInner + inner)), P.ps_scale);
-    const PairCol hc{s_apb, ps};
     OutCfg C = out_cfg(P);
     C.method = METHOD;
     C.logtab = METHOD == FIMEXCU_VINT_METHOD_LOG ? s_log : nullptr;
-    if (dir == 0 || !(ps >= hdr->ps_lo && ps <= hdr->ps_hi)) { // no proof for this launch, or a column outside its range (NaN, outlier)
-        column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, 0., 0., din, dout);
-        return;
+    const double ps_lo = hdr->ps_lo, ps_hi = hdr->ps_hi, inv_width = hdr->inv_width;
+    const size_t outer = blockIdx.y; // grid: (blocks of HT_CHUNKS * HT columns, outer)
+    // the staged tables serve HT_CHUNKS runs of HT neighbouring columns (staging them is a sixth of a single run's instructions)
+#pragma unroll 1
+    for (int chunk = 0; chunk < HT_CHUNKS; ++chunk) {
+        const size_t inner = (blockIdx.x * static_cast<size_t>(HT_CHUNKS) + chunk) * HT + threadIdx.x;
+        if (inner >= P.nInner)
+            return;
+        const float* din = P.in + outer * P.nzi * P.nInner + inner;
+        float* dout = P.out + outer * P.nzo * P.nInner + inner;
+        const double ps = __dmul_rn(static_cast<double>(__ldg(P.ps + (P.nOuterPs == 1 ? 0 : outer) * P.nInner + inner)), P.ps_scale);
+        const PairCol hc{s_apb, ps};
+        if (dir == 0 || !(ps >= ps_lo && ps <= ps_hi)) { // no proof for this launch, or a column outside its range (NaN, outlier)
+            column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, 0., 0., din, dout);
+            continue;
+        }
+        const double t = (ps - ps_lo) * inv_width;
+        const int bin = min(max(static_cast<int>(t), 0), nbins - 1);
+        if (dir > 0)
+            table_column<METHOD, true>(P, C, hc, nzi, nzo, nbins, dir, s_tab + bin, s_xf, s_xd, s_xl, din, dout);
+        else
+            table_column<METHOD, false>(P, C, hc, nzi, nzo, nbins, dir, s_tab + bin, s_xf, s_xd, s_xl, din, dout);
     }
-    const double t = (ps - hdr->ps_lo) * hdr->inv_width;
-    const int bin = min(max(static_cast<int>(t), 0), nbins - 1);
-    if (dir > 0)
-        table_column<METHOD, true>(P, C, hc, nzi, nzo, nbins, dir, s_tab + bin, s_xf, s_xd, s_xl, din, dout);
-    else
-        table_column<METHOD, false>(P, C, hc, nzi, nzo, nbins, dir, s_tab + bin, s_xf, s_xd, s_xl, din, dout);
 }
 
 // min / max of the surface pressure of a launch (NaN ignored): lets the host prove monotonicity for all columns at once
@@ -1511,7 +1541,9 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
     const size_t tab_words = (nzo * nbins + 1) / 2;
     const size_t tab_smem = (2 * nzi + 2 * nzo) * sizeof(double) + (nzo + (nzo & 1)) * sizeof(float) + tab_words * 4;
     const int init[2] = {0x7f800000, static_cast<int>(0x80800000u)}; // +inf / "-inf" in the ordered-int encoding
-    if (!no_table && ncol && nzo && nzi >= 1 && nzi < 8192 && nzo < 65535 && tab_smem <= 28 * 1024) {
+    // (the consumer kernel addresses a column's levels with 32-bit offsets and takes the outer index from blockIdx.y)
+    if (!no_table && ncol && nzo && nzi >= 2 && nzi < 8192 && nzo < 65535 && tab_smem <= 28 * 1024 && nOuter <= 65535 &&
+        nzi * nInner < (size_t(1) << 31) && nzo * nInner < (size_t(1) << 31)) {
         // launch-wide table path: ps range -> monotonicity proof + table (device side, no host round trip) -> consumer kernel
         DevBuf scratch;
         const size_t hdr_off = PS_HIST_BINS * sizeof(unsigned), tab_off = hdr_off + sizeof(HybridTableHeader);
@@ -1525,7 +1557,7 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
         hybrid_table_kernel<<<1, 256, 0, s>>>(P.ap, P.b, static_cast<int>(nzi), P.levels, static_cast<int>(nzo), reinterpret_cast<const unsigned*>(base),
                                                ps_scale, nbins, reinterpret_cast<HybridTableHeader*>(base + hdr_off),
                                                reinterpret_cast<unsigned short*>(base + tab_off));
-        const unsigned blocks = static_cast<unsigned>((ncol + HT - 1) / HT);
+        const dim3 blocks(static_cast<unsigned>((nInner + HT * HT_CHUNKS - 1) / (HT * HT_CHUNKS)), static_cast<unsigned>(nOuter));
         const HybridTableHeader* hdr = reinterpret_cast<const HybridTableHeader*>(base + hdr_off);
         const unsigned short* tab = reinterpret_cast<const unsigned short*>(base + tab_off);
         switch (method) {
