@@ -1004,13 +1004,12 @@ struct TableColumn {
 // LG target levels starting at j0 (FULL: all of them exist; otherwise the group is cut at nzo).  Straight-line code: the bracket
 // decision is all predicate logic and selects, so that the 2 * LG gathers are in flight together.
 template <int METHOD, bool INC, bool FULL>
-__device__ __forceinline__ void table_group(const OutCfg& C, const TableColumn& T, const PairCol& hc, int nzi, int nzo, int nbins, int dir, int j0,
-                                            const unsigned short* mytab, const float* s_xf, const double* s_xd, const double* s_xl,
-                                            const float* __restrict__ din, float* __restrict__ dout_j0)
+__device__ __forceinline__ float* table_group(const OutCfg& C, const TableColumn& T, const PairCol& hc, int nzi, int nzo, int nbins, int dir, int j0,
+                                              const unsigned short* mytab, const float* s_xf, const double* s_xd, const double* s_xl,
+                                              const float* __restrict__ din, float* __restrict__ dst)
 {
     constexpr bool LOGM = METHOD == FIMEXCU_VINT_METHOD_LOG;
-    float A[LG], B[LG], ca[LG], cb[LG];
-    bool slow[LG];
+    float A[LG], B[LG], ca[LG], cb[LG]; // ca = NaN marks a level for the general search (a bracket value is never NaN)
 #pragma unroll
     for (int u = 0; u < LG; ++u) {
         const int jj = FULL ? j0 + u : min(j0 + u, nzo - 1); // a short last group repeats its last level (stores are skipped below)
@@ -1047,26 +1046,26 @@ __device__ __forceinline__ void table_group(const OutCfg& C, const TableColumn& 
         second = ok ? second : 0;
         A[u] = __ldg(din + static_cast<unsigned>(first) * T.stride);
         B[u] = __ldg(din + static_cast<unsigned>(second) * T.stride);
-        ca[u] = a;
+        ca[u] = ok ? a : nan_f();
         cb[u] = b;
-        slow[u] = !ok;
     }
 #pragma unroll
     for (int u = 0; u < LG; ++u) {
         const int jj = j0 + u;
         if (FULL || jj < nzo) {
             float r;
-            if (slow[u])
+            if (isnan(ca[u]))
                 r = sweep_slow(C, hc, nzi, dir, din, s_xd[jj], s_xl[jj]);
             else
                 r = blend_levels<METHOD, LOGM>(C, A[u], B[u], ca[u], cb[u], s_xd[jj], s_xl[jj]);
-            float* dst = dout_j0 + static_cast<unsigned>(u) * T.stride;
             if (T.plain)
                 __stcs(dst, r);
             else
                 store_result(C, dst, r);
+            dst += T.stride;
         }
     }
+    return dst;
 }
 
 template <int METHOD, bool INC>
@@ -1089,8 +1088,8 @@ __device__ __forceinline__ void table_column(const VertParams& P, const OutCfg& 
         }
     }
     int j0 = 0;
-    for (; j0 + LG <= nzo; j0 += LG, dout += LG * T.stride)
-        table_group<METHOD, INC, true>(C, T, hc, nzi, nzo, nbins, dir, j0, mytab, s_xf, s_xd, s_xl, din, dout);
+    for (; j0 + LG <= nzo; j0 += LG)
+        dout = table_group<METHOD, INC, true>(C, T, hc, nzi, nzo, nbins, dir, j0, mytab, s_xf, s_xd, s_xl, din, dout);
     if (j0 < nzo)
         table_group<METHOD, INC, false>(C, T, hc, nzi, nzo, nbins, dir, j0, mytab, s_xf, s_xd, s_xl, din, dout);
 }
