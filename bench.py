@@ -380,6 +380,13 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
             n_in = fwd.getInX() * fwd.getInY()
             out[name + tag] = entry(ms, (4.0 + 4.0 * tox * toy / n_in + 8.0 / 8) * n_in * 8, n_in * 8,
                                     f"2030x1354 swath -> {tox}x{toy}, 8 levels; points = source points")
+            if name == "K12_forward_mean" and not tag:  # the same aggregation over a full 65-level slab (one launch)
+                fin65 = torch.randn((65, fwd.getInY(), fwd.getInX()), dtype=torch.float32, device="cuda")
+                fout65 = torch.empty((65, toy, tox), dtype=torch.float32, device="cuda")
+                ms = timed(lambda: _lib.check(lib.fimexcu_forward_apply_dev_f(fwd._h, fin65.data_ptr(), 65, fout65.data_ptr(), nan, nan, 0, stream), "fwd"))
+                out["K12_forward_mean_65_levels"] = entry(ms, (4.0 + 4.0 * tox * toy / n_in + 8.0 / 65) * n_in * 65, n_in * 65,
+                                                          f"2030x1354 swath -> {tox}x{toy}, 65 levels; points = source points")
+                del fin65, fout65
             fwd.close()
     # K1+K2+K3: cache build from projection strings (one-off; points/s, no roofline)
     lon, lat = S.target_axes("T1")

@@ -1891,9 +1891,11 @@ static void host_copy(void* dst, const void* src, size_t bytes)
 }
 
 // host slab -> host slab through the device; T = float or short, `apply` = the strided device apply for that element type,
-// `undef` = what that apply stores where the table has no source cell.  c is the table set on the CURRENT device.
-template <class T, class ApplyFn>
-static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T* out, size_t* newSize, T undef, ApplyFn apply)
+// `undef` = what that apply stores where the table has no source cell.  NF fields share the call (1, or 2 for the components of a
+// vector: each chunk carries both through one fused kernel).  c is the table set on the CURRENT device.
+template <class T, int NF, class ApplyFn>
+static int cache_apply_host(const fimexcu_cache* c, const T* const (&in)[NF], size_t size, T* const (&out)[NF], size_t* newSize, const T (&undef)[NF],
+                            ApplyFn apply)
 {
     const size_t inLayer = c->inX * c->inY, outLayer = c->outX * c->outY;
     const size_t nz = size / inLayer; // CachedInterpolation.cc:176
@@ -1908,7 +1910,7 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
     const Layout L = dense_layout(c);
     const int NS = e2e_streams();
     // small slabs are latency-bound: one chunk per 16 MB of traffic (at most FIMEXCU_E2E_CHUNKS)
-    const size_t traffic = nz * (inLayer + outLayer) * sizeof(T);
+    const size_t traffic = NF * nz * (inLayer + outLayer) * sizeof(T);
     const size_t nchunk = std::max<size_t>(1, std::min<size_t>(static_cast<size_t>(e2e_chunks()), traffic / (16u << 20)));
     const size_t chunk = std::max<size_t>(1, std::min<size_t>(nz, (nz + nchunk - 1) / nchunk));
     ThreadStreams* ts = thread_streams(c->device);
@@ -1918,10 +1920,14 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
     // The reference hands ordinary `new float[]` memory (include/fimex/SharedArray.h:42-48).  The DMA engines cannot read or
     // write pageable memory: such a slab goes through pinned bounce buffers from the library's pool, one per stream, filled /
     // drained by the host cores while the neighbouring chunk is on the bus.
-    const bool bounce_in = is_pageable_host(in), bounce_out = is_pageable_host(out);
+    bool bounce_in = false, bounce_out = false;
+    for (int f = 0; f < NF; ++f) {
+        bounce_in = bounce_in || is_pageable_host(in[f]);
+        bounce_out = bounce_out || is_pageable_host(out[f]);
+    }
     // Only the row bands of the table that can hold data cross the bus (pitched device->host copies run at the speed of plain
     // ones: profiles/exp/d2h_probe.cu); the rest of the result is the undefined value, written by host cores meanwhile.
-    const bool banded = e2e_bands() && !c->bands.empty() && c->band_fraction < 0.9 && nz * outLayer * sizeof(T) >= (size_t(8) << 20);
+    const bool banded = e2e_bands() && !c->bands.empty() && c->band_fraction < 0.9 && NF * nz * outLayer * sizeof(T) >= (size_t(8) << 20);
     const size_t outX = c->outX, outY = c->outY;
     E2ETrace trace;
     std::thread filler;
@@ -1937,21 +1943,27 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
                     row_x1[static_cast<size_t>(y)] = B.x1;
                 }
         // everything between the spans, as runs that continue across row ends (the right margin of a row and the left margin of
-        // the next one are one piece of memory); each thread takes a range of (level, row) pairs
+        // the next one are one piece of memory); each thread takes a range of (field, level, row) triples
         start_filler = [&]() {
           filler = std::thread([&]() {
             const E2ETrace::clock::time_point f0 = E2ETrace::clock::now();
-            parallel_ranges(nz * outY, 256, [&](size_t a, size_t b) {
-                T* run = out + a * outX; // start of the current undefined run
-                for (size_t k = a; k < b; ++k) {
-                    const size_t y = k % outY;
-                    T* row = out + k * outX;
-                    if (row_x0[y] < row_x1[y]) {
-                        fill_lines(run, static_cast<size_t>(row + row_x0[y] - run), undef);
-                        run = row + row_x1[y];
+            const size_t rows = nz * outY;
+            parallel_ranges(NF * rows, 256, [&](size_t a, size_t b) {
+                while (a < b) {
+                    const size_t f = a / rows, e = std::min(b, (f + 1) * rows); // the part of [a, b) inside field f
+                    T* const base = out[f];
+                    T* run = base + (a - f * rows) * outX; // start of the current undefined run
+                    for (size_t k = a - f * rows; k < e - f * rows; ++k) {
+                        const size_t y = k % outY;
+                        T* row = base + k * outX;
+                        if (row_x0[y] < row_x1[y]) {
+                            fill_lines(run, static_cast<size_t>(row + row_x0[y] - run), undef[f]);
+                            run = row + row_x1[y];
+                        }
                     }
+                    fill_lines(run, static_cast<size_t>(base + (e - f * rows) * outX - run), undef[f]);
+                    a = e;
                 }
-                fill_lines(run, static_cast<size_t>(out + b * outX - run), undef);
                 _mm_sfence();
             }, e2e_fill_threads());
             trace.fill = E2ETrace::ms(f0, E2ETrace::clock::now());
@@ -1974,31 +1986,32 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
         void* p = nullptr;
         ~Pinned() { host_pool_free(p); }
     };
-    Pinned hin[NS_MAX], hout[NS_MAX];
-    struct Pending { // a chunk whose result still sits in hout[i]
+    Pinned hin[NS_MAX], hout[NS_MAX]; // per stream: the NF fields of a chunk one after the other
+    struct Pending {                  // a chunk whose result still sits in hout[i]
         bool live = false;
         size_t z0 = 0, zn = 0;
     } pend[NS_MAX];
+    const size_t inChunk = chunk * L.inLevel, outChunk = chunk * L.outLevel; // elements of one field of a chunk (dense: = chunk * layer)
     int rc = FIMEXCU_OK;
     {
         DevBuf din[NS_MAX], dout[NS_MAX];
         for (int i = 0; i < NS && rc == FIMEXCU_OK; ++i) {
-            if (!din[i].alloc(chunk * L.inLevel * sizeof(T), st[i]) || !dout[i].alloc(chunk * L.outLevel * sizeof(T), st[i]))
+            if (!din[i].alloc(NF * inChunk * sizeof(T), st[i]) || !dout[i].alloc(NF * outChunk * sizeof(T), st[i]))
                 rc = FIMEXCU_ERROR;
-            if (rc == FIMEXCU_OK && bounce_in && !(hin[i].p = host_pool_alloc(chunk * inLayer * sizeof(T))))
+            if (rc == FIMEXCU_OK && bounce_in && !(hin[i].p = host_pool_alloc(NF * inChunk * sizeof(T))))
                 rc = FIMEXCU_ERROR;
-            if (rc == FIMEXCU_OK && bounce_out && !(hout[i].p = host_pool_alloc(chunk * outLayer * sizeof(T))))
+            if (rc == FIMEXCU_OK && bounce_out && !(hout[i].p = host_pool_alloc(NF * outChunk * sizeof(T))))
                 rc = FIMEXCU_ERROR;
         }
-        // device result of a chunk -> host (the caller's array or this stream's bounce buffer, same dense layout)
-        auto copy_back = [&](int i, T* dst, size_t zn) {
+        // device result of a chunk of one field -> host (the caller's array or this stream's bounce buffer, same dense layout)
+        auto copy_back = [&](int i, const T* src, T* dst, size_t zn) {
             if (!banded)
-                return cuda_ok(cudaMemcpyAsync(dst, dout[i].p, zn * outLayer * sizeof(T), cudaMemcpyDeviceToHost, st[i]), "D2H", __FILE__, __LINE__);
+                return cuda_ok(cudaMemcpyAsync(dst, src, zn * outLayer * sizeof(T), cudaMemcpyDeviceToHost, st[i]), "D2H", __FILE__, __LINE__);
             for (const fimexcu_cache::RowBand& B : c->bands) {
                 if (B.x0 >= B.x1)
                     continue;
                 cudaMemcpy3DParms p = {};
-                p.srcPtr = make_cudaPitchedPtr(dout[i].p, outX * sizeof(T), outX * sizeof(T), outY);
+                p.srcPtr = make_cudaPitchedPtr(const_cast<T*>(src), outX * sizeof(T), outX * sizeof(T), outY);
                 p.dstPtr = make_cudaPitchedPtr(dst, outX * sizeof(T), outX * sizeof(T), outY);
                 p.srcPos = make_cudaPos(static_cast<size_t>(B.x0) * sizeof(T), static_cast<size_t>(B.y0), 0);
                 p.dstPos = p.srcPos;
@@ -2009,12 +2022,12 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
             }
             return true;
         };
-        auto drain = [&](int i) { // wait for stream i; move a finished bounced result to the caller's array
+        auto drain = [&](int i) { // wait for stream i; move a finished bounced result to the caller's arrays
             if (!cuda_ok(cudaStreamSynchronize(st[i]), "cudaStreamSynchronize", __FILE__, __LINE__))
                 rc = FIMEXCU_ERROR;
-            if (pend[i].live && rc == FIMEXCU_OK) {
-                T* dst = out + pend[i].z0 * outLayer;
-                const T* src = static_cast<const T*>(hout[i].p);
+            for (int f = 0; f < NF && pend[i].live && rc == FIMEXCU_OK; ++f) {
+                T* dst = out[f] + pend[i].z0 * outLayer;
+                const T* src = static_cast<const T*>(hout[i].p) + f * outChunk;
                 if (!banded)
                     host_copy(dst, src, pend[i].zn * outLayer * sizeof(T));
                 else
@@ -2035,7 +2048,6 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
         for (size_t z0 = 0; z0 < nz && rc == FIMEXCU_OK; z0 += chunk, ++k) {
             const size_t zn = std::min(chunk, nz - z0);
             const int i = static_cast<int>(k % NS);
-            const T* src = in + z0 * inLayer;
             if (k >= static_cast<size_t>(NS)) { // the bounce buffers of this stream must be free again
                 trace.timed(trace.wait, [&]() {
                     if (bounce_out)
@@ -2046,21 +2058,37 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
                 if (rc != FIMEXCU_OK)
                     break;
             }
-            if (bounce_in) {
-                trace.timed(trace.copy_in, [&]() { host_copy(hin[i].p, src, zn * inLayer * sizeof(T)); });
-                src = static_cast<const T*>(hin[i].p);
+            const T* din_f[NF];
+            T* dout_f[NF];
+            for (int f = 0; f < NF && rc == FIMEXCU_OK; ++f) {
+                const T* src = in[f] + z0 * inLayer;
+                if (bounce_in) {
+                    T* hb = static_cast<T*>(hin[i].p) + f * inChunk;
+                    trace.timed(trace.copy_in, [&]() { host_copy(hb, src, zn * inLayer * sizeof(T)); });
+                    src = hb;
+                }
+                const E2ETrace::clock::time_point e0 = trace.on ? E2ETrace::clock::now() : E2ETrace::clock::time_point();
+                T* d = din[i].template as<T>() + f * inChunk;
+                if (!cuda_ok(cudaMemcpyAsync(d, src, zn * inLayer * sizeof(T), cudaMemcpyHostToDevice, st[i]), "H2D", __FILE__, __LINE__))
+                    rc = FIMEXCU_ERROR;
+                din_f[f] = d;
+                dout_f[f] = dout[i].template as<T>() + f * outChunk;
+                if (trace.on)
+                    trace.enqueue += E2ETrace::ms(e0, E2ETrace::clock::now());
             }
-            const E2ETrace::clock::time_point e0 = trace.on ? E2ETrace::clock::now() : E2ETrace::clock::time_point();
-            if (!cuda_ok(cudaMemcpyAsync(din[i].p, src, zn * inLayer * sizeof(T), cudaMemcpyHostToDevice, st[i]), "H2D", __FILE__, __LINE__) ||
-                (bounce_in && !cuda_ok(cudaEventRecord(ts->h2d[i], st[i]), "cudaEventRecord", __FILE__, __LINE__))) {
-                rc = FIMEXCU_ERROR;
-                break;
-            }
-            rc = apply(din[i].template as<T>(), L, zn, dout[i].template as<T>(), st[i]);
             if (rc != FIMEXCU_OK)
                 break;
-            if (!copy_back(i, bounce_out ? static_cast<T*>(hout[i].p) : out + z0 * outLayer, zn))
+            const E2ETrace::clock::time_point e0 = trace.on ? E2ETrace::clock::now() : E2ETrace::clock::time_point();
+            if (bounce_in && !cuda_ok(cudaEventRecord(ts->h2d[i], st[i]), "cudaEventRecord", __FILE__, __LINE__)) {
                 rc = FIMEXCU_ERROR;
+                break;
+            }
+            rc = apply(din_f, L, zn, dout_f, st[i]);
+            if (rc != FIMEXCU_OK)
+                break;
+            for (int f = 0; f < NF && rc == FIMEXCU_OK; ++f)
+                if (!copy_back(i, dout_f[f], bounce_out ? static_cast<T*>(hout[i].p) + f * outChunk : out[f] + z0 * outLayer, zn))
+                    rc = FIMEXCU_ERROR;
             if (bounce_out) {
                 pend[i].live = true;
                 pend[i].z0 = z0;
@@ -2069,7 +2097,7 @@ static int cache_apply_host(const fimexcu_cache* c, const T* in, size_t size, T*
             if (trace.on)
                 trace.enqueue += E2ETrace::ms(e0, E2ETrace::clock::now());
         }
-        if (banded && bounce_in)
+        if (banded && bounce_in && rc == FIMEXCU_OK)
             start_filler();
         trace.timed(trace.drain, [&]() {
             for (int i = 0; i < NS; ++i)
@@ -2236,8 +2264,11 @@ int fimexcu_cache_apply_f(const fimexcu_cache* c, const float* in, size_t size, 
     if (!require_device() || !(c = on_current_device(c, "fimexcu_cache_apply_f")))
         return FIMEXCU_ERROR;
     const float undef = std::isnan(fillOut) ? std::numeric_limits<float>::quiet_NaN() : fillOut; // store_out<FILL>(nan_f(), fill)
-    return cache_apply_host<float>(c, in, size, out, newSize, undef, [&](const float* di, const Layout& L, size_t zn, float* dout, cudaStream_t st) {
-        return cache_apply_strided(c, di, L, zn, dout, badIn, fillOut, st);
+    const float* const ins[1] = {in};
+    float* const outs[1] = {out};
+    const float undefs[1] = {undef};
+    return cache_apply_host<float, 1>(c, ins, size, outs, newSize, undefs, [&](const float* const* di, const Layout& L, size_t zn, float* const* dout, cudaStream_t st) {
+        return cache_apply_strided(c, di[0], L, zn, dout[0], badIn, fillOut, st);
     });
 }
 
@@ -2249,8 +2280,11 @@ int fimexcu_cache_apply_i16(const fimexcu_cache* c, const int16_t* in, size_t si
     if (!require_device() || !(c = on_current_device(c, "fimexcu_cache_apply_i16")))
         return FIMEXCU_ERROR;
     const short undef = static_cast<short>(badValue); // pack_i16(NaN): ScaleValue's newFill_ (DataUtils.h:49)
-    return cache_apply_host<short>(c, in, size, out, newSize, undef, [&](const short* di, const Layout& L, size_t zn, short* dout, cudaStream_t st) {
-        return cache_apply_strided_i16(c, di, L, zn, dout, badValue, st);
+    const short* const ins[1] = {in};
+    short* const outs[1] = {out};
+    const short undefs[1] = {undef};
+    return cache_apply_host<short, 1>(c, ins, size, outs, newSize, undefs, [&](const short* const* di, const Layout& L, size_t zn, short* const* dout, cudaStream_t st) {
+        return cache_apply_strided_i16(c, di[0], L, zn, dout[0], badValue, st);
     });
 }
 
@@ -2432,25 +2466,18 @@ int fimexcu_cache_apply_uv_f(const fimexcu_cache* c, const fimexcu_vecrot* r, co
         FXCU_FAIL("fimexcu_cache_apply_uv_f: null cache");
     if (!require_device() || !(c = on_current_device(c, "fimexcu_cache_apply_uv_f")))
         return FIMEXCU_ERROR;
-    const size_t inLayer = c->inX * c->inY, outLayer = c->outX * c->outY;
-    const size_t nz = size / inLayer;
-    if (newSize)
-        *newSize = nz * outLayer;
-    if (nz == 0 || outLayer == 0)
-        return FIMEXCU_OK;
-    DevBuf du, dv, ou, ov;
-    const size_t ib = nz * inLayer * sizeof(float), ob = nz * outLayer * sizeof(float);
-    if (!du.alloc(ib, nullptr) || !dv.alloc(ib, nullptr) || !ou.alloc(ob, nullptr) || !ov.alloc(ob, nullptr))
+    if (r && !(r = on_current_device(r, "fimexcu_cache_apply_uv_f (rotation matrix)")))
         return FIMEXCU_ERROR;
-    FXCU_CUDA(cudaMemcpyAsync(du.p, u_in, ib, cudaMemcpyHostToDevice, nullptr));
-    FXCU_CUDA(cudaMemcpyAsync(dv.p, v_in, ib, cudaMemcpyHostToDevice, nullptr));
-    if (fimexcu_cache_apply_uv_dev_f(c, r, du.as<float>(), dv.as<float>(), nz, ou.as<float>(), ov.as<float>(), badU, badV, fillU, fillV, nullptr) !=
-        FIMEXCU_OK)
-        return FIMEXCU_ERROR;
-    FXCU_CUDA(cudaMemcpyAsync(u_out, ou.p, ob, cudaMemcpyDeviceToHost, nullptr));
-    FXCU_CUDA(cudaMemcpyAsync(v_out, ov.p, ob, cudaMemcpyDeviceToHost, nullptr));
-    FXCU_CUDA(cudaStreamSynchronize(nullptr));
-    return FIMEXCU_OK;
+    // the level chunks of both components go through the fused kernel together (same pipelining, bounce buffers and row bands as
+    // the scalar entry point)
+    const float* const ins[2] = {u_in, v_in};
+    float* const outs[2] = {u_out, v_out};
+    const float nanv = std::numeric_limits<float>::quiet_NaN();
+    const float undefs[2] = {std::isnan(fillU) ? nanv : fillU, std::isnan(fillV) ? nanv : fillV};
+    return cache_apply_host<float, 2>(c, ins, size, outs, newSize, undefs,
+                                      [&](const float* const* di, const Layout& L, size_t zn, float* const* dout, cudaStream_t st) {
+                                          return cache_apply_uv_strided(c, r, di[0], di[1], L, zn, dout[0], dout[1], badU, badV, fillU, fillV, st);
+                                      });
 }
 
 void fimexcu_cache_destroy(fimexcu_cache* c) { delete c; }

@@ -235,7 +235,9 @@ void fimexcu_vecrot_destroy(fimexcu_vecrot* r);
 int fimexcu_vecrot_replicate(fimexcu_vecrot* r, int n_devices, const int* device_ids);
 /* The vector branch of CDMInterpolator::getDataSlice (src/CDMInterpolator.cc:232-259) as ONE pass:
  * interpolate u and v with the same cache and rotate them, instead of the reference's two
- * interpolateValues() calls per component plus reprojectValues().  r may be NULL (no rotation). */
+ * interpolateValues() calls per component plus reprojectValues().  r may be NULL (no rotation).  The host form is pipelined like
+ * fimexcu_cache_apply_f: level chunks of both components on rotating streams, pageable arrays through pinned bounce chunks, only
+ * the row bands of the target that can hold data copied back (fimexcu_cache_row_bands). */
 int fimexcu_cache_apply_uv_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* u_in, const float* v_in, size_t size, float* u_out,
                              float* v_out, size_t* newSize, float badU, float badV, float fillU, float fillV);
 int fimexcu_cache_apply_uv_dev_f(const fimexcu_cache* c, const fimexcu_vecrot* r, const float* d_u_in, const float* d_v_in, size_t nz,

@@ -612,3 +612,50 @@ def test_host_packed_result_comes_back_in_row_bands(fx):
     want = ol.o_packed_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, raw, bad)
     got = ci.interpolateValuesPacked(ci.reduceInput(raw, in_x, in_y), bad)
     assert got.dtype == np.int16 and np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("rotate", [True, False])
+@pytest.mark.parametrize("fills", [(float("nan"), float("nan")), (-999.5, 1e20)])
+def test_host_vector_result_comes_back_in_row_bands(fx, oracle, rotate, fills):
+    """the vector branch through the host entry point (fimexcu_cache_apply_uv_f): level chunks of both components through the fused
+    kernel, row bands on the way back, per-component fill values; several chunks (34 MB of results)"""
+    from fimex_b200.interpolation import interpolateVectorValues
+    rng = np.random.default_rng(500 + int(rotate))
+    in_x, in_y, out_x, out_y, nz = 110, 80, 1000, 600, 7
+    gx, gy = np.meshgrid(np.arange(out_x, dtype=np.float64), np.arange(out_y, dtype=np.float64))
+    px = -25.0 + 0.16 * gx + 0.02 * gy
+    py = -12.0 + 0.17 * gy - 0.015 * gx
+    ang = rng.uniform(-np.pi, np.pi, out_x * out_y)
+    m3 = np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy()
+    u = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    v = rng.normal(size=(nz, in_y, in_x)).astype(np.float32)
+    u[rng.random(u.shape) < 0.02] = np.nan
+    ci = fx.createCachedInterpolation("x", "y", ol.BILINEAR, px, py, in_x, in_y, out_x, out_y)
+    bands, frac = ci.rowBands()
+    assert bands and frac < 0.9
+    cvr = fx.CachedVectorReprojection(m3, out_x, out_y) if rotate else None
+    wu, _ = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, u)
+    wv, _ = ol.o_cached_apply(ol.BILINEAR, px, py, in_x, in_y, out_x, out_y, v)
+    if rotate:
+        oracle.orc_vector_reproject_values_by_matrix_f(dp(m3), out_x * out_y, fp(wu), fp(wv), nz)
+    fu, fv = fills
+    if not np.isnan(fu):
+        wu = np.where(np.isnan(wu), np.float32(fu), wu)
+        wv = np.where(np.isnan(wv), np.float32(fv), wv)
+    su, sv = ci.reduceInput(u, in_x, in_y), ci.reduceInput(v, in_x, in_y)
+    gu, gv = interpolateVectorValues(ci, cvr, su, sv, fillU=fu, fillV=fv)   # pageable arrays on both sides
+    assert _eq(gu, wu) and _eq(gv, wv)
+    lib = fx.lib
+    n_out = wu.size
+    hu, hv = lib.fimexcu_host_alloc(n_out * 4), lib.fimexcu_host_alloc(n_out * 4)
+    assert hu and hv
+    C.memset(hu, 0x5a, n_out * 4)
+    C.memset(hv, 0x5a, n_out * 4)
+    new = C.c_size_t()
+    fx._lib.check(lib.fimexcu_cache_apply_uv_f(ci._h, cvr._h if cvr else None, su.ctypes.data, sv.ctypes.data, su.size, hu, hv, C.byref(new),
+                                               float("nan"), float("nan"), fu, fv), "apply_uv")
+    au = np.frombuffer((C.c_float * n_out).from_address(hu), dtype=np.float32).reshape(wu.shape)
+    av = np.frombuffer((C.c_float * n_out).from_address(hv), dtype=np.float32).reshape(wv.shape)
+    assert new.value == n_out and _eq(au, wu) and _eq(av, wv)
+    lib.fimexcu_host_free(hu)
+    lib.fimexcu_host_free(hv)
