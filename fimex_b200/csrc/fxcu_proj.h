@@ -4,7 +4,8 @@
 // (proj_create_crs_to_crs / proj_trans_generic).  PROJ is not part of the reference tree; the formulas are the published
 // ones PROJ documents for each operation (Snyder, USGS PP 1395; Poder/Engsager for the transverse Mercator series):
 // longlat, lcc (1SP/2SP, sphere + ellipsoid), stere (polar / oblique / equatorial, sphere + ellipsoid), ob_tran over longlat
-// (rotated lat/lon), merc, tmerc / utm (extended series on the ellipsoid, closed form on the sphere), laea.
+// (rotated lat/lon), merc, tmerc / utm (extended series on the ellipsoid, closed form on the sphere), laea; fxcu_proj3.h adds
+// sinu, cea, aea, aeqd, ortho, nsper, geos and omerc.
 // One `Crs` is a plain struct passed to kernels by value; every function is __host__ __device__ so that the few scalar
 // evaluations the host needs use the same code.
 #pragma once
@@ -19,7 +20,7 @@
 
 namespace fxproj {
 
-enum Kind { LONGLAT = 0, LCC, STERE, OB_TRAN, MERC, TMERC, LAEA };
+enum Kind { LONGLAT = 0, LCC, STERE, OB_TRAN, MERC, TMERC, LAEA, SINU, CEA, AEA, AEQD, ORTHO, NSPER, GEOS, OMERC };
 enum Mode { S_POLE = 0, N_POLE = 1, OBLIQ = 2, EQUIT = 3 };
 
 struct Crs {

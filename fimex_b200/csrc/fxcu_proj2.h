@@ -319,6 +319,10 @@ FXP_HD bool laea_inv(const Crs& c, double x, double y, double& lam, double& phi)
     return true;
 }
 
+} // namespace fxproj
+#include "fxcu_proj3.h"
+namespace fxproj {
+
 // ------------------------------------------------------------------ dispatch
 // geographic radians -> CRS coordinates (metres, or degrees for geographic CRS)
 FXP_HD bool crs_fwd(const Crs& c, double lam, double phi, double& x, double& y)
@@ -346,6 +350,14 @@ FXP_HD bool crs_fwd(const Crs& c, double lam, double phi, double& x, double& y)
     case MERC: ok = merc_fwd(c, lam, phi, px, py); break;
     case TMERC: ok = tmerc_fwd(c, lam, phi, px, py); break;
     case LAEA: ok = laea_fwd(c, lam, phi, px, py); break;
+    case SINU: ok = sinu_fwd(c, lam, phi, px, py); break;
+    case CEA: ok = cea_fwd(c, lam, phi, px, py); break;
+    case AEA: ok = aea_fwd(c, lam, phi, px, py); break;
+    case AEQD: ok = aeqd_fwd(c, lam, phi, px, py); break;
+    case ORTHO: ok = ortho_fwd(c, lam, phi, px, py); break;
+    case NSPER: ok = nsper_fwd(c, lam, phi, px, py); break;
+    case GEOS: ok = geos_fwd(c, lam, phi, px, py); break;
+    case OMERC: ok = omerc_fwd(c, lam, phi, px, py); break;
     default: ok = false; break;
     }
     if (!ok || !isfinite(px) || !isfinite(py))
@@ -381,6 +393,14 @@ FXP_HD bool crs_inv(const Crs& c, double x, double y, double& lam, double& phi)
         case MERC: ok = merc_inv(c, px, py, l, p); break;
         case TMERC: ok = tmerc_inv(c, px, py, l, p); break;
         case LAEA: ok = laea_inv(c, px, py, l, p); break;
+        case SINU: ok = sinu_inv(c, px, py, l, p); break;
+        case CEA: ok = cea_inv(c, px, py, l, p); break;
+        case AEA: ok = aea_inv(c, px, py, l, p); break;
+        case AEQD: ok = aeqd_inv(c, px, py, l, p); break;
+        case ORTHO: ok = ortho_inv(c, px, py, l, p); break;
+        case NSPER: ok = nsper_inv(c, px, py, l, p); break;
+        case GEOS: ok = geos_inv(c, px, py, l, p); break;
+        case OMERC: ok = omerc_inv(c, px, py, l, p); break;
         default: ok = false; break;
         }
     }

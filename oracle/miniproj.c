@@ -1016,6 +1016,8 @@ static int mp_laea_inv(const miniproj_crs* c, double x, double y, double* lam, d
 }
 
 /* ------------------------------------------------------------------ parse */
+#include "miniproj_more.inc"
+
 int miniproj_parse(const char* def, miniproj_crs* c, char* err, size_t errlen)
 {
     mp_kv kv[48];
@@ -1127,6 +1129,54 @@ int miniproj_parse(const char* def, miniproj_crs* c, char* err, size_t errlen)
         c->kind = MP_LAEA;
         return mp_laea_setup(c);
     }
+    if (strcmp(proj, "sinu") == 0) {
+        c->kind = MP_SINU;
+        return 0;
+    }
+    if (strcmp(proj, "cea") == 0) {
+        c->kind = MP_CEA;
+        return mq_cea_setup(kv, n, c, err, errlen);
+    }
+    if (strcmp(proj, "aea") == 0) {
+        c->kind = MP_AEA;
+        return mq_aea_setup(kv, n, c, err, errlen);
+    }
+    if (strcmp(proj, "aeqd") == 0 || strcmp(proj, "ortho") == 0 || strcmp(proj, "nsper") == 0) {
+        c->kind = proj[0] == 'o' ? MP_ORTHO : (proj[0] == 'n' ? MP_NSPER : MP_AEQD);
+        c->mode = mq_aspect(c->phi0);
+        if (c->kind == MP_NSPER) {
+            const double h = mp_num(kv, n, "h", 0.);
+            if (!(h > 0)) {
+                snprintf(err, errlen, "nsper: +h must be positive");
+                return -1;
+            }
+            c->q[0] = 1. + h * c->ra;
+            c->es = c->e = 0.; /* spherical by definition: PROJ drops the flattening here */
+            c->one_es = c->rone_es = 1.;
+            c->ellips = 0;
+        } else if (c->ellips && (c->kind == MP_ORTHO || c->mode == ST_OBLIQ || c->mode == ST_EQUIT)) {
+            snprintf(err, errlen, "%s: this aspect is not implemented on an ellipsoid", proj);
+            return -1;
+        }
+        return 0;
+    }
+    if (strcmp(proj, "geos") == 0) {
+        c->kind = MP_GEOS;
+        const double h = mp_num(kv, n, "h", 0.);
+        const char* sweep = mp_get(kv, n, "sweep");
+        if (!(h > 0) || c->phi0 != 0. || (sweep && strcmp(sweep, "x") != 0 && strcmp(sweep, "y") != 0)) {
+            snprintf(err, errlen, "geos: needs +h > 0, lat_0 = 0, +sweep=x|y");
+            return -1;
+        }
+        c->mode = (sweep && sweep[0] == 'x') ? 1 : 0;
+        c->q[0] = 1. + h * c->ra;
+        c->q[1] = c->one_es;
+        return 0;
+    }
+    if (strcmp(proj, "omerc") == 0) {
+        c->kind = MP_OMERC;
+        return mq_omerc_setup(kv, n, c, err, errlen);
+    }
     snprintf(err, errlen, "unsupported projection '%s'", proj);
     return -1;
 }
@@ -1157,6 +1207,14 @@ int miniproj_fwd(const miniproj_crs* c, double lam, double phi, double* x, doubl
     case MP_MERC: rc = mp_merc_fwd(c, lam, phi, &px, &py); break;
     case MP_TMERC: rc = mp_tmerc_fwd(c, lam, phi, &px, &py); break;
     case MP_LAEA: rc = mp_laea_fwd(c, lam, phi, &px, &py); break;
+    case MP_SINU: rc = mq_sinu_fwd(c, lam, phi, &px, &py); break;
+    case MP_CEA: rc = mq_cea_fwd(c, lam, phi, &px, &py); break;
+    case MP_AEA: rc = mq_aea_fwd(c, lam, phi, &px, &py); break;
+    case MP_AEQD: rc = mq_aeqd_fwd(c, lam, phi, &px, &py); break;
+    case MP_ORTHO: rc = mq_ortho_fwd(c, lam, phi, &px, &py); break;
+    case MP_NSPER: rc = mq_nsper_fwd(c, lam, phi, &px, &py); break;
+    case MP_GEOS: rc = mq_geos_fwd(c, lam, phi, &px, &py); break;
+    case MP_OMERC: rc = mq_omerc_fwd(c, lam, phi, &px, &py); break;
     default: rc = -1; break;
     }
     if (rc || !isfinite(px) || !isfinite(py))
@@ -1193,6 +1251,14 @@ int miniproj_inv(const miniproj_crs* c, double x, double y, double* lam, double*
         case MP_MERC: rc = mp_merc_inv(c, px, py, &l, &p); break;
         case MP_TMERC: rc = mp_tmerc_inv(c, px, py, &l, &p); break;
         case MP_LAEA: rc = mp_laea_inv(c, px, py, &l, &p); break;
+        case MP_SINU: rc = mq_sinu_inv(c, px, py, &l, &p); break;
+        case MP_CEA: rc = mq_cea_inv(c, px, py, &l, &p); break;
+        case MP_AEA: rc = mq_aea_inv(c, px, py, &l, &p); break;
+        case MP_AEQD: rc = mq_aeqd_inv(c, px, py, &l, &p); break;
+        case MP_ORTHO: rc = mq_ortho_inv(c, px, py, &l, &p); break;
+        case MP_NSPER: rc = mq_nsper_inv(c, px, py, &l, &p); break;
+        case MP_GEOS: rc = mq_geos_inv(c, px, py, &l, &p); break;
+        case MP_OMERC: rc = mq_omerc_inv(c, px, py, &l, &p); break;
         default: rc = -1; break;
         }
     }

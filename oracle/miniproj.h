@@ -6,16 +6,19 @@
  * >= 6.2); it is absent from this image.  The reference reaches it only through src/reproject.cc:56-116
  * (proj_create_crs_to_crs, proj_trans_generic, proj_degree_input/output).  The formulas below follow the
  * published algorithms PROJ implements (Snyder, "Map Projections - A Working Manual", USGS PP 1395; PROJ's
- * documented lcc / stere / merc / ob_tran / tmerc(Poder-Engsager) / laea operations).
+ * documented lcc / stere / merc / ob_tran / tmerc(Poder-Engsager) / laea operations; miniproj_more.inc adds sinu, cea,
+ * aea, aeqd, ortho, nsper, geos and omerc).
  *
  * PINNED against real PROJ output for ob_tran, lcc (sphere) and polar stere (sphere): the reference's NetCDF
  * fixtures store PROJ-generated longitude/latitude fields for six projected grids; tests/test_proj_pins.py
  * reproduces them to 3e-14 degree in both directions (fixture tests/golden/reference_proj_pins.npz).
- * PARITY UNPINNED for the ellipsoidal forms, merc, tmerc/utm and laea: the reference has no test that fixes
- * reproject_axes output numerically (test/testInterpolation.cc:260-272 only checks "> 89") and no fixture
- * with those projections.  They are pinned by round trips fwd(inv(x)) <= 1e-9 deg / 1e-6 m, closed-form
- * corner coordinates of the MEPS grid, the EMEP cell test of test/testInterpolation.cc:274-385 and the
- * 90/180 degree rotation tests (:387-628), all replayed in tests/test_oracle_proj.py.
+ * Every projection, on the sphere and on an ellipsoid, is also pinned against the published worked examples of
+ * Snyder's manual (Appendix A; 21 examples, forward within 0.05 m and back: tests/test_more_projections.py).
+ * PARITY UNPINNED only below those examples' 0.1 m for the ellipsoidal forms, and for geos / omerc (limiting cases
+ * and an independent formulation instead): the reference has no test that fixes reproject_axes output numerically
+ * (test/testInterpolation.cc:260-272 only checks "> 89").  Further pins: round trips fwd(inv(x)) <= 1e-9 deg /
+ * 1e-6 m, closed-form corner coordinates of the MEPS grid, the EMEP cell test of test/testInterpolation.cc:274-385
+ * and the 90/180 degree rotation tests (:387-628), all replayed in tests/test_oracle_proj.py.
  *
  * Transform semantics (crs -> crs): source inverse projection to geographic lon/lat on the source
  * figure, NO datum shift (what proj4's pj_transform does for an unknown datum and PROJ >= 6 does as a
@@ -32,7 +35,7 @@
 extern "C" {
 #endif
 
-enum { MP_LONGLAT = 0, MP_LCC, MP_STERE, MP_OB_TRAN, MP_MERC, MP_TMERC, MP_LAEA };
+enum { MP_LONGLAT = 0, MP_LCC, MP_STERE, MP_OB_TRAN, MP_MERC, MP_TMERC, MP_LAEA, MP_SINU, MP_CEA, MP_AEA, MP_AEQD, MP_ORTHO, MP_NSPER, MP_GEOS, MP_OMERC };
 
 typedef struct {
     int kind;

@@ -12,7 +12,8 @@ Observed: 3e-14 degree for all four fixtures with floating-point axes -- the las
 as PROJ for ob_tran (rotated lon/lat), lcc (1 standard parallel, sphere) and polar stere (sphere): the three projection families
 the bench workloads and BASELINE.json's configs use.  Two fixtures (coordTest.nc, merge_target_top.nc) store their axes as
 integers rounded to the metre after lon/lat had been generated; they pin to that rounding only (1 m, 1e-5 degree).
-Ellipsoidal forms, merc/tmerc/utm/laea have no PROJ output anywhere in the reference tree: those stay "parity unpinned"."""
+Ellipsoidal forms and the other projections have no PROJ output anywhere in the reference tree; they are pinned against Snyder's
+published worked examples instead (tests/test_more_projections.py)."""
 import ctypes as C
 import os
 
