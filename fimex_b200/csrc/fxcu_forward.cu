@@ -222,11 +222,82 @@ __global__ void __launch_bounds__(256) fwd_apply_kernel(const FwdParams P)
 }
 
 // ---- round-2 forms of the apply -----------------------------------------------------------------------------------------------
+// One block of NK <= ZB levels of one target cell.  FULL: NK == ZB is known at compile time (no per-level tests).  BAD: the input
+// carries a bad value that counts as NaN.  Source offsets are 32-bit (the launch guarantees ZB * inLayer < 2^31).
+template <int KIND, bool UNDEF, bool BAD, int ZB, bool FULL>
+__device__ __forceinline__ void fwd_reduce_block(const FwdParams& P, const float* __restrict__ src, int s0, int s1, int nk, float* __restrict__ dst, bool has_fill)
+{
+    const unsigned lay = static_cast<unsigned>(P.inLayer);
+    float val[ZB];
+    int cnt[ZB];
+#pragma unroll
+    for (int q = 0; q < ZB; ++q) {
+        val[q] = 0.f;
+        cnt[q] = 0;
+    }
+    auto load = [&](unsigned idx, int q) {
+        float v = (FULL || q < nk) ? __ldg(src + (idx + static_cast<unsigned>(q) * lay)) : nan_f();
+        if (BAD && v == P.bad)
+            v = nan_f();
+        return v;
+    };
+    auto push = [&](const float (&f)[ZB]) {
+#pragma unroll
+        for (int q = 0; q < ZB; ++q) {
+            const bool take = UNDEF || !isnan(f[q]);
+            if (KIND <= 1) {
+                if (take)
+                    val[q] = __fadd_rn(val[q], f[q]); // AggSum::push
+            } else if (KIND == 3) {
+                if (take && (cnt[q] == 0 || f[q] > val[q]))
+                    val[q] = f[q]; // AggMax::push
+            } else {
+                if (take && (cnt[q] == 0 || f[q] < val[q]))
+                    val[q] = f[q]; // AggMin::push
+            }
+            if (take)
+                ++cnt[q];
+        }
+    };
+    int k = s0;
+    for (; k + 2 <= s1; k += 2) { // two sources at a time: their index loads, then all their gathers, are in flight together
+        const unsigned i0 = static_cast<unsigned>(__ldg(P.segIdx + k)), i1 = static_cast<unsigned>(__ldg(P.segIdx + k + 1));
+        float f0[ZB], f1[ZB];
+#pragma unroll
+        for (int q = 0; q < ZB; ++q) {
+            f0[q] = load(i0, q);
+            f1[q] = load(i1, q);
+        }
+        push(f0);
+        push(f1);
+    }
+    if (k < s1) {
+        const unsigned i0 = static_cast<unsigned>(__ldg(P.segIdx + k));
+        float f[ZB];
+#pragma unroll
+        for (int q = 0; q < ZB; ++q)
+            f[q] = load(i0, q);
+        push(f);
+    }
+    const unsigned nout = static_cast<unsigned>(P.nout);
+#pragma unroll
+    for (int q = 0; q < ZB; ++q) {
+        if (!FULL && q >= nk)
+            break;
+        float r = nan_f();
+        if (cnt[q] != 0)
+            r = KIND == 1 ? __fdiv_rn(val[q], static_cast<float>(cnt[q])) : val[q]; // mean: val / count (:90)
+        if (has_fill && isnan(r))
+            r = P.fill;
+        __stcs(dst + static_cast<unsigned>(q) * nout, r);
+    }
+}
+
 // Sum / mean / min / max, thread per target cell, the sources in the OUTER loop and a block of ZB levels in registers: the segment's
 // source indices are read once per level block instead of once per level, and ZB independent gathers are in flight per source.
 // Every level's values are still pushed in ascending source order, so the f32 running sums are the reference's bit for bit
-// (CachedForwardInterpolation.cc:79-86, 143-158).
-template <int KIND, bool UNDEF, int ZB>
+// (CachedForwardInterpolation.cc:79-86, 143-158).  The launch guarantees ZB * inLayer and ZB * nout < 2^31.
+template <int KIND, bool UNDEF, bool BAD, int ZB>
 __global__ void __launch_bounds__(256) fwd_reduce_kernel(const FwdParams P)
 {
     const size_t o = blockIdx.x * 256ull + threadIdx.x;
@@ -234,67 +305,14 @@ __global__ void __launch_bounds__(256) fwd_reduce_kernel(const FwdParams P)
         return;
     const int z0 = blockIdx.y * P.zchunk, z1 = min(P.nz, z0 + P.zchunk);
     const int s0 = P.segStart[o], s1 = P.segStart[o + 1];
-    const bool has_bad = !isnan(P.bad), has_fill = !isnan(P.fill);
-    for (int zb = z0; zb < z1; zb += ZB) {
-        const int nk = min(ZB, z1 - zb);
-        const float* src = P.in + static_cast<size_t>(zb) * P.inLayer;
-        float val[ZB];
-        int cnt[ZB];
-#pragma unroll
-        for (int q = 0; q < ZB; ++q) {
-            val[q] = 0.f;
-            cnt[q] = 0;
-        }
-        auto push = [&](const float (&f)[ZB]) {
-#pragma unroll
-            for (int q = 0; q < ZB; ++q) {
-                if (!UNDEF && isnan(f[q]))
-                    continue;
-                if (KIND <= 1)
-                    val[q] = __fadd_rn(val[q], f[q]); // AggSum::push
-                else if (KIND == 3) {
-                    if (cnt[q] == 0 || f[q] > val[q])
-                        val[q] = f[q]; // AggMax::push
-                } else {
-                    if (cnt[q] == 0 || f[q] < val[q])
-                        val[q] = f[q]; // AggMin::push
-                }
-                ++cnt[q];
-            }
-        };
-        int k = s0;
-        for (; k + 2 <= s1; k += 2) { // two sources at a time: their index loads, then all their gathers, are in flight together
-            const float* p0 = src + P.segIdx[k];
-            const float* p1 = src + P.segIdx[k + 1];
-            float f0[ZB], f1[ZB];
-#pragma unroll
-            for (int q = 0; q < ZB; ++q) {
-                f0[q] = q < nk ? fwd_load(p0 + static_cast<size_t>(q) * P.inLayer, P.bad, has_bad) : nan_f();
-                f1[q] = q < nk ? fwd_load(p1 + static_cast<size_t>(q) * P.inLayer, P.bad, has_bad) : nan_f();
-            }
-            push(f0);
-            push(f1);
-        }
-        if (k < s1) {
-            const float* p = src + P.segIdx[k];
-            float f[ZB];
-#pragma unroll
-            for (int q = 0; q < ZB; ++q)
-                f[q] = q < nk ? fwd_load(p + static_cast<size_t>(q) * P.inLayer, P.bad, has_bad) : nan_f();
-            push(f);
-        }
-#pragma unroll
-        for (int q = 0; q < ZB; ++q) {
-            if (q >= nk)
-                break;
-            float r = nan_f();
-            if (cnt[q] != 0)
-                r = KIND == 1 ? __fdiv_rn(val[q], static_cast<float>(cnt[q])) : val[q]; // mean: val / count (:90)
-            if (has_fill && isnan(r))
-                r = P.fill;
-            __stcs(P.out + static_cast<size_t>(zb + q) * P.nout + o, r);
-        }
-    }
+    const bool has_fill = !isnan(P.fill);
+    const float* src = P.in + static_cast<size_t>(z0) * P.inLayer;
+    float* dst = P.out + static_cast<size_t>(z0) * P.nout + o;
+    int zb = z0;
+    for (; zb + ZB <= z1; zb += ZB, src += static_cast<size_t>(ZB) * P.inLayer, dst += static_cast<size_t>(ZB) * P.nout)
+        fwd_reduce_block<KIND, UNDEF, BAD, ZB, true>(P, src, s0, s1, ZB, dst, has_fill);
+    if (zb < z1)
+        fwd_reduce_block<KIND, UNDEF, BAD, ZB, false>(P, src, s0, s1, z1 - zb, dst, has_fill);
 }
 
 // Min / max without the undef flavour do not depend on the order of the values: long segments (coarse targets: hundreds of sources
@@ -724,17 +742,28 @@ int fimexcu_forward_apply_dev_f(const fimexcu_forward* f, const float* d_in, siz
             fwd_minmax_warp_kernel<true, 4><<<gw, 256, 0, st>>>(P);
         else
             fwd_minmax_warp_kernel<false, 4><<<gw, 256, 0, st>>>(P);
+    } else if (static_cast<size_t>(ZB) * P.inLayer >= (size_t(1) << 31) || static_cast<size_t>(ZB) * nout >= (size_t(1) << 31)) {
+        fwd_apply_kernel<<<grid, 256, 0, st>>>(P); // grids beyond the 32-bit offsets of the level-blocked kernel: the general form
     } else {
+        // (f->kind: 0 sum, 1 mean, 3 max, 4 min) x undef x "the input has a bad value"
+        const bool bad = !std::isnan(P.bad);
+#define FXCU_FWD_CASE(K, U) \
+    if (bad) \
+        fwd_reduce_kernel<K, U, true, ZB><<<grid, 256, 0, st>>>(P); \
+    else \
+        fwd_reduce_kernel<K, U, false, ZB><<<grid, 256, 0, st>>>(P); \
+    break;
         switch (f->kind * 2 + (f->undef ? 1 : 0)) {
-        case 0: fwd_reduce_kernel<0, false, ZB><<<grid, 256, 0, st>>>(P); break;
-        case 1: fwd_reduce_kernel<0, true, ZB><<<grid, 256, 0, st>>>(P); break;
-        case 2: fwd_reduce_kernel<1, false, ZB><<<grid, 256, 0, st>>>(P); break;
-        case 3: fwd_reduce_kernel<1, true, ZB><<<grid, 256, 0, st>>>(P); break;
-        case 6: fwd_reduce_kernel<3, false, ZB><<<grid, 256, 0, st>>>(P); break;
-        case 7: fwd_reduce_kernel<3, true, ZB><<<grid, 256, 0, st>>>(P); break;
-        case 8: fwd_reduce_kernel<4, false, ZB><<<grid, 256, 0, st>>>(P); break;
-        default: fwd_reduce_kernel<4, true, ZB><<<grid, 256, 0, st>>>(P); break;
+        case 0: FXCU_FWD_CASE(0, false)
+        case 1: FXCU_FWD_CASE(0, true)
+        case 2: FXCU_FWD_CASE(1, false)
+        case 3: FXCU_FWD_CASE(1, true)
+        case 6: FXCU_FWD_CASE(3, false)
+        case 7: FXCU_FWD_CASE(3, true)
+        case 8: FXCU_FWD_CASE(4, false)
+        default: FXCU_FWD_CASE(4, true)
         }
+#undef FXCU_FWD_CASE
     }
     FXCU_CUDA(cudaGetLastError());
     return FIMEXCU_OK;
