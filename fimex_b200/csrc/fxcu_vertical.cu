@@ -868,6 +868,15 @@ __global__ void __launch_bounds__(256) hybrid_table_kernel(const double* __restr
     __shared__ double s_lo, s_w;
     __shared__ int s_first, s_last;
     __shared__ unsigned long long s_total;
+    // the coefficients are read many times by one thread (the monotonicity proof) and by all (the searches): staged once, so that
+    // the serial part does not pay a trip to the L2 per level (it made this kernel 24 us long: longer than a member's main kernel)
+    extern __shared__ double s_coef[]; // ap[nzi], b[nzi]
+    double* s_ap = s_coef;
+    double* s_b = s_coef + nzi;
+    for (int k = threadIdx.x; k < nzi; k += 256) {
+        s_ap[k] = ap[k];
+        s_b[k] = b[k];
+    }
     if (threadIdx.x == 0) {
         s_first = PS_HIST_BINS;
         s_last = -1;
@@ -925,7 +934,7 @@ __global__ void __launch_bounds__(256) hybrid_table_kernel(const double* __restr
             const double a0 = static_cast<double>(decode_ordered(i_lo)) * ps_scale, a1 = static_cast<double>(decode_ordered(i_hi)) * ps_scale;
             lo = fmin(a0, a1);
             hi = fmax(a0, a1);
-            dir = hybrid_direction(ap, b, nzi, lo, hi);
+            dir = hybrid_direction(s_ap, s_b, nzi, lo, hi);
         }
         const double w = dir ? (hi - lo) / nbins : 0.;
         s_dir = dir;
@@ -949,7 +958,7 @@ __global__ void __launch_bounds__(256) hybrid_table_kernel(const double* __restr
             int lo = 0, hi = nzi; // count of k with sg*c(k) <= x: c is increasing in walk order
             while (lo < hi) {
                 const int mid = (lo + hi) >> 1;
-                const float v = sg * __double2float_rn(__dadd_rn(ap[mid], __dmul_rn(b[mid], ps)));
+                const float v = sg * __double2float_rn(__dadd_rn(s_ap[mid], __dmul_rn(s_b[mid], ps)));
                 if (v <= x)
                     lo = mid + 1;
                 else
@@ -1553,7 +1562,7 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
         if (nps)
             ps_hist_kernel<<<static_cast<unsigned>(std::min<size_t>((nps + 255) / 256, static_cast<size_t>(sm_count()) * 8)), 256, 0, s>>>(
                 d_ps, nps, reinterpret_cast<unsigned*>(base));
-        hybrid_table_kernel<<<1, 256, 0, s>>>(P.ap, P.b, static_cast<int>(nzi), P.levels, static_cast<int>(nzo), reinterpret_cast<const unsigned*>(base),
+        hybrid_table_kernel<<<1, 256, 2 * nzi * sizeof(double), s>>>(P.ap, P.b, static_cast<int>(nzi), P.levels, static_cast<int>(nzo), reinterpret_cast<const unsigned*>(base),
                                                ps_scale, nbins, reinterpret_cast<HybridTableHeader*>(base + hdr_off),
                                                reinterpret_cast<unsigned short*>(base + tab_off));
         const dim3 blocks(static_cast<unsigned>((nInner + HT * HT_CHUNKS - 1) / (HT * HT_CHUNKS)), static_cast<unsigned>(nOuter));
