@@ -375,15 +375,105 @@ __device__ __forceinline__ unsigned ordered_bits(float v)
     const unsigned b = __float_as_uint(v);
     return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
 }
+// Segments of at most NMAX <= 8 values (a fine target: two to six sources per cell) never leave the registers: the source offsets are
+// read once for all levels, a level's values are sorted by a fixed network of compare-exchanges (missing and skipped values count
+// as +inf behind the real ones) and the element of rank n/2 is picked.  Same result as the counting form below.
+template <int N> __device__ __forceinline__ void sort_network(float (&v)[N])
+{
+    auto ce = [&](int i, int j) {
+        const float lo = fminf(v[i], v[j]), hi = fmaxf(v[i], v[j]);
+        v[i] = lo;
+        v[j] = hi;
+    };
+    if (N == 2) {
+        ce(0, 1);
+    } else if (N == 4) {
+        ce(0, 1); ce(2, 3); ce(0, 2); ce(1, 3); ce(1, 2);
+    } else { // 8 inputs, 19 compare-exchanges
+        ce(0, 1); ce(2, 3); ce(4, 5); ce(6, 7);
+        ce(0, 2); ce(1, 3); ce(4, 6); ce(5, 7);
+        ce(1, 2); ce(5, 6); ce(0, 4); ce(3, 7);
+        ce(1, 5); ce(2, 6);
+        ce(1, 4); ce(3, 6);
+        ce(2, 4); ce(3, 5);
+        ce(3, 4);
+    }
+}
+template <bool UNDEF, int NMAX>
+__device__ __forceinline__ void median_small(const FwdParams& P, size_t o, int s0, int nseg, int z0, int z1, bool has_bad, bool has_fill)
+{
+    static_assert(NMAX == 2 || NMAX == 4 || NMAX == 8, "sorting networks for 2, 4 and 8 values");
+    unsigned idx[NMAX];
+#pragma unroll
+    for (int j = 0; j < NMAX; ++j)
+        idx[j] = j < nseg ? static_cast<unsigned>(__ldg(P.segIdx + s0 + j)) : 0u;
+    const float* src = P.in + static_cast<size_t>(z0) * P.inLayer;
+    float* dst = P.out + static_cast<size_t>(z0) * P.nout + o;
+    for (int z = z0; z < z1; ++z, src += P.inLayer, dst += P.nout) {
+        float v[NMAX];
+        int n = 0;
+        bool any_nan = false;
+#pragma unroll
+        for (int j = 0; j < NMAX; ++j) {
+            float f = INFINITY;
+            if (j < nseg) {
+                f = __ldg(src + idx[j]);
+                if (has_bad && f == P.bad)
+                    f = nan_f();
+                if (isnan(f)) {
+                    any_nan = any_nan || UNDEF;
+                    f = INFINITY;
+                } else {
+                    ++n;
+                }
+            }
+            v[j] = f;
+        }
+        sort_network<NMAX>(v);
+        float r = nan_f();
+        if (n > 0 && !any_nan) { // NaN among the values: unspecified order in the reference, defined as NaN
+            const int rank = n / 2;
+            r = v[0];
+#pragma unroll
+            for (int j = 1; j < NMAX; ++j)
+                r = rank == j ? v[j] : r;
+            if (r == 0.f) { // one of the pushed zeros: -0.0 only if no +0.0 was pushed (as the counting form decides)
+                bool pos = false;
+#pragma unroll
+                for (int j = 0; j < NMAX; ++j)
+                    pos = pos || (v[j] == 0.f && !signbit(v[j]));
+                r = pos ? 0.f : -0.f;
+            }
+        }
+        if (has_fill && isnan(r))
+            r = P.fill;
+        __stcs(dst, r);
+    }
+}
+
 template <bool UNDEF>
 __global__ void __launch_bounds__(128) fwd_median_kernel(const FwdParams P)
 {
     const size_t o = blockIdx.x * 128ull + threadIdx.x;
-    if (o >= P.nout)
-        return;
+    const bool live = o < P.nout;
     const int z0 = blockIdx.y * P.zchunk, z1 = min(P.nz, z0 + P.zchunk);
-    const int s0 = P.segStart[o], s1 = P.segStart[o + 1];
+    const int s0 = live ? P.segStart[o] : 0, s1 = live ? P.segStart[o + 1] : 0;
     const bool has_bad = !isnan(P.bad), has_fill = !isnan(P.fill);
+    // the longest segment of the warp picks the form (one branch for the whole warp); offsets must fit 32 bits for the small forms
+    const int nmax = __reduce_max_sync(0xffffffffu, s1 - s0);
+    if (nmax <= 8 && static_cast<size_t>(P.inLayer) < (size_t(1) << 31)) {
+        if (!live)
+            return;
+        if (nmax <= 2)
+            median_small<UNDEF, 2>(P, o, s0, s1 - s0, z0, z1, has_bad, has_fill);
+        else if (nmax <= 4)
+            median_small<UNDEF, 4>(P, o, s0, s1 - s0, z0, z1, has_bad, has_fill);
+        else
+            median_small<UNDEF, 8>(P, o, s0, s1 - s0, z0, z1, has_bad, has_fill);
+        return;
+    }
+    if (!live)
+        return;
     float v[MED_LOCAL];
     for (int z = z0; z < z1; ++z) {
         const float* src = P.in + static_cast<size_t>(z) * P.inLayer;
