@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(256) fwd_apply_kernel(const FwdParams P)
 // ---- round-2 forms of the apply -----------------------------------------------------------------------------------------------
 // One block of NK <= ZB levels of one target cell.  FULL: NK == ZB is known at compile time (no per-level tests).  BAD: the input
 // carries a bad value that counts as NaN.  Source offsets are 32-bit (the launch guarantees ZB * inLayer < 2^31).
-template <int KIND, bool UNDEF, bool BAD, int ZB, bool FULL>
+template <int KIND, bool UNDEF, bool BAD, int ZB, bool FULL, int KU = 2>
 __device__ __forceinline__ void fwd_reduce_block(const FwdParams& P, const float* __restrict__ src, int s0, int s1, int nk, float* __restrict__ dst, bool has_fill)
 {
     const unsigned lay = static_cast<unsigned>(P.inLayer);
@@ -260,24 +260,52 @@ __device__ __forceinline__ void fwd_reduce_block(const FwdParams& P, const float
         }
     };
     int k = s0;
-    for (; k + 2 <= s1; k += 2) { // two sources at a time: their index loads, then all their gathers, are in flight together
-        const unsigned i0 = static_cast<unsigned>(__ldg(P.segIdx + k)), i1 = static_cast<unsigned>(__ldg(P.segIdx + k + 1));
-        float f0[ZB], f1[ZB];
+    if (KU == 2) {
+        for (; k + 2 <= s1; k += 2) { // two sources at a time: their index loads, then all their gathers, are in flight together
+            const unsigned i0 = static_cast<unsigned>(__ldg(P.segIdx + k)), i1 = static_cast<unsigned>(__ldg(P.segIdx + k + 1));
+            float f0[ZB], f1[ZB];
 #pragma unroll
-        for (int q = 0; q < ZB; ++q) {
-            f0[q] = load(i0, q);
-            f1[q] = load(i1, q);
+            for (int q = 0; q < ZB; ++q) {
+                f0[q] = load(i0, q);
+                f1[q] = load(i1, q);
+            }
+            push(f0);
+            push(f1);
         }
-        push(f0);
-        push(f1);
     }
-    if (k < s1) {
-        const unsigned i0 = static_cast<unsigned>(__ldg(P.segIdx + k));
-        float f[ZB];
+    for (; KU != 2 && k + KU <= s1; k += KU) { // KU sources at a time
+        unsigned ix[KU];
+#pragma unroll
+        for (int u = 0; u < KU; ++u)
+            ix[u] = static_cast<unsigned>(__ldg(P.segIdx + k + u));
+        float f[KU][ZB];
 #pragma unroll
         for (int q = 0; q < ZB; ++q)
-            f[q] = load(i0, q);
-        push(f);
+#pragma unroll
+            for (int u = 0; u < KU; ++u)
+                f[u][q] = load(ix[u], q);
+#pragma unroll
+        for (int u = 0; u < KU; ++u)
+            push(f[u]); // ascending source order
+    }
+    if (KU == 2) { // at most one source left
+        if (k < s1) {
+            const unsigned i0 = static_cast<unsigned>(__ldg(P.segIdx + k));
+            float f[ZB];
+#pragma unroll
+            for (int q = 0; q < ZB; ++q)
+                f[q] = load(i0, q);
+            push(f);
+        }
+    } else {
+        for (; k < s1; ++k) {
+            const unsigned i0 = static_cast<unsigned>(__ldg(P.segIdx + k));
+            float f[ZB];
+#pragma unroll
+            for (int q = 0; q < ZB; ++q)
+                f[q] = load(i0, q);
+            push(f);
+        }
     }
     const unsigned nout = static_cast<unsigned>(P.nout);
 #pragma unroll
@@ -309,10 +337,11 @@ __global__ void __launch_bounds__(256) fwd_reduce_kernel(const FwdParams P)
     const float* src = P.in + static_cast<size_t>(z0) * P.inLayer;
     float* dst = P.out + static_cast<size_t>(z0) * P.nout + o;
     int zb = z0;
+    constexpr int KU = ZB >= 8 ? 2 : (ZB >= 4 ? 4 : 8); // sixteen gathers in flight per thread whatever the level block
     for (; zb + ZB <= z1; zb += ZB, src += static_cast<size_t>(ZB) * P.inLayer, dst += static_cast<size_t>(ZB) * P.nout)
-        fwd_reduce_block<KIND, UNDEF, BAD, ZB, true>(P, src, s0, s1, ZB, dst, has_fill);
+        fwd_reduce_block<KIND, UNDEF, BAD, ZB, true, KU>(P, src, s0, s1, ZB, dst, has_fill);
     if (zb < z1)
-        fwd_reduce_block<KIND, UNDEF, BAD, ZB, false>(P, src, s0, s1, z1 - zb, dst, has_fill);
+        fwd_reduce_block<KIND, UNDEF, BAD, ZB, false, KU>(P, src, s0, s1, z1 - zb, dst, has_fill);
 }
 
 // Min / max without the undef flavour do not depend on the order of the values: long segments (coarse targets: hundreds of sources
@@ -837,11 +866,21 @@ int fimexcu_forward_apply_dev_f(const fimexcu_forward* f, const float* d_in, siz
     } else {
         // (f->kind: 0 sum, 1 mean, 3 max, 4 min) x undef x "the input has a bad value"
         const bool bad = !std::isnan(P.bad);
-#define FXCU_FWD_CASE(K, U) \
-    if (bad) \
-        fwd_reduce_kernel<K, U, true, ZB><<<grid, 256, 0, st>>>(P); \
+        // few target cells: the levels are split over blockIdx.y (fwd_zchunk) and the level block shrinks with the chunk, so that
+        // no thread issues gathers for levels it does not own
+#define FXCU_FWD_ZB(K, U, B) \
+    if (P.zchunk >= 8) \
+        fwd_reduce_kernel<K, U, B, 8><<<grid, 256, 0, st>>>(P); \
+    else if (P.zchunk >= 4) \
+        fwd_reduce_kernel<K, U, B, 4><<<grid, 256, 0, st>>>(P); \
     else \
-        fwd_reduce_kernel<K, U, false, ZB><<<grid, 256, 0, st>>>(P); \
+        fwd_reduce_kernel<K, U, B, 1><<<grid, 256, 0, st>>>(P);
+#define FXCU_FWD_CASE(K, U) \
+    if (bad) { \
+        FXCU_FWD_ZB(K, U, true) \
+    } else { \
+        FXCU_FWD_ZB(K, U, false) \
+    } \
     break;
         switch (f->kind * 2 + (f->undef ? 1 : 0)) {
         case 0: FXCU_FWD_CASE(0, false)
@@ -854,6 +893,7 @@ int fimexcu_forward_apply_dev_f(const fimexcu_forward* f, const float* d_in, siz
         default: FXCU_FWD_CASE(4, true)
         }
 #undef FXCU_FWD_CASE
+#undef FXCU_FWD_ZB
     }
     FXCU_CUDA(cudaGetLastError());
     return FIMEXCU_OK;
