@@ -593,7 +593,7 @@ constexpr int MED_WARP_CAP = 1024;
 template <bool UNDEF>
 __global__ void __launch_bounds__(256) fwd_median_warp_kernel(const FwdParams P)
 {
-    __shared__ float buf[8][MED_WARP_CAP];
+    __shared__ unsigned buf[8][MED_WARP_CAP]; // the level's values as ordered keys (NaN: all ones, which no number has)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t o = blockIdx.x * 8ull + warp;
     if (o >= P.nout)
@@ -603,12 +603,21 @@ __global__ void __launch_bounds__(256) fwd_median_warp_kernel(const FwdParams P)
     const int len = s1 - s0;
     const bool staged = len <= MED_WARP_CAP;
     const bool has_bad = !isnan(P.bad), has_fill = !isnan(P.fill);
-    float* mine = buf[warp];
+    unsigned* mine = buf[warp];
+    auto key_of = [&](const float* src, int k) { // -0.0 and +0.0 are one key (they compare equal in nth_element)
+        float f = fwd_load(src + P.segIdx[s0 + k], P.bad, has_bad);
+        if (isnan(f))
+            return 0xffffffffu;
+        if (f == 0.f)
+            f = 0.f;
+        return ordered_bits(f);
+    };
     for (int z = z0; z < z1; ++z) {
         const float* src = P.in + static_cast<size_t>(z) * P.inLayer;
         int n = 0, nans = 0, negz = 0, posz = 0;
         for (int k = lane; k < len; k += 32) {
-            float f = fwd_load(src + P.segIdx[s0 + k], P.bad, has_bad);
+            const float f = fwd_load(src + P.segIdx[s0 + k], P.bad, has_bad);
+            unsigned key = 0xffffffffu;
             if (isnan(f)) {
                 ++nans;
             } else {
@@ -616,11 +625,11 @@ __global__ void __launch_bounds__(256) fwd_median_warp_kernel(const FwdParams P)
                 if (f == 0.f) {
                     negz += signbit(f) ? 1 : 0;
                     posz += signbit(f) ? 0 : 1;
-                    f = 0.f; // -0.0 and +0.0 are one key
                 }
+                key = ordered_bits(f == 0.f ? 0.f : f);
             }
             if (staged)
-                mine[k] = f;
+                mine[k] = key;
         }
 #pragma unroll
         for (int sft = 16; sft > 0; sft >>= 1) {
@@ -632,18 +641,16 @@ __global__ void __launch_bounds__(256) fwd_median_warp_kernel(const FwdParams P)
         __syncwarp();
         float r = nan_f();
         if (n > 0 && !(UNDEF && nans > 0)) { // NaN among the values (undef flavour): unspecified order in the reference, NaN here
-            int rank = n / 2;
+            // most-significant-bit-first radix selection of the key of rank n/2; `cand` keys still share the prefix, and once a
+            // single one is left its remaining bits need no further passes (about log2(n) passes for distinct values, not 32)
+            int rank = n / 2, cand = n;
             unsigned prefix = 0, mask = 0;
-            for (int bit = 31; bit >= 0; --bit) {
+            for (int bit = 31; bit >= 0 && cand > 1; --bit) {
                 const unsigned m2 = mask | (1u << bit);
                 int zeros = 0;
                 for (int k = lane; k < len; k += 32) {
-                    float f = staged ? mine[k] : fwd_load(src + P.segIdx[s0 + k], P.bad, has_bad);
-                    if (isnan(f))
-                        continue;
-                    if (f == 0.f)
-                        f = 0.f;
-                    zeros += ((ordered_bits(f) & m2) == prefix) ? 1 : 0;
+                    const unsigned key = staged ? mine[k] : key_of(src, k);
+                    zeros += ((key & m2) == prefix) ? 1 : 0; // shares the prefix and has a 0 here (the NaN key never does)
                 }
 #pragma unroll
                 for (int sft = 16; sft > 0; sft >>= 1)
@@ -651,8 +658,23 @@ __global__ void __launch_bounds__(256) fwd_median_warp_kernel(const FwdParams P)
                 if (rank >= zeros) {
                     rank -= zeros;
                     prefix |= 1u << bit;
+                    cand -= zeros;
+                } else {
+                    cand = zeros;
                 }
                 mask = m2;
+            }
+            if (mask != 0xffffffffu) { // stopped early: fetch the one key that carries the prefix
+                unsigned found = 0;
+                for (int k = lane; k < len; k += 32) {
+                    const unsigned key = staged ? mine[k] : key_of(src, k);
+                    if ((key & mask) == prefix && key != 0xffffffffu)
+                        found = key;
+                }
+#pragma unroll
+                for (int sft = 16; sft > 0; sft >>= 1)
+                    found |= __shfl_xor_sync(0xffffffffu, found, sft); // exactly one lane holds a non-zero key... or the key is 0
+                prefix = found;
             }
             r = __uint_as_float((prefix & 0x80000000u) ? (prefix & 0x7fffffffu) : ~prefix);
             if (r == 0.f)

@@ -590,10 +590,11 @@ __device__ __forceinline__ void column_by_general_scan(const VertParams& P, cons
 // broadcast accesses; an explicit coordinate streams through registers CH levels ahead), and notes for every target level the
 // step at which the walk passes it; monotonicity is verified on the way.  Phase 2 runs over the target levels with all lanes in
 // step.  Shared memory: hybrid (ap, b) pairs, the level list (f64, log, f32 with a NaN sentinel either side), notes [nzo][VT] u16.
+constexpr int LG = 4; // target levels handled together in straight-line code (their 2 * LG gathers are in flight at once)
 constexpr int CH = 4;
 constexpr int SJC = 8; // explicit coordinate: target levels per gather batch
 
-template <bool HYBRID>
+template <bool HYBRID, int METHOD = -1> // METHOD >= 0 (explicit coordinate only): the interpolation method as a compile-time constant
 __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams P)
 {
     extern __shared__ double smem_d[];
@@ -603,6 +604,8 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
     double* s_xl = s_xd + nzo;
     float* s_xf = reinterpret_cast<float*>(s_xl + nzo) + 1; // [-1] and [nzo] are sentinels
     unsigned short* s_k = reinterpret_cast<unsigned short*>(s_xf + nzo + 1 + (nzo & 1)) + threadIdx.x; // [nzo][VT], this thread's column
+    // explicit coordinate: the walk also leaves c(step-2), c(step-1), c(step) of every target level here, [3][nzo][VT]
+    float* s_c = reinterpret_cast<float*>(s_k - threadIdx.x + static_cast<size_t>(nzo + (nzo & 1)) * VT) + threadIdx.x;
     if (HYBRID) {
         for (int k = threadIdx.x; k < nzi; k += VT)
             s_apb[k] = make_double2(P.ap[k], P.b[k]);
@@ -617,6 +620,10 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
         s_xf[-1] = nan_f();
         s_xf[nzo] = nan_f();
     }
+    __shared__ double2 s_log[(!HYBRID && METHOD == FIMEXCU_VINT_METHOD_LOG) ? 128 : 1];
+    if (!HYBRID && METHOD == FIMEXCU_VINT_METHOD_LOG && P.logtab)
+        for (int i = threadIdx.x; i < 128; i += VT)
+            s_log[i] = P.logtab[i]; // made once per device (log_table_device)
     __syncthreads();
     const size_t ncol = P.nOuter * P.nInner;
     const size_t cidx = blockIdx.x * static_cast<size_t>(VT) + threadIdx.x;
@@ -632,7 +639,9 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
     const PairCol hc{s_apb, ps};
     const StridedCol sc{gc, static_cast<int>(P.nInner)};
     auto coord = [&](int k) -> float { return HYBRID ? hc(k) : sc(k); };
-    const OutCfg C = out_cfg(P);
+    OutCfg C = out_cfg(P);
+    if (!HYBRID && METHOD == FIMEXCU_VINT_METHOD_LOG && P.logtab)
+        C.logtab = s_log;
     const double rlo = P.vmin ? P.vmin[cidx] : 0., rhi = P.vmax ? P.vmax[cidx] : 0.;
 
     // ---- phase 1: one walk along the column, in the order in which it increases after multiplication by sg ----
@@ -652,13 +661,21 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
         const float* xp = s_xf + (forward ? 0 : nzo - 1);
         unsigned short* kp = s_k + (forward ? 0 : nzo - 1) * VT;
         float x = __fmul_rn(sg, *xp); // NaN once the list is exhausted
+        float pm1 = __fmul_rn(sg, E.c0), pm2 = pm1, pcur = pm1; // walk-order values of c(k-1), c(k-2), c(k)
+        float* cp = s_c + (forward ? 0 : nzo - 1) * VT;
+        const int cplane = nzo * VT;
         auto note = [&](int step) {
             *kp = static_cast<unsigned short>(step);
+            if (!HYBRID) { // sg is +-1: multiplying again gives the stored values back exactly
+                cp[0] = __fmul_rn(sg, pm2);
+                cp[cplane] = __fmul_rn(sg, pm1);
+                cp[2 * cplane] = __fmul_rn(sg, pcur);
+                cp += kstep;
+            }
             xp += xstep;
             kp += kstep;
             x = __fmul_rn(sg, *xp);
         };
-        float pm1 = __fmul_rn(sg, E.c0);
         while (x <= pm1) // at or beyond the end that holds element 0
             note(0);
         bool mono = true;
@@ -671,29 +688,46 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
                 pm1 = pk;
             }
         } else {
+            // whole chunks of CH levels, the next chunk's loads issued before this one is used; level offsets are 32-bit
+            // (sweep_applies) and the read pointer is bumped, so a level costs a load, a compare and a branch
+            const unsigned lstride = static_cast<unsigned>(P.nInner);
+            const float* gp = gc + lstride; // level 1
+            const int nchunks = (nzi - 1) / CH;
             float ccur[CH];
 #pragma unroll
             for (int i = 0; i < CH; ++i)
-                ccur[i] = (1 + i) < nzi ? __ldg(gc + static_cast<size_t>(1 + i) * P.nInner) : 0.f;
-            for (int base = 1; base < nzi; base += CH) {
+                ccur[i] = nchunks > 0 ? __ldg(gp + static_cast<unsigned>(i) * lstride) : 0.f;
+            int k = 1;
+            for (int c = 0; c < nchunks; ++c, k += CH) {
+                gp += CH * lstride;
                 float cnx[CH];
+                const bool more = c + 1 < nchunks;
 #pragma unroll
                 for (int i = 0; i < CH; ++i)
-                    cnx[i] = (base + CH + i) < nzi ? __ldg(gc + static_cast<size_t>(base + CH + i) * P.nInner) : 0.f;
+                    cnx[i] = more ? __ldg(gp + static_cast<unsigned>(i) * lstride) : 0.f;
 #pragma unroll
                 for (int i = 0; i < CH; ++i) {
-                    const int k = base + i;
-                    if (k < nzi) {
-                        const float pk = __fmul_rn(sg, ccur[i]);
-                        mono = mono && (pk > pm1);
+                    const float pk = __fmul_rn(sg, ccur[i]);
+                    mono = mono && (pk > pm1);
+                    pcur = pk;
+                    if (__any_sync(__activemask(), x < pk)) // most levels pass no target level in any column of the warp
                         while (x < pk)
-                            note(k);
-                        pm1 = pk;
-                    }
+                            note(k + i);
+                    pm2 = pm1;
+                    pm1 = pk;
                 }
 #pragma unroll
                 for (int i = 0; i < CH; ++i)
                     ccur[i] = cnx[i];
+            }
+            for (; k < nzi; ++k, gp += lstride) { // fewer than CH levels left (gp stands at level k)
+                const float pk = __fmul_rn(sg, __ldg(gp));
+                mono = mono && (pk > pm1);
+                pcur = pk;
+                while (x < pk)
+                    note(k);
+                pm2 = pm1;
+                pm1 = pk;
             }
         }
         ok = mono;
@@ -730,67 +764,70 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
         }
         return;
     }
-    // explicit coordinate: the three coordinates and two values a level needs are known from its step alone, so a batch of
-    // levels sends for all of them at once (cp.async into shared memory) before any is used
-    float* s_g = reinterpret_cast<float*>(s_k - threadIdx.x + static_cast<size_t>(nzo) * VT) + threadIdx.x; // [5][SJC][VT]
-    const unsigned g0 = static_cast<unsigned>(__cvta_generic_to_shared(s_g));
-    auto send = [&](int slot, int u, const float* src) {
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(g0 + static_cast<unsigned>((slot * SJC + u) * VT * 4)), "l"(src) : "memory");
-    };
-    auto got = [&](int slot, int u) { return s_g[(slot * SJC + u) * VT]; };
-    for (int j0 = 0; j0 < nzo; j0 += SJC) {
-        const int jn = min(SJC, nzo - j0);
-        for (int u = 0; u < jn; ++u) {
-            const int step = s_k[(j0 + u) * VT];
-            if (step > 0 && step < nzi) {
-                send(0, u, gc + static_cast<size_t>(max(step - 2, 0)) * P.nInner);
-                send(1, u, gc + static_cast<size_t>(step - 1) * P.nInner);
-                send(2, u, gc + static_cast<size_t>(step) * P.nInner);
-                send(3, u, din + static_cast<size_t>(step - 1) * P.nInner);
-                send(4, u, din + static_cast<size_t>(step) * P.nInner);
-            } else if (step == nzi) {
-                send(3, u, din + static_cast<size_t>(nzi - 1) * P.nInner);
-                send(4, u, din + static_cast<size_t>(nzi - 2) * P.nInner);
-            }
+    // explicit coordinate: the walk left the bracket of every level in shared memory, so a level costs two gathers (the values);
+    // the decision is predicate logic and selects as in the table kernel, LG levels in straight-line code
+    constexpr bool LOGM = METHOD == FIMEXCU_VINT_METHOD_LOG;
+    const unsigned stride = static_cast<unsigned>(P.nInner); // sweep_applies(): nzi * nInner and nzo * nInner < 2^31
+    const bool ranged = P.vmin || P.vmax;
+    const bool plain = isnan(C.valid_min) && isnan(C.valid_max) && isnan(C.fill);
+    // LOG weights from the table logarithms need positive normal brackets: the column is monotone, so its ends decide
+    bool trusted = LOGM && C.logtab != nullptr;
+    if (LOGM) {
+        const unsigned b0 = __float_as_uint(E.c0), b1 = __float_as_uint(E.cl);
+        trusted = trusted && !(b0 - 0x00800000u >= 0x7f000000u || b1 - 0x00800000u >= 0x7f000000u);
+    }
+    const int cplane = nzo * VT;
+    for (int j0 = 0; j0 < nzo; j0 += LG) {
+        float A[LG], B[LG], ca[LG], cb[LG]; // ca: NaN = general search, +inf = the result is NaN (undefined level)
+#pragma unroll
+        for (int u = 0; u < LG; ++u) {
+            const int jj = min(j0 + u, nzo - 1);
+            const int step = s_k[jj * VT];
+            const float x = s_xf[jj];
+            const float g = s_c[jj * VT], plo = s_c[cplane + jj * VT], phi = s_c[2 * cplane + jj * VT];
+            const float dlo = __fsub_rn(x, plo), dhi = __fsub_rn(x, phi), dg = __fsub_rn(x, g);
+            // interior step (see value_from_step): finite differences, x != c(step-1) when walking down, no f32 tie with c(step-2)
+            bool ok_in = fabsf(dlo) < FLT_MAX && fabsf(dhi) < FLT_MAX && (inc || x != plo) && (step <= 1 || dlo != dg);
+            const bool far = step >= nzi, zero = step == 0;
+            const float d2 = fabsf(__fsub_rn(x, E.cl2));
+            const bool ok_far = fabsf(__fsub_rn(x, E.cl)) < d2 && (nzi < 3 || d2 < fabsf(__fsub_rn(x, E.cl3)));
+            const bool zero_nan = (x == E.c0) || fabsf(__fsub_rn(x, E.c0)) < fabsf(__fsub_rn(x, E.c1));
+            bool ok = !zero && (far ? ok_far : ok_in);
+            const float a = far ? E.cl : (inc ? plo : phi);
+            const float b = far ? E.cl2 : (inc ? phi : plo);
+            if (LOGM) // exact hits and levels without a usable host logarithm are the general search's business
+                ok = ok && (!trusted || (x != a && x != b && s_xd[jj] > 0. && !isnan(s_xl[jj])));
+            bool undefined = zero && zero_nan;
+            if (ranged)
+                undefined = undefined || !level_in_range(P, s_xd[jj], rlo, rhi);
+            int first = far ? nzi - 1 : (inc ? step - 1 : step);
+            int second = far ? nzi - 2 : (inc ? step : step - 1);
+            first = (ok && !undefined) ? first : 0;
+            second = (ok && !undefined) ? second : 0;
+            A[u] = __ldg(din + static_cast<unsigned>(first) * stride);
+            B[u] = __ldg(din + static_cast<unsigned>(second) * stride);
+            ca[u] = undefined ? INFINITY : (ok ? a : nan_f());
+            cb[u] = b;
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        asm volatile("cp.async.wait_all;" ::: "memory");
-        for (int u = 0; u < jn; ++u) {
+#pragma unroll
+        for (int u = 0; u < LG; ++u) {
             const int jj = j0 + u;
-            const double vout = s_xd[jj], xlog = s_xl[jj];
-            float r = nan_f();
-            if (level_in_range(P, vout, rlo, rhi)) {
-                const int step = s_k[jj * VT];
-                const float x = s_xf[jj];
-                bool fast, distinct = true;
-                float A = 0.f, B = 0.f, a = 0.f, b = 0.f;
-                if (step == 0) { // see value_from_step
-                    distinct = false;
-                    fast = (x == E.c0) || fabsf(__fsub_rn(x, E.c0)) < fabsf(__fsub_rn(x, E.c1));
-                } else if (step == nzi) {
-                    A = got(3, u);
-                    B = got(4, u);
-                    a = E.cl;
-                    b = E.cl2;
-                    const float d2 = fabsf(__fsub_rn(x, E.cl2));
-                    fast = fabsf(__fsub_rn(x, E.cl)) < d2 && (nzi < 3 || d2 < fabsf(__fsub_rn(x, E.cl3)));
-                } else {
-                    const float plo = got(1, u), phi = got(2, u);
-                    const float dlo = __fsub_rn(x, plo), dhi = __fsub_rn(x, phi);
-                    fast = fabsf(dlo) < FLT_MAX && fabsf(dhi) < FLT_MAX && (inc || x != plo);
-                    if (fast && step > 1)
-                        fast = dlo != __fsub_rn(x, got(0, u));
-                    A = inc ? got(3, u) : got(4, u);
-                    B = inc ? got(4, u) : got(3, u);
-                    a = inc ? plo : phi;
-                    b = inc ? phi : plo;
-                }
-                if (!fast)
-                    r = sweep_slow(C, sc, nzi, inc ? 1 : -1, din, vout, xlog);
-                else if (distinct)
-                    r = blend_levels(C, A, B, a, b, vout, xlog);
+            if (jj < nzo) {
+                float r;
+                if (isnan(ca[u]))
+                    r = sweep_slow(C, sc, nzi, inc ? 1 : -1, din, s_xd[jj], s_xl[jj]);
+                else if (ca[u] == INFINITY)
+                    r = nan_f();
+                else if (LOGM && trusted)
+                    r = blend_levels<METHOD, true>(C, A[u], B[u], ca[u], cb[u], s_xd[jj], s_xl[jj]);
+                else
+                    r = blend_levels<METHOD, false>(C, A[u], B[u], ca[u], cb[u], s_xd[jj], s_xl[jj]);
+                float* dst = dout + static_cast<unsigned>(jj) * stride;
+                if (plain)
+                    __stcs(dst, r);
+                else
+                    store_result(C, dst, r);
             }
-            store_result(C, dout + static_cast<size_t>(jj) * P.nInner, r);
         }
     }
 }
@@ -1001,7 +1038,6 @@ __device__ __forceinline__ unsigned classify_step(const PairCol& c, int nzi, boo
 // loads.  LG levels are handled together in straight-line code so that their 2 * LG gathers are in flight at once.  Everything
 // else (level before or equal to the first element, f32 difference ties, a second correction step, NaN levels) goes to the
 // out-of-line general search, which decides by the reference's own scan.
-constexpr int LG = 4;
 
 // per-column constants of table_column()
 struct TableColumn {
@@ -1189,12 +1225,13 @@ __global__ void __launch_bounds__(256) ps_minmax_kernel(const float* __restrict_
 static size_t sweep_smem(const VertParams& P)
 {
     return ((P.vcoord_in ? 0 : 2 * P.nzi) + 2 * P.nzo) * sizeof(double) + (P.nzo + 2 + (P.nzo & 1)) * sizeof(float) +
-           (P.nzo + (P.nzo & 1)) * VT * sizeof(unsigned short) + (P.vcoord_in ? 5 * SJC * VT * sizeof(float) : 0);
+           (P.nzo + (P.nzo & 1)) * VT * sizeof(unsigned short) + (P.vcoord_in ? 3 * P.nzo * VT * sizeof(float) : 0);
 }
 static bool sweep_applies(const VertParams& P)
 {
     static const bool disabled = std::getenv("FIMEXCU_VERTICAL_NO_SWEEP") != nullptr;
-    return !disabled && P.levels && !P.vcoord_out && P.levels_dir != 0 && P.nzi < 65535 && P.nzo < 65535 && sweep_smem(P) <= 40 * 1024;
+    return !disabled && P.levels && !P.vcoord_out && P.levels_dir != 0 && P.nzi < 65535 && P.nzo < 65535 && sweep_smem(P) <= 40 * 1024 &&
+           P.nzi * P.nInner < (size_t(1) << 31) && P.nzo * P.nInner < (size_t(1) << 31); // 32-bit level offsets in the kernel
 }
 
 // direction of a fixed level list: +1 non-decreasing, -1 non-increasing, 0 unordered / NaN
@@ -1253,6 +1290,10 @@ static int launch_vertical(const VertParams& P, cudaStream_t s)
         const size_t smem = sweep_smem(P);
         if (!P.vcoord_in)
             vertical_sweep_kernel<true><<<blocks, VT, smem, s>>>(P);
+        else if (P.method == FIMEXCU_VINT_METHOD_LOG)
+            vertical_sweep_kernel<false, FIMEXCU_VINT_METHOD_LOG><<<blocks, VT, smem, s>>>(P);
+        else if (P.method == FIMEXCU_VINT_METHOD_LIN)
+            vertical_sweep_kernel<false, FIMEXCU_VINT_METHOD_LIN><<<blocks, VT, smem, s>>>(P);
         else
             vertical_sweep_kernel<false><<<blocks, VT, smem, s>>>(P);
         FXCU_CUDA(cudaGetLastError());
@@ -1446,6 +1487,7 @@ int fimexcu_vertical_interpolate_dev_f(int method, const float* d_in, const floa
     P.bad = badIn;
     P.fill = fillOut;
     P.out = d_out;
+    P.logtab = (method == FIMEXCU_VINT_METHOD_LOG && levels_host) ? log_table_device() : nullptr; // nullptr: the kernels use the series / log() forms
     if (!d_vcoord_in)
         FXCU_FAIL("fimexcu_vertical_interpolate: null input vertical coordinate");
     const int rc = launch_vertical(P, s);
