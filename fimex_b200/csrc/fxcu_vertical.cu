@@ -874,13 +874,15 @@ __device__ __forceinline__ int ps_hist_key(float v)
     return (enc >> PS_HIST_SHIFT) + PS_HIST_BINS / 2;
 }
 
-__global__ void __launch_bounds__(256) ps_hist_kernel(const float* __restrict__ ps, size_t n, unsigned* __restrict__ hist)
+// `every`: one block of 256 values in `every` is looked at.  The histogram only has to find where the bulk of the data lies; a column
+// whose ps falls outside the range found takes the general search (slower, never wrong), so a sample serves large launches.
+__global__ void __launch_bounds__(256) ps_hist_kernel(const float* __restrict__ ps, size_t n, unsigned* __restrict__ hist, unsigned every)
 {
     __shared__ unsigned sh[PS_HIST_BINS];
     for (int i = threadIdx.x; i < PS_HIST_BINS; i += 256)
         sh[i] = 0;
     __syncthreads();
-    for (size_t base = blockIdx.x * 256ull; base < n; base += 256ull * gridDim.x) { // whole warps stay in step
+    for (size_t base = blockIdx.x * 256ull * every; base < n; base += 256ull * every * gridDim.x) { // whole warps stay in step
         const size_t i = base + threadIdx.x;
         const float v = i < n ? __ldg(ps + i) : nan_f();
         const bool valid = !isnan(v);
@@ -1601,9 +1603,12 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
             return FIMEXCU_ERROR;
         char* base = static_cast<char*>(scratch.p);
         FXCU_CUDA(cudaMemsetAsync(base, 0, hdr_off, s));
-        if (nps)
-            ps_hist_kernel<<<static_cast<unsigned>(std::min<size_t>((nps + 255) / 256, static_cast<size_t>(sm_count()) * 8)), 256, 0, s>>>(
-                d_ps, nps, reinterpret_cast<unsigned*>(base));
+        if (nps) {
+            const unsigned every = nps >= (size_t(1) << 22) ? 4u : 1u; // >= 4 M values: every fourth block of 256
+            const size_t hblocks = (nps + 256ull * every - 1) / (256ull * every);
+            ps_hist_kernel<<<static_cast<unsigned>(std::min<size_t>(hblocks, static_cast<size_t>(sm_count()) * 8)), 256, 0, s>>>(
+                d_ps, nps, reinterpret_cast<unsigned*>(base), every);
+        }
         hybrid_table_kernel<<<1, 256, 2 * nzi * sizeof(double), s>>>(P.ap, P.b, static_cast<int>(nzi), P.levels, static_cast<int>(nzo), reinterpret_cast<const unsigned*>(base),
                                                ps_scale, nbins, reinterpret_cast<HybridTableHeader*>(base + hdr_off),
                                                reinterpret_cast<unsigned short*>(base + tab_off));
