@@ -1944,8 +1944,7 @@ static int cache_apply_host(const fimexcu_cache* c, const T* const (&in)[NF], si
                 }
         // everything between the spans, as runs that continue across row ends (the right margin of a row and the left margin of
         // the next one are one piece of memory); each thread takes a range of (field, level, row) triples
-        start_filler = [&]() {
-          filler = std::thread([&]() {
+        auto fill_margins = [&]() {
             const E2ETrace::clock::time_point f0 = E2ETrace::clock::now();
             const size_t rows = nz * outY;
             parallel_ranges(NF * rows, 256, [&](size_t a, size_t b) {
@@ -1967,7 +1966,13 @@ static int cache_apply_host(const fimexcu_cache* c, const T* const (&in)[NF], si
                 _mm_sfence();
             }, e2e_fill_threads());
             trace.fill = E2ETrace::ms(f0, E2ETrace::clock::now());
-          });
+        };
+        start_filler = [&, fill_margins]() {
+            try {
+                filler = std::thread(fill_margins);
+            } catch (...) { // no thread to be had: write the margins here
+                fill_margins();
+            }
         };
         // a pageable input keeps the host cores busy with its bounce copies until the last chunk is queued, and those copies are
         // what the device waits for: the margins are then written afterwards, while the queue drains

@@ -11,6 +11,7 @@
 #include <functional>
 #include <mutex>
 #include <thread>
+#include <unistd.h>
 #include <vector>
 
 namespace fxcu {
@@ -41,6 +42,12 @@ public:
     bool submit(std::function<void()> task)
     {
         std::unique_lock<std::mutex> lock(m_);
+        if (pid_ != getpid()) { // a forked child inherits the bookkeeping but none of the threads: start over
+            pid_ = getpid();
+            started_ = 0;
+            idle_ = 0;
+            queue_.clear();
+        }
         if (idle_ <= queue_.size() && started_ < host_threads()) { // every idle worker already has a task waiting for it
             try {
                 std::thread([this]() { serve(); }).detach();
@@ -78,6 +85,7 @@ private:
     std::deque<std::function<void()>> queue_;
     unsigned started_ = 0;
     size_t idle_ = 0;
+    pid_t pid_ = getpid();
 };
 
 struct Latch {
