@@ -2050,11 +2050,9 @@ static int cache_apply_host(const fimexcu_cache* c, const T* const (&in)[NF], si
             pend[i].live = false;
         };
         size_t k = 0;
-        // the first chunks are shorter (a quarter, then half a chunk): nothing can cross the bus before the first chunk's input has
-        // been copied (pageable) and sent, so that one should be small
-        auto chunk_levels = [&](size_t kk) { return (nchunk >= 4 && kk < 2) ? std::max<size_t>(1, chunk >> (2 - kk)) : chunk; };
+        // (shorter first and last chunks -- to start and to end the bus traffic sooner -- measured no different: 15.2 / 15.0 / 15.1 ms)
         for (size_t z0 = 0, zn = 0; z0 < nz && rc == FIMEXCU_OK; z0 += zn, ++k) {
-            zn = std::min(chunk_levels(k), nz - z0);
+            zn = std::min(chunk, nz - z0);
             const int i = static_cast<int>(k % NS);
             if (k >= static_cast<size_t>(NS)) { // the bounce buffers of this stream must be free again
                 trace.timed(trace.wait, [&]() {
