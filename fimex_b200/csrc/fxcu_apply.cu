@@ -396,7 +396,7 @@ __global__ void __launch_bounds__(256) bilinear_apply_kernel(const ApplyParams P
     const int inX = P.inPitch;
     if (fx >= 0.f && fy >= 0.f) {
         const float omx = __fsub_rn(1.f, fx), omy = __fsub_rn(1.f, fy);
-#pragma unroll 4
+#pragma unroll 8
         for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel) {
             const float s00 = load_in<BAD>(p, P.bad), s01 = load_in<BAD>(p + 1, P.bad);
             const float s10 = load_in<BAD>(p + inX, P.bad), s11 = load_in<BAD>(p + inX + 1, P.bad);
@@ -404,20 +404,20 @@ __global__ void __launch_bounds__(256) bilinear_apply_kernel(const ApplyParams P
         }
     } else if (fx >= 0.f) { // linear in x on the nearest row (interpolation.c:289-299)
         const float omx = __fsub_rn(1.f, fx);
-#pragma unroll 4
+#pragma unroll 8
         for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel) {
             const float s00 = load_in<BAD>(p, P.bad), s01 = load_in<BAD>(p + 1, P.bad);
             store_out<FILL>(po, __fadd_rn(__fmul_rn(omx, s00), __fmul_rn(fx, s01)), P.fill);
         }
     } else if (fy >= 0.f) { // linear in y on the nearest column (:311-319)
         const float omy = __fsub_rn(1.f, fy);
-#pragma unroll 4
+#pragma unroll 8
         for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel) {
             const float s00 = load_in<BAD>(p, P.bad), s10 = load_in<BAD>(p + inX, P.bad);
             store_out<FILL>(po, __fadd_rn(__fmul_rn(omy, s00), __fmul_rn(fy, s10)), P.fill);
         }
     } else { // nearest cell (:321-328)
-#pragma unroll 4
+#pragma unroll 8
         for (int z = z0; z < z1; ++z, p += P.inLevel, po += P.outLevel)
             store_out<FILL>(po, load_in<BAD>(p, P.bad), P.fill);
     }
