@@ -1278,6 +1278,38 @@ static const double2* log_table_device()
     return tabs[dev];
 }
 
+// device copy of a coefficient set (hybrid ap, b, target levels and their logarithms), per host thread and device; nullptr when the
+// set cannot be kept (first sight of it: it is uploaded here, synchronously, and kept; more than 8 sets alive: not cached)
+static const double* cached_coefficients(const std::vector<double>& h)
+{
+    struct Entry {
+        int device;
+        std::vector<double> host;
+        double* dev;
+    };
+    thread_local std::vector<Entry> cache;
+    int dev = -1;
+    if (h.empty() || cudaGetDevice(&dev) != cudaSuccess)
+        return nullptr;
+    for (const Entry& e : cache)
+        if (e.device == dev && e.host.size() == h.size() && std::memcmp(e.host.data(), h.data(), h.size() * sizeof(double)) == 0)
+            return e.dev;
+    if (cache.size() >= 8)
+        return nullptr;
+    double* d = nullptr;
+    if (cudaMalloc(&d, h.size() * sizeof(double)) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    if (cudaMemcpy(d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(d);
+        return nullptr;
+    }
+    cache.push_back(Entry{dev, h, d});
+    return d;
+}
+
 static int launch_vertical(const VertParams& P, cudaStream_t s)
 {
     const size_t ncol = P.nOuter * P.nInner;
@@ -1551,27 +1583,35 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
     if (!levels_host || !ap_host || !b_host || !d_ps)
         FXCU_FAIL("fimexcu_vertical_hybrid_pressure: null argument");
     cudaStream_t s = as_stream(stream);
-    DevBuf coef;
     const size_t nc = 2 * nzi + 2 * nzo;
-    if (!coef.alloc(std::max<size_t>(nc, 1) * sizeof(double), s))
-        return FIMEXCU_ERROR;
     std::vector<double> h(nc);
     std::copy(ap_host, ap_host + nzi, h.begin());
     std::copy(b_host, b_host + nzi, h.begin() + nzi);
     std::copy(levels_host, levels_host + nzo, h.begin() + 2 * nzi);
     for (size_t k = 0; k < nzo; ++k)
         h[2 * nzi + nzo + k] = host_level_log(method, levels_host[k]);
-    FXCU_CUDA(cudaMemcpyAsync(coef.p, h.data(), nc * sizeof(double), cudaMemcpyHostToDevice, s));
+    // A reader chain calls this once per variable and time step with the same coefficients and levels: the device copy of the
+    // last few coefficient sets is kept per host thread and device (a few KB each, never freed), so that a call neither uploads
+    // from pageable memory nor has to wait for its own completion before `h` goes away.
+    const double* d_coef = cached_coefficients(h);
+    DevBuf coef;
+    const bool cached = d_coef != nullptr;
+    if (!cached) {
+        if (!coef.alloc(std::max<size_t>(nc, 1) * sizeof(double), s))
+            return FIMEXCU_ERROR;
+        FXCU_CUDA(cudaMemcpyAsync(coef.p, h.data(), nc * sizeof(double), cudaMemcpyHostToDevice, s));
+        d_coef = coef.as<double>();
+    }
     VertParams P{};
     P.method = method;
     P.in = d_in;
     P.vcoord_in = nullptr;
-    P.ap = coef.as<double>();
-    P.b = coef.as<double>() + nzi;
-    P.levels = coef.as<double>() + 2 * nzi;
+    P.ap = d_coef;
+    P.b = d_coef + nzi;
+    P.levels = d_coef + 2 * nzi;
     P.levels_dir = levels_direction(levels_host, nzo);
     if (method == FIMEXCU_VINT_METHOD_LOG || method == FIMEXCU_VINT_METHOD_LOGLOG)
-        P.xlog = coef.as<double>() + 2 * nzi + nzo;
+        P.xlog = d_coef + 2 * nzi + nzo;
     P.ps = d_ps;
     P.nOuterPs = nOuterPs;
     P.ps_scale = ps_scale;
@@ -1629,7 +1669,8 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
         default: FXCU_FAIL("fimexcu_vertical_hybrid_pressure: unknown vertical interpolation method");
         }
         FXCU_CUDA(cudaGetLastError());
-        FXCU_CUDA(cudaStreamSynchronize(s)); // `h` is a temporary
+        if (!cached)
+            FXCU_CUDA(cudaStreamSynchronize(s)); // `h` is a temporary the upload may still be reading
         return FIMEXCU_OK;
     }
     if (!sweep_applies(P)) { // the per-level search kernel profits from a launch-wide monotonicity proof
