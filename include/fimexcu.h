@@ -378,7 +378,10 @@ int fimexcu_vertical_interpolate_dev_f(int method, const float* d_in, const floa
  * -> mifi_atmosphere_hybrid_sigma_ap_pressure (src/vertical_coordinate_transformations.c:62-68) feeding the loop above.
  * p[k] = ap[k] + b[k] * (ps * ps_scale) in f64, narrowed to f32 as at CDMVerticalInterpolator.cc:483.
  * ps: f32 [nOuterPs][nInner] with nOuterPs == nOuter or 1 (broadcast over the outer dimension).
- * For hybrid_sigma (a, p0) pass ap[k] = a[k]*p0. */
+ * For hybrid_sigma (a, p0) pass ap[k] = a[k]*p0.
+ * The _dev form enqueues on `stream` and may return before the work is done (like the other _dev entry points): it keeps the
+ * device copy of the last coefficient sets (ap, b, levels: a few KB per host thread and device) between calls, and only a call
+ * that sees a new set waits for its upload. */
 int fimexcu_vertical_hybrid_pressure_f(int method, const float* in, size_t nOuter, size_t nzi, size_t nInner, const double* ap, const double* b,
                                        const float* ps, size_t nOuterPs, double ps_scale, const double* levels, size_t nzo, double valid_min,
                                        double valid_max, float badIn, float fillOut, float* out);
