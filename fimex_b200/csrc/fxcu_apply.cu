@@ -22,6 +22,7 @@
 // rounded separately; the kernels use the _rn intrinsics (never contracted by nvcc) and reproduce the
 // reference's results bit for bit.
 #include "fxcu_handles.h"
+#include "fxcu_hostfill.h"
 #include "fxcu_hostpar.h"
 
 #include <algorithm>
@@ -1297,49 +1298,15 @@ static bool build_row_bands(fimexcu_cache* c, cudaStream_t s)
         !cuda_ok(cudaMemcpyAsync(span.data(), dspan.p, outY * sizeof(int2), cudaMemcpyDeviceToHost, s), "cudaMemcpyAsync", __FILE__, __LINE__) ||
         !cuda_ok(cudaStreamSynchronize(s), "cudaStreamSynchronize", __FILE__, __LINE__))
         return false;
-    typedef fimexcu_cache::RowBand Band;
-    auto join = [](const Band& a, const Band& b) {
-        Band r{a.y0, b.y1, 0, 0};
-        if (a.x0 >= a.x1) {
-            r.x0 = b.x0;
-            r.x1 = b.x1;
-        } else if (b.x0 >= b.x1) {
-            r.x0 = a.x0;
-            r.x1 = a.x1;
-        } else {
-            r.x0 = std::min(a.x0, b.x0);
-            r.x1 = std::max(a.x1, b.x1);
-        }
-        return r;
-    };
-    auto area = [](const Band& b) { return static_cast<long long>(b.y1 - b.y0) * std::max(0, b.x1 - b.x0); };
-    // start from blocks of rows (at most 512 of them), then merge greedily
-    std::vector<Band> bands;
-    const size_t block = (outY + 511) / 512;
-    for (size_t y0 = 0; y0 < outY; y0 += block) {
-        Band b{static_cast<int>(y0), static_cast<int>(y0), 0, 0};
-        for (size_t y = y0; y < std::min(outY, y0 + block); ++y)
-            b = join(b, Band{static_cast<int>(y), static_cast<int>(y + 1), span[y].x, std::max(span[y].x, span[y].y)});
-        bands.push_back(b);
-    }
-    while (bands.size() > MAX_BANDS) {
-        size_t best = 0;
-        long long best_cost = -1;
-        for (size_t i = 0; i + 1 < bands.size(); ++i) {
-            const long long cost = area(join(bands[i], bands[i + 1])) - area(bands[i]) - area(bands[i + 1]);
-            if (best_cost < 0 || cost < best_cost) {
-                best_cost = cost;
-                best = i;
-            }
-        }
-        bands[best] = join(bands[best], bands[best + 1]);
-        bands.erase(bands.begin() + static_cast<long>(best) + 1);
-    }
-    long long total = 0;
-    for (const Band& b : bands)
-        total += area(b);
-    c->band_fraction = static_cast<double>(total) / (static_cast<double>(outX) * static_cast<double>(outY));
-    c->bands = std::move(bands);
+    std::vector<hostfill::Span> rows(outY);
+    for (size_t y = 0; y < outY; ++y)
+        rows[y] = hostfill::Span{span[y].x, span[y].y};
+    double fraction = 1.0;
+    const std::vector<hostfill::Band> merged = hostfill::merge_row_spans(rows, static_cast<int>(outX), MAX_BANDS, fraction);
+    c->bands.clear();
+    for (const hostfill::Band& b : merged)
+        c->bands.push_back(fimexcu_cache::RowBand{b.y0, b.y1, b.x0, b.x1});
+    c->band_fraction = fraction;
     return true;
 }
 
@@ -1831,57 +1798,6 @@ static bool e2e_bands() // FIMEXCU_E2E_BANDS=0: copy whole result slabs back (fo
     return v;
 }
 
-// n copies of v at p: ordinary stores up to the first 64-byte boundary and after the last one, streaming stores for the whole lines
-// in between (written once, not read by this library: an ordinary store would first pull every line into the cache).  Streaming
-// stores to PART of a line, or mixed with ordinary stores to the same line, run four times slower (profiles/exp/hostcopy_probe.cu).
-template <class T> static void fill_lines(T* p, size_t n, T v)
-{
-    static_assert(sizeof(T) == 4 || sizeof(T) == 2, "float or short");
-    while (n && (reinterpret_cast<uintptr_t>(p) & 63u)) {
-        *p++ = v;
-        --n;
-    }
-    constexpr size_t PER = 64 / sizeof(T);
-    if (n >= PER) {
-        alignas(16) T pat[16 / sizeof(T)];
-        for (T& e : pat)
-            e = v;
-        const __m128i q = _mm_load_si128(reinterpret_cast<const __m128i*>(pat));
-        for (; n >= PER; n -= PER, p += PER) {
-            __m128i* line = reinterpret_cast<__m128i*>(p);
-            _mm_stream_si128(line, q);
-            _mm_stream_si128(line + 1, q);
-            _mm_stream_si128(line + 2, q);
-            _mm_stream_si128(line + 3, q);
-        }
-    }
-    while (n) {
-        *p++ = v;
-        --n;
-    }
-}
-
-// the same for a copy: a result span leaves the pinned bounce buffer for the caller's array, whole destination lines streamed
-static void copy_lines(void* dst_, const void* src_, size_t bytes)
-{
-    char* dst = static_cast<char*>(dst_);
-    const char* src = static_cast<const char*>(src_);
-    const size_t head = std::min<size_t>(bytes, (64 - (reinterpret_cast<uintptr_t>(dst) & 63u)) & 63u);
-    std::memcpy(dst, src, head);
-    dst += head;
-    src += head;
-    bytes -= head;
-    for (; bytes >= 64; bytes -= 64, dst += 64, src += 64) {
-        const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src)), b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src) + 1);
-        const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src) + 2), d = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src) + 3);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(dst), a);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(dst) + 1, b);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(dst) + 2, c);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(dst) + 3, d);
-    }
-    std::memcpy(dst, src, bytes);
-}
-
 // pageable <-> pinned copies of one level chunk on the host cores (a single memcpy thread runs at a fraction of PCIe speed)
 static void host_copy(void* dst, const void* src, size_t bytes)
 {
@@ -1956,11 +1872,11 @@ static int cache_apply_host(const fimexcu_cache* c, const T* const (&in)[NF], si
                         const size_t y = k % outY;
                         T* row = base + k * outX;
                         if (row_x0[y] < row_x1[y]) {
-                            fill_lines(run, static_cast<size_t>(row + row_x0[y] - run), undef[f]);
+                            hostfill::fill_lines(run, static_cast<size_t>(row + row_x0[y] - run), undef[f]);
                             run = row + row_x1[y];
                         }
                     }
-                    fill_lines(run, static_cast<size_t>(base + (e - f * rows) * outX - run), undef[f]);
+                    hostfill::fill_lines(run, static_cast<size_t>(base + (e - f * rows) * outX - run), undef[f]);
                     a = e;
                 }
                 _mm_sfence();
@@ -2041,7 +1957,7 @@ static int cache_apply_host(const fimexcu_cache* c, const T* const (&in)[NF], si
                             const size_t y = k % outY;
                             if (row_x0[y] < row_x1[y]) {
                                 const size_t o = k * outX + static_cast<size_t>(row_x0[y]);
-                                copy_lines(dst + o, src + o, static_cast<size_t>(row_x1[y] - row_x0[y]) * sizeof(T));
+                                hostfill::copy_lines(dst + o, src + o, static_cast<size_t>(row_x1[y] - row_x0[y]) * sizeof(T));
                             }
                         }
                         _mm_sfence();

@@ -298,12 +298,13 @@ _native = {}
 
 def native(name):
     """tests/native/<name>.cc -> lib<name>.so (g++; built on first use).  These drive the HOST-side logic of libfimexcu's
-    coordinate searches (fimex_b200/csrc/fxcu_kdclone.h, fxcu_llscan.h) so that it can be tested without a GPU."""
+    coordinate searches (fimex_b200/csrc/fxcu_kdclone.h, fxcu_llscan.h) and host entry points (fxcu_hostfill.h, fxcu_hostpar.h) so
+    that it can be tested without a GPU."""
     if name in _native:
         return _native[name]
     src = os.path.join(HERE, "native", name + ".cc")
     so = os.path.join(HERE, "native", "lib" + name + ".so")
-    deps = [src] + [os.path.join(ROOT, "fimex_b200", "csrc", h) for h in ("fxcu_kdclone.h", "fxcu_llscan.h", "fxcu_hostpar.h")]
+    deps = [src] + [os.path.join(ROOT, "fimex_b200", "csrc", h) for h in ("fxcu_kdclone.h", "fxcu_llscan.h", "fxcu_hostpar.h", "fxcu_hostfill.h")]
     if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
         subprocess.run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-pthread", "-o", so, src], check=True)
     lib = C.CDLL(so)
@@ -311,6 +312,14 @@ def native(name):
         lib.kdclone_translate_host.restype = C.c_int
         lib.kdclone_translate_host.argtypes = [C.c_double, c_double_p, c_double_p, C.c_size_t, c_double_p, c_double_p, C.c_size_t, C.c_size_t, C.c_uint,
                                                C.c_char_p, C.c_size_t]
+    elif name == "hostfill_host":
+        lib.hostfill_fill_f.argtypes = [c_float_p, C.c_size_t, C.c_float]
+        lib.hostfill_fill_i16.argtypes = [C.c_void_p, C.c_size_t, C.c_short]
+        lib.hostfill_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        lib.hostfill_merge.restype = C.c_int
+        lib.hostfill_merge.argtypes = [C.POINTER(C.c_int), C.c_size_t, C.c_int, C.c_size_t, C.POINTER(C.c_int), c_double_p]
+        lib.hostpar_cover.restype = C.c_size_t
+        lib.hostpar_cover.argtypes = [C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int]
     elif name == "llscan_host":
         lib.llscan_translate_host.restype = C.c_int
         lib.llscan_translate_host.argtypes = [c_double_p, c_double_p, C.c_size_t, c_double_p, c_double_p, C.c_size_t, C.c_size_t, C.c_double]
