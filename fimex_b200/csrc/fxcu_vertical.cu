@@ -19,6 +19,7 @@
 #include "fxcu_common.h"
 #include "fxcu_logtable.h"
 
+#include <atomic>
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
@@ -832,6 +833,181 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
     }
 }
 
+// ---- explicit coordinate, fixed target levels: scan + bisection -----------------------------------------------------------------
+// The walk of the sweep kernel notes, for every lane, the input level at which it passes each target level -- and a warp pays for
+// every distinct such level among its 32 columns (285 of the sweep's 455 instructions per output value, ncu).  Here the column is
+// only SCANNED once (a load and two compares per level: is it strictly monotone, NaN-free?), and every target level then finds its
+// step by bisection (a fixed number of rounds; the column is hot in L1/L2 after the scan, the probes of a group of LG levels are
+// independent of each other).  The step is the same number the walk notes -- the count of elements at or before the level in
+// walk order, 0 at or before the first -- so everything downstream is the sweep kernel's second phase.  Target levels need not
+// be sorted.  Shared memory: the level list only (f64, log, f32).
+constexpr int SLG = 4; // target levels per group of the search kernel (their probes and 2 * SLG gathers are independent)
+// The block's coordinate columns are staged in shared memory ([nzi][VT], one bank per column: conflict-free whatever level a lane
+// asks for) while they are scanned, with sixteen loads in flight per thread; the probes of the bisection and the bracket values
+// then come from there instead of paying a trip to L1 / L2 per round (a first form that probed global memory was latency-bound:
+// 41 % of the stalls on the scoreboard, slower than the sweep).
+template <int METHOD> // METHOD >= 0: compile-time interpolation method; -1: the method of the launch
+__global__ void __launch_bounds__(VT, 6) vertical_search_kernel(const VertParams P, int rounds)
+{
+    extern __shared__ double smem_d[];
+    const int nzi = static_cast<int>(P.nzi), nzo = static_cast<int>(P.nzo);
+    double* s_xd = smem_d;
+    double* s_xl = s_xd + nzo;
+    float* s_xf = reinterpret_cast<float*>(s_xl + nzo);
+    float* s_col = s_xf + nzo + (nzo & 1) + threadIdx.x; // [nzi][VT], this thread's column
+    constexpr bool LOGM = METHOD == FIMEXCU_VINT_METHOD_LOG;
+    __shared__ double2 s_log[LOGM ? 128 : 1];
+    for (int k = threadIdx.x; k < nzo; k += VT) {
+        const double x = P.levels[k];
+        s_xd[k] = x;
+        s_xl[k] = P.xlog ? P.xlog[k] : nan("");
+        s_xf[k] = __double2float_rn(x);
+    }
+    if (LOGM && P.logtab)
+        for (int i = threadIdx.x; i < 128; i += VT)
+            s_log[i] = P.logtab[i];
+    __syncthreads();
+    const size_t ncol = P.nOuter * P.nInner;
+    const size_t cidx = blockIdx.x * static_cast<size_t>(VT) + threadIdx.x;
+    if (cidx >= ncol)
+        return;
+    const size_t outer = cidx / P.nInner, inner = cidx - outer * P.nInner;
+    const float* din = P.in + outer * P.nzi * P.nInner + inner;
+    float* dout = P.out + outer * P.nzo * P.nInner + inner;
+    const float* gc = P.vcoord_in + outer * P.nzi * P.nInner + inner;
+    const unsigned stride = static_cast<unsigned>(P.nInner); // the launch guarantees nzi * nInner and nzo * nInner < 2^31
+    const StridedCol sc{gc, static_cast<int>(P.nInner)};
+    OutCfg C = out_cfg(P);
+    if (LOGM && P.logtab)
+        C.logtab = s_log;
+    const double rlo = P.vmin ? P.vmin[cidx] : 0., rhi = P.vmax ? P.vmax[cidx] : 0.;
+
+    // ---- the scan: direction from the first two elements, then strictly monotone all the way (NaN fails every compare) ----
+    ColumnEnds E{};
+    E.c0 = __ldg(gc);
+    E.c1 = __ldg(gc + stride);
+    s_col[0] = E.c0;
+    s_col[VT] = E.c1;
+    const bool inc = E.c1 > E.c0;
+    bool ok = inc || (E.c1 < E.c0);
+    const float sg = inc ? 1.f : -1.f; // exact
+    {
+        float prev = __fmul_rn(sg, E.c1);
+        const float* gp = gc + 2 * stride;
+        int k = 2;
+        constexpr int SC = 16; // loads in flight per thread: the scan is all memory latency
+        for (; k + SC <= nzi; k += SC, gp += SC * stride) {
+            float v[SC];
+#pragma unroll
+            for (int i = 0; i < SC; ++i)
+                v[i] = __ldg(gp + static_cast<unsigned>(i) * stride);
+#pragma unroll
+            for (int i = 0; i < SC; ++i) {
+                s_col[(k + i) * VT] = v[i];
+                const float w = __fmul_rn(sg, v[i]);
+                ok = ok && (w > prev);
+                prev = w;
+            }
+        }
+        for (; k < nzi; ++k, gp += stride) {
+            const float c = __ldg(gp);
+            s_col[k * VT] = c;
+            const float v = __fmul_rn(sg, c);
+            ok = ok && (v > prev);
+            prev = v;
+        }
+    }
+    if (!ok) {
+        column_by_general_scan(P, C, sc, nzi, nzo, s_xd, s_xl, rlo, rhi, din, dout);
+        return;
+    }
+    E.cl = s_col[(nzi - 1) * VT];
+    E.cl2 = s_col[(nzi - 2) * VT];
+    E.cl3 = nzi >= 3 ? s_col[(nzi - 3) * VT] : 0.f;
+    const float w0 = __fmul_rn(sg, E.c0);
+    const bool ranged = P.vmin || P.vmax;
+    const bool plain = isnan(C.valid_min) && isnan(C.valid_max) && isnan(C.fill);
+    // LOG weights from the table logarithms need positive normal brackets: the column is monotone, so its ends decide
+    bool trusted = LOGM && C.logtab != nullptr;
+    if (LOGM) {
+        const unsigned b0 = __float_as_uint(E.c0), b1 = __float_as_uint(E.cl);
+        trusted = trusted && !(b0 - 0x00800000u >= 0x7f000000u || b1 - 0x00800000u >= 0x7f000000u);
+    }
+
+    // ---- the target levels, SLG at a time ----
+    for (int j0 = 0; j0 < nzo; j0 += SLG) {
+        int lo[SLG], hi[SLG];
+        float xs[SLG];
+#pragma unroll
+        for (int u = 0; u < SLG; ++u) {
+            lo[u] = 0;
+            hi[u] = nzi;
+            xs[u] = __fmul_rn(sg, s_xf[min(j0 + u, nzo - 1)]);
+        }
+        for (int r = 0; r < rounds; ++r) { // count of elements <= the level in walk order (a NaN level counts none)
+#pragma unroll
+            for (int u = 0; u < SLG; ++u) {
+                const int mid = min((lo[u] + hi[u]) >> 1, nzi - 1);
+                const float v = __fmul_rn(sg, s_col[mid * VT]);
+                const bool le = v <= xs[u];
+                lo[u] = le ? mid + 1 : lo[u];
+                hi[u] = le ? hi[u] : min(hi[u], mid);
+            }
+        }
+        float A[SLG], B[SLG], ca[SLG], cb[SLG]; // ca: NaN = general search, +inf = the result is NaN (undefined level)
+#pragma unroll
+        for (int u = 0; u < SLG; ++u) {
+            const int jj = min(j0 + u, nzo - 1);
+            const float x = s_xf[jj];
+            const int step = (xs[u] <= w0) ? 0 : lo[u]; // at or before the first element: step 0, as the walk has it
+            const float g = s_col[max(step - 2, 0) * VT], plo = s_col[max(step - 1, 0) * VT], phi = s_col[min(step, nzi - 1) * VT];
+            const float dlo = __fsub_rn(x, plo), dhi = __fsub_rn(x, phi), dg = __fsub_rn(x, g);
+            // interior step (see value_from_step): finite differences, x != c(step-1) when walking down, no f32 tie with c(step-2)
+            const bool ok_in = fabsf(dlo) < FLT_MAX && fabsf(dhi) < FLT_MAX && (inc || x != plo) && (step <= 1 || dlo != dg);
+            const bool far = step >= nzi, zero = step == 0;
+            const float d2 = fabsf(__fsub_rn(x, E.cl2));
+            const bool ok_far = fabsf(__fsub_rn(x, E.cl)) < d2 && (nzi < 3 || d2 < fabsf(__fsub_rn(x, E.cl3)));
+            const bool zero_nan = (x == E.c0) || fabsf(__fsub_rn(x, E.c0)) < fabsf(__fsub_rn(x, E.c1));
+            bool good = !zero && (far ? ok_far : ok_in);
+            const float a = far ? E.cl : (inc ? plo : phi);
+            const float b = far ? E.cl2 : (inc ? phi : plo);
+            if (LOGM) // exact hits and levels without a usable host logarithm are the general search's business
+                good = good && (!trusted || (x != a && x != b && s_xd[jj] > 0. && !isnan(s_xl[jj])));
+            bool undefined = zero && zero_nan;
+            if (ranged)
+                undefined = undefined || !level_in_range(P, s_xd[jj], rlo, rhi);
+            int first = far ? nzi - 1 : (inc ? step - 1 : step);
+            int second = far ? nzi - 2 : (inc ? step : step - 1);
+            first = (good && !undefined) ? first : 0;
+            second = (good && !undefined) ? second : 0;
+            A[u] = __ldg(din + static_cast<unsigned>(first) * stride);
+            B[u] = __ldg(din + static_cast<unsigned>(second) * stride);
+            ca[u] = undefined ? INFINITY : (good ? a : nan_f());
+            cb[u] = b;
+        }
+#pragma unroll
+        for (int u = 0; u < SLG; ++u) {
+            const int jj = j0 + u;
+            if (jj < nzo) {
+                float r;
+                if (isnan(ca[u]))
+                    r = sweep_slow(C, sc, nzi, inc ? 1 : -1, din, s_xd[jj], s_xl[jj]);
+                else if (ca[u] == INFINITY)
+                    r = nan_f();
+                else if (LOGM && trusted)
+                    r = blend_levels<METHOD, true>(C, A[u], B[u], ca[u], cb[u], s_xd[jj], s_xl[jj]);
+                else
+                    r = blend_levels<METHOD, false>(C, A[u], B[u], ca[u], cb[u], s_xd[jj], s_xl[jj]);
+                float* dst = dout + static_cast<unsigned>(jj) * stride;
+                if (plain)
+                    __stcs(dst, r);
+                else
+                    store_result(C, dst, r);
+            }
+        }
+    }
+}
+
 // ---- hybrid-sigma source, launch-wide table -----------------------------------------------------------------------------------
 // p_k(ps) = ap_k + b_k*ps depends on the column only through ps, so n(x_j) is a step function of ps.  One small kernel proves
 // from the launch's ps range that every column is strictly monotone (as hybrid_direction() does on the host) and tabulates
@@ -1236,6 +1412,17 @@ static bool sweep_applies(const VertParams& P)
            P.nzi * P.nInner < (size_t(1) << 31) && P.nzo * P.nInner < (size_t(1) << 31); // 32-bit level offsets in the kernel
 }
 
+static size_t search_smem(const VertParams& P) // level list (f64, log, f32) + the block's coordinate columns [nzi][VT]
+{
+    return 2 * P.nzo * sizeof(double) + (P.nzo + (P.nzo & 1)) * sizeof(float) + P.nzi * VT * sizeof(float);
+}
+static bool search_applies(const VertParams& P)
+{
+    static const bool disabled = std::getenv("FIMEXCU_VERTICAL_NO_SEARCH") != nullptr;
+    return !disabled && P.vcoord_in && P.levels && !P.vcoord_out && P.nzi >= 2 && P.nzo >= 1 && search_smem(P) <= 96 * 1024 &&
+           P.nzi * P.nInner < (size_t(1) << 31) && P.nzo * P.nInner < (size_t(1) << 31); // 32-bit level offsets in the kernel
+}
+
 // direction of a fixed level list: +1 non-decreasing, -1 non-increasing, 0 unordered / NaN
 static int levels_direction(const double* lv, size_t n)
 {
@@ -1320,6 +1507,28 @@ static int launch_vertical(const VertParams& P, cudaStream_t s)
     if (P.method < 0 || P.method > FIMEXCU_VINT_METHOD_LIN_CONST_EXTRA)
         FXCU_FAIL("fimexcu_vertical: unknown vertical interpolation method");
     const unsigned blocks = static_cast<unsigned>((ncol + VT - 1) / VT);
+    if (search_applies(P)) { // explicit coordinate, fixed levels (sorted or not): scan + bisection
+        int rounds = 1;
+        while ((size_t(1) << rounds) <= P.nzi)
+            ++rounds;
+        const size_t smem = search_smem(P);
+        if (smem > 48 * 1024) {
+            static std::atomic<bool> raised{false};
+            if (!raised.exchange(true)) {
+                cudaFuncSetAttribute(vertical_search_kernel<FIMEXCU_VINT_METHOD_LOG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+                cudaFuncSetAttribute(vertical_search_kernel<FIMEXCU_VINT_METHOD_LIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+                cudaFuncSetAttribute(vertical_search_kernel<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+            }
+        }
+        if (P.method == FIMEXCU_VINT_METHOD_LOG)
+            vertical_search_kernel<FIMEXCU_VINT_METHOD_LOG><<<blocks, VT, smem, s>>>(P, rounds);
+        else if (P.method == FIMEXCU_VINT_METHOD_LIN)
+            vertical_search_kernel<FIMEXCU_VINT_METHOD_LIN><<<blocks, VT, smem, s>>>(P, rounds);
+        else
+            vertical_search_kernel<-1><<<blocks, VT, smem, s>>>(P, rounds);
+        FXCU_CUDA(cudaGetLastError());
+        return FIMEXCU_OK;
+    }
     if (sweep_applies(P)) {
         const size_t smem = sweep_smem(P);
         if (!P.vcoord_in)

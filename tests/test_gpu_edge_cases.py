@@ -199,3 +199,25 @@ def test_reproject_nothing_and_fill_nothing(fx):
     full = np.arange(42, dtype=np.float32).reshape(6, 7)
     filled, n = I.mifi_fill2d_f(full.copy())
     assert np.array_equal(filled, full)
+
+
+@pytest.mark.parametrize("method", [ol.VINT_LIN, ol.VINT_LOG, ol.VINT_LIN_NO])
+def test_vertical_explicit_coordinate_unsorted_and_repeated_levels(fx, method):
+    """target levels in no order, one of them twice, one NaN, through the explicit-coordinate path (scan + bisection: the level
+    list need not be sorted), on increasing, decreasing and a few non-monotone columns"""
+    from fimex_b200 import vertical as V
+    rng = np.random.default_rng(8)
+    nzi, ncol = 33, 4000
+    eta = np.linspace(0.02, 1.0, nzi)[:, None]
+    ps = rng.uniform(900.0, 1040.0, (1, ncol))
+    p = (ps * eta + 3.0 * (1 - eta)).astype(np.float32)
+    p[:, ::5] = p[::-1, ::5]                 # every fifth column decreasing
+    p[7, 11] = p[6, 11]                      # a repeated value: not strictly monotone
+    p[3, 13] = np.nan
+    fld = rng.normal(280, 20, (1, nzi, ncol)).astype(np.float32)
+    fld[rng.random(fld.shape) < 0.02] = np.nan
+    levels = np.array([500.0, 1000.0, 30.0, 850.0, 500.0, np.nan, 925.0, 1100.0, 1.0, float(p[5, 0])])
+    want = _oracle_vertical(method, fld, np.ascontiguousarray(p[None]), levels=levels)
+    got = V.verticalInterpolate(method, fld, np.ascontiguousarray(p[None]), level1=levels)
+    ok = _close if method == ol.VINT_LOG else _eq
+    assert ok(np.asarray(got).reshape(want.shape), want)
