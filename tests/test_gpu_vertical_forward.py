@@ -463,17 +463,19 @@ def test_config5_full_size_properties(fx):
     assert _close(out[0][:, idx].cpu().numpy()[None], w)
 
 
-@pytest.mark.parametrize("env", [{"FIMEXCU_VERTICAL_NO_TABLE": "1"}, {"FIMEXCU_VERTICAL_NO_TABLE": "1", "FIMEXCU_VERTICAL_NO_SWEEP": "1"}])
+@pytest.mark.parametrize("env", [{"FIMEXCU_VERTICAL_NO_TABLE": "1"}, {"FIMEXCU_VERTICAL_NO_TABLE": "1", "FIMEXCU_VERTICAL_NO_SWEEP": "1"},
+                                 {"FIMEXCU_VERTICAL_NO_SEARCH": "1"}])
 def test_vertical_fallback_tiers(env):
-    """The hybrid-sigma path has three tiers (launch-wide table -> one-pass sweep -> bisection per level); the lower ones serve
-    shapes the upper ones do not take.  The switches are read once per process, so the hybrid and sweep parity tests are re-run
-    in a subprocess with the upper tiers switched off."""
+    """The hybrid-sigma path has three tiers (launch-wide table -> one-pass sweep -> bisection per level), the explicit coordinate
+    two above the general kernel (scan + bisection in shared memory -> sweep); the lower ones serve shapes the upper ones do not
+    take.  The switches are read once per process, so the parity tests are re-run in a subprocess with the upper tiers switched off."""
     import subprocess
     import sys
     e = dict(os.environ)
     e.update(env)
     here = os.path.dirname(os.path.abspath(__file__))
+    select = "vertical and not fallback_tiers" if "FIMEXCU_VERTICAL_NO_SEARCH" in env else "hybrid or sweep or config5 or chained"
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_vertical_forward.py"), "-m", "gpu", "-x", "-q", "-p", "no:cacheprovider",
-                        "-k", "hybrid or sweep or config5 or chained"], env=e, capture_output=True, text=True, cwd=os.path.dirname(here))
+                        "-k", select], env=e, capture_output=True, text=True, cwd=os.path.dirname(here))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout
