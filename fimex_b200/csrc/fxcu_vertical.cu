@@ -1512,9 +1512,12 @@ static int launch_vertical(const VertParams& P, cudaStream_t s)
         while ((size_t(1) << rounds) <= P.nzi)
             ++rounds;
         const size_t smem = search_smem(P);
-        if (smem > 48 * 1024) {
-            static std::atomic<bool> raised{false};
-            if (!raised.exchange(true)) {
+        if (smem > 40 * 1024) { // (static + dynamic beyond 48 KB needs the opt-in; the limit is a property of the function ON A DEVICE)
+            static std::atomic<unsigned long long> raised{0};
+            int dev = 0;
+            FXCU_CUDA(cudaGetDevice(&dev));
+            const unsigned long long bit = 1ull << (dev & 63);
+            if (!(raised.fetch_or(bit) & bit)) {
                 cudaFuncSetAttribute(vertical_search_kernel<FIMEXCU_VINT_METHOD_LOG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
                 cudaFuncSetAttribute(vertical_search_kernel<FIMEXCU_VINT_METHOD_LIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
                 cudaFuncSetAttribute(vertical_search_kernel<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);

@@ -221,3 +221,22 @@ def test_vertical_explicit_coordinate_unsorted_and_repeated_levels(fx, method):
     got = V.verticalInterpolate(method, fld, np.ascontiguousarray(p[None]), level1=levels)
     ok = _close if method == ol.VINT_LOG else _eq
     assert ok(np.asarray(got).reshape(want.shape), want)
+
+
+@pytest.mark.parametrize("nzi", [93, 137, 300])
+def test_vertical_explicit_coordinate_long_columns(fx, nzi):
+    """columns whose staged copy needs more than the default 48 KB of shared memory per block (137 levels: opt-in limit), and more
+    than the kernel takes at all (300 levels: the sweep kernel serves them)"""
+    from fimex_b200 import vertical as V
+    rng = np.random.default_rng(9 + nzi)
+    ncol = 3000
+    eta = np.linspace(0.005, 1.0, nzi)[:, None]
+    ps = rng.uniform(900.0, 1040.0, (1, ncol))
+    p = (ps * eta + 2.0 * (1 - eta)).astype(np.float32)
+    fld = rng.normal(280, 20, (1, nzi, ncol)).astype(np.float32)
+    levels = np.array([1000.0, 925.0, 850.0, 700.0, 500.0, 300.0, 100.0, 10.0, 1.0])
+    for method in (ol.VINT_LIN, ol.VINT_LOG):
+        want = _oracle_vertical(method, fld, np.ascontiguousarray(p[None]), levels=levels)
+        got = V.verticalInterpolate(method, fld, np.ascontiguousarray(p[None]), level1=levels)
+        ok = _close if method == ol.VINT_LOG else _eq
+        assert ok(np.asarray(got).reshape(want.shape), want), (nzi, method)
