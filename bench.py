@@ -391,13 +391,16 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
     # K1+K2+K3: cache build from projection strings (one-off; points/s, no roofline)
     lon, lat = S.target_axes("T1")
     mx, my = S.meps_axes()
-    t0 = time.perf_counter()
-    c = RP.cachedInterpolationFromProjection(1, S.LATLON_PROJ, S.MEPS_PROJ, lon, lat, mx, my)
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    c.close()
+    dt = float("inf")
+    for _ in range(4):  # the tables are plain cudaMalloc'd (long-lived): single builds vary between 2 and 17 ms with the allocator
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        c = RP.cachedInterpolationFromProjection(1, S.LATLON_PROJ, S.MEPS_PROJ, lon, lat, mx, my)
+        torch.cuda.synchronize()
+        dt = min(dt, time.perf_counter() - t0)
+        c.close()
     out["K1_K2_K3_cache_build_from_projection"] = {"ms": dt * 1e3, "Mpoints_per_s": ox * oy / dt / 1e6,
-                                                   "what": "reproject_axes + 2x points2position + reduced domain + tables, 2.95 M targets, wall clock incl. allocations"}
+                                                   "what": "reproject_axes + 2x points2position + reduced domain + tables + row bands, 2.95 M targets, wall clock incl. allocations, best of 4"}
     return out
 
 # ------------------------------------------------------------------------------------------------ B200 arm
