@@ -1,5 +1,6 @@
 #!/bin/bash
 # A/B of the headline kernel's store path: st.global.cs per level (shipped) against TMA tensor stores (FIMEXCU_K4_TSTORE=1)
+# (the variant is not in the library: git apply profiles/exp/k4_tstore.patch and rebuild first)
 for rep in 1 2; do
   for v in 0 1; do
     if [ $v = 1 ]; then export FIMEXCU_K4_TSTORE=1; else unset FIMEXCU_K4_TSTORE; fi
