@@ -342,7 +342,7 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
     def chain():
         c2.interpolateValuesPadded(f_in, out=f_out)
         c2.interpolateValuesPadded(ps_in, out=ps_out)
-        return V.verticalHybridPressure(0, f_out.reshape(1, 65, n_inner), ap, b, ps_out.reshape(1, n_inner), levels, ps_scale=0.01)
+        return V.verticalHybridPressure(0, f_out.reshape(1, 65, n_inner), ap, b, ps_out.reshape(1, n_inner), levels, ps_scale=0.01, rows=(ox2, op2))
     ms = timed(chain, reps=3)
     alg_h = S.bilinear_algorithmic_bytes(c2.getInX() * c2.getInY(), ox2 * oy2, 65 * nmem) + S.bilinear_algorithmic_bytes(c2.getInX() * c2.getInY(), ox2 * oy2, nmem)
     alg_v = 312.0 * nmem * ox2 * oy2

@@ -112,6 +112,10 @@ SIGNATURES = {
                                                      C.c_float, C.c_float, vp]),
     "fimexcu_vertical_hybrid_pressure_dev_f": (C.c_int, [C.c_int, vp, sz, sz, sz, vp, vp, vp, sz, C.c_double, vp, sz, C.c_double,
                                                          C.c_double, C.c_float, C.c_float, vp, vp]),
+    "fimexcu_vertical_interpolate_rows_dev_f": (C.c_int, [C.c_int, vp, vp, sz, sz, sz, vp, vp, sz, vp, vp, C.c_double, C.c_double, C.c_float,
+                                                          C.c_float, vp, sz, sz, vp]),
+    "fimexcu_vertical_hybrid_pressure_rows_dev_f": (C.c_int, [C.c_int, vp, sz, sz, sz, vp, vp, vp, sz, C.c_double, vp, sz, C.c_double,
+                                                              C.c_double, C.c_float, C.c_float, vp, sz, sz, vp]),
     "fimexcu_get_values_nearest_f": (C.c_int, _two_level),
     "fimexcu_get_values_linear_f": (C.c_int, _two_level),
     "fimexcu_get_values_linear_weak_extrapol_f": (C.c_int, _two_level),

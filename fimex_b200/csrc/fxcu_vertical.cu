@@ -52,7 +52,15 @@ struct VertParams {
     float bad, fill;
     float* out;
     const double2* logtab; // 128-entry logarithm table in device memory (fxcu_logtable.h), made once per device
+    // rows of a padded slab (fimexcu_cache_padded_layout): of every rowPitch consecutive inner indices only the first rowWidth are
+    // columns; the pad is neither read nor written.  0 / 0: every inner index is a column.  (nInner < 2^32 when set.)
+    unsigned rowWidth, rowPitch;
 };
+
+__device__ __forceinline__ bool pad_column(const VertParams& P, size_t inner)
+{
+    return P.rowPitch != 0 && static_cast<unsigned>(inner) % P.rowPitch >= P.rowWidth;
+}
 
 // 1/d to ~1e-12 (one Newton step on the hardware's approximation) or to full f64 accuracy (two steps); d normal and positive
 __device__ __forceinline__ double rcp_newton(double d, bool full)
@@ -387,6 +395,15 @@ __device__ __forceinline__ void store_result(const OutCfg& C, float* dst, float 
     __stcs(dst, r);
 }
 
+// A column whose coordinate is NaN at every level (a hybrid column over an undefined surface pressure, an explicit column outside
+// the source grid of the horizontal step before): every difference the reference's scan forms is NaN, no comparison holds, it
+// ends at (0,0) for every target level (FindNeighborElements.h:91-125) and the result is undefined whatever the values are.
+__device__ __forceinline__ void column_undefined(const OutCfg& C, int nzo, size_t nInner, float* dout)
+{
+    for (int jj = 0; jj < nzo; ++jj)
+        store_result(C, dout + static_cast<size_t>(jj) * nInner, nan_f());
+}
+
 // out-of-line copy for the rare cases the table kernel's LOG path hands back (keeps its unrolled column loop small)
 __device__ __noinline__ float two_level_out_of_line(int method, float A, float B, double a, double b, double x, double xlog)
 {
@@ -491,6 +508,8 @@ __global__ void __launch_bounds__(VT) vertical_kernel(const VertParams P)
     if (cidx >= ncol)
         return;
     const size_t outer = cidx / P.nInner, inner = cidx - outer * P.nInner;
+    if (pad_column(P, inner))
+        return;
     if (MODE == 0) {
         float* mine = reinterpret_cast<float*>(smem_d) + threadIdx.x;
         const float* g = P.vcoord_in + outer * P.nzi * P.nInner + inner;
@@ -500,7 +519,10 @@ __global__ void __launch_bounds__(VT) vertical_kernel(const VertParams P)
     } else if (MODE == 1) {
         const size_t po = (P.nOuterPs == 1 ? 0 : outer) * P.nInner + inner;
         const double ps = __dmul_rn(static_cast<double>(__ldg(P.ps + po)), P.ps_scale);
-        vertical_column(P, HybridCol{smem_d, smem_d + nzi, ps}, cidx, outer, inner, isnan(ps) ? 0 : P.dir_hint);
+        if (isnan(ps)) // ap + b * NaN is NaN at every level
+            column_undefined(out_cfg(P), static_cast<int>(P.nzo), P.nInner, P.out + outer * P.nzo * P.nInner + inner);
+        else
+            vertical_column(P, HybridCol{smem_d, smem_d + nzi, ps}, cidx, outer, inner, P.dir_hint);
     } else {
         vertical_column(P, StridedCol{P.vcoord_in + outer * P.nzi * P.nInner + inner, static_cast<int>(P.nInner)}, cidx, outer, inner, 0);
     }
@@ -577,7 +599,22 @@ template <class Col>
 __device__ __forceinline__ void column_by_general_scan(const VertParams& P, const OutCfg& C, const Col& c, int nzi, int nzo, const double* s_xd,
                                                        const double* s_xl, double rlo, double rhi, const float* din, float* dout)
 {
-    const int dir = column_direction(c, nzi);
+    // direction (as column_direction) and "nothing but NaN" in one pass
+    bool inc = nzi >= 2, dec = nzi >= 2;
+    float prev = c(0);
+    bool allnan = isnan(prev);
+    for (int k = 1; k < nzi; ++k) {
+        const float cur = c(k);
+        inc = inc && (cur > prev);
+        dec = dec && (cur < prev);
+        allnan = allnan && isnan(cur);
+        prev = cur;
+    }
+    if (allnan) {
+        column_undefined(C, nzo, P.nInner, dout);
+        return;
+    }
+    const int dir = inc ? 1 : (dec ? -1 : 0);
     for (int jj = 0; jj < nzo; ++jj) {
         const double vout = s_xd[jj];
         float r = nan_f();
@@ -631,6 +668,8 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
     if (cidx >= ncol)
         return;
     const size_t outer = cidx / P.nInner, inner = cidx - outer * P.nInner;
+    if (pad_column(P, inner))
+        return;
     const float* din = P.in + outer * P.nzi * P.nInner + inner;
     float* dout = P.out + outer * P.nzo * P.nInner + inner;
     const float* gc = HYBRID ? nullptr : P.vcoord_in + outer * P.nzi * P.nInner + inner;
@@ -737,7 +776,9 @@ __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams 
                 note(nzi);
     }
     if (!ok) {
-        if (HYBRID)
+        if (HYBRID && isnan(ps)) // NaN surface pressure: ap + b * NaN is NaN at every level
+            column_undefined(C, nzo, P.nInner, dout);
+        else if (HYBRID)
             column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, rlo, rhi, din, dout);
         else
             column_by_general_scan(P, C, sc, nzi, nzo, s_xd, s_xl, rlo, rhi, din, dout);
@@ -872,6 +913,8 @@ __global__ void __launch_bounds__(VT, 6) vertical_search_kernel(const VertParams
     if (cidx >= ncol)
         return;
     const size_t outer = cidx / P.nInner, inner = cidx - outer * P.nInner;
+    if (pad_column(P, inner))
+        return;
     const float* din = P.in + outer * P.nzi * P.nInner + inner;
     float* dout = P.out + outer * P.nzo * P.nInner + inner;
     const float* gc = P.vcoord_in + outer * P.nzi * P.nInner + inner;
@@ -1052,7 +1095,9 @@ __device__ __forceinline__ int ps_hist_key(float v)
 
 // `every`: one block of 256 values in `every` is looked at.  The histogram only has to find where the bulk of the data lies; a column
 // whose ps falls outside the range found takes the general search (slower, never wrong), so a sample serves large launches.
-__global__ void __launch_bounds__(256) ps_hist_kernel(const float* __restrict__ ps, size_t n, unsigned* __restrict__ hist, unsigned every)
+// rowWidth / rowPitch: the pad columns of padded rows are skipped (rowPitch divides the inner size, so it divides the index too)
+__global__ void __launch_bounds__(256) ps_hist_kernel(const float* __restrict__ ps, size_t n, unsigned* __restrict__ hist, unsigned every, unsigned rowWidth,
+                                                      unsigned rowPitch)
 {
     __shared__ unsigned sh[PS_HIST_BINS];
     for (int i = threadIdx.x; i < PS_HIST_BINS; i += 256)
@@ -1061,7 +1106,7 @@ __global__ void __launch_bounds__(256) ps_hist_kernel(const float* __restrict__ 
     for (size_t base = blockIdx.x * 256ull * every; base < n; base += 256ull * every * gridDim.x) { // whole warps stay in step
         const size_t i = base + threadIdx.x;
         const float v = i < n ? __ldg(ps + i) : nan_f();
-        const bool valid = !isnan(v);
+        const bool valid = !isnan(v) && !(rowPitch != 0 && static_cast<unsigned>(i % rowPitch) >= rowWidth);
         const int key = valid ? ps_hist_key(v) : -1;
         const unsigned peers = __match_any_sync(0xffffffffu, key); // the data sit in a handful of bins: one atomic per bin and warp
         if (valid && static_cast<int>(threadIdx.x & 31) == __ffs(peers) - 1)
@@ -1362,12 +1407,17 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
         const size_t inner = (blockIdx.x * static_cast<size_t>(HT_CHUNKS) + chunk) * HT + threadIdx.x;
         if (inner >= P.nInner)
             return;
+        if (pad_column(P, inner))
+            continue;
         const float* din = P.in + outer * P.nzi * P.nInner + inner;
         float* dout = P.out + outer * P.nzo * P.nInner + inner;
         const double ps = __dmul_rn(static_cast<double>(__ldg(P.ps + (P.nOuterPs == 1 ? 0 : outer) * P.nInner + inner)), P.ps_scale);
         const PairCol hc{s_apb, ps};
         if (dir == 0 || !(ps >= ps_lo && ps <= ps_hi)) { // no proof for this launch, or a column outside its range (NaN, outlier)
-            column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, 0., 0., din, dout);
+            if (isnan(ps)) // ap + b * NaN is NaN at every level (the targets of a regridded slab that lie outside its source grid)
+                column_undefined(C, nzo, P.nInner, dout);
+            else
+                column_by_general_scan(P, C, hc, nzi, nzo, s_xd, s_xl, 0., 0., din, dout);
             continue;
         }
         const double t = (ps - ps_lo) * inv_width;
@@ -1380,10 +1430,12 @@ __global__ void __launch_bounds__(HT, 8) vertical_hybrid_table_kernel(const Vert
 }
 
 // min / max of the surface pressure of a launch (NaN ignored): lets the host prove monotonicity for all columns at once
-__global__ void __launch_bounds__(256) ps_minmax_kernel(const float* __restrict__ ps, size_t n, float* __restrict__ mm)
+__global__ void __launch_bounds__(256) ps_minmax_kernel(const float* __restrict__ ps, size_t n, float* __restrict__ mm, unsigned rowWidth, unsigned rowPitch)
 {
     float lo = INFINITY, hi = -INFINITY;
     for (size_t i = blockIdx.x * 256ull + threadIdx.x; i < n; i += 256ull * gridDim.x) {
+        if (rowPitch != 0 && static_cast<unsigned>(i % rowPitch) >= rowWidth)
+            continue; // pad column of a padded row
         const float v = ps[i];
         lo = fminf(lo, v);
         hi = fmaxf(hi, v);
@@ -1686,16 +1738,35 @@ static int two_level_host(int method, const float* A, const float* B, float* out
 
 using namespace fxcu;
 
+// rows of a padded slab: validates and stores the pair (0 / 0 = every inner index is a column)
+static int set_rows(VertParams& P, size_t nInner, size_t rowWidth, size_t rowPitch)
+{
+    if (rowWidth == 0 && rowPitch == 0)
+        return FIMEXCU_OK;
+    if (rowWidth == 0 || rowWidth > rowPitch || nInner % rowPitch != 0 || nInner >= (size_t(1) << 32))
+        FXCU_FAIL("vertical interpolation: rowWidth / rowPitch must satisfy 0 < rowWidth <= rowPitch, rowPitch dividing nInner (< 2^32)");
+    P.rowWidth = static_cast<unsigned>(rowWidth);
+    P.rowPitch = rowWidth == rowPitch ? 0u : static_cast<unsigned>(rowPitch); // no pad: nothing to test per column
+    if (P.rowPitch == 0)
+        P.rowWidth = 0;
+    return FIMEXCU_OK;
+}
+
 extern "C" {
 
-int fimexcu_vertical_interpolate_dev_f(int method, const float* d_in, const float* d_vcoord_in, size_t nOuter, size_t nzi, size_t nInner,
+int fimexcu_vertical_interpolate_rows_dev_f(int method, const float* d_in, const float* d_vcoord_in, size_t nOuter, size_t nzi, size_t nInner,
                                        const double* levels_host, const float* d_vcoord_out, size_t nzo, const double* d_vmin,
                                        const double* d_vmax, double valid_min, double valid_max, float badIn, float fillOut, float* d_out,
-                                       void* stream)
+                                       size_t rowWidth, size_t rowPitch, void* stream)
 {
     clear_error();
     if (!require_device())
         return FIMEXCU_ERROR;
+    {
+        VertParams chk{};
+        if (set_rows(chk, nInner, rowWidth, rowPitch) != FIMEXCU_OK)
+            return FIMEXCU_ERROR;
+    }
     if (!levels_host && !d_vcoord_out)
         FXCU_FAIL("fimexcu_vertical_interpolate: need either fixed levels or an output vertical coordinate");
     cudaStream_t s = as_stream(stream);
@@ -1719,6 +1790,7 @@ int fimexcu_vertical_interpolate_dev_f(int method, const float* d_in, const floa
     } else {
         P.vcoord_out = d_vcoord_out;
     }
+    set_rows(P, nInner, rowWidth, rowPitch);
     P.method = method;
     P.in = d_in;
     P.vcoord_in = d_vcoord_in;
@@ -1740,6 +1812,15 @@ int fimexcu_vertical_interpolate_dev_f(int method, const float* d_in, const floa
     if (levels_host)
         FXCU_CUDA(cudaStreamSynchronize(s)); // levels_host may be a temporary of the caller
     return rc;
+}
+
+int fimexcu_vertical_interpolate_dev_f(int method, const float* d_in, const float* d_vcoord_in, size_t nOuter, size_t nzi, size_t nInner,
+                                       const double* levels_host, const float* d_vcoord_out, size_t nzo, const double* d_vmin,
+                                       const double* d_vmax, double valid_min, double valid_max, float badIn, float fillOut, float* d_out,
+                                       void* stream)
+{
+    return fimexcu_vertical_interpolate_rows_dev_f(method, d_in, d_vcoord_in, nOuter, nzi, nInner, levels_host, d_vcoord_out, nzo, d_vmin, d_vmax, valid_min,
+                                                   valid_max, badIn, fillOut, d_out, 0, 0, stream);
 }
 
 int fimexcu_vertical_interpolate_f(int method, const float* in, const float* vcoord_in, size_t nOuter, size_t nzi, size_t nInner,
@@ -1782,14 +1863,19 @@ int fimexcu_vertical_interpolate_f(int method, const float* in, const float* vco
     return FIMEXCU_OK;
 }
 
-int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t nOuter, size_t nzi, size_t nInner, const double* ap_host,
-                                           const double* b_host, const float* d_ps, size_t nOuterPs, double ps_scale, const double* levels_host,
-                                           size_t nzo, double valid_min, double valid_max, float badIn, float fillOut, float* d_out,
-                                           void* stream)
+int fimexcu_vertical_hybrid_pressure_rows_dev_f(int method, const float* d_in, size_t nOuter, size_t nzi, size_t nInner, const double* ap_host,
+                                                const double* b_host, const float* d_ps, size_t nOuterPs, double ps_scale, const double* levels_host,
+                                                size_t nzo, double valid_min, double valid_max, float badIn, float fillOut, float* d_out,
+                                                size_t rowWidth, size_t rowPitch, void* stream)
 {
     clear_error();
     if (!require_device())
         return FIMEXCU_ERROR;
+    {
+        VertParams chk{};
+        if (set_rows(chk, nInner, rowWidth, rowPitch) != FIMEXCU_OK)
+            return FIMEXCU_ERROR;
+    }
     if (!(nOuterPs == 1 || nOuterPs == nOuter))
         FXCU_FAIL("fimexcu_vertical_hybrid_pressure: ps must have 1 or nOuter outer entries");
     if (!levels_host || !ap_host || !b_host || !d_ps)
@@ -1815,6 +1901,7 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
         d_coef = coef.as<double>();
     }
     VertParams P{};
+    set_rows(P, nInner, rowWidth, rowPitch);
     P.method = method;
     P.in = d_in;
     P.vcoord_in = nullptr;
@@ -1859,7 +1946,7 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
             const unsigned every = nps >= (size_t(1) << 22) ? 4u : 1u; // >= 4 M values: every fourth block of 256
             const size_t hblocks = (nps + 256ull * every - 1) / (256ull * every);
             ps_hist_kernel<<<static_cast<unsigned>(std::min<size_t>(hblocks, static_cast<size_t>(sm_count()) * 8)), 256, 0, s>>>(
-                d_ps, nps, reinterpret_cast<unsigned*>(base), every);
+                d_ps, nps, reinterpret_cast<unsigned*>(base), every, P.rowWidth, P.rowPitch);
         }
         hybrid_table_kernel<<<1, 256, 2 * nzi * sizeof(double), s>>>(P.ap, P.b, static_cast<int>(nzi), P.levels, static_cast<int>(nzo), reinterpret_cast<const unsigned*>(base),
                                                ps_scale, nbins, reinterpret_cast<HybridTableHeader*>(base + hdr_off),
@@ -1891,7 +1978,7 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
             return FIMEXCU_ERROR;
         FXCU_CUDA(cudaMemcpyAsync(mm.p, init, sizeof(init), cudaMemcpyHostToDevice, s));
         if (nps)
-            ps_minmax_kernel<<<static_cast<unsigned>(std::min<size_t>((nps + 255) / 256, 2048)), 256, 0, s>>>(d_ps, nps, mm.as<float>());
+            ps_minmax_kernel<<<static_cast<unsigned>(std::min<size_t>((nps + 255) / 256, 2048)), 256, 0, s>>>(d_ps, nps, mm.as<float>(), P.rowWidth, P.rowPitch);
         FXCU_CUDA(cudaGetLastError());
         int enc[2];
         FXCU_CUDA(cudaMemcpyAsync(enc, mm.p, sizeof(enc), cudaMemcpyDeviceToHost, s));
@@ -1908,6 +1995,15 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
     const int rc = launch_vertical(P, s);
     FXCU_CUDA(cudaStreamSynchronize(s)); // `h` is a temporary
     return rc;
+}
+
+int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t nOuter, size_t nzi, size_t nInner, const double* ap_host,
+                                           const double* b_host, const float* d_ps, size_t nOuterPs, double ps_scale, const double* levels_host,
+                                           size_t nzo, double valid_min, double valid_max, float badIn, float fillOut, float* d_out,
+                                           void* stream)
+{
+    return fimexcu_vertical_hybrid_pressure_rows_dev_f(method, d_in, nOuter, nzi, nInner, ap_host, b_host, d_ps, nOuterPs, ps_scale, levels_host, nzo, valid_min,
+                                                       valid_max, badIn, fillOut, d_out, 0, 0, stream);
 }
 
 int fimexcu_vertical_hybrid_pressure_f(int method, const float* in, size_t nOuter, size_t nzi, size_t nInner, const double* ap, const double* b,

@@ -165,7 +165,7 @@ inline std::pair<CudaSlab_p, CudaSlab_p> interpolateVectorSlabs(const CudaCached
 // CDMVerticalInterpolator::getLevelDataSlice for a hybrid-sigma source and fixed target levels (src/CDMVerticalInterpolator.cc:
 // 356-565 with HybridSigmaApToPressureConverter.cc:71-100): field [nLevels x nOther][ny][nx] laid out level-major (hybrid, member,
 // y, x) as CDM orders it, surface pressure [nOther][ny][nx] in the SAME layout -- both typically straight out of interpolateSlab().
-// The pad columns of the layout are carried along as ordinary (unused) columns.  ap in the unit of the target levels (hPa), ps * psScale too.
+// The pad elements of padded rows are skipped (neither read nor written).  ap in the unit of the target levels (hPa), ps * psScale too.
 inline CudaSlab_p cudaVerticalToFixedLevels(int method, const CudaSlab& field, size_t nLevels, const std::vector<double>& ap, const std::vector<double>& b,
                                             const CudaSlab& ps, double psScale, const std::vector<double>& levels, double validMin = NAN, double validMax = NAN)
 {
@@ -177,8 +177,11 @@ inline CudaSlab_p cudaVerticalToFixedLevels(int method, const CudaSlab& field, s
     cuda_glue::bind_thread();
     const size_t nInner = nOther * field.levelStride(); // (member, y, padded x) is one inner index: column = everything but the level
     CudaSlab_p out = CudaSlab::allocate(CudaSlab::FLOAT, levels.size() * nOther, field.ny(), field.nx(), field.rowPitch(), field.levelStride());
-    if (fimexcu_vertical_hybrid_pressure_dev_f(method, field.floatPtr(), 1, nLevels, nInner, ap.data(), b.data(), ps.floatPtr(), 1, psScale, levels.data(),
-                                               levels.size(), validMin, validMax, NAN, NAN, out->floatPtr(), nullptr) != FIMEXCU_OK)
+    // rows: only where the level stride is a whole number of rows (the padded layout's is) and the slab is small enough for the form
+    const bool rows = field.rowPitch() > field.nx() && field.levelStride() % field.rowPitch() == 0 && nInner < (size_t(1) << 32);
+    if (fimexcu_vertical_hybrid_pressure_rows_dev_f(method, field.floatPtr(), 1, nLevels, nInner, ap.data(), b.data(), ps.floatPtr(), 1, psScale, levels.data(),
+                                                    levels.size(), validMin, validMax, NAN, NAN, out->floatPtr(), rows ? field.nx() : 0,
+                                                    rows ? field.rowPitch() : 0, nullptr) != FIMEXCU_OK)
         throw CDMException(fimexcu_last_error());
     return out;
 }

@@ -32,21 +32,28 @@ def _ptr(a):
 
 
 def verticalInterpolate(method, inData, verticalIn, level1=None, verticalOut=None, validMin=None, validMax=None, valid_min=_NAN,
-                        valid_max=_NAN, badValue=_NAN, fillValue=_NAN):
+                        valid_max=_NAN, badValue=_NAN, fillValue=_NAN, rows=None, out=None):
     """inData, verticalIn: [nOuter][nzi][nInner] f32; level1: fixed target levels (f64) or verticalOut: [nOuter][nzo][nInner] f32.
     validMin/validMax: per-column f64 [nOuter][nInner] (converter validity range); valid_min/valid_max: the variable's
-    valid range (clamp).  Returns [nOuter][nzo][nInner] f32."""
+    valid range (clamp).  Returns [nOuter][nzo][nInner] f32.
+    rows = (rowWidth, rowPitch), CUDA tensors only: the inner index runs over padded rows (the result of a device-resident
+    horizontal step); the pad elements are neither read nor written.  out: a CUDA tensor to write into (device path)."""
     if _is_torch(inData):
         import torch
         nO, nzi, nI = inData.shape
         lv = _opt(level1, np.float64)
         nzo = lv.size if lv is not None else verticalOut.shape[1]
-        out = torch.empty((nO, nzo, nI), dtype=torch.float32, device=inData.device)
-        _lib.check(lib.fimexcu_vertical_interpolate_dev_f(
+        if out is None:
+            out = torch.empty((nO, nzo, nI), dtype=torch.float32, device=inData.device)
+        assert out.is_cuda and out.is_contiguous() and out.dtype == torch.float32 and out.numel() == nO * nzo * nI
+        rw, rp = rows if rows is not None else (0, 0)
+        _lib.check(lib.fimexcu_vertical_interpolate_rows_dev_f(
             method, inData.data_ptr(), verticalIn.data_ptr(), nO, nzi, nI, _ptr(lv), None if verticalOut is None else verticalOut.data_ptr(), nzo,
             None if validMin is None else validMin.data_ptr(), None if validMax is None else validMax.data_ptr(), valid_min, valid_max,
-            badValue, fillValue, out.data_ptr(), _lib.current_stream_ptr()), "verticalInterpolate")
+            badValue, fillValue, out.data_ptr(), rw, rp, _lib.current_stream_ptr()), "verticalInterpolate")
         return out
+    if rows is not None:
+        raise ValueError("rows: device slabs only")
     a, v = _f32(inData), _f32(verticalIn)
     nO, nzi, nI = a.shape
     assert v.shape == a.shape
@@ -59,18 +66,25 @@ def verticalInterpolate(method, inData, verticalIn, level1=None, verticalOut=Non
     return out
 
 
-def verticalHybridPressure(method, inData, ap, b, ps, level1, ps_scale=1.0, valid_min=_NAN, valid_max=_NAN, badValue=_NAN, fillValue=_NAN):
+def verticalHybridPressure(method, inData, ap, b, ps, level1, ps_scale=1.0, valid_min=_NAN, valid_max=_NAN, badValue=_NAN, fillValue=_NAN, rows=None,
+                           out=None):
     """inData [nOuter][nzi][nInner] f32; ap, b [nzi] f64 (ap in the unit of level1); ps [nOuter or 1][nInner] f32, multiplied by
-    ps_scale (unit conversion); level1 target pressures."""
+    ps_scale (unit conversion); level1 target pressures.  rows = (rowWidth, rowPitch): as verticalInterpolate."""
     apv, bv, lv = _opt(ap, np.float64), _opt(b, np.float64), _opt(level1, np.float64)
     if _is_torch(inData):
         import torch
         nO, nzi, nI = inData.shape
-        out = torch.empty((nO, lv.size, nI), dtype=torch.float32, device=inData.device)
-        _lib.check(lib.fimexcu_vertical_hybrid_pressure_dev_f(method, inData.data_ptr(), nO, nzi, nI, apv.ctypes.data, bv.ctypes.data, ps.data_ptr(),
-                                                              ps.shape[0], ps_scale, lv.ctypes.data, lv.size, valid_min, valid_max, badValue,
-                                                              fillValue, out.data_ptr(), _lib.current_stream_ptr()), "verticalHybridPressure")
+        if out is None:
+            out = torch.empty((nO, lv.size, nI), dtype=torch.float32, device=inData.device)
+        assert out.is_cuda and out.is_contiguous() and out.dtype == torch.float32 and out.numel() == nO * lv.size * nI
+        rw, rp = rows if rows is not None else (0, 0)
+        _lib.check(lib.fimexcu_vertical_hybrid_pressure_rows_dev_f(method, inData.data_ptr(), nO, nzi, nI, apv.ctypes.data, bv.ctypes.data, ps.data_ptr(),
+                                                                   ps.shape[0], ps_scale, lv.ctypes.data, lv.size, valid_min, valid_max, badValue,
+                                                                   fillValue, out.data_ptr(), rw, rp, _lib.current_stream_ptr()),
+                   "verticalHybridPressure")
         return out
+    if rows is not None:
+        raise ValueError("rows: device slabs only")
     a, p = _f32(inData), _f32(ps)
     nO, nzi, nI = a.shape
     p = p.reshape(-1, nI)

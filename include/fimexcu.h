@@ -389,6 +389,22 @@ int fimexcu_vertical_hybrid_pressure_dev_f(int method, const float* d_in, size_t
                                            const double* b_host, const float* d_ps, size_t nOuterPs, double ps_scale, const double* levels_host,
                                            size_t nzo, double valid_min, double valid_max, float badIn, float fillOut, float* d_out,
                                            void* stream);
+/* The two _dev forms above for slabs whose rows are PADDED (fimexcu_cache_padded_layout: the result of a device-resident horizontal
+ * step, handed on without repacking): the inner index runs over rows of rowPitch elements of which only the first rowWidth are
+ * columns.  The pad elements are neither read nor written, in any of the arrays (in, vcoord_in / ps, vcoord_out, vmin / vmax,
+ * out all share the layout) -- whatever they hold (they are never initialised by the horizontal kernels) costs nothing and cannot
+ * reach the surface-pressure statistics of the launch.  0 < rowWidth <= rowPitch, rowPitch divides nInner, nInner < 2^32;
+ * rowWidth = rowPitch = 0 means "every inner index is a column" (the plain _dev forms).  A reader chain over the reference's
+ * Interpolator -> VerticalInterpolator (src/CDMVerticalInterpolator.cc:356-565 pulling from src/CDMInterpolator.cc:219-263)
+ * passes rowWidth = outX and rowPitch = out_row_pitch of the horizontal cache. */
+int fimexcu_vertical_interpolate_rows_dev_f(int method, const float* d_in, const float* d_vcoord_in, size_t nOuter, size_t nzi, size_t nInner,
+                                            const double* levels_host, const float* d_vcoord_out, size_t nzo, const double* d_vmin,
+                                            const double* d_vmax, double valid_min, double valid_max, float badIn, float fillOut, float* d_out,
+                                            size_t rowWidth, size_t rowPitch, void* stream);
+int fimexcu_vertical_hybrid_pressure_rows_dev_f(int method, const float* d_in, size_t nOuter, size_t nzi, size_t nInner, const double* ap_host,
+                                                const double* b_host, const float* d_ps, size_t nOuterPs, double ps_scale,
+                                                const double* levels_host, size_t nzo, double valid_min, double valid_max, float badIn,
+                                                float fillOut, float* d_out, size_t rowWidth, size_t rowPitch, void* stream);
 /* Drop-ins with the reference signatures for the two-level kernels (include/fimex/interpolation.h:153-232,
  * src/interpolation.c:416-546); HOST pointers, n values per level. */
 int fimexcu_get_values_nearest_f(const float* infieldA, const float* infieldB, float* outfield, size_t n, double a, double b, double x);

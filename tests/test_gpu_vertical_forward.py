@@ -479,3 +479,66 @@ def test_vertical_fallback_tiers(env):
                         "-k", select], env=e, capture_output=True, text=True, cwd=os.path.dirname(here))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout
+
+
+# ---------------------------------------------------------------------------------- padded rows (slabs straight from the horizontal step)
+@pytest.mark.parametrize("kind", ["hybrid", "explicit"])
+def test_vertical_padded_rows_skip_the_pad(fx, kind):
+    """rows = (width, pitch): the pad elements of every row are neither read (whatever they hold cannot slow or change anything)
+    nor written; the columns give what the dense call gives.  Also: columns whose coordinate is NaN at every level."""
+    import torch
+    from fimex_b200.vertical import verticalHybridPressure, verticalInterpolate
+    rng = np.random.default_rng(31)
+    g = np.load(os.path.join(GOLD, "reference_vertical.npz"))
+    ap, b = g["en_ap_pa"] * 0.01, g["en_b"]
+    W, pitch, ny, nO, nzi = 37, 64, 23, 2, ap.size
+    nd, npad = ny * W, ny * pitch
+    levels = np.array([1000, 925, 850, 700, 500, 400, 300, 250, 200, 150, 100, 50, 1100], dtype=np.float64)
+    ps = (101325 - 12 * rng.uniform(0, 2500, (nO, nd)) + rng.normal(0, 300, (nO, nd))).astype(np.float32)
+    ps[:, ::29] = np.nan  # outside the source grid of the horizontal step
+    ps[0, 5] = np.float32(1e30)
+    fld = rng.normal(0, 10, (nO, nzi, nd)).astype(np.float32)
+    with np.errstate(all="ignore"):
+        p = (ap[None, :, None] + b[None, :, None] * (ps.astype(np.float64) * 0.01)[:, None, :]).astype(np.float32)
+    if kind == "explicit":
+        p[1, 3:9, 11] = np.nan  # a column that is NaN in part only
+    garbage = np.array([0.0, np.nan, 1e30, -5.0, 3.0e4, np.inf, 101325.0], dtype=np.float32)
+
+    def padded(a):  # [..., nd] -> [..., npad] with garbage in the pad
+        lead = a.shape[:-1]
+        buf = np.resize(garbage, int(np.prod(lead)) * npad).reshape(lead + (ny, pitch)).copy()
+        buf[..., :W] = a.reshape(lead + (ny, W))
+        return torch.from_numpy(buf.reshape(lead + (npad,))).cuda()
+
+    for m in (ol.VINT_LIN, ol.VINT_LOG):
+        want = _oracle_vertical(m, fld, np.ascontiguousarray(p), levels=levels)
+        out = torch.full((nO, levels.size, npad), 12345.0, dtype=torch.float32, device="cuda")
+        if kind == "hybrid":
+            verticalHybridPressure(m, padded(fld), ap, b, padded(ps), levels, ps_scale=0.01, rows=(W, pitch), out=out)
+            dense = verticalHybridPressure(m, torch.from_numpy(fld).cuda(), ap, b, torch.from_numpy(ps).cuda(), levels, ps_scale=0.01)
+        else:
+            verticalInterpolate(m, padded(fld), padded(p), level1=levels, rows=(W, pitch), out=out)
+            dense = verticalInterpolate(m, torch.from_numpy(fld).cuda(), torch.from_numpy(p).cuda(), level1=levels)
+        torch.cuda.synchronize()
+        got = out.cpu().numpy().reshape(nO, levels.size, ny, pitch)
+        assert np.all(got[..., W:] == 12345.0), "pad elements were written"
+        cols = got[..., :W].reshape(nO, levels.size, nd)
+        assert _eq(cols, dense.cpu().numpy()), (kind, m)
+        assert (_eq if m == ol.VINT_LIN else _close)(cols, want), (kind, m)
+        assert np.isnan(cols[:, :, ::29]).all()
+
+
+def test_vertical_padded_rows_arguments(fx):
+    import torch
+    from fimex_b200.vertical import verticalInterpolate
+    from fimex_b200._lib import FimexCudaError
+    f = torch.zeros((1, 4, 128), dtype=torch.float32, device="cuda")
+    c = torch.arange(4, dtype=torch.float32, device="cuda").reshape(1, 4, 1).repeat(1, 1, 128).contiguous()
+    lv = np.array([1.5])
+    for rows in ((0, 64), (65, 64), (30, 48)):  # no width, width beyond the pitch, pitch that does not divide the inner size
+        with pytest.raises(FimexCudaError):
+            verticalInterpolate(ol.VINT_LIN, f, c, level1=lv, rows=rows)
+    a = verticalInterpolate(ol.VINT_LIN, f, c, level1=lv, rows=(64, 64))  # no pad: the plain form
+    b = verticalInterpolate(ol.VINT_LIN, f, c, level1=lv)
+    torch.cuda.synchronize()
+    assert _eq(a.cpu().numpy(), b.cpu().numpy())
