@@ -1243,15 +1243,31 @@ static long long clamp_ex(long long low, double v, long long extend, long long h
     return std::max(low, std::min(value, high));
 }
 
-// number of levels per blockIdx.z chunk so that small targets still fill the machine
+// Levels per blockIdx.z chunk: at least `min_chunks` chunks, none longer than ~80 levels, each a multiple of `zb` levels.
+// The cap: CTAs that walk hundreds of levels drift apart, and the source cells that neighbouring tiles share (the staged kernels'
+// boxes over-fetch 2-4x) stop meeting in L2 -- S->T1 with 650 levels in one launch ran at 5.26 us per level with one chunk per
+// tile against 3.09 us with chunks of 64 (T2, 1950 levels: 0.81 against 0.53; profiles/exp/zchunk_probe.py).  FIMEXCU_ZCHUNK_MAX
+// overrides the cap (read once).
+static int level_chunk(int nz, size_t min_chunks, int zb)
+{
+    static const int cap = []() {
+        const char* e = getenv("FIMEXCU_ZCHUNK_MAX");
+        const int v = e ? atoi(e) : 0;
+        return v > 0 ? v : 80;
+    }();
+    if (nz <= 1)
+        return std::max(nz, 1);
+    size_t chunks = std::max<size_t>(std::max<size_t>(min_chunks, 1), (static_cast<size_t>(nz) + cap - 1) / cap);
+    chunks = std::min<size_t>(chunks, static_cast<size_t>(nz));
+    const size_t per = (static_cast<size_t>(nz) + chunks - 1) / chunks;
+    return static_cast<int>((per + zb - 1) / zb * zb);
+}
+
+// direct kernels: enough chunks that small targets still fill the machine
 static int pick_zchunk(size_t tiles, int nz)
 {
     const size_t want = static_cast<size_t>(sm_count()) * 8 * 2; // two waves of 8 resident CTAs per SM
-    if (tiles >= want || nz <= 1)
-        return nz;
-    size_t chunks = (want + tiles - 1) / tiles;
-    chunks = std::min<size_t>(chunks, static_cast<size_t>(nz));
-    return static_cast<int>((nz + chunks - 1) / chunks);
+    return level_chunk(nz, tiles >= want ? 1 : (want + tiles - 1) / tiles, 1);
 }
 
 // per target row: first and one-past-last column whose table entry is defined (lo >= hi: none)
@@ -1549,7 +1565,7 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
             const size_t slots = static_cast<size_t>(sm_count()) * 6;
             size_t zsplit = std::max<size_t>(1, (8 * slots + tiles - 1) / tiles); // 16 / 24 waves measured slower on T1
             zsplit = std::min<size_t>(zsplit, std::max<size_t>(1, static_cast<size_t>(P.nz) / (4 * TMA_ZB)));
-            P.zchunk = static_cast<int>(((static_cast<size_t>(P.nz) + zsplit - 1) / zsplit + TMA_ZB - 1) / TMA_ZB * TMA_ZB);
+            P.zchunk = level_chunk(P.nz, zsplit, TMA_ZB);
             const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH),
                             static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
             if (c->kind == KIND_NN)
@@ -1568,7 +1584,7 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
             const size_t slots = static_cast<size_t>(sm_count()) * 5;
             size_t zsplit = std::max<size_t>(1, (8 * slots + tiles - 1) / tiles);
             zsplit = std::min<size_t>(zsplit, std::max<size_t>(1, static_cast<size_t>(P.nz) / (4 * CUB_ZB)));
-            P.zchunk = static_cast<int>(((static_cast<size_t>(P.nz) + zsplit - 1) / zsplit + CUB_ZB - 1) / CUB_ZB * CUB_ZB);
+            P.zchunk = level_chunk(P.nz, zsplit, CUB_ZB);
             const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH),
                             static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
             staged_bicubic_tma_kernel<BAD, FILL><<<grid, TMA_THREADS, 0, s>>>(map, P);
@@ -2314,7 +2330,7 @@ static int cache_apply_uv_strided(const fimexcu_cache* c, const fimexcu_vecrot* 
         const size_t slots = static_cast<size_t>(sm_count()) * 5; // see launch_cache_apply
         size_t zsplit = std::max<size_t>(1, (8 * slots + tiles - 1) / tiles);
         zsplit = std::min<size_t>(zsplit, std::max<size_t>(1, nz / (4 * UV_ZB)));
-        P.zchunk = static_cast<int>(((nz + zsplit - 1) / zsplit + UV_ZB - 1) / UV_ZB * UV_ZB);
+        P.zchunk = level_chunk(P.nz, zsplit, UV_ZB);
         const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH),
                         static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
         // a NaN bad value never compares equal and a NaN fill value re-writes NaN: the <true,true> variant is always correct
