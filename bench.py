@@ -592,6 +592,27 @@ def main_b200(args):
         job = {"slabs": S.MEPS_NT, "slabs_per_rank": counts, "imbalance": max(counts) * world / S.MEPS_NT,
                "device_resident": {"value": S.MEPS_NT * points_per_step / (float(tj.item()) * 1e-3) / 1e9, "unit": UNIT, "ms": float(tj.item()),
                                    "what": "all 67 slabs, inputs resident in HBM (3 rotating slabs per rank), max over ranks"}}
+        # the same with the slabs dealt over two streams, as two of the reference's writer threads would issue them
+        # (NetCDF_CDMWriter.cc:599-606): the ramp of one launch fills the tail of the other
+        two = [torch.cuda.Stream(), torch.cuda.Stream()]
+        cur = torch.cuda.current_stream()
+        barrier()
+        ev0.record()
+        for q in two:
+            q.wait_event(ev0)
+        for k, (t, z0, z1) in enumerate(mine):
+            _lib.check(lib.fimexcu_cache_apply_dev_strided_f(ci._h, slabs[k % n_slabs].data_ptr(), ip, il, nz, outs[k % 2].data_ptr(), op, ol,
+                                                             float("nan"), float("nan"), two[k % 2].cuda_stream), "apply")
+        for q in two:
+            cur.wait_stream(q)
+        ev1.record()
+        barrier()
+        launches += len(mine)
+        tj2 = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tj2, op=dist.ReduceOp.MAX)
+        job["device_resident_two_streams"] = {"value": S.MEPS_NT * points_per_step / (float(tj2.item()) * 1e-3) / 1e9, "unit": UNIT, "ms": float(tj2.item()),
+                                              "what": "the same 67 slabs issued alternately on two streams"}
         if not args.no_e2e:
             n_job = len(mine) if args.full_job else min(len(mine), 6)  # bounded sample of this rank's share unless --full-job
             barrier()

@@ -597,7 +597,12 @@ __global__ void __launch_bounds__(TMA_THREADS, 6) staged_apply_tma_kernel(const 
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    // Programmatic dependent launch: the next launch on the stream may place its CTAs as soon as every CTA of this one has started,
+    // so that its table loads and barrier set-up run while this launch drains; it touches no slab before the launch before it is
+    // complete (the wait below).  The tables read above belong to the cache and are final when a cache handle exists.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     __syncthreads();
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int bx0 = meta.x, by0 = meta.y;
     const bool all_interior = (meta.z & TILE_ALL_INTERIOR) != 0;
     // blockIdx.z selects a chunk of levels (a multiple of TMA_ZB): few tiles x many levels would otherwise leave the last wave
@@ -1568,10 +1573,20 @@ static void launch_cache_apply(const fimexcu_cache* c, const ApplyParams& P0, cu
             P.zchunk = level_chunk(P.nz, zsplit, TMA_ZB);
             const dim3 grid(static_cast<unsigned>((c->outX + 31) / 32), static_cast<unsigned>((c->outY + TMA_TH - 1) / TMA_TH),
                             static_cast<unsigned>((P.nz + P.zchunk - 1) / P.zchunk));
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = grid;
+            cfg.blockDim = dim3(TMA_THREADS);
+            cfg.stream = s;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            static const bool pdl = getenv("FIMEXCU_NO_PDL") == nullptr;
+            cfg.attrs = attr;
+            cfg.numAttrs = pdl ? 1 : 0;
             if (c->kind == KIND_NN)
-                staged_apply_tma_kernel<BAD, FILL, true><<<grid, TMA_THREADS, 0, s>>>(map, P);
+                cudaLaunchKernelEx(&cfg, staged_apply_tma_kernel<BAD, FILL, true>, map, P);
             else
-                staged_apply_tma_kernel<BAD, FILL, false><<<grid, TMA_THREADS, 0, s>>>(map, P);
+                cudaLaunchKernelEx(&cfg, staged_apply_tma_kernel<BAD, FILL, false>, map, P);
             return;
         }
     }
