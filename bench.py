@@ -388,6 +388,49 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
                                                           f"2030x1354 swath -> {tox}x{toy}, 65 levels; points = source points")
                 del fin65, fout65
             fwd.close()
+    # one-off builds and pre / post-processing of the path (wall clock of the call as a user makes it; no roofline: search- or
+    # sweep-bound, not streams)
+    def wall(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        best = float("inf")
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            torch.cuda.synchronize()
+            best = min(best, time.perf_counter() - t0)
+        return best * 1e3
+
+    try:
+        from fimex_b200.coordinates import flannTranslatePointsToClosestInputCell, fastTranslatePointsToClosestInputCell
+        slon, slat = S.swath_lonlat()
+        tlon, tlat = np.meshgrid(np.arange(0, 20, 0.025), np.arange(58, 70, 0.025))
+        maxdist = 0.025 * np.pi / 180 * 6371000.0
+        what4 = f"configs[3]: 2030x1354 swath -> {tlon.shape[1]}x{tlon.shape[0]} targets, host arrays in and out, best of 3"
+        out["K9_coord_kdtree_translate"] = {"ms": wall(lambda: flannTranslatePointsToClosestInputCell(maxdist, tlon, tlat, slon, slat)), "what": what4}
+        out["K10_coord_nearestneighbor_translate"] = {"ms": wall(lambda: fastTranslatePointsToClosestInputCell(tlon, tlat, slon, slat)), "what": what4}
+        fpx, fpy = (slon - 0.0) / 0.025, (slat - 58.0) / 0.025
+        out["K11_forward_cache_build"] = {"ms": wall(lambda: I.CachedForwardInterpolation("x", "y", 6, fpx, fpy, 1354, 2030, tlon.shape[1], tlon.shape[0]).close()),
+                                          "what": "CachedForwardInterpolation ctor, same swath and target (tables from the host), best of 3"}
+        del slon, slat, tlon, tlat, fpx, fpy
+        lonT, latT = S.target_axes("T1")
+        out["K8_vector_rotation_matrix_build"] = {"ms": wall(lambda: RP.get_vector_reproject_matrix(S.MEPS_PROJ, S.LATLON_PROJ, lonT, latT)),
+                                                  "what": "get_vector_reproject_matrix for the 2.95 M targets of T1 (host arrays out), best of 3"}
+    except Exception as exc:  # keep the bench line even if one of the one-off builds fails
+        out["one_off_builds_error"] = str(exc)[:200]
+    try:
+        yy, xx = np.meshgrid(np.arange(S.MEPS_NY), np.arange(S.MEPS_NX), indexing="ij")
+        base = (280 + 15 * np.sin(xx / 90.0) * np.cos(yy / 70.0)).astype(np.float32)
+        land = torch.from_numpy(np.sin(xx / 37.0) * np.cos(yy / 53.0) > 0.55).cuda()  # ~20 % undefined blobs
+        fld = torch.from_numpy(base).cuda()[None].repeat(nz, 1, 1) + torch.randn((nz, S.MEPS_NY, S.MEPS_NX), device="cuda")
+        fld[:, land] = nan
+        out["K16_fill2d_65_levels"] = {"ms": wall(lambda: I.mifi_fill2d_f(fld.clone(), 0.01, 1.6, 100), reps=2),
+                                       "what": "mifi_fill2d_f on 65 levels of 949x1069 with ~20 % undefined (device slab, incl. a clone of it)"}
+        out["K16_creepfill2d_65_levels"] = {"ms": wall(lambda: I.mifi_creepfill2d_f(fld.clone(), 20, 2), reps=2),
+                                            "what": "mifi_creepfill2d_f (repeat 20, weight 2), same slab"}
+        del fld, land
+    except Exception as exc:
+        out["fill_error"] = str(exc)[:200]
     # K1+K2+K3: cache build from projection strings (one-off; points/s, no roofline)
     lon, lat = S.target_axes("T1")
     mx, my = S.meps_axes()

@@ -102,3 +102,15 @@ def bilinear_algorithmic_bytes(n_in_reduced, n_out, nz, table_bytes=16):
     + table_bytes/nz; returned for one slab of nz levels."""
     per_point = 4.0 + 4.0 * n_in_reduced / n_out + table_bytes / nz
     return per_point * n_out * nz
+
+
+def swath_lonlat(nx=1354, ny=2030, seed=SEED):
+    """curvilinear longitude / latitude of a tilted satellite swath, NaN-free: [ny][nx] f64 each"""
+    rng = np.random.default_rng(seed)
+    u = np.linspace(-1, 1, nx)[None, :]
+    v = np.linspace(0, 1, ny)[:, None]
+    lat = 55 + 20 * v + 2.5 * u + 0.3 * np.sin(6 * v) * u
+    lon = 5 + 18 * u / np.cos(np.radians(lat)) * 0.5 + 9 * v
+    lat = lat + rng.normal(0, 1e-4, lat.shape)
+    lon = lon + rng.normal(0, 1e-4, lon.shape)
+    return np.ascontiguousarray(lon), np.ascontiguousarray(lat)
