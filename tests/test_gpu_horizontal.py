@@ -356,13 +356,15 @@ def test_bicubic_staged_kernel_padded_layout(fx, oracle, shape, special):
     assert _eq(out[:, :, :out_x].cpu().numpy(), wf)
     assert (~np.isnan(want)).mean() > 0.5
     ci.setFastBicubic(True)
-    fast = ci.interpolateValuesPadded(pin)[:, :, :out_x].cpu().numpy() if not special else None
+    fast = ci.interpolateValuesPadded(pin, **kw)[:, :, :out_x].cpu().numpy()
     ci.setFastBicubic(False)
-    if fast is not None:
-        assert np.array_equal(np.isnan(fast), np.isnan(want))
-        ok = ~np.isnan(want)
-        assert np.abs(fast[ok] - want[ok]).max() <= 1e-5 * np.nanmax(np.abs(clean))
-        assert not np.array_equal(fast[ok], want[ok])  # it really is the other arithmetic
+    ok = ~np.isnan(want)
+    if special:  # undefined where the reference is, and there the fill value
+        assert np.array_equal(fast == fill, ~ok) and not np.isnan(fast).any()
+    else:
+        assert np.array_equal(np.isnan(fast), ~ok)
+    assert np.abs(fast[ok] - want[ok]).max() <= 1e-5 * np.nanmax(np.abs(clean))
+    assert not np.array_equal(fast[ok], want[ok])  # it really is the other arithmetic
 
 
 def test_nearest_staged_kernel_padded_layout(fx, oracle):
