@@ -242,7 +242,8 @@ def test_meps_t1_full_slab_properties(fx, meps_t1):
 
 
 # ---------------------------------------------------------------------------------- staged (TMA) kernel and strided layouts
-@pytest.mark.parametrize("shape", [(300, 200, 1400, 900, 9), (949, 1069, 2891, 1021, 3), (128, 96, 700, 500, 65)])
+# (170 levels: more than one level chunk per tile, the last one shorter -- level_chunk() in fxcu_apply.cu)
+@pytest.mark.parametrize("shape", [(300, 200, 1400, 900, 9), (949, 1069, 2891, 1021, 3), (128, 96, 700, 500, 65), (128, 96, 700, 500, 170)])
 @pytest.mark.parametrize("special", [False, True])
 def test_bilinear_staged_kernel_padded_layout(fx, oracle, shape, special):
     """the headline kernel (TMA-staged, warp-specialised) in the padded device layout, incl. rim tiles, tiles that do
@@ -323,7 +324,7 @@ def test_output_window_equals_slice_of_full_result(fx, method):
         ci.sliceOutput(full, 0, out_x + 1, 0, 1)
 
 
-@pytest.mark.parametrize("shape", [(300, 200, 1400, 900, 9), (128, 96, 700, 500, 65)])
+@pytest.mark.parametrize("shape", [(300, 200, 1400, 900, 9), (128, 96, 700, 500, 65), (128, 96, 700, 500, 170)])
 @pytest.mark.parametrize("special", [False, True])
 def test_bicubic_staged_kernel_padded_layout(fx, oracle, shape, special):
     """bicubic on padded device slabs: bit-exact (direct kernel) incl. the fused bad/fill conversions; the opt-in f32 variant (staged
@@ -391,13 +392,14 @@ def test_nearest_staged_kernel_padded_layout(fx, oracle):
     assert _eq(dense.cpu().numpy(), w2)
 
 
+@pytest.mark.parametrize("nz", [5, 90])  # 90: two level chunks per tile
 @pytest.mark.parametrize("special", [False, True])
-def test_fused_uv_staged_kernel_padded_layout(fx, oracle, special):
+def test_fused_uv_staged_kernel_padded_layout(fx, oracle, special, nz):
     """u,v interpolation + rotation as one TMA-staged kernel (padded layout) == the three separate reference steps"""
     import torch
     from fimex_b200.interpolation import interpolateVectorValuesPadded
     rng = np.random.default_rng(77)
-    in_x, in_y, out_x, out_y, nz = 300, 200, 1400, 900, 5
+    in_x, in_y, out_x, out_y = 300, 200, 1400, 900
     gx, gy = np.meshgrid(np.arange(out_x), np.arange(out_y))
     px = -3.0 + gx * ((in_x + 5.0) / out_x) + 0.11 * gy * (in_x / out_x)
     py = -2.5 + gy * ((in_y + 4.0) / out_y) - 0.07 * gx * (in_y / out_y)
