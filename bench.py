@@ -296,6 +296,10 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
     ms = timed(lambda: _lib.check(lib.fimexcu_cache_apply_uv_dev_strided_f(ci._h, cvr._h, pin.data_ptr(), pin.data_ptr(), ip, il, nz, pu.data_ptr(),
                                                                            pv.data_ptr(), op, ol_, nan, nan, nan, nan, stream), "uv"))
     out["K7_fused_uv_bilinear_rotation_padded_staged"] = entry(ms, 2 * alg + 16.0 * ox * oy, 2 * pts, "same, padded layout, TMA-staged")
+    pu.normal_()
+    pv.normal_()
+    ms = timed(lambda: _lib.check(lib.fimexcu_vecrot_apply_dev_strided_f(cvr._h, pu.data_ptr(), pv.data_ptr(), op, ol_, nz, stream), "rot"))
+    out["K7_rotation_alone_padded"] = entry(ms, (16.0 + 16.0 / nz) * pts, 2 * pts, "in-place rotation of u,v in the padded layout (rows on 128 B: 16-byte accesses)")
     del pin, pu, pv
     ms = timed(lambda: _lib.check(lib.fimexcu_vecrot_apply_dev_f(cvr._h, dst.data_ptr(), dst2.data_ptr(), nz, stream), "rot"))
     out["K7_rotation_alone"] = entry(ms, (16.0 + 16.0 / nz) * pts, 2 * pts, "in-place rotation of u,v [65][1021][2891]")

@@ -78,6 +78,7 @@ SIGNATURES = {
     "fimexcu_vecrot_create_dev": (vp, [vp, sz, sz, vp]),
     "fimexcu_vecrot_apply_f": (C.c_int, [vp, vp, vp, sz]),
     "fimexcu_vecrot_apply_dev_f": (C.c_int, [vp, vp, vp, sz, vp]),
+    "fimexcu_vecrot_apply_dev_strided_f": (C.c_int, [vp, vp, vp, sz, sz, sz, vp]),
     "fimexcu_vecrot_direction_f": (C.c_int, [vp, vp, sz]),
     "fimexcu_vecrot_direction_dev_f": (C.c_int, [vp, vp, sz, vp]),
     "fimexcu_vecrot_destroy": (None, [vp]),

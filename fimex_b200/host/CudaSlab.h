@@ -162,6 +162,17 @@ inline std::pair<CudaSlab_p, CudaSlab_p> interpolateVectorSlabs(const CudaCached
     return {uo, vo};
 }
 
+// CDMProcessor's rotation of a vector to another projection's axes (src/CDMProcessor.cc:114-157 -> CachedVectorReprojection::
+// reprojectValues) on device slabs of whatever row pitch, in place; the pad elements of padded rows are not touched
+inline void rotateVectorSlabs(const CudaCachedVectorReprojection& cvr, CudaSlab& u, CudaSlab& v)
+{
+    if (u.rowPitch() != v.rowPitch() || u.levelStride() != v.levelStride() || u.nz() != v.nz() || u.type() != CudaSlab::FLOAT || v.type() != CudaSlab::FLOAT)
+        throw CDMException("rotateVectorSlabs: u and v differ in shape or layout, or are not float slabs");
+    cuda_glue::bind_thread();
+    if (fimexcu_vecrot_apply_dev_strided_f(cvr.handle(), u.floatPtr(), v.floatPtr(), u.rowPitch(), u.levelStride(), u.nz(), nullptr) != FIMEXCU_OK)
+        throw CDMException(std::string("error during vector rotation: ") + fimexcu_last_error());
+}
+
 // CDMVerticalInterpolator::getLevelDataSlice for a hybrid-sigma source and fixed target levels (src/CDMVerticalInterpolator.cc:
 // 356-565 with HybridSigmaApToPressureConverter.cc:71-100): field [nLevels x nOther][ny][nx] laid out level-major (hybrid, member,
 // y, x) as CDM orders it, surface pressure [nOther][ny][nx] in the SAME layout -- both typically straight out of interpolateSlab().

@@ -176,6 +176,22 @@ static int chain_mode(const char* in_path, const char* out_path)
         auto uv = interpolateVectorSlabs(ci, cvr, *psIn, *firstLevel);
         // writer side
         shared_array<float> hv = vert->asFloat(), hu = uv.first->asFloat(), hvv = uv.second->asFloat();
+        {
+            // the same pair by the separate steps (interpolate each, rotate in place on the padded slabs): identical bits
+            CudaSlab_p su = interpolateSlab(ci, *psIn), sv = interpolateSlab(ci, *firstLevel);
+            rotateVectorSlabs(cvr, *su, *sv);
+            shared_array<float> a = su->asFloat(), b2 = sv->asFloat();
+            auto same = [](const float* x, const float* y, size_t n) { // NaN where the other is NaN, equal bits elsewhere
+                for (size_t i = 0; i < n; ++i)
+                    if ((x[i] != x[i]) != (y[i] != y[i]) || (x[i] == x[i] && std::memcmp(x + i, y + i, 4) != 0))
+                        return false;
+                return true;
+            };
+            if (!same(a.get(), hu.get(), uv.first->size()) || !same(b2.get(), hvv.get(), uv.second->size())) {
+                fprintf(stderr, "rotateVectorSlabs differs from the fused vector pass\n");
+                return 7;
+            }
+        }
         FILE* o = fopen(out_path, "wb");
         fwrite(hv.get(), 4, vert->size(), o);
         fwrite(hu.get(), 4, uv.first->size(), o);

@@ -335,6 +335,14 @@ class CachedVectorReprojection:
         size = uValues.size if size is None else size
         _lib.check(lib.fimexcu_vecrot_apply_f(self._h, uValues.ctypes.data, vValues.ctypes.data, size), "reprojectValues")
 
+    def reprojectValuesPadded(self, uPadded, vPadded):
+        """in place on CUDA slabs [nz][oy][row_pitch] (the padded rows of a device-resident chain); the pad elements are not touched"""
+        assert uPadded.is_cuda and uPadded.is_contiguous() and vPadded.is_contiguous() and uPadded.shape == vPadded.shape
+        nz, oy, pitch = uPadded.shape
+        assert oy == self.oy and pitch >= self.ox
+        _lib.check(lib.fimexcu_vecrot_apply_dev_strided_f(self._h, uPadded.data_ptr(), vPadded.data_ptr(), pitch, oy * pitch, nz, _lib.current_stream_ptr()),
+                   "reprojectValues")
+
     def replicate(self, devices):
         """the matrix on every listed device (see CachedInterpolationInterface.replicate)"""
         ids = (C.c_int * len(devices))(*devices)

@@ -226,6 +226,10 @@ fimexcu_vecrot* fimexcu_vecrot_create_dev(const double* d_matrix3, size_t ox, si
  * (CachedVectorReprojection.cc:44-48, reproject.cc:488-507): in place, size = nz*ox*oy. */
 int fimexcu_vecrot_apply_f(const fimexcu_vecrot* r, float* u, float* v, size_t size);
 int fimexcu_vecrot_apply_dev_f(const fimexcu_vecrot* r, float* d_u, float* d_v, size_t nz, void* stream);
+/* the same in place on device slabs with a row pitch and a level stride in elements (the padded rows of fimexcu_cache_padded_layout,
+ * as a CDMProcessor-style rotation behind a device-resident horizontal step meets them: src/CDMProcessor.cc:114-157); the pad
+ * elements of the rows are not touched */
+int fimexcu_vecrot_apply_dev_strided_f(const fimexcu_vecrot* r, float* d_u, float* d_v, size_t row_pitch, size_t level_stride, size_t nz, void* stream);
 /* Replaces CachedVectorReprojection::reprojectDirectionValues -> vector_reproject_direction_by_matrix_f
  * (CachedVectorReprojection.cc:50-54, reproject.cc:509-530). */
 int fimexcu_vecrot_direction_f(const fimexcu_vecrot* r, float* angles, size_t size);

@@ -663,3 +663,40 @@ def test_host_vector_result_comes_back_in_row_bands(fx, oracle, rotate, fills):
     assert new.value == n_out and _eq(au, wu) and _eq(av, wv)
     lib.fimexcu_host_free(hu)
     lib.fimexcu_host_free(hv)
+
+
+@pytest.mark.parametrize("pitch_extra", [0, 21, 29])  # dense, rows on 16 bytes (float4 path), odd pitch (scalar path)
+def test_vector_rotation_on_padded_slabs(fx, oracle, pitch_extra):
+    """K7 on slabs with a row pitch: == vector_reproject_values_by_matrix_f on the cells, pad elements untouched"""
+    import torch
+    rng = np.random.default_rng(5 + pitch_extra)
+    ox, oy, nz = 2891 // 7, 131, 11  # 413 columns: not a multiple of four
+    pitch = ox + pitch_extra
+    if pitch_extra == 21:
+        pitch = (ox + 31) // 32 * 32
+    ang = rng.uniform(-np.pi, np.pi, ox * oy)
+    m3 = np.stack([np.cos(ang), np.sin(ang), np.degrees(ang)], axis=1).copy()
+    u = rng.normal(0, 8, (nz, oy, ox)).astype(np.float32)
+    v = rng.normal(0, 8, (nz, oy, ox)).astype(np.float32)
+    u[rng.random(u.shape) < 0.01] = np.nan
+    wu, wv = u.copy(), v.copy()
+    oracle.orc_vector_reproject_values_by_matrix_f(dp(m3), ox * oy, fp(wu), fp(wv), nz)
+    cvr = fx.CachedVectorReprojection(m3, ox, oy)
+    up = torch.full((nz, oy, pitch), 777.0, dtype=torch.float32, device="cuda")
+    vp = torch.full((nz, oy, pitch), 888.0, dtype=torch.float32, device="cuda")
+    up[:, :, :ox] = torch.from_numpy(u).cuda()
+    vp[:, :, :ox] = torch.from_numpy(v).cuda()
+    cvr.reprojectValuesPadded(up, vp)
+    torch.cuda.synchronize()
+    assert _eq(up[:, :, :ox].cpu().numpy(), wu) and _eq(vp[:, :, :ox].cpu().numpy(), wv)
+    assert bool((up[:, :, ox:] == 777.0).all()) and bool((vp[:, :, ox:] == 888.0).all())
+    # a view into a larger allocation that is NOT on a 16-byte boundary: the scalar path must take it
+    big = torch.full((nz * oy * pitch + 3,), 5.0, dtype=torch.float32, device="cuda")
+    uq = big[1:1 + nz * oy * pitch].view(nz, oy, pitch)
+    uq[:, :, :ox] = torch.from_numpy(u).cuda()
+    vq = vp.clone()
+    vq[:, :, :ox] = torch.from_numpy(v).cuda()
+    fx.lib.fimexcu_vecrot_apply_dev_strided_f(cvr._h, uq.data_ptr(), vq.data_ptr(), pitch, oy * pitch, nz, None)
+    torch.cuda.synchronize()
+    assert _eq(uq[:, :, :ox].cpu().numpy(), wu) and _eq(vq[:, :, :ox].cpu().numpy(), wv)
+    assert float(big[0]) == 5.0 and bool((big[-2:] == 5.0).all())
