@@ -392,6 +392,21 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
                                                           f"2030x1354 swath -> {tox}x{toy}, 65 levels; points = source points")
                 del fin65, fout65
             fwd.close()
+    # packed slabs at the ends of a device-resident chain (8(f) rank 1): int16 -> f32 of one source slab, f32 -> int16 of one T1 slab
+    try:
+        from fimex_b200 import packed as PK
+        n_src, n_dst = nz * inx * iny, nz * ox * oy
+        raw16 = torch.randint(-30000, 30000, (n_src,), dtype=torch.int16, device="cuda")
+        f32o = torch.empty((n_src,), dtype=torch.float32, device="cuda")
+        ms = timed(lambda: _lib.check(lib.fimexcu_unpack_dev_f(1, raw16.data_ptr(), n_src, -32767.0, f32o.data_ptr(), stream), "unpack"))
+        out["unpack_i16_source_slab"] = entry(ms, 6.0 * n_src, n_src, "int16 -> f32 (fill -> NaN) of one 949x1069x65 slab: 6 B per value")
+        f32i = torch.randn((n_dst,), dtype=torch.float32, device="cuda") * 1000.0
+        i16o = torch.empty((n_dst,), dtype=torch.int16, device="cuda")
+        ms = timed(lambda: _lib.check(lib.fimexcu_pack_dev_f(1, f32i.data_ptr(), n_dst, -32767.0, i16o.data_ptr(), stream), "pack"))
+        out["pack_i16_target_slab"] = entry(ms, 6.0 * n_dst, n_dst, "f32 -> int16 (NaN -> fill, lround) of one 2891x1021x65 slab: 6 B per value")
+        del raw16, f32o, f32i, i16o
+    except Exception as exc:
+        out["pack_error"] = str(exc)[:200]
     # one-off builds and pre / post-processing of the path (wall clock of the call as a user makes it; no roofline: search- or
     # sweep-bound, not streams)
     def wall(fn, reps=3):

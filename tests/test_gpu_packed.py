@@ -44,6 +44,7 @@ def test_unpack_pack_vs_oracle(P, dtype):
     d_raw = d_raw.cuda().view(td)
     got = P.unpack(d_raw, bad).cpu().numpy()
     assert np.array_equal(got, want, equal_nan=True) and np.isnan(want).any()
+    want_raw = want.copy()
     assert o.orc_unpack_scaled_f(dtype, raw.ctypes.data, n, bad, 0.01, 273.15, fp(want)) == 1
     got = P.unpackScaled(d_raw, bad, 0.01, 273.15).cpu().numpy()
     assert np.array_equal(got, want, equal_nan=True)
@@ -57,6 +58,12 @@ def test_unpack_pack_vs_oracle(P, dtype):
     gotp = P.pack(torch.from_numpy(v).cuda(), td, bad)
     gotp = gotp.view(torch.int16 if T == np.uint16 else torch.int32 if T == np.uint32 else td).cpu().numpy().view(T)
     assert np.array_equal(gotp, wantp)
+    # bases off the 16-byte boundary (a slice of a larger array): the element-by-element path, same answers
+    got1 = P.unpack(d_raw[1:], bad).cpu().numpy()
+    assert np.array_equal(got1, want_raw[1:], equal_nan=True)
+    gotp1 = P.pack(torch.from_numpy(v).cuda()[3:], td, bad)
+    gotp1 = gotp1.view(torch.int16 if T == np.uint16 else torch.int32 if T == np.uint32 else td).cpu().numpy().view(T)
+    assert np.array_equal(gotp1, wantp[3:])
 
 
 def test_packed_vertical_chain_on_device(P):
