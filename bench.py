@@ -404,7 +404,12 @@ def secondary_kernels(S, ci, px, py, ox, oy, peak):
         i16o = torch.empty((n_dst,), dtype=torch.int16, device="cuda")
         ms = timed(lambda: _lib.check(lib.fimexcu_pack_dev_f(1, f32i.data_ptr(), n_dst, -32767.0, i16o.data_ptr(), stream), "pack"))
         out["pack_i16_target_slab"] = entry(ms, 6.0 * n_dst, n_dst, "f32 -> int16 (NaN -> fill, lround) of one 2891x1021x65 slab: 6 B per value")
-        del raw16, f32o, f32i, i16o
+        # CDMTimeInterpolator between two resident T1 slabs (8(f) rank 4): A + f * (B - A), 12 B per value
+        f32b = torch.randn((n_dst,), dtype=torch.float32, device="cuda")
+        f32c = torch.empty((n_dst,), dtype=torch.float32, device="cuda")
+        ms = timed(lambda: _lib.check(lib.fimexcu_get_values_two_level_dev_f(4, f32i.data_ptr(), f32b.data_ptr(), f32c.data_ptr(), n_dst, 0.0, 3.0, 1.0, stream), "blend"))
+        out["time_blend_two_target_slabs"] = entry(ms, 12.0 * n_dst, n_dst, "linear_weak_extrapol between two 2891x1021x65 slabs: 12 B per value")
+        del raw16, f32o, f32i, i16o, f32b, f32c
     except Exception as exc:
         out["pack_error"] = str(exc)[:200]
     # one-off builds and pre / post-processing of the path (wall clock of the call as a user makes it; no roofline: search- or

@@ -1632,9 +1632,18 @@ static double host_level_log(int method, double x)
 static float narrow_or_nan(double v) { return std::isnan(v) ? std::numeric_limits<float>::quiet_NaN() : static_cast<float>(v); }
 
 // ---- two-level kernels on whole fields (interpolation.c:416-546) ----
-__global__ void __launch_bounds__(256) lin_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ out, size_t n, float f)
+// VEC (all three arrays on 16 bytes): four values per thread and access; `out` may be A (in place: a thread reads its values
+// before it writes them, and nobody else touches them)
+template <bool VEC>
+__global__ void __launch_bounds__(256) lin_kernel(const float* A, const float* B, float* out, size_t n, float f)
 {
-    for (size_t i = blockIdx.x * 256ull + threadIdx.x; i < n; i += 256ull * gridDim.x)
+    const size_t nv = VEC ? n / 4 : 0;
+    for (size_t k = blockIdx.x * 256ull + threadIdx.x; k < nv; k += 256ull * gridDim.x) {
+        const float4 a = reinterpret_cast<const float4*>(A)[k], b = reinterpret_cast<const float4*>(B)[k];
+        reinterpret_cast<float4*>(out)[k] = make_float4(__fadd_rn(a.x, __fmul_rn(f, __fsub_rn(b.x, a.x))), __fadd_rn(a.y, __fmul_rn(f, __fsub_rn(b.y, a.y))),
+                                                        __fadd_rn(a.z, __fmul_rn(f, __fsub_rn(b.z, a.z))), __fadd_rn(a.w, __fmul_rn(f, __fsub_rn(b.w, a.w))));
+    }
+    for (size_t i = nv * 4 + blockIdx.x * 256ull + threadIdx.x; i < n; i += 256ull * gridDim.x)
         out[i] = __fadd_rn(A[i], __fmul_rn(f, __fsub_rn(B[i], A[i])));
 }
 
@@ -1669,7 +1678,12 @@ static int two_level_dev(int kind, const float* dA, const float* dB, float* dO, 
         if (dO != dB)
             FXCU_CUDA(cudaMemcpyAsync(dO, dB, bytes, cudaMemcpyDeviceToDevice, s));
         break;
-    case 2: lin_kernel<<<blocks, 256, 0, s>>>(dA, dB, dO, n, f); break;
+    case 2:
+        if (((reinterpret_cast<uintptr_t>(dA) | reinterpret_cast<uintptr_t>(dB) | reinterpret_cast<uintptr_t>(dO)) & 15u) == 0)
+            lin_kernel<true><<<std::max(1u, (blocks + 3) / 4), 256, 0, s>>>(dA, dB, dO, n, f);
+        else
+            lin_kernel<false><<<blocks, 256, 0, s>>>(dA, dB, dO, n, f);
+        break;
     default: FXCU_CUDA(cudaMemsetAsync(dO, 0xff, bytes, s)); break; // all-ones is a quiet NaN
     }
     FXCU_CUDA(cudaGetLastError());

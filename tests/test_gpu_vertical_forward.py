@@ -424,6 +424,12 @@ def test_two_level_kernels_on_device_slabs(fx, oracle, name, method):
     _lib.check(_lib.lib.fimexcu_get_values_two_level_dev_f(method, dC.data_ptr(), dB.data_ptr(), dC.data_ptr(), n, 3.0, 9.0, 4.5, _lib.current_stream_ptr()), "x")
     torch.cuda.synchronize()
     assert _eq(dC.cpu().numpy(), want)
+    # slabs that do not start on a 16-byte boundary (views into larger arrays): the element-by-element path
+    A1, B1, want1 = A[1:].copy(), B[1:].copy(), np.empty(n - 1, np.float32)
+    fn(fp(A1), fp(B1), fp(want1), n - 1, 3.0, 9.0, 4.5)
+    got = timeInterpolateSlabs(dA[1:], dB[1:], 3.0, 9.0, 4.5, method=method)
+    torch.cuda.synchronize()
+    assert _eq(got.cpu().numpy(), want1)
 
 
 def test_config5_full_size_properties(fx):
