@@ -277,7 +277,7 @@ int fimexcu_points2position_dev_noalloc(double* d_points, size_t n, const double
 /* Replaces reproject::reproject_axes (include/fimex/reproject.h:211-227, src/reproject.cc:573-587): broadcast the
  * 1-D axes to an ix*iy lattice and transform proj_input -> proj_output (proj4 strings; degrees for geographic
  * CRS as with PROJ >= 6).  Points that cannot be projected become +inf.
- * Understood: every projection fimex's Projection classes emit (src/coordSys/*Projection.cc) -- longlat, lcc, stere / ups,
+ * Understood: every projection fimex's Projection classes emit (src/coordSys/ ...Projection.cc) -- longlat, lcc, stere / ups,
  * ob_tran over longlat, merc, tmerc / utm, laea, aea, aeqd, cea, ortho, sinu, nsper, geos, omerc -- on a sphere or an
  * ellipsoid (+R | +a +b/+rf/+es | +ellps | +datum=WGS84), without datum shifts.  A string that asks for anything else
  * (+towgs84 other than zero, +nadgrids, +pm, +axis, another projection, oblique aeqd or ortho on an ellipsoid, the two-point
