@@ -65,14 +65,15 @@ __global__ void __launch_bounds__(256) unpack_kernel(const T* __restrict__ in, s
 {
     typedef typename Word<4 * sizeof(T)>::type W;
     const size_t nv = VEC ? n / 4 : 0;
-    for (size_t k = blockIdx.x * 256ull + threadIdx.x; k < nv; k += 256ull * gridDim.x) {
-        union {
-            W q;
-            T e[4];
-        } a;
-        a.q = __ldcs(reinterpret_cast<const W*>(in) + k);
-        reinterpret_cast<float4*>(out)[k] = make_float4(f(a.e[0]), f(a.e[1]), f(a.e[2]), f(a.e[3]));
-    }
+    if constexpr (VEC)
+        for (size_t k = blockIdx.x * 256ull + threadIdx.x; k < nv; k += 256ull * gridDim.x) {
+            union {
+                W q;
+                T e[4];
+            } a;
+            a.q = __ldcs(reinterpret_cast<const W*>(in) + k);
+            reinterpret_cast<float4*>(out)[k] = make_float4(f(a.e[0]), f(a.e[1]), f(a.e[2]), f(a.e[3]));
+        }
     for (size_t i = nv * 4 + blockIdx.x * 256ull + threadIdx.x; i < n; i += 256ull * gridDim.x)
         out[i] = f(in[i]);
 }
@@ -83,18 +84,19 @@ __global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ in,
 {
     typedef typename Word<4 * sizeof(T)>::type W;
     const size_t nv = VEC ? n / 4 : 0;
-    for (size_t k = blockIdx.x * 256ull + threadIdx.x; k < nv; k += 256ull * gridDim.x) {
-        union {
-            W q;
-            T e[4];
-        } a;
-        const float4 v = __ldcs(reinterpret_cast<const float4*>(in) + k);
-        a.e[0] = f(v.x);
-        a.e[1] = f(v.y);
-        a.e[2] = f(v.z);
-        a.e[3] = f(v.w);
-        reinterpret_cast<W*>(out)[k] = a.q;
-    }
+    if constexpr (VEC)
+        for (size_t k = blockIdx.x * 256ull + threadIdx.x; k < nv; k += 256ull * gridDim.x) {
+            union {
+                W q;
+                T e[4];
+            } a;
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(in) + k);
+            a.e[0] = f(v.x);
+            a.e[1] = f(v.y);
+            a.e[2] = f(v.z);
+            a.e[3] = f(v.w);
+            reinterpret_cast<W*>(out)[k] = a.q;
+        }
     for (size_t i = nv * 4 + blockIdx.x * 256ull + threadIdx.x; i < n; i += 256ull * gridDim.x)
         out[i] = f(in[i]);
 }

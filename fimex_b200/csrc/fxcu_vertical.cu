@@ -630,7 +630,6 @@ __device__ __forceinline__ void column_by_general_scan(const VertParams& P, cons
 // step.  Shared memory: hybrid (ap, b) pairs, the level list (f64, log, f32 with a NaN sentinel either side), notes [nzo][VT] u16.
 constexpr int LG = 4; // target levels handled together in straight-line code (their 2 * LG gathers are in flight at once)
 constexpr int CH = 4;
-constexpr int SJC = 8; // explicit coordinate: target levels per gather batch
 
 template <bool HYBRID, int METHOD = -1> // METHOD >= 0 (explicit coordinate only): the interpolation method as a compile-time constant
 __global__ void __launch_bounds__(VT, 8) vertical_sweep_kernel(const VertParams P)
@@ -1232,7 +1231,6 @@ __global__ void __launch_bounds__(256) hybrid_table_kernel(const double* __restr
 
 constexpr int HT = 128;       // threads (columns) per block of the table kernel's consumer
 constexpr int HT_CHUNKS = 4;  // runs of HT columns one block works through with the same staged tables
-constexpr int MAX_ADJUST = 6; // corrections of a looked-up count before the general search takes over
 constexpr unsigned CODE_NAN = 0u, CODE_BLEND = 1u << 14, CODE_SLOW = 2u << 14, CODE_UP = 1u << 13; // | first (13 bits)
 
 // what value_from_step() decides, without fetching anything: NaN / general search / blend(first, first +- 1)
@@ -1638,11 +1636,12 @@ template <bool VEC>
 __global__ void __launch_bounds__(256) lin_kernel(const float* A, const float* B, float* out, size_t n, float f)
 {
     const size_t nv = VEC ? n / 4 : 0;
-    for (size_t k = blockIdx.x * 256ull + threadIdx.x; k < nv; k += 256ull * gridDim.x) {
-        const float4 a = reinterpret_cast<const float4*>(A)[k], b = reinterpret_cast<const float4*>(B)[k];
-        reinterpret_cast<float4*>(out)[k] = make_float4(__fadd_rn(a.x, __fmul_rn(f, __fsub_rn(b.x, a.x))), __fadd_rn(a.y, __fmul_rn(f, __fsub_rn(b.y, a.y))),
-                                                        __fadd_rn(a.z, __fmul_rn(f, __fsub_rn(b.z, a.z))), __fadd_rn(a.w, __fmul_rn(f, __fsub_rn(b.w, a.w))));
-    }
+    if constexpr (VEC)
+        for (size_t k = blockIdx.x * 256ull + threadIdx.x; k < nv; k += 256ull * gridDim.x) {
+            const float4 a = reinterpret_cast<const float4*>(A)[k], b = reinterpret_cast<const float4*>(B)[k];
+            reinterpret_cast<float4*>(out)[k] = make_float4(__fadd_rn(a.x, __fmul_rn(f, __fsub_rn(b.x, a.x))), __fadd_rn(a.y, __fmul_rn(f, __fsub_rn(b.y, a.y))),
+                                                            __fadd_rn(a.z, __fmul_rn(f, __fsub_rn(b.z, a.z))), __fadd_rn(a.w, __fmul_rn(f, __fsub_rn(b.w, a.w))));
+        }
     for (size_t i = nv * 4 + blockIdx.x * 256ull + threadIdx.x; i < n; i += 256ull * gridDim.x)
         out[i] = __fadd_rn(A[i], __fmul_rn(f, __fsub_rn(B[i], A[i])));
 }
