@@ -1533,8 +1533,15 @@ static bool make_source_map(CUtensorMap* m, const float* d_in, size_t inX, size_
     cuuint64_t strides[2] = {static_cast<cuuint64_t>(inPitch) * 4, static_cast<cuuint64_t>(inLevel) * 4};
     cuuint32_t box[3] = {TMA_BW, static_cast<cuuint32_t>(height), static_cast<cuuint32_t>(depth)};
     cuuint32_t es[3] = {1, 1, 1};
+    // L2 promotion of the box rows: 256 B measured 0.7 % faster than 128 B or none on S->T1 (0.2097 against 0.2112 ms), 64 B 3 % slower
+    // (profiles/exp/l2promo_ab.sh); FIMEXCU_TMA_L2PROMO = 0 / 1 / 2 / 3 selects none / 64 / 128 / 256 B (read once)
+    static const CUtensorMapL2promotion promo = []() {
+        const char* e = getenv("FIMEXCU_TMA_L2PROMO");
+        const int v = e ? atoi(e) : 3;
+        return v == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE : v == 1 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : v == 3 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+    }();
     return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(d_in), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+               CU_TENSOR_MAP_SWIZZLE_NONE, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 // A/B switch between the staged (TMA) and the direct-gather kernels: the environment variable
